@@ -1,0 +1,146 @@
+#!/usr/bin/env python
+"""Regenerate the golden fixtures in this directory FROM THE REFERENCE ITSELF.
+
+Run in the build container only (it imports ``/root/reference``, which does not exist on the
+GPU box):
+
+    python tests/golden/make_golden.py
+
+For every case it builds the unmodified ``AssetPricingGAN`` (``src/model.py:298``) under
+``torch.manual_seed``, puts it in ``eval()`` (dropout disabled, as every parity comparison
+requires), runs ``forward`` + ``loss.backward()`` for the three phases exactly as
+``train_epoch`` does (``src/train.py:77-84``; phase 2 with the SDF net frozen as at
+``src/train.py:309-312``), plus ``get_weights(normalized=True)`` (``src/model.py:565``), and
+stores inputs, parameters and every output as float32 ``.npz``.
+
+Cases
+  rand_small    T=12, N=37 (odd), 178 macros: one empty month, one never-valid stock.
+  shipped_sub   the shipped seed-42 panel through ``AssetPricingDataset`` (all 120 months,
+                96 of its 500 stocks, 8 macros) -- exercises the loader's mask contract.
+  shipped_valid the shipped validation split (30 months, 160 stocks incl. never-valid ones),
+                macro z-scored with TRAIN statistics (``src/train.py:485-497``), non-zero
+                initial LSTM state.
+  mask_raw      raw returns/features with -99.99 sentinels and NaNs -> mask, zero-filled
+                arrays (``src/data_loader.py:50-65``).  Bit-exact contract.
+  anchors       scalars of the full shipped training panel.
+"""
+import json
+import os
+import sys
+
+import numpy as np
+import torch
+
+REF = os.environ.get("DLAP_REFERENCE", "/root/reference")
+sys.path.insert(0, REF)
+from src.model import AssetPricingGAN  # noqa: E402
+from src.data_loader import AssetPricingDataset  # noqa: E402
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+PHASES = ("unconditional", "moment", "conditional")
+
+
+def run_case(name, macro, x, R, mask, seed, hidden=None):
+    cfg = {"macro_feature_dim": int(macro.shape[1]), "individual_feature_dim": int(x.shape[2])}
+    torch.manual_seed(seed)
+    model = AssetPricingGAN(cfg)
+    model.eval()
+    blob = {"macro": macro.numpy(), "x": x.numpy(), "R": R.numpy(), "mask": mask.numpy(),
+            "seed": np.int64(seed)}
+    if hidden is not None:
+        blob["h0"] = hidden[0].numpy(); blob["c0"] = hidden[1].numpy()
+    for k, v in model.state_dict().items():
+        blob["param/" + k] = v.numpy().copy()
+    for phase in PHASES:
+        model.zero_grad(set_to_none=True)
+        frozen = phase == "moment"
+        for prm in model.sdf_net.parameters():
+            prm.requires_grad = not frozen
+        out = model(macro, x, R, mask, hidden=hidden, phase=phase)
+        out["loss"].backward()
+        for key in ("weights", "loss", "loss_unconditional", "loss_conditional", "sharpe",
+                    "portfolio_returns"):
+            blob[f"{phase}/{key}"] = out[key].detach().numpy().copy()
+        blob[f"{phase}/hidden_h"] = out["hidden"][0].detach().numpy().copy()
+        blob[f"{phase}/hidden_c"] = out["hidden"][1].detach().numpy().copy()
+        if phase == "conditional":
+            blob["moments"] = out["moments"].detach().contiguous().numpy().copy()
+        for k, prm in model.named_parameters():
+            if prm.grad is not None:
+                blob[f"{phase}/grad/{k}"] = prm.grad.numpy().copy()
+    for prm in model.sdf_net.parameters():
+        prm.requires_grad = True
+    with torch.no_grad():
+        wn, _ = model.get_weights(macro, x, mask, hidden=hidden, normalized=True)
+        blob["normalized_weights"] = wn.numpy().copy()
+        blob["sdf_factor"] = model.get_sdf_factor(macro, x, R, mask, hidden=hidden).numpy().copy()
+    path = os.path.join(HERE, name + ".npz")
+    np.savez_compressed(path, **blob)
+    print(f"{name}: T={x.shape[0]} N={x.shape[1]} M={macro.shape[1]} "
+          f"valid={int(mask.sum())} -> {os.path.getsize(path) / 1024:.0f} KiB")
+
+
+def rand_small():
+    g = torch.Generator().manual_seed(1234)
+    T, N, F, M = 12, 37, 46, 178
+    mask = torch.rand(T, N, generator=g) < 0.4
+    mask[3, :] = False          # empty month  -> clamp(min=1) on N_t
+    mask[:, 5] = False          # dead stock   -> clamp(min=1) on T_i, still in the /N mean
+    x = torch.randn(T, N, F, generator=g).clamp_(-2, 2) * mask[:, :, None]
+    R = 0.1 * torch.randn(T, N, generator=g) * mask
+    macro = torch.randn(T, M, generator=g)
+    run_case("rand_small", macro, x, R, mask, seed=42)
+
+
+def shipped():
+    d = os.path.join(REF, "data", "synthetic_data")
+    tr = AssetPricingDataset(os.path.join(d, "char", "Char_train.npz"),
+                             os.path.join(d, "macro", "macro_train.npz"))
+    b = tr.get_full_batch()
+    keep = np.arange(0, 480, 5)     # 96 stocks spread over the panel
+    run_case("shipped_sub", b["macro_features"], b["individual_features"][:, keep].contiguous(),
+             b["returns"][:, keep].contiguous(), b["mask"][:, keep].contiguous(), seed=7)
+    mean, std = tr.get_macro_stats()
+    va = AssetPricingDataset(os.path.join(d, "char", "Char_valid.npz"),
+                             os.path.join(d, "macro", "macro_valid.npz"),
+                             mean_macro=mean, std_macro=std)
+    vb = va.get_full_batch()
+    keep = np.arange(0, 480, 3)
+    g = torch.Generator().manual_seed(5)
+    hidden = (0.3 * torch.randn(1, 1, 4, generator=g), 0.3 * torch.randn(1, 1, 4, generator=g))
+    run_case("shipped_valid", vb["macro_features"],
+             vb["individual_features"][:, keep].contiguous(), vb["returns"][:, keep].contiguous(),
+             vb["mask"][:, keep].contiguous(), seed=11, hidden=hidden)
+    # anchors on the full training panel
+    torch.manual_seed(42)
+    model = AssetPricingGAN({"macro_feature_dim": 8, "individual_feature_dim": 46}).eval()
+    out = model(b["macro_features"], b["individual_features"], b["returns"], b["mask"])
+    anchors = {"loss_unconditional": float(out["loss_unconditional"]),
+               "loss_conditional": float(out["loss_conditional"]),
+               "sharpe": float(out["sharpe"]),
+               "portfolio_returns_head": [float(v) for v in out["portfolio_returns"][:3]],
+               "abs_weight_sum": float(out["weights"].abs().sum()),
+               "mask_sum": int(b["mask"].sum()),
+               "torch": torch.__version__}
+    with open(os.path.join(HERE, "anchors_shipped_train.json"), "w") as f:
+        json.dump(anchors, f, indent=1)
+    print("anchors:", anchors)
+    # raw mask contract: a slab of the raw file with NaNs injected
+    raw = np.load(os.path.join(d, "char", "Char_train.npz"))["data"][:16, :64].astype(np.float32)
+    raw = raw.copy()
+    raw[2, 3, 0] = np.nan          # NaN return
+    raw[4, 7, 9] = np.nan          # NaN feature (fails the '>' test)
+    raw[5, 1, 0] = -98.99          # exactly on the threshold (not valid: strict '>')
+    raw[6, 2, 4] = -98.98
+    tmp = "/tmp/_dlap_mask_raw.npz"
+    np.savez(tmp, data=raw)
+    ds = AssetPricingDataset(tmp)
+    np.savez_compressed(os.path.join(HERE, "mask_raw.npz"), raw=raw, mask=ds.mask,
+                        returns=ds.returns, features=ds.individual_features)
+    print("mask_raw: valid", int(ds.mask.sum()), "of", ds.mask.size)
+
+
+if __name__ == "__main__":
+    torch.set_num_threads(1)        # bit-reproducible regardless of the host
+    rand_small()
+    shipped()
