@@ -1,0 +1,4 @@
+"""B200-native adversarial-SDF training step (drop-in for the reference's ``src.model``)."""
+from .model import AssetPricingGAN, MacroLSTM, MomentNetwork, SDFNetwork  # noqa: F401
+
+__all__ = ["AssetPricingGAN", "SDFNetwork", "MomentNetwork", "MacroLSTM"]

@@ -1,0 +1,128 @@
+"""ctypes binding of ``libdlap_b200.so`` (C ABI declared in ``include/dlap.h``).
+
+The library is built in-tree by ``build()`` (``nvcc -gencode arch=compute_100a,code=sm_100a``)
+and loaded with ``ctypes.CDLL``.  There is no fallback of any kind: if the shared object is
+missing, or a call returns a non-zero status, a ``RuntimeError`` is raised.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import shutil
+import subprocess
+import threading
+
+PKG_DIR = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(PKG_DIR)
+CSRC = os.path.join(PKG_DIR, "csrc")
+LIB_PATH = os.path.join(PKG_DIR, "libdlap_b200.so")
+SOURCES = ("capi.cu", "cell_fwd.cu", "cell_bwd.cu", "reduce.cu", "macro_lstm.cu")
+NVCC_FLAGS = ("-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
+              "-shared", "-Xcompiler", "-fPIC")
+
+DLAP_PREC_FP32 = 0
+
+
+class DlapDims(C.Structure):
+    _fields_ = [("T", C.c_int32), ("N", C.c_int32), ("F", C.c_int32), ("M", C.c_int32),
+                ("H", C.c_int32)]
+
+
+class DlapPlan(C.Structure):
+    _fields_ = [("dims", DlapDims), ("tpm", C.c_int32), ("grid_cell", C.c_int32),
+                ("col_splits", C.c_int32), ("row_splits", C.c_int32), ("ldw1", C.c_int32),
+                ("ldwq", C.c_int32), ("row_part_bytes", C.c_int64), ("col_part_bytes", C.c_int64),
+                ("loss_part_bytes", C.c_int64), ("ds_part_bytes", C.c_int64),
+                ("wpart_bytes", C.c_int64), ("dadc_part_bytes", C.c_int64),
+                ("lstm_save_bytes", C.c_int64), ("dpre_bytes", C.c_int64)]
+
+
+class DlapTensors(C.Structure):
+    """Twelve device pointers in the reference's state_dict order."""
+    FIELDS = ("w_ih", "w_hh", "b_ih", "b_hh", "w1", "b1", "w2", "b2", "w3", "b3", "wq", "bq")
+    _fields_ = [(n, C.c_void_p) for n in FIELDS]
+
+
+_P = C.c_void_p
+_PLAN = C.POINTER(DlapPlan)
+_TENS = C.POINTER(DlapTensors)
+_I = C.c_int
+
+# name -> argtypes; every function returns int status (except the two introspection calls)
+SIGNATURES = {
+    "dlap_make_plan": (C.POINTER(DlapDims), _I, _PLAN),
+    "dlap_macro_fwd": (_PLAN, _P, _TENS, _P, _P, _P, _P, _P, _P, _P, _P),
+    "dlap_cell_fwd": (_PLAN, _P, _P, _P, _TENS, _P, _P, _P, _P, _P, _I, C.c_float, C.c_uint64, _P),
+    "dlap_row_finish": (_PLAN, _P, _I, _P, _P, _P, _P, _P),
+    "dlap_col_partial": (_PLAN, _P, _P, _P, _P, _P, _P, _P, _P),
+    "dlap_loss_finish": (_PLAN, _P, _I, _P, _P, _P, _P, _P, _P),
+    "dlap_loss_coeff": (_PLAN, _P, _P, _P, _P, _P, _P),
+    "dlap_ds_rows": (_PLAN, _P, _P, _P, _P, _P, _P),
+    "dlap_cell_bwd": (_PLAN, _P, _P, _P, _TENS, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _P, _P, _I,
+                      C.c_float, C.c_uint64, _P),
+    "dlap_grad_finish": (_PLAN, _P, _P, _I, _I, _TENS, _P, _P),
+    "dlap_macro_bwd": (_PLAN, _P, _TENS, _P, _P, _P, _P, _P, _I, _I, _TENS, _P),
+    "dlap_weights": (_PLAN, _P, _P, _P, _I, _P, _P),
+}
+EXPORTS = ("dlap_abi_version", "dlap_error_string") + tuple(SIGNATURES)
+
+_lock = threading.Lock()
+_lib = None
+
+
+def _needs_build() -> bool:
+    if not os.path.exists(LIB_PATH):
+        return True
+    t = os.path.getmtime(LIB_PATH)
+    deps = [os.path.join(CSRC, f) for f in os.listdir(CSRC)] + [os.path.join(ROOT, "include", "dlap.h")]
+    return any(os.path.getmtime(d) > t for d in deps if os.path.isfile(d))
+
+
+def build(force: bool = False, verbose: bool = False) -> str:
+    """Compile every CUDA source for sm_100a into the in-tree shared library."""
+    if not force and not _needs_build():
+        return LIB_PATH
+    nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
+    if not os.path.exists(nvcc):
+        raise RuntimeError("nvcc not found: cannot build libdlap_b200.so")
+    cmd = [nvcc, *NVCC_FLAGS, "-o", LIB_PATH, *[os.path.join(CSRC, s) for s in SOURCES]]
+    if verbose:
+        cmd.insert(1, "-Xptxas=-v")
+    res = subprocess.run(cmd, capture_output=True, text=True)
+    if res.returncode != 0:
+        raise RuntimeError("nvcc failed:\n" + res.stdout + res.stderr)
+    if verbose:
+        print(res.stderr)
+    return LIB_PATH
+
+
+def load():
+    """The loaded library, with argtypes set.  Raises if it has not been built."""
+    global _lib
+    with _lock:
+        if _lib is not None:
+            return _lib
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(
+                f"{LIB_PATH} is missing: the CUDA library has not been built "
+                "(run `python -c 'import __graft_entry__ as g; g.build()'`). There is no CPU fallback.")
+        lib = C.CDLL(LIB_PATH)
+        lib.dlap_abi_version.restype = C.c_int
+        lib.dlap_error_string.restype = C.c_char_p
+        lib.dlap_error_string.argtypes = (C.c_int,)
+        for name, argt in SIGNATURES.items():
+            fn = getattr(lib, name)
+            fn.argtypes = argt
+            fn.restype = C.c_int
+        _lib = lib
+        return lib
+
+
+def check(rc: int, what: str) -> None:
+    if rc != 0:
+        msg = load().dlap_error_string(rc).decode()
+        raise RuntimeError(f"{what} failed with status {rc}: {msg}")
+
+
+def call(name: str, *args) -> None:
+    check(getattr(load(), name)(*args), name)

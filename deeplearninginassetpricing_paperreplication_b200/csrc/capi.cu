@@ -1,0 +1,282 @@
+// extern "C" surface of libdlap_b200.so (declared in include/dlap.h): argument checks and
+// kernel launches only.  No allocation, no synchronisation, no torch types.
+#include "../../include/dlap.h"
+#include "cell_f32.cuh"
+
+namespace dlap {
+// launchers implemented next to their kernels
+struct MacroParams;
+cudaError_t launch_cell_fwd_f32(const CellParams& P, int grid, cudaStream_t st);
+cudaError_t launch_cell_bwd_f32(const CellParams& P, int grid, bool sdf, bool mom, cudaStream_t st);
+size_t smem_bwd_bytes(int F);
+cudaError_t launch_row_finish(const double*, int, int, int, const float*, float*, float*, float*, cudaStream_t);
+cudaError_t launch_col_partial(const float*, const float*, const uint8_t*, const float*, const float*, int, int,
+                               int, double*, float*, cudaStream_t);
+cudaError_t launch_loss_finish(const double*, int, int, int, float*, float*, double*, unsigned int*, float*,
+                               cudaStream_t);
+cudaError_t launch_coeff(const float*, const float*, int, const float*, const float*, float*, cudaStream_t);
+cudaError_t launch_ds_rows(const float*, const float*, const uint8_t*, const float*, int, int, int, double*,
+                           cudaStream_t);
+cudaError_t launch_grad_finish(const float*, int, int, int, int, const float*, int, int, float*, int, float*,
+                               float*, float*, float*, float*, int, int, float*, cudaStream_t);
+cudaError_t launch_weights(const float*, const uint8_t*, const float*, int, int, int, float*, cudaStream_t);
+cudaError_t launch_macro_fwd_c(const dlap_plan* plan, const float* macro, const dlap_tensors* p, const float* h0,
+                               const float* c0, float* save, float* a_t, float* c_t, float* hn, float* cn,
+                               cudaStream_t st);
+cudaError_t launch_macro_bwd_c(const dlap_plan* plan, const float* macro, const dlap_tensors* p, const float* h0,
+                               const float* c0, const float* save, const float* dadc, float* dpre, int want_sdf,
+                               int want_mom, const dlap_tensors* g, cudaStream_t st);
+size_t macro_fwd_smem(int T, int M, int H);
+}  // namespace dlap
+
+using namespace dlap;
+
+#define REQ(p) do { if (!(p)) return DLAP_E_NULL; } while (0)
+#define CU(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return (int)e_; } while (0)
+
+static int check_dims(const dlap_dims& d) {
+  if (d.T < 1 || d.N < 1 || d.F < 1 || d.F > FMAX) return DLAP_E_SHAPE;
+  if (d.M < 0 || (d.M > 0 && (d.H < 1 || d.H > HMAX))) return DLAP_E_SHAPE;
+  if ((long long)d.T * d.N >= (1ll << 40)) return DLAP_E_SHAPE;
+  return DLAP_OK;
+}
+
+static int check_plan(const dlap_plan* p) {
+  REQ(p);
+  int rc = check_dims(p->dims);
+  if (rc) return rc;
+  if (p->tpm != (p->dims.N + TILE - 1) / TILE || p->grid_cell < 1 || p->col_splits < 1 || p->row_splits < 1)
+    return DLAP_E_PLAN;
+  return DLAP_OK;
+}
+
+extern "C" {
+
+int dlap_abi_version(void) { return DLAP_ABI_VERSION; }
+
+const char* dlap_error_string(int code) {
+  switch (code) {
+    case DLAP_OK: return "ok";
+    case DLAP_E_NULL: return "required pointer is NULL";
+    case DLAP_E_SHAPE: return "dimension outside the supported range (F<=64, H<=8, T,N>=1)";
+    case DLAP_E_ALIGN: return "pointer alignment";
+    case DLAP_E_PLAN: return "plan does not match the dims";
+    case DLAP_E_PRECISION: return "unknown precision selector";
+    case DLAP_E_NODEVICE: return "no usable CUDA device";
+    case DLAP_E_SMEM: return "configuration needs more shared memory than an SM offers";
+    default: return code > 0 ? cudaGetErrorString((cudaError_t)code) : "unknown dlap error";
+  }
+}
+
+int dlap_make_plan(const dlap_dims* dims, int device, dlap_plan* out) {
+  REQ(dims); REQ(out);
+  int rc = check_dims(*dims);
+  if (rc) return rc;
+  int sms = 0, smem_max = 0;
+  if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device) != cudaSuccess || sms < 1) {
+    cudaGetLastError();
+    return DLAP_E_NODEVICE;
+  }
+  CU(cudaDeviceGetAttribute(&smem_max, cudaDevAttrMaxSharedMemoryPerBlockOptin, device));
+  if ((size_t)smem_max < smem_bwd_bytes(dims->F)) return DLAP_E_SMEM;
+  if (dims->M > 0 && (size_t)smem_max < macro_fwd_smem(dims->T, dims->M, dims->H)) return DLAP_E_SMEM;
+  dlap_plan p;
+  p.dims = *dims;
+  const int T = dims->T, N = dims->N, F = dims->F;
+  p.tpm = (N + TILE - 1) / TILE;
+  const long long ntiles = (long long)T * p.tpm;
+  p.grid_cell = (int)(ntiles < sms ? ntiles : sms);
+  // reductions: aim for ~4 CTAs per SM
+  const int nb = (N + 255) / 256, want = 4 * sms;
+  int cs = (want + nb - 1) / nb; if (cs > T) cs = T; if (cs < 1) cs = 1;
+  p.col_splits = cs;
+  int rs = (want + T - 1) / T; if (rs > nb) rs = nb; if (rs < 1) rs = 1;
+  p.row_splits = rs;
+  p.ldw1 = F + (dims->M > 0 ? dims->H : 0);
+  p.ldwq = dims->M + F;
+  p.row_part_bytes = (int64_t)T * p.tpm * 4 * 8;
+  p.col_part_bytes = (int64_t)p.col_splits * (KM + 2) * N * 8;
+  p.loss_part_bytes = (int64_t)nb * 2 * 8;
+  p.ds_part_bytes = (int64_t)T * p.row_splits * 8;
+  p.wpart_bytes = (int64_t)p.grid_cell * wp_stride(round4(F)) * 4;
+  p.dadc_part_bytes = (int64_t)T * p.tpm * 72 * 4;
+  p.lstm_save_bytes = (int64_t)T * 6 * (dims->H > 0 ? dims->H : 1) * 4;
+  p.dpre_bytes = (int64_t)T * 4 * (dims->H > 0 ? dims->H : 1) * 4;
+  *out = p;
+  return DLAP_OK;
+}
+
+static void fill_cell(CellParams& P, const dlap_plan* plan, const float* x, const float* R, const uint8_t* mask,
+                      const dlap_tensors* w, const float* a_t, const float* c_t) {
+  const dlap_dims& d = plan->dims;
+  P = CellParams{};
+  P.x = x; P.R = R; P.mask = mask;
+  P.T = d.T; P.N = d.N; P.F = d.F;
+  P.x_bytes = (long long)d.T * d.N * d.F * 4;
+  P.W1 = w->w1; P.ldw1 = plan->ldw1; P.W2 = w->w2; P.b2 = w->b2; P.W3 = w->w3; P.b3 = w->b3;
+  P.Wq = w->wq; P.ldwq = plan->ldwq; P.wq_off = d.M;
+  P.a_t = a_t; P.c_t = c_t;
+  P.tpm = plan->tpm;
+}
+
+static int set_dropout(CellParams& P, float p, uint64_t seed) {
+  if (!(p >= 0.f) || p >= 1.f) return DLAP_E_SHAPE;
+  uint32_t thr = (uint32_t)(p * 65536.f + 0.5f);
+  if (thr > 65535u) thr = 65535u;
+  P.drop_thr = thr;
+  P.drop_scale = thr ? 65536.f / (float)(65536u - thr) : 1.f;
+  P.seed_lo = (uint32_t)seed;
+  P.seed_hi = (uint32_t)(seed >> 32);
+  return DLAP_OK;
+}
+
+int dlap_macro_fwd(const dlap_plan* plan, const float* macro, const dlap_tensors* params, const float* h0,
+                   const float* c0, float* lstm_save, float* a_t, float* c_t, float* hn, float* cn,
+                   void* stream) {
+  int rc = check_plan(plan);
+  if (rc) return rc;
+  REQ(params); REQ(a_t); REQ(c_t); REQ(params->b1); REQ(params->bq);
+  if (plan->dims.M > 0) {
+    REQ(macro); REQ(lstm_save); REQ(hn); REQ(cn);
+    REQ(params->w_ih); REQ(params->w_hh); REQ(params->b_ih); REQ(params->b_hh); REQ(params->w1); REQ(params->wq);
+  }
+  CU(launch_macro_fwd_c(plan, macro, params, h0, c0, lstm_save, a_t, c_t, hn, cn, (cudaStream_t)stream));
+  return DLAP_OK;
+}
+
+int dlap_cell_fwd(const dlap_plan* plan, const float* x, const float* R, const uint8_t* mask,
+                  const dlap_tensors* params, const float* a_t, const float* c_t, float* u, float* g,
+                  double* row_part, int precision, float dropout_p, uint64_t dropout_seed, void* stream) {
+  int rc = check_plan(plan);
+  if (rc) return rc;
+  REQ(x); REQ(mask); REQ(params); REQ(a_t); REQ(u); REQ(row_part);
+  REQ(params->w1); REQ(params->w2); REQ(params->b2); REQ(params->w3); REQ(params->b3);
+  if (g) { REQ(c_t); REQ(params->wq); }
+  if (reinterpret_cast<uintptr_t>(x) & 3) return DLAP_E_ALIGN;
+  if (precision != DLAP_PREC_FP32) return DLAP_E_PRECISION;
+  CellParams P;
+  fill_cell(P, plan, x, R, mask, params, a_t, c_t);
+  P.u = u; P.g = g; P.row_part = row_part;
+  rc = set_dropout(P, dropout_p, dropout_seed);
+  if (rc) return rc;
+  CU(launch_cell_fwd_f32(P, plan->grid_cell, (cudaStream_t)stream));
+  return DLAP_OK;
+}
+
+int dlap_row_finish(const dlap_plan* plan, const double* row_part, int weighted_loss, const float* n_bar_in,
+                    float* row_stats, float* pr, float* scalars, void* stream) {
+  int rc = check_plan(plan);
+  if (rc) return rc;
+  REQ(row_part); REQ(row_stats); REQ(pr); REQ(scalars);
+  CU(launch_row_finish(row_part, plan->dims.T, plan->tpm, weighted_loss, n_bar_in, row_stats, pr, scalars,
+                       (cudaStream_t)stream));
+  return DLAP_OK;
+}
+
+int dlap_col_partial(const dlap_plan* plan, const float* g, const float* R, const uint8_t* mask, const float* u,
+                     const float* row_stats, double* col_part, float* w_out, void* stream) {
+  int rc = check_plan(plan);
+  if (rc) return rc;
+  REQ(mask); REQ(row_stats); REQ(col_part);
+  if (w_out) REQ(u);
+  CU(launch_col_partial(g, R, mask, u, row_stats, plan->dims.T, plan->dims.N, plan->col_splits, col_part, w_out,
+                        (cudaStream_t)stream));
+  return DLAP_OK;
+}
+
+int dlap_loss_finish(const dlap_plan* plan, const double* col_part, int nsplit, float* e, float* t_i,
+                     double* loss_part, uint32_t* counter, float* scalars, void* stream) {
+  int rc = check_plan(plan);
+  if (rc) return rc;
+  REQ(col_part); REQ(e); REQ(t_i); REQ(loss_part); REQ(counter); REQ(scalars);
+  if (nsplit < 1) return DLAP_E_SHAPE;
+  CU(launch_loss_finish(col_part, nsplit, plan->dims.N, plan->dims.N, e, t_i, loss_part, counter, scalars,
+                        (cudaStream_t)stream));
+  return DLAP_OK;
+}
+
+int dlap_loss_coeff(const dlap_plan* plan, const float* e, const float* t_i, const float* gc, const float* gu,
+                    float* G, void* stream) {
+  int rc = check_plan(plan);
+  if (rc) return rc;
+  REQ(e); REQ(t_i); REQ(G);
+  CU(launch_coeff(e, t_i, plan->dims.N, gc, gu, G, (cudaStream_t)stream));
+  return DLAP_OK;
+}
+
+int dlap_ds_rows(const dlap_plan* plan, const float* g, const float* R, const uint8_t* mask, const float* G,
+                 double* dS_part, void* stream) {
+  int rc = check_plan(plan);
+  if (rc) return rc;
+  REQ(R); REQ(mask); REQ(G); REQ(dS_part);
+  CU(launch_ds_rows(g, R, mask, G, plan->dims.T, plan->dims.N, plan->row_splits, dS_part, (cudaStream_t)stream));
+  return DLAP_OK;
+}
+
+int dlap_cell_bwd(const dlap_plan* plan, const float* x, const float* R, const uint8_t* mask,
+                  const dlap_tensors* params, const float* a_t, const float* c_t, const float* row_stats,
+                  const double* dS_part, const float* dpr_cot, const float* G, const float* scalars,
+                  int weighted_loss, int want_sdf, int want_mom, float* wpart, float* dadc_part, int precision,
+                  float dropout_p, uint64_t dropout_seed, void* stream) {
+  int rc = check_plan(plan);
+  if (rc) return rc;
+  REQ(x); REQ(R); REQ(mask); REQ(params); REQ(a_t); REQ(c_t); REQ(row_stats); REQ(dS_part); REQ(G); REQ(scalars);
+  REQ(wpart); REQ(dadc_part);
+  REQ(params->w1); REQ(params->w2); REQ(params->b2); REQ(params->w3); REQ(params->b3); REQ(params->wq);
+  if (!want_sdf && !want_mom) return DLAP_E_SHAPE;
+  if (precision != DLAP_PREC_FP32) return DLAP_E_PRECISION;
+  CellParams P;
+  fill_cell(P, plan, x, R, mask, params, a_t, c_t);
+  P.row_stats = row_stats; P.dS_part = dS_part; P.ds_splits = plan->row_splits; P.dpr_cot = dpr_cot;
+  P.G = G; P.scalars = scalars; P.weighted = weighted_loss;
+  P.wpart = wpart; P.dadc_part = dadc_part;
+  rc = set_dropout(P, dropout_p, dropout_seed);
+  if (rc) return rc;
+  CU(launch_cell_bwd_f32(P, plan->grid_cell, want_sdf != 0, want_mom != 0, (cudaStream_t)stream));
+  return DLAP_OK;
+}
+
+int dlap_grad_finish(const dlap_plan* plan, const float* wpart, const float* dadc_part, int want_sdf,
+                     int want_mom, const dlap_tensors* grads, float* dadc, void* stream) {
+  int rc = check_plan(plan);
+  if (rc) return rc;
+  REQ(wpart); REQ(dadc_part); REQ(grads); REQ(dadc);
+  if (want_sdf) { REQ(grads->w1); REQ(grads->w2); REQ(grads->b2); REQ(grads->w3); REQ(grads->b3); }
+  if (want_mom) REQ(grads->wq);
+  CU(launch_grad_finish(wpart, plan->grid_cell, plan->dims.F, want_sdf, want_mom, dadc_part, plan->dims.T,
+                        plan->tpm, grads->w1, plan->ldw1, grads->w2, grads->b2, grads->w3, grads->b3, grads->wq,
+                        plan->ldwq, plan->dims.M, dadc, (cudaStream_t)stream));
+  return DLAP_OK;
+}
+
+int dlap_macro_bwd(const dlap_plan* plan, const float* macro, const dlap_tensors* params, const float* h0,
+                   const float* c0, const float* lstm_save, const float* dadc, float* dpre, int want_sdf,
+                   int want_mom, const dlap_tensors* grads, void* stream) {
+  int rc = check_plan(plan);
+  if (rc) return rc;
+  REQ(params); REQ(dadc); REQ(grads);
+  if (want_sdf) REQ(grads->b1);
+  if (want_mom) REQ(grads->bq);
+  if (plan->dims.M > 0) {
+    REQ(macro);
+    if (want_sdf) {
+      REQ(lstm_save); REQ(dpre); REQ(params->w_hh); REQ(params->w1);
+      REQ(grads->w_ih); REQ(grads->w_hh); REQ(grads->b_ih); REQ(grads->b_hh); REQ(grads->w1);
+    }
+    if (want_mom) REQ(grads->wq);
+  }
+  CU(launch_macro_bwd_c(plan, macro, params, h0, c0, lstm_save, dadc, dpre, want_sdf, want_mom, grads,
+                        (cudaStream_t)stream));
+  return DLAP_OK;
+}
+
+int dlap_weights(const dlap_plan* plan, const float* u, const uint8_t* mask, const float* row_stats,
+                 int normalized, float* w_out, void* stream) {
+  int rc = check_plan(plan);
+  if (rc) return rc;
+  REQ(u); REQ(mask); REQ(row_stats); REQ(w_out);
+  CU(launch_weights(u, mask, row_stats, plan->dims.T, plan->dims.N, normalized, w_out, (cudaStream_t)stream));
+  return DLAP_OK;
+}
+
+}  // extern "C"

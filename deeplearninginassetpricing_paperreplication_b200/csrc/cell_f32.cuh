@@ -1,0 +1,276 @@
+// Per-cell ("stock-month") kernels, exact-fp32 FFMA path.
+//
+// One tile = up to 128 consecutive stocks of ONE month.  A persistent CTA of 256 threads
+// walks tiles with a static stride; per tile it
+//   * pulls the [ncell, F] fp32 characteristic slab with one 1-D bulk copy (TMA engine) into a
+//     staging buffer, transposes it to unit-major smem, and immediately re-arms the copy for
+//     its next tile so the load overlaps the math;
+//   * runs the SDF MLP  z1 = W1x.x + a_t, h1 = relu, z2 = W2.h1 + b2, h2 = relu, u = W3.h2 + b3
+//     (reference: src/model.py:208-219, 261-268; the tile-over-N concat of :253-255 is the
+//     per-month bias a_t) as register-tiled fp32 GEMMs, weights resident in smem;
+//   * runs the moment net  q = tanh(Wqx.x + c_t)  (src/model.py:132-161, :514-516).
+// The forward kernel emits u, g = q*R*m and the four row sums of the month; the backward
+// kernel recomputes the activations instead of reading saved ones and produces per-CTA
+// weight-gradient partials plus per-tile da_t / dc_t partials.
+#pragma once
+#include "dlap_common.cuh"
+
+namespace dlap {
+
+struct CellParams {
+  // panel (caller-owned, read-only)
+  const float* x;            // [T,N,F]
+  const float* R;            // [T,N]      (may be null in weights-only inference)
+  const uint8_t* mask;       // [T,N]      torch.bool bytes
+  int T, N, F;
+  long long x_bytes;         // T*N*F*4, to keep the bulk copy inside the tensor
+  // parameters (device, reference layouts)
+  const float* W1; int ldw1; // fc_layers.0.weight [64, ldw1], characteristics are columns 0..F-1
+  const float* W2;           // fc_layers.3.weight [64,64]
+  const float* b2;           // [64]
+  const float* W3;           // output_proj.weight [1,64]
+  const float* b3;           // [1]
+  const float* Wq; int ldwq; int wq_off;  // moment output_proj.weight [8, ldwq]; chars start at wq_off
+  // per-month vectors
+  const float* a_t;          // [T,64]  W1m.h_t + b1
+  const float* c_t;          // [T,8]   Wqm.macro_t + bq
+  // forward outputs
+  float* u;                  // [T,N]
+  float* g;                  // [8,T,N]  q*R*m            (null: skip the moment net)
+  double* row_part;          // [T,tpm,4] sum m, m*u, m*u*R, m*R
+  // backward inputs
+  const float* row_stats;    // [T,RS_W]
+  const double* dS_part;     // [T,ds_splits]
+  int ds_splits;
+  const float* dpr_cot;      // [T] cotangent of portfolio_returns, or null
+  const float* G;            // [9,N]   rows 0..7: G_k, row 8: G0
+  const float* scalars;      // [SC_W]  (n_bar)
+  int weighted;              // weighted_loss flag
+  // backward outputs
+  float* wpart;              // [grid, WP_STRIDE] per-CTA weight-gradient partials
+  float* dadc_part;          // [T,tpm,72]  da_t (64) then dc_t (8)
+  int tpm;                   // tiles per month
+  // dropout after each ReLU of the SDF net (src/model.py:213), train mode only
+  uint32_t drop_thr;         // drop when a 16-bit uniform < drop_thr (0 = off)
+  float drop_scale;          // 1 / (1 - drop_thr/65536)
+  uint32_t seed_lo, seed_hi; // per-forward seed; the backward pass regenerates the same mask
+};
+
+// layout of one CTA's weight-gradient partial
+__host__ __device__ inline int wp_off_w2() { return 0; }
+__host__ __device__ inline int wp_off_w1() { return 64 * 64; }
+__host__ __device__ inline int wp_off_wq(int Fr) { return 64 * 64 + 64 * Fr; }
+__host__ __device__ inline int wp_off_w3(int Fr) { return 64 * 64 + 72 * Fr; }
+__host__ __device__ inline int wp_off_b2(int Fr) { return 64 * 64 + 72 * Fr + 64; }
+__host__ __device__ inline int wp_stride(int Fr) { return 64 * 64 + 72 * Fr + 128; }
+
+struct SmemFwd {
+  float* stage; float* xs; float* hs; float* W1s; float* W2s; float* Wqs;
+  float* b2s; float* w3s; float* as; float* cs; float* us; float* sc; double* red; uint64_t* bar;
+};
+
+__host__ __device__ inline int round4(int v) { return (v + 3) & ~3; }
+
+// bytes of dynamic smem for the forward kernel
+__host__ __device__ inline size_t smem_fwd_bytes(int F) {
+  const int Fr = round4(F);
+  size_t fl = (size_t)(TILE * F + 8) + (size_t)Fr * TILE + 64 * TILE + (size_t)Fr * 64 + 64 * 64 +
+              (size_t)Fr * 8 + 64 + 64 + 64 + 8 + TILE + 8;
+  return fl * 4 + 64 * 8 + 16 + 16;
+}
+
+__device__ __forceinline__ void carve_fwd(unsigned char* base, int F, SmemFwd& s) {
+  const int Fr = round4(F);
+  float* p = reinterpret_cast<float*>(base);
+  s.stage = p; p += TILE * F + 8;
+  p = reinterpret_cast<float*>((reinterpret_cast<uintptr_t>(p) + 15) & ~uintptr_t(15));
+  s.xs = p; p += Fr * TILE;
+  s.hs = p; p += 64 * TILE;
+  s.W1s = p; p += Fr * 64;
+  s.W2s = p; p += 64 * 64;
+  s.Wqs = p; p += Fr * 8;
+  s.b2s = p; p += 64;
+  s.w3s = p; p += 64;
+  s.as = p; p += 64;
+  s.cs = p; p += 8;
+  s.us = p; p += TILE;
+  s.sc = p; p += 8;
+  p = reinterpret_cast<float*>((reinterpret_cast<uintptr_t>(p) + 7) & ~uintptr_t(7));
+  s.red = reinterpret_cast<double*>(p); p += 64 * 2;
+  s.bar = reinterpret_cast<uint64_t*>(p);
+}
+
+// ---- tile streaming ----------------------------------------------------------------------
+struct TileLoad {
+  const float* src;   // first float of the tile in global memory
+  int ncell;          // valid cells
+  int shift;          // floats between the 16-B aligned copy start and src (0..3)
+  uint32_t bytes;     // bulk-copy size (multiple of 16), 0 => cooperative fallback
+};
+
+__device__ __forceinline__ TileLoad plan_tile(const CellParams& P, int t, int n0) {
+  TileLoad L;
+  L.ncell = min(TILE, P.N - n0);
+  L.src = P.x + ((size_t)t * P.N + n0) * P.F;
+  const uintptr_t a = reinterpret_cast<uintptr_t>(L.src);
+  const uintptr_t a0 = a & ~uintptr_t(15);
+  const uintptr_t e1 = (a + (size_t)L.ncell * P.F * 4 + 15) & ~uintptr_t(15);
+  const uintptr_t xend = reinterpret_cast<uintptr_t>(P.x) + (uintptr_t)P.x_bytes;
+  L.shift = (int)((a - a0) >> 2);
+  L.bytes = (e1 <= xend && (a & 3) == 0) ? (uint32_t)(e1 - a0) : 0u;
+  return L;
+}
+
+// Starts the copy of a tile into `stage`.  Bulk path: one elected thread arms the mbarrier and
+// issues the copy.  Fallback (copy would run past the tensor): every thread copies floats.
+__device__ __forceinline__ void issue_tile(const TileLoad& L, int F, float* stage, uint64_t* bar) {
+  if (L.bytes) {
+    if (threadIdx.x == 0) {
+      fence_proxy_async();
+      mbar_expect_tx(bar, L.bytes);
+      bulk_g2s(stage, L.src - L.shift, L.bytes, bar);
+    }
+  } else {
+    const int n = L.ncell * F;
+    for (int i = threadIdx.x; i < n; i += NT) stage[L.shift + i] = __ldg(L.src + i);
+  }
+}
+
+// stage (cell-major, as in HBM) -> xs (swizzled unit-major [Fr][128]); zero-fills missing
+// cells/rows
+__device__ __forceinline__ void transpose_tile(const TileLoad& L, int F, const float* stage,
+                                               float* xs) {
+  const int Fr = round4(F);
+  const int cell = threadIdx.x & (TILE - 1);
+  const bool live = cell < L.ncell;
+  const float* row = stage + L.shift + cell * F;
+  for (int k = threadIdx.x >> 7; k < Fr; k += NT / TILE)
+    xs[act_idx(k, cell)] = (live && k < F) ? row[k] : 0.f;
+}
+
+// ---- weights -> smem ---------------------------------------------------------------------
+__device__ __forceinline__ void load_weights_fwd(const CellParams& P, SmemFwd& s) {
+  const int F = P.F, Fr = round4(F);
+  for (int i = threadIdx.x; i < Fr * 64; i += NT) {
+    const int k = i >> 6, j = i & 63;
+    s.W1s[i] = (k < F) ? __ldg(P.W1 + (size_t)j * P.ldw1 + k) : 0.f;
+  }
+  for (int i = threadIdx.x; i < 64 * 64; i += NT) {
+    const int k = i >> 6, j = i & 63;
+    s.W2s[i] = __ldg(P.W2 + j * 64 + k);
+  }
+  for (int i = threadIdx.x; i < Fr * 8; i += NT) {
+    const int k = i >> 3, q = i & 7;
+    s.Wqs[i] = (k < F && P.Wq) ? __ldg(P.Wq + (size_t)q * P.ldwq + P.wq_off + k) : 0.f;
+  }
+  if (threadIdx.x < 64) {
+    s.b2s[threadIdx.x] = __ldg(P.b2 + threadIdx.x);
+    s.w3s[threadIdx.x] = __ldg(P.W3 + threadIdx.x);
+  }
+}
+
+// ---- register-tiled GEMM pieces ------------------------------------------------------------
+// thread (ty = tid>>3, tx = tid&7) owns cells 4*ty..4*ty+3 and units 4*tx+i, 32+4*tx+i.
+__device__ __forceinline__ int unit_of(int tx, int o) { return (o < 4) ? 4 * tx + o : 28 + 4 * tx + o; }
+
+#define DLAP_FMA4x8(acc, av, w0, w1)                                   \
+  {                                                                    \
+    const float a_[4] = {av.x, av.y, av.z, av.w};                      \
+    _Pragma("unroll") for (int c_ = 0; c_ < 4; ++c_) {                 \
+      acc[c_][0] = fmaf(a_[c_], w0.x, acc[c_][0]);                     \
+      acc[c_][1] = fmaf(a_[c_], w0.y, acc[c_][1]);                     \
+      acc[c_][2] = fmaf(a_[c_], w0.z, acc[c_][2]);                     \
+      acc[c_][3] = fmaf(a_[c_], w0.w, acc[c_][3]);                     \
+      acc[c_][4] = fmaf(a_[c_], w1.x, acc[c_][4]);                     \
+      acc[c_][5] = fmaf(a_[c_], w1.y, acc[c_][5]);                     \
+      acc[c_][6] = fmaf(a_[c_], w1.z, acc[c_][6]);                     \
+      acc[c_][7] = fmaf(a_[c_], w1.w, acc[c_][7]);                     \
+    }                                                                  \
+  }
+
+// z1 = a_t + W1x.x  -> acc ; W1s [k][64]
+__device__ __forceinline__ void layer1(const SmemFwd& s, int F, int ty, int tx, float acc[4][8]) {
+#pragma unroll
+  for (int o = 0; o < 8; ++o) {
+    const float b = s.as[unit_of(tx, o)];
+#pragma unroll
+    for (int c = 0; c < 4; ++c) acc[c][o] = b;
+  }
+  const float4* xs4 = reinterpret_cast<const float4*>(s.xs);
+  const float4* w4 = reinterpret_cast<const float4*>(s.W1s);
+#pragma unroll 2
+  for (int k = 0; k < F; ++k) {
+    const float4 xv = xs4[act_idx4(k, ty)];
+    const float4 w0 = w4[k * 16 + tx], w1 = w4[k * 16 + 8 + tx];
+    DLAP_FMA4x8(acc, xv, w0, w1);
+  }
+}
+
+// ---- dropout: counter-based, keyed on (seed, stock-month, layer, unit) ----------------------------
+__device__ __forceinline__ uint32_t mix32(uint32_t h) {
+  h ^= h >> 16; h *= 0x85ebca6bu; h ^= h >> 13; h *= 0xc2b2ae35u; h ^= h >> 16;
+  return h;
+}
+// acc <- relu(acc) * (0 | scale); one 32-bit hash decides two neighbouring units of one cell
+__device__ __forceinline__ void relu_dropout(const CellParams& P, uint32_t cell0, int layer, int tx,
+                                             float acc[4][8]) {
+#pragma unroll
+  for (int c = 0; c < 4; ++c) {
+    const uint32_t key = mix32((cell0 + c) ^ P.seed_lo) ^ P.seed_hi;
+#pragma unroll
+    for (int pr = 0; pr < 4; ++pr) {
+      const int j0 = unit_of(tx, 2 * pr);
+      const uint32_t r = mix32(key + (uint32_t)(layer * 32 + (j0 >> 1)) * 0x9E3779B9u);
+      acc[c][2 * pr] = ((r & 0xffffu) >= P.drop_thr) ? fmaxf(acc[c][2 * pr], 0.f) * P.drop_scale : 0.f;
+      acc[c][2 * pr + 1] = ((r >> 16) >= P.drop_thr) ? fmaxf(acc[c][2 * pr + 1], 0.f) * P.drop_scale : 0.f;
+    }
+  }
+}
+
+// relu(acc) -> hs (swizzled unit-major)
+__device__ __forceinline__ void store_relu(float* hs, int ty, int tx, float acc[4][8]) {
+  float4* hs4 = reinterpret_cast<float4*>(hs);
+#pragma unroll
+  for (int o = 0; o < 8; ++o) {
+    const int j = unit_of(tx, o);
+    float4 v;
+    v.x = fmaxf(acc[0][o], 0.f); v.y = fmaxf(acc[1][o], 0.f);
+    v.z = fmaxf(acc[2][o], 0.f); v.w = fmaxf(acc[3][o], 0.f);
+    hs4[act_idx4(j, ty)] = v;
+  }
+}
+
+// z2 = b2 + W2.h1 -> acc
+__device__ __forceinline__ void layer2(const SmemFwd& s, int ty, int tx, float acc[4][8]) {
+#pragma unroll
+  for (int o = 0; o < 8; ++o) {
+    const float b = s.b2s[unit_of(tx, o)];
+#pragma unroll
+    for (int c = 0; c < 4; ++c) acc[c][o] = b;
+  }
+  const float4* hs4 = reinterpret_cast<const float4*>(s.hs);
+  const float4* w4 = reinterpret_cast<const float4*>(s.W2s);
+#pragma unroll 4
+  for (int k = 0; k < 64; ++k) {
+    const float4 hv = hs4[act_idx4(k, ty)];
+    const float4 w0 = w4[k * 16 + tx], w1 = w4[k * 16 + 8 + tx];
+    DLAP_FMA4x8(acc, hv, w0, w1);
+  }
+}
+
+// moment pre-activations: thread (cell = tid&127, half = tid>>7) does moments 4*half..4*half+3
+__device__ __forceinline__ void moment_pre(const SmemFwd& s, int F, float qp[4]) {
+  const int cell = threadIdx.x & (TILE - 1), half = threadIdx.x >> 7;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) qp[i] = s.cs[4 * half + i];
+  const float4* wq4 = reinterpret_cast<const float4*>(s.Wqs);
+#pragma unroll 2
+  for (int k = 0; k < F; ++k) {
+    const float xv = s.xs[act_idx(k, cell)];
+    const float4 w = wq4[k * 2 + half];
+    qp[0] = fmaf(xv, w.x, qp[0]); qp[1] = fmaf(xv, w.y, qp[1]);
+    qp[2] = fmaf(xv, w.z, qp[2]); qp[3] = fmaf(xv, w.w, qp[3]);
+  }
+}
+
+}  // namespace dlap

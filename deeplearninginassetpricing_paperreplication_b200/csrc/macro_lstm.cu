@@ -1,0 +1,333 @@
+// Macro path: everything that is per MONTH rather than per stock-month.
+//
+//   forward  (one persistent CTA): input projection W_ih.macro_t for all months in parallel,
+//            then the serial LSTM recurrence on one warp (one lane per gate row, h broadcast by
+//            shuffles), then the per-month biases that replace the reference's two
+//            tile-over-N concats:  a_t = W1[:,F:].h_t + b1  (src/model.py:253-255, :211)
+//                                  c_t = Wq[:,:M].macro_t + bq (src/model.py:514-516, :152).
+//            LSTM semantics: torch.nn.LSTM, gates i,f,g,o (src/model.py:39-45, :68).
+//   backward (one persistent CTA): dh_t = W1[:,F:]^T.da_t, BPTT on one warp, then the
+//            month-summed weight gradients (LSTM, W1[:,F:], b1, Wq[:,:M], bq).
+#include "../../include/dlap.h"
+#include "dlap_common.cuh"
+
+namespace dlap {
+
+struct MacroParams {
+  const float* macro;   // [T,M]
+  int T, M, H, F;
+  const float* Wih;     // [4H,M]
+  const float* Whh;     // [4H,H]
+  const float* bih;     // [4H]
+  const float* bhh;     // [4H]
+  const float* W1; int ldw1;   // [64, ldw1]; macro-state columns start at F
+  const float* b1;      // [64]
+  const float* Wq; int ldwq;   // [8, ldwq]; macro columns 0..M-1
+  const float* bq;      // [8]
+  const float* h0;      // [H] or null
+  const float* c0;      // [H] or null
+  // forward outputs
+  float* save;          // [T, 6H]: h(H) c(H) i f g o (4H), post-activation
+  float* a_t;           // [T,64]
+  float* c_t;           // [T,8]
+  float* hn;            // [H]
+  float* cn;            // [H]
+  // backward
+  const float* dadc;    // [T,72]  da_t (64) | dc_t (8), summed over stocks
+  float* dpre;          // [T,4H] scratch: LSTM pre-activation gradients
+  int have_sdf, have_mom;
+  float* gWih; float* gWhh; float* gbih; float* gbhh;   // LSTM grads
+  float* gW1;           // [64, ldw1]  (columns F.. written here)
+  float* gb1;           // [64]
+  float* gWq;           // [8, ldwq]   (columns 0..M-1 written here)
+  float* gbq;           // [8]
+};
+
+__device__ __forceinline__ float sigmoidf_acc(float v) { return 1.f / (1.f + expf(-v)); }
+
+constexpr int MT = 512;    // threads of the single-CTA macro kernels
+
+// dynamic smem: xp[T][4H] | Wih[4H][M] | Wqm[8][M]
+template <int H>
+__global__ void __launch_bounds__(MT, 1) macro_fwd_kernel(const MacroParams P) {
+  extern __shared__ float sm[];
+  const int T = P.T, M = P.M;
+  constexpr int G4 = 4 * H;
+  float* xp = sm;
+  float* wih = xp + (size_t)T * G4;
+  float* wqm = wih + (size_t)G4 * M;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, nwarp = MT / 32;
+
+  for (int i = tid; i < G4 * M; i += MT) wih[i] = __ldg(P.Wih + i);
+  for (int i = tid; i < KM * M; i += MT) wqm[i] = __ldg(P.Wq + (size_t)(i / M) * P.ldwq + (i % M));
+  __syncthreads();
+
+  // phase 1: one warp per month, lanes stride over the M macro series
+  for (int t = warp; t < T; t += nwarp) {
+    float acc[G4 + KM];
+#pragma unroll
+    for (int r = 0; r < G4 + KM; ++r) acc[r] = 0.f;
+    const float* row = P.macro + (size_t)t * M;
+    for (int k = lane; k < M; k += 32) {
+      const float v = __ldg(row + k);
+#pragma unroll
+      for (int r = 0; r < G4; ++r) acc[r] = fmaf(v, wih[r * M + k], acc[r]);
+#pragma unroll
+      for (int q = 0; q < KM; ++q) acc[G4 + q] = fmaf(v, wqm[q * M + k], acc[G4 + q]);
+    }
+#pragma unroll
+    for (int r = 0; r < G4 + KM; ++r) acc[r] = warp_sum(acc[r]);
+    if (lane == 0) {
+#pragma unroll
+      for (int r = 0; r < G4; ++r) xp[t * G4 + r] = acc[r] + __ldg(P.bih + r) + __ldg(P.bhh + r);
+#pragma unroll
+      for (int q = 0; q < KM; ++q) P.c_t[(size_t)t * KM + q] = acc[G4 + q] + __ldg(P.bq + q);
+    }
+  }
+  __syncthreads();
+
+  // phase 2: the recurrence, warp 0.  lane r < 4H owns gate row r; lanes j < H also own (h_j, c_j)
+  if (warp == 0) {
+    float whh[H];
+#pragma unroll
+    for (int j = 0; j < H; ++j) whh[j] = (lane < G4) ? __ldg(P.Whh + lane * H + j) : 0.f;
+    float h = (lane < H && P.h0) ? __ldg(P.h0 + lane) : 0.f;
+    float c = (lane < H && P.c0) ? __ldg(P.c0 + lane) : 0.f;
+    const bool is_g = lane >= 2 * H && lane < 3 * H;
+    for (int t = 0; t < T; ++t) {
+      float pre = (lane < G4) ? xp[t * G4 + lane] : 0.f;
+#pragma unroll
+      for (int j = 0; j < H; ++j) pre = fmaf(whh[j], __shfl_sync(0xffffffffu, h, j), pre);
+      const float act = is_g ? tanhf(pre) : sigmoidf_acc(pre);
+      const int j = lane < H ? lane : 0;
+      const float gi = __shfl_sync(0xffffffffu, act, j);
+      const float gf = __shfl_sync(0xffffffffu, act, H + j);
+      const float gg = __shfl_sync(0xffffffffu, act, 2 * H + j);
+      const float go = __shfl_sync(0xffffffffu, act, 3 * H + j);
+      c = gf * c + gi * gg;
+      h = go * tanhf(c);
+      float* sv = P.save + (size_t)t * 6 * H;
+      if (lane < H) { sv[lane] = h; sv[H + lane] = c; }
+      if (lane < G4) sv[2 * H + lane] = act;
+    }
+    if (lane < H) { P.hn[lane] = h; P.cn[lane] = c; }
+  }
+  __syncthreads();
+
+  // phase 3: a_t = W1[:,F:F+H].h_t + b1
+  for (int i = tid; i < T * D1; i += MT) {
+    const int t = i / D1, j = i % D1;
+    float v = __ldg(P.b1 + j);
+    const float* hrow = P.save + (size_t)t * 6 * H;
+    for (int k = 0; k < H; ++k) v = fmaf(__ldg(P.W1 + (size_t)j * P.ldw1 + P.F + k), hrow[k], v);
+    P.a_t[i] = v;
+  }
+}
+
+// BPTT: one CTA.  dynamic smem: dh[T][H].  Writes dpre[T][4H] (pre-activation gradients) to P.dpre.
+template <int H>
+__global__ void __launch_bounds__(MT, 1) macro_bptt_kernel(const MacroParams P) {
+  extern __shared__ float sm[];
+  const int T = P.T;
+  constexpr int G4 = 4 * H;
+  float* dh = sm;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  // dh_t = W1[:,F:]^T . da_t
+  for (int i = tid; i < T * H; i += MT) {
+    const int t = i / H, k = i % H;
+    float v = 0.f;
+    for (int j = 0; j < D1; ++j)
+      v = fmaf(__ldg(P.W1 + (size_t)j * P.ldw1 + P.F + k), __ldg(P.dadc + (size_t)t * 72 + j), v);
+    dh[i] = v;
+  }
+  __syncthreads();
+  if (warp != 0) return;
+  // lane j < H carries (dh_rec_j, dc_j)
+  float whh_col[G4];           // Whh[r][lane] for every gate row r
+#pragma unroll
+  for (int r = 0; r < G4; ++r) whh_col[r] = (lane < H) ? __ldg(P.Whh + r * H + lane) : 0.f;
+  float dh_rec = 0.f, dc = 0.f;
+  const int j = lane < H ? lane : 0;
+  for (int t = T - 1; t >= 0; --t) {
+    const float* sv = P.save + (size_t)t * 6 * H;
+    const float cc = sv[H + j], gi = sv[2 * H + j], gf = sv[3 * H + j], gg = sv[4 * H + j],
+                go = sv[5 * H + j];
+    const float cprev = (t > 0) ? P.save[(size_t)(t - 1) * 6 * H + H + j] : (P.c0 ? __ldg(P.c0 + j) : 0.f);
+    const float dht = dh[t * H + j] + dh_rec;
+    const float tc = tanhf(cc);
+    dc = fmaf(dht * go, 1.f - tc * tc, dc);
+    const float di = dc * gg * gi * (1.f - gi);
+    const float df = dc * cprev * gf * (1.f - gf);
+    const float dg = dc * gi * (1.f - gg * gg);
+    const float d_o = dht * tc * go * (1.f - go);
+    if (lane < H) {
+      float* dp = P.dpre + (size_t)t * G4;
+      dp[lane] = di; dp[H + lane] = df; dp[2 * H + lane] = dg; dp[3 * H + lane] = d_o;
+    }
+    float acc = 0.f;
+#pragma unroll
+    for (int s = 0; s < H; ++s) {
+      acc = fmaf(whh_col[s], __shfl_sync(0xffffffffu, di, s), acc);
+      acc = fmaf(whh_col[H + s], __shfl_sync(0xffffffffu, df, s), acc);
+      acc = fmaf(whh_col[2 * H + s], __shfl_sync(0xffffffffu, dg, s), acc);
+      acc = fmaf(whh_col[3 * H + s], __shfl_sync(0xffffffffu, d_o, s), acc);
+    }
+    dh_rec = acc;
+    dc *= gf;
+  }
+}
+
+// Month-summed gradients: one thread per output element, a T-long dot product each.
+__global__ void __launch_bounds__(128) macro_wgrad_kernel(const MacroParams P) {
+  const int T = P.T, M = P.M, H = P.H, G4 = 4 * H;
+  const int n_sdf = P.have_sdf ? (G4 * M + G4 * H + G4 + D1 * H + D1) : 0;
+  const int n_mom = P.have_mom ? (KM * M + KM) : 0;
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_sdf + n_mom) return;
+  float v = 0.f;
+  if (i < n_sdf) {
+    if (i < G4 * M) {                                  // dW_ih[r][m] = sum_t dpre[t][r] macro[t][m]
+      const int r = i / M, m = i % M;
+#pragma unroll 4
+      for (int t = 0; t < T; ++t) v = fmaf(__ldg(P.dpre + (size_t)t * G4 + r), __ldg(P.macro + (size_t)t * M + m), v);
+      P.gWih[i] = v;
+      return;
+    }
+    i -= G4 * M;
+    if (i < G4 * H) {                                  // dW_hh[r][k] = sum_t dpre[t][r] h_{t-1}[k]
+      const int r = i / H, k = i % H;
+      for (int t = 0; t < T; ++t) {
+        const float hp = (t > 0) ? __ldg(P.save + (size_t)(t - 1) * 6 * H + k) : (P.h0 ? __ldg(P.h0 + k) : 0.f);
+        v = fmaf(__ldg(P.dpre + (size_t)t * G4 + r), hp, v);
+      }
+      P.gWhh[i] = v;
+      return;
+    }
+    i -= G4 * H;
+    if (i < G4) {
+      for (int t = 0; t < T; ++t) v += __ldg(P.dpre + (size_t)t * G4 + i);
+      P.gbih[i] = v; P.gbhh[i] = v;
+      return;
+    }
+    i -= G4;
+    if (i < D1 * H) {                                  // dW1[:,F+k] = sum_t da_t[j] h_t[k]
+      const int j = i / H, k = i % H;
+      for (int t = 0; t < T; ++t)
+        v = fmaf(__ldg(P.dadc + (size_t)t * 72 + j), __ldg(P.save + (size_t)t * 6 * H + k), v);
+      P.gW1[(size_t)j * P.ldw1 + P.F + k] = v;
+      return;
+    }
+    i -= D1 * H;
+    for (int t = 0; t < T; ++t) v += __ldg(P.dadc + (size_t)t * 72 + i);
+    P.gb1[i] = v;
+    return;
+  }
+  i -= n_sdf;
+  if (i < KM * M) {                                    // dWq[k][m] = sum_t dc_t[k] macro[t][m]
+    const int k = i / M, m = i % M;
+#pragma unroll 4
+    for (int t = 0; t < T; ++t)
+      v = fmaf(__ldg(P.dadc + (size_t)t * 72 + 64 + k), __ldg(P.macro + (size_t)t * M + m), v);
+    P.gWq[(size_t)k * P.ldwq + m] = v;
+    return;
+  }
+  i -= KM * M;
+  for (int t = 0; t < T; ++t) v += __ldg(P.dadc + (size_t)t * 72 + 64 + i);
+  P.gbq[i] = v;
+}
+
+size_t macro_fwd_smem(int T, int M, int H) { return ((size_t)T * 4 * H + (size_t)4 * H * M + (size_t)KM * M) * 4; }
+size_t macro_bwd_smem(int T, int H) { return ((size_t)T * H) * 4; }
+
+template <int H>
+static cudaError_t launch_fwd_h(const MacroParams& P, size_t smem, cudaStream_t st) {
+  cudaError_t e = cudaFuncSetAttribute(macro_fwd_kernel<H>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return e;
+  macro_fwd_kernel<H><<<1, MT, smem, st>>>(P);
+  return cudaGetLastError();
+}
+template <int H>
+static cudaError_t launch_bptt_h(const MacroParams& P, size_t smem, cudaStream_t st) {
+  cudaError_t e = cudaFuncSetAttribute(macro_bptt_kernel<H>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return e;
+  macro_bptt_kernel<H><<<1, MT, smem, st>>>(P);
+  return cudaGetLastError();
+}
+#define DLAP_H_SWITCH(FN, ...)                       \
+  switch (P.H) {                                     \
+    case 1: return FN<1>(__VA_ARGS__);               \
+    case 2: return FN<2>(__VA_ARGS__);               \
+    case 3: return FN<3>(__VA_ARGS__);               \
+    case 4: return FN<4>(__VA_ARGS__);               \
+    case 5: return FN<5>(__VA_ARGS__);               \
+    case 6: return FN<6>(__VA_ARGS__);               \
+    case 7: return FN<7>(__VA_ARGS__);               \
+    case 8: return FN<8>(__VA_ARGS__);               \
+    default: return cudaErrorInvalidValue;           \
+  }
+
+cudaError_t launch_macro_fwd(const MacroParams& P, cudaStream_t st) {
+  const size_t smem = macro_fwd_smem(P.T, P.M, P.H);
+  DLAP_H_SWITCH(launch_fwd_h, P, smem, st)
+}
+static cudaError_t launch_bptt(const MacroParams& P, cudaStream_t st) {
+  const size_t smem = macro_bwd_smem(P.T, P.H);
+  DLAP_H_SWITCH(launch_bptt_h, P, smem, st)
+}
+cudaError_t launch_macro_bwd(const MacroParams& P, cudaStream_t st) {
+  if (P.have_sdf && P.H > 0) {
+    cudaError_t e = launch_bptt(P, st);
+    if (e != cudaSuccess) return e;
+  }
+  const int G4 = 4 * P.H;
+  const int total = (P.have_sdf ? (G4 * P.M + G4 * P.H + G4 + D1 * P.H + D1) : 0) +
+                    (P.have_mom ? (KM * P.M + KM) : 0);
+  if (total > 0) macro_wgrad_kernel<<<(total + 127) / 128, 128, 0, st>>>(P);
+  return cudaGetLastError();
+}
+
+// M = 0 (macro_features=None, src/model.py:247-257, :517-518): the per-month biases are just b1 / bq.
+__global__ void const_bias_kernel(const float* __restrict__ b1, const float* __restrict__ bq, int T,
+                                  float* __restrict__ a_t, float* __restrict__ c_t) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < T * D1) a_t[i] = __ldg(b1 + (i % D1));
+  if (i < T * KM) c_t[i] = __ldg(bq + (i % KM));
+}
+
+static void fill_macro(MacroParams& P, const dlap_plan* plan, const float* macro, const dlap_tensors* p,
+                       const float* h0, const float* c0) {
+  P = MacroParams{};
+  P.macro = macro; P.T = plan->dims.T; P.M = plan->dims.M; P.H = plan->dims.M > 0 ? plan->dims.H : 0;
+  P.F = plan->dims.F;
+  P.Wih = p->w_ih; P.Whh = p->w_hh; P.bih = p->b_ih; P.bhh = p->b_hh;
+  P.W1 = p->w1; P.ldw1 = plan->ldw1; P.b1 = p->b1; P.Wq = p->wq; P.ldwq = plan->ldwq; P.bq = p->bq;
+  P.h0 = h0; P.c0 = c0;
+}
+
+cudaError_t launch_macro_fwd_c(const dlap_plan* plan, const float* macro, const dlap_tensors* p, const float* h0,
+                               const float* c0, float* save, float* a_t, float* c_t, float* hn, float* cn,
+                               cudaStream_t st) {
+  if (plan->dims.M == 0) {
+    const int n = plan->dims.T * D1;
+    const_bias_kernel<<<(n + 255) / 256, 256, 0, st>>>(p->b1, p->bq, plan->dims.T, a_t, c_t);
+    return cudaGetLastError();
+  }
+  MacroParams P;
+  fill_macro(P, plan, macro, p, h0, c0);
+  P.save = save; P.a_t = a_t; P.c_t = c_t; P.hn = hn; P.cn = cn;
+  return launch_macro_fwd(P, st);
+}
+
+cudaError_t launch_macro_bwd_c(const dlap_plan* plan, const float* macro, const dlap_tensors* p, const float* h0,
+                               const float* c0, const float* save, const float* dadc, float* dpre, int want_sdf,
+                               int want_mom, const dlap_tensors* g, cudaStream_t st) {
+  MacroParams P;
+  fill_macro(P, plan, macro, p, h0, c0);
+  P.save = const_cast<float*>(save); P.dadc = dadc; P.dpre = dpre;
+  P.have_sdf = want_sdf; P.have_mom = want_mom;
+  P.gWih = g->w_ih; P.gWhh = g->w_hh; P.gbih = g->b_ih; P.gbhh = g->b_hh;
+  P.gW1 = g->w1; P.gb1 = g->b1; P.gWq = g->wq; P.gbq = g->bq;
+  return launch_macro_bwd(P, st);
+}
+
+}  // namespace dlap

@@ -1,0 +1,297 @@
+// Row (per month over N) and column (per stock over T) reductions, loss and gradient finishing
+// kernels.  All HBM-bound or tiny; every cross-CTA sum is done in a fixed order (no float
+// atomics) so that results are run-to-run reproducible like the reference's CPU path.
+#include "dlap_common.cuh"
+#include "cell_f32.cuh"
+
+namespace dlap {
+
+// ---- row finish ------------------------------------------------------------------------------
+// N_t = clamp(sum m, 1), mu_t = sum(m u)/N_t                      src/model.py:276-278
+// P_t = sum m (u - mu_t) R = sum(m u R) - mu_t sum(m R)           src/model.py:363,367
+// pr_t = P_t / N_t * N_bar (weighted_loss) ; S_t = 1 + pr_t       src/model.py:360,367,380
+// sharpe = mean(pr) / (std_unbiased(pr) + 1e-8)                   src/model.py:551
+__global__ void row_finish_kernel(const double* __restrict__ row_part, int T, int tpm, int weighted,
+                                  const float* __restrict__ n_bar_in, float* __restrict__ row_stats,
+                                  float* __restrict__ pr_out, float* __restrict__ scalars) {
+  __shared__ double red[32];
+  const int tid = threadIdx.x;
+  double nsum = 0.0;
+  for (int t = tid; t < T; t += blockDim.x) {
+    double c = 0, su = 0, sur = 0, sr = 0;
+    const double* p = row_part + (size_t)t * tpm * 4;
+    for (int j = 0; j < tpm; ++j) { c += p[4 * j]; su += p[4 * j + 1]; sur += p[4 * j + 2]; sr += p[4 * j + 3]; }
+    const double nt = fmax(c, 1.0);
+    const float mu = (float)(su / nt);
+    float* rs = row_stats + (size_t)t * RS_W;
+    rs[RS_NT] = (float)nt;
+    rs[RS_MU] = mu;
+    rs[RS_P] = (float)(sur - (double)mu * sr);
+    rs[RS_RBAR] = (float)(sr / nt);
+    nsum += nt;
+  }
+  nsum = block_sum(nsum, red);
+  const float n_bar = n_bar_in ? *n_bar_in : (float)(nsum / (double)T);
+  double s1 = 0.0;
+  for (int t = tid; t < T; t += blockDim.x) {
+    float* rs = row_stats + (size_t)t * RS_W;
+    const float pr = weighted ? (float)((double)rs[RS_P] / (double)rs[RS_NT] * (double)n_bar) : rs[RS_P];
+    rs[RS_PR] = pr;
+    rs[RS_S] = 1.f + pr;
+    pr_out[t] = pr;
+    s1 += pr;
+  }
+  s1 = block_sum(s1, red);
+  const double mean = s1 / (double)T;
+  double s2 = 0.0;
+  for (int t = tid; t < T; t += blockDim.x) {
+    const double d = (double)pr_out[t] - mean;
+    s2 += d * d;
+  }
+  s2 = block_sum(s2, red);
+  if (tid == 0) {
+    scalars[SC_NBAR] = n_bar;
+    scalars[SC_SHARPE] = (T > 1) ? (float)(mean / (sqrt(s2 / (double)(T - 1)) + 1e-8)) : nanf("");
+  }
+}
+
+// ---- column partial sums + weights ---------------------------------------------------------------
+// per stock i over the months of one T-chunk:  sum_t g_k S_t (k<8), sum_t R m S_t, sum_t m
+// (src/model.py:376,382,428) and, fused, w = m (u - mu_t) (src/model.py:271-279).
+__global__ void __launch_bounds__(256) col_partial_kernel(
+    const float* __restrict__ g, const float* __restrict__ R, const uint8_t* __restrict__ mask,
+    const float* __restrict__ u, const float* __restrict__ row_stats, int T, int N, int tchunk,
+    double* __restrict__ col_part, float* __restrict__ w_out) {
+  extern __shared__ float sm[];            // S_t then mu_t for this chunk
+  const int t0 = blockIdx.y * tchunk, t1 = min(T, t0 + tchunk);
+  for (int t = t0 + threadIdx.x; t < t1; t += blockDim.x) {
+    sm[t - t0] = row_stats[(size_t)t * RS_W + RS_S];
+    sm[tchunk + t - t0] = row_stats[(size_t)t * RS_W + RS_MU];
+  }
+  __syncthreads();
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= N) return;
+  const size_t plane = (size_t)T * N;
+  double acc[KM + 2];
+#pragma unroll
+  for (int k = 0; k < KM + 2; ++k) acc[k] = 0.0;
+#pragma unroll 4
+  for (int t = t0; t < t1; ++t) {
+    const size_t gi = (size_t)t * N + i;
+    const float S = sm[t - t0];
+    const float m = mask[gi] ? 1.f : 0.f;
+    const float r = R ? __ldg(R + gi) : 0.f;
+    if (w_out) w_out[gi] = m * (__ldg(u + gi) - sm[tchunk + t - t0]);
+    acc[KM] += (double)(r * m * S);
+    acc[KM + 1] += (double)m;
+    if (g) {
+#pragma unroll
+      for (int k = 0; k < KM; ++k) acc[k] += (double)(__ldg(g + k * plane + gi) * S);
+    }
+  }
+  double* out = col_part + (size_t)blockIdx.y * (KM + 2) * N + i;
+#pragma unroll
+  for (int k = 0; k < KM + 2; ++k) out[(size_t)k * N] = acc[k];
+}
+
+// ---- loss finish -----------------------------------------------------------------------------
+// e_ki = colsum / T_i ; L_c = mean_k mean_i e_ki^2 ; L_u = mean_i e0_i^2   src/model.py:382-385,428-431
+__global__ void __launch_bounds__(256) loss_finish_kernel(
+    const double* __restrict__ col_part, int nsplit, int N, int n_total, float* __restrict__ e_out,
+    float* __restrict__ ti_out, double* __restrict__ loss_part, unsigned int* __restrict__ counter,
+    float* __restrict__ scalars) {
+  __shared__ double red[32];
+  __shared__ bool last;
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  double sc = 0.0, su = 0.0;
+  if (i < N) {
+    double v[KM + 2];
+#pragma unroll
+    for (int k = 0; k < KM + 2; ++k) v[k] = 0.0;
+    for (int s = 0; s < nsplit; ++s)
+#pragma unroll
+      for (int k = 0; k < KM + 2; ++k) v[k] += col_part[((size_t)s * (KM + 2) + k) * N + i];
+    const double ti = fmax(v[KM + 1], 1.0);
+    ti_out[i] = (float)ti;
+#pragma unroll
+    for (int k = 0; k <= KM; ++k) {
+      const float e = (float)(v[k] / ti);
+      e_out[(size_t)k * N + i] = e;
+      if (k < KM) sc += (double)e * (double)e; else su += (double)e * (double)e;
+    }
+  }
+  sc = block_sum(sc, red);
+  su = block_sum(su, red);
+  if (threadIdx.x == 0) {
+    loss_part[2 * blockIdx.x] = sc;
+    loss_part[2 * blockIdx.x + 1] = su;
+    __threadfence();
+    last = (atomicAdd(counter, 1u) == gridDim.x - 1);
+  }
+  __syncthreads();
+  if (last && threadIdx.x < 32) {
+    __threadfence();
+    double a = 0.0, b = 0.0;
+    for (int j = threadIdx.x; j < (int)gridDim.x; j += 32) {
+      a += ((volatile double*)loss_part)[2 * j];
+      b += ((volatile double*)loss_part)[2 * j + 1];
+    }
+    a = warp_sum(a); b = warp_sum(b);
+    if (threadIdx.x == 0) {
+      // means run over ALL columns, dead ones included (src/model.py:385); n_total = global N
+      scalars[SC_LC] = (float)(a / ((double)KM * (double)n_total));
+      scalars[SC_LU] = (float)(b / (double)n_total);
+      *counter = 0u;
+    }
+  }
+}
+
+// ---- backward: loss cotangents -> per-stock coefficients -------------------------------------------
+// G_ki = gc * 2 e_ki / (K N T_i) ; G0_i = gu * 2 e0_i / (N T_i)          
+__global__ void coeff_kernel(const float* __restrict__ e, const float* __restrict__ ti, int N,
+                             const float* __restrict__ gc, const float* __restrict__ gu,
+                             float* __restrict__ G) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= N) return;
+  const float c = gc ? *gc : 0.f, uu = gu ? *gu : 0.f;
+  const float inv = 1.f / ((float)N * ti[i]);
+#pragma unroll
+  for (int k = 0; k < KM; ++k) G[(size_t)k * N + i] = c * (2.f / KM) * e[(size_t)k * N + i] * inv;
+  G[(size_t)KM * N + i] = uu * 2.f * e[(size_t)KM * N + i] * inv;
+}
+
+// dS_t partial = sum_i ( sum_k G_ki g_kti + G0_i R m )
+__global__ void __launch_bounds__(256) ds_rows_kernel(
+    const float* __restrict__ g, const float* __restrict__ R, const uint8_t* __restrict__ mask,
+    const float* __restrict__ G, int T, int N, int nchunk, double* __restrict__ dS_part) {
+  __shared__ double red[32];
+  const int t = blockIdx.x, sp = blockIdx.y;
+  const int i0 = sp * nchunk, i1 = min(N, i0 + nchunk);
+  const size_t plane = (size_t)T * N;
+  double acc = 0.0;
+  for (int i = i0 + threadIdx.x; i < i1; i += blockDim.x) {
+    const size_t gi = (size_t)t * N + i;
+    float v = mask[gi] ? __ldg(G + (size_t)KM * N + i) * __ldg(R + gi) : 0.f;
+    if (g) {
+#pragma unroll
+      for (int k = 0; k < KM; ++k) v = fmaf(__ldg(G + (size_t)k * N + i), __ldg(g + k * plane + gi), v);
+    }
+    acc += (double)v;
+  }
+  acc = block_sum(acc, red);
+  if (threadIdx.x == 0) dS_part[(size_t)t * gridDim.y + sp] = acc;
+}
+
+// ---- backward: sum per-CTA / per-tile partials into the reference's gradient layouts ----------------
+__global__ void __launch_bounds__(256) grad_finish_kernel(
+    const float* __restrict__ wpart, int ncta, int F, int have_sdf, int have_mom,
+    const float* __restrict__ dadc_part, int T, int tpm,
+    float* __restrict__ gW1, int ldw1, float* __restrict__ gW2, float* __restrict__ gb2,
+    float* __restrict__ gW3, float* __restrict__ gb3, float* __restrict__ gWq, int ldwq, int wq_off,
+    float* __restrict__ dadc) {
+  const int Fr = round4(F), stride = wp_stride(Fr);
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx < stride) {
+    float v = 0.f;
+    for (int c = 0; c < ncta; ++c) v += wpart[(size_t)c * stride + idx];
+    if (idx < wp_off_w1()) {
+      if (have_sdf) gW2[idx] = v;
+    } else if (idx < wp_off_wq(Fr)) {
+      const int j = (idx - wp_off_w1()) / Fr, f = (idx - wp_off_w1()) % Fr;
+      if (have_sdf && f < F) gW1[(size_t)j * ldw1 + f] = v;
+    } else if (idx < wp_off_w3(Fr)) {
+      const int k = (idx - wp_off_wq(Fr)) / Fr, f = (idx - wp_off_wq(Fr)) % Fr;
+      if (have_mom && f < F) gWq[(size_t)k * ldwq + wq_off + f] = v;
+    } else if (idx < wp_off_b2(Fr)) {
+      if (have_sdf) gW3[idx - wp_off_w3(Fr)] = v;
+    } else if (idx < wp_off_b2(Fr) + 64) {
+      if (have_sdf) gb2[idx - wp_off_b2(Fr)] = v;
+    }
+    // d b3 = sum du = dP_t * sum m (R - Rbar_t) = 0 identically (demeaning, src/model.py:279)
+    if (idx == 0 && have_sdf) gb3[0] = 0.f;
+  } else {
+    const int r = idx - stride;
+    if (r < T * 72) {
+      const int t = r / 72, c = r % 72;
+      float v = 0.f;
+      const float* p = dadc_part + (size_t)t * tpm * 72 + c;
+      for (int j = 0; j < tpm; ++j) v += p[(size_t)j * 72];
+      dadc[r] = v;
+    }
+  }
+}
+
+// ---- inference: weights, optionally per-month |w|-normalised -----------------------------------------
+// w = m (u - mu_t) ; normalised: w / clamp(sum_i |w| m, 1e-8)          src/model.py:581-592
+__global__ void __launch_bounds__(256) weights_kernel(
+    const float* __restrict__ u, const uint8_t* __restrict__ mask, const float* __restrict__ row_stats,
+    int N, int normalized, float* __restrict__ w_out) {
+  __shared__ double red[32];
+  const int t = blockIdx.x;
+  const float mu = row_stats[(size_t)t * RS_W + RS_MU];
+  const size_t base = (size_t)t * N;
+  float denom = 1.f;
+  if (normalized) {
+    double s = 0.0;
+    for (int i = threadIdx.x; i < N; i += blockDim.x)
+      if (mask[base + i]) s += (double)fabsf(__ldg(u + base + i) - mu);
+    s = block_sum(s, red);
+    denom = fmaxf((float)s, 1e-8f);
+  }
+  for (int i = threadIdx.x; i < N; i += blockDim.x) {
+    const float w = mask[base + i] ? (__ldg(u + base + i) - mu) : 0.f;
+    w_out[base + i] = normalized ? w / denom : w;
+  }
+}
+
+// ---- launchers ---------------------------------------------------------------------------------------
+cudaError_t launch_row_finish(const double* row_part, int T, int tpm, int weighted, const float* n_bar_in,
+                              float* row_stats, float* pr_out, float* scalars, cudaStream_t st) {
+  row_finish_kernel<<<1, 256, 0, st>>>(row_part, T, tpm, weighted, n_bar_in, row_stats, pr_out, scalars);
+  return cudaGetLastError();
+}
+cudaError_t launch_col_partial(const float* g, const float* R, const uint8_t* mask, const float* u,
+                               const float* row_stats, int T, int N, int nsplit, double* col_part,
+                               float* w_out, cudaStream_t st) {
+  const int tchunk = (T + nsplit - 1) / nsplit;
+  dim3 grid((N + 255) / 256, nsplit);
+  col_partial_kernel<<<grid, 256, 2 * tchunk * sizeof(float), st>>>(g, R, mask, u, row_stats, T, N, tchunk,
+                                                                    col_part, w_out);
+  return cudaGetLastError();
+}
+cudaError_t launch_loss_finish(const double* col_part, int nsplit, int N, int n_total, float* e_out,
+                               float* ti_out, double* loss_part, unsigned int* counter, float* scalars,
+                               cudaStream_t st) {
+  loss_finish_kernel<<<(N + 255) / 256, 256, 0, st>>>(col_part, nsplit, N, n_total, e_out, ti_out,
+                                                      loss_part, counter, scalars);
+  return cudaGetLastError();
+}
+cudaError_t launch_coeff(const float* e, const float* ti, int N, const float* gc, const float* gu, float* G,
+                         cudaStream_t st) {
+  coeff_kernel<<<(N + 255) / 256, 256, 0, st>>>(e, ti, N, gc, gu, G);
+  return cudaGetLastError();
+}
+cudaError_t launch_ds_rows(const float* g, const float* R, const uint8_t* mask, const float* G, int T, int N,
+                           int nsplit, double* dS_part, cudaStream_t st) {
+  const int nchunk = (N + nsplit - 1) / nsplit;
+  dim3 grid(T, nsplit);
+  ds_rows_kernel<<<grid, 256, 0, st>>>(g, R, mask, G, T, N, nchunk, dS_part);
+  return cudaGetLastError();
+}
+cudaError_t launch_grad_finish(const float* wpart, int ncta, int F, int have_sdf, int have_mom,
+                               const float* dadc_part, int T, int tpm, float* gW1, int ldw1, float* gW2,
+                               float* gb2, float* gW3, float* gb3, float* gWq, int ldwq, int wq_off,
+                               float* dadc, cudaStream_t st) {
+  const int total = wp_stride(round4(F)) + T * 72;
+  grad_finish_kernel<<<(total + 255) / 256, 256, 0, st>>>(wpart, ncta, F, have_sdf, have_mom, dadc_part, T,
+                                                          tpm, gW1, ldw1, gW2, gb2, gW3, gb3, gWq, ldwq,
+                                                          wq_off, dadc);
+  return cudaGetLastError();
+}
+cudaError_t launch_weights(const float* u, const uint8_t* mask, const float* row_stats, int T, int N,
+                           int normalized, float* w_out, cudaStream_t st) {
+  weights_kernel<<<T, 256, 0, st>>>(u, mask, row_stats, N, normalized, w_out);
+  return cudaGetLastError();
+}
+
+}  // namespace dlap

@@ -1,0 +1,296 @@
+"""The adversarial-SDF step as one ``torch.autograd.Function`` over the C ABI.
+
+Forward  : macro_fwd -> cell_fwd -> row_finish -> col_partial -> loss_finish
+Backward : loss_coeff -> ds_rows -> cell_bwd -> grad_finish -> macro_bwd
+
+Every stage is a kernel launch through ``libdlap_b200.so`` on torch's current stream; torch is
+used for device memory and streams only.  Nothing here synchronises with the host, so a whole
+training step can be captured in a CUDA graph.
+
+Month-sharded multi-GPU runs (``shard`` argument): each rank owns a contiguous slab of months
+of ``x``/``R``/``mask`` and the full macro series.  The only exchanges are an all-reduce of the
+per-stock column sums ``[10, N]`` in the forward pass and, in the backward pass, an all-reduce
+of the per-month ``da_t | dc_t`` rows (zero outside the rank's slab) together with the
+per-cell weight gradients; every rank then runs the (tiny, serial) LSTM BPTT redundantly.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass
+from typing import Dict, Optional, Tuple
+
+import torch
+
+from . import _lib
+from ._lib import DlapDims, DlapPlan, DlapTensors
+
+RS_W = 8      # row_stats row width  (csrc/dlap_common.cuh)
+SC_W = 8      # scalars width
+SC_LC, SC_LU, SC_SHARPE, SC_NBAR = 0, 1, 2, 3
+RS_NT, RS_MU, RS_P, RS_PR, RS_S, RS_RBAR = 0, 1, 2, 3, 4, 5
+KM = 8
+
+_PRECISIONS = {"fp32": _lib.DLAP_PREC_FP32}
+
+
+def _ptr(t: Optional[torch.Tensor]):
+    return None if t is None else t.data_ptr()
+
+
+def _stream(dev: torch.device):
+    return torch.cuda.current_stream(dev).cuda_stream
+
+
+def _tensors(ts) -> DlapTensors:
+    s = DlapTensors()
+    for name, t in zip(DlapTensors.FIELDS, ts):
+        setattr(s, name, _ptr(t))
+    return s
+
+
+class Workspace:
+    """Plan + pure scratch buffers for one (shape, device).  Scratch is reused by every call on
+    that shape (single-stream semantics, like the reference); nothing that the backward pass
+    needs from the forward pass lives here."""
+
+    def __init__(self, T: int, N: int, F: int, M: int, H: int, device: torch.device):
+        self.device = device
+        dims = DlapDims(T, N, F, M, H if M > 0 else 0)
+        self.plan = DlapPlan()
+        _lib.call("dlap_make_plan", C.byref(dims), device.index if device.index is not None
+                  else torch.cuda.current_device(), C.byref(self.plan))
+        p = self.plan
+        self.pp = C.byref(p)
+        f64 = lambda nbytes: torch.empty(max(nbytes // 8, 1), dtype=torch.float64, device=device)
+        f32 = lambda nbytes: torch.empty(max(nbytes // 4, 1), dtype=torch.float32, device=device)
+        self.row_part = f64(p.row_part_bytes)
+        self.col_part = f64(p.col_part_bytes)
+        self.loss_part = f64(p.loss_part_bytes)
+        self.ds_part = f64(p.ds_part_bytes)
+        self.wpart = f32(p.wpart_bytes)
+        self.dadc_part = f32(p.dadc_part_bytes)
+        self.dpre = f32(p.dpre_bytes)
+        self.counter = torch.zeros(1, dtype=torch.int32, device=device)
+        self.launches = 0          # kernels launched through this workspace (bench bookkeeping)
+
+
+_workspaces: Dict[Tuple, Workspace] = {}
+
+
+def workspace(T, N, F, M, H, device) -> Workspace:
+    key = (T, N, F, M, H if M > 0 else 0, device.index)
+    ws = _workspaces.get(key)
+    if ws is None:
+        ws = _workspaces[key] = Workspace(T, N, F, M, H, device)
+    return ws
+
+
+@dataclass
+class StepOptions:
+    weighted_loss: bool = True
+    need_moments: bool = True       # False in phase 'unconditional': the moment net is unused
+    precision: str = "fp32"
+    dropout_p: float = 0.0          # > 0 only in train mode (src/model.py:213)
+    dropout_seed: int = 0
+    shard: Optional["MonthShard"] = None
+
+
+@dataclass
+class MonthShard:
+    """This rank's slab of months [t0, t1) of a T_total-month panel (see module docstring)."""
+    group: object
+    t0: int
+    t1: int
+    T_total: int
+    n_bar: torch.Tensor             # [1] float32, global mean of clamp(N_t, 1)
+
+
+def check_panel(macro, x, R, mask) -> None:
+    """The reference needs contiguous inputs too (x.view at src/model.py:143,261); beyond that
+    the kernels need fp32 CUDA tensors.  No silent conversion, no CPU fallback."""
+    if not x.is_cuda:
+        raise ValueError("individual_features must be a CUDA tensor: this build has no CPU path")
+    if x.dtype != torch.float32 or x.dim() != 3 or not x.is_contiguous():
+        raise ValueError("individual_features must be a contiguous float32 [T,N,F] tensor")
+    T, N, _ = x.shape
+    if mask.dtype != torch.bool or tuple(mask.shape) != (T, N) or not mask.is_contiguous() \
+            or mask.device != x.device:
+        raise ValueError("mask must be a contiguous bool [T,N] tensor on the same device")
+    if R is not None and (R.dtype != torch.float32 or tuple(R.shape) != (T, N)
+                          or not R.is_contiguous() or R.device != x.device):
+        raise ValueError("returns must be a contiguous float32 [T,N] tensor on the same device")
+    if macro is not None and (macro.dtype != torch.float32 or macro.dim() != 2
+                              or not macro.is_contiguous() or macro.device != x.device):
+        raise ValueError("macro_features must be a contiguous float32 [T,M] tensor on the same device")
+
+
+def _flat_state(h, H, dev):
+    if h is None:
+        return None
+    h = h.detach().reshape(-1).to(device=dev, dtype=torch.float32).contiguous()
+    if h.numel() != H:
+        raise ValueError(f"hidden state must have {H} elements")
+    return h
+
+
+def macro_forward(ws: Workspace, macro, params, h0, c0):
+    """dlap_macro_fwd: LSTM states + per-month biases.  `macro` covers all months of the panel."""
+    dev = ws.device
+    T, H = ws.plan.dims.T, max(ws.plan.dims.H, 1)
+    save = torch.empty(T, 6 * H, dtype=torch.float32, device=dev)
+    a_t = torch.empty(T, 64, dtype=torch.float32, device=dev)
+    c_t = torch.empty(T, KM, dtype=torch.float32, device=dev)
+    hn = torch.empty(H, dtype=torch.float32, device=dev)
+    cn = torch.empty(H, dtype=torch.float32, device=dev)
+    tens = _tensors(params)
+    _lib.call("dlap_macro_fwd", ws.pp, _ptr(macro), C.byref(tens), _ptr(h0), _ptr(c0), _ptr(save),
+              _ptr(a_t), _ptr(c_t), _ptr(hn), _ptr(cn), _stream(dev))
+    ws.launches += 1
+    return save, a_t, c_t, hn, cn
+
+
+class GanStepFn(torch.autograd.Function):
+    """(L_c, L_u, pr, weights, sharpe, h_n, c_n) = step(panel, params)."""
+
+    @staticmethod
+    def forward(ctx, opts: StepOptions, macro, x, R, mask, h0, c0, *params):
+        dev = x.device
+        T, N, F = x.shape
+        M = 0 if macro is None else macro.shape[1]
+        H = 0 if macro is None else params[1].shape[1]
+        prec = _PRECISIONS[opts.precision]
+        sh = opts.shard
+        with torch.cuda.device(dev):
+            st = _stream(dev)
+            ws = workspace(T, N, F, M, H, dev)
+            tens = _tensors(params)
+            if sh is None:
+                save, a_t, c_t, hn, cn = macro_forward(ws, macro, params, h0, c0)
+                a_loc, c_loc = a_t, c_t
+            else:   # LSTM replicated over the full series; this rank uses its slab of a_t / c_t
+                wsm = workspace(sh.T_total, N, F, M, H, dev)
+                save, a_t, c_t, hn, cn = macro_forward(wsm, macro, params, h0, c0)
+                a_loc, c_loc = a_t[sh.t0:sh.t1], c_t[sh.t0:sh.t1]
+            u = torch.empty(T, N, dtype=torch.float32, device=dev)
+            g = torch.empty(KM, T, N, dtype=torch.float32, device=dev) if opts.need_moments else None
+            _lib.call("dlap_cell_fwd", ws.pp, _ptr(x), _ptr(R), _ptr(mask), C.byref(tens), _ptr(a_loc),
+                      _ptr(c_loc), _ptr(u), _ptr(g), _ptr(ws.row_part), prec, float(opts.dropout_p),
+                      int(opts.dropout_seed), st)
+            row_stats = torch.empty(T, RS_W, dtype=torch.float32, device=dev)
+            pr = torch.empty(T, dtype=torch.float32, device=dev)
+            scalars = torch.zeros(SC_W, dtype=torch.float32, device=dev)
+            _lib.call("dlap_row_finish", ws.pp, _ptr(ws.row_part), int(opts.weighted_loss),
+                      _ptr(sh.n_bar) if sh is not None else None, _ptr(row_stats), _ptr(pr),
+                      _ptr(scalars), st)
+            w = torch.empty(T, N, dtype=torch.float32, device=dev)
+            _lib.call("dlap_col_partial", ws.pp, _ptr(g), _ptr(R), _ptr(mask), _ptr(u), _ptr(row_stats),
+                      _ptr(ws.col_part), _ptr(w), st)
+            e = torch.empty(KM + 1, N, dtype=torch.float32, device=dev)
+            t_i = torch.empty(N, dtype=torch.float32, device=dev)
+            if sh is None:
+                col, nsplit = ws.col_part, ws.plan.col_splits
+            else:   # exchange 1: per-stock sums over ALL months
+                col = ws.col_part.view(ws.plan.col_splits, KM + 2, N).sum(dim=0)
+                torch.distributed.all_reduce(col, group=sh.group)
+                nsplit = 1
+            _lib.call("dlap_loss_finish", ws.pp, _ptr(col), nsplit, _ptr(e), _ptr(t_i),
+                      _ptr(ws.loss_part), _ptr(ws.counter), _ptr(scalars), st)
+            ws.launches += 4
+        ctx.save_for_backward(x, R, mask, macro, h0, c0, *params)
+        ctx.opts, ctx.ws = opts, ws
+        ctx.inter = (save, a_t, c_t, row_stats, scalars, g, e, t_i)
+        l_c, l_u, sharpe = scalars[SC_LC], scalars[SC_LU], scalars[SC_SHARPE]
+        ctx.mark_non_differentiable(w, sharpe, hn, cn)
+        return l_c, l_u, pr, w, sharpe, hn, cn
+
+    @staticmethod
+    def backward(ctx, g_lc, g_lu, g_pr, *_unused):
+        x, R, mask, macro, h0, c0, *params = ctx.saved_tensors
+        save, a_t, c_t, row_stats, scalars, g, e, t_i = ctx.inter
+        opts, ws = ctx.opts, ctx.ws
+        sh = opts.shard
+        dev = x.device
+        T, N, F = x.shape
+        M = 0 if macro is None else macro.shape[1]
+        need = ctx.needs_input_grad[7:]
+        want_sdf = any(need[:10])
+        want_mom = any(need[10:]) and g is not None
+        if not (want_sdf or want_mom):
+            return (None,) * (7 + len(params))
+        prec = _PRECISIONS[opts.precision]
+
+        def scalar(t):
+            return None if t is None else t.detach().reshape(1).to(torch.float32).contiguous()
+
+        g_lc, g_lu = scalar(g_lc), scalar(g_lu)
+        if g_pr is not None:
+            g_pr = g_pr.detach().to(torch.float32).contiguous()
+        with torch.cuda.device(dev):
+            st = _stream(dev)
+            tens = _tensors(params)
+            G = torch.empty(KM + 1, N, dtype=torch.float32, device=dev)
+            _lib.call("dlap_loss_coeff", ws.pp, _ptr(e), _ptr(t_i), _ptr(g_lc) if g is not None else None,
+                      _ptr(g_lu), _ptr(G), st)
+            _lib.call("dlap_ds_rows", ws.pp, _ptr(g), _ptr(R), _ptr(mask), _ptr(G), _ptr(ws.ds_part), st)
+            if sh is None:
+                a_loc, c_loc = a_t, c_t
+            else:
+                a_loc, c_loc = a_t[sh.t0:sh.t1], c_t[sh.t0:sh.t1]
+            _lib.call("dlap_cell_bwd", ws.pp, _ptr(x), _ptr(R), _ptr(mask), C.byref(tens), _ptr(a_loc),
+                      _ptr(c_loc), _ptr(row_stats), _ptr(ws.ds_part), _ptr(g_pr), _ptr(G), _ptr(scalars),
+                      int(opts.weighted_loss), int(want_sdf), int(want_mom), _ptr(ws.wpart),
+                      _ptr(ws.dadc_part), prec, float(opts.dropout_p), int(opts.dropout_seed), st)
+            grads = [None if p is None else torch.zeros_like(p) for p in params]
+            gt = _tensors(grads)
+            dadc = torch.empty(T, 72, dtype=torch.float32, device=dev)
+            _lib.call("dlap_grad_finish", ws.pp, _ptr(ws.wpart), _ptr(ws.dadc_part), int(want_sdf),
+                      int(want_mom), C.byref(gt), _ptr(dadc), st)
+            ws.launches += 4
+            if sh is None:
+                wsm, dadc_all = ws, dadc
+            else:   # exchange 2: per-cell weight grads + every month's da_t | dc_t row
+                wsm = workspace(sh.T_total, N, F, M, ws.plan.dims.H, dev)
+                dadc_all = torch.zeros(sh.T_total, 72, dtype=torch.float32, device=dev)
+                dadc_all[sh.t0:sh.t1] = dadc
+                flat = [dadc_all] + [grads[i] for i in (4, 6, 7, 8, 9, 10) if grads[i] is not None]
+                buf = torch.cat([f.reshape(-1) for f in flat])
+                torch.distributed.all_reduce(buf, group=sh.group)
+                off = 0
+                for f in flat:
+                    f.copy_(buf[off:off + f.numel()].view_as(f))
+                    off += f.numel()
+            _lib.call("dlap_macro_bwd", wsm.pp, _ptr(macro), C.byref(tens), _ptr(h0), _ptr(c0), _ptr(save),
+                      _ptr(dadc_all), _ptr(wsm.dpre), int(want_sdf), int(want_mom), C.byref(gt), st)
+            ws.launches += 2 if (want_sdf and M > 0) else 1
+        out = []
+        for i, gr in enumerate(grads):
+            live = need[i] and ((i < 10 and want_sdf) or (i >= 10 and want_mom))
+            out.append(gr if live else None)
+        return (None,) * 7 + tuple(out)
+
+
+def sdf_weights(macro, x, mask, params, h0=None, c0=None, normalized=False, precision="fp32",
+                weighted_loss=True):
+    """Inference path of SDFNetwork.forward / get_weights (src/model.py:221-281, :565-594):
+    weights [T,N] (demeaned, optionally |w|-normalised per month) and the final LSTM state."""
+    dev = x.device
+    T, N, F = x.shape
+    M = 0 if macro is None else macro.shape[1]
+    H = 0 if macro is None else params[1].shape[1]
+    with torch.cuda.device(dev):
+        st = _stream(dev)
+        ws = workspace(T, N, F, M, H, dev)
+        tens = _tensors(params)
+        save, a_t, c_t, hn, cn = macro_forward(ws, macro, params, h0, c0)
+        u = torch.empty(T, N, dtype=torch.float32, device=dev)
+        _lib.call("dlap_cell_fwd", ws.pp, _ptr(x), None, _ptr(mask), C.byref(tens), _ptr(a_t), _ptr(c_t),
+                  _ptr(u), None, _ptr(ws.row_part), _PRECISIONS[precision], 0.0, 0, st)
+        row_stats = torch.empty(T, RS_W, dtype=torch.float32, device=dev)
+        pr = torch.empty(T, dtype=torch.float32, device=dev)
+        scalars = torch.empty(SC_W, dtype=torch.float32, device=dev)
+        _lib.call("dlap_row_finish", ws.pp, _ptr(ws.row_part), int(weighted_loss), None, _ptr(row_stats),
+                  _ptr(pr), _ptr(scalars), st)
+        w = torch.empty(T, N, dtype=torch.float32, device=dev)
+        _lib.call("dlap_weights", ws.pp, _ptr(u), _ptr(mask), _ptr(row_stats), int(normalized), _ptr(w), st)
+        ws.launches += 3
+    return w, hn, cn, save

@@ -1,0 +1,298 @@
+"""Drop-in mirror of the reference's model classes (``src/model.py``) on the B200 kernels.
+
+Same constructors, same attribute names, same ``state_dict`` keys/shapes and the same default
+initialisation (real ``nn.LSTM`` / ``nn.Linear`` modules hold the parameters and are created in
+the reference's order, so ``torch.manual_seed(s)`` gives identical initial weights).  The math
+does not run through those modules: every forward goes through ``libdlap_b200.so``.
+
+Configurations outside the fast path raise ``NotImplementedError`` rather
+than silently taking another route; there is no CPU path.
+"""
+from __future__ import annotations
+
+from typing import Dict, List, Optional, Tuple
+
+import torch
+import torch.nn as nn
+
+from . import functional as Fn
+
+
+def _unsupported(what: str):
+    raise NotImplementedError(
+        f"{what} is outside the B200 fast path of this build (see DESIGN.md, 'out of scope'); "
+        "there is no fallback path.")
+
+
+def _hidden_pair(hidden, H, dev):
+    if hidden is None:
+        return None, None
+    h0, c0 = hidden
+    return Fn._flat_state(h0, H, dev), Fn._flat_state(c0, H, dev)
+
+
+class MacroLSTM(nn.Module):
+    """src/model.py:21-84."""
+
+    def __init__(self, input_dim: int, hidden_dims: List[int], dropout: float = 0.0):
+        super().__init__()
+        self.hidden_dims = hidden_dims
+        self.num_layers = len(hidden_dims)
+        self.lstm = nn.LSTM(input_size=input_dim, hidden_size=hidden_dims[-1],
+                            num_layers=self.num_layers, batch_first=True,
+                            dropout=dropout if self.num_layers > 1 else 0)
+        self.output_dim = hidden_dims[-1]
+
+    def _params(self):
+        if self.num_layers != 1:
+            _unsupported("a multi-layer macro LSTM")
+        if self.output_dim > 8:
+            _unsupported("an LSTM wider than 8 units")
+        l = self.lstm
+        return [l.weight_ih_l0, l.weight_hh_l0, l.bias_ih_l0, l.bias_hh_l0]
+
+    def forward(self, x: torch.Tensor, hidden=None):
+        """x [T, input_dim] -> (output [T, H], (h_n, c_n) each [1,1,H]).  Inference only when
+        called on its own (the training gradient flows through AssetPricingGAN.forward)."""
+        if not x.is_cuda or x.dtype != torch.float32 or not x.is_contiguous() or x.dim() != 2:
+            raise ValueError("macro features must be a contiguous float32 CUDA [T,M] tensor")
+        H = self.output_dim
+        lstm = [p.detach() for p in self._params()]
+        dev = x.device
+        T, M = x.shape
+        # stand-alone call: only the LSTM part of the macro kernel matters; feed neutral MLP params
+        z = lambda *s: torch.zeros(*s, dtype=torch.float32, device=dev)
+        params = lstm + [z(64, 1 + H), z(64), None, None, None, None, z(8, M + 1), z(8)]
+        h0, c0 = _hidden_pair(hidden, H, dev)
+        with torch.cuda.device(dev):
+            ws = Fn.workspace(T, 1, 1, M, H, dev)
+            save, _, _, hn, cn = Fn.macro_forward(ws, x, params, h0, c0)
+        return save[:, :H], (hn.view(1, 1, H), cn.view(1, 1, H))
+
+    def init_hidden(self, device: torch.device):
+        h0 = torch.zeros(self.num_layers, 1, self.hidden_dims[-1], device=device)
+        return (h0, torch.zeros_like(h0))
+
+
+class MomentNetwork(nn.Module):
+    """src/model.py:87-161.  Stand-alone calls on an arbitrary [T,N,D] tensor use torch ops
+    (this module is not on the step's hot path: AssetPricingGAN.forward fuses the moment net into
+    the per-cell kernel and never materialises its [T,N,M+F] input)."""
+
+    def __init__(self, input_dim: int, hidden_dims: List[int], num_moments: int,
+                 use_rnn: bool = False, rnn_hidden_dims: List[int] = None, dropout: float = 0.05):
+        super().__init__()
+        self.use_rnn = use_rnn
+        self.num_moments = num_moments
+        layers = []
+        prev = input_dim
+        for hd in hidden_dims:
+            layers += [nn.Linear(prev, hd), nn.ReLU(), nn.Dropout(dropout)]
+            prev = hd
+        self.fc_layers = nn.Sequential(*layers) if layers else nn.Identity()
+        self.output_proj = nn.Linear(prev if hidden_dims else input_dim, num_moments)
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        T, N, D = x.shape
+        h = x.view(T * N, D)
+        if not isinstance(self.fc_layers, nn.Identity):
+            h = self.fc_layers(h)
+        return torch.tanh(self.output_proj(h)).view(T, N, -1).permute(2, 0, 1)
+
+
+class SDFNetwork(nn.Module):
+    """src/model.py:164-281."""
+
+    def __init__(self, macro_dim: int, individual_dim: int, hidden_dims: List[int],
+                 use_rnn: bool = True, rnn_hidden_dims: List[int] = None, dropout: float = 0.05,
+                 normalize_weights: bool = True):
+        super().__init__()
+        self.use_rnn = use_rnn
+        self.normalize_weights = normalize_weights
+        self.macro_dim = macro_dim
+        self.individual_dim = individual_dim
+        self.dropout_p = float(dropout)
+        if use_rnn and rnn_hidden_dims and macro_dim > 0:
+            self.macro_lstm = MacroLSTM(input_dim=macro_dim, hidden_dims=rnn_hidden_dims, dropout=dropout)
+            processed = self.macro_lstm.output_dim
+        else:
+            self.macro_lstm = None
+            processed = macro_dim
+        layers = []
+        prev = processed + individual_dim
+        for hd in hidden_dims:
+            layers += [nn.Linear(prev, hd), nn.ReLU(), nn.Dropout(dropout)]
+            prev = hd
+        self.fc_layers = nn.Sequential(*layers)
+        self.output_proj = nn.Linear(prev, 1)
+        self._hidden_dims = list(hidden_dims)
+
+    # -- fast-path plumbing -------------------------------------------------------------------
+    def _mlp_params(self, with_macro: bool):
+        if self._hidden_dims != [64, 64]:
+            _unsupported(f"hidden_dim={self._hidden_dims} (only [64, 64])")
+        if not self.normalize_weights:
+            _unsupported("normalize_w=False")
+        if with_macro and self.macro_lstm is None:
+            _unsupported("macro features without the LSTM (use_rnn=False)")
+        if self.individual_dim > 64:
+            _unsupported("more than 64 characteristics")
+        fc0, fc3 = self.fc_layers[0], self.fc_layers[3]
+        exp_in = self.individual_dim + (self.macro_lstm.output_dim if with_macro else 0)
+        if fc0.in_features != exp_in:
+            raise ValueError("macro_features=None needs a model built with macro_feature_dim=0")
+        return [fc0.weight, fc0.bias, fc3.weight, fc3.bias, self.output_proj.weight, self.output_proj.bias]
+
+    def kernel_params(self, with_macro: bool):
+        lstm = self.macro_lstm._params() if with_macro else [None] * 4
+        return lstm + self._mlp_params(with_macro)
+
+    def forward(self, macro_features, individual_features, mask, hidden=None):
+        """-> (weights [T,N], new_hidden).  Stand-alone use is the inference path (no autograd
+        graph is attached to the returned weights)."""
+        return _weights(self, None, macro_features, individual_features, mask, hidden, False)
+
+
+def _weights(sdf: SDFNetwork, moment: Optional[MomentNetwork], macro, x, mask, hidden, normalized,
+             precision="fp32"):
+    Fn.check_panel(macro, x, None, mask)
+    with_macro = macro is not None
+    params = [p.detach() if p is not None else None for p in sdf.kernel_params(with_macro)]
+    dev = x.device
+    T, N, F = x.shape
+    M = macro.shape[1] if with_macro else 0
+    # the moment net takes no part in the weights; the kernel ABI still wants its two tensors
+    z = torch.zeros(8, M + F, dtype=torch.float32, device=dev), torch.zeros(8, dtype=torch.float32, device=dev)
+    H = sdf.macro_lstm.output_dim if with_macro else 0
+    h0, c0 = _hidden_pair(hidden, H, dev) if with_macro else (None, None)
+    w, hn, cn, _ = Fn.sdf_weights(macro, x, mask, params + list(z), h0, c0, normalized, precision)
+    new_hidden = (hn.view(1, 1, H), cn.view(1, 1, H)) if with_macro else None
+    return w, new_hidden
+
+
+class StepOutputs(dict):
+    """Forward dict of AssetPricingGAN (src/model.py:553-563).  ``moments`` [K,T,N] is produced on
+    first access: no caller in the reference reads it (src/train.py:96-103, :144-153) and writing
+    it every step would cost 32 B per stock-month."""
+
+    def __init__(self, *a, moments_fn=None, **kw):
+        super().__init__(*a, **kw)
+        self._moments_fn = moments_fn
+        dict.__setitem__(self, "moments", None)
+
+    def __getitem__(self, k):
+        v = dict.__getitem__(self, k)
+        if k == "moments" and v is None and self._moments_fn is not None:
+            v = self._moments_fn()
+            dict.__setitem__(self, k, v)
+        return v
+
+    def get(self, k, default=None):
+        return self[k] if k in self else default
+
+
+class AssetPricingGAN(nn.Module):
+    """src/model.py:284-617 (compute_residual_loss excluded: residual_loss_factor must be 0)."""
+
+    def __init__(self, config: Dict):
+        super().__init__()
+        self.config = config
+        rnn_hidden = config.get('num_units_rnn', [4])
+        if isinstance(rnn_hidden, int):
+            rnn_hidden = [rnn_hidden]
+        rnn_hidden_moment = config.get('num_units_rnn_moment', [32])
+        if isinstance(rnn_hidden_moment, int):
+            rnn_hidden_moment = [rnn_hidden_moment]
+        dropout = config.get('dropout', 0.05)
+        self.sdf_net = SDFNetwork(
+            macro_dim=config.get('macro_feature_dim', 0),
+            individual_dim=config['individual_feature_dim'],
+            hidden_dims=config.get('hidden_dim', [64, 64]),
+            use_rnn=config.get('use_rnn', True),
+            rnn_hidden_dims=rnn_hidden if config.get('use_rnn', True) else None,
+            dropout=dropout,
+            normalize_weights=config.get('normalize_w', True))
+        self._hidden_dim_moment = list(config.get('hidden_dim_moment', []))
+        self.moment_net = MomentNetwork(
+            input_dim=config.get('macro_feature_dim', 0) + config['individual_feature_dim'],
+            hidden_dims=self._hidden_dim_moment,
+            num_moments=config.get('num_condition_moment', 8),
+            use_rnn=config.get('use_rnn_moment', True),
+            rnn_hidden_dims=rnn_hidden_moment if config.get('use_rnn_moment', True) else None,
+            dropout=dropout)
+        self.residual_loss_factor = config.get('residual_loss_factor', 0.0)
+        self.weighted_loss = config.get('weighted_loss', True)
+        # kernel arithmetic of the per-cell contractions ("fp32" = exact FFMA)
+        self.precision = config.get('b200_precision', 'fp32')
+        self.month_shard: Optional[Fn.MonthShard] = None
+
+    # -- fast-path plumbing -------------------------------------------------------------------
+    def _kernel_params(self, with_macro: bool):
+        if self._hidden_dim_moment:
+            _unsupported("hidden layers in the moment network (hidden_dim_moment != [])")
+        if self.moment_net.num_moments != 8:
+            _unsupported("num_condition_moment != 8")
+        if self.residual_loss_factor > 0:
+            _unsupported("residual_loss_factor > 0")
+        mp = self.moment_net.output_proj
+        return self.sdf_net.kernel_params(with_macro) + [mp.weight, mp.bias]
+
+    def forward(self, macro_features, individual_features, returns, mask, hidden=None,
+                phase: str = 'conditional'):
+        Fn.check_panel(macro_features, individual_features, returns, mask)
+        with_macro = macro_features is not None
+        params = self._kernel_params(with_macro)
+        x = individual_features
+        dev = x.device
+        H = self.sdf_net.macro_lstm.output_dim if with_macro else 0
+        h0, c0 = _hidden_pair(hidden, H, dev) if with_macro else (None, None)
+        p_drop = self.sdf_net.dropout_p if self.training else 0.0
+        seed = int(torch.randint(0, 2 ** 62, (1,)).item()) if p_drop > 0 else 0   # CPU generator: no sync
+        opts = Fn.StepOptions(weighted_loss=bool(self.weighted_loss),
+                              need_moments=(phase != 'unconditional'), precision=self.precision,
+                              dropout_p=p_drop, dropout_seed=seed, shard=self.month_shard)
+        l_c, l_u, pr, w, sharpe, hn, cn = Fn.GanStepFn.apply(
+            opts, macro_features, x, returns, mask, h0, c0, *params)
+        zero = torch.zeros((), dtype=torch.float32, device=dev)
+        if phase == 'unconditional':            # src/model.py:524-528
+            loss_unc, loss_cond, total = l_u, zero, l_u
+        elif phase == 'moment':                 # src/model.py:530-535
+            loss_unc, loss_cond, total = zero, l_c, -l_c
+        else:                                   # src/model.py:537-541
+            loss_unc, loss_cond, total = l_u, l_c, l_c
+        if self.month_shard is not None:
+            pr, sharpe = _gather_months(pr, self.month_shard)
+        new_hidden = (hn.view(1, 1, H), cn.view(1, 1, H)) if with_macro else None
+
+        def moments():
+            mp = self.moment_net.output_proj
+            M = macro_features.shape[1] if with_macro else 0
+            pre = x @ mp.weight[:, M:].t()
+            bias = mp.bias if not with_macro else macro_features @ mp.weight[:, :M].t() + mp.bias
+            pre = pre + (bias[:, None, :] if with_macro else bias)
+            return torch.tanh(pre).permute(2, 0, 1)
+
+        return StepOutputs({
+            'weights': w, 'loss': total, 'loss_unconditional': loss_unc, 'loss_conditional': loss_cond,
+            'loss_residual': zero, 'sharpe': sharpe, 'portfolio_returns': pr, 'hidden': new_hidden,
+        }, moments_fn=moments)
+
+    def get_weights(self, macro_features, individual_features, mask, hidden=None, normalized: bool = False):
+        """src/model.py:565-594."""
+        return _weights(self.sdf_net, self.moment_net, macro_features, individual_features, mask, hidden,
+                        normalized, self.precision)
+
+    def get_sdf_factor(self, macro_features, individual_features, returns, mask, hidden=None,
+                       normalized: bool = True):
+        """src/model.py:596-617."""
+        w, _ = self.get_weights(macro_features, individual_features, mask, hidden, normalized=normalized)
+        return (w * returns * mask.float()).sum(dim=1)
+
+
+def _gather_months(pr_local, shard):
+    import torch.distributed as dist
+    full = torch.zeros(shard.T_total, dtype=pr_local.dtype, device=pr_local.device)
+    full[shard.t0:shard.t1] = pr_local.detach()
+    dist.all_reduce(full, group=shard.group)
+    sharpe = full.mean() / (full.std() + 1e-8)
+    return full, sharpe

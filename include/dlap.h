@@ -1,0 +1,167 @@
+/* dlap.h -- C ABI of libdlap_b200.so: the adversarial-SDF training step of
+ * omroot/DeepLearningInAssetPricing_PaperReplication as hand-written sm_100a kernels.
+ *
+ * The reference has no FFI of its own (pure Python): its boundary is the class
+ * API of src/model.py.  Each entry point below replaces the torch op sequence of the cited
+ * reference lines; the Python mirror of the class API
+ * (deeplearninginassetpricing_paperreplication_b200/model.py) is a thin ctypes caller of these.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer on the current CUDA device unless it says "host";
+ *     all floating-point data is fp32, row-major, contiguous; `mask` is torch.bool bytes (0/1);
+ *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream); calls only
+ *     enqueue work, they never synchronise and never allocate;
+ *   - return value: 0 = ok, negative = argument error (DLAP_E_*), positive = cudaError_t;
+ *   - all buffers are caller-owned; sizes come from dlap_make_plan().  Inputs are not mutated;
+ *   - no CPU fallback: on a machine without a CUDA device every compute call returns an error.
+ *
+ * Shapes: T months, N stocks, F characteristics (<= 64), M macro series, H LSTM units (<= 8),
+ * hidden widths 64/64 and 8 moments (the reference defaults, src/model.py:304-344).
+ */
+#ifndef DLAP_H
+#define DLAP_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DLAP_ABI_VERSION 1
+
+enum {
+  DLAP_OK = 0,
+  DLAP_E_NULL = -1,       /* a required pointer is NULL */
+  DLAP_E_SHAPE = -2,      /* dimension out of the supported range */
+  DLAP_E_ALIGN = -3,      /* pointer not aligned as required (16 B for x, 4 B for floats) */
+  DLAP_E_PLAN = -4,       /* plan does not belong to these dims */
+  DLAP_E_PRECISION = -5,  /* unknown precision selector */
+  DLAP_E_NODEVICE = -6,   /* no usable CUDA device */
+  DLAP_E_SMEM = -7        /* configuration needs more shared memory than one SM has */
+};
+
+/* arithmetic of the per-cell contractions */
+enum {
+  DLAP_PREC_FP32 = 0      /* exact fp32 FFMA */
+};
+
+typedef struct dlap_dims {
+  int32_t T, N, F, M, H;  /* M = 0: no macro input (src/model.py:243-257, macro_features=None) */
+} dlap_dims;
+
+/* Launch geometry and scratch sizes for one (dims, device).  Filled by dlap_make_plan. */
+typedef struct dlap_plan {
+  dlap_dims dims;
+  int32_t tpm;            /* tiles (128 stocks) per month */
+  int32_t grid_cell;      /* persistent CTAs of the per-cell kernels (= SM count) */
+  int32_t col_splits;     /* month chunks of the per-stock (column) reduction */
+  int32_t row_splits;     /* stock chunks of the per-month (row) reduction of dS */
+  int32_t ldw1;           /* row pitch of fc_layers.0.weight  = F + H (F when M = 0) */
+  int32_t ldwq;           /* row pitch of moment output_proj.weight = M + F */
+  int64_t row_part_bytes;   /* double [T, tpm, 4]           */
+  int64_t col_part_bytes;   /* double [col_splits, 10, N]   */
+  int64_t loss_part_bytes;  /* double [ceil(N/256), 2]      */
+  int64_t ds_part_bytes;    /* double [T, row_splits]       */
+  int64_t wpart_bytes;      /* float  [grid_cell, wstride]  */
+  int64_t dadc_part_bytes;  /* float  [T, tpm, 72]          */
+  int64_t lstm_save_bytes;  /* float  [T, 6H]               */
+  int64_t dpre_bytes;       /* float  [T, 4H]               */
+} dlap_plan;
+
+/* The twelve parameter tensors in the reference's state_dict order.
+ * LSTM pointers may be NULL when M = 0.  Used const for parameters, mutable for gradients. */
+typedef struct dlap_tensors {
+  float *w_ih, *w_hh, *b_ih, *b_hh;   /* sdf_net.macro_lstm.lstm.{weight_ih,weight_hh,bias_ih,bias_hh}_l0 */
+  float *w1, *b1;                     /* sdf_net.fc_layers.0.{weight [64,F+H], bias [64]} */
+  float *w2, *b2;                     /* sdf_net.fc_layers.3.{weight [64,64], bias [64]} */
+  float *w3, *b3;                     /* sdf_net.output_proj.{weight [1,64], bias [1]} */
+  float *wq, *bq;                     /* moment_net.output_proj.{weight [8,M+F], bias [8]} */
+} dlap_tensors;
+
+int dlap_abi_version(void);
+const char* dlap_error_string(int code);
+
+/* Geometry for a panel shape on CUDA device `device` (host-side, no GPU work). */
+int dlap_make_plan(const dlap_dims* dims, int device, dlap_plan* out);
+
+/* MacroLSTM.forward (src/model.py:50-73, nn.LSTM at :39-45) plus the two per-month biases that
+ * replace the tile-over-N concats: a_t = W1[:,F:].h_t + b1 (src/model.py:253-255, :211) and
+ * c_t = Wq[:,:M].macro_t + bq (src/model.py:514-516, :152).  h0/c0 [H] may be NULL (zero state).
+ * Outputs: lstm_save [T,6H] (h,c,i,f,g,o), a_t [T,64], c_t [T,8], hn/cn [H].  With M = 0 only
+ * a_t = b1 and c_t = bq are produced. */
+int dlap_macro_fwd(const dlap_plan* plan, const float* macro, const dlap_tensors* params,
+                   const float* h0, const float* c0, float* lstm_save, float* a_t, float* c_t,
+                   float* hn, float* cn, void* stream);
+
+/* SDFNetwork.forward body on every stock-month (src/model.py:251-271) and MomentNetwork.forward
+ * (src/model.py:132-161 with the input of :514-518): u = MLP(x | a_t) [T,N];
+ * g = tanh(Wqx.x + c_t) * R * m [8,T,N] (g NULL: moment net skipped, phase 'unconditional');
+ * row_part = per-tile sums of m, m u, m u R, m R.  R may be NULL (weights-only inference).
+ * dropout_p > 0 (model.train(), src/model.py:213, src/train.py:66): each hidden unit of each
+ * stock-month is dropped with probability round(p*65536)/65536 by a counter-based generator keyed
+ * on (dropout_seed, stock-month, layer, unit); pass the same seed to dlap_cell_bwd. */
+int dlap_cell_fwd(const dlap_plan* plan, const float* x, const float* R, const uint8_t* mask,
+                  const dlap_tensors* params, const float* a_t, const float* c_t, float* u,
+                  float* g, double* row_part, int precision, float dropout_p, uint64_t dropout_seed,
+                  void* stream);
+
+/* Per-month statistics: N_t, mu_t (src/model.py:276-278), P_t, portfolio return pr_t and
+ * S_t = 1 + pr_t (src/model.py:359-367, :380), Rbar_t; N_bar (src/model.py:360) and the Sharpe
+ * ratio of pr (src/model.py:551) into scalars[3], scalars[2].  n_bar_in (device, 1 float) overrides
+ * N_bar when the panel is one month-shard of a larger one; NULL otherwise. */
+int dlap_row_finish(const dlap_plan* plan, const double* row_part, int weighted_loss,
+                    const float* n_bar_in, float* row_stats, float* pr, float* scalars, void* stream);
+
+/* Per-stock sums over the months of each chunk: sum_t g_k S_t, sum_t R m S_t, sum_t m
+ * (src/model.py:376, :382, :428) into col_part [col_splits,10,N]; fused: the demeaned weights
+ * w = m (u - mu_t) (src/model.py:271-279) into w_out [T,N] when non-NULL.  g may be NULL. */
+int dlap_col_partial(const dlap_plan* plan, const float* g, const float* R, const uint8_t* mask,
+                     const float* u, const float* row_stats, double* col_part, float* w_out,
+                     void* stream);
+
+/* e_ki = colsum / T_i, L_c = mean_k mean_i e_ki^2, L_u = mean_i e0_i^2 (src/model.py:382-385,
+ * :428-431) -> e [9,N], t_i [N], scalars[0] = L_c, scalars[1] = L_u.  `nsplit` chunks are summed
+ * in order (1 after an all-reduce across month shards).  counter: one zero-initialised uint32. */
+int dlap_loss_finish(const dlap_plan* plan, const double* col_part, int nsplit, float* e, float* t_i,
+                     double* loss_part, uint32_t* counter, float* scalars, void* stream);
+
+/* Backward of the two losses (autograd at src/train.py:84): G_ki = gc 2 e_ki/(K N T_i),
+ * G0_i = gu 2 e0_i/(N T_i); gc/gu are device scalars = dL/dL_c, dL/dL_u (NULL = 0). -> G [9,N] */
+int dlap_loss_coeff(const dlap_plan* plan, const float* e, const float* t_i, const float* gc,
+                    const float* gu, float* G, void* stream);
+
+/* dS_t partials = sum_i (sum_k G_ki g_kti + G0_i R m) -> dS_part [T,row_splits] */
+int dlap_ds_rows(const dlap_plan* plan, const float* g, const float* R, const uint8_t* mask,
+                 const float* G, double* dS_part, void* stream);
+
+/* Per-cell backward with activation recompute (autograd of src/model.py:261-279
+ * and :152-153).  want_sdf / want_mom select the parameter groups (requires_grad semantics of
+ * src/train.py:309-312).  dpr_cot [T] = extra cotangent of portfolio_returns or NULL.
+ * Outputs: wpart (per-CTA weight-gradient partials), dadc_part (per-tile da_t | dc_t). */
+int dlap_cell_bwd(const dlap_plan* plan, const float* x, const float* R, const uint8_t* mask,
+                  const dlap_tensors* params, const float* a_t, const float* c_t,
+                  const float* row_stats, const double* dS_part, const float* dpr_cot,
+                  const float* G, const float* scalars, int weighted_loss, int want_sdf,
+                  int want_mom, float* wpart, float* dadc_part, int precision, float dropout_p,
+                  uint64_t dropout_seed, void* stream);
+
+/* Fixed-order sum of the partials into the reference's gradient layouts: grads->w1[:, :F], w2, b2,
+ * w3, b3 (= 0, demeaning), wq[:, M:]; and dadc [T,72] = da_t | dc_t summed over stocks. */
+int dlap_grad_finish(const dlap_plan* plan, const float* wpart, const float* dadc_part, int want_sdf,
+                     int want_mom, const dlap_tensors* grads, float* dadc, void* stream);
+
+/* Month-level backward: dh_t = W1[:,F:]^T da_t, LSTM BPTT, and the month-summed gradients
+ * grads->{w_ih,w_hh,b_ih,b_hh}, w1[:, F:], b1, wq[:, :M], bq.  dpre [T,4H] is scratch. */
+int dlap_macro_bwd(const dlap_plan* plan, const float* macro, const dlap_tensors* params,
+                   const float* h0, const float* c0, const float* lstm_save, const float* dadc,
+                   float* dpre, int want_sdf, int want_mom, const dlap_tensors* grads, void* stream);
+
+/* get_weights (src/model.py:565-594): w = m (u - mu_t); normalized != 0 divides each month by
+ * clamp(sum_i |w| m, 1e-8) (the Python loop of :586-590). */
+int dlap_weights(const dlap_plan* plan, const float* u, const uint8_t* mask, const float* row_stats,
+                 int normalized, float* w_out, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DLAP_H */

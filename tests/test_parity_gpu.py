@@ -1,0 +1,362 @@
+"""GPU parity tests proper: the CUDA path (through the C ABI) against the oracle and the goldens
+written by the reference itself.  Tolerances are BASELINE.json's: 1e-5 relative on losses,
+1e-4 on weights (relative to the largest weight), mask/index logic exact."""
+import ctypes as C
+
+import numpy as np
+import pytest
+import torch
+
+from _dlap_testlib import PHASES, golden_params, load_golden, rel_err
+from deeplearninginassetpricing_paperreplication_b200 import AssetPricingGAN, _lib
+from deeplearninginassetpricing_paperreplication_b200 import functional as Fn
+from oracle import closed_form as cf
+
+pytestmark = pytest.mark.gpu
+LOSS_RTOL = 1e-5
+WEIGHT_TOL = 1e-4
+GRAD_TOL = 2e-4     # fp32 path: relative to the largest entry of each gradient tensor
+
+
+def dev():
+    return torch.device("cuda:0")
+
+
+def _model_from(params, M, F=46, **cfg):
+    model = AssetPricingGAN({"macro_feature_dim": M, "individual_feature_dim": F, **cfg})
+    model.load_state_dict({k: torch.as_tensor(v) for k, v in params.items()})
+    return model.to(dev())
+
+
+def _panel(g):
+    d = dev()
+    hidden = None
+    if "h0" in g:
+        hidden = (torch.from_numpy(g["h0"]).to(d), torch.from_numpy(g["c0"]).to(d))
+    return (torch.from_numpy(g["macro"]).to(d), torch.from_numpy(g["x"]).to(d),
+            torch.from_numpy(g["R"]).to(d), torch.from_numpy(g["mask"]).to(d), hidden)
+
+
+def make_panel(T, N, M=178, F=46, seed=0, valid=0.4):
+    g = torch.Generator().manual_seed(seed)
+    mask = torch.rand(T, N, generator=g) < valid
+    x = torch.randn(T, N, F, generator=g).clamp_(-2, 2) * mask[:, :, None]
+    R = 0.1 * torch.randn(T, N, generator=g) * mask
+    macro = torch.randn(T, M, generator=g) if M else None
+    return macro, x, R, mask
+
+
+def _np(t):
+    return None if t is None else t.detach().cpu().numpy()
+
+
+def _check_against_cf(model, macro, x, R, mask, phase, hidden=None, grad_tol=GRAD_TOL):
+    d = dev()
+    params = {k: _np(v) for k, v in model.state_dict().items()}
+    model.zero_grad(set_to_none=True)
+    frozen = phase == "moment"
+    for p in model.sdf_net.parameters():
+        p.requires_grad = not frozen
+    to = lambda t: None if t is None else t.to(d)
+    hid = None if hidden is None else (hidden[0].to(d), hidden[1].to(d))
+    out = model(to(macro), to(x), to(R), to(mask), hidden=hid, phase=phase)
+    out["loss"].backward()
+    torch.cuda.synchronize()
+    h0 = None if hidden is None else _np(hidden[0]).reshape(-1)
+    c0 = None if hidden is None else _np(hidden[1]).reshape(-1)
+    ref = cf.forward(params, _np(macro), _np(x), _np(R), _np(mask), h0=h0, c0=c0, phase=phase)
+    gref = cf.backward(params, _np(macro), _np(x), _np(R), _np(mask), ref, phase=phase)
+    w = _np(out["weights"])
+    assert np.all(w[~_np(mask)] == 0.0), "masked cells must be exactly zero"
+    assert rel_err(w, ref["weights"]) < WEIGHT_TOL
+    assert rel_err(_np(out["portfolio_returns"]), ref["portfolio_returns"]) < WEIGHT_TOL
+    for key in ("loss", "loss_unconditional", "loss_conditional"):
+        a, b = float(out[key]), float(ref[key])
+        assert abs(a - b) <= LOSS_RTOL * abs(b) + 1e-30, (key, a, b)
+    if x.shape[0] > 1:
+        assert abs(float(out["sharpe"]) - float(ref["sharpe"])) <= 1e-4 * abs(float(ref["sharpe"])) + 1e-7
+    for k, p in model.named_parameters():
+        is_mom = k.startswith("moment_net")
+        expect = (is_mom and phase != "unconditional") or (not is_mom and phase != "moment")
+        if not expect:
+            assert p.grad is None, k
+            continue
+        assert p.grad is not None, k
+        r = gref[k].reshape(p.shape)
+        if k == "sdf_net.output_proj.bias":
+            assert float(p.grad.abs().max()) < 1e-9     # identically zero (demeaning)
+            continue
+        scale = max(np.abs(r).max(), 1e-30)
+        err = np.abs(_np(p.grad) - r).max() / scale
+        assert err < grad_tol, (k, err)
+    for p in model.sdf_net.parameters():
+        p.requires_grad = True
+    return out, ref
+
+
+# ---- stage-level checks through the raw C ABI ------------------------------------------------------
+def test_macro_fwd_stage():
+    g = load_golden("rand_small")
+    params = golden_params(g)
+    model = _model_from(params, 178)
+    macro = torch.from_numpy(g["macro"]).to(dev())
+    out, (hn, cn) = model.sdf_net.macro_lstm(macro)
+    hs, saved = cf.lstm_forward({k: v.astype(np.float64) for k, v in params.items()}, g["macro"].astype(np.float64))
+    assert np.abs(_np(out) - hs).max() < 2e-6
+    assert np.abs(_np(hn).reshape(-1) - saved["hn"]).max() < 2e-6
+    assert np.abs(_np(cn).reshape(-1) - saved["cn"]).max() < 2e-6
+
+
+def test_forward_stages_rand_small():
+    g = load_golden("rand_small")
+    params = golden_params(g)
+    model = _model_from(params, 178).eval()
+    macro, x, R, mask, _ = _panel(g)
+    T, N, F = x.shape
+    ref = cf.forward(params, g["macro"], g["x"], g["R"], g["mask"])
+    s = ref["_saved"]
+    kp = [p.detach() for p in model._kernel_params(True)]
+    ws = Fn.workspace(T, N, F, 178, 4, dev())
+    save, a_t, c_t, hn, cn = Fn.macro_forward(ws, macro, kp, None, None)
+    assert np.abs(_np(a_t) - s["a"]).max() < 5e-6
+    assert np.abs(_np(c_t) - s["c"]).max() < 2e-5
+    tens = Fn._tensors(kp)
+    u = torch.empty(T, N, device=dev()); gq = torch.empty(8, T, N, device=dev())
+    _lib.call("dlap_cell_fwd", ws.pp, x.data_ptr(), R.data_ptr(), mask.data_ptr(), C.byref(tens),
+              a_t.data_ptr(), c_t.data_ptr(), u.data_ptr(), gq.data_ptr(), ws.row_part.data_ptr(), 0, 0.0, 0,
+              None)
+    torch.cuda.synchronize()
+    assert np.abs(_np(u) - s["u"]).max() < 1e-5 * max(1.0, np.abs(s["u"]).max())
+    gref = np.transpose(s["q"], (2, 0, 1)) * s["rm"][None]
+    assert np.abs(_np(gq) - gref).max() < 1e-6
+    rp = _np(ws.row_part)[: T * ws.plan.tpm * 4].reshape(T, ws.plan.tpm, 4).sum(axis=1)
+    m = s["m"]
+    assert np.array_equal(rp[:, 0], m.sum(axis=1))          # counts are exact integers
+    assert np.abs(rp[:, 1] - (m * s["u"]).sum(axis=1)).max() < 1e-4
+    assert np.abs(rp[:, 3] - s["rm"].sum(axis=1)).max() < 1e-6
+
+
+# ---- full step against the reference's own outputs ---------------------------------------------------
+@pytest.mark.parametrize("phase", PHASES)
+def test_step_matches_reference_goldens(golden, phase):
+    params = golden_params(golden)
+    M = golden["macro"].shape[1]
+    model = _model_from(params, M).eval()
+    macro, x, R, mask, hidden = _panel(golden)
+    frozen = phase == "moment"
+    for p in model.sdf_net.parameters():
+        p.requires_grad = not frozen
+    out = model(macro, x, R, mask, hidden=hidden, phase=phase)
+    out["loss"].backward()
+    torch.cuda.synchronize()
+    for key in ("loss", "loss_unconditional", "loss_conditional"):
+        a, b = float(out[key]), float(golden[f"{phase}/{key}"])
+        assert abs(a - b) <= LOSS_RTOL * abs(b) + 1e-30, (key, a, b)
+    assert rel_err(_np(out["weights"]), golden[f"{phase}/weights"]) < WEIGHT_TOL
+    assert np.all(_np(out["weights"])[~golden["mask"]] == 0.0)
+    assert rel_err(_np(out["portfolio_returns"]), golden[f"{phase}/portfolio_returns"]) < WEIGHT_TOL
+    assert abs(float(out["sharpe"]) - float(golden[f"{phase}/sharpe"])) < 1e-4 * abs(float(golden[f"{phase}/sharpe"])) + 1e-7
+    assert np.abs(_np(out["hidden"][0]) - golden[f"{phase}/hidden_h"]).max() < 2e-6
+    assert np.abs(_np(out["hidden"][1]) - golden[f"{phase}/hidden_c"]).max() < 2e-6
+    assert tuple(out["hidden"][0].shape) == (1, 1, 4)
+    seen = 0
+    for k, p in model.named_parameters():
+        gk = f"{phase}/grad/{k}"
+        if gk not in golden:
+            assert p.grad is None, k
+            continue
+        seen += 1
+        ref = golden[gk]
+        if k == "sdf_net.output_proj.bias":
+            continue
+        err = np.abs(_np(p.grad) - ref).max() / max(np.abs(ref).max(), 1e-30)
+        assert err < 1e-3, (k, err)        # the reference's own fp32 autograd noise is ~1e-4 here
+    assert seen >= 2
+    if phase == "conditional":
+        q = out["moments"]
+        assert tuple(q.shape) == golden["moments"].shape
+        assert np.abs(_np(q) - golden["moments"]).max() < 2e-6
+
+
+def test_normalized_weights_match_reference(golden):
+    params = golden_params(golden)
+    model = _model_from(params, golden["macro"].shape[1]).eval()
+    macro, x, R, mask, hidden = _panel(golden)
+    with torch.no_grad():
+        wn, new_hidden = model.get_weights(macro, x, mask, hidden=hidden, normalized=True)
+        w, _ = model.get_weights(macro, x, mask, hidden=hidden)
+        w2, _ = model.sdf_net(macro, x, mask, hidden)
+        f = model.get_sdf_factor(macro, x, R, mask, hidden=hidden)
+    assert rel_err(_np(wn), golden["normalized_weights"]) < WEIGHT_TOL
+    assert rel_err(_np(w), golden["conditional/weights"]) < WEIGHT_TOL
+    assert torch.equal(w, w2)
+    assert rel_err(_np(f), golden["sdf_factor"]) < WEIGHT_TOL
+    live = golden["mask"].any(axis=1)
+    s = (np.abs(_np(wn)) * golden["mask"]).sum(axis=1)
+    assert np.allclose(s[live & (np.abs(golden["conditional/weights"]).sum(axis=1) > 1e-6)], 1.0, atol=1e-5)
+
+
+# ---- oracle parity on shapes the goldens do not cover ---------------------------------------------------
+@pytest.mark.parametrize("T,N,M", [(1, 1, 8), (3, 127, 8), (5, 129, 178), (7, 1000, 178), (2, 257, 3),
+                                   (16, 513, 178)])
+@pytest.mark.parametrize("phase", PHASES)
+def test_step_vs_oracle_shapes(T, N, M, phase):
+    macro, x, R, mask = make_panel(T, N, M, seed=T * 1000 + N)
+    if T > 2:
+        mask[1] = False                 # an empty month
+    if N > 3:
+        mask[:, 2] = False              # a never-valid stock
+    x = x * mask[:, :, None]; R = R * mask
+    torch.manual_seed(N)
+    model = AssetPricingGAN({"macro_feature_dim": M, "individual_feature_dim": 46}).to(dev()).eval()
+    _check_against_cf(model, macro, x, R, mask, phase)
+
+
+def test_no_macro_and_other_feature_counts():
+    for F in (46, 13, 64):
+        _, x, R, mask = make_panel(6, 200, 0, F=F, seed=F)
+        torch.manual_seed(1)
+        model = AssetPricingGAN({"individual_feature_dim": F}).to(dev()).eval()
+        _check_against_cf(model, None, x, R, mask, "conditional")
+        macro, x, R, mask = make_panel(6, 200, 20, F=F, seed=F)
+        model = AssetPricingGAN({"individual_feature_dim": F, "macro_feature_dim": 20,
+                                 "num_units_rnn": [6]}).to(dev()).eval()
+        _check_against_cf(model, macro, x, R, mask, "conditional")
+
+
+def test_unaligned_panel_view():
+    """x as a view whose first element is only 8-byte aligned, odd N: exercises the copy shift."""
+    macro, x, R, mask = make_panel(5, 131, 8, seed=9)
+    d = dev()
+    big = torch.zeros(5 * 131 * 46 + 2, device=d)
+    xv = big[2:].view(5, 131, 46)
+    xv.copy_(x)
+    assert xv.data_ptr() % 16 == 8
+    torch.manual_seed(2)
+    model = AssetPricingGAN({"macro_feature_dim": 8, "individual_feature_dim": 46}).to(d).eval()
+    o1 = model(macro.to(d), xv, R.to(d), mask.to(d))
+    o2 = model(macro.to(d), x.to(d), R.to(d), mask.to(d))
+    assert torch.equal(o1["weights"], o2["weights"]) and torch.equal(o1["loss"], o2["loss"])
+
+
+def test_all_masked_panel():
+    macro, x, R, mask = make_panel(4, 150, 8, seed=1)
+    mask[:] = False
+    x = x * 0; R = R * 0
+    model = AssetPricingGAN({"macro_feature_dim": 8, "individual_feature_dim": 46}).to(dev()).eval()
+    out = model(macro.to(dev()), x.to(dev()), R.to(dev()), mask.to(dev()))
+    out["loss"].backward()
+    assert float(out["loss"]) == 0.0 and float(out["weights"].abs().max()) == 0.0
+    assert all(torch.isfinite(p.grad).all() for p in model.parameters() if p.grad is not None)
+
+
+def test_bit_reproducible():
+    macro, x, R, mask = make_panel(12, 700, 178, seed=4)
+    d = dev()
+    torch.manual_seed(3)
+    model = AssetPricingGAN({"macro_feature_dim": 178, "individual_feature_dim": 46}).to(d).eval()
+    args = (macro.to(d), x.to(d), R.to(d), mask.to(d))
+    res = []
+    for _ in range(2):
+        model.zero_grad(set_to_none=True)
+        out = model(*args)
+        out["loss"].backward()
+        res.append((out["loss"].clone(), out["weights"].clone(), [p.grad.clone() for p in model.parameters()]))
+    assert torch.equal(res[0][0], res[1][0]) and torch.equal(res[0][1], res[1][1])
+    assert all(torch.equal(a, b) for a, b in zip(res[0][2], res[1][2]))
+
+
+def test_grad_accumulates_and_cotangents():
+    """loss.backward() accumulates into .grad like autograd; gradients are linear in the cotangent."""
+    macro, x, R, mask = make_panel(6, 300, 8, seed=5)
+    d = dev()
+    torch.manual_seed(3)
+    model = AssetPricingGAN({"macro_feature_dim": 8, "individual_feature_dim": 46}).to(d).eval()
+    args = (macro.to(d), x.to(d), R.to(d), mask.to(d))
+    model(*args)["loss"].backward()
+    g1 = [p.grad.clone() for p in model.parameters()]
+    (2.0 * model(*args)["loss"]).backward()
+    for p, a in zip(model.parameters(), g1):
+        assert torch.allclose(p.grad, 3.0 * a, rtol=1e-5, atol=1e-12)
+    # loss_unconditional and portfolio_returns are differentiable outputs too
+    model.zero_grad(set_to_none=True)
+    out = model(*args)
+    (out["loss_unconditional"] + out["portfolio_returns"].sum() * 1e-3).backward()
+    assert model.sdf_net.output_proj.weight.grad.abs().max() > 0
+
+
+def test_trajectory_matches_oracle():
+    """Five Adam steps of phase 1 then five of phase 3 (dropout 0): losses track the CPU oracle."""
+    from oracle import torch_port as tp
+    macro, x, R, mask = make_panel(24, 400, 8, seed=6)
+    d = dev()
+    torch.manual_seed(5)
+    model = AssetPricingGAN({"macro_feature_dim": 8, "individual_feature_dim": 46, "dropout": 0.0}).to(d)
+    ref = {k: v.detach().cpu().clone().requires_grad_(True) for k, v in model.state_dict().items()}
+    opt = torch.optim.Adam(model.sdf_net.parameters(), lr=1e-3)
+    ropt = torch.optim.Adam([ref[k] for k in tp.SDF_KEYS], lr=1e-3)
+    args = (macro.to(d), x.to(d), R.to(d), mask.to(d))
+    for phase in ["unconditional"] * 5 + ["conditional"] * 5:
+        model.train()
+        opt.zero_grad(); ropt.zero_grad()
+        out = model(*args, phase=phase)
+        out["loss"].backward()
+        torch.nn.utils.clip_grad_norm_(model.sdf_net.parameters(), 1.0)
+        opt.step()
+        rout = tp.forward(ref, macro, x, R, mask, phase=phase)
+        rout["loss"].backward()
+        torch.nn.utils.clip_grad_norm_([ref[k] for k in tp.SDF_KEYS], 1.0)
+        ropt.step()
+        a, b = float(out["loss"]), float(rout["loss"])
+        assert abs(a - b) <= 1e-4 * abs(b), (phase, a, b)
+
+
+def test_dropout_train_mode():
+    macro, x, R, mask = make_panel(8, 600, 8, seed=7)
+    d = dev()
+    torch.manual_seed(5)
+    model = AssetPricingGAN({"macro_feature_dim": 8, "individual_feature_dim": 46, "dropout": 0.05}).to(d)
+    args = (macro.to(d), x.to(d), R.to(d), mask.to(d))
+    model.eval()
+    base = model(*args)
+    model.train()
+    torch.manual_seed(11); o1 = model(*args)
+    torch.manual_seed(11); o2 = model(*args)
+    torch.manual_seed(12); o3 = model(*args)
+    assert torch.equal(o1["weights"], o2["weights"])              # same seed -> same mask
+    assert not torch.equal(o1["weights"], o3["weights"])
+    assert not torch.equal(o1["weights"], base["weights"])
+    rel = float((o1["weights"] - base["weights"]).abs().max() / base["weights"].abs().max())
+    assert 1e-3 < rel < 2.0
+    # forward/backward use the same mask: directional derivative along W3 matches the gradient
+    w3 = model.sdf_net.output_proj.weight
+    torch.manual_seed(11)
+    model.zero_grad(set_to_none=True)
+    l0 = model(*args, phase="unconditional")["loss"]; l0.backward()
+    gdir = w3.grad.clone()
+    direction = torch.randn_like(w3)
+    eps = 1e-2
+    with torch.no_grad():
+        w3.add_(eps * direction)
+    torch.manual_seed(11); lp = model(*args, phase="unconditional")["loss"]
+    with torch.no_grad():
+        w3.add_(-2 * eps * direction)
+    torch.manual_seed(11); lm = model(*args, phase="unconditional")["loss"]
+    fd = float(lp - lm) / (2 * eps)
+    an = float((gdir * direction).sum())
+    assert abs(fd - an) <= 5e-2 * abs(an) + 1e-9, (fd, an)
+
+
+def test_errors_are_loud():
+    d = dev()
+    macro, x, R, mask = make_panel(4, 50, 8, seed=8)
+    model = AssetPricingGAN({"macro_feature_dim": 8, "individual_feature_dim": 46}).to(d)
+    with pytest.raises(ValueError):
+        model(macro.to(d), x.to(d).double(), R.to(d), mask.to(d))
+    with pytest.raises(ValueError):
+        model(macro.to(d), x.to(d).transpose(0, 1), R.to(d), mask.to(d))
+    for cfg in ({"hidden_dim": [64, 32]}, {"hidden_dim_moment": [32]}, {"use_rnn": False},
+                {"residual_loss_factor": 0.1}, {"normalize_w": False}, {"num_units_rnn": [4, 4]}):
+        bad = AssetPricingGAN({"macro_feature_dim": 8, "individual_feature_dim": 46, **cfg}).to(d)
+        with pytest.raises(NotImplementedError):
+            bad(macro.to(d), x.to(d), R.to(d), mask.to(d))
