@@ -1,0 +1,273 @@
+#!/usr/bin/env python
+"""Benchmark of the adversarial-SDF step (BASELINE.json metric: stock-months/s per fwd+bwd GAN
+step, and % of HBM roofline, next to the reference CPU path).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+One step = model.zero_grad(); out = model(panel, phase='conditional'); out['loss'].backward()
+(src/train.py:77-84) on the paper-shape synthetic panel T=240, N=10,000, 46 characteristics,
+178 macro series (BASELINE.json configs[1]); dropout disabled (the parity configuration).
+Under torchrun (N > 1) every rank owns 240 months of a 240*N-month panel (weak scaling, month
+sharding); the value is all ranks' stock-months / max-over-ranks device time.
+
+Prints ONE JSON line on rank 0.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+T_MONTHS, N_STOCKS, F_CHARS, M_MACRO = 240, 10_000, 46, 178
+ALGO_BYTES_FWD = 46 * 4 + 4 + 1          # x + R + mask per stock-month
+ALGO_BYTES_STEP = 2 * ALGO_BYTES_FWD     # forward + recomputing backward
+CPU_SAMPLE_N = 2_500                     # stocks in the CPU sample (cost is linear in T*N)
+
+
+def synthetic_panel(T, N, F, M, seed, valid=0.4):
+    """SURVEY.md §8d generator: Bernoulli(0.40) mask, N(0,1) characteristics clipped to [-2,2],
+    returns N(0, 0.1^2), both zero-filled where masked (src/data_loader.py:61-65), z-scored macro."""
+    g = torch.Generator().manual_seed(seed)
+    mask = torch.rand(T, N, generator=g) < valid
+    x = torch.randn(T, N, F, generator=g).clamp_(-2, 2) * mask[:, :, None]
+    R = 0.1 * torch.randn(T, N, generator=g) * mask
+    macro = torch.randn(T, M, generator=g)
+    return macro, x, R, mask
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks + throttle reasons during the timed region (B200_PROFILING.md)."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.rows, self._halt = index, [], threading.Event()
+
+    def run(self):
+        while not self._halt.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
+                                      "--format=csv,noheader,nounits"], capture_output=True, text=True,
+                                     timeout=5).stdout.strip()
+                if out:
+                    self.rows.append([c.strip() for c in out.split(",")])
+            except Exception:
+                pass
+            self._halt.wait(0.1)
+
+    def stop(self):
+        self._halt.set()
+        self.join(timeout=6)
+        sm = sorted(int(r[0]) for r in self.rows if r and r[0].isdigit())
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({n for r in self.rows for n, v in zip(names, r[2:6]) if v.lower().startswith("active")})
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None,
+                "sm_max_mhz": int(self.rows[0][1]) if self.rows and self.rows[0][1].isdigit() else None,
+                "reasons": reasons, "samples": len(self.rows)}
+
+
+def hbm_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return float(json.load(open(p))["hbm_gbs"]), "measured"
+    return 6650.0, "fallback"
+
+
+def ncu_traffic():
+    p = os.path.join(ROOT, "profiles", "dominant_kernel.json")
+    if os.path.exists(p):
+        return json.load(open(p)).get("dram_bytes_per_launch")
+    return None
+
+
+def cpu_step_rate(threads=None, budget_s=20.0, min_steps=2, max_steps=5, warmup=1, steps=None):
+    """The oracle port (torch CPU restatement of src/model.py, autograd backward) timed on the host
+    cores: stock-months/s of fwd+bwd, phase 'conditional', dropout off."""
+    from oracle import torch_port as tp
+    if threads:
+        torch.set_num_threads(threads)
+    macro, x, R, mask = synthetic_panel(T_MONTHS, CPU_SAMPLE_N, F_CHARS, M_MACRO, seed=1234)
+    params = tp.init_params(M_MACRO, F_CHARS, seed=42)
+
+    def one():
+        t0 = time.perf_counter()
+        tp.step(params, macro, x, R, mask, phase="conditional")
+        return time.perf_counter() - t0
+
+    first = [one() for _ in range(max(warmup, 1))][-1]
+    if steps is None:
+        steps = int(min(max_steps, max(min_steps, budget_s / max(first, 1e-3))))
+    times = [one() for _ in range(steps)]
+    best, mean = min(times), sum(times) / len(times)
+    cells = T_MONTHS * CPU_SAMPLE_N
+    return {"rate_best": cells / best, "rate_mean": cells / mean, "ms_per_step": 1e3 * mean, "steps": steps,
+            "cores": torch.get_num_threads(), "host_cpus": os.cpu_count(),
+            "sample": f"T={T_MONTHS} N={CPU_SAMPLE_N} slice of the workload, {steps} timed steps after "
+                      f"{max(warmup, 1)} warm-up (cost is linear in T*N)"}
+
+
+def run_reference(args, rank):
+    if rank != 0:
+        return
+    r = cpu_step_rate(warmup=args.warmup, steps=args.steps)
+    line = {
+        "impl": "reference", "metric": "stock-months/sec per fwd+bwd GAN step", "value": r["rate_mean"],
+        "unit": "stock-months/s", "n_gpus": args.gpus, "steps": r["steps"], "warmup": max(args.warmup, 1),
+        "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"paper-shape panel T={T_MONTHS} N={N_STOCKS} F={F_CHARS} M={M_MACRO}, "
+                               "phase 'conditional' fwd+bwd, dropout 0; timed on a bounded sample"},
+        "cpu_baseline": {"value": r["rate_mean"], "unit": "stock-months/s", "cores": r["cores"], "kind": "port",
+                         "sample": r["sample"]},
+        "e2e": {"value": r["rate_mean"], "unit": "stock-months/s", "h2d_bytes_per_step": 0,
+                "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line))
+
+
+def run_ours(args, rank, world):
+    from deeplearninginassetpricing_paperreplication_b200 import AssetPricingGAN
+    from deeplearninginassetpricing_paperreplication_b200 import functional as Fn
+    import torch.distributed as dist
+
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    dev = torch.device("cuda", local)
+    torch.cuda.set_device(dev)
+    T, N = T_MONTHS, N_STOCKS
+    T_total = T * world
+    macro_all = torch.randn(T_total, M_MACRO, generator=torch.Generator().manual_seed(99))
+    _, x, R, mask = synthetic_panel(T, N, F_CHARS, M_MACRO, seed=1234 + rank)
+    torch.manual_seed(42)
+    model = AssetPricingGAN({"macro_feature_dim": M_MACRO, "individual_feature_dim": F_CHARS,
+                             "dropout": 0.0, "b200_precision": args.precision}).to(dev)
+    model.train()
+    host = [t.pin_memory() for t in (macro_all, x, R, mask)]
+    d_macro, d_x, d_R, d_mask = [t.to(dev) for t in host]
+    if world > 1:
+        n_t = d_mask.sum(dim=1).clamp(min=1).float().sum().reshape(1)
+        dist.all_reduce(n_t)
+        model.month_shard = Fn.MonthShard(group=dist.group.WORLD, t0=rank * T, t1=(rank + 1) * T,
+                                          T_total=T_total, n_bar=(n_t / T_total).contiguous())
+
+    def step(inputs):
+        model.zero_grad(set_to_none=True)
+        out = model(*inputs, phase="conditional")
+        out["loss"].backward()
+        return out
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, k):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(k):
+            fn()
+        e1.record()
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms)
+
+    resident = (d_macro, d_x, d_R, d_mask)
+    for _ in range(max(args.warmup, 3)):
+        step(resident)
+    ws = Fn.workspace(T, N, F_CHARS, M_MACRO, 4, dev)
+    sampler = ClockSampler(local)
+    sampler.start()
+    l0 = sum(w.launches for w in Fn._workspaces.values())
+    Fn.kernel_timer = Fn.KernelTimer("dlap_cell_bwd")
+    ms = timed(lambda: step(resident), args.steps)
+    timer, Fn.kernel_timer = Fn.kernel_timer, None
+    launches = sum(w.launches for w in Fn._workspaces.values()) - l0
+    clocks = sampler.stop()
+    cells = T * N * world
+    value = cells * args.steps / (ms * 1e-3)
+
+    # end to end: pinned host panel -> device every step, loss read back every step
+    def e2e_step():
+        ins = [t.to(dev, non_blocking=True) for t in host]
+        out = step(ins)
+        return out["loss"].item()
+
+    for _ in range(2):
+        e2e_step()
+    k2 = max(3, min(args.steps, 10))
+    ms2 = timed(e2e_step, k2)
+    h2d = sum(t.numel() * t.element_size() for t in host)
+    e2e = cells * k2 / (ms2 * 1e-3)
+
+    if rank != 0:
+        return
+    peak, peak_kind = hbm_peak()
+    k_ms = timer.mean_ms()
+    achieved = ALGO_BYTES_FWD * T * N / (k_ms * 1e-3) / 1e9
+    line = {
+        "metric": "stock-months/sec per fwd+bwd GAN step", "value": value, "unit": "stock-months/s",
+        "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32" if args.precision == "fp32" else args.precision, "data": "synthetic",
+        "config": {"workload": f"paper-shape panel T={T} N={N} F={F_CHARS} M={M_MACRO} per GPU "
+                               f"(BASELINE.json configs[1]); phase 'conditional' fwd+bwd, dropout 0, "
+                               f"hidden [64,64], rnn [4], 8 moments; months sharded across {world} GPU(s)",
+                   "l2": "inputs (442 MB panel per GPU) larger than the 126 MB L2; no flush needed",
+                   "precision": args.precision},
+        "clocks": clocks,
+        "e2e": {"value": e2e, "unit": "stock-months/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
+                "ms_per_step": ms2 / k2},
+        "gpu_launches": launches,
+        "roofline": {"bound": "hbm", "kernel": "cell_bwd (recomputing per-cell backward)",
+                     "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                     "peak_kind": peak_kind, "kernel_ms": k_ms, "kernel_share_of_step": k_ms * args.steps / ms,
+                     "traffic": ncu_traffic(),
+                     "step_frac": value * ALGO_BYTES_STEP / 1e9 / peak,
+                     "note": "algorithmic bytes = 189 B per stock-month per launch (x, R, mask read once); "
+                             "step_frac = whole step at 378 B per stock-month"},
+    }
+    if not args.no_cpu:
+        r = cpu_step_rate()
+        line["cpu_baseline"] = {"value": r["rate_mean"], "unit": "stock-months/s", "cores": r["cores"],
+                                "kind": "port", "sample": r["sample"], "host_cpus": r["host_cpus"]}
+    print(json.dumps(line))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--precision", default="fp32")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    if args.impl == "reference":
+        run_reference(args, rank)
+        return
+    if world > 1:
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", int(os.environ.get("LOCAL_RANK", 0))))
+    try:
+        run_ours(args, rank, world)
+    finally:
+        if world > 1:
+            import torch.distributed as dist
+            dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

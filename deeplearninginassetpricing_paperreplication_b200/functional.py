@@ -48,6 +48,36 @@ def _tensors(ts) -> DlapTensors:
     return s
 
 
+class KernelTimer:
+    """CUDA-event bracket around every launch of one entry point (bench.py's roofline leg): the
+    events are recorded on the launching stream, read after the caller synchronises."""
+
+    def __init__(self, name: str):
+        self.name, self.pairs = name, []
+
+    def bracket(self, name, dev):
+        if name != self.name:
+            return None
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(torch.cuda.current_stream(dev))
+        self.pairs.append((e0, e1))
+        return e1
+
+    def mean_ms(self) -> float:
+        ts = [a.elapsed_time(b) for a, b in self.pairs]
+        return sum(ts) / max(len(ts), 1)
+
+
+kernel_timer: Optional[KernelTimer] = None
+
+
+def _timed_call(name, dev, *args):
+    end = kernel_timer.bracket(name, dev) if kernel_timer is not None else None
+    _lib.call(name, *args)
+    if end is not None:
+        end.record(torch.cuda.current_stream(dev))
+
+
 class Workspace:
     """Plan + pure scratch buffers for one (shape, device).  Scratch is reused by every call on
     that shape (single-stream semantics, like the reference); nothing that the backward pass
@@ -173,7 +203,7 @@ class GanStepFn(torch.autograd.Function):
                 a_loc, c_loc = a_t[sh.t0:sh.t1], c_t[sh.t0:sh.t1]
             u = torch.empty(T, N, dtype=torch.float32, device=dev)
             g = torch.empty(KM, T, N, dtype=torch.float32, device=dev) if opts.need_moments else None
-            _lib.call("dlap_cell_fwd", ws.pp, _ptr(x), _ptr(R), _ptr(mask), C.byref(tens), _ptr(a_loc),
+            _timed_call("dlap_cell_fwd", dev, ws.pp, _ptr(x), _ptr(R), _ptr(mask), C.byref(tens), _ptr(a_loc),
                       _ptr(c_loc), _ptr(u), _ptr(g), _ptr(ws.row_part), prec, float(opts.dropout_p),
                       int(opts.dropout_seed), st)
             row_stats = torch.empty(T, RS_W, dtype=torch.float32, device=dev)
@@ -236,7 +266,7 @@ class GanStepFn(torch.autograd.Function):
                 a_loc, c_loc = a_t, c_t
             else:
                 a_loc, c_loc = a_t[sh.t0:sh.t1], c_t[sh.t0:sh.t1]
-            _lib.call("dlap_cell_bwd", ws.pp, _ptr(x), _ptr(R), _ptr(mask), C.byref(tens), _ptr(a_loc),
+            _timed_call("dlap_cell_bwd", dev, ws.pp, _ptr(x), _ptr(R), _ptr(mask), C.byref(tens), _ptr(a_loc),
                       _ptr(c_loc), _ptr(row_stats), _ptr(ws.ds_part), _ptr(g_pr), _ptr(G), _ptr(scalars),
                       int(opts.weighted_loss), int(want_sdf), int(want_mom), _ptr(ws.wpart),
                       _ptr(ws.dadc_part), prec, float(opts.dropout_p), int(opts.dropout_seed), st)
