@@ -144,8 +144,9 @@ class SDFNetwork(nn.Module):
         return [fc0.weight, fc0.bias, fc3.weight, fc3.bias, self.output_proj.weight, self.output_proj.bias]
 
     def kernel_params(self, with_macro: bool):
+        mlp = self._mlp_params(with_macro)          # raises for configurations off the fast path
         lstm = self.macro_lstm._params() if with_macro else [None] * 4
-        return lstm + self._mlp_params(with_macro)
+        return lstm + mlp
 
     def forward(self, macro_features, individual_features, mask, hidden=None):
         """-> (weights [T,N], new_hidden).  Stand-alone use is the inference path (no autograd
