@@ -56,6 +56,7 @@ SIGNATURES = {
     "dlap_row_finish": (_PLAN, _P, _I, _P, _P, _P, _P, _P),
     "dlap_col_partial": (_PLAN, _P, _P, _P, _P, _P, _P, _P, _P),
     "dlap_loss_finish": (_PLAN, _P, _I, _P, _P, _P, _P, _P, _P),
+    "dlap_loss_finish_noalloc": (_PLAN, _P, _I, _P, _P, _P, _P),
     "dlap_loss_coeff": (_PLAN, _P, _P, _P, _P, _P, _P),
     "dlap_ds_rows": (_PLAN, _P, _P, _P, _P, _P, _P),
     "dlap_cell_bwd": (_PLAN, _P, _P, _P, _TENS, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _P, _P, _I,

@@ -64,6 +64,8 @@ const char* dlap_error_string(int code) {
     case DLAP_E_PRECISION: return "unknown precision selector";
     case DLAP_E_NODEVICE: return "no usable CUDA device";
     case DLAP_E_SMEM: return "configuration needs more shared memory than an SM offers";
+    case DLAP_E_LIMIT: return "size exceeds the fixed capacity of this no-allocation entry point "
+                              "(see DLAP_NOALLOC_MAX_STOCKS in dlap.h)";
     default: return code > 0 ? cudaGetErrorString((cudaError_t)code) : "unknown dlap error";
   }
 }

@@ -1,6 +1,9 @@
 // Row (per month over N) and column (per stock over T) reductions, loss and gradient finishing
 // kernels.  All HBM-bound or tiny; every cross-CTA sum is done in a fixed order (no float
 // atomics) so that results are run-to-run reproducible like the reference's CPU path.
+#include <mutex>
+
+#include "../../include/dlap.h"
 #include "dlap_common.cuh"
 #include "cell_f32.cuh"
 
@@ -294,4 +297,67 @@ cudaError_t launch_weights(const float* u, const uint8_t* mask, const float* row
   return cudaGetLastError();
 }
 
+// ---- loss finish without caller-provided scratch -------------------------------------------------------
+// Some hosts of this library are not allowed to enter the CUDA allocator once they are running: a
+// service that was given a fixed, fully pre-partitioned slice of device memory at start-up; an
+// evaluation loop with a latency budget, for which cudaMalloc/cudaFree are off limits because they
+// take driver-wide locks and synchronise the device; or glue code that simply has no allocator handle
+// (it receives raw pointers from another runtime and must not create memory of its own).  Such callers
+// cannot produce the two scratch buffers dlap_loss_finish wants, so this variant keeps them in a
+// fixed-size array that lives inside the loaded library image, once per GPU, until the process exits.
+//
+// The array name below is only a HOST-SIDE HANDLE in host code.  Passing it to a kernel would hand the
+// kernel a host address; the device address has to be asked for with cudaGetSymbolAddress, per device.
+namespace {
+constexpr int kNoAllocMaxStocks = DLAP_NOALLOC_MAX_STOCKS;
+constexpr int kNoAllocBlocks = (kNoAllocMaxStocks + 255) / 256;
+constexpr size_t kLossPartBytes = (size_t)kNoAllocBlocks * 2 * sizeof(double);
+constexpr size_t kCounterOffset = kLossPartBytes;                 // 8-byte aligned, holds one uint32
+constexpr size_t kNoAllocBytes = kLossPartBytes + 256;
+constexpr int kMaxDevices = 64;
+
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoAllocBytes];
+
+std::mutex g_noalloc_mutex;
+unsigned char* g_noalloc_ptr[kMaxDevices] = {nullptr};
+
+// Device address of the array on the CURRENT device; resolved on the first call per device.
+int noalloc_scratch(unsigned char** out) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return (int)e;
+  if (dev < 0 || dev >= kMaxDevices) return DLAP_E_NODEVICE;
+  std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+  if (!g_noalloc_ptr[dev]) {
+    void* p = nullptr;
+    e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+    if (e != cudaSuccess) return (int)e;
+    if (!p) return DLAP_E_NODEVICE;
+    g_noalloc_ptr[dev] = static_cast<unsigned char*>(p);
+  }
+  *out = g_noalloc_ptr[dev];
+  return DLAP_OK;
+}
+}  // namespace
 }  // namespace dlap
+
+extern "C" int dlap_loss_finish_noalloc(const dlap_plan* plan, const double* col_part, int nsplit, float* e,
+                                        float* t_i, float* scalars, void* stream) {
+  using namespace dlap;
+  if (!plan || !col_part || !e || !t_i || !scalars) return DLAP_E_NULL;
+  const int N = plan->dims.N;
+  if (N < 1 || nsplit < 1) return DLAP_E_SHAPE;
+  if (N > kNoAllocMaxStocks) return DLAP_E_LIMIT;     // the built-in scratch is sized for this many stocks
+  unsigned char* base = nullptr;
+  int rc = noalloc_scratch(&base);
+  if (rc) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  double* loss_part = reinterpret_cast<double*>(base);
+  unsigned int* counter = reinterpret_cast<unsigned int*>(base + kCounterOffset);
+  // The array keeps whatever the previous call left behind.  loss_part is fully overwritten before it
+  // is read; the block counter is the one thing that must start at zero, so clear it on the stream.
+  cudaError_t ce = cudaMemsetAsync(counter, 0, sizeof(unsigned int), st);
+  if (ce != cudaSuccess) return (int)ce;
+  ce = launch_loss_finish(col_part, nsplit, N, N, e, t_i, loss_part, counter, scalars, st);
+  return ce == cudaSuccess ? DLAP_OK : (int)ce;
+}

@@ -37,7 +37,8 @@ enum {
   DLAP_E_PLAN = -4,       /* plan does not belong to these dims */
   DLAP_E_PRECISION = -5,  /* unknown precision selector */
   DLAP_E_NODEVICE = -6,   /* no usable CUDA device */
-  DLAP_E_SMEM = -7        /* configuration needs more shared memory than one SM has */
+  DLAP_E_SMEM = -7,       /* configuration needs more shared memory than one SM has */
+  DLAP_E_LIMIT = -8       /* size beyond the fixed capacity of a no-allocation entry point */
 };
 
 /* arithmetic of the per-cell contractions */
@@ -124,6 +125,23 @@ int dlap_col_partial(const dlap_plan* plan, const float* g, const float* R, cons
  * in order (1 after an all-reduce across month shards).  counter: one zero-initialised uint32. */
 int dlap_loss_finish(const dlap_plan* plan, const double* col_part, int nsplit, float* e, float* t_i,
                      double* loss_part, uint32_t* counter, float* scalars, void* stream);
+
+/* Same result as dlap_loss_finish, for callers that cannot allocate device memory.  No counterpart
+ * in the reference: it exists for hosts that run on a fixed, pre-partitioned memory budget, that sit
+ * in a latency-bound loop where cudaMalloc/cudaFree (driver locks, device synchronisation) are
+ * forbidden, or that only ever receive raw pointers from another runtime.  The two scratch buffers
+ * (`loss_part`, `counter`) live in an array inside the library image instead: ~17 KB on every GPU that
+ * loads the library, for the life of the process.  Limits and rules:
+ *   - at most DLAP_NOALLOC_MAX_STOCKS stocks (plan->dims.N); beyond that the call returns DLAP_E_LIMIT;
+ *   - the first call on each device looks up the array's device address (one-time set-up with that
+ *     device current); make that first call before starting any stream capture;
+ *   - every call on a device shares the one array and it keeps the previous call's contents (the call
+ *     itself clears the one word that must start at zero); two calls that overlap on the GPU - different
+ *     streams, or different threads - race on it.  Serialise them.
+ * It calls no cudaMalloc/cudaFree and no allocating library routine.  Inputs/outputs as dlap_loss_finish. */
+#define DLAP_NOALLOC_MAX_STOCKS 262144
+int dlap_loss_finish_noalloc(const dlap_plan* plan, const double* col_part, int nsplit, float* e,
+                             float* t_i, float* scalars, void* stream);
 
 /* Backward of the two losses (autograd at src/train.py:84): G_ki = gc 2 e_ki/(K N T_i),
  * G0_i = gu 2 e0_i/(N T_i); gc/gu are device scalars = dL/dL_c, dL/dL_u (NULL = 0). -> G [9,N] */
