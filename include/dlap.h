@@ -179,6 +179,14 @@ int dlap_macro_bwd(const dlap_plan* plan, const float* macro, const dlap_tensors
 int dlap_weights(const dlap_plan* plan, const float* u, const uint8_t* mask, const float* row_stats,
                  int normalized, float* w_out, void* stream);
 
+/* Hardware self-test of the tensor-core plumbing (no counterpart in the reference): one CTA computes
+ * D[128,N] = A.B^T (bf16 operands, fp32 accumulate in TMEM) from two operand images laid out by the
+ * caller in the library's no-swizzle canonical layout, with caller-given descriptor strides (bytes) and
+ * majors (0 = K-major, 1 = MN-major).  tests/ pin the layout conventions of csrc/tc_sm100.cuh with it. */
+int dlap_umma_selftest(const void* a_img, int a_bytes, const void* b_img, int b_bytes, int M, int N, int K,
+                       int a_mn_major, int b_mn_major, int a_lbo, int a_sbo, int a_kstep, int b_lbo,
+                       int b_sbo, int b_kstep, float* D, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
