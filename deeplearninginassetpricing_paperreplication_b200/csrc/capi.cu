@@ -8,6 +8,7 @@ namespace dlap {
 struct MacroParams;
 cudaError_t launch_cell_fwd_f32(const CellParams& P, int grid, cudaStream_t st);
 cudaError_t launch_cell_bwd_f32(const CellParams& P, int grid, bool sdf, bool mom, cudaStream_t st);
+cudaError_t launch_cell_fwd_tc(const CellParams& P, int grid, cudaStream_t st);
 size_t smem_bwd_bytes(int F);
 cudaError_t launch_row_finish(const double*, int, int, int, const float*, float*, float*, float*, cudaStream_t);
 cudaError_t launch_col_partial(const float*, const float*, const uint8_t*, const float*, const float*, int, int,
@@ -96,7 +97,7 @@ int dlap_make_plan(const dlap_dims* dims, int device, dlap_plan* out) {
   p.row_splits = rs;
   p.ldw1 = F + (dims->M > 0 ? dims->H : 0);
   p.ldwq = dims->M + F;
-  p.row_part_bytes = (int64_t)T * p.tpm * 4 * 8;
+  p.row_part_bytes = (int64_t)T * p.tpm * 4 * 4 * 8;
   p.col_part_bytes = (int64_t)p.col_splits * (KM + 2) * N * 8;
   p.loss_part_bytes = (int64_t)nb * 2 * 8;
   p.ds_part_bytes = (int64_t)T * p.row_splits * 8;
@@ -155,22 +156,29 @@ int dlap_cell_fwd(const dlap_plan* plan, const float* x, const float* R, const u
   REQ(params->w1); REQ(params->w2); REQ(params->b2); REQ(params->w3); REQ(params->b3);
   if (g) { REQ(c_t); REQ(params->wq); }
   if (reinterpret_cast<uintptr_t>(x) & 3) return DLAP_E_ALIGN;
-  if (precision != DLAP_PREC_FP32) return DLAP_E_PRECISION;
+  if (precision != DLAP_PREC_FP32 && precision != DLAP_PREC_BF16X3) return DLAP_E_PRECISION;
   CellParams P;
   fill_cell(P, plan, x, R, mask, params, a_t, c_t);
   P.u = u; P.g = g; P.row_part = row_part;
   rc = set_dropout(P, dropout_p, dropout_seed);
   if (rc) return rc;
+  if (precision == DLAP_PREC_BF16X3) {
+    if (plan->dims.F > 46) return DLAP_E_SHAPE;      // the ones column lives at k = 46
+    if (P.drop_thr) return DLAP_E_PRECISION;         // dropout: fp32 kernels only
+    CU(launch_cell_fwd_tc(P, plan->grid_cell, (cudaStream_t)stream));
+    return DLAP_OK;
+  }
   CU(launch_cell_fwd_f32(P, plan->grid_cell, (cudaStream_t)stream));
   return DLAP_OK;
 }
 
-int dlap_row_finish(const dlap_plan* plan, const double* row_part, int weighted_loss, const float* n_bar_in,
-                    float* row_stats, float* pr, float* scalars, void* stream) {
+int dlap_row_finish(const dlap_plan* plan, const double* row_part, int slots_per_tile, int weighted_loss,
+                    const float* n_bar_in, float* row_stats, float* pr, float* scalars, void* stream) {
   int rc = check_plan(plan);
   if (rc) return rc;
   REQ(row_part); REQ(row_stats); REQ(pr); REQ(scalars);
-  CU(launch_row_finish(row_part, plan->dims.T, plan->tpm, weighted_loss, n_bar_in, row_stats, pr, scalars,
+  if (slots_per_tile != 1 && slots_per_tile != 4) return DLAP_E_SHAPE;
+  CU(launch_row_finish(row_part, plan->dims.T, plan->tpm * slots_per_tile, weighted_loss, n_bar_in, row_stats, pr, scalars,
                        (cudaStream_t)stream));
   return DLAP_OK;
 }

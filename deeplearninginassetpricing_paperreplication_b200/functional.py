@@ -30,7 +30,9 @@ SC_LC, SC_LU, SC_SHARPE, SC_NBAR = 0, 1, 2, 3
 RS_NT, RS_MU, RS_P, RS_PR, RS_S, RS_RBAR = 0, 1, 2, 3, 4, 5
 KM = 8
 
-_PRECISIONS = {"fp32": _lib.DLAP_PREC_FP32}
+_PRECISIONS = {"fp32": _lib.DLAP_PREC_FP32, "bf16x3": _lib.DLAP_PREC_BF16X3}
+_ROW_SLOTS = {"fp32": 1, "bf16x3": 4}
+_BWD_PRECISION = {"fp32": "fp32", "bf16x3": "fp32"}     # arithmetic of dlap_cell_bwd per model precision
 
 
 def _ptr(t: Optional[torch.Tensor]):
@@ -209,7 +211,8 @@ class GanStepFn(torch.autograd.Function):
             row_stats = torch.empty(T, RS_W, dtype=torch.float32, device=dev)
             pr = torch.empty(T, dtype=torch.float32, device=dev)
             scalars = torch.zeros(SC_W, dtype=torch.float32, device=dev)
-            _lib.call("dlap_row_finish", ws.pp, _ptr(ws.row_part), int(opts.weighted_loss),
+            _lib.call("dlap_row_finish", ws.pp, _ptr(ws.row_part), _ROW_SLOTS[opts.precision],
+                      int(opts.weighted_loss),
                       _ptr(sh.n_bar) if sh is not None else None, _ptr(row_stats), _ptr(pr),
                       _ptr(scalars), st)
             w = torch.empty(T, N, dtype=torch.float32, device=dev)
@@ -247,7 +250,7 @@ class GanStepFn(torch.autograd.Function):
         want_mom = any(need[10:]) and g is not None
         if not (want_sdf or want_mom):
             return (None,) * (7 + len(params))
-        prec = _PRECISIONS[opts.precision]
+        prec = _PRECISIONS[_BWD_PRECISION[opts.precision]]
 
         def scalar(t):
             return None if t is None else t.detach().reshape(1).to(torch.float32).contiguous()
@@ -318,7 +321,8 @@ def sdf_weights(macro, x, mask, params, h0=None, c0=None, normalized=False, prec
         row_stats = torch.empty(T, RS_W, dtype=torch.float32, device=dev)
         pr = torch.empty(T, dtype=torch.float32, device=dev)
         scalars = torch.empty(SC_W, dtype=torch.float32, device=dev)
-        _lib.call("dlap_row_finish", ws.pp, _ptr(ws.row_part), int(weighted_loss), None, _ptr(row_stats),
+        _lib.call("dlap_row_finish", ws.pp, _ptr(ws.row_part), _ROW_SLOTS[precision], int(weighted_loss), None,
+                  _ptr(row_stats),
                   _ptr(pr), _ptr(scalars), st)
         w = torch.empty(T, N, dtype=torch.float32, device=dev)
         _lib.call("dlap_weights", ws.pp, _ptr(u), _ptr(mask), _ptr(row_stats), int(normalized), _ptr(w), st)

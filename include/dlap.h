@@ -43,7 +43,9 @@ enum {
 
 /* arithmetic of the per-cell contractions */
 enum {
-  DLAP_PREC_FP32 = 0      /* exact fp32 FFMA */
+  DLAP_PREC_FP32 = 0,     /* exact fp32 FFMA on CUDA cores */
+  DLAP_PREC_BF16X3 = 1    /* tcgen05 BF16 MMAs on hi/lo-split operands, 3 products per fp32 product,
+                             fp32 accumulation in TMEM; needs F <= 46; row_part has 4 slots per tile */
 };
 
 typedef struct dlap_dims {
@@ -59,7 +61,7 @@ typedef struct dlap_plan {
   int32_t row_splits;     /* stock chunks of the per-month (row) reduction of dS */
   int32_t ldw1;           /* row pitch of fc_layers.0.weight  = F + H (F when M = 0) */
   int32_t ldwq;           /* row pitch of moment output_proj.weight = M + F */
-  int64_t row_part_bytes;   /* double [T, tpm, 4]           */
+  int64_t row_part_bytes;   /* double [T, tpm, 4 slots, 4]  */
   int64_t col_part_bytes;   /* double [col_splits, 10, N]   */
   int64_t loss_part_bytes;  /* double [ceil(N/256), 2]      */
   int64_t ds_part_bytes;    /* double [T, row_splits]       */
@@ -109,8 +111,9 @@ int dlap_cell_fwd(const dlap_plan* plan, const float* x, const float* R, const u
 /* Per-month statistics: N_t, mu_t (src/model.py:276-278), P_t, portfolio return pr_t and
  * S_t = 1 + pr_t (src/model.py:359-367, :380), Rbar_t; N_bar (src/model.py:360) and the Sharpe
  * ratio of pr (src/model.py:551) into scalars[3], scalars[2].  n_bar_in (device, 1 float) overrides
- * N_bar when the panel is one month-shard of a larger one; NULL otherwise. */
-int dlap_row_finish(const dlap_plan* plan, const double* row_part, int weighted_loss,
+ * N_bar when the panel is one month-shard of a larger one; NULL otherwise.  slots_per_tile: partial
+ * sums dlap_cell_fwd wrote per tile (1 for DLAP_PREC_FP32, 4 for DLAP_PREC_BF16X3). */
+int dlap_row_finish(const dlap_plan* plan, const double* row_part, int slots_per_tile, int weighted_loss,
                     const float* n_bar_in, float* row_stats, float* pr, float* scalars, void* stream);
 
 /* Per-stock sums over the months of each chunk: sum_t g_k S_t, sum_t R m S_t, sum_t m

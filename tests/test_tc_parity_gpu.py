@@ -1,0 +1,98 @@
+"""Parity of the tensor-core path (b200_precision='bf16x3': tcgen05 BF16 MMAs on hi/lo-split fp32
+operands) against the reference's goldens and the fp64 oracle, at BASELINE.json's tolerances:
+1e-5 relative on losses, 1e-4 on weights."""
+import numpy as np
+import pytest
+import torch
+
+from _dlap_testlib import PHASES, golden_params, rel_err
+from deeplearninginassetpricing_paperreplication_b200 import AssetPricingGAN
+from oracle import closed_form as cf
+from test_parity_gpu import LOSS_RTOL, WEIGHT_TOL, _model_from, _np, _panel, dev, make_panel
+
+pytestmark = pytest.mark.gpu
+TC_GRAD_TOL = 1e-3
+
+
+@pytest.mark.parametrize("phase", PHASES)
+def test_tc_step_matches_reference_goldens(golden, phase):
+    params = golden_params(golden)
+    model = _model_from(params, golden["macro"].shape[1], b200_precision="bf16x3").eval()
+    macro, x, R, mask, hidden = _panel(golden)
+    for p in model.sdf_net.parameters():
+        p.requires_grad = phase != "moment"
+    out = model(macro, x, R, mask, hidden=hidden, phase=phase)
+    out["loss"].backward()
+    torch.cuda.synchronize()
+    for key in ("loss", "loss_unconditional", "loss_conditional"):
+        a, b = float(out[key]), float(golden[f"{phase}/{key}"])
+        assert abs(a - b) <= LOSS_RTOL * abs(b) + 1e-30, (key, a, b)
+    assert rel_err(_np(out["weights"]), golden[f"{phase}/weights"]) < WEIGHT_TOL
+    assert np.all(_np(out["weights"])[~golden["mask"]] == 0.0)
+    assert rel_err(_np(out["portfolio_returns"]), golden[f"{phase}/portfolio_returns"]) < WEIGHT_TOL
+    for k, p in model.named_parameters():
+        gk = f"{phase}/grad/{k}"
+        if gk not in golden:
+            assert p.grad is None, k
+            continue
+        if k == "sdf_net.output_proj.bias":
+            continue
+        ref = golden[gk]
+        err = np.abs(_np(p.grad) - ref).max() / max(np.abs(ref).max(), 1e-30)
+        assert err < 2e-3, (k, err)
+
+
+@pytest.mark.parametrize("T,N,M", [(1, 1, 8), (3, 127, 8), (5, 129, 178), (7, 1000, 178), (40, 513, 178)])
+@pytest.mark.parametrize("phase", PHASES)
+def test_tc_step_vs_oracle_shapes(T, N, M, phase):
+    macro, x, R, mask = make_panel(T, N, M, seed=T * 1000 + N)
+    if T > 2:
+        mask[1] = False
+    if N > 3:
+        mask[:, 2] = False
+    x = x * mask[:, :, None]; R = R * mask
+    torch.manual_seed(N)
+    model = AssetPricingGAN({"macro_feature_dim": M, "individual_feature_dim": 46,
+                             "b200_precision": "bf16x3"}).to(dev()).eval()
+    d = dev()
+    params = {k: _np(v) for k, v in model.state_dict().items()}
+    for p in model.sdf_net.parameters():
+        p.requires_grad = phase != "moment"
+    out = model(macro.to(d), x.to(d), R.to(d), mask.to(d), phase=phase)
+    out["loss"].backward()
+    torch.cuda.synchronize()
+    ref = cf.forward(params, _np(macro), _np(x), _np(R), _np(mask), phase=phase)
+    gref = cf.backward(params, _np(macro), _np(x), _np(R), _np(mask), ref, phase=phase)
+    w = _np(out["weights"])
+    assert np.all(w[~_np(mask)] == 0.0)
+    assert rel_err(w, ref["weights"]) < WEIGHT_TOL
+    for key in ("loss", "loss_unconditional", "loss_conditional"):
+        a, b = float(out[key]), float(ref[key])
+        assert abs(a - b) <= LOSS_RTOL * abs(b) + 1e-30, (key, a, b)
+    for k, p in model.named_parameters():
+        if p.grad is None or k == "sdf_net.output_proj.bias":
+            continue
+        r = gref[k].reshape(p.shape)
+        err = np.abs(_np(p.grad) - r).max() / max(np.abs(r).max(), 1e-30)
+        assert err < TC_GRAD_TOL, (k, err)
+
+
+def test_tc_forward_close_to_fp32_path_large():
+    """Paper-width panel slice: the two arithmetic paths agree far inside the parity tolerance."""
+    macro, x, R, mask = make_panel(24, 3000, 178, seed=77)
+    d = dev()
+    args = (macro.to(d), x.to(d), R.to(d), mask.to(d))
+    torch.manual_seed(9)
+    m32 = AssetPricingGAN({"macro_feature_dim": 178, "individual_feature_dim": 46}).to(d).eval()
+    mtc = AssetPricingGAN({"macro_feature_dim": 178, "individual_feature_dim": 46, "b200_precision": "bf16x3"}).to(d).eval()
+    mtc.load_state_dict(m32.state_dict())
+    with torch.no_grad():
+        a, b = m32(*args), mtc(*args)
+        wa, _ = m32.get_weights(*args[:2], args[3], normalized=True)
+        wb, _ = mtc.get_weights(*args[:2], args[3], normalized=True)
+    assert rel_err(_np(b["weights"]), _np(a["weights"])) < 2e-5
+    assert rel_err(_np(wb), _np(wa)) < 2e-5
+    for key in ("loss", "loss_unconditional"):
+        assert abs(float(a[key]) - float(b[key])) <= 2e-6 * abs(float(a[key]))
+    rerun = mtc(*args)
+    assert torch.equal(rerun["weights"], b["weights"]) and torch.equal(rerun["loss"], b["loss"])   # deterministic
