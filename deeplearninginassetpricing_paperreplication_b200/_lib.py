@@ -16,7 +16,7 @@ PKG_DIR = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(PKG_DIR)
 CSRC = os.path.join(PKG_DIR, "csrc")
 LIB_PATH = os.path.join(PKG_DIR, "libdlap_b200.so")
-SOURCES = ("capi.cu", "cell_fwd.cu", "cell_bwd.cu", "reduce.cu", "macro_lstm.cu", "tc_selftest.cu", "cell_fwd_tc.cu")
+SOURCES = ("capi.cu", "cell_fwd.cu", "cell_bwd.cu", "reduce.cu", "macro_lstm.cu", "tc_selftest.cu", "cell_fwd_tc.cu", "cell_bwd_tc.cu")
 NVCC_FLAGS = ("-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-shared", "-Xcompiler", "-fPIC")
 
@@ -62,7 +62,7 @@ SIGNATURES = {
     "dlap_ds_rows": (_PLAN, _P, _P, _P, _P, _P, _P),
     "dlap_cell_bwd": (_PLAN, _P, _P, _P, _TENS, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _P, _P, _I,
                       C.c_float, C.c_uint64, _P),
-    "dlap_grad_finish": (_PLAN, _P, _P, _I, _I, _TENS, _P, _P),
+    "dlap_grad_finish": (_PLAN, _P, _P, _I, _I, _I, _TENS, _P, _P),
     "dlap_macro_bwd": (_PLAN, _P, _TENS, _P, _P, _P, _P, _P, _I, _I, _TENS, _P),
     "dlap_weights": (_PLAN, _P, _P, _P, _I, _P, _P),
     "dlap_umma_selftest": (_P, _I, _P, _I, _I, _I, _I, _I, _I, _I, _I, _I, _I, _I, _I, _P, _P),

@@ -9,6 +9,7 @@ struct MacroParams;
 cudaError_t launch_cell_fwd_f32(const CellParams& P, int grid, cudaStream_t st);
 cudaError_t launch_cell_bwd_f32(const CellParams& P, int grid, bool sdf, bool mom, cudaStream_t st);
 cudaError_t launch_cell_fwd_tc(const CellParams& P, int grid, cudaStream_t st);
+cudaError_t launch_cell_bwd_tc(const CellParams& P, int grid, bool sdf, bool mom, cudaStream_t st);
 size_t smem_bwd_bytes(int F);
 cudaError_t launch_row_finish(const double*, int, int, int, const float*, float*, float*, float*, cudaStream_t);
 cudaError_t launch_col_partial(const float*, const float*, const uint8_t*, const float*, const float*, int, int,
@@ -102,7 +103,7 @@ int dlap_make_plan(const dlap_dims* dims, int device, dlap_plan* out) {
   p.loss_part_bytes = (int64_t)nb * 2 * 8;
   p.ds_part_bytes = (int64_t)T * p.row_splits * 8;
   p.wpart_bytes = (int64_t)p.grid_cell * wp_stride(round4(F)) * 4;
-  p.dadc_part_bytes = (int64_t)T * p.tpm * 72 * 4;
+  p.dadc_part_bytes = (int64_t)T * p.tpm * 4 * 72 * 4;
   p.lstm_save_bytes = (int64_t)T * 6 * (dims->H > 0 ? dims->H : 1) * 4;
   p.dpre_bytes = (int64_t)T * 4 * (dims->H > 0 ? dims->H : 1) * 4;
   *out = p;
@@ -234,7 +235,7 @@ int dlap_cell_bwd(const dlap_plan* plan, const float* x, const float* R, const u
   REQ(wpart); REQ(dadc_part);
   REQ(params->w1); REQ(params->w2); REQ(params->b2); REQ(params->w3); REQ(params->b3); REQ(params->wq);
   if (!want_sdf && !want_mom) return DLAP_E_SHAPE;
-  if (precision != DLAP_PREC_FP32) return DLAP_E_PRECISION;
+  if (precision != DLAP_PREC_FP32 && precision != DLAP_PREC_BF16X3) return DLAP_E_PRECISION;
   CellParams P;
   fill_cell(P, plan, x, R, mask, params, a_t, c_t);
   P.row_stats = row_stats; P.dS_part = dS_part; P.ds_splits = plan->row_splits; P.dpr_cot = dpr_cot;
@@ -242,19 +243,26 @@ int dlap_cell_bwd(const dlap_plan* plan, const float* x, const float* R, const u
   P.wpart = wpart; P.dadc_part = dadc_part;
   rc = set_dropout(P, dropout_p, dropout_seed);
   if (rc) return rc;
+  if (precision == DLAP_PREC_BF16X3) {
+    if (plan->dims.F > 46) return DLAP_E_SHAPE;
+    if (P.drop_thr) return DLAP_E_PRECISION;
+    CU(launch_cell_bwd_tc(P, plan->grid_cell, want_sdf != 0, want_mom != 0, (cudaStream_t)stream));
+    return DLAP_OK;
+  }
   CU(launch_cell_bwd_f32(P, plan->grid_cell, want_sdf != 0, want_mom != 0, (cudaStream_t)stream));
   return DLAP_OK;
 }
 
-int dlap_grad_finish(const dlap_plan* plan, const float* wpart, const float* dadc_part, int want_sdf,
-                     int want_mom, const dlap_tensors* grads, float* dadc, void* stream) {
+int dlap_grad_finish(const dlap_plan* plan, const float* wpart, const float* dadc_part, int slots_per_tile,
+                     int want_sdf, int want_mom, const dlap_tensors* grads, float* dadc, void* stream) {
   int rc = check_plan(plan);
   if (rc) return rc;
+  if (slots_per_tile != 1 && slots_per_tile != 4) return DLAP_E_SHAPE;
   REQ(wpart); REQ(dadc_part); REQ(grads); REQ(dadc);
   if (want_sdf) { REQ(grads->w1); REQ(grads->w2); REQ(grads->b2); REQ(grads->w3); REQ(grads->b3); }
   if (want_mom) REQ(grads->wq);
   CU(launch_grad_finish(wpart, plan->grid_cell, plan->dims.F, want_sdf, want_mom, dadc_part, plan->dims.T,
-                        plan->tpm, grads->w1, plan->ldw1, grads->w2, grads->b2, grads->w3, grads->b3, grads->wq,
+                        plan->tpm * slots_per_tile, grads->w1, plan->ldw1, grads->w2, grads->b2, grads->w3, grads->b3, grads->wq,
                         plan->ldwq, plan->dims.M, dadc, (cudaStream_t)stream));
   return DLAP_OK;
 }

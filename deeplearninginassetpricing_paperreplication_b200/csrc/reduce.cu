@@ -188,7 +188,7 @@ __global__ void __launch_bounds__(256) ds_rows_kernel(
 // ---- backward: sum per-CTA / per-tile partials into the reference's gradient layouts ----------------
 __global__ void __launch_bounds__(256) grad_finish_kernel(
     const float* __restrict__ wpart, int ncta, int F, int have_sdf, int have_mom,
-    const float* __restrict__ dadc_part, int T, int tpm,
+    const float* __restrict__ dadc_part, int T, int tpm /* partial slots per month */,
     float* __restrict__ gW1, int ldw1, float* __restrict__ gW2, float* __restrict__ gb2,
     float* __restrict__ gW3, float* __restrict__ gb3, float* __restrict__ gWq, int ldwq, int wq_off,
     float* __restrict__ dadc) {

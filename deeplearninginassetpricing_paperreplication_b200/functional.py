@@ -32,7 +32,7 @@ KM = 8
 
 _PRECISIONS = {"fp32": _lib.DLAP_PREC_FP32, "bf16x3": _lib.DLAP_PREC_BF16X3}
 _ROW_SLOTS = {"fp32": 1, "bf16x3": 4}
-_BWD_PRECISION = {"fp32": "fp32", "bf16x3": "fp32"}     # arithmetic of dlap_cell_bwd per model precision
+_BWD_PRECISION = {"fp32": "fp32", "bf16x3": "bf16x3"}     # arithmetic of dlap_cell_bwd per model precision
 
 
 def _ptr(t: Optional[torch.Tensor]):
@@ -276,7 +276,8 @@ class GanStepFn(torch.autograd.Function):
             grads = [None if p is None else torch.zeros_like(p) for p in params]
             gt = _tensors(grads)
             dadc = torch.empty(T, 72, dtype=torch.float32, device=dev)
-            _lib.call("dlap_grad_finish", ws.pp, _ptr(ws.wpart), _ptr(ws.dadc_part), int(want_sdf),
+            _lib.call("dlap_grad_finish", ws.pp, _ptr(ws.wpart), _ptr(ws.dadc_part),
+                      _ROW_SLOTS[_BWD_PRECISION[opts.precision]], int(want_sdf),
                       int(want_mom), C.byref(gt), _ptr(dadc), st)
             ws.launches += 4
             if sh is None:

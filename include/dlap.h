@@ -66,7 +66,7 @@ typedef struct dlap_plan {
   int64_t loss_part_bytes;  /* double [ceil(N/256), 2]      */
   int64_t ds_part_bytes;    /* double [T, row_splits]       */
   int64_t wpart_bytes;      /* float  [grid_cell, wstride]  */
-  int64_t dadc_part_bytes;  /* float  [T, tpm, 72]          */
+  int64_t dadc_part_bytes;  /* float  [T, tpm, 4 slots, 72] */
   int64_t lstm_save_bytes;  /* float  [T, 6H]               */
   int64_t dpre_bytes;       /* float  [T, 4H]               */
 } dlap_plan;
@@ -167,9 +167,10 @@ int dlap_cell_bwd(const dlap_plan* plan, const float* x, const float* R, const u
                   uint64_t dropout_seed, void* stream);
 
 /* Fixed-order sum of the partials into the reference's gradient layouts: grads->w1[:, :F], w2, b2,
- * w3, b3 (= 0, demeaning), wq[:, M:]; and dadc [T,72] = da_t | dc_t summed over stocks. */
-int dlap_grad_finish(const dlap_plan* plan, const float* wpart, const float* dadc_part, int want_sdf,
-                     int want_mom, const dlap_tensors* grads, float* dadc, void* stream);
+ * w3, b3 (= 0, demeaning), wq[:, M:]; and dadc [T,72] = da_t | dc_t summed over stocks.
+ * slots_per_tile: da_t|dc_t partials dlap_cell_bwd wrote per tile (1 for FP32, 4 for BF16X3). */
+int dlap_grad_finish(const dlap_plan* plan, const float* wpart, const float* dadc_part, int slots_per_tile,
+                     int want_sdf, int want_mom, const dlap_tensors* grads, float* dadc, void* stream);
 
 /* Month-level backward: dh_t = W1[:,F:]^T da_t, LSTM BPTT, and the month-summed gradients
  * grads->{w_ih,w_hh,b_ih,b_hh}, w1[:, F:], b1, wq[:, :M], bq.  dpre [T,4H] is scratch. */
