@@ -75,7 +75,7 @@ template <bool SDF, bool MOM>
 __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P) {
   extern __shared__ __align__(128) uint8_t smem_raw[];
   SmemB s;
-  s.base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~uintptr_t(127));
+  s.base = tc::smem_align128(smem_raw);
   uint64_t* bar = s.bars();
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int ntiles = P.T * P.tpm;
@@ -284,24 +284,19 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
       tc::fence_after_sync();
       uint32_t m1 = 0u;
       if (SDF) {
+        float v[32];
+        tc::tmem_ld32(dA + U0, v);
 #pragma unroll
-        for (int c = 0; c < 2; ++c) {
-          float v[16];
-          tc::tmem_ld16(dA + U0 + c * 16, v);
-          tc::tmem_wait_ld();
+        for (int k = 0; k < 32; ++k) {
+          if (v[k] > 0.f) m1 |= 1u << k;
+          v[k] = fmaxf(v[k], 0.f);
+        }
 #pragma unroll
-          for (int k = 0; k < 16; ++k) {
-            if (v[k] > 0.f) m1 |= 1u << (c * 16 + k);
-            v[k] = fmaxf(v[k], 0.f);
-          }
+        for (int g = 0; g < 4; ++g) {
           uint4 hi, lo;
-          const int g0 = (U0 >> 3) + 2 * c;
-          tc::split8(v, hi, lo);
-          *reinterpret_cast<uint4*>(s.hh() + (g0 * TILE + cell) * 16) = hi;
-          *reinterpret_cast<uint4*>(s.hl() + (g0 * TILE + cell) * 16) = lo;
-          tc::split8(v + 8, hi, lo);
-          *reinterpret_cast<uint4*>(s.hh() + ((g0 + 1) * TILE + cell) * 16) = hi;
-          *reinterpret_cast<uint4*>(s.hl() + ((g0 + 1) * TILE + cell) * 16) = lo;
+          tc::split8(v + 8 * g, hi, lo);
+          *reinterpret_cast<uint4*>(s.hh() + (((U0 >> 3) + g) * TILE + cell) * 16) = hi;
+          *reinterpret_cast<uint4*>(s.hl() + (((U0 >> 3) + g) * TILE + cell) * 16) = lo;
         }
       }
       if (MOM && hf == 1) {
@@ -310,7 +305,7 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
         tc::tmem_wait_ld();
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
-          const float qq = tanhf(q[k]);
+          const float qq = tc::tanh_fast(q[k]);
           const float gk = live ? __ldg(P.G + (size_t)k * P.N + n0 + cell) : 0.f;
           q[k] = gk * cq * (1.f - qq * qq);              // dpre_k
         }
@@ -336,26 +331,29 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
         mbar_wait(bar + B_D2_FULL, par);
         tc::fence_after_sync();
         float pw[32], dz[32];
+        {
+          float v[32];
+          tc::tmem_ld32(tbase + lane_base + C_B + U0, v);
+          const float4* b4 = reinterpret_cast<const float4*>(s.b2s() + U0);
+          const float4* w4 = reinterpret_cast<const float4*>(s.w3s() + U0);
 #pragma unroll
-        for (int c = 0; c < 2; ++c) {
-          float v[16];
-          tc::tmem_ld16(tbase + lane_base + C_B + U0 + c * 16, v);
-          tc::tmem_wait_ld();
+          for (int k = 0; k < 8; ++k) {
+            const float4 bb = b4[k], ww = w4[k];
+            const float b_[4] = {bb.x, bb.y, bb.z, bb.w}, w_[4] = {ww.x, ww.y, ww.z, ww.w};
 #pragma unroll
-          for (int k = 0; k < 16; ++k) {
-            const int j = U0 + c * 16 + k;
-            const float z = v[k] + s.b2s()[j];
-            pw[c * 16 + k] = du * fmaxf(z, 0.f);
-            dz[c * 16 + k] = (z > 0.f) ? du * s.w3s()[j] : 0.f;
+            for (int e = 0; e < 4; ++e) {
+              const float z = v[4 * k + e] + b_[e];
+              pw[4 * k + e] = du * fmaxf(z, 0.f);
+              dz[4 * k + e] = (z > 0.f) ? du * w_[e] : 0.f;
+            }
           }
+        }
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
           uint4 hi, lo;
-          const int g0 = (U0 >> 3) + 2 * c;
-          tc::split8(dz + c * 16, hi, lo);
-          *reinterpret_cast<uint4*>(s.dzh() + (g0 * TILE + cell) * 16) = hi;
-          *reinterpret_cast<uint4*>(s.dzl() + (g0 * TILE + cell) * 16) = lo;
-          tc::split8(dz + c * 16 + 8, hi, lo);
-          *reinterpret_cast<uint4*>(s.dzh() + ((g0 + 1) * TILE + cell) * 16) = hi;
-          *reinterpret_cast<uint4*>(s.dzl() + ((g0 + 1) * TILE + cell) * 16) = lo;
+          tc::split8(dz + 8 * g, hi, lo);
+          *reinterpret_cast<uint4*>(s.dzh() + (((U0 >> 3) + g) * TILE + cell) * 16) = hi;
+          *reinterpret_cast<uint4*>(s.dzl() + (((U0 >> 3) + g) * TILE + cell) * 16) = lo;
         }
         tc::fence_before_sync();
         fence_proxy_async();
@@ -367,24 +365,15 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
         // ---- E3: dz1 = (dz2 . W2) [z1 > 0] -> DZ image (over dz2) ; da_t
         mbar_wait(bar + B_D3_FULL, par);
         tc::fence_after_sync();
+        tc::tmem_ld32(tbase + lane_base + C_C + U0, dz);
 #pragma unroll
-        for (int c = 0; c < 2; ++c) {
-          float v[16];
-          tc::tmem_ld16(tbase + lane_base + C_C + U0 + c * 16, v);
-          tc::tmem_wait_ld();
+        for (int k = 0; k < 32; ++k) dz[k] = ((m1 >> k) & 1u) ? dz[k] : 0.f;
 #pragma unroll
-          for (int k = 0; k < 16; ++k) {
-            v[k] = ((m1 >> (c * 16 + k)) & 1u) ? v[k] : 0.f;
-            dz[c * 16 + k] = v[k];
-          }
+        for (int g = 0; g < 4; ++g) {
           uint4 hi, lo;
-          const int g0 = (U0 >> 3) + 2 * c;
-          tc::split8(v, hi, lo);
-          *reinterpret_cast<uint4*>(s.dzh() + (g0 * TILE + cell) * 16) = hi;
-          *reinterpret_cast<uint4*>(s.dzl() + (g0 * TILE + cell) * 16) = lo;
-          tc::split8(v + 8, hi, lo);
-          *reinterpret_cast<uint4*>(s.dzh() + ((g0 + 1) * TILE + cell) * 16) = hi;
-          *reinterpret_cast<uint4*>(s.dzl() + ((g0 + 1) * TILE + cell) * 16) = lo;
+          tc::split8(dz + 8 * g, hi, lo);
+          *reinterpret_cast<uint4*>(s.dzh() + (((U0 >> 3) + g) * TILE + cell) * 16) = hi;
+          *reinterpret_cast<uint4*>(s.dzl() + (((U0 >> 3) + g) * TILE + cell) * 16) = lo;
         }
         tc::fence_before_sync();
         fence_proxy_async();

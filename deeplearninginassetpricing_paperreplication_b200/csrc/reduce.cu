@@ -14,24 +14,28 @@ namespace dlap {
 // P_t = sum m (u - mu_t) R = sum(m u R) - mu_t sum(m R)           src/model.py:363,367
 // pr_t = P_t / N_t * N_bar (weighted_loss) ; S_t = 1 + pr_t       src/model.py:360,367,380
 // sharpe = mean(pr) / (std_unbiased(pr) + 1e-8)                   src/model.py:551
-__global__ void row_finish_kernel(const double* __restrict__ row_part, int T, int tpm, int weighted,
-                                  const float* __restrict__ n_bar_in, float* __restrict__ row_stats,
-                                  float* __restrict__ pr_out, float* __restrict__ scalars) {
+__global__ void __launch_bounds__(1024) row_finish_kernel(
+    const double* __restrict__ row_part, int T, int tpm, int weighted, const float* __restrict__ n_bar_in,
+    float* __restrict__ row_stats, float* __restrict__ pr_out, float* __restrict__ scalars) {
   __shared__ double red[32];
-  const int tid = threadIdx.x;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, nwarp = blockDim.x >> 5;
+  // one warp per month: lanes stride over the partial slots, fixed-tree warp sum
   double nsum = 0.0;
-  for (int t = tid; t < T; t += blockDim.x) {
+  for (int t = warp; t < T; t += nwarp) {
     double c = 0, su = 0, sur = 0, sr = 0;
     const double* p = row_part + (size_t)t * tpm * 4;
-    for (int j = 0; j < tpm; ++j) { c += p[4 * j]; su += p[4 * j + 1]; sur += p[4 * j + 2]; sr += p[4 * j + 3]; }
+    for (int j = lane; j < tpm; j += 32) { c += p[4 * j]; su += p[4 * j + 1]; sur += p[4 * j + 2]; sr += p[4 * j + 3]; }
+    c = warp_sum(c); su = warp_sum(su); sur = warp_sum(sur); sr = warp_sum(sr);
     const double nt = fmax(c, 1.0);
     const float mu = (float)(su / nt);
-    float* rs = row_stats + (size_t)t * RS_W;
-    rs[RS_NT] = (float)nt;
-    rs[RS_MU] = mu;
-    rs[RS_P] = (float)(sur - (double)mu * sr);
-    rs[RS_RBAR] = (float)(sr / nt);
-    nsum += nt;
+    if (lane == 0) {
+      float* rs = row_stats + (size_t)t * RS_W;
+      rs[RS_NT] = (float)nt;
+      rs[RS_MU] = mu;
+      rs[RS_P] = (float)(sur - (double)mu * sr);
+      rs[RS_RBAR] = (float)(sr / nt);
+      nsum += nt;
+    }
   }
   nsum = block_sum(nsum, red);
   const float n_bar = n_bar_in ? *n_bar_in : (float)(nsum / (double)T);
@@ -250,7 +254,7 @@ __global__ void __launch_bounds__(256) weights_kernel(
 // ---- launchers ---------------------------------------------------------------------------------------
 cudaError_t launch_row_finish(const double* row_part, int T, int tpm, int weighted, const float* n_bar_in,
                               float* row_stats, float* pr_out, float* scalars, cudaStream_t st) {
-  row_finish_kernel<<<1, 256, 0, st>>>(row_part, T, tpm, weighted, n_bar_in, row_stats, pr_out, scalars);
+  row_finish_kernel<<<1, 1024, 0, st>>>(row_part, T, tpm, weighted, n_bar_in, row_stats, pr_out, scalars);
   return cudaGetLastError();
 }
 cudaError_t launch_col_partial(const float* g, const float* R, const uint8_t* mask, const float* u,

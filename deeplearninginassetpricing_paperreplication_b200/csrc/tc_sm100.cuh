@@ -106,6 +106,30 @@ __device__ __forceinline__ uint32_t tmem_addr(uint32_t base, uint32_t lane, uint
   return base + (lane << 16) + col;
 }
 
+// issue-only variants: several loads in flight, one tmem_wait_ld() before the registers are used
+__device__ __forceinline__ void tmem_ld16_nowait(uint32_t taddr, uint32_t* r) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr));
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, float* v) {
+  uint32_t r[32];
+  tmem_ld16_nowait(taddr, r);
+  tmem_ld16_nowait(taddr + 16, r + 16);
+  tmem_wait_ld();
+#pragma unroll
+  for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
+}
+// aligned start of the dynamic shared memory window, keeping the pointer in the shared address space
+__device__ __forceinline__ uint8_t* smem_align128(uint8_t* raw) {
+  return raw + ((128u - (smem_u32(raw) & 127u)) & 127u);
+}
+__device__ __forceinline__ float sigmoid_fast(float v) { return __fdividef(1.f, 1.f + __expf(-v)); }
+// |error| ~ 2e-7 absolute
+__device__ __forceinline__ float tanh_fast(float v) { return fmaf(2.f, sigmoid_fast(2.f * v), -1.f); }
+
 // ---- fp32 -> bf16 hi / lo split (a = hi + lo up to 2^-18 |a|) --------------------------------------
 // two values at a time; hi/lo are packed bf16x2 words with x in the low half
 __device__ __forceinline__ void split2(float x, float y, uint32_t& hi, uint32_t& lo) {
