@@ -24,11 +24,12 @@ cudaError_t launch_grad_finish(const float*, int, int, int, int, const float*, i
 cudaError_t launch_weights(const float*, const uint8_t*, const float*, int, int, int, float*, cudaStream_t);
 cudaError_t launch_macro_fwd_c(const dlap_plan* plan, const float* macro, const dlap_tensors* p, const float* h0,
                                const float* c0, float* save, float* a_t, float* c_t, float* hn, float* cn,
-                               cudaStream_t st);
+                               float* xp, cudaStream_t st);
 cudaError_t launch_macro_bwd_c(const dlap_plan* plan, const float* macro, const dlap_tensors* p, const float* h0,
                                const float* c0, const float* save, const float* dadc, float* dpre, int want_sdf,
                                int want_mom, const dlap_tensors* g, cudaStream_t st);
 size_t macro_fwd_smem(int T, int M, int H);
+size_t macro_bwd_smem(int T, int H);
 }  // namespace dlap
 
 using namespace dlap;
@@ -83,7 +84,8 @@ int dlap_make_plan(const dlap_dims* dims, int device, dlap_plan* out) {
   }
   CU(cudaDeviceGetAttribute(&smem_max, cudaDevAttrMaxSharedMemoryPerBlockOptin, device));
   if ((size_t)smem_max < smem_bwd_bytes(dims->F)) return DLAP_E_SMEM;
-  if (dims->M > 0 && (size_t)smem_max < macro_fwd_smem(dims->T, dims->M, dims->H)) return DLAP_E_SMEM;
+  if (dims->M > 0 && ((size_t)smem_max < macro_fwd_smem(dims->T, dims->M, dims->H) ||
+                      (size_t)smem_max < macro_bwd_smem(dims->T, dims->H))) return DLAP_E_SMEM;
   dlap_plan p;
   p.dims = *dims;
   const int T = dims->T, N = dims->N, F = dims->F;
@@ -100,7 +102,7 @@ int dlap_make_plan(const dlap_dims* dims, int device, dlap_plan* out) {
   p.ldwq = dims->M + F;
   p.row_part_bytes = (int64_t)T * p.tpm * 4 * 4 * 8;
   p.col_part_bytes = (int64_t)p.col_splits * (KM + 2) * N * 8;
-  p.loss_part_bytes = (int64_t)nb * 2 * 8;
+  p.loss_part_bytes = (int64_t)((N + 63) / 64) * 2 * 8;
   p.ds_part_bytes = (int64_t)T * p.row_splits * 8;
   p.wpart_bytes = (int64_t)p.grid_cell * wp_stride(round4(F)) * 4;
   p.dadc_part_bytes = (int64_t)T * p.tpm * 4 * 72 * 4;
@@ -136,15 +138,16 @@ static int set_dropout(CellParams& P, float p, uint64_t seed) {
 
 int dlap_macro_fwd(const dlap_plan* plan, const float* macro, const dlap_tensors* params, const float* h0,
                    const float* c0, float* lstm_save, float* a_t, float* c_t, float* hn, float* cn,
-                   void* stream) {
+                   float* xproj_scratch, void* stream) {
   int rc = check_plan(plan);
   if (rc) return rc;
   REQ(params); REQ(a_t); REQ(c_t); REQ(params->b1); REQ(params->bq);
   if (plan->dims.M > 0) {
-    REQ(macro); REQ(lstm_save); REQ(hn); REQ(cn);
+    REQ(macro); REQ(lstm_save); REQ(hn); REQ(cn); REQ(xproj_scratch);
     REQ(params->w_ih); REQ(params->w_hh); REQ(params->b_ih); REQ(params->b_hh); REQ(params->w1); REQ(params->wq);
   }
-  CU(launch_macro_fwd_c(plan, macro, params, h0, c0, lstm_save, a_t, c_t, hn, cn, (cudaStream_t)stream));
+  CU(launch_macro_fwd_c(plan, macro, params, h0, c0, lstm_save, a_t, c_t, hn, cn, xproj_scratch,
+                        (cudaStream_t)stream));
   return DLAP_OK;
 }
 

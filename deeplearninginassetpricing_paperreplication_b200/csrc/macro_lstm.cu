@@ -28,6 +28,7 @@ struct MacroParams {
   const float* c0;      // [H] or null
   // forward outputs
   float* save;          // [T, 6H]: h(H) c(H) i f g o (4H), post-activation
+  float* xp;            // [T, 4H] scratch: input projection (shares the dpre buffer)
   float* a_t;           // [T,64]
   float* c_t;           // [T,8]
   float* hn;            // [H]
@@ -50,43 +51,60 @@ __device__ __forceinline__ float tanh_fast(float v) { return fmaf(2.f, sigmoid_f
 
 constexpr int MT = 512;    // threads of the single-CTA macro kernels
 
-// dynamic smem: xp[T][4H] | Wih[4H][M] | Wqm[8][M]
+// Input projection for every month (multi-CTA, one warp per month):
+//   xp[t][r] = W_ih[r].macro_t + b_ih[r] + b_hh[r]   and   c_t[t][q] = Wq[q,:M].macro_t + bq[q]
+// dynamic smem: Wih[4H][M] | Wqm[8][M]
 template <int H>
-__global__ void __launch_bounds__(MT, 1) macro_fwd_kernel(const MacroParams P) {
+__global__ void __launch_bounds__(256) macro_proj_kernel(const MacroParams P) {
   extern __shared__ float sm[];
   const int T = P.T, M = P.M;
   constexpr int G4 = 4 * H;
-  float* xp = sm;
-  float* wih = xp + (size_t)T * G4;
+  float* wih = sm;
   float* wqm = wih + (size_t)G4 * M;
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, nwarp = MT / 32;
-
-  for (int i = tid; i < G4 * M; i += MT) wih[i] = __ldg(P.Wih + i);
-  for (int i = tid; i < KM * M; i += MT) wqm[i] = __ldg(P.Wq + (size_t)(i / M) * P.ldwq + (i % M));
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  for (int i = tid; i < G4 * M; i += 256) wih[i] = __ldg(P.Wih + i);
+  for (int i = tid; i < KM * M; i += 256) wqm[i] = __ldg(P.Wq + (size_t)(i / M) * P.ldwq + (i % M));
   __syncthreads();
-
-  // phase 1: one warp per month, lanes stride over the M macro series
-  for (int t = warp; t < T; t += nwarp) {
-    float acc[G4 + KM];
+  const int t = blockIdx.x * 8 + warp;
+  if (t >= T) return;
+  float acc[G4 + KM];
 #pragma unroll
-    for (int r = 0; r < G4 + KM; ++r) acc[r] = 0.f;
-    const float* row = P.macro + (size_t)t * M;
-    for (int k = lane; k < M; k += 32) {
-      const float v = __ldg(row + k);
+  for (int r = 0; r < G4 + KM; ++r) acc[r] = 0.f;
+  const float* row = P.macro + (size_t)t * M;
+  for (int k0 = 0; k0 < M; k0 += 128) {              // four independent loads in flight per lane
+    float v[4];
 #pragma unroll
-      for (int r = 0; r < G4; ++r) acc[r] = fmaf(v, wih[r * M + k], acc[r]);
+    for (int u = 0; u < 4; ++u) v[u] = (k0 + u * 32 + lane < M) ? __ldg(row + k0 + u * 32 + lane) : 0.f;
 #pragma unroll
-      for (int q = 0; q < KM; ++q) acc[G4 + q] = fmaf(v, wqm[q * M + k], acc[G4 + q]);
-    }
+    for (int u = 0; u < 4; ++u) {
+      const int k = k0 + u * 32 + lane;
+      if (k < M) {
 #pragma unroll
-    for (int r = 0; r < G4 + KM; ++r) acc[r] = warp_sum(acc[r]);
-    if (lane == 0) {
+        for (int r = 0; r < G4; ++r) acc[r] = fmaf(v[u], wih[r * M + k], acc[r]);
 #pragma unroll
-      for (int r = 0; r < G4; ++r) xp[t * G4 + r] = acc[r] + __ldg(P.bih + r) + __ldg(P.bhh + r);
-#pragma unroll
-      for (int q = 0; q < KM; ++q) P.c_t[(size_t)t * KM + q] = acc[G4 + q] + __ldg(P.bq + q);
+        for (int q = 0; q < KM; ++q) acc[G4 + q] = fmaf(v[u], wqm[q * M + k], acc[G4 + q]);
+      }
     }
   }
+#pragma unroll
+  for (int r = 0; r < G4 + KM; ++r) acc[r] = warp_sum(acc[r]);
+  if (lane == 0) {
+#pragma unroll
+    for (int r = 0; r < G4; ++r) P.xp[(size_t)t * G4 + r] = acc[r] + __ldg(P.bih + r) + __ldg(P.bhh + r);
+#pragma unroll
+    for (int q = 0; q < KM; ++q) P.c_t[(size_t)t * KM + q] = acc[G4 + q] + __ldg(P.bq + q);
+  }
+}
+
+// The serial part: one CTA.  dynamic smem: xp[T][4H]
+template <int H>
+__global__ void __launch_bounds__(MT, 1) macro_fwd_kernel(const MacroParams P) {
+  extern __shared__ float sm[];
+  const int T = P.T;
+  constexpr int G4 = 4 * H;
+  float* xp = sm;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  for (int i = tid; i < T * G4; i += MT) xp[i] = P.xp[i];
   __syncthreads();
 
   // phase 2: the recurrence on warp 0.  Lane j < H owns unit j and evaluates its four gates itself
@@ -144,7 +162,9 @@ __global__ void __launch_bounds__(MT, 1) macro_bptt_kernel(const MacroParams P) 
   const int T = P.T;
   constexpr int G4 = 4 * H;
   float* dh = sm;
+  float* sv_s = dh + (size_t)T * H;          // saved h,c,i,f,g,o of every month, [T][6H]
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  for (int i = tid; i < T * 6 * H; i += MT) sv_s[i] = P.save[i];
   // dh_t = W1[:,F:]^T . da_t
   for (int i = tid; i < T * H; i += MT) {
     const int t = i / H, k = i % H;
@@ -164,9 +184,9 @@ __global__ void __launch_bounds__(MT, 1) macro_bptt_kernel(const MacroParams P) 
   struct Step { float cc, gi, gf, gg, go, cprev, dhe; };
   auto fetch = [&](int t) {
     Step q;
-    const float* sv = P.save + (size_t)t * 6 * H;
+    const float* sv = sv_s + (size_t)t * 6 * H;
     q.cc = sv[H + j]; q.gi = sv[2 * H + j]; q.gf = sv[3 * H + j]; q.gg = sv[4 * H + j]; q.go = sv[5 * H + j];
-    q.cprev = (t > 0) ? P.save[(size_t)(t - 1) * 6 * H + H + j] : (P.c0 ? __ldg(P.c0 + j) : 0.f);
+    q.cprev = (t > 0) ? sv_s[(size_t)(t - 1) * 6 * H + H + j] : (P.c0 ? __ldg(P.c0 + j) : 0.f);
     q.dhe = dh[t * H + j];
     return q;
   };
@@ -208,7 +228,7 @@ __global__ void __launch_bounds__(128) macro_wgrad_kernel(const MacroParams P) {
   if (i < n_sdf) {
     if (i < G4 * M) {                                  // dW_ih[r][m] = sum_t dpre[t][r] macro[t][m]
       const int r = i / M, m = i % M;
-#pragma unroll 4
+#pragma unroll 8
       for (int t = 0; t < T; ++t) v = fmaf(__ldg(P.dpre + (size_t)t * G4 + r), __ldg(P.macro + (size_t)t * M + m), v);
       P.gWih[i] = v;
       return;
@@ -245,7 +265,7 @@ __global__ void __launch_bounds__(128) macro_wgrad_kernel(const MacroParams P) {
   i -= n_sdf;
   if (i < KM * M) {                                    // dWq[k][m] = sum_t dc_t[k] macro[t][m]
     const int k = i / M, m = i % M;
-#pragma unroll 4
+#pragma unroll 8
     for (int t = 0; t < T; ++t)
       v = fmaf(__ldg(P.dadc + (size_t)t * 72 + 64 + k), __ldg(P.macro + (size_t)t * M + m), v);
     P.gWq[(size_t)k * P.ldwq + m] = v;
@@ -256,12 +276,19 @@ __global__ void __launch_bounds__(128) macro_wgrad_kernel(const MacroParams P) {
   P.gbq[i] = v;
 }
 
-size_t macro_fwd_smem(int T, int M, int H) { return ((size_t)T * 4 * H + (size_t)4 * H * M + (size_t)KM * M) * 4; }
-size_t macro_bwd_smem(int T, int H) { return ((size_t)T * H) * 4; }
+size_t macro_fwd_smem(int T, int M, int H) { return (size_t)T * 4 * H * 4 + 0 * (size_t)M; }
+size_t macro_proj_smem(int M, int H) { return ((size_t)4 * H * M + (size_t)KM * M) * 4; }
+size_t macro_bwd_smem(int T, int H) { return ((size_t)T * H + (size_t)T * 6 * H) * 4; }
 
 template <int H>
 static cudaError_t launch_fwd_h(const MacroParams& P, size_t smem, cudaStream_t st) {
-  cudaError_t e = cudaFuncSetAttribute(macro_fwd_kernel<H>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  const size_t psm = macro_proj_smem(P.M, H);
+  cudaError_t e = cudaFuncSetAttribute(macro_proj_kernel<H>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)psm);
+  if (e != cudaSuccess) return e;
+  macro_proj_kernel<H><<<(P.T + 7) / 8, 256, psm, st>>>(P);
+  e = cudaGetLastError();
+  if (e != cudaSuccess) return e;
+  e = cudaFuncSetAttribute(macro_fwd_kernel<H>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
   macro_fwd_kernel<H><<<1, MT, smem, st>>>(P);
   return cudaGetLastError();
@@ -326,7 +353,7 @@ static void fill_macro(MacroParams& P, const dlap_plan* plan, const float* macro
 
 cudaError_t launch_macro_fwd_c(const dlap_plan* plan, const float* macro, const dlap_tensors* p, const float* h0,
                                const float* c0, float* save, float* a_t, float* c_t, float* hn, float* cn,
-                               cudaStream_t st) {
+                               float* xp, cudaStream_t st) {
   if (plan->dims.M == 0) {
     const int n = plan->dims.T * D1;
     const_bias_kernel<<<(n + 255) / 256, 256, 0, st>>>(p->b1, p->bq, plan->dims.T, a_t, c_t);
@@ -334,7 +361,7 @@ cudaError_t launch_macro_fwd_c(const dlap_plan* plan, const float* macro, const 
   }
   MacroParams P;
   fill_macro(P, plan, macro, p, h0, c0);
-  P.save = save; P.a_t = a_t; P.c_t = c_t; P.hn = hn; P.cn = cn;
+  P.save = save; P.a_t = a_t; P.c_t = c_t; P.hn = hn; P.cn = cn; P.xp = xp;
   return launch_macro_fwd(P, st);
 }
 

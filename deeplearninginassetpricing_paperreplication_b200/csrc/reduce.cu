@@ -14,29 +14,38 @@ namespace dlap {
 // P_t = sum m (u - mu_t) R = sum(m u R) - mu_t sum(m R)           src/model.py:363,367
 // pr_t = P_t / N_t * N_bar (weighted_loss) ; S_t = 1 + pr_t       src/model.py:360,367,380
 // sharpe = mean(pr) / (std_unbiased(pr) + 1e-8)                   src/model.py:551
-__global__ void __launch_bounds__(1024) row_finish_kernel(
-    const double* __restrict__ row_part, int T, int tpm, int weighted, const float* __restrict__ n_bar_in,
-    float* __restrict__ row_stats, float* __restrict__ pr_out, float* __restrict__ scalars) {
-  __shared__ double red[32];
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, nwarp = blockDim.x >> 5;
-  // one warp per month: lanes stride over the partial slots, fixed-tree warp sum
-  double nsum = 0.0;
-  for (int t = warp; t < T; t += nwarp) {
-    double c = 0, su = 0, sur = 0, sr = 0;
-    const double* p = row_part + (size_t)t * tpm * 4;
-    for (int j = lane; j < tpm; j += 32) { c += p[4 * j]; su += p[4 * j + 1]; sur += p[4 * j + 2]; sr += p[4 * j + 3]; }
-    c = warp_sum(c); su = warp_sum(su); sur = warp_sum(sur); sr = warp_sum(sr);
+// stage 1 (multi-CTA): one warp per month sums the per-tile partial slots in a fixed tree
+__global__ void __launch_bounds__(256) row_sum_kernel(const double* __restrict__ row_part, int T, int tpm,
+                                                      float* __restrict__ row_stats) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int t = blockIdx.x * 8 + warp;
+  if (t >= T) return;
+  double c = 0, su = 0, sur = 0, sr = 0;
+  const double4* p = reinterpret_cast<const double4*>(row_part) + (size_t)t * tpm;
+  for (int j = lane; j < tpm; j += 32) {
+    const double4 v = p[j];
+    c += v.x; su += v.y; sur += v.z; sr += v.w;
+  }
+  c = warp_sum(c); su = warp_sum(su); sur = warp_sum(sur); sr = warp_sum(sr);
+  if (lane == 0) {
     const double nt = fmax(c, 1.0);
     const float mu = (float)(su / nt);
-    if (lane == 0) {
-      float* rs = row_stats + (size_t)t * RS_W;
-      rs[RS_NT] = (float)nt;
-      rs[RS_MU] = mu;
-      rs[RS_P] = (float)(sur - (double)mu * sr);
-      rs[RS_RBAR] = (float)(sr / nt);
-      nsum += nt;
-    }
+    float* rs = row_stats + (size_t)t * RS_W;
+    rs[RS_NT] = (float)nt;
+    rs[RS_MU] = mu;
+    rs[RS_P] = (float)(sur - (double)mu * sr);
+    rs[RS_RBAR] = (float)(sr / nt);
   }
+}
+
+// stage 2 (one CTA): N_bar, pr_t, S_t, Sharpe from the T per-month rows
+__global__ void __launch_bounds__(1024) row_finish_kernel(
+    int T, int weighted, const float* __restrict__ n_bar_in, float* __restrict__ row_stats,
+    float* __restrict__ pr_out, float* __restrict__ scalars) {
+  __shared__ double red[32];
+  const int tid = threadIdx.x;
+  double nsum = 0.0;
+  for (int t = tid; t < T; t += blockDim.x) nsum += (double)row_stats[(size_t)t * RS_W + RS_NT];
   nsum = block_sum(nsum, red);
   const float n_bar = n_bar_in ? *n_bar_in : (float)(nsum / (double)T);
   double s1 = 0.0;
@@ -103,7 +112,7 @@ __global__ void __launch_bounds__(256) col_partial_kernel(
 
 // ---- loss finish -----------------------------------------------------------------------------
 // e_ki = colsum / T_i ; L_c = mean_k mean_i e_ki^2 ; L_u = mean_i e0_i^2   src/model.py:382-385,428-431
-__global__ void __launch_bounds__(256) loss_finish_kernel(
+__global__ void __launch_bounds__(64) loss_finish_kernel(
     const double* __restrict__ col_part, int nsplit, int N, int n_total, float* __restrict__ e_out,
     float* __restrict__ ti_out, double* __restrict__ loss_part, unsigned int* __restrict__ counter,
     float* __restrict__ scalars) {
@@ -199,8 +208,14 @@ __global__ void __launch_bounds__(256) grad_finish_kernel(
   const int Fr = round4(F), stride = wp_stride(Fr);
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx < stride) {
-    float v = 0.f;
-    for (int c = 0; c < ncta; ++c) v += wpart[(size_t)c * stride + idx];
+    float v4[4] = {0.f, 0.f, 0.f, 0.f};
+    int c = 0;
+    for (; c + 4 <= ncta; c += 4) {
+#pragma unroll
+      for (int u = 0; u < 4; ++u) v4[u] += wpart[(size_t)(c + u) * stride + idx];
+    }
+    for (; c < ncta; ++c) v4[0] += wpart[(size_t)c * stride + idx];
+    const float v = (v4[0] + v4[1]) + (v4[2] + v4[3]);
     if (idx < wp_off_w1()) {
       if (have_sdf) gW2[idx] = v;
     } else if (idx < wp_off_wq(Fr)) {
@@ -220,10 +235,15 @@ __global__ void __launch_bounds__(256) grad_finish_kernel(
     const int r = idx - stride;
     if (r < T * 72) {
       const int t = r / 72, c = r % 72;
-      float v = 0.f;
+      float v8[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
       const float* p = dadc_part + (size_t)t * tpm * 72 + c;
-      for (int j = 0; j < tpm; ++j) v += p[(size_t)j * 72];
-      dadc[r] = v;
+      int j = 0;
+      for (; j + 8 <= tpm; j += 8) {
+#pragma unroll
+        for (int u = 0; u < 8; ++u) v8[u] += p[(size_t)(j + u) * 72];
+      }
+      for (; j < tpm; ++j) v8[0] += p[(size_t)j * 72];
+      dadc[r] = ((v8[0] + v8[1]) + (v8[2] + v8[3])) + ((v8[4] + v8[5]) + (v8[6] + v8[7]));
     }
   }
 }
@@ -254,7 +274,8 @@ __global__ void __launch_bounds__(256) weights_kernel(
 // ---- launchers ---------------------------------------------------------------------------------------
 cudaError_t launch_row_finish(const double* row_part, int T, int tpm, int weighted, const float* n_bar_in,
                               float* row_stats, float* pr_out, float* scalars, cudaStream_t st) {
-  row_finish_kernel<<<1, 1024, 0, st>>>(row_part, T, tpm, weighted, n_bar_in, row_stats, pr_out, scalars);
+  row_sum_kernel<<<(T + 7) / 8, 256, 0, st>>>(row_part, T, tpm, row_stats);
+  row_finish_kernel<<<1, T < 1024 ? ((T + 31) / 32) * 32 : 1024, 0, st>>>(T, weighted, n_bar_in, row_stats, pr_out, scalars);
   return cudaGetLastError();
 }
 cudaError_t launch_col_partial(const float* g, const float* R, const uint8_t* mask, const float* u,
@@ -269,7 +290,7 @@ cudaError_t launch_col_partial(const float* g, const float* R, const uint8_t* ma
 cudaError_t launch_loss_finish(const double* col_part, int nsplit, int N, int n_total, float* e_out,
                                float* ti_out, double* loss_part, unsigned int* counter, float* scalars,
                                cudaStream_t st) {
-  loss_finish_kernel<<<(N + 255) / 256, 256, 0, st>>>(col_part, nsplit, N, n_total, e_out, ti_out,
+  loss_finish_kernel<<<(N + 63) / 64, 64, 0, st>>>(col_part, nsplit, N, n_total, e_out, ti_out,
                                                       loss_part, counter, scalars);
   return cudaGetLastError();
 }
@@ -314,7 +335,7 @@ cudaError_t launch_weights(const float* u, const uint8_t* mask, const float* row
 // kernel a host address; the device address has to be asked for with cudaGetSymbolAddress, per device.
 namespace {
 constexpr int kNoAllocMaxStocks = DLAP_NOALLOC_MAX_STOCKS;
-constexpr int kNoAllocBlocks = (kNoAllocMaxStocks + 255) / 256;
+constexpr int kNoAllocBlocks = (kNoAllocMaxStocks + 63) / 64;
 constexpr size_t kLossPartBytes = (size_t)kNoAllocBlocks * 2 * sizeof(double);
 constexpr size_t kCounterOffset = kLossPartBytes;                 // 8-byte aligned, holds one uint32
 constexpr size_t kNoAllocBytes = kLossPartBytes + 256;

@@ -176,8 +176,8 @@ def macro_forward(ws: Workspace, macro, params, h0, c0):
     cn = torch.empty(H, dtype=torch.float32, device=dev)
     tens = _tensors(params)
     _lib.call("dlap_macro_fwd", ws.pp, _ptr(macro), C.byref(tens), _ptr(h0), _ptr(c0), _ptr(save),
-              _ptr(a_t), _ptr(c_t), _ptr(hn), _ptr(cn), _stream(dev))
-    ws.launches += 1
+              _ptr(a_t), _ptr(c_t), _ptr(hn), _ptr(cn), _ptr(ws.dpre), _stream(dev))
+    ws.launches += 2 if ws.plan.dims.M > 0 else 1
     return save, a_t, c_t, hn, cn
 
 

@@ -63,7 +63,7 @@ typedef struct dlap_plan {
   int32_t ldwq;           /* row pitch of moment output_proj.weight = M + F */
   int64_t row_part_bytes;   /* double [T, tpm, 4 slots, 4]  */
   int64_t col_part_bytes;   /* double [col_splits, 10, N]   */
-  int64_t loss_part_bytes;  /* double [ceil(N/256), 2]      */
+  int64_t loss_part_bytes;  /* double [ceil(N/64), 2]       */
   int64_t ds_part_bytes;    /* double [T, row_splits]       */
   int64_t wpart_bytes;      /* float  [grid_cell, wstride]  */
   int64_t dadc_part_bytes;  /* float  [T, tpm, 4 slots, 72] */
@@ -91,10 +91,12 @@ int dlap_make_plan(const dlap_dims* dims, int device, dlap_plan* out);
  * replace the tile-over-N concats: a_t = W1[:,F:].h_t + b1 (src/model.py:253-255, :211) and
  * c_t = Wq[:,:M].macro_t + bq (src/model.py:514-516, :152).  h0/c0 [H] may be NULL (zero state).
  * Outputs: lstm_save [T,6H] (h,c,i,f,g,o), a_t [T,64], c_t [T,8], hn/cn [H].  With M = 0 only
- * a_t = b1 and c_t = bq are produced. */
+ * a_t = b1 and c_t = bq are produced.  xproj_scratch: [T,4H] floats (plan->dpre_bytes; the same buffer
+ * may later serve as dlap_macro_bwd's dpre).  Two launches: a multi-CTA input projection, then the
+ * single-CTA recurrence. */
 int dlap_macro_fwd(const dlap_plan* plan, const float* macro, const dlap_tensors* params,
                    const float* h0, const float* c0, float* lstm_save, float* a_t, float* c_t,
-                   float* hn, float* cn, void* stream);
+                   float* hn, float* cn, float* xproj_scratch, void* stream);
 
 /* SDFNetwork.forward body on every stock-month (src/model.py:251-271) and MomentNetwork.forward
  * (src/model.py:132-161 with the input of :514-518): u = MLP(x | a_t) [T,N];
@@ -133,7 +135,7 @@ int dlap_loss_finish(const dlap_plan* plan, const double* col_part, int nsplit, 
  * in the reference: it exists for hosts that run on a fixed, pre-partitioned memory budget, that sit
  * in a latency-bound loop where cudaMalloc/cudaFree (driver locks, device synchronisation) are
  * forbidden, or that only ever receive raw pointers from another runtime.  The two scratch buffers
- * (`loss_part`, `counter`) live in an array inside the library image instead: ~17 KB on every GPU that
+ * (`loss_part`, `counter`) live in an array inside the library image instead: ~66 KB on every GPU that
  * loads the library, for the life of the process.  Limits and rules:
  *   - at most DLAP_NOALLOC_MAX_STOCKS stocks (plan->dims.N); beyond that the call returns DLAP_E_LIMIT;
  *   - the first call on each device looks up the array's device address (one-time set-up with that
