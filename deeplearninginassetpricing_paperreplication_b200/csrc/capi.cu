@@ -19,8 +19,8 @@ cudaError_t launch_loss_finish(const double*, int, int, int, float*, float*, dou
 cudaError_t launch_coeff(const float*, const float*, int, const float*, const float*, float*, cudaStream_t);
 cudaError_t launch_ds_rows(const float*, const float*, const uint8_t*, const float*, int, int, int, double*,
                            cudaStream_t);
-cudaError_t launch_grad_finish(const float*, int, int, int, int, const float*, int, int, float*, int, float*,
-                               float*, float*, float*, float*, int, int, float*, cudaStream_t);
+cudaError_t launch_grad_finish(const float*, int, int, int, int, const float*, int, int, int, int, float*, int,
+                               float*, float*, float*, float*, float*, int, int, float*, cudaStream_t);
 cudaError_t launch_weights(const float*, const uint8_t*, const float*, int, int, int, float*, cudaStream_t);
 cudaError_t launch_macro_fwd_c(const dlap_plan* plan, const float* macro, const dlap_tensors* p, const float* h0,
                                const float* c0, float* save, float* a_t, float* c_t, float* hn, float* cn,
@@ -105,7 +105,7 @@ int dlap_make_plan(const dlap_dims* dims, int device, dlap_plan* out) {
   p.loss_part_bytes = (int64_t)((N + 63) / 64) * 2 * 8;
   p.ds_part_bytes = (int64_t)T * p.row_splits * 8;
   p.wpart_bytes = (int64_t)p.grid_cell * wp_stride(round4(F)) * 4;
-  p.dadc_part_bytes = (int64_t)T * p.tpm * 4 * 72 * 4;
+  p.dadc_part_bytes = (int64_t)T * (p.tpm > 4 ? p.tpm : 4) * 72 * 4;
   p.lstm_save_bytes = (int64_t)T * 6 * (dims->H > 0 ? dims->H : 1) * 4;
   p.dpre_bytes = (int64_t)T * 4 * (dims->H > 0 ? dims->H : 1) * 4;
   *out = p;
@@ -176,12 +176,13 @@ int dlap_cell_fwd(const dlap_plan* plan, const float* x, const float* R, const u
   return DLAP_OK;
 }
 
-int dlap_row_finish(const dlap_plan* plan, const double* row_part, int slots_per_tile, int weighted_loss,
+int dlap_row_finish(const dlap_plan* plan, const double* row_part, int precision, int weighted_loss,
                     const float* n_bar_in, float* row_stats, float* pr, float* scalars, void* stream) {
   int rc = check_plan(plan);
   if (rc) return rc;
   REQ(row_part); REQ(row_stats); REQ(pr); REQ(scalars);
-  if (slots_per_tile != 1 && slots_per_tile != 4) return DLAP_E_SHAPE;
+  if (precision != DLAP_PREC_FP32 && precision != DLAP_PREC_BF16X3) return DLAP_E_PRECISION;
+  const int slots_per_tile = precision == DLAP_PREC_BF16X3 ? 4 : 1;
   CU(launch_row_finish(row_part, plan->dims.T, plan->tpm * slots_per_tile, weighted_loss, n_bar_in, row_stats, pr, scalars,
                        (cudaStream_t)stream));
   return DLAP_OK;
@@ -256,16 +257,22 @@ int dlap_cell_bwd(const dlap_plan* plan, const float* x, const float* R, const u
   return DLAP_OK;
 }
 
-int dlap_grad_finish(const dlap_plan* plan, const float* wpart, const float* dadc_part, int slots_per_tile,
+int dlap_grad_finish(const dlap_plan* plan, const float* wpart, const float* dadc_part, int precision,
                      int want_sdf, int want_mom, const dlap_tensors* grads, float* dadc, void* stream) {
   int rc = check_plan(plan);
   if (rc) return rc;
-  if (slots_per_tile != 1 && slots_per_tile != 4) return DLAP_E_SHAPE;
+  if (precision != DLAP_PREC_FP32 && precision != DLAP_PREC_BF16X3) return DLAP_E_PRECISION;
+  // fp32 kernel: one da_t|dc_t partial per tile; tensor-core kernel: one per (month, CTA) segment
+  int slots = plan->tpm, seg_chunk = 0;
+  if (precision == DLAP_PREC_BF16X3) {
+    seg_chunk = tc_chunk((long long)plan->dims.T * plan->tpm, plan->grid_cell);
+    slots = tc_seg_max(plan->tpm, seg_chunk);
+  }
   REQ(wpart); REQ(dadc_part); REQ(grads); REQ(dadc);
   if (want_sdf) { REQ(grads->w1); REQ(grads->w2); REQ(grads->b2); REQ(grads->w3); REQ(grads->b3); }
   if (want_mom) REQ(grads->wq);
   CU(launch_grad_finish(wpart, plan->grid_cell, plan->dims.F, want_sdf, want_mom, dadc_part, plan->dims.T,
-                        plan->tpm * slots_per_tile, grads->w1, plan->ldw1, grads->w2, grads->b2, grads->w3, grads->b3, grads->wq,
+                        slots, plan->tpm, seg_chunk, grads->w1, plan->ldw1, grads->w2, grads->b2, grads->w3, grads->b3, grads->wq,
                         plan->ldwq, plan->dims.M, dadc, (cudaStream_t)stream));
   return DLAP_OK;
 }

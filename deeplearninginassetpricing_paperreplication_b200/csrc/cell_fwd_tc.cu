@@ -106,7 +106,7 @@ __global__ void __launch_bounds__(NT_TC, 1) cell_fwd_tc_kernel(const CellParams 
           const uint64_t ah = tc::smem_desc(smem_u32(s.xh(sl)), TILE * 16, 128), al = tc::smem_desc(smem_u32(s.xl(sl)), TILE * 16, 128);
           const uint64_t bh = tc::smem_desc(smem_u32(s.w1h(sl)), N1 * 16, 128), bl = tc::smem_desc(smem_u32(s.w1l(sl)), N1 * 16, 128);
           const uint32_t d = tbase + (sl ? COL_A1 : COL_A0);
-          if (lane == 0) {
+          if (tc::elect_one()) {
 #pragma unroll
             for (int ks = 0; ks < KG1 / 2; ++ks)
               umma3(d, tc::desc_advance(ah, ks * 2 * TILE * 16), tc::desc_advance(al, ks * 2 * TILE * 16),
@@ -123,7 +123,7 @@ __global__ void __launch_bounds__(NT_TC, 1) cell_fwd_tc_kernel(const CellParams 
           tc::fence_after_sync();
           const uint64_t ah = tc::smem_desc(smem_u32(s.hh(sl)), TILE * 16, 128), al = tc::smem_desc(smem_u32(s.hl(sl)), TILE * 16, 128);
           const uint32_t d = tbase + (sl ? COL_B1 : COL_B0);
-          if (lane == 0) {
+          if (tc::elect_one()) {
 #pragma unroll
             for (int ks = 0; ks < KG2 / 2; ++ks)
               umma3(d, tc::desc_advance(ah, ks * 2 * TILE * 16), tc::desc_advance(al, ks * 2 * TILE * 16),

@@ -201,7 +201,8 @@ __global__ void __launch_bounds__(256) ds_rows_kernel(
 // ---- backward: sum per-CTA / per-tile partials into the reference's gradient layouts ----------------
 __global__ void __launch_bounds__(256) grad_finish_kernel(
     const float* __restrict__ wpart, int ncta, int F, int have_sdf, int have_mom,
-    const float* __restrict__ dadc_part, int T, int tpm /* partial slots per month */,
+    const float* __restrict__ dadc_part, int T, int tpm /* partial slots per month */, int tpm_tiles,
+    int seg_chunk /* > 0: segment layout of the tensor-core kernel */,
     float* __restrict__ gW1, int ldw1, float* __restrict__ gW2, float* __restrict__ gb2,
     float* __restrict__ gW3, float* __restrict__ gb3, float* __restrict__ gWq, int ldwq, int wq_off,
     float* __restrict__ dadc) {
@@ -237,6 +238,8 @@ __global__ void __launch_bounds__(256) grad_finish_kernel(
       const int t = r / 72, c = r % 72;
       float v8[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
       const float* p = dadc_part + (size_t)t * tpm * 72 + c;
+      if (seg_chunk > 0)       // only the segments that exist for this month were written
+        tpm = ((t + 1) * tpm_tiles - 1) / seg_chunk - (t * tpm_tiles) / seg_chunk + 1;
       int j = 0;
       for (; j + 8 <= tpm; j += 8) {
 #pragma unroll
@@ -307,12 +310,13 @@ cudaError_t launch_ds_rows(const float* g, const float* R, const uint8_t* mask, 
   return cudaGetLastError();
 }
 cudaError_t launch_grad_finish(const float* wpart, int ncta, int F, int have_sdf, int have_mom,
-                               const float* dadc_part, int T, int tpm, float* gW1, int ldw1, float* gW2,
+                               const float* dadc_part, int T, int tpm, int tpm_tiles, int seg_chunk, float* gW1,
+                               int ldw1, float* gW2,
                                float* gb2, float* gW3, float* gb3, float* gWq, int ldwq, int wq_off,
                                float* dadc, cudaStream_t st) {
   const int total = wp_stride(round4(F)) + T * 72;
   grad_finish_kernel<<<(total + 255) / 256, 256, 0, st>>>(wpart, ncta, F, have_sdf, have_mom, dadc_part, T,
-                                                          tpm, gW1, ldw1, gW2, gb2, gW3, gb3, gWq, ldwq,
+                                                          tpm, tpm_tiles, seg_chunk, gW1, ldw1, gW2, gb2, gW3, gb3, gWq, ldwq,
                                                           wq_off, dadc);
   return cudaGetLastError();
 }

@@ -31,7 +31,6 @@ RS_NT, RS_MU, RS_P, RS_PR, RS_S, RS_RBAR = 0, 1, 2, 3, 4, 5
 KM = 8
 
 _PRECISIONS = {"fp32": _lib.DLAP_PREC_FP32, "bf16x3": _lib.DLAP_PREC_BF16X3}
-_ROW_SLOTS = {"fp32": 1, "bf16x3": 4}
 _BWD_PRECISION = {"fp32": "fp32", "bf16x3": "bf16x3"}     # arithmetic of dlap_cell_bwd per model precision
 
 
@@ -211,7 +210,7 @@ class GanStepFn(torch.autograd.Function):
             row_stats = torch.empty(T, RS_W, dtype=torch.float32, device=dev)
             pr = torch.empty(T, dtype=torch.float32, device=dev)
             scalars = torch.zeros(SC_W, dtype=torch.float32, device=dev)
-            _lib.call("dlap_row_finish", ws.pp, _ptr(ws.row_part), _ROW_SLOTS[opts.precision],
+            _lib.call("dlap_row_finish", ws.pp, _ptr(ws.row_part), prec,
                       int(opts.weighted_loss),
                       _ptr(sh.n_bar) if sh is not None else None, _ptr(row_stats), _ptr(pr),
                       _ptr(scalars), st)
@@ -276,8 +275,7 @@ class GanStepFn(torch.autograd.Function):
             grads = [None if p is None else torch.zeros_like(p) for p in params]
             gt = _tensors(grads)
             dadc = torch.empty(T, 72, dtype=torch.float32, device=dev)
-            _lib.call("dlap_grad_finish", ws.pp, _ptr(ws.wpart), _ptr(ws.dadc_part),
-                      _ROW_SLOTS[_BWD_PRECISION[opts.precision]], int(want_sdf),
+            _lib.call("dlap_grad_finish", ws.pp, _ptr(ws.wpart), _ptr(ws.dadc_part), prec, int(want_sdf),
                       int(want_mom), C.byref(gt), _ptr(dadc), st)
             ws.launches += 4
             if sh is None:
@@ -322,7 +320,7 @@ def sdf_weights(macro, x, mask, params, h0=None, c0=None, normalized=False, prec
         row_stats = torch.empty(T, RS_W, dtype=torch.float32, device=dev)
         pr = torch.empty(T, dtype=torch.float32, device=dev)
         scalars = torch.empty(SC_W, dtype=torch.float32, device=dev)
-        _lib.call("dlap_row_finish", ws.pp, _ptr(ws.row_part), _ROW_SLOTS[precision], int(weighted_loss), None,
+        _lib.call("dlap_row_finish", ws.pp, _ptr(ws.row_part), _PRECISIONS[precision], int(weighted_loss), None,
                   _ptr(row_stats),
                   _ptr(pr), _ptr(scalars), st)
         w = torch.empty(T, N, dtype=torch.float32, device=dev)

@@ -66,7 +66,7 @@ typedef struct dlap_plan {
   int64_t loss_part_bytes;  /* double [ceil(N/64), 2]       */
   int64_t ds_part_bytes;    /* double [T, row_splits]       */
   int64_t wpart_bytes;      /* float  [grid_cell, wstride]  */
-  int64_t dadc_part_bytes;  /* float  [T, tpm, 4 slots, 72] */
+  int64_t dadc_part_bytes;  /* float  [T, max(tpm,4), 72]   */
   int64_t lstm_save_bytes;  /* float  [T, 6H]               */
   int64_t dpre_bytes;       /* float  [T, 4H]               */
 } dlap_plan;
@@ -113,9 +113,9 @@ int dlap_cell_fwd(const dlap_plan* plan, const float* x, const float* R, const u
 /* Per-month statistics: N_t, mu_t (src/model.py:276-278), P_t, portfolio return pr_t and
  * S_t = 1 + pr_t (src/model.py:359-367, :380), Rbar_t; N_bar (src/model.py:360) and the Sharpe
  * ratio of pr (src/model.py:551) into scalars[3], scalars[2].  n_bar_in (device, 1 float) overrides
- * N_bar when the panel is one month-shard of a larger one; NULL otherwise.  slots_per_tile: partial
- * sums dlap_cell_fwd wrote per tile (1 for DLAP_PREC_FP32, 4 for DLAP_PREC_BF16X3). */
-int dlap_row_finish(const dlap_plan* plan, const double* row_part, int slots_per_tile, int weighted_loss,
+ * N_bar when the panel is one month-shard of a larger one; NULL otherwise.  precision: the selector
+ * dlap_cell_fwd ran with (it fixes the layout of row_part). */
+int dlap_row_finish(const dlap_plan* plan, const double* row_part, int precision, int weighted_loss,
                     const float* n_bar_in, float* row_stats, float* pr, float* scalars, void* stream);
 
 /* Per-stock sums over the months of each chunk: sum_t g_k S_t, sum_t R m S_t, sum_t m
@@ -170,8 +170,9 @@ int dlap_cell_bwd(const dlap_plan* plan, const float* x, const float* R, const u
 
 /* Fixed-order sum of the partials into the reference's gradient layouts: grads->w1[:, :F], w2, b2,
  * w3, b3 (= 0, demeaning), wq[:, M:]; and dadc [T,72] = da_t | dc_t summed over stocks.
- * slots_per_tile: da_t|dc_t partials dlap_cell_bwd wrote per tile (1 for FP32, 4 for BF16X3). */
-int dlap_grad_finish(const dlap_plan* plan, const float* wpart, const float* dadc_part, int slots_per_tile,
+ * precision: the selector dlap_cell_bwd ran with (it fixes the layout of dadc_part: one partial per
+ * tile for FP32, one per (month, CTA) segment for BF16X3). */
+int dlap_grad_finish(const dlap_plan* plan, const float* wpart, const float* dadc_part, int precision,
                      int want_sdf, int want_mom, const dlap_tensors* grads, float* dadc, void* stream);
 
 /* Month-level backward: dh_t = W1[:,F:]^T da_t, LSTM BPTT, and the month-summed gradients
@@ -192,6 +193,19 @@ int dlap_weights(const dlap_plan* plan, const float* u, const uint8_t* mask, con
 int dlap_umma_selftest(const void* a_img, int a_bytes, const void* b_img, int b_bytes, int M, int N, int K,
                        int a_mn_major, int b_mn_major, int a_lbo, int a_sbo, int a_kstep, int b_lbo,
                        int b_sbo, int b_kstep, float* D, void* stream);
+
+/* As dlap_umma_selftest, but the A operand [128,K] (row-major bf16 in global memory) is placed in
+ * tensor memory by its owning lanes and the MMA reads it from there (A-from-TMEM form). repeat > 1 and a
+ * non-NULL cycles turn it into a timing run.  No counterpart in the reference. */
+int dlap_umma_ts_selftest(const void* a_rowmajor, const void* b_img, int b_bytes, int N, int K,
+                          int b_mn_major, int b_lbo, int b_sbo, int b_kstep, int repeat, float* D,
+                          long long* cycles, void* stream);
+
+/* Timing twin of dlap_umma_selftest (no counterpart in the reference): the K loop is issued `repeat`
+ * times back to back on one CTA; *cycles (device int64) receives the SM cycles until completion. */
+int dlap_umma_cycles(const void* a_img, int a_bytes, const void* b_img, int b_bytes, int M, int N, int K,
+                     int a_mn_major, int b_mn_major, int a_lbo, int a_sbo, int a_kstep, int b_lbo, int b_sbo,
+                     int b_kstep, int repeat, float* D, long long* cycles, void* stream);
 
 #ifdef __cplusplus
 }

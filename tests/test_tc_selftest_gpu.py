@@ -96,3 +96,33 @@ def test_umma_m64_row_mapping_is_recorded():
     os.makedirs("gpurun_out", exist_ok=True)
     open("gpurun_out/umma_m64_map.txt", "w").write(" ".join(map(str, rows)) + "\n")
     assert sum(r >= 0 for r in rows) == 64
+
+
+@pytest.mark.parametrize("N,K,b_mn", [(64, 64, 0), (64, 64, 1), (80, 48, 0)])
+def test_umma_a_from_tmem(N, K, b_mn):
+    """A operand in tensor memory (lane = row, 32-bit column = two consecutive K values)."""
+    dev = torch.device("cuda:0")
+    g = torch.Generator().manual_seed(N + K + b_mn)
+    A = torch.randn(128, K, generator=g).to(torch.bfloat16)
+    if b_mn:
+        Tb = torch.randn(K, N, generator=g); b_img, b_val = pack(Tb); B = b_val.t(); b_other = K
+    else:
+        Tb = torch.randn(N, K, generator=g); b_img, b_val = pack(Tb); B = b_val; b_other = N
+    ref = (A.double() @ B.double().t()).float()
+    D = torch.full((128, N), float("nan"), device=dev)
+    b_img = b_img.to(dev); A_d = A.contiguous().to(dev)
+    _lib.call("dlap_umma_ts_selftest", A_d.data_ptr(), b_img.data_ptr(), b_img.numel() * 2, N, K, b_mn,
+              *strides(b_other, b_mn), 1, D.data_ptr(), None, None)
+    torch.cuda.synchronize()
+    err = (D.cpu() - ref).abs().max().item()
+    assert err < 1e-3 * ref.abs().max().item(), err
+    cyc = torch.zeros(1, dtype=torch.int64, device=dev)
+    out = []
+    for rep in (1, 64):
+        _lib.call("dlap_umma_ts_selftest", A_d.data_ptr(), b_img.data_ptr(), b_img.numel() * 2, N, K, b_mn,
+                  *strides(b_other, b_mn), rep, D.data_ptr(), cyc.data_ptr(), None)
+        torch.cuda.synchronize()
+        out.append(int(cyc))
+    per = (out[1] - out[0]) / (63 * (K // 16))
+    os.makedirs("gpurun_out", exist_ok=True)
+    open("gpurun_out/umma_ts_cycles.txt", "a").write(f"TS N={N} K={K} b_mn={b_mn}: {per:.1f} cycles per MMA\n")
