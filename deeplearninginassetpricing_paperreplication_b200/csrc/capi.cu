@@ -11,7 +11,8 @@ cudaError_t launch_cell_bwd_f32(const CellParams& P, int grid, bool sdf, bool mo
 cudaError_t launch_cell_fwd_tc(const CellParams& P, int grid, cudaStream_t st);
 cudaError_t launch_cell_bwd_tc(const CellParams& P, int grid, bool sdf, bool mom, cudaStream_t st);
 size_t smem_bwd_bytes(int F);
-cudaError_t launch_row_finish(const double*, int, int, int, const float*, float*, float*, float*, cudaStream_t);
+cudaError_t launch_row_finish(const double*, int, int, int, int, int, const float*, float*, float*, float*,
+                              cudaStream_t);
 cudaError_t launch_col_partial(const float*, const float*, const uint8_t*, const float*, const float*, int, int,
                                int, double*, float*, cudaStream_t);
 cudaError_t launch_loss_finish(const double*, int, int, int, float*, float*, double*, unsigned int*, float*,
@@ -93,7 +94,7 @@ int dlap_make_plan(const dlap_dims* dims, int device, dlap_plan* out) {
   const long long ntiles = (long long)T * p.tpm;
   p.grid_cell = (int)(ntiles < sms ? ntiles : sms);
   // reductions: aim for ~4 CTAs per SM
-  const int nb = (N + 255) / 256, want = 4 * sms;
+  const int nb = (N + 255) / 256, want = 2 * sms;
   int cs = (want + nb - 1) / nb; if (cs > T) cs = T; if (cs < 1) cs = 1;
   p.col_splits = cs;
   int rs = (want + T - 1) / T; if (rs > nb) rs = nb; if (rs < 1) rs = 1;
@@ -182,8 +183,9 @@ int dlap_row_finish(const dlap_plan* plan, const double* row_part, int precision
   if (rc) return rc;
   REQ(row_part); REQ(row_stats); REQ(pr); REQ(scalars);
   if (precision != DLAP_PREC_FP32 && precision != DLAP_PREC_BF16X3) return DLAP_E_PRECISION;
-  const int slots_per_tile = precision == DLAP_PREC_BF16X3 ? 4 : 1;
-  CU(launch_row_finish(row_part, plan->dims.T, plan->tpm * slots_per_tile, weighted_loss, n_bar_in, row_stats, pr, scalars,
+  // fp32 kernel: one row-sum partial per tile; tensor-core kernel: one per tile and TMEM lane quarter
+  const int slots = plan->tpm * (precision == DLAP_PREC_BF16X3 ? 4 : 1), seg_chunk = 0;
+  CU(launch_row_finish(row_part, plan->dims.T, slots, plan->tpm, seg_chunk, weighted_loss, n_bar_in, row_stats, pr, scalars,
                        (cudaStream_t)stream));
   return DLAP_OK;
 }

@@ -183,6 +183,12 @@ __global__ void __launch_bounds__(NT_TC, 1) cell_fwd_tc_kernel(const CellParams 
       const int t = tile / P.tpm, jt = tile % P.tpm, n0 = jt * TILE;
       const int ncell = min(TILE, P.N - n0);
       const uint32_t dA = tbase + lane_base + (sl ? COL_A1 : COL_A0), dB = tbase + lane_base + (sl ? COL_B1 : COL_B0);
+      // this cell's mask / return: issued now, consumed after both layers (HBM latency hidden)
+      const bool live = cell < ncell;
+      const size_t gi = (size_t)t * P.N + n0 + cell;
+      unsigned char m8 = 0;
+      float r = 0.f;
+      if (live) { m8 = P.mask[gi]; if (P.R) r = __ldg(P.R + gi); }
       // -- after layer 1: h1 = relu(z1) -> bf16 hi/lo image
       mbar_wait(bar + F_D1_FULL + sl, use & 1);
       tc::fence_after_sync();
@@ -237,12 +243,8 @@ __global__ void __launch_bounds__(NT_TC, 1) cell_fwd_tc_kernel(const CellParams 
       __syncwarp();
       if (lane == 0) mbar_arrive(bar + F_D2_EMPTY + sl);
       // -- outputs
-      const bool live = cell < ncell;
-      const size_t gi = (size_t)t * P.N + n0 + cell;
-      float m = 0.f, r = 0.f;
+      const float m = m8 ? 1.f : 0.f;
       if (live) {
-        m = P.mask[gi] ? 1.f : 0.f;
-        r = P.R ? __ldg(P.R + gi) : 0.f;
         P.u[gi] = u;
         if (MOM) {
           const size_t plane = (size_t)P.T * P.N;

@@ -174,19 +174,36 @@ __global__ void __launch_bounds__(MT, 1) macro_bptt_kernel(const MacroParams P) 
     dh[i] = v;
   }
   __syncthreads();
+  // Pre-pass (all threads): everything of step t that does not depend on the carried (dh_rec, dc):
+  //   co[t][j] = { a_c, a_i, a_f, a_g, a_o, f }  with  dc += dh*a_c ; d{i,f,g} = dc*a_{i,f,g} ; do = dh*a_o
+  float* co = sv_s + (size_t)T * 6 * H;
+  for (int i = tid; i < T * H; i += MT) {
+    const int t = i / H, j = i % H;
+    const float* sv = sv_s + (size_t)t * 6 * H;
+    const float cc = sv[H + j], gi = sv[2 * H + j], gf = sv[3 * H + j], gg = sv[4 * H + j], go = sv[5 * H + j];
+    const float cprev = (t > 0) ? sv_s[(size_t)(t - 1) * 6 * H + H + j] : (P.c0 ? __ldg(P.c0 + j) : 0.f);
+    const float tc = tanh_fast(cc);
+    float* c6 = co + (size_t)i * 6;
+    c6[0] = go * (1.f - tc * tc);
+    c6[1] = gg * gi * (1.f - gi);
+    c6[2] = cprev * gf * (1.f - gf);
+    c6[3] = gi * (1.f - gg * gg);
+    c6[4] = tc * go * (1.f - go);
+    c6[5] = gf;
+  }
+  __syncthreads();
   if (warp != 0) return;
-  // lane j < H carries (dh_rec_j, dc_j); saved gates of step t-1 are fetched while step t computes
+  // lane j < H carries (dh_rec_j, dc_j)
   float whh_col[G4];           // Whh[r][lane] for every gate row r
 #pragma unroll
   for (int r = 0; r < G4; ++r) whh_col[r] = (lane < H) ? __ldg(P.Whh + r * H + lane) : 0.f;
   float dh_rec = 0.f, dc = 0.f;
   const int j = lane < H ? lane : 0;
-  struct Step { float cc, gi, gf, gg, go, cprev, dhe; };
+  struct Step { float a_c, a_i, a_f, a_g, a_o, gf, dhe; };
   auto fetch = [&](int t) {
     Step q;
-    const float* sv = sv_s + (size_t)t * 6 * H;
-    q.cc = sv[H + j]; q.gi = sv[2 * H + j]; q.gf = sv[3 * H + j]; q.gg = sv[4 * H + j]; q.go = sv[5 * H + j];
-    q.cprev = (t > 0) ? sv_s[(size_t)(t - 1) * 6 * H + H + j] : (P.c0 ? __ldg(P.c0 + j) : 0.f);
+    const float* c6 = co + ((size_t)t * H + j) * 6;
+    q.a_c = c6[0]; q.a_i = c6[1]; q.a_f = c6[2]; q.a_g = c6[3]; q.a_o = c6[4]; q.gf = c6[5];
     q.dhe = dh[t * H + j];
     return q;
   };
@@ -194,12 +211,9 @@ __global__ void __launch_bounds__(MT, 1) macro_bptt_kernel(const MacroParams P) 
   for (int t = T - 1; t >= 0; --t) {
     const Step q = nxt;
     if (t > 0) nxt = fetch(t - 1);
-    const float tc = tanh_fast(q.cc);                        // off the dependency chain
-    const float a_o = tc * q.go * (1.f - q.go), a_c = q.go * (1.f - tc * tc);
-    const float a_i = q.gg * q.gi * (1.f - q.gi), a_f = q.cprev * q.gf * (1.f - q.gf), a_g = q.gi * (1.f - q.gg * q.gg);
     const float dht = q.dhe + dh_rec;
-    dc = fmaf(dht, a_c, dc);
-    const float di = dc * a_i, df = dc * a_f, dg = dc * a_g, d_o = dht * a_o;
+    dc = fmaf(dht, q.a_c, dc);
+    const float di = dc * q.a_i, df = dc * q.a_f, dg = dc * q.a_g, d_o = dht * q.a_o;
     if (lane < H) {
       float* dp = P.dpre + (size_t)t * G4;
       dp[lane] = di; dp[H + lane] = df; dp[2 * H + lane] = dg; dp[3 * H + lane] = d_o;
@@ -217,68 +231,108 @@ __global__ void __launch_bounds__(MT, 1) macro_bptt_kernel(const MacroParams P) 
   }
 }
 
-// Month-summed gradients: one thread per output element, a T-long dot product each.
-__global__ void __launch_bounds__(128) macro_wgrad_kernel(const MacroParams P) {
-  const int T = P.T, M = P.M, H = P.H, G4 = 4 * H;
-  const int n_sdf = P.have_sdf ? (G4 * M + G4 * H + G4 + D1 * H + D1) : 0;
-  const int n_mom = P.have_mom ? (KM * M + KM) : 0;
-  int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n_sdf + n_mom) return;
-  float v = 0.f;
-  if (i < n_sdf) {
-    if (i < G4 * M) {                                  // dW_ih[r][m] = sum_t dpre[t][r] macro[t][m]
-      const int r = i / M, m = i % M;
-#pragma unroll 8
-      for (int t = 0; t < T; ++t) v = fmaf(__ldg(P.dpre + (size_t)t * G4 + r), __ldg(P.macro + (size_t)t * M + m), v);
-      P.gWih[i] = v;
-      return;
-    }
-    i -= G4 * M;
-    if (i < G4 * H) {                                  // dW_hh[r][k] = sum_t dpre[t][r] h_{t-1}[k]
-      const int r = i / H, k = i % H;
-      for (int t = 0; t < T; ++t) {
-        const float hp = (t > 0) ? __ldg(P.save + (size_t)(t - 1) * 6 * H + k) : (P.h0 ? __ldg(P.h0 + k) : 0.f);
-        v = fmaf(__ldg(P.dpre + (size_t)t * G4 + r), hp, v);
+// Month-summed gradients.  Blocks 0 .. ceil(M/32)-1: 32 macro columns each, the months split across the
+// 8 warps, coefficients (dpre | dc_t) staged in shared memory, fixed-order cross-warp reduction:
+//   dW_ih[r][m] = sum_t dpre[t][r] macro[t][m]        dWq[k][m] = sum_t dc_t[k] macro[t][m]
+// Last block: the small ones (dW_hh, db, dW1[:,F:], db1, dbq), one thread per output.
+// dynamic smem: coef[T][G4+8] | red[8][G4+8][32]
+__global__ void __launch_bounds__(256) macro_wgrad_kernel(const MacroParams P) {
+  extern __shared__ float sm[];
+  const int T = P.T, M = P.M, H = P.H, G4 = 4 * H, NR = G4 + KM;
+  float* coef = sm;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int nmb = (M + 31) / 32;
+  for (int i = tid; i < T * NR; i += 256) {
+    const int t = i / NR, r = i % NR;
+    coef[i] = (r < G4) ? (P.have_sdf ? P.dpre[(size_t)t * G4 + r] : 0.f)
+                       : (P.have_mom ? __ldg(P.dadc + (size_t)t * 72 + 64 + (r - G4)) : 0.f);
+  }
+  __syncthreads();
+  if ((int)blockIdx.x < nmb) {
+    float* red = coef + (size_t)T * NR;
+    const int m = blockIdx.x * 32 + lane;
+    float acc[4 * HMAX + KM];
+#pragma unroll
+    for (int r = 0; r < 4 * HMAX + KM; ++r) acc[r] = 0.f;
+    for (int t0 = warp; t0 < T; t0 += 32) {            // four months in flight per lane
+      float v[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int t = t0 + 8 * u;
+        v[u] = (t < T && m < M) ? __ldg(P.macro + (size_t)t * M + m) : 0.f;
       }
-      P.gWhh[i] = v;
-      return;
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int t = t0 + 8 * u;
+        if (t < T) {
+          const float* c = coef + (size_t)t * NR;
+#pragma unroll
+          for (int r = 0; r < 4 * HMAX + KM; ++r)
+            if (r < NR) acc[r] = fmaf(c[r], v[u], acc[r]);
+        }
+      }
     }
-    i -= G4 * H;
-    if (i < G4) {
-      for (int t = 0; t < T; ++t) v += __ldg(P.dpre + (size_t)t * G4 + i);
-      P.gbih[i] = v; P.gbhh[i] = v;
-      return;
+#pragma unroll
+    for (int r = 0; r < 4 * HMAX + KM; ++r)
+      if (r < NR) red[(warp * NR + r) * 32 + lane] = acc[r];
+    __syncthreads();
+    for (int i = tid; i < NR * 32; i += 256) {
+      const int r = i >> 5, l = i & 31, mm = blockIdx.x * 32 + l;
+      float v = 0.f;
+      for (int w = 0; w < 8; ++w) v += red[(w * NR + r) * 32 + l];
+      if (mm < M) {
+        if (r < G4) { if (P.have_sdf) P.gWih[(size_t)r * M + mm] = v; }
+        else if (P.have_mom) P.gWq[(size_t)(r - G4) * P.ldwq + mm] = v;
+      }
     }
-    i -= G4;
-    if (i < D1 * H) {                                  // dW1[:,F+k] = sum_t da_t[j] h_t[k]
-      const int j = i / H, k = i % H;
-      for (int t = 0; t < T; ++t)
-        v = fmaf(__ldg(P.dadc + (size_t)t * 72 + j), __ldg(P.save + (size_t)t * 6 * H + k), v);
-      P.gW1[(size_t)j * P.ldw1 + P.F + k] = v;
-      return;
-    }
-    i -= D1 * H;
-    for (int t = 0; t < T; ++t) v += __ldg(P.dadc + (size_t)t * 72 + i);
-    P.gb1[i] = v;
     return;
   }
-  i -= n_sdf;
-  if (i < KM * M) {                                    // dWq[k][m] = sum_t dc_t[k] macro[t][m]
-    const int k = i / M, m = i % M;
-#pragma unroll 8
-    for (int t = 0; t < T; ++t)
-      v = fmaf(__ldg(P.dadc + (size_t)t * 72 + 64 + k), __ldg(P.macro + (size_t)t * M + m), v);
-    P.gWq[(size_t)k * P.ldwq + m] = v;
-    return;
+  // ---- small outputs
+  const int n_sdf = P.have_sdf ? (G4 * H + G4 + D1 * H + D1) : 0;
+  const int n_mom = P.have_mom ? KM : 0;
+  for (int i = tid; i < n_sdf + n_mom; i += 256) {
+    float v = 0.f;
+    int o = i;
+    if (o < n_sdf) {
+      if (o < G4 * H) {                                // dW_hh[r][k] = sum_t dpre[t][r] h_{t-1}[k]
+        const int r = o / H, k = o % H;
+        for (int t = 0; t < T; ++t) {
+          const float hp = (t > 0) ? __ldg(P.save + (size_t)(t - 1) * 6 * H + k) : (P.h0 ? __ldg(P.h0 + k) : 0.f);
+          v = fmaf(coef[(size_t)t * NR + r], hp, v);
+        }
+        P.gWhh[o] = v;
+        continue;
+      }
+      o -= G4 * H;
+      if (o < G4) {
+        for (int t = 0; t < T; ++t) v += coef[(size_t)t * NR + o];
+        P.gbih[o] = v; P.gbhh[o] = v;
+        continue;
+      }
+      o -= G4;
+      if (o < D1 * H) {                                // dW1[:,F+k] = sum_t da_t[j] h_t[k]
+        const int j = o / H, k = o % H;
+#pragma unroll 4
+        for (int t = 0; t < T; ++t)
+          v = fmaf(__ldg(P.dadc + (size_t)t * 72 + j), __ldg(P.save + (size_t)t * 6 * H + k), v);
+        P.gW1[(size_t)j * P.ldw1 + P.F + k] = v;
+        continue;
+      }
+      o -= D1 * H;
+#pragma unroll 4
+      for (int t = 0; t < T; ++t) v += __ldg(P.dadc + (size_t)t * 72 + o);
+      P.gb1[o] = v;
+      continue;
+    }
+    o -= n_sdf;
+    for (int t = 0; t < T; ++t) v += coef[(size_t)t * NR + G4 + o];
+    P.gbq[o] = v;
   }
-  i -= KM * M;
-  for (int t = 0; t < T; ++t) v += __ldg(P.dadc + (size_t)t * 72 + 64 + i);
-  P.gbq[i] = v;
 }
 
 size_t macro_fwd_smem(int T, int M, int H) { return (size_t)T * 4 * H * 4 + 0 * (size_t)M; }
 size_t macro_proj_smem(int M, int H) { return ((size_t)4 * H * M + (size_t)KM * M) * 4; }
-size_t macro_bwd_smem(int T, int H) { return ((size_t)T * H + (size_t)T * 6 * H) * 4; }
+size_t macro_bwd_smem(int T, int H) { return ((size_t)T * H + (size_t)T * 12 * H) * 4; }
 
 template <int H>
 static cudaError_t launch_fwd_h(const MacroParams& P, size_t smem, cudaStream_t st) {
@@ -326,10 +380,11 @@ cudaError_t launch_macro_bwd(const MacroParams& P, cudaStream_t st) {
     cudaError_t e = launch_bptt(P, st);
     if (e != cudaSuccess) return e;
   }
-  const int G4 = 4 * P.H;
-  const int total = (P.have_sdf ? (G4 * P.M + G4 * P.H + G4 + D1 * P.H + D1) : 0) +
-                    (P.have_mom ? (KM * P.M + KM) : 0);
-  if (total > 0) macro_wgrad_kernel<<<(total + 127) / 128, 128, 0, st>>>(P);
+  const int NR = 4 * P.H + KM;
+  const size_t smem = ((size_t)P.T * NR + (size_t)8 * NR * 32) * 4;
+  cudaError_t e = cudaFuncSetAttribute(macro_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return e;
+  macro_wgrad_kernel<<<(P.M + 31) / 32 + 1, 256, smem, st>>>(P);
   return cudaGetLastError();
 }
 

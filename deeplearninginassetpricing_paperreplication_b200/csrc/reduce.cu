@@ -16,12 +16,15 @@ namespace dlap {
 // sharpe = mean(pr) / (std_unbiased(pr) + 1e-8)                   src/model.py:551
 // stage 1 (multi-CTA): one warp per month sums the per-tile partial slots in a fixed tree
 __global__ void __launch_bounds__(256) row_sum_kernel(const double* __restrict__ row_part, int T, int tpm,
-                                                      float* __restrict__ row_stats) {
+                                                      int tpm_tiles, int seg_chunk, float* __restrict__ row_stats) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int t = blockIdx.x * 8 + warp;
   if (t >= T) return;
+  const int stride = tpm;
+  if (seg_chunk > 0)           // tensor-core layout: only the (month, CTA) segments that exist were written
+    tpm = ((t + 1) * tpm_tiles - 1) / seg_chunk - (t * tpm_tiles) / seg_chunk + 1;
   double c = 0, su = 0, sur = 0, sr = 0;
-  const double4* p = reinterpret_cast<const double4*>(row_part) + (size_t)t * tpm;
+  const double4* p = reinterpret_cast<const double4*>(row_part) + (size_t)t * stride;
   for (int j = lane; j < tpm; j += 32) {
     const double4 v = p[j];
     c += v.x; su += v.y; sur += v.z; sr += v.w;
@@ -275,9 +278,10 @@ __global__ void __launch_bounds__(256) weights_kernel(
 }
 
 // ---- launchers ---------------------------------------------------------------------------------------
-cudaError_t launch_row_finish(const double* row_part, int T, int tpm, int weighted, const float* n_bar_in,
-                              float* row_stats, float* pr_out, float* scalars, cudaStream_t st) {
-  row_sum_kernel<<<(T + 7) / 8, 256, 0, st>>>(row_part, T, tpm, row_stats);
+cudaError_t launch_row_finish(const double* row_part, int T, int tpm, int tpm_tiles, int seg_chunk, int weighted,
+                              const float* n_bar_in, float* row_stats, float* pr_out, float* scalars,
+                              cudaStream_t st) {
+  row_sum_kernel<<<(T + 7) / 8, 256, 0, st>>>(row_part, T, tpm, tpm_tiles, seg_chunk, row_stats);
   row_finish_kernel<<<1, T < 1024 ? ((T + 31) / 32) * 32 : 1024, 0, st>>>(T, weighted, n_bar_in, row_stats, pr_out, scalars);
   return cudaGetLastError();
 }

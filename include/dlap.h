@@ -45,7 +45,8 @@ enum {
 enum {
   DLAP_PREC_FP32 = 0,     /* exact fp32 FFMA on CUDA cores */
   DLAP_PREC_BF16X3 = 1    /* tcgen05 BF16 MMAs on hi/lo-split operands, 3 products per fp32 product,
-                             fp32 accumulation in TMEM; needs F <= 46; row_part has 4 slots per tile */
+                             fp32 accumulation in TMEM; needs F <= 46; per-month partials are written
+                             per (month, CTA) segment instead of per tile */
 };
 
 typedef struct dlap_dims {
