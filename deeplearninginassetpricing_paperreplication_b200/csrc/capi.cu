@@ -94,7 +94,7 @@ int dlap_make_plan(const dlap_dims* dims, int device, dlap_plan* out) {
   const long long ntiles = (long long)T * p.tpm;
   p.grid_cell = (int)(ntiles < sms ? ntiles : sms);
   // reductions: aim for ~4 CTAs per SM
-  const int nb = (N + 255) / 256, want = 2 * sms;
+  const int nb = (N + 255) / 256, want = 4 * sms;
   int cs = (want + nb - 1) / nb; if (cs > T) cs = T; if (cs < 1) cs = 1;
   p.col_splits = cs;
   int rs = (want + T - 1) / T; if (rs > nb) rs = nb; if (rs < 1) rs = 1;

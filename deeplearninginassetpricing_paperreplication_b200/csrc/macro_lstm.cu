@@ -103,6 +103,7 @@ __global__ void __launch_bounds__(MT, 1) macro_fwd_kernel(const MacroParams P) {
   const int T = P.T;
   constexpr int G4 = 4 * H;
   float* xp = sm;
+  float* hs = xp + (size_t)T * G4;           // h_t of every month, for the a_t pass
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   for (int i = tid; i < T * G4; i += MT) xp[i] = P.xp[i];
   __syncthreads();
@@ -137,6 +138,7 @@ __global__ void __launch_bounds__(MT, 1) macro_fwd_kernel(const MacroParams P) {
       h = go * tanh_fast(c);
       if (lane < H) {
         float* sv = P.save + (size_t)t * 6 * H;
+        hs[t * H + lane] = h;
         sv[lane] = h; sv[H + lane] = c;
         sv[2 * H + lane] = gi; sv[3 * H + lane] = gf; sv[4 * H + lane] = gg; sv[5 * H + lane] = go;
       }
@@ -145,13 +147,19 @@ __global__ void __launch_bounds__(MT, 1) macro_fwd_kernel(const MacroParams P) {
   }
   __syncthreads();
 
-  // phase 3: a_t = W1[:,F:F+H].h_t + b1
-  for (int i = tid; i < T * D1; i += MT) {
-    const int t = i / D1, j = i % D1;
-    float v = __ldg(P.b1 + j);
-    const float* hrow = P.save + (size_t)t * 6 * H;
-    for (int k = 0; k < H; ++k) v = fmaf(__ldg(P.W1 + (size_t)j * P.ldw1 + P.F + k), hrow[k], v);
-    P.a_t[i] = v;
+  // phase 3: a_t = W1[:,F:F+H].h_t + b1 ; thread = (unit j, month slice), weights in registers
+  {
+    const int j = tid % D1;
+    float w[H];
+#pragma unroll
+    for (int k = 0; k < H; ++k) w[k] = __ldg(P.W1 + (size_t)j * P.ldw1 + P.F + k);
+    const float b = __ldg(P.b1 + j);
+    for (int t = tid / D1; t < T; t += MT / D1) {
+      float v = b;
+#pragma unroll
+      for (int k = 0; k < H; ++k) v = fmaf(w[k], hs[t * H + k], v);
+      P.a_t[(size_t)t * D1 + j] = v;
+    }
   }
 }
 
@@ -165,13 +173,21 @@ __global__ void __launch_bounds__(MT, 1) macro_bptt_kernel(const MacroParams P) 
   float* sv_s = dh + (size_t)T * H;          // saved h,c,i,f,g,o of every month, [T][6H]
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   for (int i = tid; i < T * 6 * H; i += MT) sv_s[i] = P.save[i];
-  // dh_t = W1[:,F:]^T . da_t
+  // dh_t = W1[:,F:]^T . da_t   (W1m staged in smem behind the coefficient table)
+  float* w1m = sv_s + (size_t)T * 12 * H;
+  for (int i = tid; i < D1 * H; i += MT) w1m[i] = __ldg(P.W1 + (size_t)(i / H) * P.ldw1 + P.F + (i % H));
+  __syncthreads();
   for (int i = tid; i < T * H; i += MT) {
     const int t = i / H, k = i % H;
-    float v = 0.f;
-    for (int j = 0; j < D1; ++j)
-      v = fmaf(__ldg(P.W1 + (size_t)j * P.ldw1 + P.F + k), __ldg(P.dadc + (size_t)t * 72 + j), v);
-    dh[i] = v;
+    const float4* da4 = reinterpret_cast<const float4*>(P.dadc + (size_t)t * 72);
+    float v0 = 0.f, v1 = 0.f;
+#pragma unroll 4
+    for (int j4 = 0; j4 < D1 / 4; ++j4) {
+      const float4 d = __ldg(da4 + j4);
+      v0 = fmaf(w1m[(4 * j4) * H + k], d.x, v0);     v1 = fmaf(w1m[(4 * j4 + 1) * H + k], d.y, v1);
+      v0 = fmaf(w1m[(4 * j4 + 2) * H + k], d.z, v0); v1 = fmaf(w1m[(4 * j4 + 3) * H + k], d.w, v1);
+    }
+    dh[i] = v0 + v1;
   }
   __syncthreads();
   // Pre-pass (all threads): everything of step t that does not depend on the carried (dh_rec, dc):
@@ -287,52 +303,67 @@ __global__ void __launch_bounds__(256) macro_wgrad_kernel(const MacroParams P) {
     }
     return;
   }
-  // ---- small outputs
-  const int n_sdf = P.have_sdf ? (G4 * H + G4 + D1 * H + D1) : 0;
-  const int n_mom = P.have_mom ? KM : 0;
-  for (int i = tid; i < n_sdf + n_mom; i += 256) {
-    float v = 0.f;
-    int o = i;
-    if (o < n_sdf) {
-      if (o < G4 * H) {                                // dW_hh[r][k] = sum_t dpre[t][r] h_{t-1}[k]
-        const int r = o / H, k = o % H;
-        for (int t = 0; t < T; ++t) {
-          const float hp = (t > 0) ? __ldg(P.save + (size_t)(t - 1) * 6 * H + k) : (P.h0 ? __ldg(P.h0 + k) : 0.f);
-          v = fmaf(coef[(size_t)t * NR + r], hp, v);
-        }
-        P.gWhh[o] = v;
-        continue;
+  // ---- small outputs: one warp per output row, lanes stride over the months, fixed-tree warp sum
+  if (P.have_sdf) {
+    for (int j = warp; j < D1; j += 8) {               // dW1[j][F+k] = sum_t da_t[j] h_t[k] ; db1[j] = sum_t da_t[j]
+      float a[HMAX], b = 0.f;
+#pragma unroll
+      for (int k = 0; k < HMAX; ++k) a[k] = 0.f;
+      for (int t = lane; t < T; t += 32) {
+        const float d = __ldg(P.dadc + (size_t)t * 72 + j);
+        b += d;
+#pragma unroll
+        for (int k = 0; k < HMAX; ++k)
+          if (k < H) a[k] = fmaf(d, __ldg(P.save + (size_t)t * 6 * H + k), a[k]);
       }
-      o -= G4 * H;
-      if (o < G4) {
-        for (int t = 0; t < T; ++t) v += coef[(size_t)t * NR + o];
-        P.gbih[o] = v; P.gbhh[o] = v;
-        continue;
+      b = warp_sum(b);
+#pragma unroll
+      for (int k = 0; k < HMAX; ++k) a[k] = warp_sum(a[k]);
+      if (lane == 0) {
+        P.gb1[j] = b;
+#pragma unroll
+        for (int k = 0; k < HMAX; ++k)
+          if (k < H) P.gW1[(size_t)j * P.ldw1 + P.F + k] = a[k];
       }
-      o -= G4;
-      if (o < D1 * H) {                                // dW1[:,F+k] = sum_t da_t[j] h_t[k]
-        const int j = o / H, k = o % H;
-#pragma unroll 4
-        for (int t = 0; t < T; ++t)
-          v = fmaf(__ldg(P.dadc + (size_t)t * 72 + j), __ldg(P.save + (size_t)t * 6 * H + k), v);
-        P.gW1[(size_t)j * P.ldw1 + P.F + k] = v;
-        continue;
-      }
-      o -= D1 * H;
-#pragma unroll 4
-      for (int t = 0; t < T; ++t) v += __ldg(P.dadc + (size_t)t * 72 + o);
-      P.gb1[o] = v;
-      continue;
     }
-    o -= n_sdf;
-    for (int t = 0; t < T; ++t) v += coef[(size_t)t * NR + G4 + o];
-    P.gbq[o] = v;
+    for (int r = warp; r < G4; r += 8) {               // dW_hh[r][k] = sum_t dpre[t][r] h_{t-1}[k] ; db[r]
+      float a[HMAX], b = 0.f;
+#pragma unroll
+      for (int k = 0; k < HMAX; ++k) a[k] = 0.f;
+      for (int t = lane; t < T; t += 32) {
+        const float d = coef[(size_t)t * NR + r];
+        b += d;
+#pragma unroll
+        for (int k = 0; k < HMAX; ++k)
+          if (k < H) {
+            const float hp = (t > 0) ? __ldg(P.save + (size_t)(t - 1) * 6 * H + k) : (P.h0 ? __ldg(P.h0 + k) : 0.f);
+            a[k] = fmaf(d, hp, a[k]);
+          }
+      }
+      b = warp_sum(b);
+#pragma unroll
+      for (int k = 0; k < HMAX; ++k) a[k] = warp_sum(a[k]);
+      if (lane == 0) {
+        P.gbih[r] = b; P.gbhh[r] = b;
+#pragma unroll
+        for (int k = 0; k < HMAX; ++k)
+          if (k < H) P.gWhh[r * H + k] = a[k];
+      }
+    }
+  }
+  if (P.have_mom) {
+    for (int q = warp; q < KM; q += 8) {               // dbq[q] = sum_t dc_t[q]
+      float b = 0.f;
+      for (int t = lane; t < T; t += 32) b += coef[(size_t)t * NR + G4 + q];
+      b = warp_sum(b);
+      if (lane == 0) P.gbq[q] = b;
+    }
   }
 }
 
-size_t macro_fwd_smem(int T, int M, int H) { return (size_t)T * 4 * H * 4 + 0 * (size_t)M; }
+size_t macro_fwd_smem(int T, int M, int H) { return (size_t)T * 5 * H * 4 + 0 * (size_t)M; }
 size_t macro_proj_smem(int M, int H) { return ((size_t)4 * H * M + (size_t)KM * M) * 4; }
-size_t macro_bwd_smem(int T, int H) { return ((size_t)T * H + (size_t)T * 12 * H) * 4; }
+size_t macro_bwd_smem(int T, int H) { return ((size_t)T * H + (size_t)T * 12 * H + (size_t)D1 * H) * 4; }
 
 template <int H>
 static cudaError_t launch_fwd_h(const MacroParams& P, size_t smem, cudaStream_t st) {
