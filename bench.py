@@ -61,7 +61,7 @@ class ClockSampler(threading.Thread):
                     self.rows.append([c.strip() for c in out.split(",")])
             except Exception:
                 pass
-            self._halt.wait(0.1)
+            self._halt.wait(0.02)
 
     def stop(self):
         self._halt.set()
@@ -152,10 +152,7 @@ def run_ours(args, rank, world):
     host = [t.pin_memory() for t in (macro_all, x, R, mask)]
     d_macro, d_x, d_R, d_mask = [t.to(dev) for t in host]
     if world > 1:
-        n_t = d_mask.sum(dim=1).clamp(min=1).float().sum().reshape(1)
-        dist.all_reduce(n_t)
-        model.month_shard = Fn.MonthShard(group=dist.group.WORLD, t0=rank * T, t1=(rank + 1) * T,
-                                          T_total=T_total, n_bar=(n_t / T_total).contiguous())
+        model.month_shard = Fn.make_month_shard(d_mask, rank * T, T_total, dist.group.WORLD)
 
     def step(inputs):
         model.zero_grad(set_to_none=True)
@@ -218,7 +215,8 @@ def run_ours(args, rank, world):
         "metric": "stock-months/sec per fwd+bwd GAN step", "value": value, "unit": "stock-months/s",
         "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "f32" if args.precision == "fp32" else args.precision, "data": "synthetic",
+        "dtype": "f32" if args.precision == "fp32" else "bf16x3 (fp32 split in hi+lo bf16, 3 MMAs per product, f32 accumulate)",
+        "data": "synthetic",
         "config": {"workload": f"paper-shape panel T={T} N={N} F={F_CHARS} M={M_MACRO} per GPU "
                                f"(BASELINE.json configs[1]); phase 'conditional' fwd+bwd, dropout 0, "
                                f"hidden [64,64], rnn [4], 8 moments; months sharded across {world} GPU(s)",
@@ -228,14 +226,31 @@ def run_ours(args, rank, world):
         "e2e": {"value": e2e, "unit": "stock-months/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
                 "ms_per_step": ms2 / k2},
         "gpu_launches": launches,
-        "roofline": {"bound": "hbm", "kernel": "cell_bwd (recomputing per-cell backward)",
+        "roofline": {"bound": "hbm", "kernel": "cell_bwd (recomputing per-cell backward, %s)" % args.precision,
                      "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "peak_kind": peak_kind, "kernel_ms": k_ms, "kernel_share_of_step": k_ms * args.steps / ms,
                      "traffic": ncu_traffic(),
                      "step_frac": value * ALGO_BYTES_STEP / 1e9 / peak,
+                     "tensor_tflops": 3 * 36.9e3 * T * N / (k_ms * 1e-3) / 1e12 if args.precision != "fp32" else None,
                      "note": "algorithmic bytes = 189 B per stock-month per launch (x, R, mask read once); "
-                             "step_frac = whole step at 378 B per stock-month"},
+                             "step_frac = whole step at 378 B per stock-month; the kernel is bound by tensor-core "
+                             "MMA issue + CUDA-core epilogue (138 FLOP/B), not by HBM; tensor_tflops = issued bf16 "
+                             "MMA work (3 x 36.9 kFLOP per stock-month)"},
     }
+    if args.precision != "fp32" and world == 1:       # the exact-fp32 CUDA-core path, for reference
+        m32 = AssetPricingGAN({"macro_feature_dim": M_MACRO, "individual_feature_dim": F_CHARS,
+                               "dropout": 0.0, "b200_precision": "fp32"}).to(dev)
+        m32.load_state_dict(model.state_dict())
+
+        def step32():
+            m32.zero_grad(set_to_none=True)
+            m32(*resident, phase="conditional")["loss"].backward()
+
+        for _ in range(3):
+            step32()
+        k3 = max(3, min(args.steps, 10))
+        ms3 = timed(step32, k3)
+        line["fp32_path"] = {"value": T * N * k3 / (ms3 * 1e-3), "unit": "stock-months/s", "ms_per_step": ms3 / k3}
     if not args.no_cpu:
         r = cpu_step_rate()
         line["cpu_baseline"] = {"value": r["rate_mean"], "unit": "stock-months/s", "cores": r["cores"],
@@ -246,10 +261,12 @@ def run_ours(args, rank, world):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=100)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--precision", default="fp32")
+    ap.add_argument("--precision", default="bf16x3", choices=["bf16x3", "fp32"],
+                    help="arithmetic of the per-cell contractions: bf16x3 = tcgen05 BF16 MMAs on hi/lo-split "
+                         "fp32 operands (3 products per fp32 product, fp32 accumulate); fp32 = CUDA-core FFMA")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", 0))

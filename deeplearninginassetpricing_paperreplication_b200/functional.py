@@ -136,6 +136,18 @@ class MonthShard:
     n_bar: torch.Tensor             # [1] float32, global mean of clamp(N_t, 1)
 
 
+def make_month_shard(mask_local: torch.Tensor, t0: int, T_total: int, group=None) -> MonthShard:
+    """MonthShard for this rank's slab `mask_local` = months [t0, t0 + T_local) of a T_total-month panel.
+    The only mask-derived global quantity the row stage needs is N_bar = mean_t clamp(N_t, 1)
+    (src/model.py:359-360); it is all-reduced here, once per panel, not per step."""
+    import torch.distributed as dist
+    n_t = mask_local.sum(dim=1).clamp(min=1).to(torch.float32).sum().reshape(1)
+    dist.all_reduce(n_t, group=group)
+    n_bar = (n_t / float(T_total)).to(torch.float32).contiguous()
+    return MonthShard(group=group, t0=int(t0), t1=int(t0) + int(mask_local.shape[0]), T_total=int(T_total),
+                      n_bar=n_bar)
+
+
 def check_panel(macro, x, R, mask) -> None:
     """The reference needs contiguous inputs too (x.view at src/model.py:143,261); beyond that
     the kernels need fp32 CUDA tensors.  No silent conversion, no CPU fallback."""

@@ -1,0 +1,95 @@
+"""Month-sharded step on the GPU: two processes share cuda:0 (gloo carries the all-reduces, so one GPU
+is enough) and must reproduce the single-process losses, weights and gradients."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+pytestmark = pytest.mark.gpu
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _panel(T, N, M):
+    g = torch.Generator().manual_seed(21)
+    mask = torch.rand(T, N, generator=g) < 0.4
+    x = torch.randn(T, N, 46, generator=g).clamp_(-2, 2) * mask[:, :, None]
+    R = 0.1 * torch.randn(T, N, generator=g) * mask
+    macro = torch.randn(T, M, generator=g)
+    return macro, x, R, mask
+
+
+def _worker(rank, world, port, precision, out_q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from deeplearninginassetpricing_paperreplication_b200 import AssetPricingGAN
+        from deeplearninginassetpricing_paperreplication_b200 import functional as Fn
+        dev = torch.device("cuda:0")
+        T, N, M = 22, 700, 8
+        macro, x, R, mask = _panel(T, N, M)
+        t0, t1 = (0, 9) if rank == 0 else (9, T)          # uneven slabs on purpose
+        torch.manual_seed(4)
+        model = AssetPricingGAN({"macro_feature_dim": M, "individual_feature_dim": 46, "dropout": 0.0,
+                                 "b200_precision": precision}).to(dev)
+        model.month_shard = Fn.make_month_shard(mask[t0:t1].to(dev), t0, T, None)
+        out = model(macro.to(dev), x[t0:t1].contiguous().to(dev), R[t0:t1].contiguous().to(dev),
+                    mask[t0:t1].contiguous().to(dev), phase="conditional")
+        out["loss"].backward()
+        torch.cuda.synchronize()
+        res = {"loss": float(out["loss"]), "loss_u": float(out["loss_unconditional"]), "sharpe": float(out["sharpe"]),
+               "pr": out["portfolio_returns"].cpu().numpy(), "w": out["weights"].cpu().numpy(),
+               "grads": {k: p.grad.cpu().numpy() for k, p in model.named_parameters()}}
+        out_q.put((rank, res))
+    except Exception as exc:  # pragma: no cover
+        import traceback
+        out_q.put((rank, "ERR " + traceback.format_exc()))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("precision", ["fp32", "bf16x3"])
+def test_two_month_shards_match_single_process(precision):
+    from deeplearninginassetpricing_paperreplication_b200 import AssetPricingGAN
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, precision, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = dict(q.get(timeout=240) for _ in procs)
+    for p in procs:
+        p.join(timeout=60)
+    assert all(not isinstance(v, str) for v in res.values()), res
+    dev = torch.device("cuda:0")
+    T, N, M = 22, 700, 8
+    macro, x, R, mask = _panel(T, N, M)
+    torch.manual_seed(4)
+    model = AssetPricingGAN({"macro_feature_dim": M, "individual_feature_dim": 46, "dropout": 0.0,
+                             "b200_precision": precision}).to(dev)
+    ref = model(macro.to(dev), x.to(dev), R.to(dev), mask.to(dev), phase="conditional")
+    ref["loss"].backward()
+    for r in (0, 1):
+        assert abs(res[r]["loss"] - float(ref["loss"])) <= 1e-5 * abs(float(ref["loss"]))
+        assert abs(res[r]["loss_u"] - float(ref["loss_unconditional"])) <= 1e-5 * abs(float(ref["loss_unconditional"]))
+        assert np.allclose(res[r]["pr"], ref["portfolio_returns"].detach().cpu().numpy(), rtol=1e-4, atol=1e-7)
+        assert abs(res[r]["sharpe"] - float(ref["sharpe"])) <= 1e-4 * abs(float(ref["sharpe"])) + 1e-6
+    w = np.concatenate([res[0]["w"], res[1]["w"]], axis=0)
+    wref = ref["weights"].detach().cpu().numpy()
+    assert np.abs(w - wref).max() <= 1e-4 * np.abs(wref).max()
+    tol = 2e-4 if precision == "fp32" else 2e-2
+    for k, p in model.named_parameters():
+        if k == "sdf_net.output_proj.bias":
+            continue
+        gr = p.grad.cpu().numpy()
+        for r in (0, 1):                      # every rank ends with the full gradient
+            err = np.abs(res[r]["grads"][k] - gr).max() / max(np.abs(gr).max(), 1e-30)
+            assert err < tol, (k, r, err)
