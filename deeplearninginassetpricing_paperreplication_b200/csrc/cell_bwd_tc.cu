@@ -4,10 +4,9 @@
 // Per tile of 128 stock-months, on split bf16 operands (3 MMAs per fp32 product):
 //   L1    D_A[128,80] = X.[W1x;Wqx]^T (+ a_t|c_t through the ones column)      -> E1: h1, relu mask, dpre
 //   L2    D_B[128,64] = H1.W2^T                                                -> E2: dz2, dW3, db2
-//   MQ    D_Q[64,8]  += X^T.DPRE        (moment-net weight gradient, accumulated over the CTA's tiles)
 //   WG2   D_W2[64,64] += DZ2^T.H1       (dW2)
 //   DG    D_C[128,64] = DZ2.W2                                                 -> E3: dz1, da_t
-//   WG1   D_W1[64,48] += DZ1^T.X        (dW1x)
+//   WG1   D_W1[64,72] += X^T.[DZ1|DPRE]  (dW1x^T and dWq^T in one MMA: dz1 and dpre are adjacent images)
 // All activation tiles live in shared memory as [group of 8 units][cell][8] bf16 images, so the same
 // bytes serve as K-major operand (forward / dgrad) and MN-major operand (weight gradients).
 //
@@ -39,25 +38,27 @@ struct SmemB {
   __device__ uint8_t* w1l(int sl) const { return w1h(sl) + W1_IMG; }
   __device__ uint8_t* w2h() const { return base + STAGE_BYTES + 4 * X_IMG + 4 * W1_IMG; }
   __device__ uint8_t* w2l() const { return w2h() + W2_IMG; }
-  __device__ uint8_t* hh(int sl) const { return w2l() + W2_IMG + sl * 2 * H_IMG; }
-  __device__ uint8_t* hl(int sl) const { return hh(sl) + H_IMG; }
-  __device__ uint8_t* dzh() const { return w2l() + W2_IMG + 4 * H_IMG; }
+  // per slot: [H hi (8 groups) | DPRE hi (1 group) | H lo | DPRE lo]: dz1 (written over h1) and dpre are
+  // adjacent, so one MN-major B operand of 9 groups (N = 72) feeds dW1x and dWq in the same MMA
+  __device__ uint8_t* hh(int sl) const { return w2l() + W2_IMG + sl * 2 * (H_IMG + DPS_IMG); }
+  __device__ uint8_t* dph(int sl) const { return hh(sl) + H_IMG; }
+  __device__ uint8_t* hl(int sl) const { return dph(sl) + DPS_IMG; }
+  __device__ uint8_t* dpl(int sl) const { return hl(sl) + H_IMG; }
+  __device__ uint8_t* dzh() const { return w2l() + W2_IMG + 4 * (H_IMG + DPS_IMG); }
   __device__ uint8_t* dzl() const { return dzh() + H_IMG; }
-  __device__ uint8_t* dph() const { return dzl() + H_IMG; }
-  __device__ uint8_t* dpl() const { return dph() + DPS_IMG; }
-  __device__ float* b2s() const { return reinterpret_cast<float*>(dpl() + DPS_IMG); }
+  __device__ float* b2s() const { return reinterpret_cast<float*>(dzl() + H_IMG); }
   __device__ float* w3s() const { return b2s() + 64; }
   __device__ float* red() const { return w3s() + 64; }                       // [16 warps][16][2] + [4][8]
   __device__ uint64_t* bars() const { return reinterpret_cast<uint64_t*>(red() + NEPI * 32 + 32); }
   __device__ uint32_t* tmem_slot() const { return reinterpret_cast<uint32_t*>(bars() + 24); }
 };
-constexpr size_t SMEM_B_BYTES = (size_t)STAGE_BYTES + 4 * X_IMG + 4 * W1_IMG + 2 * W2_IMG + 6 * H_IMG + 2 * DPS_IMG +
+constexpr size_t SMEM_B_BYTES = (size_t)STAGE_BYTES + 4 * X_IMG + 4 * W1_IMG + 2 * W2_IMG + 6 * H_IMG + 4 * DPS_IMG +
                                 128 * 4 + (NEPI * 32 + 32) * 4 + 24 * 8 + 16 + 128;
 
 enum { B_STAGE_FULL = 0, B_STAGE_EMPTY = 1, B_XOP_FULL = 2, B_XOP_EMPTY = 4, B_D1_FULL = 6, B_H1_FULL = 8,
        B_W1_DONE = 10, B_D2_FULL = 12, B_DZ2_FULL = 13, B_D3_FULL = 14, B_DZ1_FULL = 15, B_ALL_DONE = 16 };
 
-constexpr uint32_t C_A0 = 0, C_A1 = 96, C_B = 192, C_C = 256, C_W2 = 320, C_W1 = 384, C_Q = 448, TMEM_COLS = 512;
+constexpr uint32_t C_A0 = 0, C_A1 = 96, C_B = 192, C_C = 256, C_W2 = 320, C_W1 = 384, TMEM_COLS = 512;   // C_W1: 72 cols
 
 // Sum over the 32 lanes of 16 per-lane values: every lane L returns sum_lanes v[L & 15].
 __device__ __forceinline__ float lane_transpose_sum16(float (&v)[16], int lane) {
@@ -92,7 +93,11 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
   // ---- one-time set-up ----
   for (int sl = 0; sl < 2; ++sl) fill_w1_images(P, s.w1h(sl), s.w1l(sl), tid, NT_B);
   fill_w2_images(P, s.w2h(), s.w2l(), tid, NT_B);
-  for (int i = tid; i < 2 * (int)DPS_IMG / 4; i += NT_B) reinterpret_cast<uint32_t*>(s.dph())[i] = 0u;
+  for (int sl = 0; sl < 2; ++sl)
+    for (int i = tid; i < (int)DPS_IMG / 4; i += NT_B) {
+      reinterpret_cast<uint32_t*>(s.dph(sl))[i] = 0u;
+      reinterpret_cast<uint32_t*>(s.dpl(sl))[i] = 0u;
+    }
   if (tid < 64) { s.b2s()[tid] = __ldg(P.b2 + tid); s.w3s()[tid] = __ldg(P.W3 + tid); }
   if (tid == 0) {
     mbar_init(bar + B_STAGE_FULL, 1);  mbar_init(bar + B_STAGE_EMPTY, 2);
@@ -136,14 +141,13 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
     // ===== MMA issuer (all lanes wait, lane 0 issues) =====
     const uint32_t id_l1 = tc::idesc_bf16(128, N1, 0, 0), id_l2 = tc::idesc_bf16(128, 64, 0, 0);
     const uint32_t id_dg = tc::idesc_bf16(128, 64, 0, 1);                 // A K-major, B = W2 MN-major
-    const uint32_t id_w2 = tc::idesc_bf16(64, 64, 1, 1), id_w1 = tc::idesc_bf16(64, 48, 1, 1);
-    const uint32_t id_q = tc::idesc_bf16(64, 8, 1, 1);
+    const uint32_t id_w2 = tc::idesc_bf16(64, 64, 1, 1);
+    const uint32_t id_w1q = tc::idesc_bf16(64, 72, 1, 1);                 // A = X (chars), B = [dz1 | dpre]
     const uint32_t KM_A = TILE * 16;                                      // K-major activation: LBO
     const uint64_t dzh_k = tc::smem_desc(smem_u32(s.dzh()), KM_A, 128), dzl_k = tc::smem_desc(smem_u32(s.dzl()), KM_A, 128);
     const uint64_t dzh_m = tc::smem_desc(smem_u32(s.dzh()), 128, KM_A), dzl_m = tc::smem_desc(smem_u32(s.dzl()), 128, KM_A);
     const uint64_t w2h_k = tc::smem_desc(smem_u32(s.w2h()), 64 * 16, 128), w2l_k = tc::smem_desc(smem_u32(s.w2l()), 64 * 16, 128);
     const uint64_t w2h_m = tc::smem_desc(smem_u32(s.w2h()), 128, 64 * 16), w2l_m = tc::smem_desc(smem_u32(s.w2l()), 128, 64 * 16);
-    const uint64_t dph_m = tc::smem_desc(smem_u32(s.dph()), 128, KM_A), dpl_m = tc::smem_desc(smem_u32(s.dpl()), 128, KM_A);
 
     auto issue_l1 = [&](int i) {
       const int sl = i & 1, use = i >> 1;
@@ -175,12 +179,13 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
                   tc::desc_advance(w2h_k, ks * 2 * 64 * 16), tc::desc_advance(w2l_k, ks * 2 * 64 * 16), id_l2, ks == 0);
           tc::umma_commit(bar + B_D2_FULL);
         }
-        if (MOM) {
+        if (MOM && !SDF) {   // moment-only step: nothing else will read X(i); dWq^T = X^T.[.. | dpre] right away
           const uint64_t xh_m = tc::smem_desc(smem_u32(s.xh(sl)), 128, KM_A), xl_m = tc::smem_desc(smem_u32(s.xl(sl)), 128, KM_A);
+          const uint64_t bh_m = tc::smem_desc(smem_u32(s.hh(sl)), 128, KM_A), bl_m = tc::smem_desc(smem_u32(s.hl(sl)), 128, KM_A);
 #pragma unroll
           for (int ks = 0; ks < TILE / 16; ++ks)
-            umma3(tbase + C_Q, tc::desc_advance(xh_m, ks * 256), tc::desc_advance(xl_m, ks * 256),
-                  tc::desc_advance(dph_m, ks * 256), tc::desc_advance(dpl_m, ks * 256), id_q, i == 0 && ks == 0);
+            umma3(tbase + C_W1, tc::desc_advance(xh_m, ks * 256), tc::desc_advance(xl_m, ks * 256),
+                  tc::desc_advance(bh_m, ks * 256), tc::desc_advance(bl_m, ks * 256), id_w1q, i == 0 && ks == 0);
         }
       }
       __syncwarp();
@@ -212,14 +217,14 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
       }
       if (i + 1 < my_tiles) issue_l2(i + 1);            // runs under E3(i)
       if (SDF) {
-        // -- after E3(i): dW1x; dz1 sits in the H buffer of this tile
+        // -- after E3(i): [dW1x | dWq]^T = X^T . [dz1 | dpre]; dz1 sits in the H buffer of this tile, dpre next to it
         mbar_wait(bar + B_DZ1_FULL, par);
         tc::fence_after_sync();
         if (tc::elect_one()) {
 #pragma unroll
           for (int ks = 0; ks < TILE / 16; ++ks)
-            umma3(tbase + C_W1, tc::desc_advance(hh_m, ks * 256), tc::desc_advance(hl_m, ks * 256),
-                  tc::desc_advance(xh_m, ks * 256), tc::desc_advance(xl_m, ks * 256), id_w1, first && ks == 0);
+            umma3(tbase + C_W1, tc::desc_advance(xh_m, ks * 256), tc::desc_advance(xl_m, ks * 256),
+                  tc::desc_advance(hh_m, ks * 256), tc::desc_advance(hl_m, ks * 256), id_w1q, first && ks == 0);
         }
         __syncwarp();
       }
@@ -292,7 +297,8 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
 
     // per-cell inputs of the next E1 tile are fetched one phase early (HBM latency off the critical path);
     // the per-month scalars (dP_t, Rbar_t, S_t) are recomputed only when the month changes
-    float pf_m = 0.f, pf_r = 0.f, pf_g[8];
+    unsigned char pf_m8 = 0;
+    float pf_r = 0.f, pf_g[8];
 #pragma unroll
     for (int k = 0; k < 8; ++k) pf_g[k] = 0.f;
     int ms_month = -1;
@@ -302,8 +308,8 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
       const int t = tile / P.tpm, n0 = (tile % P.tpm) * TILE;
       const bool live = cell < min(TILE, P.N - n0);
       const size_t gi = (size_t)t * P.N + n0 + cell;
-      pf_m = 0.f; pf_r = 0.f;
-      if (live) { pf_m = P.mask[gi] ? 1.f : 0.f; pf_r = __ldg(P.R + gi); }
+      pf_m8 = 0; pf_r = 0.f;
+      if (live) { pf_m8 = P.mask[gi]; pf_r = __ldg(P.R + gi); }      // consumed one phase later: no stall here
       if (mom_warp) {
 #pragma unroll
         for (int k = 0; k < 8; ++k) pf_g[k] = live ? __ldg(P.G + (size_t)k * P.N + n0 + cell) : 0.f;
@@ -324,6 +330,7 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
     auto do_e1 = [&](int i) {
       const int tile = tile_lo + i, sl = i & 1, use = i >> 1;
       const int t = tile / P.tpm;
+      const float pf_m = pf_m8 ? 1.f : 0.f;
       du_nxt = pf_m * ms_dP * (pf_r - ms_rbar);
       const float cq = pf_r * pf_m * ms_S;
       float gk[8];
@@ -362,8 +369,8 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
         }
         uint4 hi, lo;
         tc::split8(q, hi, lo);
-        *reinterpret_cast<uint4*>(s.dph() + cell * 16) = hi;
-        *reinterpret_cast<uint4*>(s.dpl() + cell * 16) = lo;
+        *reinterpret_cast<uint4*>(s.dph(sl) + cell * 16) = hi;
+        *reinterpret_cast<uint4*>(s.dpl(sl) + cell * 16) = lo;
         if (t == cur_month) {
 #pragma unroll
           for (int k = 0; k < 8; ++k) dc_cur[k] += q[k];
@@ -491,16 +498,13 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
       if (SDF) { tc::tmem_ld16(tbase + lane_base + C_W2 + U0, v); tc::tmem_wait_ld(); }
       if (lane < 16)
         for (int k = 0; k < 16; ++k) wp[wp_off_w2() + row * 64 + U0 + k] = (SDF && have) ? v[k] : 0.f;
-      if (hf < 3) {                                  // dW1x[j][f], f < 48: three column chunks
-        if (SDF) { tc::tmem_ld16(tbase + lane_base + C_W1 + U0, v); tc::tmem_wait_ld(); }
-        if (lane < 16)
-          for (int k = 0; k < 16; ++k) {
-            const int f = U0 + k;
-            if (f < Fr) wp[wp_off_w1() + row * Fr + f] = (SDF && have && f < P.F) ? v[k] : 0.f;
-          }
-      } else {                                       // dWq[k][f] = D_Q[f][k]
+      // [dW1x | dWq]^T: row = characteristic f (valid for f < F), columns 0..63 = hidden unit, 64..71 = moment
+      if (SDF) { tc::tmem_ld16(tbase + lane_base + C_W1 + U0, v); tc::tmem_wait_ld(); }
+      if (lane < 16 && row < Fr)
+        for (int k = 0; k < 16; ++k) wp[wp_off_w1() + (U0 + k) * Fr + row] = (SDF && have && row < P.F) ? v[k] : 0.f;
+      if (hf == 3) {
         float q[8];
-        if (MOM) { tc::tmem_ld8(tbase + lane_base + C_Q, q); tc::tmem_wait_ld(); }
+        if (MOM) { tc::tmem_ld8(tbase + lane_base + C_W1 + 64, q); tc::tmem_wait_ld(); }
         if (lane < 16 && row < Fr)
           for (int k = 0; k < 8; ++k) wp[wp_off_wq(Fr) + k * Fr + row] = (MOM && have && row < P.F) ? q[k] : 0.f;
       }
