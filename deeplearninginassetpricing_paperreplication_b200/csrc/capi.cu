@@ -169,7 +169,6 @@ int dlap_cell_fwd(const dlap_plan* plan, const float* x, const float* R, const u
   if (rc) return rc;
   if (precision == DLAP_PREC_BF16X3) {
     if (plan->dims.F > 46) return DLAP_E_SHAPE;      // the ones column lives at k = 46
-    if (P.drop_thr) return DLAP_E_PRECISION;         // dropout: fp32 kernels only
     CU(launch_cell_fwd_tc(P, plan->grid_cell, (cudaStream_t)stream));
     return DLAP_OK;
   }
@@ -251,7 +250,6 @@ int dlap_cell_bwd(const dlap_plan* plan, const float* x, const float* R, const u
   if (rc) return rc;
   if (precision == DLAP_PREC_BF16X3) {
     if (plan->dims.F > 46) return DLAP_E_SHAPE;
-    if (P.drop_thr) return DLAP_E_PRECISION;
     CU(launch_cell_bwd_tc(P, plan->grid_cell, want_sdf != 0, want_mom != 0, (cudaStream_t)stream));
     return DLAP_OK;
   }

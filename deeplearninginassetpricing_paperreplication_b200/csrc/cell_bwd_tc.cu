@@ -77,7 +77,7 @@ __device__ __forceinline__ float lane_transpose_sum16(float (&v)[16], int lane) 
 __device__ __forceinline__ void epi_barrier() { asm volatile("bar.sync 1, 512;" ::: "memory"); }
 }  // namespace
 
-template <bool SDF, bool MOM>
+template <bool SDF, bool MOM, bool DROP>
 __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P) {
   extern __shared__ __align__(128) uint8_t smem_raw[];
   SmemB s;
@@ -326,6 +326,11 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
       }
     };
 
+    auto cell_global = [&](int i) {
+      const int tile = tile_lo + i;
+      return (uint32_t)((size_t)(tile / P.tpm) * P.N + (size_t)(tile % P.tpm) * TILE + cell);
+    };
+    const float dscale = DROP ? P.drop_scale : 1.f;
     // E1 of local tile i: h1 -> H[sl] image, relu mask, this cell's du ; moment warps: dpre
     auto do_e1 = [&](int i) {
       const int tile = tile_lo + i, sl = i & 1, use = i >> 1;
@@ -346,10 +351,11 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
         tc::tmem_ld16(dA + U0, v);
         tc::tmem_wait_ld();
 #pragma unroll
-        for (int k = 0; k < 16; ++k) {
-          if (v[k] > 0.f) m1_nxt |= 1u << k;
-          v[k] = fmaxf(v[k], 0.f);
-        }
+        for (int k = 0; k < 16; ++k) v[k] = fmaxf(v[k], 0.f);
+        if (DROP) tc_dropout<16>(P, cell_global(i), 0, U0, v);        // the image holds h1 AFTER dropout
+#pragma unroll
+        for (int k = 0; k < 16; ++k)
+          if (v[k] > 0.f) m1_nxt |= 1u << k;                          // kept and z1 > 0
 #pragma unroll
         for (int g = 0; g < 2; ++g) {
           uint4 hi, lo;
@@ -435,14 +441,22 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
         const float4* w4 = reinterpret_cast<const float4*>(s.w3s() + U0);
 #pragma unroll
         for (int k4 = 0; k4 < 4; ++k4) {
-          const float4 bb = b4[k4], ww = w4[k4];
-          const float b_[4] = {bb.x, bb.y, bb.z, bb.w}, w_[4] = {ww.x, ww.y, ww.z, ww.w};
+          const float4 bb = b4[k4];
+          const float b_[4] = {bb.x, bb.y, bb.z, bb.w};
+#pragma unroll
+          for (int e = 0; e < 4; ++e) v[4 * k4 + e] = fmaxf(v[4 * k4 + e] + b_[e], 0.f);
+        }
+        if (DROP) tc_dropout<16>(P, cell_global(i), 1, U0, v);        // h2 after dropout: > 0 iff kept and z2 > 0
+#pragma unroll
+        for (int k4 = 0; k4 < 4; ++k4) {
+          const float4 ww = w4[k4];
+          const float w_[4] = {ww.x, ww.y, ww.z, ww.w};
 #pragma unroll
           for (int e = 0; e < 4; ++e) {
             const int k = 4 * k4 + e;
-            const float z = v[k] + b_[e];
-            w3acc[k] = fmaf(du_cur, fmaxf(z, 0.f), w3acc[k]);
-            v[k] = (z > 0.f) ? du_cur * w_[e] : 0.f;
+            const float h2 = v[k];
+            w3acc[k] = fmaf(du_cur, h2, w3acc[k]);
+            v[k] = (h2 > 0.f) ? du_cur * w_[e] * dscale : 0.f;
             b2acc[k] += v[k];
           }
         }
@@ -468,7 +482,7 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
         tc::tmem_wait_ld();
 #pragma unroll
         for (int k = 0; k < 16; ++k) {
-          v[k] = ((m1_cur >> k) & 1u) ? v[k] : 0.f;
+          v[k] = ((m1_cur >> k) & 1u) ? v[k] * dscale : 0.f;
           daacc[k] += v[k];
         }
 #pragma unroll
@@ -528,20 +542,22 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
   if (warp == 0) tc::tmem_dealloc(tbase, TMEM_COLS);
 }
 
-cudaError_t launch_cell_bwd_tc(const CellParams& P, int grid, bool sdf, bool mom, cudaStream_t st) {
-  cudaError_t e = cudaSuccess;
-#define DLAP_LAUNCH_TC(S, M)                                                                              \
-  {                                                                                                       \
-    e = cudaFuncSetAttribute(cell_bwd_tc_kernel<S, M>, cudaFuncAttributeMaxDynamicSharedMemorySize,       \
-                             (int)SMEM_B_BYTES);                                                          \
-    if (e != cudaSuccess) return e;                                                                       \
-    cell_bwd_tc_kernel<S, M><<<grid, NT_B, SMEM_B_BYTES, st>>>(P);                                        \
-  }
-  if (sdf && mom) DLAP_LAUNCH_TC(true, true)
-  else if (sdf) DLAP_LAUNCH_TC(true, false)
-  else DLAP_LAUNCH_TC(false, true)
-#undef DLAP_LAUNCH_TC
+template <bool SDF, bool MOM, bool DROP>
+static cudaError_t launch_bwd_tc_variant(const CellParams& P, int grid, cudaStream_t st) {
+  cudaError_t e = cudaFuncSetAttribute(cell_bwd_tc_kernel<SDF, MOM, DROP>,
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_B_BYTES);
+  if (e != cudaSuccess) return e;
+  cell_bwd_tc_kernel<SDF, MOM, DROP><<<grid, NT_B, SMEM_B_BYTES, st>>>(P);
   return cudaGetLastError();
+}
+
+cudaError_t launch_cell_bwd_tc(const CellParams& P, int grid, bool sdf, bool mom, cudaStream_t st) {
+  const bool drop = P.drop_thr != 0 && sdf;
+  if (sdf && mom) return drop ? launch_bwd_tc_variant<true, true, true>(P, grid, st)
+                              : launch_bwd_tc_variant<true, true, false>(P, grid, st);
+  if (sdf) return drop ? launch_bwd_tc_variant<true, false, true>(P, grid, st)
+                       : launch_bwd_tc_variant<true, false, false>(P, grid, st);
+  return launch_bwd_tc_variant<false, true, false>(P, grid, st);
 }
 
 }  // namespace dlap

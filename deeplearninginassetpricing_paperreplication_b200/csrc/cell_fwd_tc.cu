@@ -44,7 +44,7 @@ constexpr size_t SMEM_TC_BYTES = 2 * (size_t)STAGE_BYTES_F + 4 * X_IMG + 4 * W1_
 constexpr uint32_t COL_A0 = 0, COL_B0 = 96, COL_A1 = 160, COL_B1 = 256, TMEM_COLS = 512;
 }  // namespace
 
-template <bool MOM>
+template <bool MOM, bool DROP>
 __global__ void __launch_bounds__(NT_TC, 1) cell_fwd_tc_kernel(const CellParams P) {
   extern __shared__ __align__(128) uint8_t smem_raw[];
   SmemTc s;
@@ -198,6 +198,7 @@ __global__ void __launch_bounds__(NT_TC, 1) cell_fwd_tc_kernel(const CellParams 
         tc::tmem_ld32(dA + c * 32, v);
 #pragma unroll
         for (int k = 0; k < 32; ++k) v[k] = fmaxf(v[k], 0.f);
+        if (DROP) tc_dropout<32>(P, (uint32_t)gi, 0, c * 32, v);
 #pragma unroll
         for (int g = 0; g < 4; ++g) {
           uint4 hi, lo;
@@ -231,11 +232,16 @@ __global__ void __launch_bounds__(NT_TC, 1) cell_fwd_tc_kernel(const CellParams 
         const float4* w4 = reinterpret_cast<const float4*>(s.w3s() + c * 32);
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
-          const float4 bb = b4[k], ww = w4[k];
-          up[0] = fmaf(fmaxf(v[4 * k] + bb.x, 0.f), ww.x, up[0]);
-          up[1] = fmaf(fmaxf(v[4 * k + 1] + bb.y, 0.f), ww.y, up[1]);
-          up[2] = fmaf(fmaxf(v[4 * k + 2] + bb.z, 0.f), ww.z, up[2]);
-          up[3] = fmaf(fmaxf(v[4 * k + 3] + bb.w, 0.f), ww.w, up[3]);
+          const float4 bb = b4[k];
+          v[4 * k] = fmaxf(v[4 * k] + bb.x, 0.f);         v[4 * k + 1] = fmaxf(v[4 * k + 1] + bb.y, 0.f);
+          v[4 * k + 2] = fmaxf(v[4 * k + 2] + bb.z, 0.f); v[4 * k + 3] = fmaxf(v[4 * k + 3] + bb.w, 0.f);
+        }
+        if (DROP) tc_dropout<32>(P, (uint32_t)gi, 1, c * 32, v);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          const float4 ww = w4[k];
+          up[0] = fmaf(v[4 * k], ww.x, up[0]);     up[1] = fmaf(v[4 * k + 1], ww.y, up[1]);
+          up[2] = fmaf(v[4 * k + 2], ww.z, up[2]); up[3] = fmaf(v[4 * k + 3], ww.w, up[3]);
         }
       }
       const float u = (up[0] + up[1]) + (up[2] + up[3]);
@@ -270,18 +276,19 @@ __global__ void __launch_bounds__(NT_TC, 1) cell_fwd_tc_kernel(const CellParams 
   if (warp == 2) tc::tmem_dealloc(tbase, TMEM_COLS);
 }
 
-cudaError_t launch_cell_fwd_tc(const CellParams& P, int grid, cudaStream_t st) {
-  cudaError_t e;
-  if (P.g) {
-    e = cudaFuncSetAttribute(cell_fwd_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_TC_BYTES);
-    if (e != cudaSuccess) return e;
-    cell_fwd_tc_kernel<true><<<grid, NT_TC, SMEM_TC_BYTES, st>>>(P);
-  } else {
-    e = cudaFuncSetAttribute(cell_fwd_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_TC_BYTES);
-    if (e != cudaSuccess) return e;
-    cell_fwd_tc_kernel<false><<<grid, NT_TC, SMEM_TC_BYTES, st>>>(P);
-  }
+template <bool MOM, bool DROP>
+static cudaError_t launch_fwd_tc_variant(const CellParams& P, int grid, cudaStream_t st) {
+  cudaError_t e = cudaFuncSetAttribute(cell_fwd_tc_kernel<MOM, DROP>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)SMEM_TC_BYTES);
+  if (e != cudaSuccess) return e;
+  cell_fwd_tc_kernel<MOM, DROP><<<grid, NT_TC, SMEM_TC_BYTES, st>>>(P);
   return cudaGetLastError();
+}
+
+cudaError_t launch_cell_fwd_tc(const CellParams& P, int grid, cudaStream_t st) {
+  const bool drop = P.drop_thr != 0;
+  if (P.g) return drop ? launch_fwd_tc_variant<true, true>(P, grid, st) : launch_fwd_tc_variant<true, false>(P, grid, st);
+  return drop ? launch_fwd_tc_variant<false, true>(P, grid, st) : launch_fwd_tc_variant<false, false>(P, grid, st);
 }
 
 }  // namespace dlap

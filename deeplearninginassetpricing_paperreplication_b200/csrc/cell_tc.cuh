@@ -62,6 +62,20 @@ __device__ __forceinline__ void fill_w2_images(const CellParams& P, uint8_t* hi,
   }
 }
 
+// Dropout on N consecutive hidden units U0.. of one stock-month (N even): v[k] <- v[k] * (0 | scale).
+// Same counter-based generator and keying as relu_dropout() of the fp32 kernels (cell_f32.cuh), so the
+// two precisions drop exactly the same units for a given seed, forward and backward.
+template <int N>
+__device__ __forceinline__ void tc_dropout(const CellParams& P, uint32_t cell_global, int layer, int U0, float* v) {
+  const uint32_t key = mix32(cell_global ^ P.seed_lo) ^ P.seed_hi;
+#pragma unroll
+  for (int k = 0; k < N; k += 2) {
+    const uint32_t r = mix32(key + (uint32_t)(layer * 32 + ((U0 + k) >> 1)) * 0x9E3779B9u);
+    v[k] = ((r & 0xffffu) >= P.drop_thr) ? v[k] * P.drop_scale : 0.f;
+    v[k + 1] = ((r >> 16) >= P.drop_thr) ? v[k + 1] * P.drop_scale : 0.f;
+  }
+}
+
 // three-term split product for one K = 16 step
 __device__ __forceinline__ void umma3(uint32_t d, uint64_t ah, uint64_t al, uint64_t bh, uint64_t bl,
                                       uint32_t idesc, bool first) {

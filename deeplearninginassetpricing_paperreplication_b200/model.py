@@ -248,8 +248,6 @@ class AssetPricingGAN(nn.Module):
         H = self.sdf_net.macro_lstm.output_dim if with_macro else 0
         h0, c0 = _hidden_pair(hidden, H, dev) if with_macro else (None, None)
         p_drop = self.sdf_net.dropout_p if self.training else 0.0
-        if p_drop > 0 and self.precision != 'fp32':
-            _unsupported("train-mode dropout with b200_precision != 'fp32'")
         seed = int(torch.randint(0, 2 ** 62, (1,)).item()) if p_drop > 0 else 0   # CPU generator: no sync
         opts = Fn.StepOptions(weighted_loss=bool(self.weighted_loss),
                               need_moments=(phase != 'unconditional'), precision=self.precision,

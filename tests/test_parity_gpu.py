@@ -311,11 +311,13 @@ def test_trajectory_matches_oracle():
         assert abs(a - b) <= 1e-4 * abs(b), (phase, a, b)
 
 
-def test_dropout_train_mode():
+@pytest.mark.parametrize("precision", ["fp32", "bf16x3"])
+def test_dropout_train_mode(precision):
     macro, x, R, mask = make_panel(8, 600, 8, seed=7)
     d = dev()
     torch.manual_seed(5)
-    model = AssetPricingGAN({"macro_feature_dim": 8, "individual_feature_dim": 46, "dropout": 0.05}).to(d)
+    model = AssetPricingGAN({"macro_feature_dim": 8, "individual_feature_dim": 46, "dropout": 0.05,
+                             "b200_precision": precision}).to(d)
     args = (macro.to(d), x.to(d), R.to(d), mask.to(d))
     model.eval()
     base = model(*args)
@@ -345,6 +347,26 @@ def test_dropout_train_mode():
     fd = float(lp - lm) / (2 * eps)
     an = float((gdir * direction).sum())
     assert abs(fd - an) <= 5e-2 * abs(an) + 1e-9, (fd, an)
+
+
+def test_dropout_mask_is_the_same_in_both_precisions():
+    """Counter-based dropout is keyed on (seed, stock-month, layer, unit) only: the tensor-core kernels
+    drop exactly the units the fp32 kernels drop, so a training run does not depend on the arithmetic."""
+    macro, x, R, mask = make_panel(6, 900, 8, seed=17)
+    d = dev()
+    args = (macro.to(d), x.to(d), R.to(d), mask.to(d))
+    torch.manual_seed(5)
+    m32 = AssetPricingGAN({"macro_feature_dim": 8, "individual_feature_dim": 46, "dropout": 0.05}).to(d)
+    mtc = AssetPricingGAN({"macro_feature_dim": 8, "individual_feature_dim": 46, "dropout": 0.05,
+                           "b200_precision": "bf16x3"}).to(d)
+    mtc.load_state_dict(m32.state_dict())
+    m32.train(); mtc.train()
+    torch.manual_seed(3); a = m32(*args); a["loss"].backward()
+    torch.manual_seed(3); b = mtc(*args); b["loss"].backward()
+    assert rel_err(_np(b["weights"]), _np(a["weights"])) < 5e-5
+    assert abs(float(a["loss"]) - float(b["loss"])) <= 1e-5 * abs(float(a["loss"]))
+    ga, gb = m32.sdf_net.fc_layers[3].weight.grad, mtc.sdf_net.fc_layers[3].weight.grad
+    assert float((ga - gb).norm() / ga.norm()) < 2e-2      # same mask; residual = ReLU-kink noise (see test_tc_parity)
 
 
 def test_errors_are_loud():
