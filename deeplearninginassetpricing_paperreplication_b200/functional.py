@@ -221,7 +221,7 @@ class GanStepFn(torch.autograd.Function):
                       int(opts.dropout_seed), st)
             row_stats = torch.empty(T, RS_W, dtype=torch.float32, device=dev)
             pr = torch.empty(T, dtype=torch.float32, device=dev)
-            scalars = torch.zeros(SC_W, dtype=torch.float32, device=dev)
+            scalars = torch.empty(SC_W, dtype=torch.float32, device=dev)
             _lib.call("dlap_row_finish", ws.pp, _ptr(ws.row_part), prec,
                       int(opts.weighted_loss),
                       _ptr(sh.n_bar) if sh is not None else None, _ptr(row_stats), _ptr(pr),
@@ -284,7 +284,13 @@ class GanStepFn(torch.autograd.Function):
                       _ptr(c_loc), _ptr(row_stats), _ptr(ws.ds_part), _ptr(g_pr), _ptr(G), _ptr(scalars),
                       int(opts.weighted_loss), int(want_sdf), int(want_mom), _ptr(ws.wpart),
                       _ptr(ws.dadc_part), prec, float(opts.dropout_p), int(opts.dropout_seed), st)
-            grads = [None if p is None else torch.zeros_like(p) for p in params]
+            # one zero fill for all twelve gradient tensors (views of one flat buffer)
+            sizes = [0 if p is None else p.numel() for p in params]
+            flat_g = torch.zeros(sum(sizes), dtype=torch.float32, device=dev)
+            grads, off = [], 0
+            for p, n in zip(params, sizes):
+                grads.append(None if p is None else flat_g[off:off + n].view_as(p))
+                off += n
             gt = _tensors(grads)
             dadc = torch.empty(T, 72, dtype=torch.float32, device=dev)
             _lib.call("dlap_grad_finish", ws.pp, _ptr(ws.wpart), _ptr(ws.dadc_part), prec, int(want_sdf),

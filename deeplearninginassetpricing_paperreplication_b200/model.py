@@ -228,6 +228,12 @@ class AssetPricingGAN(nn.Module):
         self.month_shard: Optional[Fn.MonthShard] = None
 
     # -- fast-path plumbing -------------------------------------------------------------------
+    def _zero(self, dev):
+        z = getattr(self, "_zero_cache", None)
+        if z is None or z.device != dev:
+            z = self._zero_cache = torch.zeros((), dtype=torch.float32, device=dev)
+        return z
+
     def _kernel_params(self, with_macro: bool):
         if self._hidden_dim_moment:
             _unsupported("hidden layers in the moment network (hidden_dim_moment != [])")
@@ -254,7 +260,7 @@ class AssetPricingGAN(nn.Module):
                               dropout_p=p_drop, dropout_seed=seed, shard=self.month_shard)
         l_c, l_u, pr, w, sharpe, hn, cn = Fn.GanStepFn.apply(
             opts, macro_features, x, returns, mask, h0, c0, *params)
-        zero = torch.zeros((), dtype=torch.float32, device=dev)
+        zero = self._zero(dev)
         if phase == 'unconditional':            # src/model.py:524-528
             loss_unc, loss_cond, total = l_u, zero, l_u
         elif phase == 'moment':                 # src/model.py:530-535
