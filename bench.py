@@ -7,8 +7,9 @@ step, and % of HBM roofline, next to the reference CPU path).
 One step = model.zero_grad(); out = model(panel, phase='conditional'); out['loss'].backward()
 (src/train.py:77-84) on the paper-shape synthetic panel T=240, N=10,000, 46 characteristics,
 178 macro series (BASELINE.json configs[1]); dropout disabled (the parity configuration).
-Under torchrun (N > 1) every rank owns 240 months of a 240*N-month panel (weak scaling, month
-sharding); the value is all ranks' stock-months / max-over-ranks device time.
+Under torchrun (N > 1) the panel grows to 10,000*N stocks and is sharded BY MONTH: every rank owns
+240/N months of all stocks, i.e. the same 2.4 M stock-months per GPU (weak scaling; the LSTM, replicated
+on every rank, keeps its 240 steps); the value is all ranks' stock-months / max-over-ranks device time.
 
 Prints ONE JSON line on rank 0.
 """
@@ -141,8 +142,10 @@ def run_ours(args, rank, world):
     local = int(os.environ.get("LOCAL_RANK", 0))
     dev = torch.device("cuda", local)
     torch.cuda.set_device(dev)
-    T, N = T_MONTHS, N_STOCKS
-    T_total = T * world
+    if T_MONTHS % world:
+        raise SystemExit(f"--gpus must divide {T_MONTHS} months")
+    T, N = T_MONTHS // world, N_STOCKS * world           # this rank's slab: T months of all N stocks
+    T_total = T_MONTHS
     macro_all = torch.randn(T_total, M_MACRO, generator=torch.Generator().manual_seed(99))
     _, x, R, mask = synthetic_panel(T, N, F_CHARS, M_MACRO, seed=1234 + rank)
     torch.manual_seed(42)
@@ -181,7 +184,6 @@ def run_ours(args, rank, world):
     resident = (d_macro, d_x, d_R, d_mask)
     for _ in range(max(args.warmup, 3)):
         step(resident)
-    ws = Fn.workspace(T, N, F_CHARS, M_MACRO, 4, dev)
     sampler = ClockSampler(local)
     sampler.start()
     l0 = sum(w.launches for w in Fn._workspaces.values())
@@ -240,9 +242,11 @@ def run_ours(args, rank, world):
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32" if args.precision == "fp32" else "bf16x3 (fp32 split in hi+lo bf16, 3 MMAs per product, f32 accumulate)",
         "data": "synthetic",
-        "config": {"workload": f"paper-shape panel T={T} N={N} F={F_CHARS} M={M_MACRO} per GPU "
-                               f"(BASELINE.json configs[1]); phase 'conditional' fwd+bwd, dropout 0, "
-                               f"hidden [64,64], rnn [4], 8 moments; months sharded across {world} GPU(s)",
+        "config": {"workload": (f"paper-shape panel T={T_total} N={N} F={F_CHARS} M={M_MACRO} "
+                                f"(BASELINE.json configs[1]" + ("" if world == 1 else f", stocks x{world}") +
+                                f"); phase 'conditional' fwd+bwd, dropout 0, hidden [64,64], rnn [4], 8 moments; "
+                                f"sharded by month, {T} months x {N} stocks = {T * N} stock-months per GPU "
+                                f"on {world} GPU(s)"),
                    "l2": "inputs (442 MB panel per GPU) larger than the 126 MB L2; no flush needed",
                    "precision": args.precision},
         "clocks": clocks,

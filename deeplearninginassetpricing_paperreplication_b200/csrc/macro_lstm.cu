@@ -37,6 +37,7 @@ struct MacroParams {
   const float* dadc;    // [T,72]  da_t (64) | dc_t (8), summed over stocks
   float* dpre;          // [T,4H] scratch: LSTM pre-activation gradients
   int have_sdf, have_mom;
+  int wgrad_staged;     // macro_wgrad: h_t / da_t staged in shared memory (fits for T up to ~600)
   float* gWih; float* gWhh; float* gbih; float* gbhh;   // LSTM grads
   float* gW1;           // [64, ldw1]  (columns F.. written here)
   float* gb1;           // [64]
@@ -303,18 +304,29 @@ __global__ void __launch_bounds__(256) macro_wgrad_kernel(const MacroParams P) {
     }
     return;
   }
-  // ---- small outputs: one warp per output row, lanes stride over the months, fixed-tree warp sum
+  // ---- small outputs: one warp per output row, lanes stride over the months, fixed-tree warp sum;
+  //      h_t and da_t staged in shared memory first (behind coef)
+  float* hsm = coef + (size_t)T * NR;                  // [T][H]
+  float* dasm = hsm + (size_t)T * (H > 0 ? H : 1);     // [T][64]
+  const bool staged = P.wgrad_staged != 0;
+  if (P.have_sdf && staged) {
+    for (int i = tid; i < T * H; i += 256) hsm[i] = __ldg(P.save + (size_t)(i / H) * 6 * H + (i % H));
+    for (int i = tid; i < T * D1; i += 256) dasm[i] = __ldg(P.dadc + (size_t)(i / D1) * 72 + (i % D1));
+  }
+  __syncthreads();
+  auto h_at = [&](int t, int k) { return staged ? hsm[t * H + k] : __ldg(P.save + (size_t)t * 6 * H + k); };
+  auto da_at = [&](int t, int j) { return staged ? dasm[t * D1 + j] : __ldg(P.dadc + (size_t)t * 72 + j); };
   if (P.have_sdf) {
     for (int j = warp; j < D1; j += 8) {               // dW1[j][F+k] = sum_t da_t[j] h_t[k] ; db1[j] = sum_t da_t[j]
       float a[HMAX], b = 0.f;
 #pragma unroll
       for (int k = 0; k < HMAX; ++k) a[k] = 0.f;
       for (int t = lane; t < T; t += 32) {
-        const float d = __ldg(P.dadc + (size_t)t * 72 + j);
+        const float d = da_at(t, j);
         b += d;
 #pragma unroll
         for (int k = 0; k < HMAX; ++k)
-          if (k < H) a[k] = fmaf(d, __ldg(P.save + (size_t)t * 6 * H + k), a[k]);
+          if (k < H) a[k] = fmaf(d, h_at(t, k), a[k]);
       }
       b = warp_sum(b);
 #pragma unroll
@@ -336,7 +348,7 @@ __global__ void __launch_bounds__(256) macro_wgrad_kernel(const MacroParams P) {
 #pragma unroll
         for (int k = 0; k < HMAX; ++k)
           if (k < H) {
-            const float hp = (t > 0) ? __ldg(P.save + (size_t)(t - 1) * 6 * H + k) : (P.h0 ? __ldg(P.h0 + k) : 0.f);
+            const float hp = (t > 0) ? h_at(t - 1, k) : (P.h0 ? __ldg(P.h0 + k) : 0.f);
             a[k] = fmaf(d, hp, a[k]);
           }
       }
@@ -412,10 +424,14 @@ cudaError_t launch_macro_bwd(const MacroParams& P, cudaStream_t st) {
     if (e != cudaSuccess) return e;
   }
   const int NR = 4 * P.H + KM;
-  const size_t smem = ((size_t)P.T * NR + (size_t)8 * NR * 32) * 4;
+  const size_t main_sm = ((size_t)P.T * NR + (size_t)8 * NR * 32) * 4;
+  const size_t small_sm = ((size_t)P.T * NR + (size_t)P.T * (P.H > 0 ? P.H : 1) + (size_t)P.T * D1) * 4;
+  MacroParams Q = P;
+  Q.wgrad_staged = small_sm <= 200 * 1024;
+  const size_t smem = (Q.wgrad_staged && small_sm > main_sm) ? small_sm : main_sm;
   cudaError_t e = cudaFuncSetAttribute(macro_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
-  macro_wgrad_kernel<<<(P.M + 31) / 32 + 1, 256, smem, st>>>(P);
+  macro_wgrad_kernel<<<(Q.M + 31) / 32 + 1, 256, smem, st>>>(Q);
   return cudaGetLastError();
 }
 
