@@ -52,7 +52,9 @@ __global__ void __launch_bounds__(NT_TC, 1) cell_fwd_tc_kernel(const CellParams 
   uint64_t* bar = s.bars();
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int ntiles = P.T * P.tpm;
-  const int my_tiles = (ntiles > (int)blockIdx.x) ? (ntiles - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;
+  const int chunk = tc_chunk(ntiles, gridDim.x);           // contiguous tile range per CTA (sequential HBM stream)
+  const int tile_lo = min(ntiles, (int)blockIdx.x * chunk);
+  const int my_tiles = min(ntiles, tile_lo + chunk) - tile_lo;
 
   // ---- one-time set-up ----
   for (int sl = 0; sl < 2; ++sl) fill_w1_images(P, s.w1h(sl), s.w1l(sl), tid, NT_TC);
@@ -77,7 +79,7 @@ __global__ void __launch_bounds__(NT_TC, 1) cell_fwd_tc_kernel(const CellParams 
   if (warp == 0) {
     // ===== producer =====
     for (int i = 0; i < my_tiles; ++i) {
-      const int tile = blockIdx.x + i * gridDim.x, st = i & 1, use = i >> 1;
+      const int tile = tile_lo + i, st = i & 1, use = i >> 1;
       mbar_wait(bar + F_STAGE_EMPTY + st, (use & 1) ^ 1);
       const TileLoad L = plan_tile(P, tile / P.tpm, (tile % P.tpm) * TILE);
       __syncwarp();
@@ -138,7 +140,7 @@ __global__ void __launch_bounds__(NT_TC, 1) cell_fwd_tc_kernel(const CellParams 
     // ===== converter: thread = cell =====
     const int cell = tid - 128;
     for (int i = 0; i < my_tiles; ++i) {
-      const int tile = blockIdx.x + i * gridDim.x, st = i & 1, sl = i & 1, use = i >> 1;
+      const int tile = tile_lo + i, st = i & 1, sl = i & 1, use = i >> 1;
       const int t = tile / P.tpm, n0 = (tile % P.tpm) * TILE;
       const TileLoad L = plan_tile(P, t, n0);
       mbar_wait(bar + F_STAGE_FULL + st, use & 1);
@@ -179,7 +181,7 @@ __global__ void __launch_bounds__(NT_TC, 1) cell_fwd_tc_kernel(const CellParams 
     const uint32_t lane_base = (uint32_t)(q4 * 32) << 16;
     const float b3 = __ldg(P.b3);
     for (int i = e; i < my_tiles; i += 2) {
-      const int tile = blockIdx.x + i * gridDim.x, sl = i & 1, use = i >> 1;
+      const int tile = tile_lo + i, sl = i & 1, use = i >> 1;
       const int t = tile / P.tpm, jt = tile % P.tpm, n0 = jt * TILE;
       const int ncell = min(TILE, P.N - n0);
       const uint32_t dA = tbase + lane_base + (sl ? COL_A1 : COL_A0), dB = tbase + lane_base + (sl ? COL_B1 : COL_B0);

@@ -21,7 +21,7 @@ __global__ void __launch_bounds__(256) row_sum_kernel(const double* __restrict__
   const int t = blockIdx.x * 8 + warp;
   if (t >= T) return;
   const int stride = tpm;
-  if (seg_chunk > 0)           // tensor-core layout: only the (month, CTA) segments that exist were written
+  if (seg_chunk > 0)           // segment layout: only the (month, CTA) segments that exist were written
     tpm = ((t + 1) * tpm_tiles - 1) / seg_chunk - (t * tpm_tiles) / seg_chunk + 1;
   double c = 0, su = 0, sur = 0, sr = 0;
   const double4* p = reinterpret_cast<const double4*>(row_part) + (size_t)t * stride;
