@@ -239,7 +239,7 @@ class GanStepFn(torch.autograd.Function):
                 nsplit = 1
             _lib.call("dlap_loss_finish", ws.pp, _ptr(col), nsplit, _ptr(e), _ptr(t_i),
                       _ptr(ws.loss_part), _ptr(ws.counter), _ptr(scalars), st)
-            ws.launches += 4
+            ws.launches += 5
         ctx.save_for_backward(x, R, mask, macro, h0, c0, *params)
         ctx.opts, ctx.ws = opts, ws
         ctx.inter = (save, a_t, c_t, row_stats, scalars, g, e, t_i)
@@ -343,5 +343,5 @@ def sdf_weights(macro, x, mask, params, h0=None, c0=None, normalized=False, prec
                   _ptr(pr), _ptr(scalars), st)
         w = torch.empty(T, N, dtype=torch.float32, device=dev)
         _lib.call("dlap_weights", ws.pp, _ptr(u), _ptr(mask), _ptr(row_stats), int(normalized), _ptr(w), st)
-        ws.launches += 3
+        ws.launches += 4
     return w, hn, cn, save

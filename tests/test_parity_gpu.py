@@ -312,6 +312,57 @@ def test_trajectory_matches_oracle():
 
 
 @pytest.mark.parametrize("precision", ["fp32", "bf16x3"])
+def test_three_phase_schedule_matches_oracle(precision):
+    """The 3-phase loop of src/train.py:238-394 in miniature (two Adam optimisers, clip at 1.0, SDF net
+    frozen with requires_grad=False in phase 2 as at :309-312, dropout 0), driven through the drop-in
+    classes on the GPU and through the oracle port on the CPU: the loss trajectories and the final
+    normalised-weight Sharpe ratio (evaluate(), src/train.py:133-137) must agree."""
+    from oracle import torch_port as tp
+    macro, x, R, mask = make_panel(30, 500, 8, seed=16)
+    d = dev()
+    torch.manual_seed(8)
+    model = AssetPricingGAN({"macro_feature_dim": 8, "individual_feature_dim": 46, "dropout": 0.0,
+                             "b200_precision": precision}).to(d)
+    ref = {k: v.detach().cpu().clone().requires_grad_(True) for k, v in model.state_dict().items()}
+    opt_s = torch.optim.Adam(model.sdf_net.parameters(), lr=1e-3)
+    opt_m = torch.optim.Adam(model.moment_net.parameters(), lr=1e-3)
+    ropt_s = torch.optim.Adam([ref[k] for k in tp.SDF_KEYS], lr=1e-3)
+    ropt_m = torch.optim.Adam([ref[k] for k in tp.MOMENT_KEYS], lr=1e-3)
+    args = (macro.to(d), x.to(d), R.to(d), mask.to(d))
+    tol = 2e-4 if precision == "fp32" else 1e-3
+    schedule = [("unconditional", "sdf")] * 4 + [("moment", "moment")] * 3 + [("conditional", "sdf")] * 4
+    for phase, scope in schedule:
+        model.train()
+        frozen = phase == "moment"
+        for p in model.sdf_net.parameters():
+            p.requires_grad = not frozen
+        for k in tp.SDF_KEYS:
+            ref[k].requires_grad_(not frozen)
+        opt, ropt = (opt_s, ropt_s) if scope == "sdf" else (opt_m, ropt_m)
+        group = model.sdf_net.parameters() if scope == "sdf" else model.moment_net.parameters()
+        rgroup = [ref[k] for k in (tp.SDF_KEYS if scope == "sdf" else tp.MOMENT_KEYS)]
+        opt.zero_grad(); ropt.zero_grad()
+        out = model(*args, phase=phase)
+        out["loss"].backward()
+        torch.nn.utils.clip_grad_norm_(group, 1.0)
+        opt.step()
+        rout = tp.forward(ref, macro, x, R, mask, phase=phase)
+        rout["loss"].backward()
+        torch.nn.utils.clip_grad_norm_(rgroup, 1.0)
+        ropt.step()
+        a, b = float(out["loss"]), float(rout["loss"])
+        assert abs(a - b) <= tol * abs(b), (phase, a, b)
+    model.eval()
+    with torch.no_grad():
+        wn, _ = model.get_weights(args[0], args[1], args[3], normalized=True)
+        pr = (wn * args[2] * args[3].float()).sum(dim=1).cpu()
+        rwn, _ = tp.normalized_weights({k: v.detach() for k, v in ref.items()}, macro, x, mask)
+        rpr = (rwn * R * mask.float()).sum(dim=1)
+    sa, sb = float(pr.mean() / pr.std()), float(rpr.mean() / rpr.std())
+    assert abs(sa - sb) <= 5e-3 * abs(sb) + 1e-4, (sa, sb)
+
+
+@pytest.mark.parametrize("precision", ["fp32", "bf16x3"])
 def test_dropout_train_mode(precision):
     macro, x, R, mask = make_panel(8, 600, 8, seed=7)
     d = dev()
