@@ -65,6 +65,7 @@ SIGNATURES = {
     "dlap_grad_finish": (_PLAN, _P, _P, _I, _I, _I, _TENS, _P, _P),
     "dlap_macro_bwd": (_PLAN, _P, _TENS, _P, _P, _P, _P, _P, _I, _I, _TENS, _P),
     "dlap_weights": (_PLAN, _P, _P, _P, _I, _P, _P),
+    "dlap_debug_timeline": (_P,),
     "dlap_umma_selftest": (_P, _I, _P, _I, _I, _I, _I, _I, _I, _I, _I, _I, _I, _I, _I, _P, _P),
     "dlap_umma_ts_selftest": (_P, _P, _I, _I, _I, _I, _I, _I, _I, _I, _P, _P, _P),
     "dlap_umma_cycles": (_P, _I, _P, _I, _I, _I, _I, _I, _I, _I, _I, _I, _I, _I, _I, _I, _P, _P, _P),

@@ -30,6 +30,7 @@ cudaError_t launch_macro_bwd_c(const dlap_plan* plan, const float* macro, const 
                                const float* c0, const float* save, const float* dadc, float* dpre, int want_sdf,
                                int want_mom, const dlap_tensors* g, cudaStream_t st);
 size_t macro_fwd_smem(int T, int M, int H);
+void set_bwd_tc_timeline(long long* p);
 size_t macro_bwd_smem(int T, int H);
 }  // namespace dlap
 
@@ -57,6 +58,11 @@ static int check_plan(const dlap_plan* p) {
 extern "C" {
 
 int dlap_abi_version(void) { return DLAP_ABI_VERSION; }
+
+int dlap_debug_timeline(long long* stamps) {
+  set_bwd_tc_timeline(stamps);
+  return DLAP_OK;
+}
 
 const char* dlap_error_string(int code) {
   switch (code) {

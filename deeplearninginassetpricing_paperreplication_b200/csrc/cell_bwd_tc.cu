@@ -77,6 +77,12 @@ __device__ __forceinline__ float lane_transpose_sum16(float (&v)[16], int lane) 
 __device__ __forceinline__ void epi_barrier() { asm volatile("bar.sync 1, 512;" ::: "memory"); }
 }  // namespace
 
+// diagnostics: stamp slot k of local tile i (CTA 0 only, one thread per role)
+#define DLAP_STAMP(i, k)                                                                    \
+  do {                                                                                      \
+    if (P.timeline && blockIdx.x == 0 && (i) < 256) P.timeline[(i) * 16 + (k)] = clock64(); \
+  } while (0)
+
 template <bool SDF, bool MOM, bool DROP>
 __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P) {
   extern __shared__ __align__(128) uint8_t smem_raw[];
@@ -202,6 +208,7 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
         // -- after E2(i): dW2 and dgrad
         mbar_wait(bar + B_DZ2_FULL, par);
         tc::fence_after_sync();
+        if (lane == 0) DLAP_STAMP(i, 8);
         if (tc::elect_one()) {
 #pragma unroll
           for (int ks = 0; ks < TILE / 16; ++ks)
@@ -214,12 +221,15 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
           tc::umma_commit(bar + B_D3_FULL);
         }
         __syncwarp();
+        if (lane == 0) DLAP_STAMP(i, 9);
       }
       if (i + 1 < my_tiles) issue_l2(i + 1);            // runs under E3(i)
+      if (lane == 0) DLAP_STAMP(i, 10);
       if (SDF) {
         // -- after E3(i): [dW1x | dWq]^T = X^T . [dz1 | dpre]; dz1 sits in the H buffer of this tile, dpre next to it
         mbar_wait(bar + B_DZ1_FULL, par);
         tc::fence_after_sync();
+        if (lane == 0) DLAP_STAMP(i, 11);
         if (tc::elect_one()) {
 #pragma unroll
           for (int ks = 0; ks < TILE / 16; ++ks)
@@ -234,6 +244,7 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
       }
       __syncwarp();
       if (i + 2 < my_tiles) issue_l1(i + 2);
+      if (lane == 0) DLAP_STAMP(i, 12);
     }
     if (tc::elect_one()) tc::umma_commit(bar + B_ALL_DONE);
     __syncwarp();
@@ -429,11 +440,14 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
       const int tile = tile_lo + i, sl = i & 1, par = i & 1;
       const int t = tile / P.tpm;
       du_cur = du_nxt; m1_cur = m1_nxt;
+      const bool stamp = ew == 0 && lane == 0;
+      if (stamp) DLAP_STAMP(i, 0);
       if (i + 1 < my_tiles) prefetch(i + 1);
       if (SDF) {
         // ---- E2: dz2 = du W3 [z2 > 0] -> DZ image ; dW3 += du h2 ; db2 += dz2
         mbar_wait(bar + B_D2_FULL, par);
         tc::fence_after_sync();
+        if (stamp) DLAP_STAMP(i, 1);
         float v[16];
         tc::tmem_ld16(tbase + lane_base + C_B + U0, v);
         tc::tmem_wait_ld();
@@ -471,12 +485,15 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
         fence_proxy_async();
         __syncwarp();
         if (lane == 0) mbar_arrive(bar + B_DZ2_FULL);
+        if (stamp) DLAP_STAMP(i, 2);
       }
       if (i + 1 < my_tiles) do_e1(i + 1);               // overlaps dW2 / dgrad of tile i on the tensor core
+      if (stamp) DLAP_STAMP(i, 3);
       if (SDF) {
         // ---- E3: dz1 = (dz2 . W2) [z1 > 0] -> H[sl] image (h1 of this tile is dead) ; da_t
         mbar_wait(bar + B_D3_FULL, par);
         tc::fence_after_sync();
+        if (stamp) DLAP_STAMP(i, 4);
         float v[16];
         tc::tmem_ld16(tbase + lane_base + C_C + U0, v);
         tc::tmem_wait_ld();
@@ -496,6 +513,7 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
         fence_proxy_async();
         __syncwarp();
         if (lane == 0) mbar_arrive(bar + B_DZ1_FULL);
+        if (stamp) DLAP_STAMP(i, 5);
       }
       const int t_next = (i + 1 < my_tiles) ? (tile + 1) / P.tpm : -1;
       if (t_next != t) { flush_month(t); cur_month = t_next; }
@@ -551,7 +569,12 @@ static cudaError_t launch_bwd_tc_variant(const CellParams& P, int grid, cudaStre
   return cudaGetLastError();
 }
 
-cudaError_t launch_cell_bwd_tc(const CellParams& P, int grid, bool sdf, bool mom, cudaStream_t st) {
+static long long* g_timeline = nullptr;
+void set_bwd_tc_timeline(long long* p) { g_timeline = p; }
+
+cudaError_t launch_cell_bwd_tc(const CellParams& P0, int grid, bool sdf, bool mom, cudaStream_t st) {
+  CellParams P = P0;
+  P.timeline = g_timeline;
   const bool drop = P.drop_thr != 0 && sdf;
   if (sdf && mom) return drop ? launch_bwd_tc_variant<true, true, true>(P, grid, st)
                               : launch_bwd_tc_variant<true, true, false>(P, grid, st);

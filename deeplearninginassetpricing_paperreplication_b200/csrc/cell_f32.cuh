@@ -54,6 +54,7 @@ struct CellParams {
   uint32_t drop_thr;         // drop when a 16-bit uniform < drop_thr (0 = off)
   float drop_scale;          // 1 / (1 - drop_thr/65536)
   uint32_t seed_lo, seed_hi; // per-forward seed; the backward pass regenerates the same mask
+  long long* timeline;       // diagnostics (dlap_debug_timeline): per-tile clock64 stamps of CTA 0, or null
 };
 
 // layout of one CTA's weight-gradient partial

@@ -187,6 +187,12 @@ int dlap_macro_bwd(const dlap_plan* plan, const float* macro, const dlap_tensors
 int dlap_weights(const dlap_plan* plan, const float* u, const uint8_t* mask, const float* row_stats,
                  int normalized, float* w_out, void* stream);
 
+/* Diagnostics (no counterpart in the reference): when `stamps` is a device buffer of 256*16 int64, every
+ * following tensor-core dlap_cell_bwd launch makes CTA 0 record clock64() at fixed points of each of its
+ * first 256 tiles (slots 0-5: epilogue warp, 8-12: MMA warp; see csrc/cell_bwd_tc.cu).  NULL switches it
+ * off.  scripts/bwd_timeline.py turns the stamps into per-phase cycle counts. */
+int dlap_debug_timeline(long long* stamps);
+
 /* Hardware self-test of the tensor-core plumbing (no counterpart in the reference): one CTA computes
  * D[128,N] = A.B^T (bf16 operands, fp32 accumulate in TMEM) from two operand images laid out by the
  * caller in the library's no-swizzle canonical layout, with caller-given descriptor strides (bytes) and
