@@ -16,7 +16,8 @@ PKG_DIR = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(PKG_DIR)
 CSRC = os.path.join(PKG_DIR, "csrc")
 LIB_PATH = os.path.join(PKG_DIR, "libdlap_b200.so")
-SOURCES = ("capi.cu", "cell_fwd.cu", "cell_bwd.cu", "reduce.cu", "macro_lstm.cu", "tc_selftest.cu", "cell_fwd_tc.cu", "cell_bwd_tc.cu")
+SOURCES = ("capi.cu", "cell_fwd.cu", "cell_bwd.cu", "reduce.cu", "macro_lstm.cu", "tc_selftest.cu", "cell_fwd_tc.cu", "cell_bwd_tc.cu",
+           "panel_index.cu")
 NVCC_FLAGS = ("-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-shared", "-Xcompiler", "-fPIC")
 
@@ -35,7 +36,7 @@ class DlapPlan(C.Structure):
                 ("ldwq", C.c_int32), ("row_part_bytes", C.c_int64), ("col_part_bytes", C.c_int64),
                 ("loss_part_bytes", C.c_int64), ("ds_part_bytes", C.c_int64),
                 ("wpart_bytes", C.c_int64), ("dadc_part_bytes", C.c_int64),
-                ("lstm_save_bytes", C.c_int64), ("dpre_bytes", C.c_int64)]
+                ("lstm_save_bytes", C.c_int64), ("dpre_bytes", C.c_int64), ("index_bytes", C.c_int64)]
 
 
 class DlapTensors(C.Structure):
@@ -53,16 +54,17 @@ _I = C.c_int
 SIGNATURES = {
     "dlap_make_plan": (C.POINTER(DlapDims), _I, _PLAN),
     "dlap_macro_fwd": (_PLAN, _P, _TENS, _P, _P, _P, _P, _P, _P, _P, _P, _P),
-    "dlap_cell_fwd": (_PLAN, _P, _P, _P, _TENS, _P, _P, _P, _P, _P, _I, C.c_float, C.c_uint64, _P),
-    "dlap_row_finish": (_PLAN, _P, _I, _I, _P, _P, _P, _P, _P),
+    "dlap_panel_index": (_PLAN, _P, _P, _P),
+    "dlap_cell_fwd": (_PLAN, _P, _P, _P, _P, _TENS, _P, _P, _P, _P, _P, _I, C.c_float, C.c_uint64, _P),
+    "dlap_row_finish": (_PLAN, _P, _P, _I, _I, _P, _P, _P, _P, _P),
     "dlap_col_partial": (_PLAN, _P, _P, _P, _P, _P, _P, _P, _P),
     "dlap_loss_finish": (_PLAN, _P, _I, _P, _P, _P, _P, _P, _P),
     "dlap_loss_finish_noalloc": (_PLAN, _P, _I, _P, _P, _P, _P),
     "dlap_loss_coeff": (_PLAN, _P, _P, _P, _P, _P, _P),
     "dlap_ds_rows": (_PLAN, _P, _P, _P, _P, _P, _P),
-    "dlap_cell_bwd": (_PLAN, _P, _P, _P, _TENS, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _P, _P, _I,
+    "dlap_cell_bwd": (_PLAN, _P, _P, _P, _P, _TENS, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _P, _P, _I,
                       C.c_float, C.c_uint64, _P),
-    "dlap_grad_finish": (_PLAN, _P, _P, _I, _I, _I, _TENS, _P, _P),
+    "dlap_grad_finish": (_PLAN, _P, _P, _P, _I, _I, _I, _TENS, _P, _P),
     "dlap_macro_bwd": (_PLAN, _P, _TENS, _P, _P, _P, _P, _P, _I, _I, _TENS, _P),
     "dlap_weights": (_PLAN, _P, _P, _P, _I, _P, _P),
     "dlap_debug_timeline": (_P,),

@@ -11,8 +11,9 @@ cudaError_t launch_cell_bwd_f32(const CellParams& P, int grid, bool sdf, bool mo
 cudaError_t launch_cell_fwd_tc(const CellParams& P, int grid, cudaStream_t st);
 cudaError_t launch_cell_bwd_tc(const CellParams& P, int grid, bool sdf, bool mom, cudaStream_t st);
 size_t smem_bwd_bytes(int F);
-cudaError_t launch_row_finish(const double*, int, int, int, int, int, const float*, float*, float*, float*,
+cudaError_t launch_row_finish(const double*, int, int, const int*, int, const float*, float*, float*, float*,
                               cudaStream_t);
+cudaError_t launch_panel_index(const uint8_t* mask, int T, int N, int* index, cudaStream_t st);
 cudaError_t launch_col_partial(const float*, const float*, const uint8_t*, const float*, const float*, int, int,
                                int, double*, float*, cudaStream_t);
 cudaError_t launch_loss_finish(const double*, int, int, int, float*, float*, double*, unsigned int*, float*,
@@ -20,7 +21,7 @@ cudaError_t launch_loss_finish(const double*, int, int, int, float*, float*, dou
 cudaError_t launch_coeff(const float*, const float*, int, const float*, const float*, float*, cudaStream_t);
 cudaError_t launch_ds_rows(const float*, const float*, const uint8_t*, const float*, int, int, int, double*,
                            cudaStream_t);
-cudaError_t launch_grad_finish(const float*, int, int, int, int, const float*, int, int, int, int, float*, int,
+cudaError_t launch_grad_finish(const float*, int, int, int, int, const float*, int, int, const int*, float*, int,
                                float*, float*, float*, float*, float*, int, int, float*, cudaStream_t);
 cudaError_t launch_weights(const float*, const uint8_t*, const float*, int, int, int, float*, cudaStream_t);
 cudaError_t launch_macro_fwd_c(const dlap_plan* plan, const float* macro, const dlap_tensors* p, const float* h0,
@@ -31,6 +32,7 @@ cudaError_t launch_macro_bwd_c(const dlap_plan* plan, const float* macro, const 
                                int want_mom, const dlap_tensors* g, cudaStream_t st);
 size_t macro_fwd_smem(int T, int M, int H);
 void set_bwd_tc_timeline(long long* p);
+void set_fwd_tc_timeline(long long* p);
 size_t macro_bwd_smem(int T, int H);
 }  // namespace dlap
 
@@ -61,6 +63,7 @@ int dlap_abi_version(void) { return DLAP_ABI_VERSION; }
 
 int dlap_debug_timeline(long long* stamps) {
   set_bwd_tc_timeline(stamps);
+  set_fwd_tc_timeline(stamps ? stamps + 256 * 16 : nullptr);
   return DLAP_OK;
 }
 
@@ -113,6 +116,7 @@ int dlap_make_plan(const dlap_dims* dims, int device, dlap_plan* out) {
   p.ds_part_bytes = (int64_t)T * p.row_splits * 8;
   p.wpart_bytes = (int64_t)p.grid_cell * wp_stride(round4(F)) * 4;
   p.dadc_part_bytes = (int64_t)T * (p.tpm > 4 ? p.tpm : 4) * 72 * 4;
+  p.index_bytes = (int64_t)idx_ints(T, N) * 4;
   p.lstm_save_bytes = (int64_t)T * 6 * (dims->H > 0 ? dims->H : 1) * 4;
   p.dpre_bytes = (int64_t)T * 4 * (dims->H > 0 ? dims->H : 1) * 4;
   *out = p;
@@ -158,7 +162,16 @@ int dlap_macro_fwd(const dlap_plan* plan, const float* macro, const dlap_tensors
   return DLAP_OK;
 }
 
-int dlap_cell_fwd(const dlap_plan* plan, const float* x, const float* R, const uint8_t* mask,
+int dlap_panel_index(const dlap_plan* plan, const uint8_t* mask, int32_t* index, void* stream) {
+  int rc = check_plan(plan);
+  if (rc) return rc;
+  REQ(mask); REQ(index);
+  if (reinterpret_cast<uintptr_t>(index) & 15) return DLAP_E_ALIGN;
+  CU(launch_panel_index(mask, plan->dims.T, plan->dims.N, index, (cudaStream_t)stream));
+  return DLAP_OK;
+}
+
+int dlap_cell_fwd(const dlap_plan* plan, const float* x, const float* R, const uint8_t* mask, const int32_t* index,
                   const dlap_tensors* params, const float* a_t, const float* c_t, float* u, float* g,
                   double* row_part, int precision, float dropout_p, uint64_t dropout_seed, void* stream) {
   int rc = check_plan(plan);
@@ -175,6 +188,8 @@ int dlap_cell_fwd(const dlap_plan* plan, const float* x, const float* R, const u
   if (rc) return rc;
   if (precision == DLAP_PREC_BF16X3) {
     if (plan->dims.F > 46) return DLAP_E_SHAPE;      // the ones column lives at k = 46
+    REQ(index);
+    P.index = index;
     CU(launch_cell_fwd_tc(P, plan->grid_cell, (cudaStream_t)stream));
     return DLAP_OK;
   }
@@ -182,16 +197,19 @@ int dlap_cell_fwd(const dlap_plan* plan, const float* x, const float* R, const u
   return DLAP_OK;
 }
 
-int dlap_row_finish(const dlap_plan* plan, const double* row_part, int precision, int weighted_loss,
-                    const float* n_bar_in, float* row_stats, float* pr, float* scalars, void* stream) {
+int dlap_row_finish(const dlap_plan* plan, const double* row_part, const int32_t* index, int precision,
+                    int weighted_loss, const float* n_bar_in, float* row_stats, float* pr, float* scalars,
+                    void* stream) {
   int rc = check_plan(plan);
   if (rc) return rc;
   REQ(row_part); REQ(row_stats); REQ(pr); REQ(scalars);
   if (precision != DLAP_PREC_FP32 && precision != DLAP_PREC_BF16X3) return DLAP_E_PRECISION;
-  // fp32 kernel: one row-sum partial per tile; tensor-core kernel: one per tile and TMEM lane quarter
-  const int slots = plan->tpm * (precision == DLAP_PREC_BF16X3 ? 4 : 1), seg_chunk = 0;
-  CU(launch_row_finish(row_part, plan->dims.T, slots, plan->tpm, seg_chunk, weighted_loss, n_bar_in, row_stats, pr, scalars,
-                       (cudaStream_t)stream));
+  // fp32 kernel: one row-sum partial per dense tile; tensor-core kernel: one per valid-cell tile and TMEM
+  // lane quarter
+  const bool tc = precision == DLAP_PREC_BF16X3;
+  if (tc) REQ(index);
+  CU(launch_row_finish(row_part, plan->dims.T, plan->tpm, tc ? index : nullptr, weighted_loss, n_bar_in, row_stats,
+                       pr, scalars, (cudaStream_t)stream));
   return DLAP_OK;
 }
 
@@ -235,7 +253,7 @@ int dlap_ds_rows(const dlap_plan* plan, const float* g, const float* R, const ui
   return DLAP_OK;
 }
 
-int dlap_cell_bwd(const dlap_plan* plan, const float* x, const float* R, const uint8_t* mask,
+int dlap_cell_bwd(const dlap_plan* plan, const float* x, const float* R, const uint8_t* mask, const int32_t* index,
                   const dlap_tensors* params, const float* a_t, const float* c_t, const float* row_stats,
                   const double* dS_part, const float* dpr_cot, const float* G, const float* scalars,
                   int weighted_loss, int want_sdf, int want_mom, float* wpart, float* dadc_part, int precision,
@@ -256,6 +274,8 @@ int dlap_cell_bwd(const dlap_plan* plan, const float* x, const float* R, const u
   if (rc) return rc;
   if (precision == DLAP_PREC_BF16X3) {
     if (plan->dims.F > 46) return DLAP_E_SHAPE;
+    REQ(index);
+    P.index = index;
     CU(launch_cell_bwd_tc(P, plan->grid_cell, want_sdf != 0, want_mom != 0, (cudaStream_t)stream));
     return DLAP_OK;
   }
@@ -263,22 +283,20 @@ int dlap_cell_bwd(const dlap_plan* plan, const float* x, const float* R, const u
   return DLAP_OK;
 }
 
-int dlap_grad_finish(const dlap_plan* plan, const float* wpart, const float* dadc_part, int precision,
-                     int want_sdf, int want_mom, const dlap_tensors* grads, float* dadc, void* stream) {
+int dlap_grad_finish(const dlap_plan* plan, const float* wpart, const float* dadc_part, const int32_t* index,
+                     int precision, int want_sdf, int want_mom, const dlap_tensors* grads, float* dadc,
+                     void* stream) {
   int rc = check_plan(plan);
   if (rc) return rc;
   if (precision != DLAP_PREC_FP32 && precision != DLAP_PREC_BF16X3) return DLAP_E_PRECISION;
-  // fp32 kernel: one da_t|dc_t partial per tile; tensor-core kernel: one per (month, CTA) segment
-  int slots = plan->tpm, seg_chunk = 0;
-  if (precision == DLAP_PREC_BF16X3) {
-    seg_chunk = tc_chunk((long long)plan->dims.T * plan->tpm, plan->grid_cell);
-    slots = tc_seg_max(plan->tpm, seg_chunk);
-  }
+  // fp32 kernel: one da_t|dc_t partial per dense tile; tensor-core kernel: one per (month, CTA) segment
+  const bool tc = precision == DLAP_PREC_BF16X3;
+  if (tc) REQ(index);
   REQ(wpart); REQ(dadc_part); REQ(grads); REQ(dadc);
   if (want_sdf) { REQ(grads->w1); REQ(grads->w2); REQ(grads->b2); REQ(grads->w3); REQ(grads->b3); }
   if (want_mom) REQ(grads->wq);
   CU(launch_grad_finish(wpart, plan->grid_cell, plan->dims.F, want_sdf, want_mom, dadc_part, plan->dims.T,
-                        slots, plan->tpm, seg_chunk, grads->w1, plan->ldw1, grads->w2, grads->b2, grads->w3, grads->b3, grads->wq,
+                        plan->tpm, tc ? index : nullptr, grads->w1, plan->ldw1, grads->w2, grads->b2, grads->w3, grads->b3, grads->wq,
                         plan->ldwq, plan->dims.M, dadc, (cudaStream_t)stream));
   return DLAP_OK;
 }

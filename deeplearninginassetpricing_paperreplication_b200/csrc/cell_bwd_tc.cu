@@ -10,14 +10,18 @@
 // All activation tiles live in shared memory as [group of 8 units][cell][8] bf16 images, so the same
 // bytes serve as K-major operand (forward / dgrad) and MN-major operand (weight gradients).
 //
+// Tiles are the valid-cell tiles of dlap_panel_index (<= 128 unmasked stocks of one month, gathered row
+// by row); masked cells contribute exactly 0 to every gradient and are never visited.
+//
 // Scheduling.  A CTA owns a CONTIGUOUS range of tiles, so the tiles of one month are consecutive: the
 // per-month sums (da_t, dc_t) and the per-CTA sums (dW3, db2) are accumulated in registers per cell and
 // reduced across cells only when the month changes / at the end.  H1 is double buffered and dz1 is
 // written over the (dead) H1 of its own tile, so the epilogue of tile i+1's layer 1 runs while the
 // tensor core works on dW2/dgrad of tile i, and layer 2 of tile i+1 runs under E3 of tile i.
 //
-// 20 warps: 0 TMA producer + TMEM owner, 1 MMA issuer, 2-3 converter, 4-19 epilogue (four warps per
-// TMEM lane quarter; each thread handles 16 of the 64 hidden units of its cell).
+// 20 warps: 0 TMEM owner, 1 MMA issuer, 2-3 gather + convert (each fetches two shares of 32 rows of the tile
+// with coalesced loads, 32 rows in flight, then every lane converts one row per share into the X image);
+// 4-19 epilogue (four warps per TMEM lane quarter; each thread handles 16 of the 64 hidden units of its cell).
 #include "cell_tc.cuh"
 
 namespace dlap {
@@ -26,7 +30,7 @@ using namespace tcl;
 namespace {
 constexpr int NT_B = 640;
 constexpr int NEPI = 16;                               // epilogue warps
-constexpr int STAGE_BYTES = ((TILE * 46 + 8) * 4 + 127) & ~127;
+constexpr int STAGE_BYTES = TILE * ROW_PITCH * 4;        // one 208-B slot per gathered characteristic row
 constexpr uint32_t DPS_IMG = TILE * 16;                // one group: [cell][8 moments]
 
 struct SmemB {
@@ -55,7 +59,7 @@ struct SmemB {
 constexpr size_t SMEM_B_BYTES = (size_t)STAGE_BYTES + 4 * X_IMG + 4 * W1_IMG + 2 * W2_IMG + 6 * H_IMG + 4 * DPS_IMG +
                                 128 * 4 + (NEPI * 32 + 32) * 4 + 24 * 8 + 16 + 128;
 
-enum { B_STAGE_FULL = 0, B_STAGE_EMPTY = 1, B_XOP_FULL = 2, B_XOP_EMPTY = 4, B_D1_FULL = 6, B_H1_FULL = 8,
+enum { B_XOP_FULL = 2, B_XOP_EMPTY = 4, B_D1_FULL = 6, B_H1_FULL = 8,
        B_W1_DONE = 10, B_D2_FULL = 12, B_DZ2_FULL = 13, B_D3_FULL = 14, B_DZ1_FULL = 15, B_ALL_DONE = 16 };
 
 constexpr uint32_t C_A0 = 0, C_A1 = 96, C_B = 192, C_C = 256, C_W2 = 320, C_W1 = 384, TMEM_COLS = 512;   // C_W1: 72 cols
@@ -90,7 +94,7 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
   s.base = tc::smem_align128(smem_raw);
   uint64_t* bar = s.bars();
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int ntiles = P.T * P.tpm;
+  const int ntiles = __ldg(P.index);                       // tiles of valid cells (dlap_panel_index)
   const int chunk = tc_chunk(ntiles, gridDim.x);
   const int tile_lo = min(ntiles, (int)blockIdx.x * chunk);
   const int my_tiles = min(ntiles, tile_lo + chunk) - tile_lo;
@@ -106,7 +110,6 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
     }
   if (tid < 64) { s.b2s()[tid] = __ldg(P.b2 + tid); s.w3s()[tid] = __ldg(P.W3 + tid); }
   if (tid == 0) {
-    mbar_init(bar + B_STAGE_FULL, 1);  mbar_init(bar + B_STAGE_EMPTY, 2);
     for (int i = 0; i < 2; ++i) {
       mbar_init(bar + B_XOP_FULL + i, 2);    mbar_init(bar + B_XOP_EMPTY + i, 1);
       mbar_init(bar + B_D1_FULL + i, 1);     mbar_init(bar + B_H1_FULL + i, NEPI);
@@ -124,26 +127,7 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
   tc::fence_after_sync();
   const uint32_t tbase = *s.tmem_slot();
 
-  if (warp == 0) {
-    // ===== producer (single staging buffer; the X images are double buffered) =====
-    for (int i = 0; i < my_tiles; ++i) {
-      const int tile = tile_lo + i;
-      mbar_wait(bar + B_STAGE_EMPTY, (i & 1) ^ 1);
-      const TileLoad L = plan_tile(P, tile / P.tpm, (tile % P.tpm) * TILE);
-      __syncwarp();
-      if (L.bytes) {
-        if (lane == 0) {
-          mbar_expect_tx(bar + B_STAGE_FULL, L.bytes);
-          bulk_g2s(s.stage(), L.src - L.shift, L.bytes, bar + B_STAGE_FULL);
-        }
-      } else {
-        const int n = L.ncell * P.F;
-        for (int j = lane; j < n; j += 32) s.stage()[L.shift + j] = __ldg(L.src + j);
-        __syncwarp();
-        if (lane == 0) mbar_arrive(bar + B_STAGE_FULL);
-      }
-    }
-  } else if (warp == 1) {
+  if (warp == 1) {
     // ===== MMA issuer (all lanes wait, lane 0 issues) =====
     const uint32_t id_l1 = tc::idesc_bf16(128, N1, 0, 0), id_l2 = tc::idesc_bf16(128, 64, 0, 0);
     const uint32_t id_dg = tc::idesc_bf16(128, 64, 0, 1);                 // A K-major, B = W2 MN-major
@@ -249,34 +233,53 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
     if (tc::elect_one()) tc::umma_commit(bar + B_ALL_DONE);
     __syncwarp();
   } else if (warp == 2 || warp == 3) {
-    // ===== converter: each thread converts cells c0 and c0 + 64 =====
-    const int c0 = tid - 64;
+    // ===== gather + convert: this warp owns rows 64w .. 64w+63 of every tile, as two shares of 32; lane = cell =====
+    const int c0 = (warp - 2) * 64 + lane;                           // cells c0 and c0 + 32
+    float* stage = s.stage() + (warp - 2) * 64 * ROW_PITCH;          // private to this warp
+    MonthCursor mc;
+    if (my_tiles > 0) mc.init(P, tile_lo);
+    int n_nxt[2] = {-1, -1}, t_nxt = 0;
+    auto load_n = [&](int tile) {
+      mc.seek(P, tile);
+      t_nxt = mc.t;
+      const int* vr = vidx_row(P, mc.t) + mc.j0(tile);
+      const int nc = mc.ncell(tile);
+#pragma unroll
+      for (int sh = 0; sh < 2; ++sh) n_nxt[sh] = (c0 + 32 * sh < nc) ? __ldg(vr + c0 + 32 * sh) : -1;
+    };
+    if (my_tiles > 0) load_n(tile_lo);
     for (int i = 0; i < my_tiles; ++i) {
-      const int tile = tile_lo + i, sl = i & 1, use = i >> 1;
-      const int t = tile / P.tpm, n0 = (tile % P.tpm) * TILE;
-      const TileLoad L = plan_tile(P, t, n0);
-      mbar_wait(bar + B_STAGE_FULL, i & 1);
+      const int sl = i & 1, use = i >> 1;
+      const int n2[2] = {n_nxt[0], n_nxt[1]}, t = t_nxt;
+      if (i + 1 < my_tiles) load_n(tile_lo + i + 1);
+#pragma unroll
+      for (int sh = 0; sh < 2; ++sh) {
+        float2 ra[16], rb[16];
+        gather_load<16>(P, t, n2[sh], 0, lane, ra);
+        gather_load<16>(P, t, n2[sh], 16, lane, rb);
+        gather_store<16>(P, stage + sh * 32 * ROW_PITCH, 0, lane, ra);
+        gather_store<16>(P, stage + sh * 32 * ROW_PITCH, 16, lane, rb);
+      }
+      __syncwarp();
       mbar_wait(bar + B_XOP_EMPTY + sl, (use & 1) ^ 1);
 #pragma unroll
-      for (int rep = 0; rep < 2; ++rep) {
-        const int cell = c0 + 64 * rep;
-        const float* row = s.stage() + L.shift + cell * P.F;
-        const bool live = cell < L.ncell;
+      for (int sh = 0; sh < 2; ++sh) {
+        const int cell = c0 + 32 * sh;
+        const bool live = n2[sh] >= 0;
+        const float* slot = stage + (sh * 32 + lane) * ROW_PITCH;
 #pragma unroll
         for (int g = 0; g < KG1; ++g) {
           float v[8];
+          row_group(slot, g, v);
 #pragma unroll
-          for (int e = 0; e < 8; ++e) {
-            const int k = g * 8 + e;
-            v[e] = (live && k < P.F) ? row[k] : 0.f;
-          }
+          for (int e = 0; e < 8; ++e) v[e] = (live && g * 8 + e < P.F) ? v[e] : 0.f;
           if (g == KG1 - 1) v[ONES_K - 8 * (KG1 - 1)] = 1.f;
           uint4 hi, lo;
           tc::split8(v, hi, lo);
           *reinterpret_cast<uint4*>(s.xh(sl) + (g * TILE + cell) * 16) = hi;
           *reinterpret_cast<uint4*>(s.xl(sl) + (g * TILE + cell) * 16) = lo;
         }
-        if (cell < N1) {                               // per-month bias column (k = 46) of this slot's W1
+        if (cell < N1) {                             // per-month bias column (k = 46) of this slot's W1
           float b = 0.f;
           if (cell < 64) b = __ldg(P.a_t + (size_t)t * 64 + cell);
           else if (cell < 72) b = __ldg(P.c_t + (size_t)t * 8 + cell - 64);
@@ -288,10 +291,10 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
         }
       }
       fence_proxy_async();
-      __syncwarp();
-      if (lane == 0) { mbar_arrive(bar + B_XOP_FULL + sl); mbar_arrive(bar + B_STAGE_EMPTY); }
+      __syncwarp();                                  // also: every lane is done with the staging slots
+      if (lane == 0) mbar_arrive(bar + B_XOP_FULL + sl);
     }
-  } else if (warp >= 4) {
+  } else if (warp >= 4 && warp < 20) {
     // ===== epilogue: thread = (cell, 16 of the hidden units) =====
     const int ew = warp - 4, q4 = warp & 3, hf = ew >> 2, cell = q4 * 32 + lane, U0 = hf * 16;
     const bool mom_warp = MOM && hf == 3;
@@ -301,29 +304,36 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
     for (int k = 0; k < 16; ++k) w3acc[k] = b2acc[k] = daacc[k] = 0.f;
 #pragma unroll
     for (int k = 0; k < 8; ++k) dc_cur[k] = dc_nxt[k] = 0.f;
-    const int seg_max = (P.tpm + chunk - 2) / chunk + 1;
     float du_cur = 0.f, du_nxt = 0.f;
     uint32_t m1_cur = 0u, m1_nxt = 0u;
-    int cur_month = my_tiles > 0 ? tile_lo / P.tpm : 0;
 
-    // per-cell inputs of the next E1 tile are fetched one phase early (HBM latency off the critical path);
-    // the per-month scalars (dP_t, Rbar_t, S_t) are recomputed only when the month changes
-    unsigned char pf_m8 = 0;
+    // Per-cell inputs of the next E1 tile are fetched one phase early and its stock number one tile before
+    // that (HBM latency off the critical path); the per-month scalars (dP_t, Rbar_t, S_t) are recomputed
+    // only when the month changes.
+    MonthCursor mc;
+    int nn_n = -1;                                       // stock of this thread's cell in the next tile to prefetch (month: mc.t)
+    int pf_t = 0;                                        // month of the prefetched tile
+    uint32_t pf_gi = 0u;
+    bool pf_live = false;
     float pf_r = 0.f, pf_g[8];
 #pragma unroll
     for (int k = 0; k < 8; ++k) pf_g[k] = 0.f;
     int ms_month = -1;
     float ms_dP = 0.f, ms_rbar = 0.f, ms_S = 0.f;
-    auto prefetch = [&](int i) {
+    auto load_n = [&](int i) {
       const int tile = tile_lo + i;
-      const int t = tile / P.tpm, n0 = (tile % P.tpm) * TILE;
-      const bool live = cell < min(TILE, P.N - n0);
-      const size_t gi = (size_t)t * P.N + n0 + cell;
-      pf_m8 = 0; pf_r = 0.f;
-      if (live) { pf_m8 = P.mask[gi]; pf_r = __ldg(P.R + gi); }      // consumed one phase later: no stall here
+      mc.seek(P, tile);
+      nn_n = (cell < mc.ncell(tile)) ? __ldg(vidx_row(P, mc.t) + mc.j0(tile) + cell) : -1;
+    };
+    auto prefetch = [&](int i) {                         // mc / nn_n describe tile i
+      const int t = mc.t, n = nn_n;
+      pf_t = t; pf_live = n >= 0;
+      const size_t gi = (size_t)t * P.N + (pf_live ? n : 0);
+      pf_gi = (uint32_t)gi;
+      pf_r = pf_live ? __ldg(P.R + gi) : 0.f;            // consumed one phase later: no stall here
       if (mom_warp) {
 #pragma unroll
-        for (int k = 0; k < 8; ++k) pf_g[k] = live ? __ldg(P.G + (size_t)k * P.N + n0 + cell) : 0.f;
+        for (int k = 0; k < 8; ++k) pf_g[k] = pf_live ? __ldg(P.G + (size_t)k * P.N + n) : 0.f;
       }
       if (t != ms_month) {
         ms_month = t;
@@ -335,18 +345,18 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
         ms_rbar = rs[RS_RBAR];
         ms_S = rs[RS_S];
       }
+      if (i + 1 < my_tiles) load_n(i + 1);
     };
+    int cur_month = 0, e1_t = 0;
+    uint32_t gi_cur = 0u, gi_nxt = 0u;                   // dense cell number (dropout key) of tile i / i+1
 
-    auto cell_global = [&](int i) {
-      const int tile = tile_lo + i;
-      return (uint32_t)((size_t)(tile / P.tpm) * P.N + (size_t)(tile % P.tpm) * TILE + cell);
-    };
     const float dscale = DROP ? P.drop_scale : 1.f;
     // E1 of local tile i: h1 -> H[sl] image, relu mask, this cell's du ; moment warps: dpre
     auto do_e1 = [&](int i) {
-      const int tile = tile_lo + i, sl = i & 1, use = i >> 1;
-      const int t = tile / P.tpm;
-      const float pf_m = pf_m8 ? 1.f : 0.f;
+      const int sl = i & 1, use = i >> 1;
+      const int t = pf_t;
+      e1_t = pf_t; gi_nxt = pf_gi;
+      const float pf_m = pf_live ? 1.f : 0.f;            // every listed cell is unmasked
       du_nxt = pf_m * ms_dP * (pf_r - ms_rbar);
       const float cq = pf_r * pf_m * ms_S;
       float gk[8];
@@ -363,7 +373,7 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
         tc::tmem_wait_ld();
 #pragma unroll
         for (int k = 0; k < 16; ++k) v[k] = fmaxf(v[k], 0.f);
-        if (DROP) tc_dropout<16>(P, cell_global(i), 0, U0, v);        // the image holds h1 AFTER dropout
+        if (DROP) tc_dropout<16>(P, gi_nxt, 0, U0, v);                // the image holds h1 AFTER dropout
 #pragma unroll
         for (int k = 0; k < 16; ++k)
           if (v[k] > 0.f) m1_nxt |= 1u << k;                          // kept and z1 > 0
@@ -415,8 +425,9 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
         }
       }
       epi_barrier();
-      const int seg = (int)blockIdx.x - (t * P.tpm) / chunk;
-      float* out = P.dadc_part + ((size_t)t * seg_max + seg) * 72;
+      // CTAs that touch month t are consecutive, starting with the owner of the month's first tile
+      const int seg = (int)blockIdx.x - __ldg(P.index + idx_off_ts() + t) / chunk;
+      float* out = P.dadc_part + ((size_t)t * P.tpm + seg) * 72;
       const int et = tid - 128;                                      // 0..511
       if (et < 64) {                                                 // unit et: quarters 0..3 in order
         const int h = et >> 4, k = et & 15;
@@ -435,11 +446,17 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
       for (int k = 0; k < 8; ++k) { dc_cur[k] = dc_nxt[k]; dc_nxt[k] = 0.f; }
     };
 
-    if (my_tiles > 0) { prefetch(0); do_e1(0); }
+    if (my_tiles > 0) {
+      mc.init(P, tile_lo);
+      load_n(0);
+      prefetch(0);
+      cur_month = pf_t;
+      do_e1(0);
+    }
     for (int i = 0; i < my_tiles; ++i) {
-      const int tile = tile_lo + i, sl = i & 1, par = i & 1;
-      const int t = tile / P.tpm;
-      du_cur = du_nxt; m1_cur = m1_nxt;
+      const int sl = i & 1, par = i & 1;
+      const int t = e1_t;
+      du_cur = du_nxt; m1_cur = m1_nxt; gi_cur = gi_nxt;
       const bool stamp = ew == 0 && lane == 0;
       if (stamp) DLAP_STAMP(i, 0);
       if (i + 1 < my_tiles) prefetch(i + 1);
@@ -460,7 +477,7 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
 #pragma unroll
           for (int e = 0; e < 4; ++e) v[4 * k4 + e] = fmaxf(v[4 * k4 + e] + b_[e], 0.f);
         }
-        if (DROP) tc_dropout<16>(P, cell_global(i), 1, U0, v);        // h2 after dropout: > 0 iff kept and z2 > 0
+        if (DROP) tc_dropout<16>(P, gi_cur, 1, U0, v);                // h2 after dropout: > 0 iff kept and z2 > 0
 #pragma unroll
         for (int k4 = 0; k4 < 4; ++k4) {
           const float4 ww = w4[k4];
@@ -515,7 +532,7 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
         if (lane == 0) mbar_arrive(bar + B_DZ1_FULL);
         if (stamp) DLAP_STAMP(i, 5);
       }
-      const int t_next = (i + 1 < my_tiles) ? (tile + 1) / P.tpm : -1;
+      const int t_next = (i + 1 < my_tiles) ? e1_t : -1;   // do_e1(i + 1) has run
       if (t_next != t) { flush_month(t); cur_month = t_next; }
     }
 

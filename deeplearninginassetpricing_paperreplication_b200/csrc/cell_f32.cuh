@@ -55,7 +55,108 @@ struct CellParams {
   float drop_scale;          // 1 / (1 - drop_thr/65536)
   uint32_t seed_lo, seed_hi; // per-forward seed; the backward pass regenerates the same mask
   long long* timeline;       // diagnostics (dlap_debug_timeline): per-tile clock64 stamps of CTA 0, or null
+  // valid-cell index (dlap_panel_index); tensor-core kernels only, null = not built
+  const int* index;
 };
+
+// ---- valid-cell index ----------------------------------------------------------------------
+// The reference pushes every cell through both nets and multiplies by the mask afterwards
+// (src/model.py:261-279, :376-382); a masked cell therefore contributes exactly 0 to every loss, weight
+// and gradient.  dlap_panel_index lists, per month, the stocks with mask = 1 in ascending order and cuts
+// each list into tiles of <= 128 cells; the tensor-core kernels walk those tiles only.
+//   int32 index[]:  [0] total tiles | [4, 4+T] tile_start (exclusive prefix, [T] = total) | cnt [T] |
+//                   vidx [T, N] (16-B aligned): row t holds cnt[t] stock numbers, rest undefined
+__host__ __device__ inline int idx_off_ts() { return 4; }
+__host__ __device__ inline int idx_off_cnt(int T) { return 4 + T + 1; }
+__host__ __device__ inline long long idx_off_vidx(int T) { return (4 + 2 * T + 1 + 3) & ~3; }
+__host__ __device__ inline long long idx_ints(int T, int N) { return idx_off_vidx(T) + (long long)T * N; }
+
+__device__ __forceinline__ const int* vidx_row(const CellParams& P, int t) {
+  return P.index + idx_off_vidx(P.T) + (size_t)t * P.N;
+}
+
+// Walks the tile list in ascending order: month of a tile, its position in the month's list.
+struct MonthCursor {
+  int t, first, next, cnt;   // month, its first tile, first tile of the following month, valid cells
+  // first use: `tile` < total tiles
+  __device__ __forceinline__ void init(const CellParams& P, int tile) {
+    const int* ts = P.index + idx_off_ts();
+    int lo = 0, hi = P.T - 1;                    // largest t with ts[t] <= tile (lands on a non-empty month)
+    while (lo < hi) {
+      const int mid = (lo + hi + 1) >> 1;
+      if (__ldg(ts + mid) <= tile) lo = mid; else hi = mid - 1;
+    }
+    t = lo; first = __ldg(ts + t); next = __ldg(ts + t + 1);
+    cnt = __ldg(P.index + idx_off_cnt(P.T) + t);
+  }
+  // move forward to `tile` (>= the current one, < total tiles)
+  __device__ __forceinline__ void seek(const CellParams& P, int tile) {
+    if (tile < next) return;
+    const int* ts = P.index + idx_off_ts();
+    do { ++t; first = next; next = __ldg(ts + t + 1); } while (tile >= next);
+    cnt = __ldg(P.index + idx_off_cnt(P.T) + t);
+  }
+  __device__ __forceinline__ int j0(int tile) const { return (tile - first) * TILE; }
+  __device__ __forceinline__ int ncell(int tile) const { return min(TILE, cnt - (tile - first) * TILE); }
+};
+
+// A gathered tile sits in the staging buffer as one 208-B slot per characteristic row (row at the slot start).
+constexpr int ROW_PITCH = 52;           // floats; 13 x 16 B: LDS.128 over consecutive rows is conflict-free
+
+// Gather by one warp.  Lane l knows the stock number of row l of the warp's share (n_lane, -1 = no row).
+// Row j is fetched by ONE coalesced warp-wide load (lane k takes floats 2k, 2k+1; when x or F do not allow
+// 8-byte loads: floats k and k+32), so ROWS independent loads are in flight per warp -- scattered 184-B rows
+// need that memory-level parallelism; per-row TMA bulk copies and cp.async both serialise on a short queue
+// (measured: 78 and 190 cycles per row).
+// The loads are unconditional on clamped addresses (a missing row reads the month's first row, lanes past
+// the row re-read its last element; the converter zeroes what does not exist): a predicated load followed by
+// a select makes ptxas wait for each load before issuing the next one.
+template <int ROWS>
+__device__ __forceinline__ void gather_load(const CellParams& P, int t, int n_lane, int row0, int lane,
+                                            float2 (&r)[ROWS]) {
+  const bool wide = ((P.F & 1) == 0) && ((reinterpret_cast<uintptr_t>(P.x) & 7) == 0);
+  const float* xt = P.x + (size_t)t * P.N * P.F;
+  if (wide) {
+    const int k = min(lane, (P.F >> 1) - 1);
+#pragma unroll
+    for (int j = 0; j < ROWS; ++j) {
+      const int nr = max(__shfl_sync(0xffffffffu, n_lane, row0 + j), 0);
+      r[j] = __ldg(reinterpret_cast<const float2*>(xt + (size_t)nr * P.F) + k);
+    }
+  } else {
+    const int k0 = min(lane, P.F - 1), k1 = min(lane + 32, P.F - 1);
+#pragma unroll
+    for (int j = 0; j < ROWS; ++j) {
+      const int nr = max(__shfl_sync(0xffffffffu, n_lane, row0 + j), 0);
+      const float* src = xt + (size_t)nr * P.F;
+      r[j].x = __ldg(src + k0);
+      r[j].y = __ldg(src + k1);
+    }
+  }
+}
+// rows row0 .. row0+ROWS-1 of the warp's share -> its staging slots
+template <int ROWS>
+__device__ __forceinline__ void gather_store(const CellParams& P, float* stage_warp, int row0, int lane,
+                                             const float2 (&r)[ROWS]) {
+  const bool wide = ((P.F & 1) == 0) && ((reinterpret_cast<uintptr_t>(P.x) & 7) == 0);
+#pragma unroll
+  for (int j = 0; j < ROWS; ++j) {
+    float* dst = stage_warp + (row0 + j) * ROW_PITCH;
+    if (wide) {
+      if (2 * lane < P.F) reinterpret_cast<float2*>(dst)[lane] = r[j];
+    } else {
+      if (lane < P.F) dst[lane] = r[j].x;
+      if (lane + 32 < P.F) dst[lane + 32] = r[j].y;
+    }
+  }
+}
+// floats 8g..8g+7 of the row in slot `slot`
+__device__ __forceinline__ void row_group(const float* slot, int g, float (&v)[8]) {
+  const float4* p = reinterpret_cast<const float4*>(slot) + 2 * g;
+  const float4 a0 = p[0], a1 = p[1];
+  v[0] = a0.x; v[1] = a0.y; v[2] = a0.z; v[3] = a0.w;
+  v[4] = a1.x; v[5] = a1.y; v[6] = a1.z; v[7] = a1.w;
+}
 
 // layout of one CTA's weight-gradient partial
 __host__ __device__ inline int wp_off_w2() { return 0; }

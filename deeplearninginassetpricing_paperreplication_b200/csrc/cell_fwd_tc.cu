@@ -1,11 +1,16 @@
 // Forward per-cell kernel on the 5th-gen tensor cores (tcgen05 + TMEM), precision "bf16x3".
 // Same contract as cell_fwd_f32_kernel (cell_fwd.cu); see cell_tc.cuh for the arithmetic.
 //
+// The kernel walks the valid-cell tiles of dlap_panel_index (cell_f32.cuh): a tile is <= 128 unmasked
+// stocks of one month, gathered row by row.
+//
 // Persistent CTA, one per SM, 16 warps with fixed roles; two tiles are in flight (slot = tile & 1):
-//   warp 0      TMA producer: 1-D bulk copies of fp32 characteristic slabs into a 2-stage ring
 //   warp 1      MMA issuer (one lane): layer 1 of tile i is issued before layer 2 of tile i-1
 //   warp 2      TMEM allocator
-//   warps 4-7   converter: fp32 slab -> bf16 hi/lo X image (+ ones column), per-month bias column of W1
+//   warps 4-7   gather + convert: each warp fetches 32 rows of the tile with coalesced loads (the rows of tile
+//               i+1 are in flight in registers while tile i is converted), drops them into its private staging
+//               slots, then every lane turns one row into the bf16 hi/lo X image (+ ones column) and the warps
+//               write the per-month bias column of W1
 //   warps 8-11  epilogue of even tiles   } z1 -> relu -> split -> H1 image ; tanh(q) ;
 //   warps 12-15 epilogue of odd tiles    } z2 -> relu -> .W3 -> u ; g = q R m ; row sums
 #include "cell_tc.cuh"
@@ -15,34 +20,38 @@ using namespace tcl;
 
 namespace {
 constexpr int NT_TC = 512;
-constexpr int STAGE_FLOATS = TILE * 46 + 8;
-
-constexpr int STAGE_BYTES_F = ((STAGE_FLOATS * 4 + 127) & ~127);
+constexpr int STAGE_BYTES_F = TILE * ROW_PITCH * 4;      // 26 624 B: 32 row slots for each of the four gather warps
 struct SmemTc {
   uint8_t* base;
-  __device__ float* stage(int i) const { return reinterpret_cast<float*>(base + i * STAGE_BYTES_F); }
-  __device__ uint8_t* xh(int sl) const { return base + 2 * STAGE_BYTES_F + sl * 2 * X_IMG; }
+  __device__ float* stage() const { return reinterpret_cast<float*>(base); }
+  __device__ uint8_t* xh(int sl) const { return base + STAGE_BYTES_F + sl * 2 * X_IMG; }
   __device__ uint8_t* xl(int sl) const { return xh(sl) + X_IMG; }
-  __device__ uint8_t* w1h(int sl) const { return base + 2 * STAGE_BYTES_F + 4 * X_IMG + sl * 2 * W1_IMG; }
+  __device__ uint8_t* w1h(int sl) const { return base + STAGE_BYTES_F + 4 * X_IMG + sl * 2 * W1_IMG; }
   __device__ uint8_t* w1l(int sl) const { return w1h(sl) + W1_IMG; }
-  __device__ uint8_t* hh(int sl) const { return base + 2 * STAGE_BYTES_F + 4 * X_IMG + 4 * W1_IMG + sl * 2 * H_IMG; }
+  __device__ uint8_t* hh(int sl) const { return base + STAGE_BYTES_F + 4 * X_IMG + 4 * W1_IMG + sl * 2 * H_IMG; }
   __device__ uint8_t* hl(int sl) const { return hh(sl) + H_IMG; }
-  __device__ uint8_t* w2h() const { return base + 2 * STAGE_BYTES_F + 4 * X_IMG + 4 * W1_IMG + 4 * H_IMG; }
+  __device__ uint8_t* w2h() const { return base + STAGE_BYTES_F + 4 * X_IMG + 4 * W1_IMG + 4 * H_IMG; }
   __device__ uint8_t* w2l() const { return w2h() + W2_IMG; }
   __device__ float* b2s() const { return reinterpret_cast<float*>(w2l() + W2_IMG); }
   __device__ float* w3s() const { return b2s() + 64; }
   __device__ uint64_t* bars() const { return reinterpret_cast<uint64_t*>(w3s() + 64); }
   __device__ uint32_t* tmem_slot() const { return reinterpret_cast<uint32_t*>(bars() + 16); }
 };
-enum { F_STAGE_FULL = 0, F_STAGE_EMPTY = 2, F_XOP_FULL = 4, F_XOP_EMPTY = 6, F_D1_FULL = 8, F_H1_FULL = 10,
+enum { F_XOP_FULL = 4, F_XOP_EMPTY = 6, F_D1_FULL = 8, F_H1_FULL = 10,
        F_D2_FULL = 12, F_D2_EMPTY = 14 };
 
-constexpr size_t SMEM_TC_BYTES = 2 * (size_t)STAGE_BYTES_F + 4 * X_IMG + 4 * W1_IMG + 4 * H_IMG + 2 * W2_IMG +
+constexpr size_t SMEM_TC_BYTES = (size_t)STAGE_BYTES_F + 4 * X_IMG + 4 * W1_IMG + 4 * H_IMG + 2 * W2_IMG +
                                  128 * 4 + 16 * 8 + 16 + 256;
 
 // TMEM columns
 constexpr uint32_t COL_A0 = 0, COL_B0 = 96, COL_A1 = 160, COL_B1 = 256, TMEM_COLS = 512;
 }  // namespace
+
+// diagnostics: stamp slot k of local tile i (CTA 0 only, one thread per role)
+#define DLAP_STAMP(i, k)                                                                    \
+  do {                                                                                      \
+    if (P.timeline && blockIdx.x == 0 && (i) < 256) P.timeline[(i) * 16 + (k)] = clock64(); \
+  } while (0)
 
 template <bool MOM, bool DROP>
 __global__ void __launch_bounds__(NT_TC, 1) cell_fwd_tc_kernel(const CellParams P) {
@@ -51,8 +60,8 @@ __global__ void __launch_bounds__(NT_TC, 1) cell_fwd_tc_kernel(const CellParams 
   s.base = tc::smem_align128(smem_raw);
   uint64_t* bar = s.bars();
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int ntiles = P.T * P.tpm;
-  const int chunk = tc_chunk(ntiles, gridDim.x);           // contiguous tile range per CTA (sequential HBM stream)
+  const int ntiles = __ldg(P.index);                       // tiles of valid cells (dlap_panel_index)
+  const int chunk = tc_chunk(ntiles, gridDim.x);           // contiguous tile range per CTA
   const int tile_lo = min(ntiles, (int)blockIdx.x * chunk);
   const int my_tiles = min(ntiles, tile_lo + chunk) - tile_lo;
 
@@ -62,7 +71,6 @@ __global__ void __launch_bounds__(NT_TC, 1) cell_fwd_tc_kernel(const CellParams 
   if (tid < 64) { s.b2s()[tid] = __ldg(P.b2 + tid); s.w3s()[tid] = __ldg(P.W3 + tid); }
   if (tid == 0) {
     for (int i = 0; i < 2; ++i) {
-      mbar_init(bar + F_STAGE_FULL + i, 1);  mbar_init(bar + F_STAGE_EMPTY + i, 4);
       mbar_init(bar + F_XOP_FULL + i, 4);    mbar_init(bar + F_XOP_EMPTY + i, 1);
       mbar_init(bar + F_D1_FULL + i, 1);     mbar_init(bar + F_H1_FULL + i, 4);
       mbar_init(bar + F_D2_FULL + i, 1);     mbar_init(bar + F_D2_EMPTY + i, 4);
@@ -76,26 +84,7 @@ __global__ void __launch_bounds__(NT_TC, 1) cell_fwd_tc_kernel(const CellParams 
   tc::fence_after_sync();
   const uint32_t tbase = *s.tmem_slot();
 
-  if (warp == 0) {
-    // ===== producer =====
-    for (int i = 0; i < my_tiles; ++i) {
-      const int tile = tile_lo + i, st = i & 1, use = i >> 1;
-      mbar_wait(bar + F_STAGE_EMPTY + st, (use & 1) ^ 1);
-      const TileLoad L = plan_tile(P, tile / P.tpm, (tile % P.tpm) * TILE);
-      __syncwarp();
-      if (L.bytes) {
-        if (lane == 0) {
-          mbar_expect_tx(bar + F_STAGE_FULL + st, L.bytes);
-          bulk_g2s(s.stage(st), L.src - L.shift, L.bytes, bar + F_STAGE_FULL + st);
-        }
-      } else {                                       // copy would run past the tensor: plain loads
-        const int n = L.ncell * P.F;
-        for (int j = lane; j < n; j += 32) s.stage(st)[L.shift + j] = __ldg(L.src + j);
-        __syncwarp();
-        if (lane == 0) mbar_arrive(bar + F_STAGE_FULL + st);
-      }
-    }
-  } else if (warp == 1) {
+  if (warp == 1) {
     // ===== MMA issuer (all lanes wait, lane 0 issues) =====
     {
       const uint32_t id1 = tc::idesc_bf16(128, N1, 0, 0), id2 = tc::idesc_bf16(128, 64, 0, 0);
@@ -105,6 +94,7 @@ __global__ void __launch_bounds__(NT_TC, 1) cell_fwd_tc_kernel(const CellParams 
           const int sl = i & 1, use = i >> 1;
           mbar_wait(bar + F_XOP_FULL + sl, use & 1);
           tc::fence_after_sync();
+          if (lane == 0) DLAP_STAMP(i, 8);
           const uint64_t ah = tc::smem_desc(smem_u32(s.xh(sl)), TILE * 16, 128), al = tc::smem_desc(smem_u32(s.xl(sl)), TILE * 16, 128);
           const uint64_t bh = tc::smem_desc(smem_u32(s.w1h(sl)), N1 * 16, 128), bl = tc::smem_desc(smem_u32(s.w1l(sl)), N1 * 16, 128);
           const uint32_t d = tbase + (sl ? COL_A1 : COL_A0);
@@ -117,12 +107,14 @@ __global__ void __launch_bounds__(NT_TC, 1) cell_fwd_tc_kernel(const CellParams 
             tc::umma_commit(bar + F_D1_FULL + sl);
           }
           __syncwarp();
+          if (lane == 0) DLAP_STAMP(i, 9);
         }
         if (i > 0) {                                 // layer 2 of tile i-1
           const int j = i - 1, sl = j & 1, use = j >> 1;
           mbar_wait(bar + F_H1_FULL + sl, use & 1);
           mbar_wait(bar + F_D2_EMPTY + sl, (use & 1) ^ 1);
           tc::fence_after_sync();
+          if (lane == 0) DLAP_STAMP(j, 10);
           const uint64_t ah = tc::smem_desc(smem_u32(s.hh(sl)), TILE * 16, 128), al = tc::smem_desc(smem_u32(s.hl(sl)), TILE * 16, 128);
           const uint32_t d = tbase + (sl ? COL_B1 : COL_B0);
           if (tc::elect_one()) {
@@ -133,28 +125,54 @@ __global__ void __launch_bounds__(NT_TC, 1) cell_fwd_tc_kernel(const CellParams 
             tc::umma_commit(bar + F_D2_FULL + sl);
           }
           __syncwarp();
+          if (lane == 0) DLAP_STAMP(j, 11);
         }
       }
     }
   } else if (warp >= 4 && warp < 8) {
-    // ===== converter: thread = cell =====
+    // ===== gather + convert: warp w owns rows 32w .. 32w+31 of every tile; lane = cell =====
     const int cell = tid - 128;
+    float* stage = s.stage() + (warp - 4) * 32 * ROW_PITCH;          // private to this warp
+    MonthCursor mc;
+    if (my_tiles > 0) mc.init(P, tile_lo);
+    int n_nxt = -1, t_nxt = 0;
+    auto load_n = [&](int tile) {
+      mc.seek(P, tile);
+      t_nxt = mc.t;
+      n_nxt = (cell < mc.ncell(tile)) ? __ldg(vidx_row(P, mc.t) + mc.j0(tile) + cell) : -1;
+    };
+    float2 rows[32];
+    int n = -1, t = 0;
+    if (my_tiles > 0) {
+      load_n(tile_lo);
+      n = n_nxt; t = t_nxt;
+      gather_load<32>(P, t, n, 0, lane, rows);
+      if (my_tiles > 1) load_n(tile_lo + 1);
+    }
     for (int i = 0; i < my_tiles; ++i) {
-      const int tile = tile_lo + i, st = i & 1, sl = i & 1, use = i >> 1;
-      const int t = tile / P.tpm, n0 = (tile % P.tpm) * TILE;
-      const TileLoad L = plan_tile(P, t, n0);
-      mbar_wait(bar + F_STAGE_FULL + st, use & 1);
+      const int sl = i & 1, use = i >> 1;
+      const bool live = n >= 0;
+      const int t_now = t;
+      const bool stamp = warp == 4 && lane == 0;
+      if (stamp) DLAP_STAMP(i, 0);
+      gather_store<32>(P, stage, 0, lane, rows);                     // rows of tile i (loaded one tile ago)
+      __syncwarp();
+      if (stamp) DLAP_STAMP(i, 1);
+      if (i + 1 < my_tiles) {                                        // rows of tile i+1 fly during the conversion
+        n = n_nxt; t = t_nxt;
+        gather_load<32>(P, t, n, 0, lane, rows);
+        if (i + 2 < my_tiles) load_n(tile_lo + i + 2);
+      }
+      if (stamp) DLAP_STAMP(i, 2);
       mbar_wait(bar + F_XOP_EMPTY + sl, (use & 1) ^ 1);
-      const float* row = s.stage(st) + L.shift + cell * P.F;
-      const bool live = cell < L.ncell;
+      if (stamp) DLAP_STAMP(i, 3);
+      const float* slot = stage + lane * ROW_PITCH;
 #pragma unroll
       for (int g = 0; g < KG1; ++g) {
         float v[8];
+        row_group(slot, g, v);
 #pragma unroll
-        for (int e = 0; e < 8; ++e) {
-          const int k = g * 8 + e;
-          v[e] = (live && k < P.F) ? row[k] : 0.f;
-        }
+        for (int e = 0; e < 8; ++e) v[e] = (live && g * 8 + e < P.F) ? v[e] : 0.f;
         if (g == KG1 - 1) v[ONES_K - 8 * (KG1 - 1)] = 1.f;
         uint4 hi, lo;
         tc::split8(v, hi, lo);
@@ -163,8 +181,8 @@ __global__ void __launch_bounds__(NT_TC, 1) cell_fwd_tc_kernel(const CellParams 
       }
       if (cell < N1) {                               // bias column k = 46 of this slot's W1 image
         float b = 0.f;
-        if (cell < 64) b = __ldg(P.a_t + (size_t)t * 64 + cell);
-        else if (cell < 72 && MOM) b = __ldg(P.c_t + (size_t)t * 8 + cell - 64);
+        if (cell < 64) b = __ldg(P.a_t + (size_t)t_now * 64 + cell);
+        else if (cell < 72 && MOM) b = __ldg(P.c_t + (size_t)t_now * 8 + cell - 64);
         const __nv_bfloat16 bh = __float2bfloat16_rn(b);
         const __nv_bfloat16 bl = __float2bfloat16_rn(b - __bfloat162float(bh));
         const int off = ((KG1 - 1) * N1 + cell) * 16 + (ONES_K - 8 * (KG1 - 1)) * 2;
@@ -172,28 +190,40 @@ __global__ void __launch_bounds__(NT_TC, 1) cell_fwd_tc_kernel(const CellParams 
         *reinterpret_cast<__nv_bfloat16*>(s.w1l(sl) + off) = bl;
       }
       fence_proxy_async();
-      __syncwarp();
-      if (lane == 0) { mbar_arrive(bar + F_XOP_FULL + sl); mbar_arrive(bar + F_STAGE_EMPTY + st); }
+      __syncwarp();                                  // also: every lane is done with the staging slots
+      if (lane == 0) mbar_arrive(bar + F_XOP_FULL + sl);
+      if (stamp) DLAP_STAMP(i, 4);
     }
   } else if (warp >= 8) {
     // ===== epilogue: group e handles tiles with (i & 1) == e ; thread = TMEM lane = cell =====
     const int e = (warp - 8) >> 2, q4 = warp & 3, cell = q4 * 32 + lane;
     const uint32_t lane_base = (uint32_t)(q4 * 32) << 16;
     const float b3 = __ldg(P.b3);
+    MonthCursor mc;
+    if (e < my_tiles) mc.init(P, tile_lo + e);
+    int n_nxt = -1, t_nxt = 0;
+    auto load_row = [&](int tile) {
+      mc.seek(P, tile);
+      t_nxt = mc.t;
+      n_nxt = (cell < mc.ncell(tile)) ? __ldg(vidx_row(P, mc.t) + mc.j0(tile) + cell) : -1;
+    };
+    if (e < my_tiles) load_row(tile_lo + e);
     for (int i = e; i < my_tiles; i += 2) {
       const int tile = tile_lo + i, sl = i & 1, use = i >> 1;
-      const int t = tile / P.tpm, jt = tile % P.tpm, n0 = jt * TILE;
-      const int ncell = min(TILE, P.N - n0);
+      const int t = t_nxt, n = n_nxt;
       const uint32_t dA = tbase + lane_base + (sl ? COL_A1 : COL_A0), dB = tbase + lane_base + (sl ? COL_B1 : COL_B0);
-      // this cell's mask / return: issued now, consumed after both layers (HBM latency hidden)
-      const bool live = cell < ncell;
-      const size_t gi = (size_t)t * P.N + n0 + cell;
-      unsigned char m8 = 0;
+      // this cell's return: issued now, consumed after both layers (HBM latency hidden); every listed cell
+      // is unmasked, so m = 1 exactly where the row exists
+      const bool live = n >= 0;
+      const size_t gi = (size_t)t * P.N + (live ? n : 0);
       float r = 0.f;
-      if (live) { m8 = P.mask[gi]; if (P.R) r = __ldg(P.R + gi); }
+      if (live && P.R) r = __ldg(P.R + gi);
+      if (i + 2 < my_tiles) load_row(tile_lo + i + 2);
       // -- after layer 1: h1 = relu(z1) -> bf16 hi/lo image
+      const bool stamp = q4 == 0 && lane == 0;
       mbar_wait(bar + F_D1_FULL + sl, use & 1);
       tc::fence_after_sync();
+      if (stamp) DLAP_STAMP(i, 12);
 #pragma unroll
       for (int c = 0; c < 2; ++c) {
         float v[32];
@@ -218,6 +248,7 @@ __global__ void __launch_bounds__(NT_TC, 1) cell_fwd_tc_kernel(const CellParams 
       fence_proxy_async();
       __syncwarp();
       if (lane == 0) mbar_arrive(bar + F_H1_FULL + sl);
+      if (stamp) DLAP_STAMP(i, 13);
       if (MOM) {
 #pragma unroll
         for (int k = 0; k < 8; ++k) q[k] = tc::tanh_fast(q[k]);
@@ -225,6 +256,7 @@ __global__ void __launch_bounds__(NT_TC, 1) cell_fwd_tc_kernel(const CellParams 
       // -- after layer 2: u = b3 + W3 . relu(z2 + b2)
       mbar_wait(bar + F_D2_FULL + sl, use & 1);
       tc::fence_after_sync();
+      if (stamp) DLAP_STAMP(i, 14);
       float up[4] = {b3, 0.f, 0.f, 0.f};
 #pragma unroll
       for (int c = 0; c < 2; ++c) {
@@ -251,7 +283,7 @@ __global__ void __launch_bounds__(NT_TC, 1) cell_fwd_tc_kernel(const CellParams 
       __syncwarp();
       if (lane == 0) mbar_arrive(bar + F_D2_EMPTY + sl);
       // -- outputs
-      const float m = m8 ? 1.f : 0.f;
+      const float m = live ? 1.f : 0.f;
       if (live) {
         P.u[gi] = u;
         if (MOM) {
@@ -268,9 +300,10 @@ __global__ void __launch_bounds__(NT_TC, 1) cell_fwd_tc_kernel(const CellParams 
       }
       v0 = warp_sum(v0); v1 = warp_sum(v1); v2 = warp_sum(v2); v3 = warp_sum(v3);
       if (lane == 0) {
-        double* rp = P.row_part + (((size_t)t * P.tpm + jt) * 4 + q4) * 4;
+        double* rp = P.row_part + ((size_t)tile * 4 + q4) * 4;
         rp[0] = v0; rp[1] = v1; rp[2] = v2; rp[3] = v3;
       }
+      if (stamp) DLAP_STAMP(i, 15);
     }
   }
   tc::fence_before_sync();
@@ -287,7 +320,12 @@ static cudaError_t launch_fwd_tc_variant(const CellParams& P, int grid, cudaStre
   return cudaGetLastError();
 }
 
-cudaError_t launch_cell_fwd_tc(const CellParams& P, int grid, cudaStream_t st) {
+static long long* g_timeline_fwd = nullptr;
+void set_fwd_tc_timeline(long long* p) { g_timeline_fwd = p; }
+
+cudaError_t launch_cell_fwd_tc(const CellParams& P0, int grid, cudaStream_t st) {
+  CellParams P = P0;
+  P.timeline = g_timeline_fwd;
   const bool drop = P.drop_thr != 0;
   if (P.g) return drop ? launch_fwd_tc_variant<true, true>(P, grid, st) : launch_fwd_tc_variant<true, false>(P, grid, st);
   return drop ? launch_fwd_tc_variant<false, true>(P, grid, st) : launch_fwd_tc_variant<false, false>(P, grid, st);

@@ -15,16 +15,21 @@ namespace dlap {
 // pr_t = P_t / N_t * N_bar (weighted_loss) ; S_t = 1 + pr_t       src/model.py:360,367,380
 // sharpe = mean(pr) / (std_unbiased(pr) + 1e-8)                   src/model.py:551
 // stage 1 (multi-CTA): one warp per month sums the per-tile partial slots in a fixed tree
+// `index` != null (tensor-core kernels): the partials of month t are the 4 slots of each of its valid-cell
+// tiles, tile_start[t] .. tile_start[t+1]; otherwise `tpm` slots per month.
 __global__ void __launch_bounds__(256) row_sum_kernel(const double* __restrict__ row_part, int T, int tpm,
-                                                      int tpm_tiles, int seg_chunk, float* __restrict__ row_stats) {
+                                                      const int* __restrict__ index, float* __restrict__ row_stats) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int t = blockIdx.x * 8 + warp;
   if (t >= T) return;
-  const int stride = tpm;
-  if (seg_chunk > 0)           // segment layout: only the (month, CTA) segments that exist were written
-    tpm = ((t + 1) * tpm_tiles - 1) / seg_chunk - (t * tpm_tiles) / seg_chunk + 1;
+  size_t first = (size_t)t * tpm;
+  if (index) {
+    const int* ts = index + idx_off_ts();
+    first = (size_t)ts[t] * 4;
+    tpm = (ts[t + 1] - ts[t]) * 4;
+  }
   double c = 0, su = 0, sur = 0, sr = 0;
-  const double4* p = reinterpret_cast<const double4*>(row_part) + (size_t)t * stride;
+  const double4* p = reinterpret_cast<const double4*>(row_part) + first;
   for (int j = lane; j < tpm; j += 32) {
     const double4 v = p[j];
     c += v.x; su += v.y; sur += v.z; sr += v.w;
@@ -98,14 +103,17 @@ __global__ void __launch_bounds__(256) col_partial_kernel(
   for (int t = t0; t < t1; ++t) {
     const size_t gi = (size_t)t * N + i;
     const float S = sm[t - t0];
-    const float m = mask[gi] ? 1.f : 0.f;
-    const float r = R ? __ldg(R + gi) : 0.f;
-    if (w_out) w_out[gi] = m * (__ldg(u + gi) - sm[tchunk + t - t0]);
-    acc[KM] += (double)(r * m * S);
-    acc[KM + 1] += (double)m;
-    if (g) {
+    // u and g are defined at unmasked cells only (the tensor-core kernels never visit the others)
+    const bool live = mask[gi] != 0;
+    if (w_out) w_out[gi] = live ? (__ldg(u + gi) - sm[tchunk + t - t0]) : 0.f;
+    if (live) {
+      const float r = R ? __ldg(R + gi) : 0.f;
+      acc[KM] += (double)(r * S);
+      acc[KM + 1] += 1.0;
+      if (g) {
 #pragma unroll
-      for (int k = 0; k < KM; ++k) acc[k] += (double)(__ldg(g + k * plane + gi) * S);
+        for (int k = 0; k < KM; ++k) acc[k] += (double)(__ldg(g + k * plane + gi) * S);
+      }
     }
   }
   double* out = col_part + (size_t)blockIdx.y * (KM + 2) * N + i;
@@ -190,7 +198,8 @@ __global__ void __launch_bounds__(256) ds_rows_kernel(
   double acc = 0.0;
   for (int i = i0 + threadIdx.x; i < i1; i += blockDim.x) {
     const size_t gi = (size_t)t * N + i;
-    float v = mask[gi] ? __ldg(G + (size_t)KM * N + i) * __ldg(R + gi) : 0.f;
+    if (!mask[gi]) continue;                         // g is defined at unmasked cells only
+    float v = __ldg(G + (size_t)KM * N + i) * __ldg(R + gi);
     if (g) {
 #pragma unroll
       for (int k = 0; k < KM; ++k) v = fmaf(__ldg(G + (size_t)k * N + i), __ldg(g + k * plane + gi), v);
@@ -204,8 +213,8 @@ __global__ void __launch_bounds__(256) ds_rows_kernel(
 // ---- backward: sum per-CTA / per-tile partials into the reference's gradient layouts ----------------
 __global__ void __launch_bounds__(256) grad_finish_kernel(
     const float* __restrict__ wpart, int ncta, int F, int have_sdf, int have_mom,
-    const float* __restrict__ dadc_part, int T, int tpm /* partial slots per month */, int tpm_tiles,
-    int seg_chunk /* > 0: segment layout of the tensor-core kernel */,
+    const float* __restrict__ dadc_part, int T, int tpm /* partial slots per month */,
+    const int* __restrict__ index /* != null: (month, CTA) segment layout of the tensor-core kernel */,
     float* __restrict__ gW1, int ldw1, float* __restrict__ gW2, float* __restrict__ gb2,
     float* __restrict__ gW3, float* __restrict__ gb3, float* __restrict__ gWq, int ldwq, int wq_off,
     float* __restrict__ dadc) {
@@ -241,8 +250,11 @@ __global__ void __launch_bounds__(256) grad_finish_kernel(
       const int t = r / 72, c = r % 72;
       float v8[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
       const float* p = dadc_part + (size_t)t * tpm * 72 + c;
-      if (seg_chunk > 0)       // only the segments that exist for this month were written
-        tpm = ((t + 1) * tpm_tiles - 1) / seg_chunk - (t * tpm_tiles) / seg_chunk + 1;
+      if (index) {             // one partial per CTA that owns tiles of this month (consecutive CTAs)
+        const int* ts = index + idx_off_ts();
+        const int chunk = tc_chunk(index[0], ncta), a = ts[t], b = ts[t + 1];
+        tpm = b > a ? (b - 1) / chunk - a / chunk + 1 : 0;
+      }
       int j = 0;
       for (; j + 8 <= tpm; j += 8) {
 #pragma unroll
@@ -278,10 +290,10 @@ __global__ void __launch_bounds__(256) weights_kernel(
 }
 
 // ---- launchers ---------------------------------------------------------------------------------------
-cudaError_t launch_row_finish(const double* row_part, int T, int tpm, int tpm_tiles, int seg_chunk, int weighted,
+cudaError_t launch_row_finish(const double* row_part, int T, int tpm, const int* index, int weighted,
                               const float* n_bar_in, float* row_stats, float* pr_out, float* scalars,
                               cudaStream_t st) {
-  row_sum_kernel<<<(T + 7) / 8, 256, 0, st>>>(row_part, T, tpm, tpm_tiles, seg_chunk, row_stats);
+  row_sum_kernel<<<(T + 7) / 8, 256, 0, st>>>(row_part, T, tpm, index, row_stats);
   row_finish_kernel<<<1, T < 1024 ? ((T + 31) / 32) * 32 : 1024, 0, st>>>(T, weighted, n_bar_in, row_stats, pr_out, scalars);
   return cudaGetLastError();
 }
@@ -314,13 +326,13 @@ cudaError_t launch_ds_rows(const float* g, const float* R, const uint8_t* mask, 
   return cudaGetLastError();
 }
 cudaError_t launch_grad_finish(const float* wpart, int ncta, int F, int have_sdf, int have_mom,
-                               const float* dadc_part, int T, int tpm, int tpm_tiles, int seg_chunk, float* gW1,
+                               const float* dadc_part, int T, int tpm, const int* index, float* gW1,
                                int ldw1, float* gW2,
                                float* gb2, float* gW3, float* gb3, float* gWq, int ldwq, int wq_off,
                                float* dadc, cudaStream_t st) {
   const int total = wp_stride(round4(F)) + T * 72;
   grad_finish_kernel<<<(total + 255) / 256, 256, 0, st>>>(wpart, ncta, F, have_sdf, have_mom, dadc_part, T,
-                                                          tpm, tpm_tiles, seg_chunk, gW1, ldw1, gW2, gb2, gW3, gb3, gWq, ldwq,
+                                                          tpm, index, gW1, ldw1, gW2, gb2, gW3, gb3, gWq, ldwq,
                                                           wq_off, dadc);
   return cudaGetLastError();
 }

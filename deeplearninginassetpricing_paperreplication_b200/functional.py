@@ -1,6 +1,6 @@
 """The adversarial-SDF step as one ``torch.autograd.Function`` over the C ABI.
 
-Forward  : macro_fwd -> cell_fwd -> row_finish -> col_partial -> loss_finish
+Forward  : macro_fwd -> [panel_index] -> cell_fwd -> row_finish -> col_partial -> loss_finish
 Backward : loss_coeff -> ds_rows -> cell_bwd -> grad_finish -> macro_bwd
 
 Every stage is a kernel launch through ``libdlap_b200.so`` on torch's current stream; torch is
@@ -16,6 +16,7 @@ per-cell weight gradients; every rank then runs the (tiny, serial) LSTM BPTT red
 from __future__ import annotations
 
 import ctypes as C
+import weakref
 from dataclasses import dataclass
 from typing import Dict, Optional, Tuple
 
@@ -103,6 +104,21 @@ class Workspace:
         self.dpre = f32(p.dpre_bytes)
         self.counter = torch.zeros(1, dtype=torch.int32, device=device)
         self.launches = 0          # kernels launched through this workspace (bench bookkeeping)
+        self._index = None         # (weakref to mask tensor, its version, index) of the last mask seen
+
+    def panel_index(self, mask: torch.Tensor) -> torch.Tensor:
+        """dlap_panel_index for `mask` (tensor-core kernels).  Reused only while the caller passes the very
+        same tensor object with an unchanged version counter (full-batch training loops do); any other
+        mask gets a freshly allocated index, so an index captured for a pending backward is never
+        overwritten."""
+        hit = self._index
+        if hit is not None and hit[0]() is mask and hit[1] == mask._version:
+            return hit[2]
+        index = torch.empty(max(self.plan.index_bytes // 4, 4), dtype=torch.int32, device=self.device)
+        _lib.call("dlap_panel_index", self.pp, _ptr(mask), _ptr(index), _stream(self.device))
+        self.launches += 2
+        self._index = (weakref.ref(mask), mask._version, index)
+        return index
 
 
 _workspaces: Dict[Tuple, Workspace] = {}
@@ -214,15 +230,16 @@ class GanStepFn(torch.autograd.Function):
                 wsm = workspace(sh.T_total, N, F, M, H, dev)
                 save, a_t, c_t, hn, cn = macro_forward(wsm, macro, params, h0, c0)
                 a_loc, c_loc = a_t[sh.t0:sh.t1], c_t[sh.t0:sh.t1]
+            index = ws.panel_index(mask) if opts.precision == "bf16x3" else None
             u = torch.empty(T, N, dtype=torch.float32, device=dev)
             g = torch.empty(KM, T, N, dtype=torch.float32, device=dev) if opts.need_moments else None
-            _timed_call("dlap_cell_fwd", dev, ws.pp, _ptr(x), _ptr(R), _ptr(mask), C.byref(tens), _ptr(a_loc),
+            _timed_call("dlap_cell_fwd", dev, ws.pp, _ptr(x), _ptr(R), _ptr(mask), _ptr(index), C.byref(tens), _ptr(a_loc),
                       _ptr(c_loc), _ptr(u), _ptr(g), _ptr(ws.row_part), prec, float(opts.dropout_p),
                       int(opts.dropout_seed), st)
             row_stats = torch.empty(T, RS_W, dtype=torch.float32, device=dev)
             pr = torch.empty(T, dtype=torch.float32, device=dev)
             scalars = torch.empty(SC_W, dtype=torch.float32, device=dev)
-            _lib.call("dlap_row_finish", ws.pp, _ptr(ws.row_part), prec,
+            _lib.call("dlap_row_finish", ws.pp, _ptr(ws.row_part), _ptr(index), prec,
                       int(opts.weighted_loss),
                       _ptr(sh.n_bar) if sh is not None else None, _ptr(row_stats), _ptr(pr),
                       _ptr(scalars), st)
@@ -242,7 +259,7 @@ class GanStepFn(torch.autograd.Function):
             ws.launches += 5
         ctx.save_for_backward(x, R, mask, macro, h0, c0, *params)
         ctx.opts, ctx.ws = opts, ws
-        ctx.inter = (save, a_t, c_t, row_stats, scalars, g, e, t_i)
+        ctx.inter = (save, a_t, c_t, row_stats, scalars, g, e, t_i, index)
         l_c, l_u, sharpe = scalars[SC_LC], scalars[SC_LU], scalars[SC_SHARPE]
         ctx.mark_non_differentiable(w, sharpe, hn, cn)
         return l_c, l_u, pr, w, sharpe, hn, cn
@@ -250,7 +267,7 @@ class GanStepFn(torch.autograd.Function):
     @staticmethod
     def backward(ctx, g_lc, g_lu, g_pr, *_unused):
         x, R, mask, macro, h0, c0, *params = ctx.saved_tensors
-        save, a_t, c_t, row_stats, scalars, g, e, t_i = ctx.inter
+        save, a_t, c_t, row_stats, scalars, g, e, t_i, index = ctx.inter
         opts, ws = ctx.opts, ctx.ws
         sh = opts.shard
         dev = x.device
@@ -280,7 +297,7 @@ class GanStepFn(torch.autograd.Function):
                 a_loc, c_loc = a_t, c_t
             else:
                 a_loc, c_loc = a_t[sh.t0:sh.t1], c_t[sh.t0:sh.t1]
-            _timed_call("dlap_cell_bwd", dev, ws.pp, _ptr(x), _ptr(R), _ptr(mask), C.byref(tens), _ptr(a_loc),
+            _timed_call("dlap_cell_bwd", dev, ws.pp, _ptr(x), _ptr(R), _ptr(mask), _ptr(index), C.byref(tens), _ptr(a_loc),
                       _ptr(c_loc), _ptr(row_stats), _ptr(ws.ds_part), _ptr(g_pr), _ptr(G), _ptr(scalars),
                       int(opts.weighted_loss), int(want_sdf), int(want_mom), _ptr(ws.wpart),
                       _ptr(ws.dadc_part), prec, float(opts.dropout_p), int(opts.dropout_seed), st)
@@ -293,7 +310,7 @@ class GanStepFn(torch.autograd.Function):
                 off += n
             gt = _tensors(grads)
             dadc = torch.empty(T, 72, dtype=torch.float32, device=dev)
-            _lib.call("dlap_grad_finish", ws.pp, _ptr(ws.wpart), _ptr(ws.dadc_part), prec, int(want_sdf),
+            _lib.call("dlap_grad_finish", ws.pp, _ptr(ws.wpart), _ptr(ws.dadc_part), _ptr(index), prec, int(want_sdf),
                       int(want_mom), C.byref(gt), _ptr(dadc), st)
             ws.launches += 4
             if sh is None:
@@ -332,13 +349,14 @@ def sdf_weights(macro, x, mask, params, h0=None, c0=None, normalized=False, prec
         ws = workspace(T, N, F, M, H, dev)
         tens = _tensors(params)
         save, a_t, c_t, hn, cn = macro_forward(ws, macro, params, h0, c0)
+        index = ws.panel_index(mask) if precision == "bf16x3" else None
         u = torch.empty(T, N, dtype=torch.float32, device=dev)
-        _lib.call("dlap_cell_fwd", ws.pp, _ptr(x), None, _ptr(mask), C.byref(tens), _ptr(a_t), _ptr(c_t),
+        _lib.call("dlap_cell_fwd", ws.pp, _ptr(x), None, _ptr(mask), _ptr(index), C.byref(tens), _ptr(a_t), _ptr(c_t),
                   _ptr(u), None, _ptr(ws.row_part), _PRECISIONS[precision], 0.0, 0, st)
         row_stats = torch.empty(T, RS_W, dtype=torch.float32, device=dev)
         pr = torch.empty(T, dtype=torch.float32, device=dev)
         scalars = torch.empty(SC_W, dtype=torch.float32, device=dev)
-        _lib.call("dlap_row_finish", ws.pp, _ptr(ws.row_part), _PRECISIONS[precision], int(weighted_loss), None,
+        _lib.call("dlap_row_finish", ws.pp, _ptr(ws.row_part), _ptr(index), _PRECISIONS[precision], int(weighted_loss), None,
                   _ptr(row_stats),
                   _ptr(pr), _ptr(scalars), st)
         w = torch.empty(T, N, dtype=torch.float32, device=dev)

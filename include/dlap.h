@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define DLAP_ABI_VERSION 1
+#define DLAP_ABI_VERSION 2
 
 enum {
   DLAP_OK = 0,
@@ -45,8 +45,8 @@ enum {
 enum {
   DLAP_PREC_FP32 = 0,     /* exact fp32 FFMA on CUDA cores */
   DLAP_PREC_BF16X3 = 1    /* tcgen05 BF16 MMAs on hi/lo-split operands, 3 products per fp32 product,
-                             fp32 accumulation in TMEM; needs F <= 46; per-month partials are written
-                             per (month, CTA) segment instead of per tile */
+                             fp32 accumulation in TMEM; needs F <= 46 and the valid-cell index of
+                             dlap_panel_index: only unmasked stock-months are visited */
 };
 
 typedef struct dlap_dims {
@@ -70,6 +70,7 @@ typedef struct dlap_plan {
   int64_t dadc_part_bytes;  /* float  [T, max(tpm,4), 72]   */
   int64_t lstm_save_bytes;  /* float  [T, 6H]               */
   int64_t dpre_bytes;       /* float  [T, 4H]               */
+  int64_t index_bytes;      /* int32  valid-cell index (dlap_panel_index), 16-B aligned */
 } dlap_plan;
 
 /* The twelve parameter tensors in the reference's state_dict order.
@@ -99,15 +100,25 @@ int dlap_macro_fwd(const dlap_plan* plan, const float* macro, const dlap_tensors
                    const float* h0, const float* c0, float* lstm_save, float* a_t, float* c_t,
                    float* hn, float* cn, float* xproj_scratch, void* stream);
 
+/* Valid-cell index of the panel: for every month the ascending list of stocks with mask != 0, cut into
+ * tiles of <= 128 cells (layout: csrc/cell_f32.cuh).  The reference runs both nets over every cell and
+ * multiplies by the mask afterwards (src/model.py:261-279, :363, :376-382, :428), so a masked cell
+ * contributes exactly 0 to every weight, loss and gradient; the BF16X3 kernels use this list to skip
+ * those cells altogether (u and g are then written at unmasked cells only).  Integer work, bit-exact;
+ * the mask contract is src/data_loader.py:50-65.  Rebuild whenever the mask bytes change.  Two launches. */
+int dlap_panel_index(const dlap_plan* plan, const uint8_t* mask, int32_t* index, void* stream);
+
 /* SDFNetwork.forward body on every stock-month (src/model.py:251-271) and MomentNetwork.forward
  * (src/model.py:132-161 with the input of :514-518): u = MLP(x | a_t) [T,N];
  * g = tanh(Wqx.x + c_t) * R * m [8,T,N] (g NULL: moment net skipped, phase 'unconditional');
  * row_part = per-tile sums of m, m u, m u R, m R.  R may be NULL (weights-only inference).
  * dropout_p > 0 (model.train(), src/model.py:213, src/train.py:66): each hidden unit of each
  * stock-month is dropped with probability round(p*65536)/65536 by a counter-based generator keyed
- * on (dropout_seed, stock-month, layer, unit); pass the same seed to dlap_cell_bwd. */
+ * on (dropout_seed, stock-month, layer, unit); pass the same seed to dlap_cell_bwd.
+ * index: dlap_panel_index output, required for BF16X3 (row_part is then per valid-cell tile and u, g are
+ * written at unmasked cells only), ignored (may be NULL) for FP32. */
 int dlap_cell_fwd(const dlap_plan* plan, const float* x, const float* R, const uint8_t* mask,
-                  const dlap_tensors* params, const float* a_t, const float* c_t, float* u,
+                  const int32_t* index, const dlap_tensors* params, const float* a_t, const float* c_t, float* u,
                   float* g, double* row_part, int precision, float dropout_p, uint64_t dropout_seed,
                   void* stream);
 
@@ -115,13 +126,15 @@ int dlap_cell_fwd(const dlap_plan* plan, const float* x, const float* R, const u
  * S_t = 1 + pr_t (src/model.py:359-367, :380), Rbar_t; N_bar (src/model.py:360) and the Sharpe
  * ratio of pr (src/model.py:551) into scalars[3], scalars[2].  n_bar_in (device, 1 float) overrides
  * N_bar when the panel is one month-shard of a larger one; NULL otherwise.  precision: the selector
- * dlap_cell_fwd ran with (it fixes the layout of row_part). */
-int dlap_row_finish(const dlap_plan* plan, const double* row_part, int precision, int weighted_loss,
-                    const float* n_bar_in, float* row_stats, float* pr, float* scalars, void* stream);
+ * and index dlap_cell_fwd ran with (they fix the layout of row_part). */
+int dlap_row_finish(const dlap_plan* plan, const double* row_part, const int32_t* index, int precision,
+                    int weighted_loss, const float* n_bar_in, float* row_stats, float* pr, float* scalars,
+                    void* stream);
 
 /* Per-stock sums over the months of each chunk: sum_t g_k S_t, sum_t R m S_t, sum_t m
  * (src/model.py:376, :382, :428) into col_part [col_splits,10,N]; fused: the demeaned weights
- * w = m (u - mu_t) (src/model.py:271-279) into w_out [T,N] when non-NULL.  g may be NULL. */
+ * w = m (u - mu_t) (src/model.py:271-279) into w_out [T,N] when non-NULL.  g may be NULL.  u and g are
+ * read at unmasked cells only. */
 int dlap_col_partial(const dlap_plan* plan, const float* g, const float* R, const uint8_t* mask,
                      const float* u, const float* row_stats, double* col_part, float* w_out,
                      void* stream);
@@ -161,9 +174,10 @@ int dlap_ds_rows(const dlap_plan* plan, const float* g, const float* R, const ui
 /* Per-cell backward with activation recompute (autograd of src/model.py:261-279
  * and :152-153).  want_sdf / want_mom select the parameter groups (requires_grad semantics of
  * src/train.py:309-312).  dpr_cot [T] = extra cotangent of portfolio_returns or NULL.
- * Outputs: wpart (per-CTA weight-gradient partials), dadc_part (per-tile da_t | dc_t). */
+ * Outputs: wpart (per-CTA weight-gradient partials), dadc_part (per-tile da_t | dc_t).
+ * index: as for dlap_cell_fwd. */
 int dlap_cell_bwd(const dlap_plan* plan, const float* x, const float* R, const uint8_t* mask,
-                  const dlap_tensors* params, const float* a_t, const float* c_t,
+                  const int32_t* index, const dlap_tensors* params, const float* a_t, const float* c_t,
                   const float* row_stats, const double* dS_part, const float* dpr_cot,
                   const float* G, const float* scalars, int weighted_loss, int want_sdf,
                   int want_mom, float* wpart, float* dadc_part, int precision, float dropout_p,
@@ -171,10 +185,11 @@ int dlap_cell_bwd(const dlap_plan* plan, const float* x, const float* R, const u
 
 /* Fixed-order sum of the partials into the reference's gradient layouts: grads->w1[:, :F], w2, b2,
  * w3, b3 (= 0, demeaning), wq[:, M:]; and dadc [T,72] = da_t | dc_t summed over stocks.
- * precision: the selector dlap_cell_bwd ran with (it fixes the layout of dadc_part: one partial per
+ * precision, index: what dlap_cell_bwd ran with (they fix the layout of dadc_part: one partial per
  * tile for FP32, one per (month, CTA) segment for BF16X3). */
-int dlap_grad_finish(const dlap_plan* plan, const float* wpart, const float* dadc_part, int precision,
-                     int want_sdf, int want_mom, const dlap_tensors* grads, float* dadc, void* stream);
+int dlap_grad_finish(const dlap_plan* plan, const float* wpart, const float* dadc_part, const int32_t* index,
+                     int precision, int want_sdf, int want_mom, const dlap_tensors* grads, float* dadc,
+                     void* stream);
 
 /* Month-level backward: dh_t = W1[:,F:]^T da_t, LSTM BPTT, and the month-summed gradients
  * grads->{w_ih,w_hh,b_ih,b_hh}, w1[:, F:], b1, wq[:, :M], bq.  dpre [T,4H] is scratch. */
@@ -187,10 +202,11 @@ int dlap_macro_bwd(const dlap_plan* plan, const float* macro, const dlap_tensors
 int dlap_weights(const dlap_plan* plan, const float* u, const uint8_t* mask, const float* row_stats,
                  int normalized, float* w_out, void* stream);
 
-/* Diagnostics (no counterpart in the reference): when `stamps` is a device buffer of 256*16 int64, every
- * following tensor-core dlap_cell_bwd launch makes CTA 0 record clock64() at fixed points of each of its
- * first 256 tiles (slots 0-5: epilogue warp, 8-12: MMA warp; see csrc/cell_bwd_tc.cu).  NULL switches it
- * off.  scripts/bwd_timeline.py turns the stamps into per-phase cycle counts. */
+/* Diagnostics (no counterpart in the reference): when `stamps` is a device buffer of 2*256*16 int64, every
+ * following tensor-core dlap_cell_bwd (first half of the buffer) and dlap_cell_fwd (second half) launch makes
+ * CTA 0 record clock64() at fixed points of each of its first 256 tiles (see the DLAP_STAMP sites in
+ * csrc/cell_bwd_tc.cu, csrc/cell_fwd_tc.cu).  NULL switches it off.  scripts/bwd_timeline.py turns the stamps
+ * into per-phase cycle counts. */
 int dlap_debug_timeline(long long* stamps);
 
 /* Hardware self-test of the tensor-core plumbing (no counterpart in the reference): one CTA computes

@@ -122,7 +122,7 @@ def test_forward_stages_rand_small():
     assert np.abs(_np(c_t) - s["c"]).max() < 2e-5
     tens = Fn._tensors(kp)
     u = torch.empty(T, N, device=dev()); gq = torch.empty(8, T, N, device=dev())
-    _lib.call("dlap_cell_fwd", ws.pp, x.data_ptr(), R.data_ptr(), mask.data_ptr(), C.byref(tens),
+    _lib.call("dlap_cell_fwd", ws.pp, x.data_ptr(), R.data_ptr(), mask.data_ptr(), None, C.byref(tens),
               a_t.data_ptr(), c_t.data_ptr(), u.data_ptr(), gq.data_ptr(), ws.row_part.data_ptr(), 0, 0.0, 0,
               None)
     torch.cuda.synchronize()
@@ -134,6 +134,69 @@ def test_forward_stages_rand_small():
     assert np.array_equal(rp[:, 0], m.sum(axis=1))          # counts are exact integers
     assert np.abs(rp[:, 1] - (m * s["u"]).sum(axis=1)).max() < 1e-4
     assert np.abs(rp[:, 3] - s["rm"].sum(axis=1)).max() < 1e-6
+
+
+def _index_layout(T, N):
+    off_ts, off_cnt = 4, 4 + T + 1
+    off_vidx = (4 + 2 * T + 1 + 3) & ~3
+    return off_ts, off_cnt, off_vidx
+
+
+@pytest.mark.parametrize("shape,density", [((7, 1000), 0.4), ((5, 130), 0.0), ((3, 257), 1.0), ((240, 3000), 0.35),
+                                           ((2, 1), 0.5), ((1100, 40), 0.5)])
+def test_panel_index_bit_exact(shape, density):
+    """dlap_panel_index against numpy: counts, tile prefix and the ascending stock lists, bit for bit."""
+    T, N = shape
+    rng = np.random.default_rng(T * 1000 + N)
+    mask = rng.random((T, N)) < density
+    if T > 2 and 0.0 < density < 1.0:
+        mask[1] = False                              # an empty month in the middle
+    ws = Fn.workspace(T, N, 46, 0, 0, dev())
+    idx = _np(ws.panel_index(torch.from_numpy(mask).to(dev())))
+    off_ts, off_cnt, off_vidx = _index_layout(T, N)
+    cnt = mask.sum(axis=1)
+    tiles = (cnt + 127) // 128
+    ts = np.concatenate([[0], np.cumsum(tiles)])
+    assert idx[0] == ts[-1]
+    assert np.array_equal(idx[off_ts:off_ts + T + 1], ts)
+    assert np.array_equal(idx[off_cnt:off_cnt + T], cnt)
+    vidx = idx[off_vidx:off_vidx + T * N].reshape(T, N)
+    for t in range(T):
+        assert np.array_equal(vidx[t, :cnt[t]], np.nonzero(mask[t])[0])
+
+
+def test_forward_stages_tensor_core_visits_only_unmasked_cells():
+    """BF16X3 forward through the raw ABI: u and g are written at unmasked cells only (poisoned buffers keep
+    their poison elsewhere), and the row partials of the valid-cell tiles add up to the oracle's row sums."""
+    g = load_golden("rand_small")
+    params = golden_params(g)
+    model = _model_from(params, 178).eval()
+    macro, x, R, mask, _ = _panel(g)
+    T, N, F = x.shape
+    s = cf.forward(params, g["macro"], g["x"], g["R"], g["mask"])["_saved"]
+    kp = [p.detach() for p in model._kernel_params(True)]
+    ws = Fn.workspace(T, N, F, 178, 4, dev())
+    save, a_t, c_t, hn, cn = Fn.macro_forward(ws, macro, kp, None, None)
+    tens = Fn._tensors(kp)
+    index = ws.panel_index(mask)
+    u = torch.full((T, N), float("nan"), device=dev()); gq = torch.full((8, T, N), float("nan"), device=dev())
+    _lib.call("dlap_cell_fwd", ws.pp, x.data_ptr(), R.data_ptr(), mask.data_ptr(), index.data_ptr(), C.byref(tens),
+              a_t.data_ptr(), c_t.data_ptr(), u.data_ptr(), gq.data_ptr(), ws.row_part.data_ptr(), 1, 0.0, 0,
+              None)
+    torch.cuda.synchronize()
+    m = g["mask"]
+    un, gn = _np(u), _np(gq)
+    assert np.isnan(un[~m]).all() and np.isnan(gn[:, ~m]).all()
+    assert np.abs(un[m] - s["u"][m]).max() < 1e-5 * max(1.0, np.abs(s["u"]).max())
+    gref = np.transpose(s["q"], (2, 0, 1)) * s["rm"][None]
+    assert np.abs(gn[:, m] - gref[:, m]).max() < 2e-6
+    ntiles = int(index[0])
+    ts = _np(index)[4:4 + T + 1]
+    rp = _np(ws.row_part)[: ntiles * 16].reshape(ntiles, 4, 4).sum(axis=1)
+    rows = np.stack([rp[ts[t]:ts[t + 1]].sum(axis=0) for t in range(T)])
+    assert np.array_equal(rows[:, 0], s["m"].sum(axis=1))
+    assert np.abs(rows[:, 1] - (s["m"] * s["u"]).sum(axis=1)).max() < 1e-4
+    assert np.abs(rows[:, 3] - s["rm"].sum(axis=1)).max() < 1e-6
 
 
 # ---- full step against the reference's own outputs ---------------------------------------------------
