@@ -45,6 +45,7 @@ static int check_dims(const dlap_dims& d) {
   if (d.T < 1 || d.N < 1 || d.F < 1 || d.F > FMAX) return DLAP_E_SHAPE;
   if (d.M < 0 || (d.M > 0 && (d.H < 1 || d.H > HMAX))) return DLAP_E_SHAPE;
   if ((long long)d.T * d.N >= (1ll << 40)) return DLAP_E_SHAPE;
+  if ((long long)d.N * d.F * 4 >= (1ll << 32)) return DLAP_E_SHAPE;   // byte offsets inside a month are 32-bit
   return DLAP_OK;
 }
 

@@ -30,7 +30,7 @@ using namespace tcl;
 namespace {
 constexpr int NT_B = 640;
 constexpr int NEPI = 16;                               // epilogue warps
-constexpr int STAGE_BYTES = TILE * ROW_PITCH * 4;        // one 208-B slot per gathered characteristic row
+constexpr int STAGE_BYTES = TILE * ROW_PITCH * 4;        // 2 x 32 row slots (208 B) for each of the two gather warps
 constexpr uint32_t DPS_IMG = TILE * 16;                // one group: [cell][8 moments]
 
 struct SmemB {
@@ -233,66 +233,108 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
     if (tc::elect_one()) tc::umma_commit(bar + B_ALL_DONE);
     __syncwarp();
   } else if (warp == 2 || warp == 3) {
-    // ===== gather + convert: this warp owns rows 64w .. 64w+63 of every tile, as two shares of 32; lane = cell =====
-    const int c0 = (warp - 2) * 64 + lane;                           // cells c0 and c0 + 32
-    float* stage = s.stage() + (warp - 2) * 64 * ROW_PITCH;          // private to this warp
+    // ===== gather + convert: this warp owns rows 64w .. 64w+63 of every tile, handled as a stream of shares of
+    // 32 rows (share k = tile k/2, half k%2); lane = cell.  Only 16 rows (32 registers) are in flight at a time
+    // -- the kernel runs at 96 registers per thread -- so a share arrives as two half-shares A and B, each
+    // overlapped with one half of the conversion of the previous share; two staging areas alternate.
+    const int c0 = (warp - 2) * 64 + lane;
+    float* stage = s.stage() + (warp - 2) * 64 * ROW_PITCH;          // 2 x 32 slots, private to this warp
+    const int nshare = 2 * my_tiles;
     MonthCursor mc;
     if (my_tiles > 0) mc.init(P, tile_lo);
-    int n_nxt[2] = {-1, -1}, t_nxt = 0;
-    auto load_n = [&](int tile) {
+    int t_seek = 0;
+    // where this lane's stock number of share k lives (cells past the end of the tile repeat its last row);
+    // moves the month cursor, whose rare loads are consumed right here
+    auto n_addr = [&](int k) {
+      const int tile = tile_lo + (k >> 1), cell = c0 + 32 * (k & 1);
       mc.seek(P, tile);
-      t_nxt = mc.t;
-      const int* vr = vidx_row(P, mc.t) + mc.j0(tile);
-      const int nc = mc.ncell(tile);
-#pragma unroll
-      for (int sh = 0; sh < 2; ++sh) n_nxt[sh] = (c0 + 32 * sh < nc) ? __ldg(vr + c0 + 32 * sh) : -1;
+      t_seek = mc.t;
+      return vidx_row(P, mc.t) + mc.j0(tile) + min(cell, mc.ncell(tile) - 1);
     };
-    if (my_tiles > 0) load_n(tile_lo);
-    for (int i = 0; i < my_tiles; ++i) {
-      const int sl = i & 1, use = i >> 1;
-      const int n2[2] = {n_nxt[0], n_nxt[1]}, t = t_nxt;
-      if (i + 1 < my_tiles) load_n(tile_lo + i + 1);
+    auto load_bias = [&](int t, int cell) {        // per-month bias column (k = 46) of the W1 image, cells 0..79
+      float b = 0.f;
+      if (cell < 64) b = __ldg(P.a_t + (size_t)t * 64 + cell);
+      else if (cell < 72) b = __ldg(P.c_t + (size_t)t * 8 + cell - 64);
+      return b;
+    };
+    // groups g0 .. g0+2 of this lane's row of share k -> X image
+    auto convert = [&](int k, int g0) {
+      const int sl = (k >> 1) & 1, cell = c0 + 32 * (k & 1);
+      const float* slot = stage + ((k & 1) * 32 + lane) * ROW_PITCH;
 #pragma unroll
-      for (int sh = 0; sh < 2; ++sh) {
-        float2 ra[16], rb[16];
-        gather_load<16>(P, t, n2[sh], 0, lane, ra);
-        gather_load<16>(P, t, n2[sh], 16, lane, rb);
-        gather_store<16>(P, stage + sh * 32 * ROW_PITCH, 0, lane, ra);
-        gather_store<16>(P, stage + sh * 32 * ROW_PITCH, 16, lane, rb);
+      for (int g = g0; g < g0 + 3; ++g) {
+        float v[8];
+        row_group(slot, g, v);                       // floats >= F are zero in the slot
+        if (g == KG1 - 1) v[ONES_K - 8 * (KG1 - 1)] = 1.f;
+        uint4 hi, lo;
+        tc::split8(v, hi, lo);
+        *reinterpret_cast<uint4*>(s.xh(sl) + (g * TILE + cell) * 16) = hi;
+        *reinterpret_cast<uint4*>(s.xl(sl) + (g * TILE + cell) * 16) = lo;
       }
+    };
+    float2 rows[16];
+    int n_a = 0, t_a = 0;                          // share k+1 (its half B is loaded in iteration k)
+    int n_b = 0, t_b = 0;                          // share k+2 (half A loaded at the end of iteration k)
+    int n_c = 0, t_c = 0;                          // share k+3 (stock numbers loaded during iteration k)
+    float b_cur = 0.f, b_nxt = 0.f;
+    for (int i = lane; i < 64 * ROW_PITCH; i += 32) stage[i] = 0.f;   // floats >= F of every slot stay zero
+    __syncwarp();
+    if (nshare > 0) {                              // share 0 completely, half A of share 1
+      n_c = __ldg(n_addr(0)); t_c = t_seek;
+      n_a = __ldg(n_addr(1)); t_a = t_seek;
+      if (nshare > 2) { n_b = __ldg(n_addr(2)); t_b = t_seek; }
+      b_cur = load_bias(t_c, c0);
+      b_nxt = load_bias(t_a, c0 + 32);
+      gather_load<16>(P, t_c, n_c, 0, lane, rows);
+      gather_store<16>(P, stage, 0, lane, rows);
+      gather_load<16>(P, t_c, n_c, 16, lane, rows);
+      gather_store<16>(P, stage, 16, lane, rows);
+      if (nshare > 2) prefetch_row(P, t_b, n_b);
+      gather_load<16>(P, t_a, n_a, 0, lane, rows);
       __syncwarp();
-      mbar_wait(bar + B_XOP_EMPTY + sl, (use & 1) ^ 1);
-#pragma unroll
-      for (int sh = 0; sh < 2; ++sh) {
-        const int cell = c0 + 32 * sh;
-        const bool live = n2[sh] >= 0;
-        const float* slot = stage + (sh * 32 + lane) * ROW_PITCH;
-#pragma unroll
-        for (int g = 0; g < KG1; ++g) {
-          float v[8];
-          row_group(slot, g, v);
-#pragma unroll
-          for (int e = 0; e < 8; ++e) v[e] = (live && g * 8 + e < P.F) ? v[e] : 0.f;
-          if (g == KG1 - 1) v[ONES_K - 8 * (KG1 - 1)] = 1.f;
-          uint4 hi, lo;
-          tc::split8(v, hi, lo);
-          *reinterpret_cast<uint4*>(s.xh(sl) + (g * TILE + cell) * 16) = hi;
-          *reinterpret_cast<uint4*>(s.xl(sl) + (g * TILE + cell) * 16) = lo;
-        }
-        if (cell < N1) {                             // per-month bias column (k = 46) of this slot's W1
-          float b = 0.f;
-          if (cell < 64) b = __ldg(P.a_t + (size_t)t * 64 + cell);
-          else if (cell < 72) b = __ldg(P.c_t + (size_t)t * 8 + cell - 64);
-          const __nv_bfloat16 bh = __float2bfloat16_rn(b);
-          const __nv_bfloat16 bl = __float2bfloat16_rn(b - __bfloat162float(bh));
-          const int off = ((KG1 - 1) * N1 + cell) * 16 + (ONES_K - 8 * (KG1 - 1)) * 2;
-          *reinterpret_cast<__nv_bfloat16*>(s.w1h(sl) + off) = bh;
-          *reinterpret_cast<__nv_bfloat16*>(s.w1l(sl) + off) = bl;
-        }
+    }
+    // Loop order as in the forward kernel (cell_fwd_tc.cu): every consumer of a long-latency load comes before
+    // the next batch of row loads is issued (a wait placed after them shares a scoreboard with the batch).
+    for (int k = 0; k < nshare; ++k) {
+      // here: share k sits in staging area k&1; registers hold half A of share k+1
+      const int i = k >> 1, sh = k & 1, sl = i & 1, use = i >> 1;
+      const int cell = c0 + 32 * sh;
+      const bool more = k + 1 < nshare;
+      float* area_nxt = stage + ((k + 1) & 1) * 32 * ROW_PITCH;
+      const __nv_bfloat16 bh = __float2bfloat16_rn(b_cur);           // bias of share k
+      const __nv_bfloat16 bl = __float2bfloat16_rn(b_cur - __bfloat162float(bh));
+      b_cur = b_nxt;
+      const bool stamp = warp == 2 && lane == 0;
+      if (stamp) DLAP_STAMP(k, 6);
+      if (sh == 0) mbar_wait(bar + B_XOP_EMPTY + sl, (use & 1) ^ 1);
+      if (stamp) DLAP_STAMP(k, 7);
+      convert(k, 0);
+      if (stamp) DLAP_STAMP(k, 13);
+      if (more) {
+        const int* pn = (k + 3 < nshare) ? n_addr(k + 3) : nullptr;
+        if (k + 2 < nshare) b_nxt = load_bias(t_b, c0 + 32 * sh);    // share k+2 has the parity of share k
+        gather_store<16>(P, area_nxt, 0, lane, rows);                // half A of share k+1
+        gather_load<16>(P, t_a, n_a, 16, lane, rows);                // half B of share k+1
+        if (pn) { n_c = __ldg(pn); t_c = t_seek; }
+      }
+      if (stamp) DLAP_STAMP(k, 14);
+      convert(k, 3);
+      if (cell < N1) {
+        const int off = ((KG1 - 1) * N1 + cell) * 16 + (ONES_K - 8 * (KG1 - 1)) * 2;
+        *reinterpret_cast<__nv_bfloat16*>(s.w1h(sl) + off) = bh;
+        *reinterpret_cast<__nv_bfloat16*>(s.w1l(sl) + off) = bl;
       }
       fence_proxy_async();
-      __syncwarp();                                  // also: every lane is done with the staging slots
-      if (lane == 0) mbar_arrive(bar + B_XOP_FULL + sl);
+      __syncwarp();
+      if (sh == 1 && lane == 0) mbar_arrive(bar + B_XOP_FULL + sl);
+      if (stamp) DLAP_STAMP(k, 15);
+      if (more) {
+        gather_store<16>(P, area_nxt, 16, lane, rows);               // half B of share k+1
+        n_a = n_b; t_a = t_b; n_b = n_c; t_b = t_c;                  // n_a: share k+2, n_b: share k+3
+        if (k + 3 < nshare) prefetch_row(P, t_b, n_b);               // share k+3 -> L2, loaded one iteration later
+        if (k + 2 < nshare) gather_load<16>(P, t_a, n_a, 0, lane, rows);   // half A of share k+2
+        __syncwarp();
+      }
     }
   } else if (warp >= 4 && warp < 20) {
     // ===== epilogue: thread = (cell, 16 of the hidden units) =====

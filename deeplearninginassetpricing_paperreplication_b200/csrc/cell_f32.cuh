@@ -103,37 +103,50 @@ struct MonthCursor {
 // A gathered tile sits in the staging buffer as one 208-B slot per characteristic row (row at the slot start).
 constexpr int ROW_PITCH = 52;           // floats; 13 x 16 B: LDS.128 over consecutive rows is conflict-free
 
-// Gather by one warp.  Lane l knows the stock number of row l of the warp's share (n_lane, -1 = no row).
+// Gather by one warp.  Lane l knows the stock number of row l of the warp's share (n_lane; a cell past the
+// end of the tile repeats the tile's last row, so the images only ever hold real, finite panel rows).
 // Row j is fetched by ONE coalesced warp-wide load (lane k takes floats 2k, 2k+1; when x or F do not allow
 // 8-byte loads: floats k and k+32), so ROWS independent loads are in flight per warp -- scattered 184-B rows
 // need that memory-level parallelism; per-row TMA bulk copies and cp.async both serialise on a short queue
 // (measured: 78 and 190 cycles per row).
-// The loads are unconditional on clamped addresses (a missing row reads the month's first row, lanes past
-// the row re-read its last element; the converter zeroes what does not exist): a predicated load followed by
-// a select makes ptxas wait for each load before issuing the next one.
+// The loads are unconditional (cells past the end of a tile carry the number of the tile's last row, lanes
+// past the row re-read its last element): a predicated load followed by a select makes ptxas wait for each
+// load before issuing the next one.  Addresses are a 64-bit base plus a 32-bit byte offset (one IMAD.WIDE).
 template <int ROWS>
 __device__ __forceinline__ void gather_load(const CellParams& P, int t, int n_lane, int row0, int lane,
                                             float2 (&r)[ROWS]) {
   const bool wide = ((P.F & 1) == 0) && ((reinterpret_cast<uintptr_t>(P.x) & 7) == 0);
-  const float* xt = P.x + (size_t)t * P.N * P.F;
+  const char* xt = reinterpret_cast<const char*>(P.x + (size_t)t * P.N * P.F);
+  const uint32_t pitch = (uint32_t)P.F * 4u;                 // N * F * 4 < 2^32 (checked by dlap_make_plan)
   if (wide) {
-    const int k = min(lane, (P.F >> 1) - 1);
+    const char* base = xt + 8 * min(lane, (P.F >> 1) - 1);
 #pragma unroll
     for (int j = 0; j < ROWS; ++j) {
-      const int nr = max(__shfl_sync(0xffffffffu, n_lane, row0 + j), 0);
-      r[j] = __ldg(reinterpret_cast<const float2*>(xt + (size_t)nr * P.F) + k);
+      const uint32_t nr = (uint32_t)__shfl_sync(0xffffffffu, n_lane, row0 + j);
+      r[j] = __ldg(reinterpret_cast<const float2*>(base + nr * pitch));
     }
   } else {
-    const int k0 = min(lane, P.F - 1), k1 = min(lane + 32, P.F - 1);
+    const char* b0 = xt + 4 * min(lane, P.F - 1);
+    const char* b1 = xt + 4 * min(lane + 32, P.F - 1);
 #pragma unroll
     for (int j = 0; j < ROWS; ++j) {
-      const int nr = max(__shfl_sync(0xffffffffu, n_lane, row0 + j), 0);
-      const float* src = xt + (size_t)nr * P.F;
-      r[j].x = __ldg(src + k0);
-      r[j].y = __ldg(src + k1);
+      const uint32_t nr = (uint32_t)__shfl_sync(0xffffffffu, n_lane, row0 + j);
+      r[j].x = __ldg(reinterpret_cast<const float*>(b0 + nr * pitch));
+      r[j].y = __ldg(reinterpret_cast<const float*>(b1 + nr * pitch));
     }
   }
 }
+// L2 prefetch of this lane's own row (stock n of month t), issued two tiles ahead of its gather_load so that
+// the loads find the row in L2 instead of paying the HBM latency of a scattered 184-B read
+__device__ __forceinline__ void prefetch_row(const CellParams& P, int t, int n) {
+  const char* a = reinterpret_cast<const char*>(P.x + ((size_t)t * P.N + n) * P.F);
+  const int bytes = P.F * 4;
+  asm volatile("prefetch.global.L2 [%0];" ::"l"(a));
+  if (bytes > 64) asm volatile("prefetch.global.L2 [%0];" ::"l"(a + 64));
+  if (bytes > 128) asm volatile("prefetch.global.L2 [%0];" ::"l"(a + 128));
+  asm volatile("prefetch.global.L2 [%0];" ::"l"(a + bytes - 4));
+}
+
 // rows row0 .. row0+ROWS-1 of the warp's share -> its staging slots
 template <int ROWS>
 __device__ __forceinline__ void gather_store(const CellParams& P, float* stage_warp, int row0, int lane,

@@ -135,33 +135,55 @@ __global__ void __launch_bounds__(NT_TC, 1) cell_fwd_tc_kernel(const CellParams 
     float* stage = s.stage() + (warp - 4) * 32 * ROW_PITCH;          // private to this warp
     MonthCursor mc;
     if (my_tiles > 0) mc.init(P, tile_lo);
-    int n_nxt = -1, t_nxt = 0;
-    auto load_n = [&](int tile) {
+    int n_nxt = 0, t_nxt = 0;                      // tile i+1: rows loaded next
+    int n_pf = 0, t_pf = 0, t_seek = 0;            // tile i+2: rows prefetched to L2 now, loaded one tile later
+    // where this lane's stock number of `tile` lives (cells past the end of the tile repeat its last row);
+    // moves the month cursor, whose rare loads are consumed right here
+    auto n_addr = [&](int tile) {
       mc.seek(P, tile);
-      t_nxt = mc.t;
-      n_nxt = (cell < mc.ncell(tile)) ? __ldg(vidx_row(P, mc.t) + mc.j0(tile) + cell) : -1;
+      t_seek = mc.t;
+      return vidx_row(P, mc.t) + mc.j0(tile) + min(cell, mc.ncell(tile) - 1);
+    };
+    // bias column k = 46 of the W1 image: a_t (units 0..63) | c_t (moments) of the tile's month, by cells 0..79
+    auto load_bias = [&](int t) {
+      float b = 0.f;
+      if (cell < 64) b = __ldg(P.a_t + (size_t)t * 64 + cell);
+      else if (cell < 72 && MOM) b = __ldg(P.c_t + (size_t)t * 8 + cell - 64);
+      return b;
     };
     float2 rows[32];
-    int n = -1, t = 0;
+    float b_nxt = 0.f;
+    for (int i = lane; i < 32 * ROW_PITCH; i += 32) stage[i] = 0.f;   // floats >= F of every slot stay zero
+    __syncwarp();
     if (my_tiles > 0) {
-      load_n(tile_lo);
-      n = n_nxt; t = t_nxt;
-      gather_load<32>(P, t, n, 0, lane, rows);
-      if (my_tiles > 1) load_n(tile_lo + 1);
+      n_nxt = __ldg(n_addr(tile_lo)); t_nxt = t_seek;
+      b_nxt = load_bias(t_nxt);
+      gather_load<32>(P, t_nxt, n_nxt, 0, lane, rows);
+      if (my_tiles > 1) { n_nxt = __ldg(n_addr(tile_lo + 1)); t_nxt = t_seek; prefetch_row(P, t_nxt, n_nxt); }
+      if (my_tiles > 2) { n_pf = __ldg(n_addr(tile_lo + 2)); t_pf = t_seek; }
     }
+    // Loop order matters.  ptxas tracks loads with six scoreboards per warp, so a wait placed after the 32 row
+    // loads of the next tile shares a scoreboard with them and stalls for the whole gather: every consumer of a
+    // long-latency load (month cursor, bias, stock numbers) therefore sits BEFORE the row loads are issued.  The
+    // stock-number load for tile i+2 is issued AFTER them, once the old value is dead, so that it can land in
+    // the loop-carried register itself (otherwise a register copy at the loop end waits for it).  Stock numbers
+    // run two tiles ahead of the row loads: the rows of tile i+2 are prefetched to L2 while tile i+1 is loaded.
     for (int i = 0; i < my_tiles; ++i) {
       const int sl = i & 1, use = i >> 1;
-      const bool live = n >= 0;
-      const int t_now = t;
       const bool stamp = warp == 4 && lane == 0;
       if (stamp) DLAP_STAMP(i, 0);
       gather_store<32>(P, stage, 0, lane, rows);                     // rows of tile i (loaded one tile ago)
       __syncwarp();
       if (stamp) DLAP_STAMP(i, 1);
+      const __nv_bfloat16 bh = __float2bfloat16_rn(b_nxt);           // bias of tile i (loaded one tile ago)
+      const __nv_bfloat16 bl = __float2bfloat16_rn(b_nxt - __bfloat162float(bh));
       if (i + 1 < my_tiles) {                                        // rows of tile i+1 fly during the conversion
-        n = n_nxt; t = t_nxt;
-        gather_load<32>(P, t, n, 0, lane, rows);
-        if (i + 2 < my_tiles) load_n(tile_lo + i + 2);
+        const int* pn = (i + 3 < my_tiles) ? n_addr(tile_lo + i + 3) : nullptr;
+        b_nxt = load_bias(t_nxt);
+        gather_load<32>(P, t_nxt, n_nxt, 0, lane, rows);
+        if (i + 2 < my_tiles) prefetch_row(P, t_pf, n_pf);
+        n_nxt = n_pf; t_nxt = t_pf;
+        if (pn) { n_pf = __ldg(pn); t_pf = t_seek; }
       }
       if (stamp) DLAP_STAMP(i, 2);
       mbar_wait(bar + F_XOP_EMPTY + sl, (use & 1) ^ 1);
@@ -170,21 +192,14 @@ __global__ void __launch_bounds__(NT_TC, 1) cell_fwd_tc_kernel(const CellParams 
 #pragma unroll
       for (int g = 0; g < KG1; ++g) {
         float v[8];
-        row_group(slot, g, v);
-#pragma unroll
-        for (int e = 0; e < 8; ++e) v[e] = (live && g * 8 + e < P.F) ? v[e] : 0.f;
+        row_group(slot, g, v);                       // floats >= F are zero in the slot
         if (g == KG1 - 1) v[ONES_K - 8 * (KG1 - 1)] = 1.f;
         uint4 hi, lo;
         tc::split8(v, hi, lo);
         *reinterpret_cast<uint4*>(s.xh(sl) + (g * TILE + cell) * 16) = hi;
         *reinterpret_cast<uint4*>(s.xl(sl) + (g * TILE + cell) * 16) = lo;
       }
-      if (cell < N1) {                               // bias column k = 46 of this slot's W1 image
-        float b = 0.f;
-        if (cell < 64) b = __ldg(P.a_t + (size_t)t_now * 64 + cell);
-        else if (cell < 72 && MOM) b = __ldg(P.c_t + (size_t)t_now * 8 + cell - 64);
-        const __nv_bfloat16 bh = __float2bfloat16_rn(b);
-        const __nv_bfloat16 bl = __float2bfloat16_rn(b - __bfloat162float(bh));
+      if (cell < N1) {
         const int off = ((KG1 - 1) * N1 + cell) * 16 + (ONES_K - 8 * (KG1 - 1)) * 2;
         *reinterpret_cast<__nv_bfloat16*>(s.w1h(sl) + off) = bh;
         *reinterpret_cast<__nv_bfloat16*>(s.w1l(sl) + off) = bl;

@@ -31,6 +31,12 @@ print("epilogue: wait D2_FULL", d(0, 1), "| E2 body", d(1, 2), "| E1(i+1) incl. 
 print("MMA: wait DZ2_FULL -> issued WG2+DG", d(8, 9), "| L2(i+1) incl. wait h1", d(9, 10), "| wait DZ1_FULL", d(10, 11),
       "| WG1 + L1(i+2) issue", d(11, 12), "| next wait DZ2_FULL", d(12, 8, 1))
 
+def gd(a, b, shift=0):
+    idx = torch.arange(10, 2 * ntile - 12)
+    return float((s[idx + shift, b] - s[idx, a]).mean())
+print("BWD gather warp per 32-row share: period", gd(6, 6, 1), "| wait XOP_EMPTY", gd(6, 7), "| convert groups 0-2", gd(7, 13),
+      "| STS A + issue B loads", gd(13, 14), "| convert groups 3-5 + arrive", gd(14, 15), "| STS B + prefetch + issue A loads", gd(15, 6, 1))
+
 
 def fd(a, b, shift=0, step=1):
     idx = torch.arange(lo, hi - 2, step)

@@ -97,6 +97,55 @@ __global__ void __launch_bounds__(1024, 1) tma_rows_kernel(const float* __restri
   if (acc == 123.456f) out[0] = acc;
 }
 
+// same, but ONE lane per warp issues the 32 copies of a batch from indices it loads itself (no per-lane
+// issue loop around the uniform-datapath copy instruction)
+__global__ void __launch_bounds__(1024, 1) tma_rows1_kernel(const float* __restrict__ x, const int* __restrict__ rows, int nrows,
+                                                            int F, float* __restrict__ out) {
+  extern __shared__ __align__(128) unsigned char sm[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
+  unsigned long long* bars = reinterpret_cast<unsigned long long*>(sm);
+  float* stage = reinterpret_cast<float*>(sm + 1024) + (size_t)warp * 2 * 32 * 52;
+  if (lane == 0) for (int s = 0; s < 2; ++s)
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(bars + warp * 2 + s)));
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  __syncthreads();
+  const long long per = (nrows + gridDim.x - 1) / gridDim.x;
+  const long long lo = (long long)blockIdx.x * per, hi = min((long long)nrows, lo + per);
+  float acc = 0.f;
+  int it = 0;
+  for (long long r0 = lo + warp * 32; r0 < hi + (long long)nw * 32; r0 += (long long)nw * 32, ++it) {
+    if (r0 < hi) {
+      const int st = it & 1;
+      if (lane == 0) {
+        const int cnt = (int)min((long long)32, hi - r0);
+        const unsigned bar = smem_u32(bars + warp * 2 + st);
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(cnt * 192u) : "memory");
+        int n[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) n[j] = (j < cnt) ? rows[r0 + j] : -1;
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          if (n[j] >= 0) {
+            const uintptr_t a = reinterpret_cast<uintptr_t>(x + (size_t)n[j] * F) & ~uintptr_t(15);
+            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::
+                         "r"(smem_u32(stage + (st * 32 + j) * 52)), "l"(a), "r"(192u), "r"(bar) : "memory");
+          }
+        }
+      }
+      __syncwarp();
+    }
+    if (it > 0) {
+      const int st = (it - 1) & 1, par = ((it - 1) >> 1) & 1;
+      asm volatile("{\n.reg .pred p;\nW_%=:\nmbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n@p bra D_%=;\nbra W_%=;\nD_%=:\n}\n" ::
+                   "r"(smem_u32(bars + warp * 2 + st)), "r"(par) : "memory");
+      acc += stage[(st * 32 + lane) * 52 + 3];
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+      __syncwarp();
+    }
+  }
+  if (acc == 123.456f) out[0] = acc;
+}
+
 int main() {
   const int T = 240, N = 10000, F = 46;
   const size_t cells = (size_t)T * N;
@@ -128,6 +177,14 @@ int main() {
           cudaEventRecord(e1); CK(cudaEventSynchronize(e1));
           float ms; cudaEventElapsedTime(&ms, e0, e1); ms /= 5;
           printf("density %.1f warps %2d TMA rows (2 stages x 32 rows per warp): %.3f ms  %.0f GB/s useful\n", dens, warps, ms,
+                 rows.size() * 184.0 / ms / 1e6);
+          CK(cudaFuncSetAttribute(tma_rows1_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smb));
+          for (int it = 0; it < 3; ++it) tma_rows1_kernel<<<148, warps * 32, smb>>>(x, d, (int)rows.size(), F, out);
+          cudaEventRecord(e0);
+          for (int it = 0; it < 5; ++it) tma_rows1_kernel<<<148, warps * 32, smb>>>(x, d, (int)rows.size(), F, out);
+          cudaEventRecord(e1); CK(cudaEventSynchronize(e1));
+          cudaEventElapsedTime(&ms, e0, e1); ms /= 5;
+          printf("density %.1f warps %2d TMA rows, one issuing lane per warp:     %.3f ms  %.0f GB/s useful\n", dens, warps, ms,
                  rows.size() * 184.0 / ms / 1e6);
         }
       }
