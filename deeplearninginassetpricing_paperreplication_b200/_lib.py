@@ -15,7 +15,7 @@ import threading
 PKG_DIR = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(PKG_DIR)
 CSRC = os.path.join(PKG_DIR, "csrc")
-LIB_PATH = os.path.join(PKG_DIR, "libdlap_b200.so")
+LIB_PATH = os.environ.get("DLAP_LIB_EXP") or os.path.join(PKG_DIR, "libdlap_b200.so")
 SOURCES = ("capi.cu", "cell_fwd.cu", "cell_bwd.cu", "reduce.cu", "macro_lstm.cu", "tc_selftest.cu", "cell_fwd_tc.cu", "cell_bwd_tc.cu",
            "panel_index.cu")
 NVCC_FLAGS = ("-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",

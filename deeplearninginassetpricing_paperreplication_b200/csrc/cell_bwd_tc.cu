@@ -19,9 +19,9 @@
 // written over the (dead) H1 of its own tile, so the epilogue of tile i+1's layer 1 runs while the
 // tensor core works on dW2/dgrad of tile i, and layer 2 of tile i+1 runs under E3 of tile i.
 //
-// 20 warps: 0 TMEM owner, 1 MMA issuer, 2-3 gather + convert (each fetches two shares of 32 rows of the tile
-// with coalesced loads, 32 rows in flight, then every lane converts one row per share into the X image);
-// 4-19 epilogue (four warps per TMEM lane quarter; each thread handles 16 of the 64 hidden units of its cell).
+// 20 warps: 1 MMA issuer; 0 (also TMEM owner), 2, 3 gather + convert (batches of 16 rows are fetched with
+// coalesced loads, one row per load and a column pair per lane, split into bf16 hi/lo and stored straight into
+// the X image; batches go round-robin over the three warps); 4-19 epilogue (four warps per TMEM lane quarter; each thread handles 16 of the 64 hidden units of its cell).
 #include "cell_tc.cuh"
 
 namespace dlap {
@@ -30,17 +30,18 @@ using namespace tcl;
 namespace {
 constexpr int NT_B = 640;
 constexpr int NEPI = 16;                               // epilogue warps
-constexpr int STAGE_BYTES = TILE * ROW_PITCH * 4;        // 2 x 32 row slots (208 B) for each of the two gather warps
+constexpr int BR = 16;                                   // rows per gather batch (32 registers in flight per lane)
+constexpr int NB = TILE / BR;                            // batches per tile
+constexpr int NGW = 3;                                   // gather warps (0, 2, 3)
 constexpr uint32_t DPS_IMG = TILE * 16;                // one group: [cell][8 moments]
 
 struct SmemB {
   uint8_t* base;
-  __device__ float* stage() const { return reinterpret_cast<float*>(base); }
-  __device__ uint8_t* xh(int sl) const { return base + STAGE_BYTES + sl * 2 * X_IMG; }
+  __device__ uint8_t* xh(int sl) const { return base + sl * 2 * X_IMG; }
   __device__ uint8_t* xl(int sl) const { return xh(sl) + X_IMG; }
-  __device__ uint8_t* w1h(int sl) const { return base + STAGE_BYTES + 4 * X_IMG + sl * 2 * W1_IMG; }
+  __device__ uint8_t* w1h(int sl) const { return base + 4 * X_IMG + sl * 2 * W1_IMG; }
   __device__ uint8_t* w1l(int sl) const { return w1h(sl) + W1_IMG; }
-  __device__ uint8_t* w2h() const { return base + STAGE_BYTES + 4 * X_IMG + 4 * W1_IMG; }
+  __device__ uint8_t* w2h() const { return base + 4 * X_IMG + 4 * W1_IMG; }
   __device__ uint8_t* w2l() const { return w2h() + W2_IMG; }
   // per slot: [H hi (8 groups) | DPRE hi (1 group) | H lo | DPRE lo]: dz1 (written over h1) and dpre are
   // adjacent, so one MN-major B operand of 9 groups (N = 72) feeds dW1x and dWq in the same MMA
@@ -56,7 +57,7 @@ struct SmemB {
   __device__ uint64_t* bars() const { return reinterpret_cast<uint64_t*>(red() + NEPI * 32 + 32); }
   __device__ uint32_t* tmem_slot() const { return reinterpret_cast<uint32_t*>(bars() + 24); }
 };
-constexpr size_t SMEM_B_BYTES = (size_t)STAGE_BYTES + 4 * X_IMG + 4 * W1_IMG + 2 * W2_IMG + 6 * H_IMG + 4 * DPS_IMG +
+constexpr size_t SMEM_B_BYTES = (size_t)4 * X_IMG + 4 * W1_IMG + 2 * W2_IMG + 6 * H_IMG + 4 * DPS_IMG +
                                 128 * 4 + (NEPI * 32 + 32) * 4 + 24 * 8 + 16 + 128;
 
 enum { B_XOP_FULL = 2, B_XOP_EMPTY = 4, B_D1_FULL = 6, B_H1_FULL = 8,
@@ -103,6 +104,7 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
   // ---- one-time set-up ----
   for (int sl = 0; sl < 2; ++sl) fill_w1_images(P, s.w1h(sl), s.w1l(sl), tid, NT_B);
   fill_w2_images(P, s.w2h(), s.w2l(), tid, NT_B);
+  for (int sl = 0; sl < 2; ++sl) init_x_images(s.xh(sl), s.xl(sl), tid, NT_B);
   for (int sl = 0; sl < 2; ++sl)
     for (int i = tid; i < (int)DPS_IMG / 4; i += NT_B) {
       reinterpret_cast<uint32_t*>(s.dph(sl))[i] = 0u;
@@ -111,7 +113,7 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
   if (tid < 64) { s.b2s()[tid] = __ldg(P.b2 + tid); s.w3s()[tid] = __ldg(P.W3 + tid); }
   if (tid == 0) {
     for (int i = 0; i < 2; ++i) {
-      mbar_init(bar + B_XOP_FULL + i, 2);    mbar_init(bar + B_XOP_EMPTY + i, 1);
+      mbar_init(bar + B_XOP_FULL + i, NB);   mbar_init(bar + B_XOP_EMPTY + i, 1);
       mbar_init(bar + B_D1_FULL + i, 1);     mbar_init(bar + B_H1_FULL + i, NEPI);
       mbar_init(bar + B_W1_DONE + i, 1);
     }
@@ -144,12 +146,12 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
       mbar_wait(bar + B_XOP_FULL + sl, use & 1);
       tc::fence_after_sync();
       if (tc::elect_one()) {
-        const uint64_t ah = tc::smem_desc(smem_u32(s.xh(sl)), KM_A, 128), al = tc::smem_desc(smem_u32(s.xl(sl)), KM_A, 128);
+        const uint64_t ah = tc::smem_desc(smem_u32(s.xh(sl)), X_LBO, 128), al = tc::smem_desc(smem_u32(s.xl(sl)), X_LBO, 128);
         const uint64_t bh = tc::smem_desc(smem_u32(s.w1h(sl)), N1 * 16, 128), bl = tc::smem_desc(smem_u32(s.w1l(sl)), N1 * 16, 128);
         const uint32_t d = tbase + (sl ? C_A1 : C_A0);
 #pragma unroll
         for (int ks = 0; ks < KG1 / 2; ++ks)
-          umma3(d, tc::desc_advance(ah, ks * 2 * KM_A), tc::desc_advance(al, ks * 2 * KM_A),
+          umma3(d, tc::desc_advance(ah, ks * 2 * X_LBO), tc::desc_advance(al, ks * 2 * X_LBO),
                 tc::desc_advance(bh, ks * 2 * N1 * 16), tc::desc_advance(bl, ks * 2 * N1 * 16), id_l1, ks == 0);
         tc::umma_commit(bar + B_D1_FULL + sl);
       }
@@ -170,7 +172,7 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
           tc::umma_commit(bar + B_D2_FULL);
         }
         if (MOM && !SDF) {   // moment-only step: nothing else will read X(i); dWq^T = X^T.[.. | dpre] right away
-          const uint64_t xh_m = tc::smem_desc(smem_u32(s.xh(sl)), 128, KM_A), xl_m = tc::smem_desc(smem_u32(s.xl(sl)), 128, KM_A);
+          const uint64_t xh_m = tc::smem_desc(smem_u32(s.xh(sl)), 128, X_LBO), xl_m = tc::smem_desc(smem_u32(s.xl(sl)), 128, X_LBO);
           const uint64_t bh_m = tc::smem_desc(smem_u32(s.hh(sl)), 128, KM_A), bl_m = tc::smem_desc(smem_u32(s.hl(sl)), 128, KM_A);
 #pragma unroll
           for (int ks = 0; ks < TILE / 16; ++ks)
@@ -186,7 +188,7 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
     for (int i = 0; i < my_tiles; ++i) {
       const int sl = i & 1, par = i & 1;
       const bool first = (i == 0);
-      const uint64_t xh_m = tc::smem_desc(smem_u32(s.xh(sl)), 128, KM_A), xl_m = tc::smem_desc(smem_u32(s.xl(sl)), 128, KM_A);
+      const uint64_t xh_m = tc::smem_desc(smem_u32(s.xh(sl)), 128, X_LBO), xl_m = tc::smem_desc(smem_u32(s.xl(sl)), 128, X_LBO);
       const uint64_t hh_m = tc::smem_desc(smem_u32(s.hh(sl)), 128, KM_A), hl_m = tc::smem_desc(smem_u32(s.hl(sl)), 128, KM_A);
       if (SDF) {
         // -- after E2(i): dW2 and dgrad
@@ -232,110 +234,16 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
     }
     if (tc::elect_one()) tc::umma_commit(bar + B_ALL_DONE);
     __syncwarp();
-  } else if (warp == 2 || warp == 3) {
-    // ===== gather + convert: this warp owns rows 64w .. 64w+63 of every tile, handled as a stream of shares of
-    // 32 rows (share k = tile k/2, half k%2); lane = cell.  Only 16 rows (32 registers) are in flight at a time
-    // -- the kernel runs at 96 registers per thread -- so a share arrives as two half-shares A and B, each
-    // overlapped with one half of the conversion of the previous share; two staging areas alternate.
-    const int c0 = (warp - 2) * 64 + lane;
-    float* stage = s.stage() + (warp - 2) * 64 * ROW_PITCH;          // 2 x 32 slots, private to this warp
-    const int nshare = 2 * my_tiles;
-    MonthCursor mc;
-    if (my_tiles > 0) mc.init(P, tile_lo);
-    int t_seek = 0;
-    // where this lane's stock number of share k lives (cells past the end of the tile repeat its last row);
-    // moves the month cursor, whose rare loads are consumed right here
-    auto n_addr = [&](int k) {
-      const int tile = tile_lo + (k >> 1), cell = c0 + 32 * (k & 1);
-      mc.seek(P, tile);
-      t_seek = mc.t;
-      return vidx_row(P, mc.t) + mc.j0(tile) + min(cell, mc.ncell(tile) - 1);
-    };
-    auto load_bias = [&](int t, int cell) {        // per-month bias column (k = 46) of the W1 image, cells 0..79
-      float b = 0.f;
-      if (cell < 64) b = __ldg(P.a_t + (size_t)t * 64 + cell);
-      else if (cell < 72) b = __ldg(P.c_t + (size_t)t * 8 + cell - 64);
-      return b;
-    };
-    // groups g0 .. g0+2 of this lane's row of share k -> X image
-    auto convert = [&](int k, int g0) {
-      const int sl = (k >> 1) & 1, cell = c0 + 32 * (k & 1);
-      const float* slot = stage + ((k & 1) * 32 + lane) * ROW_PITCH;
-#pragma unroll
-      for (int g = g0; g < g0 + 3; ++g) {
-        float v[8];
-        row_group(slot, g, v);                       // floats >= F are zero in the slot
-        if (g == KG1 - 1) v[ONES_K - 8 * (KG1 - 1)] = 1.f;
-        uint4 hi, lo;
-        tc::split8(v, hi, lo);
-        *reinterpret_cast<uint4*>(s.xh(sl) + (g * TILE + cell) * 16) = hi;
-        *reinterpret_cast<uint4*>(s.xl(sl) + (g * TILE + cell) * 16) = lo;
-      }
-    };
-    float2 rows[16];
-    int n_a = 0, t_a = 0;                          // share k+1 (its half B is loaded in iteration k)
-    int n_b = 0, t_b = 0;                          // share k+2 (half A loaded at the end of iteration k)
-    int n_c = 0, t_c = 0;                          // share k+3 (stock numbers loaded during iteration k)
-    float b_cur = 0.f, b_nxt = 0.f;
-    for (int i = lane; i < 64 * ROW_PITCH; i += 32) stage[i] = 0.f;   // floats >= F of every slot stay zero
-    __syncwarp();
-    if (nshare > 0) {                              // share 0 completely, half A of share 1
-      n_c = __ldg(n_addr(0)); t_c = t_seek;
-      n_a = __ldg(n_addr(1)); t_a = t_seek;
-      if (nshare > 2) { n_b = __ldg(n_addr(2)); t_b = t_seek; }
-      b_cur = load_bias(t_c, c0);
-      b_nxt = load_bias(t_a, c0 + 32);
-      gather_load<16>(P, t_c, n_c, 0, lane, rows);
-      gather_store<16>(P, stage, 0, lane, rows);
-      gather_load<16>(P, t_c, n_c, 16, lane, rows);
-      gather_store<16>(P, stage, 16, lane, rows);
-      if (nshare > 2) prefetch_row(P, t_b, n_b);
-      gather_load<16>(P, t_a, n_a, 0, lane, rows);
-      __syncwarp();
-    }
-    // Loop order as in the forward kernel (cell_fwd_tc.cu): every consumer of a long-latency load comes before
-    // the next batch of row loads is issued (a wait placed after them shares a scoreboard with the batch).
-    for (int k = 0; k < nshare; ++k) {
-      // here: share k sits in staging area k&1; registers hold half A of share k+1
-      const int i = k >> 1, sh = k & 1, sl = i & 1, use = i >> 1;
-      const int cell = c0 + 32 * sh;
-      const bool more = k + 1 < nshare;
-      float* area_nxt = stage + ((k + 1) & 1) * 32 * ROW_PITCH;
-      const __nv_bfloat16 bh = __float2bfloat16_rn(b_cur);           // bias of share k
-      const __nv_bfloat16 bl = __float2bfloat16_rn(b_cur - __bfloat162float(bh));
-      b_cur = b_nxt;
-      const bool stamp = warp == 2 && lane == 0;
-      if (stamp) DLAP_STAMP(k, 6);
-      if (sh == 0) mbar_wait(bar + B_XOP_EMPTY + sl, (use & 1) ^ 1);
-      if (stamp) DLAP_STAMP(k, 7);
-      convert(k, 0);
-      if (stamp) DLAP_STAMP(k, 13);
-      if (more) {
-        const int* pn = (k + 3 < nshare) ? n_addr(k + 3) : nullptr;
-        if (k + 2 < nshare) b_nxt = load_bias(t_b, c0 + 32 * sh);    // share k+2 has the parity of share k
-        gather_store<16>(P, area_nxt, 0, lane, rows);                // half A of share k+1
-        gather_load<16>(P, t_a, n_a, 16, lane, rows);                // half B of share k+1
-        if (pn) { n_c = __ldg(pn); t_c = t_seek; }
-      }
-      if (stamp) DLAP_STAMP(k, 14);
-      convert(k, 3);
-      if (cell < N1) {
-        const int off = ((KG1 - 1) * N1 + cell) * 16 + (ONES_K - 8 * (KG1 - 1)) * 2;
-        *reinterpret_cast<__nv_bfloat16*>(s.w1h(sl) + off) = bh;
-        *reinterpret_cast<__nv_bfloat16*>(s.w1l(sl) + off) = bl;
-      }
-      fence_proxy_async();
-      __syncwarp();
-      if (sh == 1 && lane == 0) mbar_arrive(bar + B_XOP_FULL + sl);
-      if (stamp) DLAP_STAMP(k, 15);
-      if (more) {
-        gather_store<16>(P, area_nxt, 16, lane, rows);               // half B of share k+1
-        n_a = n_b; t_a = t_b; n_b = n_c; t_b = t_c;                  // n_a: share k+2, n_b: share k+3
-        if (k + 3 < nshare) prefetch_row(P, t_b, n_b);               // share k+3 -> L2, loaded one iteration later
-        if (k + 2 < nshare) gather_load<16>(P, t_a, n_a, 0, lane, rows);   // half A of share k+2
-        __syncwarp();
-      }
-    }
+  } else if (warp == 0 || warp == 2 || warp == 3) {
+    // ===== gather + convert (cell_tc.cuh); stamps 4-7 of row q / NGW: loop top, slot free, converted, loads issued
+    const int gw = warp == 0 ? 0 : warp - 1;
+    long long* tl = (P.timeline && blockIdx.x == 0 && gw == 1 && lane == 0) ? P.timeline + 256 * 16 * 2 : nullptr;
+    if (gather_wide(P))
+      gather_role<BR, NGW, true, true>(P, gw, lane, tile_lo, my_tiles, s.xh(0), s.w1h(0), bar + B_XOP_FULL,
+                                       bar + B_XOP_EMPTY, tl, 0, true);
+    else
+      gather_role<BR, NGW, false, true>(P, gw, lane, tile_lo, my_tiles, s.xh(0), s.w1h(0), bar + B_XOP_FULL,
+                                        bar + B_XOP_EMPTY, tl, 0, true);
   } else if (warp >= 4 && warp < 20) {
     // ===== epilogue: thread = (cell, 16 of the hidden units) =====
     const int ew = warp - 4, q4 = warp & 3, hf = ew >> 2, cell = q4 * 32 + lane, U0 = hf * 16;

@@ -100,75 +100,57 @@ struct MonthCursor {
   __device__ __forceinline__ int ncell(int tile) const { return min(TILE, cnt - (tile - first) * TILE); }
 };
 
-// A gathered tile sits in the staging buffer as one 208-B slot per characteristic row (row at the slot start).
-constexpr int ROW_PITCH = 52;           // floats; 13 x 16 B: LDS.128 over consecutive rows is conflict-free
-
-// Gather by one warp.  Lane l knows the stock number of row l of the warp's share (n_lane; a cell past the
-// end of the tile repeats the tile's last row, so the images only ever hold real, finite panel rows).
-// Row j is fetched by ONE coalesced warp-wide load (lane k takes floats 2k, 2k+1; when x or F do not allow
-// 8-byte loads: floats k and k+32), so ROWS independent loads are in flight per warp -- scattered 184-B rows
-// need that memory-level parallelism; per-row TMA bulk copies and cp.async both serialise on a short queue
-// (measured: 78 and 190 cycles per row).
-// The loads are unconditional (cells past the end of a tile carry the number of the tile's last row, lanes
-// past the row re-read its last element): a predicated load followed by a select makes ptxas wait for each
-// load before issuing the next one.  Addresses are a 64-bit base plus a 32-bit byte offset (one IMAD.WIDE).
-template <int ROWS>
-__device__ __forceinline__ void gather_load(const CellParams& P, int t, int n_lane, int row0, int lane,
-                                            float2 (&r)[ROWS]) {
-  const bool wide = ((P.F & 1) == 0) && ((reinterpret_cast<uintptr_t>(P.x) & 7) == 0);
+// Gather of characteristic rows by one warp.  Lane l (< ROWS) knows the stock number of row l of the batch
+// (n_lane; a cell past the end of the tile repeats the tile's last row, so only real, finite panel rows are
+// ever fetched).  Row j is fetched by ONE coalesced warp-wide load -- lane p takes columns 2p, 2p+1 -- so ROWS
+// independent loads are in flight per warp; scattered 184-B rows need that memory-level parallelism (per-row
+// TMA bulk copies and cp.async both serialise: measured 78 and 190 cycles per row and warp).
+// The loads are unconditional on clamped addresses (lanes past the row re-read its last element; whoever
+// consumes the registers ignores them): a predicated load followed by a select makes ptxas wait for each load
+// before issuing the next one.  Addresses are a 64-bit base plus a 32-bit byte offset (one IMAD.WIDE).
+// A row lands in ONE 64-bit register per lane (low word = column 2p, high word = column 2p+1): 64-bit scalars
+// live in aligned register pairs.  WIDE (8-byte loads: F even, x 8-B aligned) is a template parameter so that
+// the row registers have a single definition inside the caller's loop: with two definitions (a prologue, or
+// an if/else over the load width) ptxas gives them different homes and copies every loaded value after the
+// loads -- one full-latency wait per load, inside the issue loop.
+template <int ROWS, bool WIDE>
+__device__ __forceinline__ void gather_load(const CellParams& P, int t, int n_lane, int lane, uint64_t (&r)[ROWS]) {
   const char* xt = reinterpret_cast<const char*>(P.x + (size_t)t * P.N * P.F);
   const uint32_t pitch = (uint32_t)P.F * 4u;                 // N * F * 4 < 2^32 (checked by dlap_make_plan)
-  if (wide) {
+  if (WIDE) {
     const char* base = xt + 8 * min(lane, (P.F >> 1) - 1);
 #pragma unroll
     for (int j = 0; j < ROWS; ++j) {
-      const uint32_t nr = (uint32_t)__shfl_sync(0xffffffffu, n_lane, row0 + j);
-      r[j] = __ldg(reinterpret_cast<const float2*>(base + nr * pitch));
+      const uint32_t nr = (uint32_t)__shfl_sync(0xffffffffu, n_lane, j);
+      r[j] = __ldg(reinterpret_cast<const unsigned long long*>(base + nr * pitch));
     }
   } else {
-    const char* b0 = xt + 4 * min(lane, P.F - 1);
-    const char* b1 = xt + 4 * min(lane + 32, P.F - 1);
+    const char* b0 = xt + 4 * min(2 * lane, P.F - 1);
+    const char* b1 = xt + 4 * min(2 * lane + 1, P.F - 1);
 #pragma unroll
     for (int j = 0; j < ROWS; ++j) {
-      const uint32_t nr = (uint32_t)__shfl_sync(0xffffffffu, n_lane, row0 + j);
-      r[j].x = __ldg(reinterpret_cast<const float*>(b0 + nr * pitch));
-      r[j].y = __ldg(reinterpret_cast<const float*>(b1 + nr * pitch));
+      const uint32_t nr = (uint32_t)__shfl_sync(0xffffffffu, n_lane, j);
+      const uint32_t lo = __ldg(reinterpret_cast<const unsigned int*>(b0 + nr * pitch));
+      const uint32_t hi = __ldg(reinterpret_cast<const unsigned int*>(b1 + nr * pitch));
+      r[j] = ((uint64_t)hi << 32) | lo;
     }
   }
 }
-// L2 prefetch of this lane's own row (stock n of month t), issued two tiles ahead of its gather_load so that
+__device__ __forceinline__ bool gather_wide(const CellParams& P) {
+  return ((P.F & 1) == 0) && ((reinterpret_cast<uintptr_t>(P.x) & 7) == 0);
+}
+// L2 prefetch of this lane's own row (stock n of month t), issued two batches ahead of its gather_load so that
 // the loads find the row in L2 instead of paying the HBM latency of a scattered 184-B read
 __device__ __forceinline__ void prefetch_row(const CellParams& P, int t, int n) {
+#ifdef EXP_NOPF
+  return;
+#endif
   const char* a = reinterpret_cast<const char*>(P.x + ((size_t)t * P.N + n) * P.F);
   const int bytes = P.F * 4;
   asm volatile("prefetch.global.L2 [%0];" ::"l"(a));
   if (bytes > 64) asm volatile("prefetch.global.L2 [%0];" ::"l"(a + 64));
   if (bytes > 128) asm volatile("prefetch.global.L2 [%0];" ::"l"(a + 128));
   asm volatile("prefetch.global.L2 [%0];" ::"l"(a + bytes - 4));
-}
-
-// rows row0 .. row0+ROWS-1 of the warp's share -> its staging slots
-template <int ROWS>
-__device__ __forceinline__ void gather_store(const CellParams& P, float* stage_warp, int row0, int lane,
-                                             const float2 (&r)[ROWS]) {
-  const bool wide = ((P.F & 1) == 0) && ((reinterpret_cast<uintptr_t>(P.x) & 7) == 0);
-#pragma unroll
-  for (int j = 0; j < ROWS; ++j) {
-    float* dst = stage_warp + (row0 + j) * ROW_PITCH;
-    if (wide) {
-      if (2 * lane < P.F) reinterpret_cast<float2*>(dst)[lane] = r[j];
-    } else {
-      if (lane < P.F) dst[lane] = r[j].x;
-      if (lane + 32 < P.F) dst[lane + 32] = r[j].y;
-    }
-  }
-}
-// floats 8g..8g+7 of the row in slot `slot`
-__device__ __forceinline__ void row_group(const float* slot, int g, float (&v)[8]) {
-  const float4* p = reinterpret_cast<const float4*>(slot) + 2 * g;
-  const float4 a0 = p[0], a1 = p[1];
-  v[0] = a0.x; v[1] = a0.y; v[2] = a0.z; v[3] = a0.w;
-  v[4] = a1.x; v[5] = a1.y; v[6] = a1.z; v[7] = a1.w;
 }
 
 // layout of one CTA's weight-gradient partial

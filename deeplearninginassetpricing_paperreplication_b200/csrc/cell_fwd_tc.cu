@@ -6,11 +6,10 @@
 //
 // Persistent CTA, one per SM, 16 warps with fixed roles; two tiles are in flight (slot = tile & 1):
 //   warp 1      MMA issuer (one lane): layer 1 of tile i is issued before layer 2 of tile i-1
-//   warp 2      TMEM allocator
-//   warps 4-7   gather + convert: each warp fetches 32 rows of the tile with coalesced loads (the rows of tile
-//               i+1 are in flight in registers while tile i is converted), drops them into its private staging
-//               slots, then every lane turns one row into the bf16 hi/lo X image (+ ones column) and the warps
-//               write the per-month bias column of W1
+//   warps 0, 2-7  gather + convert (warp 2 also owns the TMEM allocation): batches of 32 rows, round-robin over
+//               the seven warps, are fetched with coalesced loads (one row per load, a column pair per lane),
+//               split into bf16 hi/lo and stored straight into the X image; the warp that handles the first
+//               batch of a tile also writes the per-month bias column of W1
 //   warps 8-11  epilogue of even tiles   } z1 -> relu -> split -> H1 image ; tanh(q) ;
 //   warps 12-15 epilogue of odd tiles    } z2 -> relu -> .W3 -> u ; g = q R m ; row sums
 #include "cell_tc.cuh"
@@ -20,17 +19,18 @@ using namespace tcl;
 
 namespace {
 constexpr int NT_TC = 512;
-constexpr int STAGE_BYTES_F = TILE * ROW_PITCH * 4;      // 26 624 B: 32 row slots for each of the four gather warps
+constexpr int BR = 32;                                   // rows per gather batch (64 registers in flight per lane)
+constexpr int NB = TILE / BR;                            // batches per tile
+constexpr int NGW = 7;                                   // gather warps: 0, 2 (also TMEM owner), 3, 4..7
 struct SmemTc {
   uint8_t* base;
-  __device__ float* stage() const { return reinterpret_cast<float*>(base); }
-  __device__ uint8_t* xh(int sl) const { return base + STAGE_BYTES_F + sl * 2 * X_IMG; }
+  __device__ uint8_t* xh(int sl) const { return base + sl * 2 * X_IMG; }
   __device__ uint8_t* xl(int sl) const { return xh(sl) + X_IMG; }
-  __device__ uint8_t* w1h(int sl) const { return base + STAGE_BYTES_F + 4 * X_IMG + sl * 2 * W1_IMG; }
+  __device__ uint8_t* w1h(int sl) const { return base + 4 * X_IMG + sl * 2 * W1_IMG; }
   __device__ uint8_t* w1l(int sl) const { return w1h(sl) + W1_IMG; }
-  __device__ uint8_t* hh(int sl) const { return base + STAGE_BYTES_F + 4 * X_IMG + 4 * W1_IMG + sl * 2 * H_IMG; }
+  __device__ uint8_t* hh(int sl) const { return base + 4 * X_IMG + 4 * W1_IMG + sl * 2 * H_IMG; }
   __device__ uint8_t* hl(int sl) const { return hh(sl) + H_IMG; }
-  __device__ uint8_t* w2h() const { return base + STAGE_BYTES_F + 4 * X_IMG + 4 * W1_IMG + 4 * H_IMG; }
+  __device__ uint8_t* w2h() const { return base + 4 * X_IMG + 4 * W1_IMG + 4 * H_IMG; }
   __device__ uint8_t* w2l() const { return w2h() + W2_IMG; }
   __device__ float* b2s() const { return reinterpret_cast<float*>(w2l() + W2_IMG); }
   __device__ float* w3s() const { return b2s() + 64; }
@@ -40,7 +40,7 @@ struct SmemTc {
 enum { F_XOP_FULL = 4, F_XOP_EMPTY = 6, F_D1_FULL = 8, F_H1_FULL = 10,
        F_D2_FULL = 12, F_D2_EMPTY = 14 };
 
-constexpr size_t SMEM_TC_BYTES = (size_t)STAGE_BYTES_F + 4 * X_IMG + 4 * W1_IMG + 4 * H_IMG + 2 * W2_IMG +
+constexpr size_t SMEM_TC_BYTES = (size_t)4 * X_IMG + 4 * W1_IMG + 4 * H_IMG + 2 * W2_IMG +
                                  128 * 4 + 16 * 8 + 16 + 256;
 
 // TMEM columns
@@ -68,10 +68,11 @@ __global__ void __launch_bounds__(NT_TC, 1) cell_fwd_tc_kernel(const CellParams 
   // ---- one-time set-up ----
   for (int sl = 0; sl < 2; ++sl) fill_w1_images(P, s.w1h(sl), s.w1l(sl), tid, NT_TC);
   fill_w2_images(P, s.w2h(), s.w2l(), tid, NT_TC);
+  for (int sl = 0; sl < 2; ++sl) init_x_images(s.xh(sl), s.xl(sl), tid, NT_TC);
   if (tid < 64) { s.b2s()[tid] = __ldg(P.b2 + tid); s.w3s()[tid] = __ldg(P.W3 + tid); }
   if (tid == 0) {
     for (int i = 0; i < 2; ++i) {
-      mbar_init(bar + F_XOP_FULL + i, 4);    mbar_init(bar + F_XOP_EMPTY + i, 1);
+      mbar_init(bar + F_XOP_FULL + i, NB);   mbar_init(bar + F_XOP_EMPTY + i, 1);
       mbar_init(bar + F_D1_FULL + i, 1);     mbar_init(bar + F_H1_FULL + i, 4);
       mbar_init(bar + F_D2_FULL + i, 1);     mbar_init(bar + F_D2_EMPTY + i, 4);
     }
@@ -95,13 +96,13 @@ __global__ void __launch_bounds__(NT_TC, 1) cell_fwd_tc_kernel(const CellParams 
           mbar_wait(bar + F_XOP_FULL + sl, use & 1);
           tc::fence_after_sync();
           if (lane == 0) DLAP_STAMP(i, 8);
-          const uint64_t ah = tc::smem_desc(smem_u32(s.xh(sl)), TILE * 16, 128), al = tc::smem_desc(smem_u32(s.xl(sl)), TILE * 16, 128);
+          const uint64_t ah = tc::smem_desc(smem_u32(s.xh(sl)), X_LBO, 128), al = tc::smem_desc(smem_u32(s.xl(sl)), X_LBO, 128);
           const uint64_t bh = tc::smem_desc(smem_u32(s.w1h(sl)), N1 * 16, 128), bl = tc::smem_desc(smem_u32(s.w1l(sl)), N1 * 16, 128);
           const uint32_t d = tbase + (sl ? COL_A1 : COL_A0);
           if (tc::elect_one()) {
 #pragma unroll
             for (int ks = 0; ks < KG1 / 2; ++ks)
-              umma3(d, tc::desc_advance(ah, ks * 2 * TILE * 16), tc::desc_advance(al, ks * 2 * TILE * 16),
+              umma3(d, tc::desc_advance(ah, ks * 2 * X_LBO), tc::desc_advance(al, ks * 2 * X_LBO),
                     tc::desc_advance(bh, ks * 2 * N1 * 16), tc::desc_advance(bl, ks * 2 * N1 * 16), id1, ks == 0);
             tc::umma_commit(bar + F_XOP_EMPTY + sl);
             tc::umma_commit(bar + F_D1_FULL + sl);
@@ -129,86 +130,17 @@ __global__ void __launch_bounds__(NT_TC, 1) cell_fwd_tc_kernel(const CellParams 
         }
       }
     }
-  } else if (warp >= 4 && warp < 8) {
-    // ===== gather + convert: warp w owns rows 32w .. 32w+31 of every tile; lane = cell =====
-    const int cell = tid - 128;
-    float* stage = s.stage() + (warp - 4) * 32 * ROW_PITCH;          // private to this warp
-    MonthCursor mc;
-    if (my_tiles > 0) mc.init(P, tile_lo);
-    int n_nxt = 0, t_nxt = 0;                      // tile i+1: rows loaded next
-    int n_pf = 0, t_pf = 0, t_seek = 0;            // tile i+2: rows prefetched to L2 now, loaded one tile later
-    // where this lane's stock number of `tile` lives (cells past the end of the tile repeat its last row);
-    // moves the month cursor, whose rare loads are consumed right here
-    auto n_addr = [&](int tile) {
-      mc.seek(P, tile);
-      t_seek = mc.t;
-      return vidx_row(P, mc.t) + mc.j0(tile) + min(cell, mc.ncell(tile) - 1);
-    };
-    // bias column k = 46 of the W1 image: a_t (units 0..63) | c_t (moments) of the tile's month, by cells 0..79
-    auto load_bias = [&](int t) {
-      float b = 0.f;
-      if (cell < 64) b = __ldg(P.a_t + (size_t)t * 64 + cell);
-      else if (cell < 72 && MOM) b = __ldg(P.c_t + (size_t)t * 8 + cell - 64);
-      return b;
-    };
-    float2 rows[32];
-    float b_nxt = 0.f;
-    for (int i = lane; i < 32 * ROW_PITCH; i += 32) stage[i] = 0.f;   // floats >= F of every slot stay zero
-    __syncwarp();
-    if (my_tiles > 0) {
-      n_nxt = __ldg(n_addr(tile_lo)); t_nxt = t_seek;
-      b_nxt = load_bias(t_nxt);
-      gather_load<32>(P, t_nxt, n_nxt, 0, lane, rows);
-      if (my_tiles > 1) { n_nxt = __ldg(n_addr(tile_lo + 1)); t_nxt = t_seek; prefetch_row(P, t_nxt, n_nxt); }
-      if (my_tiles > 2) { n_pf = __ldg(n_addr(tile_lo + 2)); t_pf = t_seek; }
-    }
-    // Loop order matters.  ptxas tracks loads with six scoreboards per warp, so a wait placed after the 32 row
-    // loads of the next tile shares a scoreboard with them and stalls for the whole gather: every consumer of a
-    // long-latency load (month cursor, bias, stock numbers) therefore sits BEFORE the row loads are issued.  The
-    // stock-number load for tile i+2 is issued AFTER them, once the old value is dead, so that it can land in
-    // the loop-carried register itself (otherwise a register copy at the loop end waits for it).  Stock numbers
-    // run two tiles ahead of the row loads: the rows of tile i+2 are prefetched to L2 while tile i+1 is loaded.
-    for (int i = 0; i < my_tiles; ++i) {
-      const int sl = i & 1, use = i >> 1;
-      const bool stamp = warp == 4 && lane == 0;
-      if (stamp) DLAP_STAMP(i, 0);
-      gather_store<32>(P, stage, 0, lane, rows);                     // rows of tile i (loaded one tile ago)
-      __syncwarp();
-      if (stamp) DLAP_STAMP(i, 1);
-      const __nv_bfloat16 bh = __float2bfloat16_rn(b_nxt);           // bias of tile i (loaded one tile ago)
-      const __nv_bfloat16 bl = __float2bfloat16_rn(b_nxt - __bfloat162float(bh));
-      if (i + 1 < my_tiles) {                                        // rows of tile i+1 fly during the conversion
-        const int* pn = (i + 3 < my_tiles) ? n_addr(tile_lo + i + 3) : nullptr;
-        b_nxt = load_bias(t_nxt);
-        gather_load<32>(P, t_nxt, n_nxt, 0, lane, rows);
-        if (i + 2 < my_tiles) prefetch_row(P, t_pf, n_pf);
-        n_nxt = n_pf; t_nxt = t_pf;
-        if (pn) { n_pf = __ldg(pn); t_pf = t_seek; }
-      }
-      if (stamp) DLAP_STAMP(i, 2);
-      mbar_wait(bar + F_XOP_EMPTY + sl, (use & 1) ^ 1);
-      if (stamp) DLAP_STAMP(i, 3);
-      const float* slot = stage + lane * ROW_PITCH;
-#pragma unroll
-      for (int g = 0; g < KG1; ++g) {
-        float v[8];
-        row_group(slot, g, v);                       // floats >= F are zero in the slot
-        if (g == KG1 - 1) v[ONES_K - 8 * (KG1 - 1)] = 1.f;
-        uint4 hi, lo;
-        tc::split8(v, hi, lo);
-        *reinterpret_cast<uint4*>(s.xh(sl) + (g * TILE + cell) * 16) = hi;
-        *reinterpret_cast<uint4*>(s.xl(sl) + (g * TILE + cell) * 16) = lo;
-      }
-      if (cell < N1) {
-        const int off = ((KG1 - 1) * N1 + cell) * 16 + (ONES_K - 8 * (KG1 - 1)) * 2;
-        *reinterpret_cast<__nv_bfloat16*>(s.w1h(sl) + off) = bh;
-        *reinterpret_cast<__nv_bfloat16*>(s.w1l(sl) + off) = bl;
-      }
-      fence_proxy_async();
-      __syncwarp();                                  // also: every lane is done with the staging slots
-      if (lane == 0) mbar_arrive(bar + F_XOP_FULL + sl);
-      if (stamp) DLAP_STAMP(i, 4);
-    }
+  } else if (warp < 8) {
+    // ===== gather + convert (cell_tc.cuh); stamps 0-3 of timeline row q / NGW: loop top, slot free, converted,
+    // loads issued
+    const int gw = warp == 0 ? 0 : warp - 1;
+    long long* tl = (P.timeline && blockIdx.x == 0 && warp == 4 && lane == 0) ? P.timeline : nullptr;
+    if (gather_wide(P))
+      gather_role<BR, NGW, true, MOM>(P, gw, lane, tile_lo, my_tiles, s.xh(0), s.w1h(0), bar + F_XOP_FULL,
+                                      bar + F_XOP_EMPTY, tl, 0, true);
+    else
+      gather_role<BR, NGW, false, MOM>(P, gw, lane, tile_lo, my_tiles, s.xh(0), s.w1h(0), bar + F_XOP_FULL,
+                                       bar + F_XOP_EMPTY, tl, 0, true);
   } else if (warp >= 8) {
     // ===== epilogue: group e handles tiles with (i & 1) == e ; thread = TMEM lane = cell =====
     const int e = (warp - 8) >> 2, q4 = warp & 3, cell = q4 * 32 + lane;

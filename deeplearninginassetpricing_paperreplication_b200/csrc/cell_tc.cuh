@@ -6,7 +6,9 @@
 // which keeps ~fp32 accuracy (measured against the oracle in tests/) at 3x the MMA count.
 //
 // Shared-memory operand images use the no-swizzle canonical layout [group of 8][row][8] (tc_sm100.cuh).
-//   X  [6][128][8]   characteristics of the tile; k = 46 holds 1.0 (the "ones column"), k = 47 = 0
+//   X  [6][128+1][8] characteristics of the tile; k = 46 holds 1.0 (the "ones column"), k = 47 = 0.  The group
+//                    stride is padded by one row (2064 B) so that a warp holding one row as a column pair per
+//                    lane stores it without bank conflicts (rows_to_image)
 //   W1 [6][80][8]    rows 0..63 = W1[:, :F], rows 64..71 = Wq[:, M:], rows 72..79 = 0;
 //                    column k = 46 carries the per-month bias a_t | c_t, so both first-layer biases
 //                    are added by the MMA itself
@@ -22,11 +24,133 @@ namespace tcl {
 constexpr int KG1 = 6;                  // k-groups of layer 1 (K = 48)
 constexpr int N1 = 80;                  // layer-1 MMA N: 64 hidden + 8 moments + 8 pad
 constexpr int KG2 = 8;                  // k-groups of layer 2 (K = 64)
-constexpr uint32_t X_IMG = KG1 * TILE * 16;      // 12288 B per hi or lo image
+constexpr uint32_t X_LBO = TILE * 16 + 16;       // byte stride between the k-groups of an X image
+constexpr uint32_t X_IMG = KG1 * X_LBO;          // 12384 B per hi or lo image
 constexpr uint32_t W1_IMG = KG1 * N1 * 16;       //  7680 B
 constexpr uint32_t H_IMG = KG2 * TILE * 16;      // 16384 B
 constexpr uint32_t W2_IMG = KG2 * 64 * 16;       //  8192 B
 constexpr int ONES_K = 46;              // index of the ones column inside X (needs F <= 46)
+
+// X image pair before the first tile: zeros, and 1.0 in column k = 46 of the hi image.  The gather warps only
+// ever overwrite columns < F, so the ones column and the zero padding survive every tile.
+__device__ __forceinline__ void init_x_images(uint8_t* hi, uint8_t* lo, int tid, int nthr) {
+  for (uint32_t i = tid; i < X_IMG / 4; i += nthr) {
+    const uint32_t byte = 4 * i, g = byte / X_LBO, w = byte % X_LBO;
+    const bool ones = g == (uint32_t)(ONES_K >> 3) && w < TILE * 16 && (w & 15) == (uint32_t)(ONES_K & 7) * 2;
+    reinterpret_cast<uint32_t*>(hi)[i] = ones ? 0x00003F80u : 0u;     // bf16 (1.0, 0.0)
+    reinterpret_cast<uint32_t*>(lo)[i] = 0u;
+  }
+}
+
+// ROWS rows of a tile (cells cell0 .. cell0+ROWS-1), held as one 64-bit register per lane (lane p = columns
+// 2p, 2p+1; gather_load), -> the bf16 hi/lo X image pair.  Lane p writes 4 bytes per row and image at
+// [group p/4][cell][(p%4)*4]; with the padded group stride the lanes of a warp hit distinct banks.
+template <int ROWS>
+__device__ __forceinline__ void rows_to_image(const uint64_t (&r)[ROWS], uint8_t* xh, uint8_t* xl, int cell0, int lane,
+                                              int F) {
+  const bool odd_tail = 2 * lane + 1 >= F;       // last pair of an odd F: column 2p+1 does not exist
+  if (2 * lane < F) {
+    const uint32_t off = (uint32_t)(lane >> 2) * X_LBO + (uint32_t)cell0 * 16 + (uint32_t)(lane & 3) * 4;
+#pragma unroll
+    for (int j = 0; j < ROWS; ++j) {
+      uint32_t h, l;
+      const float x = __uint_as_float((uint32_t)r[j]), y = __uint_as_float((uint32_t)(r[j] >> 32));
+      tc::split2(x, odd_tail ? 0.f : y, h, l);
+      *reinterpret_cast<uint32_t*>(xh + off + j * 16) = h;
+      *reinterpret_cast<uint32_t*>(xl + off + j * 16) = l;
+    }
+  }
+}
+
+// ---- gather + convert role (forward and backward kernels) -----------------------------------------------
+// The tiles of a CTA are cut into batches of BR rows; batch q = (tile q / NB, rows BR * (q % NB) ..) goes to
+// gather warp q % NGW.  A batch is fetched with coalesced loads (gather_load), waits in registers, and is
+// written into the X image of its tile's slot (rows_to_image) once the slot is free; the warp that handles
+// the first batch of a tile also writes the per-month bias column (k = 46) of the slot's W1 image:
+// a_t (units 0..63) | c_t (moments) | 0.  x0 / w10: hi image of slot 0; slots are 2 images apart.
+//
+// Loop order matters.  ptxas tracks loads with six scoreboards per warp, so a wait placed after the row loads of
+// the next batch shares a scoreboard with them and stalls for the whole gather: every consumer of a long-latency
+// load (month cursor, bias, stock numbers) sits BEFORE the row loads are issued, and the stock-number load for
+// a later batch is issued AFTER them, once the old value is dead, so that it lands in the loop-carried register
+// itself (a register copy at the loop end would wait for it).  Stock numbers run two batches ahead of the row
+// loads: those rows are prefetched to L2 in the meantime.  The loop starts one step early (q < 0: loads only)
+// so that the row registers have a single definition.
+template <int BR, int NGW, bool WIDE, bool MOM>
+__device__ __forceinline__ void gather_role(const CellParams& P, int gw, int lane, int tile_lo, int my_tiles,
+                                            uint8_t* x0, uint8_t* w10, uint64_t* xop_full, uint64_t* xop_empty,
+                                            long long* tl /* stamps or null */, int tl_slot, bool tl_per_batch) {
+  constexpr int NB = TILE / BR;
+  const int nbatch = my_tiles * NB;
+  MonthCursor mc;
+  if (my_tiles > 0) mc.init(P, tile_lo);
+  int t_seek = 0;
+  // where lane l's stock number of batch q lives (cells past the end of the tile repeat its last row); moves the
+  // month cursor, whose rare loads are consumed right here
+  auto n_addr = [&](int q) {
+    const int tile = tile_lo + q / NB, cell = (q % NB) * BR + (lane & (BR - 1));
+    mc.seek(P, tile);
+    t_seek = mc.t;
+    return vidx_row(P, mc.t) + mc.j0(tile) + min(cell, mc.ncell(tile) - 1);
+  };
+  auto load_bias = [&](int t, float (&b)[3]) {       // entries lane, lane + 32, lane + 64 of the bias column
+    b[0] = __ldg(P.a_t + (size_t)t * 64 + lane);
+    b[1] = __ldg(P.a_t + (size_t)t * 64 + 32 + lane);
+    b[2] = (MOM && lane < 8) ? __ldg(P.c_t + (size_t)t * 8 + lane) : 0.f;
+  };
+  uint64_t rows[BR];
+#pragma unroll
+  for (int j = 0; j < BR; ++j) rows[j] = 0ull;
+  float bias[3] = {0.f, 0.f, 0.f};
+  int n_nxt = 0, t_nxt = 0;                        // this warp's next batch: rows loaded next
+  int n_pf = 0, t_pf = 0;                          // the batch after it: rows prefetched to L2, loaded one batch later
+  if (gw < nbatch) { n_nxt = __ldg(n_addr(gw)); t_nxt = t_seek; }
+  if (gw + NGW < nbatch) { n_pf = __ldg(n_addr(gw + NGW)); t_pf = t_seek; }
+  for (int q = gw - NGW; q < nbatch; q += NGW) {
+    long long* st = (tl && q >= 0) ? tl + (size_t)(tl_per_batch ? q / NGW : q / NB) * 16 + tl_slot : nullptr;
+    if (st && (tl_per_batch ? q / NGW : q / NB) >= 256) st = nullptr;
+    if (q >= 0) {
+      const int i = q / NB, b = q % NB, sl = i & 1, use = i >> 1;
+      uint8_t* xh = x0 + sl * 2 * X_IMG;
+      uint8_t* w1h = w10 + sl * 2 * W1_IMG;
+      if (st) st[0] = clock64();
+      __nv_bfloat16 bh[3], bl[3];
+#pragma unroll
+      for (int e = 0; e < 3; ++e) {
+        bh[e] = __float2bfloat16_rn(bias[e]);
+        bl[e] = __float2bfloat16_rn(bias[e] - __bfloat162float(bh[e]));
+      }
+      mbar_wait(xop_empty + sl, (use & 1) ^ 1);
+      if (st) st[1] = clock64();
+      rows_to_image<BR>(rows, xh, xh + X_IMG, b * BR, lane, P.F);        // waits for the row loads
+      if (b == 0) {
+#pragma unroll
+        for (int e = 0; e < 3; ++e) {
+          const int unit = lane + 32 * e;
+          if (unit < N1) {
+            const int off = ((KG1 - 1) * N1 + unit) * 16 + (ONES_K - 8 * (KG1 - 1)) * 2;
+            *reinterpret_cast<__nv_bfloat16*>(w1h + off) = bh[e];
+            *reinterpret_cast<__nv_bfloat16*>(w1h + W1_IMG + off) = bl[e];
+          }
+        }
+      }
+      fence_proxy_async();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(xop_full + sl);
+      if (st) st[2] = clock64();
+    }
+    if (q + NGW < nbatch) {
+      const int* pn = (q + 3 * NGW < nbatch) ? n_addr(q + 3 * NGW) : nullptr;
+      const int n2 = n_pf, t2 = t_pf;
+      if ((q + NGW) % NB == 0) load_bias(t_nxt, bias);
+      gather_load<BR, WIDE>(P, t_nxt, n_nxt, lane, rows);
+      if (q + 2 * NGW < nbatch) prefetch_row(P, t2, n2);
+      n_nxt = n2; t_nxt = t2;
+      if (pn) { n_pf = __ldg(pn); t_pf = t_seek; }
+    }
+    if (st) st[3] = clock64();
+  }
+}
 
 // fill the static part of a W1 image pair (hi, lo) from global parameters
 __device__ __forceinline__ void fill_w1_images(const CellParams& P, uint8_t* hi, uint8_t* lo, int tid, int nthr) {

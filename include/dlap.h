@@ -202,11 +202,12 @@ int dlap_macro_bwd(const dlap_plan* plan, const float* macro, const dlap_tensors
 int dlap_weights(const dlap_plan* plan, const float* u, const uint8_t* mask, const float* row_stats,
                  int normalized, float* w_out, void* stream);
 
-/* Diagnostics (no counterpart in the reference): when `stamps` is a device buffer of 2*256*16 int64, every
- * following tensor-core dlap_cell_bwd (first half of the buffer) and dlap_cell_fwd (second half) launch makes
- * CTA 0 record clock64() at fixed points of each of its first 256 tiles (see the DLAP_STAMP sites in
- * csrc/cell_bwd_tc.cu, csrc/cell_fwd_tc.cu).  NULL switches it off.  scripts/bwd_timeline.py turns the stamps
- * into per-phase cycle counts. */
+/* Diagnostics (no counterpart in the reference): when `stamps` is a device buffer of 3*256*16 int64, every
+ * following tensor-core dlap_cell_bwd (first third of the buffer: epilogue and MMA warps per tile; last third:
+ * one gather warp per batch) and dlap_cell_fwd (second third) launch makes CTA 0 record clock64() at fixed
+ * points of each of its first 256 tiles / batches (see the DLAP_STAMP sites in csrc/cell_bwd_tc.cu,
+ * csrc/cell_fwd_tc.cu and gather_role in csrc/cell_tc.cuh).  NULL switches it off.  scripts/bwd_timeline.py
+ * turns the stamps into per-phase cycle counts. */
 int dlap_debug_timeline(long long* stamps);
 
 /* Hardware self-test of the tensor-core plumbing (no counterpart in the reference): one CTA computes

@@ -13,13 +13,14 @@ model = AssetPricingGAN({"macro_feature_dim": 178, "individual_feature_dim": 46,
                          "b200_precision": "bf16x3"}).to(dev)
 for _ in range(3):
     model.zero_grad(); model(macro, x, R, mask)["loss"].backward()
-st = torch.zeros(2 * 256 * 16, dtype=torch.int64, device=dev)
+st = torch.zeros(3 * 256 * 16, dtype=torch.int64, device=dev)
 _lib.call("dlap_debug_timeline", st.data_ptr())
 model.zero_grad(); model(macro, x, R, mask)["loss"].backward()
 torch.cuda.synchronize()
 _lib.call("dlap_debug_timeline", None)
 s = st[:256 * 16].view(256, 16).cpu().double()
-f = st[256 * 16:].view(256, 16).cpu().double()
+f = st[256 * 16:2 * 256 * 16].view(256, 16).cpu().double()
+gb = st[2 * 256 * 16:].view(256, 16).cpu().double()
 ntile = int((s[:, 0] > 0).sum())
 lo, hi = 5, max(ntile - 5, 7)
 print('tiles of CTA 0:', ntile)
@@ -32,20 +33,21 @@ print("MMA: wait DZ2_FULL -> issued WG2+DG", d(8, 9), "| L2(i+1) incl. wait h1",
       "| WG1 + L1(i+2) issue", d(11, 12), "| next wait DZ2_FULL", d(12, 8, 1))
 
 def gd(a, b, shift=0):
-    idx = torch.arange(10, 2 * ntile - 12)
-    return float((s[idx + shift, b] - s[idx, a]).mean())
-print("BWD gather warp per 32-row share: period", gd(6, 6, 1), "| wait XOP_EMPTY", gd(6, 7), "| convert groups 0-2", gd(7, 13),
-      "| STS A + issue B loads", gd(13, 14), "| convert groups 3-5 + arrive", gd(14, 15), "| STS B + prefetch + issue A loads", gd(15, 6, 1))
+    nb = int((gb[:, 0] > 0).sum())
+    idx = torch.arange(4, max(nb - 6, 6))
+    return float((gb[idx + shift, b] - gb[idx, a]).mean())
+print("BWD gather warp per 16-row batch (8 batches per tile over 3 warps): period", gd(0, 0, 1), "| wait XOP_EMPTY", gd(0, 1),
+      "| convert (waits for the row loads) + arrive", gd(1, 2), "| issue next loads", gd(2, 3), "| loop tail", gd(3, 0, 1))
 
 
 def fd(a, b, shift=0, step=1):
     idx = torch.arange(lo, hi - 2, step)
     return float((f[idx + shift, b] - f[idx, a]).mean())
-print("FWD gather warp: period", fd(0, 0, 1), "| STS (waits for loads)", fd(0, 1), "| issue loads", fd(1, 2),
-      "| wait XOP_EMPTY", fd(2, 3), "| convert", fd(3, 4), "| loop tail", fd(4, 0, 1))
+print("FWD gather warp 4 per 32-row batch (4 batches per tile over 7 warps): period", fd(0, 0, 1), "| wait XOP_EMPTY", fd(0, 1),
+      "| convert (waits for the row loads) + arrive", fd(1, 2), "| issue next loads", fd(2, 3), "| loop tail", fd(3, 0, 1))
 print("FWD MMA: wait XOP_FULL(i) after L2(i-2).. L1 issue", fd(8, 9), "| L1 issued -> H1_FULL(i-1) waited", fd(9, 10, -1) if lo > 0 else 0,
       "| L2 issue", fd(10, 11), "| period", fd(8, 8, 1))
 print("FWD epilogue (even tiles): D1_FULL -> E1 done", fd(12, 13, 0, 2), "| -> D2_FULL", fd(13, 14, 0, 2), "| E2+outputs", fd(14, 15, 0, 2),
       "| period per 2 tiles", fd(12, 12, 2, 2))
-print("FWD chain for tile i: gather done(4) -> L1 start(8)", fd(4, 8), "| L1 issued(9) -> D1_FULL seen(12)", fd(9, 12, 0, 2),
+print("FWD chain for tile i:", "| L1 issued(9) -> D1_FULL seen(12)", fd(9, 12, 0, 2),
       "| E1 done(13) -> L2 start(10)", fd(13, 10, 0, 2), "| L2 issued(11) -> D2_FULL seen(14)", fd(11, 14, 0, 2))
