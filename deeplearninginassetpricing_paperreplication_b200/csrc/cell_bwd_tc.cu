@@ -33,15 +33,23 @@ constexpr int NEPI = 16;                               // epilogue warps
 constexpr int BR = 16;                                   // rows per gather batch (32 registers in flight per lane)
 constexpr int NB = TILE / BR;                            // batches per tile
 constexpr int NGW = 3;                                   // gather warps (0, 2, 3)
+constexpr int NXS = 3;                                   // X image slots
+constexpr uint32_t G5_BLK = N1 * 16;                     // one k-group of a W1 image: [N1][8] bf16
+constexpr uint32_t W1_STATIC = (KG1 - 1) * G5_BLK;       // k-groups 0..4
 constexpr uint32_t DPS_IMG = TILE * 16;                // one group: [cell][8 moments]
 
 struct SmemB {
   uint8_t* base;
+  // X images: NXS slots, so the gather warps run a full tile ahead of the last reader (dW1) of a slot
   __device__ uint8_t* xh(int sl) const { return base + sl * 2 * X_IMG; }
   __device__ uint8_t* xl(int sl) const { return xh(sl) + X_IMG; }
-  __device__ uint8_t* w1h(int sl) const { return base + 4 * X_IMG + sl * 2 * W1_IMG; }
-  __device__ uint8_t* w1l(int sl) const { return w1h(sl) + W1_IMG; }
-  __device__ uint8_t* w2h() const { return base + 4 * X_IMG + 4 * W1_IMG; }
+  // W1 image: k-groups 0..4 once (static); k-group 5, which carries the per-month bias column, once per X slot.
+  // The MMA descriptor of the last K step reaches its second group through the leading-dimension offset.
+  __device__ uint8_t* w1h() const { return base + NXS * 2 * X_IMG; }
+  __device__ uint8_t* w1l() const { return w1h() + W1_STATIC; }
+  __device__ uint8_t* g5h(int sl) const { return w1l() + W1_STATIC + sl * G5_BLK; }
+  __device__ uint8_t* g5l(int sl) const { return g5h(sl) + NXS * G5_BLK; }
+  __device__ uint8_t* w2h() const { return base + NXS * 2 * X_IMG + 2 * W1_STATIC + 2 * NXS * G5_BLK; }
   __device__ uint8_t* w2l() const { return w2h() + W2_IMG; }
   // per slot: [H hi (8 groups) | DPRE hi (1 group) | H lo | DPRE lo]: dz1 (written over h1) and dpre are
   // adjacent, so one MN-major B operand of 9 groups (N = 72) feeds dW1x and dWq in the same MMA
@@ -57,10 +65,10 @@ struct SmemB {
   __device__ uint64_t* bars() const { return reinterpret_cast<uint64_t*>(red() + NEPI * 32 + 32); }
   __device__ uint32_t* tmem_slot() const { return reinterpret_cast<uint32_t*>(bars() + 24); }
 };
-constexpr size_t SMEM_B_BYTES = (size_t)4 * X_IMG + 4 * W1_IMG + 2 * W2_IMG + 6 * H_IMG + 4 * DPS_IMG +
+constexpr size_t SMEM_B_BYTES = (size_t)NXS * 2 * X_IMG + 2 * W1_STATIC + 2 * NXS * G5_BLK + 2 * W2_IMG + 6 * H_IMG + 4 * DPS_IMG +
                                 128 * 4 + (NEPI * 32 + 32) * 4 + 24 * 8 + 16 + 128;
 
-enum { B_XOP_FULL = 2, B_XOP_EMPTY = 4, B_D1_FULL = 6, B_H1_FULL = 8,
+enum { B_XOP_FULL = 0, B_XOP_EMPTY = 3, B_D1_FULL = 6, B_H1_FULL = 8,
        B_W1_DONE = 10, B_D2_FULL = 12, B_DZ2_FULL = 13, B_D3_FULL = 14, B_DZ1_FULL = 15, B_ALL_DONE = 16 };
 
 constexpr uint32_t C_A0 = 0, C_A1 = 96, C_B = 192, C_C = 256, C_W2 = 320, C_W1 = 384, TMEM_COLS = 512;   // C_W1: 72 cols
@@ -78,6 +86,21 @@ __device__ __forceinline__ float lane_transpose_sum16(float (&v)[16], int lane) 
     }
   }
   return v[0] + __shfl_xor_sync(0xffffffffu, v[0], 16);
+}
+// Same for 8 per-lane values: every lane L returns sum_lanes v[L & 7].
+__device__ __forceinline__ float lane_transpose_sum8(float (&v)[8], int lane) {
+#pragma unroll
+  for (int s = 4; s >= 1; s >>= 1) {
+    const bool up = (lane & s) != 0;
+#pragma unroll
+    for (int i = 0; i < s; ++i) {
+      const float send = up ? v[i] : v[i + s];
+      const float keep = up ? v[i + s] : v[i];
+      v[i] = keep + __shfl_xor_sync(0xffffffffu, send, s);
+    }
+  }
+  float r = v[0] + __shfl_xor_sync(0xffffffffu, v[0], 8);
+  return r + __shfl_xor_sync(0xffffffffu, r, 16);
 }
 __device__ __forceinline__ void epi_barrier() { asm volatile("bar.sync 1, 512;" ::: "memory"); }
 }  // namespace
@@ -102,9 +125,10 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
   const int Fr = round4(P.F);
 
   // ---- one-time set-up ----
-  for (int sl = 0; sl < 2; ++sl) fill_w1_images(P, s.w1h(sl), s.w1l(sl), tid, NT_B);
+  fill_w1_groups(P, s.w1h(), s.w1l(), 0, KG1 - 1, tid, NT_B);
+  for (int sl = 0; sl < NXS; ++sl) fill_w1_groups(P, s.g5h(sl), s.g5l(sl), KG1 - 1, 1, tid, NT_B);
   fill_w2_images(P, s.w2h(), s.w2l(), tid, NT_B);
-  for (int sl = 0; sl < 2; ++sl) init_x_images(s.xh(sl), s.xl(sl), tid, NT_B);
+  for (int sl = 0; sl < NXS; ++sl) init_x_images(s.xh(sl), s.xl(sl), tid, NT_B);
   for (int sl = 0; sl < 2; ++sl)
     for (int i = tid; i < (int)DPS_IMG / 4; i += NT_B) {
       reinterpret_cast<uint32_t*>(s.dph(sl))[i] = 0u;
@@ -113,10 +137,10 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
   if (tid < 64) { s.b2s()[tid] = __ldg(P.b2 + tid); s.w3s()[tid] = __ldg(P.W3 + tid); }
   if (tid == 0) {
     for (int i = 0; i < 2; ++i) {
-      mbar_init(bar + B_XOP_FULL + i, NB);   mbar_init(bar + B_XOP_EMPTY + i, 1);
       mbar_init(bar + B_D1_FULL + i, 1);     mbar_init(bar + B_H1_FULL + i, NEPI);
       mbar_init(bar + B_W1_DONE + i, 1);
     }
+    for (int i = 0; i < NXS; ++i) { mbar_init(bar + B_XOP_FULL + i, NB); mbar_init(bar + B_XOP_EMPTY + i, 1); }
     mbar_init(bar + B_D2_FULL, 1);  mbar_init(bar + B_DZ2_FULL, NEPI);
     mbar_init(bar + B_D3_FULL, 1);  mbar_init(bar + B_DZ1_FULL, NEPI);
     mbar_init(bar + B_ALL_DONE, 1);
@@ -142,17 +166,24 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
     const uint64_t w2h_m = tc::smem_desc(smem_u32(s.w2h()), 128, 64 * 16), w2l_m = tc::smem_desc(smem_u32(s.w2l()), 128, 64 * 16);
 
     auto issue_l1 = [&](int i) {
-      const int sl = i & 1, use = i >> 1;
-      mbar_wait(bar + B_XOP_FULL + sl, use & 1);
+      const int sl = i & 1, xs = i % NXS, xuse = i / NXS;
+      mbar_wait(bar + B_XOP_FULL + xs, xuse & 1);
       tc::fence_after_sync();
       if (tc::elect_one()) {
-        const uint64_t ah = tc::smem_desc(smem_u32(s.xh(sl)), X_LBO, 128), al = tc::smem_desc(smem_u32(s.xl(sl)), X_LBO, 128);
-        const uint64_t bh = tc::smem_desc(smem_u32(s.w1h(sl)), N1 * 16, 128), bl = tc::smem_desc(smem_u32(s.w1l(sl)), N1 * 16, 128);
+        const uint64_t ah = tc::smem_desc(smem_u32(s.xh(xs)), X_LBO, 128), al = tc::smem_desc(smem_u32(s.xl(xs)), X_LBO, 128);
+        const uint64_t bh = tc::smem_desc(smem_u32(s.w1h()), G5_BLK, 128), bl = tc::smem_desc(smem_u32(s.w1l()), G5_BLK, 128);
+        // last K step: k-group 4 is static, k-group 5 (bias column of this slot) sits g5 - g4 bytes further
+        const uint32_t g4h = smem_u32(s.w1h()) + (KG1 - 2) * G5_BLK, g4l = smem_u32(s.w1l()) + (KG1 - 2) * G5_BLK;
+        const uint64_t bh5 = tc::smem_desc(g4h, smem_u32(s.g5h(xs)) - g4h, 128);
+        const uint64_t bl5 = tc::smem_desc(g4l, smem_u32(s.g5l(xs)) - g4l, 128);
         const uint32_t d = tbase + (sl ? C_A1 : C_A0);
 #pragma unroll
-        for (int ks = 0; ks < KG1 / 2; ++ks)
+        for (int ks = 0; ks < KG1 / 2; ++ks) {
+          const bool last = ks == KG1 / 2 - 1;
           umma3(d, tc::desc_advance(ah, ks * 2 * X_LBO), tc::desc_advance(al, ks * 2 * X_LBO),
-                tc::desc_advance(bh, ks * 2 * N1 * 16), tc::desc_advance(bl, ks * 2 * N1 * 16), id_l1, ks == 0);
+                last ? bh5 : tc::desc_advance(bh, ks * 2 * G5_BLK), last ? bl5 : tc::desc_advance(bl, ks * 2 * G5_BLK),
+                id_l1, ks == 0);
+        }
         tc::umma_commit(bar + B_D1_FULL + sl);
       }
       __syncwarp();
@@ -172,7 +203,7 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
           tc::umma_commit(bar + B_D2_FULL);
         }
         if (MOM && !SDF) {   // moment-only step: nothing else will read X(i); dWq^T = X^T.[.. | dpre] right away
-          const uint64_t xh_m = tc::smem_desc(smem_u32(s.xh(sl)), 128, X_LBO), xl_m = tc::smem_desc(smem_u32(s.xl(sl)), 128, X_LBO);
+          const uint64_t xh_m = tc::smem_desc(smem_u32(s.xh(i % NXS)), 128, X_LBO), xl_m = tc::smem_desc(smem_u32(s.xl(i % NXS)), 128, X_LBO);
           const uint64_t bh_m = tc::smem_desc(smem_u32(s.hh(sl)), 128, KM_A), bl_m = tc::smem_desc(smem_u32(s.hl(sl)), 128, KM_A);
 #pragma unroll
           for (int ks = 0; ks < TILE / 16; ++ks)
@@ -188,7 +219,7 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
     for (int i = 0; i < my_tiles; ++i) {
       const int sl = i & 1, par = i & 1;
       const bool first = (i == 0);
-      const uint64_t xh_m = tc::smem_desc(smem_u32(s.xh(sl)), 128, X_LBO), xl_m = tc::smem_desc(smem_u32(s.xl(sl)), 128, X_LBO);
+      const uint64_t xh_m = tc::smem_desc(smem_u32(s.xh(i % NXS)), 128, X_LBO), xl_m = tc::smem_desc(smem_u32(s.xl(i % NXS)), 128, X_LBO);
       const uint64_t hh_m = tc::smem_desc(smem_u32(s.hh(sl)), 128, KM_A), hl_m = tc::smem_desc(smem_u32(s.hl(sl)), 128, KM_A);
       if (SDF) {
         // -- after E2(i): dW2 and dgrad
@@ -226,7 +257,7 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
       }
       if (tc::elect_one()) {                                   // every reader of X(i) / H(i) has been issued
         tc::umma_commit(bar + B_W1_DONE + sl);
-        tc::umma_commit(bar + B_XOP_EMPTY + sl);
+        tc::umma_commit(bar + B_XOP_EMPTY + i % NXS);
       }
       __syncwarp();
       if (i + 2 < my_tiles) issue_l1(i + 2);
@@ -239,21 +270,22 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
     const int gw = warp == 0 ? 0 : warp - 1;
     long long* tl = (P.timeline && blockIdx.x == 0 && gw == 1 && lane == 0) ? P.timeline + 256 * 16 * 2 : nullptr;
     if (gather_wide(P))
-      gather_role<BR, NGW, true, true>(P, gw, lane, tile_lo, my_tiles, s.xh(0), s.w1h(0), bar + B_XOP_FULL,
+      gather_role<BR, NGW, NXS, true, true>(P, gw, lane, tile_lo, my_tiles, s.xh(0), s.g5h(0), G5_BLK, NXS * G5_BLK, bar + B_XOP_FULL,
                                        bar + B_XOP_EMPTY, tl, 0, true);
     else
-      gather_role<BR, NGW, false, true>(P, gw, lane, tile_lo, my_tiles, s.xh(0), s.w1h(0), bar + B_XOP_FULL,
+      gather_role<BR, NGW, NXS, false, true>(P, gw, lane, tile_lo, my_tiles, s.xh(0), s.g5h(0), G5_BLK, NXS * G5_BLK, bar + B_XOP_FULL,
                                         bar + B_XOP_EMPTY, tl, 0, true);
   } else if (warp >= 4 && warp < 20) {
     // ===== epilogue: thread = (cell, 16 of the hidden units) =====
     const int ew = warp - 4, q4 = warp & 3, hf = ew >> 2, cell = q4 * 32 + lane, U0 = hf * 16;
     const bool mom_warp = MOM && hf == 3;
     const uint32_t lane_base = (uint32_t)(q4 * 32) << 16;
-    float w3acc[16], b2acc[16], daacc[16], dc_cur[8], dc_nxt[8];
-#pragma unroll
-    for (int k = 0; k < 16; ++k) w3acc[k] = b2acc[k] = daacc[k] = 0.f;
-#pragma unroll
-    for (int k = 0; k < 8; ++k) dc_cur[k] = dc_nxt[k] = 0.f;
+    // dW3 / db2 of unit U0 + (lane & 15), summed over this warp's 32 cells tile by tile (the sixteen per-cell
+    // running sums each would not fit the register budget: they spilled, and E2 crawled through local memory)
+    float w3l = 0.f, b2l = 0.f;
+    // da_t of unit U0 + (lane & 15) and dc_t of moment lane & 7 over this warp's cells, current month (and, for
+    // dc_t, the next one: E1 runs one tile ahead)
+    float dal = 0.f, dcl_cur = 0.f, dcl_nxt = 0.f;
     float du_cur = 0.f, du_nxt = 0.f;
     uint32_t m1_cur = 0u, m1_nxt = 0u;
 
@@ -348,32 +380,25 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
         tc::split8(q, hi, lo);
         *reinterpret_cast<uint4*>(s.dph(sl) + cell * 16) = hi;
         *reinterpret_cast<uint4*>(s.dpl(sl) + cell * 16) = lo;
-        if (t == cur_month) {
-#pragma unroll
-          for (int k = 0; k < 8; ++k) dc_cur[k] += q[k];
-        } else {
-#pragma unroll
-          for (int k = 0; k < 8; ++k) dc_nxt[k] += q[k];
-        }
+        tc::fence_before_sync();
+        fence_proxy_async();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar + B_H1_FULL + sl);
+        const float tot = lane_transpose_sum8(q, lane);             // after the arrival: off the critical path
+        if (t == cur_month) dcl_cur += tot; else dcl_nxt += tot;
+      } else {
+        tc::fence_before_sync();
+        fence_proxy_async();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar + B_H1_FULL + sl);
       }
-      tc::fence_before_sync();
-      fence_proxy_async();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(bar + B_H1_FULL + sl);
     };
 
     // write the finished month's da_t | dc_t partial of this CTA (all 16 epilogue warps take part)
     auto flush_month = [&](int t) {
       float* red = s.red();
-      const float tot = lane_transpose_sum16(daacc, lane);          // unit U0 + (lane & 15)
-      if (lane < 16) red[ew * 16 + lane] = SDF ? tot : 0.f;
-      if (mom_warp) {
-#pragma unroll
-        for (int k = 0; k < 8; ++k) {
-          const float sum = warp_sum(dc_cur[k]);
-          if (lane == 0) red[NEPI * 32 + q4 * 8 + k] = sum;
-        }
-      }
+      if (lane < 16) red[ew * 16 + lane] = SDF ? dal : 0.f;         // unit U0 + lane
+      if (mom_warp && lane < 8) red[NEPI * 32 + q4 * 8 + lane] = dcl_cur;
       epi_barrier();
       // CTAs that touch month t are consecutive, starting with the owner of the month's first tile
       const int seg = (int)blockIdx.x - __ldg(P.index + idx_off_ts() + t) / chunk;
@@ -390,10 +415,8 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
         out[et] = v;
       }
       epi_barrier();
-#pragma unroll
-      for (int k = 0; k < 16; ++k) daacc[k] = 0.f;
-#pragma unroll
-      for (int k = 0; k < 8; ++k) { dc_cur[k] = dc_nxt[k]; dc_nxt[k] = 0.f; }
+      dal = 0.f;
+      dcl_cur = dcl_nxt; dcl_nxt = 0.f;
     };
 
     if (my_tiles > 0) {
@@ -415,7 +438,7 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
         mbar_wait(bar + B_D2_FULL, par);
         tc::fence_after_sync();
         if (stamp) DLAP_STAMP(i, 1);
-        float v[16];
+        float v[16], cw[16];
         tc::tmem_ld16(tbase + lane_base + C_B + U0, v);
         tc::tmem_wait_ld();
         const float4* b4 = reinterpret_cast<const float4*>(s.b2s() + U0);
@@ -436,9 +459,8 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
           for (int e = 0; e < 4; ++e) {
             const int k = 4 * k4 + e;
             const float h2 = v[k];
-            w3acc[k] = fmaf(du_cur, h2, w3acc[k]);
+            cw[k] = du_cur * h2;
             v[k] = (h2 > 0.f) ? du_cur * w_[e] * dscale : 0.f;
-            b2acc[k] += v[k];
           }
         }
 #pragma unroll
@@ -453,6 +475,9 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
         __syncwarp();
         if (lane == 0) mbar_arrive(bar + B_DZ2_FULL);
         if (stamp) DLAP_STAMP(i, 2);
+        // off the critical path (the tensor core is busy with dW2 / dgrad now): this tile's dW3, db2 contributions
+        w3l += lane_transpose_sum16(cw, lane);
+        b2l += lane_transpose_sum16(v, lane);
       }
       if (i + 1 < my_tiles) do_e1(i + 1);               // overlaps dW2 / dgrad of tile i on the tensor core
       if (stamp) DLAP_STAMP(i, 3);
@@ -467,7 +492,6 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
 #pragma unroll
         for (int k = 0; k < 16; ++k) {
           v[k] = ((m1_cur >> k) & 1u) ? v[k] * dscale : 0.f;
-          daacc[k] += v[k];
         }
 #pragma unroll
         for (int g = 0; g < 2; ++g) {
@@ -481,6 +505,7 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
         __syncwarp();
         if (lane == 0) mbar_arrive(bar + B_DZ1_FULL);
         if (stamp) DLAP_STAMP(i, 5);
+        dal += lane_transpose_sum16(v, lane);                         // off the critical path
       }
       const int t_next = (i + 1 < my_tiles) ? e1_t : -1;   // do_e1(i + 1) has run
       if (t_next != t) { flush_month(t); cur_month = t_next; }
@@ -510,7 +535,7 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
     }
     // dW3 / db2: reduce over this warp's cells, then over the four lane quarters in a fixed order
     float* red = s.red();
-    const float a = lane_transpose_sum16(w3acc, lane), b = lane_transpose_sum16(b2acc, lane);
+    const float a = w3l, b = b2l;
     if (lane < 16) { red[(ew * 16 + lane) * 2] = a; red[(ew * 16 + lane) * 2 + 1] = b; }
     epi_barrier();
     const int et = tid - 128;

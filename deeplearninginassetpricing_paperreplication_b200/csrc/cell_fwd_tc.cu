@@ -136,10 +136,12 @@ __global__ void __launch_bounds__(NT_TC, 1) cell_fwd_tc_kernel(const CellParams 
     const int gw = warp == 0 ? 0 : warp - 1;
     long long* tl = (P.timeline && blockIdx.x == 0 && warp == 4 && lane == 0) ? P.timeline : nullptr;
     if (gather_wide(P))
-      gather_role<BR, NGW, true, MOM>(P, gw, lane, tile_lo, my_tiles, s.xh(0), s.w1h(0), bar + F_XOP_FULL,
+      gather_role<BR, NGW, 2, true, MOM>(P, gw, lane, tile_lo, my_tiles, s.xh(0), s.w1h(0) + (KG1 - 1) * N1 * 16,
+                                         2 * W1_IMG, W1_IMG, bar + F_XOP_FULL,
                                       bar + F_XOP_EMPTY, tl, 0, true);
     else
-      gather_role<BR, NGW, false, MOM>(P, gw, lane, tile_lo, my_tiles, s.xh(0), s.w1h(0), bar + F_XOP_FULL,
+      gather_role<BR, NGW, 2, false, MOM>(P, gw, lane, tile_lo, my_tiles, s.xh(0), s.w1h(0) + (KG1 - 1) * N1 * 16,
+                                          2 * W1_IMG, W1_IMG, bar + F_XOP_FULL,
                                        bar + F_XOP_EMPTY, tl, 0, true);
   } else if (warp >= 8) {
     // ===== epilogue: group e handles tiles with (i & 1) == e ; thread = TMEM lane = cell =====

@@ -67,7 +67,8 @@ __device__ __forceinline__ void rows_to_image(const uint64_t (&r)[ROWS], uint8_t
 // gather warp q % NGW.  A batch is fetched with coalesced loads (gather_load), waits in registers, and is
 // written into the X image of its tile's slot (rows_to_image) once the slot is free; the warp that handles
 // the first batch of a tile also writes the per-month bias column (k = 46) of the slot's W1 image:
-// a_t (units 0..63) | c_t (moments) | 0.  x0 / w10: hi image of slot 0; slots are 2 images apart.
+// a_t (units 0..63) | c_t (moments) | 0.  x0: hi X image of slot 0 (slots are 2 images apart); g5h0: the hi
+// [N1][8] block of k-group 5 of slot 0's W1 image, g5_stride bytes between slots, g5_lo bytes to the lo block.
 //
 // Loop order matters.  ptxas tracks loads with six scoreboards per warp, so a wait placed after the row loads of
 // the next batch shares a scoreboard with them and stalls for the whole gather: every consumer of a long-latency
@@ -76,9 +77,10 @@ __device__ __forceinline__ void rows_to_image(const uint64_t (&r)[ROWS], uint8_t
 // itself (a register copy at the loop end would wait for it).  Stock numbers run two batches ahead of the row
 // loads: those rows are prefetched to L2 in the meantime.  The loop starts one step early (q < 0: loads only)
 // so that the row registers have a single definition.
-template <int BR, int NGW, bool WIDE, bool MOM>
+template <int BR, int NGW, int NSLOT, bool WIDE, bool MOM>
 __device__ __forceinline__ void gather_role(const CellParams& P, int gw, int lane, int tile_lo, int my_tiles,
-                                            uint8_t* x0, uint8_t* w10, uint64_t* xop_full, uint64_t* xop_empty,
+                                            uint8_t* x0, uint8_t* g5h0, uint32_t g5_stride, uint32_t g5_lo,
+                                            uint64_t* xop_full, uint64_t* xop_empty,
                                             long long* tl /* stamps or null */, int tl_slot, bool tl_per_batch) {
   constexpr int NB = TILE / BR;
   const int nbatch = my_tiles * NB;
@@ -110,9 +112,9 @@ __device__ __forceinline__ void gather_role(const CellParams& P, int gw, int lan
     long long* st = (tl && q >= 0) ? tl + (size_t)(tl_per_batch ? q / NGW : q / NB) * 16 + tl_slot : nullptr;
     if (st && (tl_per_batch ? q / NGW : q / NB) >= 256) st = nullptr;
     if (q >= 0) {
-      const int i = q / NB, b = q % NB, sl = i & 1, use = i >> 1;
+      const int i = q / NB, b = q % NB, sl = i % NSLOT, use = i / NSLOT;
       uint8_t* xh = x0 + sl * 2 * X_IMG;
-      uint8_t* w1h = w10 + sl * 2 * W1_IMG;
+      uint8_t* g5h = g5h0 + sl * g5_stride;
       if (st) st[0] = clock64();
       __nv_bfloat16 bh[3], bl[3];
 #pragma unroll
@@ -128,9 +130,9 @@ __device__ __forceinline__ void gather_role(const CellParams& P, int gw, int lan
         for (int e = 0; e < 3; ++e) {
           const int unit = lane + 32 * e;
           if (unit < N1) {
-            const int off = ((KG1 - 1) * N1 + unit) * 16 + (ONES_K - 8 * (KG1 - 1)) * 2;
-            *reinterpret_cast<__nv_bfloat16*>(w1h + off) = bh[e];
-            *reinterpret_cast<__nv_bfloat16*>(w1h + W1_IMG + off) = bl[e];
+            const int off = unit * 16 + (ONES_K - 8 * (KG1 - 1)) * 2;
+            *reinterpret_cast<__nv_bfloat16*>(g5h + off) = bh[e];
+            *reinterpret_cast<__nv_bfloat16*>(g5h + g5_lo + off) = bl[e];
           }
         }
       }
@@ -152,10 +154,12 @@ __device__ __forceinline__ void gather_role(const CellParams& P, int gw, int lan
   }
 }
 
-// fill the static part of a W1 image pair (hi, lo) from global parameters
-__device__ __forceinline__ void fill_w1_images(const CellParams& P, uint8_t* hi, uint8_t* lo, int tid, int nthr) {
-  for (int i = tid; i < KG1 * N1 * 4; i += nthr) {      // one bf16x2 pair per step
-    const int g = i / (N1 * 4), n = (i / 4) % N1, pr = i % 4;
+// fill k-groups g0 .. g0+ng-1 of a W1 image pair (hi, lo: contiguous [ng][N1][8] blocks) from global
+// parameters; the bias column k = 46 is left zero (the gather warps write it per tile)
+__device__ __forceinline__ void fill_w1_groups(const CellParams& P, uint8_t* hi, uint8_t* lo, int g0, int ng, int tid,
+                                               int nthr) {
+  for (int i = tid; i < ng * N1 * 4; i += nthr) {       // one bf16x2 pair per step
+    const int g = g0 + i / (N1 * 4), n = (i / 4) % N1, pr = i % 4;
     const int k0 = g * 8 + pr * 2;
     float v[2];
 #pragma unroll
@@ -175,6 +179,9 @@ __device__ __forceinline__ void fill_w1_images(const CellParams& P, uint8_t* hi,
   }
 }
 // W2 image: element (row n = out unit j, k = in unit) = W2[j][k]
+__device__ __forceinline__ void fill_w1_images(const CellParams& P, uint8_t* hi, uint8_t* lo, int tid, int nthr) {
+  fill_w1_groups(P, hi, lo, 0, KG1, tid, nthr);
+}
 __device__ __forceinline__ void fill_w2_images(const CellParams& P, uint8_t* hi, uint8_t* lo, int tid, int nthr) {
   for (int i = tid; i < KG2 * 64 * 4; i += nthr) {
     const int g = i / (64 * 4), n = (i / 4) % 64, pr = i % 4;
