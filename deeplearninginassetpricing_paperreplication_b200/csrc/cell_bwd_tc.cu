@@ -19,20 +19,20 @@
 // written over the (dead) H1 of its own tile, so the epilogue of tile i+1's layer 1 runs while the
 // tensor core works on dW2/dgrad of tile i, and layer 2 of tile i+1 runs under E3 of tile i.
 //
-// 20 warps: 1 MMA issuer; 0 (also TMEM owner), 2, 3 gather + convert (batches of 16 rows are fetched with
-// coalesced loads, one row per load and a column pair per lane, split into bf16 hi/lo and stored straight into
-// the X image; batches go round-robin over the three warps); 4-19 epilogue (four warps per TMEM lane quarter; each thread handles 16 of the 64 hidden units of its cell).
+// 24 warps (80 registers per thread): 1 MMA issuer; 0 (also TMEM owner), 2, 3, 20-23 gather + convert (batches
+// of 16 rows are fetched with coalesced loads, one row per load and a column pair per lane, split into bf16
+// hi/lo and stored straight into the X image; batches go round-robin over the seven warps); 4-19 epilogue (four warps per TMEM lane quarter; each thread handles 16 of the 64 hidden units of its cell).
 #include "cell_tc.cuh"
 
 namespace dlap {
 using namespace tcl;
 
 namespace {
-constexpr int NT_B = 640;
+constexpr int NT_B = 768;
 constexpr int NEPI = 16;                               // epilogue warps
 constexpr int BR = 16;                                   // rows per gather batch (32 registers in flight per lane)
 constexpr int NB = TILE / BR;                            // batches per tile
-constexpr int NGW = 3;                                   // gather warps (0, 2, 3)
+constexpr int NGW = 7;                                   // gather warps (0, 2, 3, 20..23)
 constexpr int NXS = 3;                                   // X image slots
 constexpr uint32_t G5_BLK = N1 * 16;                     // one k-group of a W1 image: [N1][8] bf16
 constexpr uint32_t W1_STATIC = (KG1 - 1) * G5_BLK;       // k-groups 0..4
@@ -265,9 +265,9 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
     }
     if (tc::elect_one()) tc::umma_commit(bar + B_ALL_DONE);
     __syncwarp();
-  } else if (warp == 0 || warp == 2 || warp == 3) {
+  } else if (warp == 0 || warp == 2 || warp == 3 || warp >= 20) {
     // ===== gather + convert (cell_tc.cuh); stamps 4-7 of row q / NGW: loop top, slot free, converted, loads issued
-    const int gw = warp == 0 ? 0 : warp - 1;
+    const int gw = warp == 0 ? 0 : (warp < 4 ? warp - 1 : warp - 17);
     long long* tl = (P.timeline && blockIdx.x == 0 && gw == 1 && lane == 0) ? P.timeline + 256 * 16 * 2 : nullptr;
     if (gather_wide(P))
       gather_role<BR, NGW, NXS, true, true>(P, gw, lane, tile_lo, my_tiles, s.xh(0), s.g5h(0), G5_BLK, NXS * G5_BLK, bar + B_XOP_FULL,

@@ -95,6 +95,9 @@ struct MonthCursor {
     const int* ts = P.index + idx_off_ts();
     do { ++t; first = next; next = __ldg(ts + t + 1); } while (tile >= next);
     cnt = __ldg(P.index + idx_off_cnt(P.T) + t);
+    // consume the load inside this (warp-uniform, once-a-month) branch: its first consumer would otherwise be an
+    // instruction on the per-tile path, whose scoreboard wait then also catches every other load in flight
+    cnt = __shfl_sync(0xffffffffu, cnt, 0);
   }
   __device__ __forceinline__ int j0(int tile) const { return (tile - first) * TILE; }
   __device__ __forceinline__ int ncell(int tile) const { return min(TILE, cnt - (tile - first) * TILE); }
