@@ -13,6 +13,13 @@
 // Tiles are the valid-cell tiles of dlap_panel_index (<= 128 unmasked stocks of one month, gathered row
 // by row); masked cells contribute exactly 0 to every gradient and are never visited.
 //
+// Per-month sums.  X carries a ones column (k = 46), so row 46 of the dW1 accumulator is sum_cells [dz1 | dpre]
+// = da_t | dc_t of the tiles accumulated so far: nothing has to be summed over cells by the CUDA cores.  A CTA
+// owns a CONTIGUOUS range of tiles, so a month's tiles are consecutive; when the month changes, the epilogue
+// threads that own that TMEM lane wait for the month's last dW1 MMA, copy the row out as this CTA's partial
+// of the month and write zeros back.  dW3 and db2 (sums over all tiles of the CTA) are reduced over the 32
+// cells of a warp tile by tile with shuffles and kept as one value per lane.
+//
 // Scheduling.  A CTA owns a CONTIGUOUS range of tiles, so the tiles of one month are consecutive: the
 // per-month sums (da_t, dc_t) and the per-CTA sums (dW3, db2) are accumulated in registers per cell and
 // reduced across cells only when the month changes / at the end.  H1 is double buffered and dz1 is
@@ -240,6 +247,13 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
         __syncwarp();
         if (lane == 0) DLAP_STAMP(i, 9);
       }
+      if (!SDF) {              // moment-only: the one reader of X(i) / H(i), dWq(i), was issued by issue_l2(i); the
+        if (tc::elect_one()) { // epilogue may wait for it (month change) before it lets issue_l2(i + 1) go
+          tc::umma_commit(bar + B_W1_DONE + sl);
+          tc::umma_commit(bar + B_XOP_EMPTY + i % NXS);
+        }
+        __syncwarp();
+      }
       if (i + 1 < my_tiles) issue_l2(i + 1);            // runs under E3(i)
       if (lane == 0) DLAP_STAMP(i, 10);
       if (SDF) {
@@ -254,12 +268,12 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
                   tc::desc_advance(hh_m, ks * 256), tc::desc_advance(hl_m, ks * 256), id_w1q, first && ks == 0);
         }
         __syncwarp();
+        if (tc::elect_one()) {                                 // every reader of X(i) / H(i) has been issued
+          tc::umma_commit(bar + B_W1_DONE + sl);
+          tc::umma_commit(bar + B_XOP_EMPTY + i % NXS);
+        }
+        __syncwarp();
       }
-      if (tc::elect_one()) {                                   // every reader of X(i) / H(i) has been issued
-        tc::umma_commit(bar + B_W1_DONE + sl);
-        tc::umma_commit(bar + B_XOP_EMPTY + i % NXS);
-      }
-      __syncwarp();
       if (i + 2 < my_tiles) issue_l1(i + 2);
       if (lane == 0) DLAP_STAMP(i, 12);
     }
@@ -283,9 +297,7 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
     // dW3 / db2 of unit U0 + (lane & 15), summed over this warp's 32 cells tile by tile (the sixteen per-cell
     // running sums each would not fit the register budget: they spilled, and E2 crawled through local memory)
     float w3l = 0.f, b2l = 0.f;
-    // da_t of unit U0 + (lane & 15) and dc_t of moment lane & 7 over this warp's cells, current month (and, for
-    // dc_t, the next one: E1 runs one tile ahead)
-    float dal = 0.f, dcl_cur = 0.f, dcl_nxt = 0.f;
+
     float du_cur = 0.f, du_nxt = 0.f;
     uint32_t m1_cur = 0u, m1_nxt = 0u;
 
@@ -329,7 +341,7 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
       }
       if (i + 1 < my_tiles) load_n(i + 1);
     };
-    int cur_month = 0, e1_t = 0;
+    int e1_t = 0;
     uint32_t gi_cur = 0u, gi_nxt = 0u;                   // dense cell number (dropout key) of tile i / i+1
 
     const float dscale = DROP ? P.drop_scale : 1.f;
@@ -380,50 +392,54 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
         tc::split8(q, hi, lo);
         *reinterpret_cast<uint4*>(s.dph(sl) + cell * 16) = hi;
         *reinterpret_cast<uint4*>(s.dpl(sl) + cell * 16) = lo;
-        tc::fence_before_sync();
-        fence_proxy_async();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(bar + B_H1_FULL + sl);
-        const float tot = lane_transpose_sum8(q, lane);             // after the arrival: off the critical path
-        if (t == cur_month) dcl_cur += tot; else dcl_nxt += tot;
-      } else {
-        tc::fence_before_sync();
-        fence_proxy_async();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(bar + B_H1_FULL + sl);
       }
+      tc::fence_before_sync();
+      fence_proxy_async();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar + B_H1_FULL + sl);
     };
 
-    // write the finished month's da_t | dc_t partial of this CTA (all 16 epilogue warps take part)
-    auto flush_month = [&](int t) {
-      float* red = s.red();
-      if (lane < 16) red[ew * 16 + lane] = SDF ? dal : 0.f;         // unit U0 + lane
-      if (mom_warp && lane < 8) red[NEPI * 32 + q4 * 8 + lane] = dcl_cur;
-      epi_barrier();
+    // The finished month's da_t | dc_t partial of this CTA: row 46 of the dW1 accumulator (M = 64 layout: TMEM
+    // lane 32*(46/16) + 46%16 = 78, i.e. lane 14 of the third lane quarter), read and reset to zero.  i_last: the
+    // month's last tile; its dW1 MMA must be complete, and the next one cannot start before these threads have
+    // passed E3 / E1 of the following tile, so the accumulator is quiet in between.
+    auto flush_month = [&](int t, int i_last) {
+      if (q4 != 2) return;
+      mbar_wait(bar + B_W1_DONE + (i_last & 1), (i_last >> 1) & 1);
+      tc::fence_after_sync();
       // CTAs that touch month t are consecutive, starting with the owner of the month's first tile
       const int seg = (int)blockIdx.x - __ldg(P.index + idx_off_ts() + t) / chunk;
       float* out = P.dadc_part + ((size_t)t * P.tpm + seg) * 72;
-      const int et = tid - 128;                                      // 0..511
-      if (et < 64) {                                                 // unit et: quarters 0..3 in order
-        const int h = et >> 4, k = et & 15;
-        float v = 0.f;
-        for (int q = 0; q < 4; ++q) v += red[(h * 4 + q) * 16 + k];  // warps 4+4h.. are quarters 0..3
-        out[et] = v;
-      } else if (et < 72) {
-        float v = 0.f;
-        if (MOM) for (int q = 0; q < 4; ++q) v += red[NEPI * 32 + q * 8 + (et - 64)];
-        out[et] = v;
+      const uint32_t row = tbase + lane_base + C_W1;
+      {
+        float v[16];
+        tc::tmem_ld16(row + U0, v);
+        tc::tmem_wait_ld();
+        if (lane == 14) {
+#pragma unroll
+          for (int k = 0; k < 16; ++k) { out[U0 + k] = SDF ? v[k] : 0.f; v[k] = 0.f; }
+        }
+        tc::tmem_st8(row + U0, reinterpret_cast<const uint32_t*>(v));
+        tc::tmem_st8(row + U0 + 8, reinterpret_cast<const uint32_t*>(v) + 8);
       }
-      epi_barrier();
-      dal = 0.f;
-      dcl_cur = dcl_nxt; dcl_nxt = 0.f;
+      if (hf == 3) {
+        float q[8];
+        tc::tmem_ld8(row + 64, q);
+        tc::tmem_wait_ld();
+        if (lane == 14) {
+#pragma unroll
+          for (int k = 0; k < 8; ++k) { out[64 + k] = MOM ? q[k] : 0.f; q[k] = 0.f; }
+        }
+        tc::tmem_st8(row + 64, reinterpret_cast<const uint32_t*>(q));
+      }
+      tc::tmem_wait_st();
+      tc::fence_before_sync();
     };
 
     if (my_tiles > 0) {
       mc.init(P, tile_lo);
       load_n(0);
       prefetch(0);
-      cur_month = pf_t;
       do_e1(0);
     }
     for (int i = 0; i < my_tiles; ++i) {
@@ -479,6 +495,10 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
         w3l += lane_transpose_sum16(cw, lane);
         b2l += lane_transpose_sum16(v, lane);
       }
+      if (!SDF) {              // moment-only: dWq(i + 1) follows E1(i + 1) directly, so a finished month goes out first
+        const int tn = (i + 1 < my_tiles) ? pf_t : -1;
+        if (tn != t) flush_month(t, i);
+      }
       if (i + 1 < my_tiles) do_e1(i + 1);               // overlaps dW2 / dgrad of tile i on the tensor core
       if (stamp) DLAP_STAMP(i, 3);
       if (SDF) {
@@ -505,10 +525,11 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
         __syncwarp();
         if (lane == 0) mbar_arrive(bar + B_DZ1_FULL);
         if (stamp) DLAP_STAMP(i, 5);
-        dal += lane_transpose_sum16(v, lane);                         // off the critical path
       }
-      const int t_next = (i + 1 < my_tiles) ? e1_t : -1;   // do_e1(i + 1) has run
-      if (t_next != t) { flush_month(t); cur_month = t_next; }
+      if (SDF) {
+        const int t_next = (i + 1 < my_tiles) ? e1_t : -1;   // do_e1(i + 1) has run
+        if (t_next != t) flush_month(t, i);
+      }
     }
 
     // ---- per-CTA partials: accumulators live in TMEM (M = 64: row r sits in lane 32*(r/16) + r%16)
