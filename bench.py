@@ -193,6 +193,7 @@ def run_ours(args, rank, world):
     launches = sum(w.launches for w in Fn._workspaces.values()) - l0
     clocks = sampler.stop()
     cells = T * N * world
+    valid_cells = int(mask.sum()) if args.precision != "fp32" else T * N
     value = cells * args.steps / (ms * 1e-3)
 
     # end to end: every step's panel comes from pinned host memory and its loss goes back to the host.
@@ -205,10 +206,11 @@ def run_ours(args, rank, world):
     state = {"k": 0}
 
     def upload(slot):
+        # the reference's per-epoch `batch[k].to(device)` (src/train.py:69-75): mask, returns and macro series by
+        # DMA, the characteristic rows of unmasked stock-months pulled out of pinned host memory by a kernel
         with torch.cuda.stream(copy_stream):
             copy_stream.wait_event(consumed[slot])
-            for dst, src in zip(bufs[slot], host):
-                dst.copy_(src, non_blocking=True)
+            Fn.upload_panel(*host, device=dev, out=bufs[slot])
             ready[slot].record(copy_stream)
 
     def e2e_step():
@@ -228,7 +230,8 @@ def run_ours(args, rank, world):
     k2 = max(5, min(args.steps, 20))
     ms2 = timed(e2e_step, k2)
     torch.cuda.synchronize()
-    h2d = sum(t.numel() * t.element_size() for t in host)
+    # bytes that cross the bus per step: macro, returns, mask whole; of x only the rows of unmasked stock-months
+    h2d = sum(t.numel() * t.element_size() for t in (host[0], host[2], host[3])) + int(mask.sum()) * F_CHARS * 4
     e2e = cells * k2 / (ms2 * 1e-3)
 
     if rank != 0:
@@ -251,18 +254,25 @@ def run_ours(args, rank, world):
                    "precision": args.precision},
         "clocks": clocks,
         "e2e": {"value": e2e, "unit": "stock-months/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
-                "ms_per_step": ms2 / k2},
+                "ms_per_step": ms2 / k2,
+                "note": "every step: upload_panel(pinned host panel) + fwd + bwd + loss.item(); macro, returns and "
+                        "mask go by DMA, the characteristic rows of unmasked stock-months (40 %) are read out of "
+                        "pinned host memory by dlap_panel_pull, masked rows never cross the bus"},
         "gpu_launches": launches,
         "roofline": {"bound": "hbm", "kernel": "cell_bwd (recomputing per-cell backward, %s)" % args.precision,
                      "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "peak_kind": peak_kind, "kernel_ms": k_ms, "kernel_share_of_step": k_ms * args.steps / ms,
                      "traffic": ncu_traffic(),
                      "step_frac": value * ALGO_BYTES_STEP / 1e9 / peak,
-                     "tensor_tflops": 3 * 36.9e3 * T * N / (k_ms * 1e-3) / 1e12 if args.precision != "fp32" else None,
-                     "note": "algorithmic bytes = 189 B per stock-month per launch (x, R, mask read once); "
-                             "step_frac = whole step at 378 B per stock-month; the kernel is bound by tensor-core "
-                             "MMA issue + CUDA-core epilogue (138 FLOP/B), not by HBM; tensor_tflops = issued bf16 "
-                             "MMA work (3 x 36.9 kFLOP per stock-month)"},
+                     "tensor_tflops": (3 * 36.9e3 * valid_cells / (k_ms * 1e-3) / 1e12
+                                       if args.precision != "fp32" else None),
+                     "valid_fraction": valid_cells / float(T * N),
+                     "note": "algorithmic bytes = 189 B per stock-month of the dense panel per launch (x, R, mask read "
+                             "once, SURVEY.md 8d); the bf16x3 kernels visit only the unmasked stock-months "
+                             "(valid_fraction; masked cells contribute exactly 0), so their real HBM traffic is lower "
+                             "(`traffic`); step_frac = whole step at 378 B per stock-month; the kernel is bound by "
+                             "tensor-core operand bandwidth + CUDA-core epilogue (138 FLOP/B), not by HBM; "
+                             "tensor_tflops = issued bf16 MMA work (3 x 36.9 kFLOP per visited stock-month)"},
     }
     if args.precision != "fp32" and world == 1:       # the exact-fp32 CUDA-core path, for reference
         m32 = AssetPricingGAN({"macro_feature_dim": M_MACRO, "individual_feature_dim": F_CHARS,
@@ -288,7 +298,7 @@ def run_ours(args, rank, world):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=100)
+    ap.add_argument("--steps", type=int, default=500)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--precision", default="bf16x3", choices=["bf16x3", "fp32"],

@@ -15,7 +15,7 @@ import threading
 PKG_DIR = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(PKG_DIR)
 CSRC = os.path.join(PKG_DIR, "csrc")
-LIB_PATH = os.environ.get("DLAP_LIB_EXP") or os.path.join(PKG_DIR, "libdlap_b200.so")
+LIB_PATH = os.path.join(PKG_DIR, "libdlap_b200.so")
 SOURCES = ("capi.cu", "cell_fwd.cu", "cell_bwd.cu", "reduce.cu", "macro_lstm.cu", "tc_selftest.cu", "cell_fwd_tc.cu", "cell_bwd_tc.cu",
            "panel_index.cu")
 NVCC_FLAGS = ("-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
@@ -55,6 +55,7 @@ SIGNATURES = {
     "dlap_make_plan": (C.POINTER(DlapDims), _I, _PLAN),
     "dlap_macro_fwd": (_PLAN, _P, _TENS, _P, _P, _P, _P, _P, _P, _P, _P, _P),
     "dlap_panel_index": (_PLAN, _P, _P, _P),
+    "dlap_panel_pull": (_PLAN, _P, _P, _P, _P),
     "dlap_cell_fwd": (_PLAN, _P, _P, _P, _P, _TENS, _P, _P, _P, _P, _P, _I, C.c_float, C.c_uint64, _P),
     "dlap_row_finish": (_PLAN, _P, _P, _I, _I, _P, _P, _P, _P, _P),
     "dlap_col_partial": (_PLAN, _P, _P, _P, _P, _P, _P, _P, _P),

@@ -14,6 +14,8 @@ size_t smem_bwd_bytes(int F);
 cudaError_t launch_row_finish(const double*, int, int, const int*, int, const float*, float*, float*, float*,
                               cudaStream_t);
 cudaError_t launch_panel_index(const uint8_t* mask, int T, int N, int* index, cudaStream_t st);
+cudaError_t launch_panel_pull(const float* x_host, const int* index, int T, int N, int F, float* x_dev, int sms,
+                              cudaStream_t st);
 cudaError_t launch_col_partial(const float*, const float*, const uint8_t*, const float*, const float*, int, int,
                                int, double*, float*, cudaStream_t);
 cudaError_t launch_loss_finish(const double*, int, int, int, float*, float*, double*, unsigned int*, float*,
@@ -169,6 +171,16 @@ int dlap_panel_index(const dlap_plan* plan, const uint8_t* mask, int32_t* index,
   REQ(mask); REQ(index);
   if (reinterpret_cast<uintptr_t>(index) & 15) return DLAP_E_ALIGN;
   CU(launch_panel_index(mask, plan->dims.T, plan->dims.N, index, (cudaStream_t)stream));
+  return DLAP_OK;
+}
+
+int dlap_panel_pull(const dlap_plan* plan, const float* x_host, const int32_t* index, float* x_dev, void* stream) {
+  int rc = check_plan(plan);
+  if (rc) return rc;
+  REQ(x_host); REQ(index); REQ(x_dev);
+  if ((reinterpret_cast<uintptr_t>(x_host) | reinterpret_cast<uintptr_t>(x_dev)) & 3) return DLAP_E_ALIGN;
+  CU(launch_panel_pull(x_host, index, plan->dims.T, plan->dims.N, plan->dims.F, x_dev, plan->grid_cell,
+                       (cudaStream_t)stream));
   return DLAP_OK;
 }
 

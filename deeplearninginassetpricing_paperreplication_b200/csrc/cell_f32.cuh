@@ -145,9 +145,6 @@ __device__ __forceinline__ bool gather_wide(const CellParams& P) {
 // L2 prefetch of this lane's own row (stock n of month t), issued two batches ahead of its gather_load so that
 // the loads find the row in L2 instead of paying the HBM latency of a scattered 184-B read
 __device__ __forceinline__ void prefetch_row(const CellParams& P, int t, int n) {
-#ifdef EXP_NOPF
-  return;
-#endif
   const char* a = reinterpret_cast<const char*>(P.x + ((size_t)t * P.N + n) * P.F);
   const int bytes = P.F * 4;
   asm volatile("prefetch.global.L2 [%0];" ::"l"(a));

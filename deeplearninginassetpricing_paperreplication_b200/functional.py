@@ -104,21 +104,30 @@ class Workspace:
         self.dpre = f32(p.dpre_bytes)
         self.counter = torch.zeros(1, dtype=torch.int32, device=device)
         self.launches = 0          # kernels launched through this workspace (bench bookkeeping)
-        self._index = None         # (weakref to mask tensor, its version, index) of the last mask seen
 
     def panel_index(self, mask: torch.Tensor) -> torch.Tensor:
-        """dlap_panel_index for `mask` (tensor-core kernels).  Reused only while the caller passes the very
-        same tensor object with an unchanged version counter (full-batch training loops do); any other
-        mask gets a freshly allocated index, so an index captured for a pending backward is never
-        overwritten."""
-        hit = self._index
-        if hit is not None and hit[0]() is mask and hit[1] == mask._version:
+        return panel_index(self, mask)
+
+
+_index_cache = []          # up to 4 x (weakref to a mask tensor, its version, index), most recent last
+
+
+def panel_index(ws: "Workspace", mask: torch.Tensor) -> torch.Tensor:
+    """dlap_panel_index for `mask` (tensor-core kernels, dlap_panel_pull).  Reused only while the caller passes
+    the very same tensor object with an unchanged version counter (full-batch training loops do; a loop that
+    double-buffers its panels alternates between two); any other mask gets a freshly allocated index, so an
+    index captured for a pending backward is never overwritten.  The index depends on T and N only, so one
+    small cache serves every workspace."""
+    for k, hit in enumerate(_index_cache):
+        if hit[0]() is mask and hit[1] == mask._version:
+            _index_cache.append(_index_cache.pop(k))
             return hit[2]
-        index = torch.empty(max(self.plan.index_bytes // 4, 4), dtype=torch.int32, device=self.device)
-        _lib.call("dlap_panel_index", self.pp, _ptr(mask), _ptr(index), _stream(self.device))
-        self.launches += 2
-        self._index = (weakref.ref(mask), mask._version, index)
-        return index
+    index = torch.empty(max(ws.plan.index_bytes // 4, 4), dtype=torch.int32, device=ws.device)
+    _lib.call("dlap_panel_index", ws.pp, _ptr(mask), _ptr(index), _stream(ws.device))
+    ws.launches += 2
+    _index_cache.append((weakref.ref(mask), mask._version, index))
+    del _index_cache[:-4]
+    return index
 
 
 _workspaces: Dict[Tuple, Workspace] = {}
@@ -162,6 +171,34 @@ def make_month_shard(mask_local: torch.Tensor, t0: int, T_total: int, group=None
     n_bar = (n_t / float(T_total)).to(torch.float32).contiguous()
     return MonthShard(group=group, t0=int(t0), t1=int(t0) + int(mask_local.shape[0]), T_total=int(T_total),
                       n_bar=n_bar)
+
+
+def upload_panel(macro, x, R, mask, device, out=None):
+    """`batch = {k: v.to(device) ...}` of src/train.py:69-75 for one panel: (macro, x, R, mask) on `device`,
+    enqueued on the current stream.  When x sits in pinned host memory only the rows of unmasked stock-months
+    cross the bus (dlap_panel_pull: the kernel reads them straight out of host memory; masked rows arrive as
+    zeros, which is what the loader stores there anyway); otherwise x is copied whole.  `out`: device tensors
+    to fill instead of allocating (a training loop that double-buffers its panels)."""
+    device = torch.device(device)
+    host = (macro, x, R, mask)
+    if out is None:
+        out = [None if t is None else torch.empty_like(t, device=device) for t in host]
+    d_macro, d_x, d_R, d_mask = out
+    with torch.cuda.device(device):
+        d_mask.copy_(mask, non_blocking=True)
+        if R is not None:
+            d_R.copy_(R, non_blocking=True)
+        if macro is not None:
+            d_macro.copy_(macro, non_blocking=True)
+        T, N, F = x.shape
+        if x.is_pinned() and x.dtype == torch.float32 and x.is_contiguous() and mask.dtype == torch.bool:
+            ws = workspace(T, N, F, 0, 0, device)
+            index = panel_index(ws, d_mask)
+            _lib.call("dlap_panel_pull", ws.pp, x.data_ptr(), _ptr(index), _ptr(d_x), _stream(device))
+            ws.launches += 1
+        else:
+            d_x.copy_(x, non_blocking=True)
+    return d_macro, d_x, d_R, d_mask
 
 
 def check_panel(macro, x, R, mask) -> None:

@@ -108,6 +108,14 @@ int dlap_macro_fwd(const dlap_plan* plan, const float* macro, const dlap_tensors
  * the mask contract is src/data_loader.py:50-65.  Rebuild whenever the mask bytes change.  Two launches. */
 int dlap_panel_index(const dlap_plan* plan, const uint8_t* mask, int32_t* index, void* stream);
 
+/* Panel ingest without a staging copy (the per-epoch `batch[k].to(device)` of src/train.py:69-75 for the
+ * characteristics): x_host is the [T,N,F] panel in page-locked host memory that the device can address
+ * (cudaHostAlloc / cudaHostRegister; torch: tensor.pin_memory()), x_dev the device panel.  The rows of unmasked
+ * stock-months (index: dlap_panel_index of the mask, already on the device) are read over the bus by the
+ * kernel itself; masked rows are not transferred and arrive as zeros (the loader zero-fills them anyway,
+ * src/data_loader.py:61-65).  One memset + one launch. */
+int dlap_panel_pull(const dlap_plan* plan, const float* x_host, const int32_t* index, float* x_dev, void* stream);
+
 /* SDFNetwork.forward body on every stock-month (src/model.py:251-271) and MomentNetwork.forward
  * (src/model.py:132-161 with the input of :514-518): u = MLP(x | a_t) [T,N];
  * g = tanh(Wqx.x + c_t) * R * m [8,T,N] (g NULL: moment net skipped, phase 'unconditional');

@@ -1,6 +1,7 @@
 // Micro-benchmark: how fast can one persistent CTA per SM gather scattered 184-B rows of a [T,N,46] fp32 panel?
 // Variants: warps per CTA, rows in flight per warp, load width.  Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3
 #include <cstdio>
+#include <cstring>
 #include <cstdint>
 #include <cstdlib>
 #include <vector>
@@ -146,10 +147,22 @@ __global__ void __launch_bounds__(1024, 1) tma_rows1_kernel(const float* __restr
   if (acc == 123.456f) out[0] = acc;
 }
 
-int main() {
+int main(int argc, char** argv) {
   const int T = 240, N = 10000, F = 46;
   const size_t cells = (size_t)T * N;
-  float* x; CK(cudaMalloc(&x, cells * F * 4)); CK(cudaMemset(x, 0, cells * F * 4));
+  const bool host = argc > 1;                 // any argument: the panel stays in pinned host memory (zero-copy pull)
+  float* x;
+  if (host) {
+    CK(cudaHostAlloc(&x, cells * F * 4, cudaHostAllocDefault)); memset(x, 0, cells * F * 4);
+    float* d; CK(cudaMalloc(&d, cells * F * 4));
+    cudaEvent_t a, b; cudaEventCreate(&a); cudaEventCreate(&b);
+    for (int it = 0; it < 2; ++it) {
+      cudaEventRecord(a); CK(cudaMemcpyAsync(d, x, cells * F * 4, cudaMemcpyHostToDevice)); cudaEventRecord(b);
+      CK(cudaEventSynchronize(b)); float ms; cudaEventElapsedTime(&ms, a, b);
+      printf("dense H2D copy of the panel: %.3f ms  %.1f GB/s\n", ms, cells * F * 4 / ms / 1e6);
+    }
+    cudaFree(d);
+  } else { CK(cudaMalloc(&x, cells * F * 4)); CK(cudaMemset(x, 0, cells * F * 4)); }
   float* out; CK(cudaMalloc(&out, 4));
   for (double dens : {0.4}) {
     std::vector<int> rows;

@@ -199,6 +199,40 @@ def test_forward_stages_tensor_core_visits_only_unmasked_cells():
     assert np.abs(rows[:, 3] - s["rm"].sum(axis=1)).max() < 1e-6
 
 
+@pytest.mark.parametrize("shape", [(7, 1000, 46), (3, 130, 45), (2, 257, 46)])
+def test_upload_panel_pulls_exactly_the_unmasked_rows(shape):
+    """upload_panel from pinned host memory (dlap_panel_pull): unmasked rows bit-identical to the host panel,
+    masked rows zero; returns, mask and macro series copied whole.  A step on the pulled panel is bit-identical
+    to a step on a plain .to(device) copy."""
+    from deeplearninginassetpricing_paperreplication_b200 import upload_panel
+    T, N, F = shape
+    rng = np.random.default_rng(5)
+    mask = torch.from_numpy(rng.random((T, N)) < 0.4)
+    mask[1] = False
+    x = torch.from_numpy(rng.standard_normal((T, N, F)).astype(np.float32))       # NOT zero-filled where masked
+    R = torch.from_numpy((0.1 * rng.standard_normal((T, N))).astype(np.float32)) * mask
+    macro = torch.from_numpy(rng.standard_normal((T, 178)).astype(np.float32))
+    host = [t.pin_memory() for t in (macro, x, R, mask)]
+    d_macro, d_x, d_R, d_mask = upload_panel(*host, device=dev())
+    torch.cuda.synchronize()
+    assert torch.equal(d_mask.cpu(), mask) and torch.equal(d_R.cpu(), R) and torch.equal(d_macro.cpu(), macro)
+    xd = d_x.cpu()
+    assert torch.equal(xd[mask], x[mask])
+    assert float(xd[~mask].abs().max()) == 0.0
+    if F == 46:
+        outs = []
+        for xin in (d_x, (x * mask[:, :, None]).to(dev())):
+            torch.manual_seed(3)
+            model = AssetPricingGAN({"macro_feature_dim": 178, "individual_feature_dim": F, "dropout": 0.0,
+                                     "b200_precision": "bf16x3"}).to(dev())
+            out = model(d_macro, xin, d_R, d_mask)
+            out["loss"].backward()
+            outs.append((out["loss"].detach().clone(), out["weights"].detach().clone(),
+                         model.sdf_net.fc_layers[0].weight.grad.clone()))
+        for a, b in zip(*outs):
+            assert torch.equal(a, b)
+
+
 # ---- full step against the reference's own outputs ---------------------------------------------------
 @pytest.mark.parametrize("phase", PHASES)
 def test_step_matches_reference_goldens(golden, phase):
