@@ -248,128 +248,101 @@ __global__ void __launch_bounds__(MT, 1) macro_bptt_kernel(const MacroParams P) 
   }
 }
 
-// Month-summed gradients.  Blocks 0 .. ceil(M/32)-1: 32 macro columns each, the months split across the
-// 8 warps, coefficients (dpre | dc_t) staged in shared memory, fixed-order cross-warp reduction:
-//   dW_ih[r][m] = sum_t dpre[t][r] macro[t][m]        dWq[k][m] = sum_t dc_t[k] macro[t][m]
-// Last block: the small ones (dW_hh, db, dW1[:,F:], db1, dbq), one thread per output.
-// dynamic smem: coef[T][G4+8] | red[8][G4+8][32]
+// Month-summed gradients, one warp per output row ("task"), lanes striding over the months, fixed-tree warp
+// sums; eight tasks per CTA, the coefficients (dpre | dc_t) staged in shared memory once per CTA:
+//   task m < M           dW_ih[r][m] = sum_t dpre[t][r] macro[t][m]  (r < 4H) ; dWq[k][m] = sum_t dc_t[k] macro[t][m]
+//   task M + j, j < 64   dW1[j][F+k] = sum_t da_t[j] h_t[k] ; db1[j] = sum_t da_t[j]
+//   task M + 64 + r      dW_hh[r][k] = sum_t dpre[t][r] h_{t-1}[k] ; db_ih[r] = db_hh[r] = sum_t dpre[t][r]
+//   task M + 64 + 4H + q dbq[q] = sum_t dc_t[q]
+// dynamic smem: coef[T][NR + 1]   (NR = 4H + 8; the odd pitch keeps the month-strided reads conflict-free)
 __global__ void __launch_bounds__(256) macro_wgrad_kernel(const MacroParams P) {
   extern __shared__ float sm[];
-  const int T = P.T, M = P.M, H = P.H, G4 = 4 * H, NR = G4 + KM;
+  const int T = P.T, M = P.M, H = P.H, G4 = 4 * H, NR = G4 + KM, CP = NR + 1;
   float* coef = sm;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int nmb = (M + 31) / 32;
   for (int i = tid; i < T * NR; i += 256) {
     const int t = i / NR, r = i % NR;
-    coef[i] = (r < G4) ? (P.have_sdf ? P.dpre[(size_t)t * G4 + r] : 0.f)
-                       : (P.have_mom ? __ldg(P.dadc + (size_t)t * 72 + 64 + (r - G4)) : 0.f);
+    coef[t * CP + r] = (r < G4) ? (P.have_sdf ? P.dpre[(size_t)t * G4 + r] : 0.f)
+                                : (P.have_mom ? __ldg(P.dadc + (size_t)t * 72 + 64 + (r - G4)) : 0.f);
   }
   __syncthreads();
-  if ((int)blockIdx.x < nmb) {
-    float* red = coef + (size_t)T * NR;
-    const int m = blockIdx.x * 32 + lane;
+  const int task = blockIdx.x * 8 + warp;
+  if (task < M) {
+    const int m = task;
     float acc[4 * HMAX + KM];
 #pragma unroll
     for (int r = 0; r < 4 * HMAX + KM; ++r) acc[r] = 0.f;
-    for (int t0 = warp; t0 < T; t0 += 32) {            // four months in flight per lane
-      float v[4];
+    for (int t = lane; t < T; t += 32) {
+      const float v = __ldg(P.macro + (size_t)t * M + m);
+      const float* c = coef + t * CP;
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        const int t = t0 + 8 * u;
-        v[u] = (t < T && m < M) ? __ldg(P.macro + (size_t)t * M + m) : 0.f;
-      }
+      for (int r = 0; r < 4 * HMAX + KM; ++r)
+        if (r < NR) acc[r] = fmaf(c[r], v, acc[r]);
+    }
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        const int t = t0 + 8 * u;
-        if (t < T) {
-          const float* c = coef + (size_t)t * NR;
-#pragma unroll
-          for (int r = 0; r < 4 * HMAX + KM; ++r)
-            if (r < NR) acc[r] = fmaf(c[r], v[u], acc[r]);
+    for (int r = 0; r < 4 * HMAX + KM; ++r) {
+      if (r < NR) {
+        const float v = warp_sum(acc[r]);
+        if (lane == 0) {
+          if (r < G4) { if (P.have_sdf) P.gWih[(size_t)r * M + m] = v; }
+          else if (P.have_mom) P.gWq[(size_t)(r - G4) * P.ldwq + m] = v;
         }
       }
     }
+  } else if (task < M + D1) {
+    if (!P.have_sdf) return;
+    const int j = task - M;
+    float a[HMAX], b = 0.f;
 #pragma unroll
-    for (int r = 0; r < 4 * HMAX + KM; ++r)
-      if (r < NR) red[(warp * NR + r) * 32 + lane] = acc[r];
-    __syncthreads();
-    for (int i = tid; i < NR * 32; i += 256) {
-      const int r = i >> 5, l = i & 31, mm = blockIdx.x * 32 + l;
-      float v = 0.f;
-      for (int w = 0; w < 8; ++w) v += red[(w * NR + r) * 32 + l];
-      if (mm < M) {
-        if (r < G4) { if (P.have_sdf) P.gWih[(size_t)r * M + mm] = v; }
-        else if (P.have_mom) P.gWq[(size_t)(r - G4) * P.ldwq + mm] = v;
-      }
+    for (int k = 0; k < HMAX; ++k) a[k] = 0.f;
+    for (int t = lane; t < T; t += 32) {
+      const float d = __ldg(P.dadc + (size_t)t * 72 + j);
+      b += d;
+#pragma unroll
+      for (int k = 0; k < HMAX; ++k)
+        if (k < H) a[k] = fmaf(d, __ldg(P.save + (size_t)t * 6 * H + k), a[k]);
     }
-    return;
-  }
-  // ---- small outputs: one warp per output row, lanes stride over the months, fixed-tree warp sum;
-  //      h_t and da_t staged in shared memory first (behind coef)
-  float* hsm = coef + (size_t)T * NR;                  // [T][H]
-  float* dasm = hsm + (size_t)T * (H > 0 ? H : 1);     // [T][64]
-  const bool staged = P.wgrad_staged != 0;
-  if (P.have_sdf && staged) {
-    for (int i = tid; i < T * H; i += 256) hsm[i] = __ldg(P.save + (size_t)(i / H) * 6 * H + (i % H));
-    for (int i = tid; i < T * D1; i += 256) dasm[i] = __ldg(P.dadc + (size_t)(i / D1) * 72 + (i % D1));
-  }
-  __syncthreads();
-  auto h_at = [&](int t, int k) { return staged ? hsm[t * H + k] : __ldg(P.save + (size_t)t * 6 * H + k); };
-  auto da_at = [&](int t, int j) { return staged ? dasm[t * D1 + j] : __ldg(P.dadc + (size_t)t * 72 + j); };
-  if (P.have_sdf) {
-    for (int j = warp; j < D1; j += 8) {               // dW1[j][F+k] = sum_t da_t[j] h_t[k] ; db1[j] = sum_t da_t[j]
-      float a[HMAX], b = 0.f;
+    b = warp_sum(b);
 #pragma unroll
-      for (int k = 0; k < HMAX; ++k) a[k] = 0.f;
-      for (int t = lane; t < T; t += 32) {
-        const float d = da_at(t, j);
-        b += d;
+    for (int k = 0; k < HMAX; ++k) a[k] = warp_sum(a[k]);
+    if (lane == 0) {
+      P.gb1[j] = b;
 #pragma unroll
-        for (int k = 0; k < HMAX; ++k)
-          if (k < H) a[k] = fmaf(d, h_at(t, k), a[k]);
-      }
-      b = warp_sum(b);
-#pragma unroll
-      for (int k = 0; k < HMAX; ++k) a[k] = warp_sum(a[k]);
-      if (lane == 0) {
-        P.gb1[j] = b;
-#pragma unroll
-        for (int k = 0; k < HMAX; ++k)
-          if (k < H) P.gW1[(size_t)j * P.ldw1 + P.F + k] = a[k];
-      }
+      for (int k = 0; k < HMAX; ++k)
+        if (k < H) P.gW1[(size_t)j * P.ldw1 + P.F + k] = a[k];
     }
-    for (int r = warp; r < G4; r += 8) {               // dW_hh[r][k] = sum_t dpre[t][r] h_{t-1}[k] ; db[r]
-      float a[HMAX], b = 0.f;
+  } else if (task < M + D1 + G4) {
+    if (!P.have_sdf) return;
+    const int r = task - M - D1;
+    float a[HMAX], b = 0.f;
 #pragma unroll
-      for (int k = 0; k < HMAX; ++k) a[k] = 0.f;
-      for (int t = lane; t < T; t += 32) {
-        const float d = coef[(size_t)t * NR + r];
-        b += d;
+    for (int k = 0; k < HMAX; ++k) a[k] = 0.f;
+    for (int t = lane; t < T; t += 32) {
+      const float d = coef[t * CP + r];
+      b += d;
 #pragma unroll
-        for (int k = 0; k < HMAX; ++k)
-          if (k < H) {
-            const float hp = (t > 0) ? h_at(t - 1, k) : (P.h0 ? __ldg(P.h0 + k) : 0.f);
-            a[k] = fmaf(d, hp, a[k]);
-          }
-      }
-      b = warp_sum(b);
-#pragma unroll
-      for (int k = 0; k < HMAX; ++k) a[k] = warp_sum(a[k]);
-      if (lane == 0) {
-        P.gbih[r] = b; P.gbhh[r] = b;
-#pragma unroll
-        for (int k = 0; k < HMAX; ++k)
-          if (k < H) P.gWhh[r * H + k] = a[k];
-      }
+      for (int k = 0; k < HMAX; ++k)
+        if (k < H) {
+          const float hp = (t > 0) ? __ldg(P.save + (size_t)(t - 1) * 6 * H + k) : (P.h0 ? __ldg(P.h0 + k) : 0.f);
+          a[k] = fmaf(d, hp, a[k]);
+        }
     }
-  }
-  if (P.have_mom) {
-    for (int q = warp; q < KM; q += 8) {               // dbq[q] = sum_t dc_t[q]
-      float b = 0.f;
-      for (int t = lane; t < T; t += 32) b += coef[(size_t)t * NR + G4 + q];
-      b = warp_sum(b);
-      if (lane == 0) P.gbq[q] = b;
+    b = warp_sum(b);
+#pragma unroll
+    for (int k = 0; k < HMAX; ++k) a[k] = warp_sum(a[k]);
+    if (lane == 0) {
+      P.gbih[r] = b; P.gbhh[r] = b;
+#pragma unroll
+      for (int k = 0; k < HMAX; ++k)
+        if (k < H) P.gWhh[r * H + k] = a[k];
     }
+  } else if (task < M + D1 + G4 + KM) {
+    if (!P.have_mom) return;
+    const int q = task - M - D1 - G4;
+    float b = 0.f;
+    for (int t = lane; t < T; t += 32) b += coef[t * CP + G4 + q];
+    b = warp_sum(b);
+    if (lane == 0) P.gbq[q] = b;
   }
 }
 
@@ -424,14 +397,11 @@ cudaError_t launch_macro_bwd(const MacroParams& P, cudaStream_t st) {
     if (e != cudaSuccess) return e;
   }
   const int NR = 4 * P.H + KM;
-  const size_t main_sm = ((size_t)P.T * NR + (size_t)8 * NR * 32) * 4;
-  const size_t small_sm = ((size_t)P.T * NR + (size_t)P.T * (P.H > 0 ? P.H : 1) + (size_t)P.T * D1) * 4;
-  MacroParams Q = P;
-  Q.wgrad_staged = small_sm <= 200 * 1024;
-  const size_t smem = (Q.wgrad_staged && small_sm > main_sm) ? small_sm : main_sm;
+  const size_t smem = (size_t)P.T * (NR + 1) * 4;
   cudaError_t e = cudaFuncSetAttribute(macro_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
-  macro_wgrad_kernel<<<(Q.M + 31) / 32 + 1, 256, smem, st>>>(Q);
+  const int tasks = P.M + D1 + 4 * P.H + KM;
+  macro_wgrad_kernel<<<(tasks + 7) / 8, 256, smem, st>>>(P);
   return cudaGetLastError();
 }
 

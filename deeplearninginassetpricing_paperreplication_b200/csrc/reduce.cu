@@ -123,21 +123,34 @@ __global__ void __launch_bounds__(256) col_partial_kernel(
 
 // ---- loss finish -----------------------------------------------------------------------------
 // e_ki = colsum / T_i ; L_c = mean_k mean_i e_ki^2 ; L_u = mean_i e0_i^2   src/model.py:382-385,428-431
-__global__ void __launch_bounds__(64) loss_finish_kernel(
+// 256 threads = 64 stocks x 4 groups of chunks: group q sums chunks q, q+4, ... in order, the four partial sums
+// are then added in order through shared memory (fixed summation order, four times the loads in flight).
+__global__ void __launch_bounds__(256) loss_finish_kernel(
     const double* __restrict__ col_part, int nsplit, int N, int n_total, float* __restrict__ e_out,
     float* __restrict__ ti_out, double* __restrict__ loss_part, unsigned int* __restrict__ counter,
     float* __restrict__ scalars) {
   __shared__ double red[32];
+  __shared__ double part[3][KM + 2][64];
   __shared__ bool last;
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int il = threadIdx.x & 63, q = threadIdx.x >> 6;
+  const int i = blockIdx.x * 64 + il;
   double sc = 0.0, su = 0.0;
-  if (i < N) {
-    double v[KM + 2];
+  double v[KM + 2];
 #pragma unroll
-    for (int k = 0; k < KM + 2; ++k) v[k] = 0.0;
-    for (int s = 0; s < nsplit; ++s)
+  for (int k = 0; k < KM + 2; ++k) v[k] = 0.0;
+  if (i < N) {
+    for (int s = q; s < nsplit; s += 4)
 #pragma unroll
       for (int k = 0; k < KM + 2; ++k) v[k] += col_part[((size_t)s * (KM + 2) + k) * N + i];
+  }
+  if (q > 0) {
+#pragma unroll
+    for (int k = 0; k < KM + 2; ++k) part[q - 1][k][il] = v[k];
+  }
+  __syncthreads();
+  if (q == 0 && i < N) {
+#pragma unroll
+    for (int k = 0; k < KM + 2; ++k) v[k] = ((v[k] + part[0][k][il]) + part[1][k][il]) + part[2][k][il];
     const double ti = fmax(v[KM + 1], 1.0);
     ti_out[i] = (float)ti;
 #pragma unroll
@@ -309,7 +322,7 @@ cudaError_t launch_col_partial(const float* g, const float* R, const uint8_t* ma
 cudaError_t launch_loss_finish(const double* col_part, int nsplit, int N, int n_total, float* e_out,
                                float* ti_out, double* loss_part, unsigned int* counter, float* scalars,
                                cudaStream_t st) {
-  loss_finish_kernel<<<(N + 63) / 64, 64, 0, st>>>(col_part, nsplit, N, n_total, e_out, ti_out,
+  loss_finish_kernel<<<(N + 63) / 64, 256, 0, st>>>(col_part, nsplit, N, n_total, e_out, ti_out,
                                                       loss_part, counter, scalars);
   return cudaGetLastError();
 }

@@ -294,6 +294,7 @@ class GanStepFn(torch.autograd.Function):
             _lib.call("dlap_loss_finish", ws.pp, _ptr(col), nsplit, _ptr(e), _ptr(t_i),
                       _ptr(ws.loss_part), _ptr(ws.counter), _ptr(scalars), st)
             ws.launches += 5
+        ctx.set_materialize_grads(False)      # unused outputs come back as None, not as zero tensors (fill kernels)
         ctx.save_for_backward(x, R, mask, macro, h0, c0, *params)
         ctx.opts, ctx.ws = opts, ws
         ctx.inter = (save, a_t, c_t, row_stats, scalars, g, e, t_i, index)
