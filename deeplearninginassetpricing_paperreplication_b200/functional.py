@@ -239,7 +239,7 @@ def macro_forward(ws: Workspace, macro, params, h0, c0):
     hn = torch.empty(H, dtype=torch.float32, device=dev)
     cn = torch.empty(H, dtype=torch.float32, device=dev)
     tens = _tensors(params)
-    _lib.call("dlap_macro_fwd", ws.pp, _ptr(macro), C.byref(tens), _ptr(h0), _ptr(c0), _ptr(save),
+    _timed_call("dlap_macro_fwd", dev, ws.pp, _ptr(macro), C.byref(tens), _ptr(h0), _ptr(c0), _ptr(save),
               _ptr(a_t), _ptr(c_t), _ptr(hn), _ptr(cn), _ptr(ws.dpre), _stream(dev))
     ws.launches += 2 if ws.plan.dims.M > 0 else 1
     return save, a_t, c_t, hn, cn
@@ -276,12 +276,12 @@ class GanStepFn(torch.autograd.Function):
             row_stats = torch.empty(T, RS_W, dtype=torch.float32, device=dev)
             pr = torch.empty(T, dtype=torch.float32, device=dev)
             scalars = torch.empty(SC_W, dtype=torch.float32, device=dev)
-            _lib.call("dlap_row_finish", ws.pp, _ptr(ws.row_part), _ptr(index), prec,
+            _timed_call("dlap_row_finish", dev, ws.pp, _ptr(ws.row_part), _ptr(index), prec,
                       int(opts.weighted_loss),
                       _ptr(sh.n_bar) if sh is not None else None, _ptr(row_stats), _ptr(pr),
                       _ptr(scalars), st)
             w = torch.empty(T, N, dtype=torch.float32, device=dev)
-            _lib.call("dlap_col_partial", ws.pp, _ptr(g), _ptr(R), _ptr(mask), _ptr(u), _ptr(row_stats),
+            _timed_call("dlap_col_partial", dev, ws.pp, _ptr(g), _ptr(R), _ptr(mask), _ptr(u), _ptr(row_stats),
                       _ptr(ws.col_part), _ptr(w), st)
             e = torch.empty(KM + 1, N, dtype=torch.float32, device=dev)
             t_i = torch.empty(N, dtype=torch.float32, device=dev)
@@ -291,7 +291,7 @@ class GanStepFn(torch.autograd.Function):
                 col = ws.col_part.view(ws.plan.col_splits, KM + 2, N).sum(dim=0)
                 torch.distributed.all_reduce(col, group=sh.group)
                 nsplit = 1
-            _lib.call("dlap_loss_finish", ws.pp, _ptr(col), nsplit, _ptr(e), _ptr(t_i),
+            _timed_call("dlap_loss_finish", dev, ws.pp, _ptr(col), nsplit, _ptr(e), _ptr(t_i),
                       _ptr(ws.loss_part), _ptr(ws.counter), _ptr(scalars), st)
             ws.launches += 5
         ctx.set_materialize_grads(False)      # unused outputs come back as None, not as zero tensors (fill kernels)
@@ -328,9 +328,9 @@ class GanStepFn(torch.autograd.Function):
             st = _stream(dev)
             tens = _tensors(params)
             G = torch.empty(KM + 1, N, dtype=torch.float32, device=dev)
-            _lib.call("dlap_loss_coeff", ws.pp, _ptr(e), _ptr(t_i), _ptr(g_lc) if g is not None else None,
+            _timed_call("dlap_loss_coeff", dev, ws.pp, _ptr(e), _ptr(t_i), _ptr(g_lc) if g is not None else None,
                       _ptr(g_lu), _ptr(G), st)
-            _lib.call("dlap_ds_rows", ws.pp, _ptr(g), _ptr(R), _ptr(mask), _ptr(G), _ptr(ws.ds_part), st)
+            _timed_call("dlap_ds_rows", dev, ws.pp, _ptr(g), _ptr(R), _ptr(mask), _ptr(G), _ptr(ws.ds_part), st)
             if sh is None:
                 a_loc, c_loc = a_t, c_t
             else:
@@ -348,7 +348,7 @@ class GanStepFn(torch.autograd.Function):
                 off += n
             gt = _tensors(grads)
             dadc = torch.empty(T, 72, dtype=torch.float32, device=dev)
-            _lib.call("dlap_grad_finish", ws.pp, _ptr(ws.wpart), _ptr(ws.dadc_part), _ptr(index), prec, int(want_sdf),
+            _timed_call("dlap_grad_finish", dev, ws.pp, _ptr(ws.wpart), _ptr(ws.dadc_part), _ptr(index), prec, int(want_sdf),
                       int(want_mom), C.byref(gt), _ptr(dadc), st)
             ws.launches += 4
             if sh is None:
@@ -364,7 +364,7 @@ class GanStepFn(torch.autograd.Function):
                 for f in flat:
                     f.copy_(buf[off:off + f.numel()].view_as(f))
                     off += f.numel()
-            _lib.call("dlap_macro_bwd", wsm.pp, _ptr(macro), C.byref(tens), _ptr(h0), _ptr(c0), _ptr(save),
+            _timed_call("dlap_macro_bwd", dev, wsm.pp, _ptr(macro), C.byref(tens), _ptr(h0), _ptr(c0), _ptr(save),
                       _ptr(dadc_all), _ptr(wsm.dpre), int(want_sdf), int(want_mom), C.byref(gt), st)
             ws.launches += 2 if (want_sdf and M > 0) else 1
         out = []
@@ -394,7 +394,7 @@ def sdf_weights(macro, x, mask, params, h0=None, c0=None, normalized=False, prec
         row_stats = torch.empty(T, RS_W, dtype=torch.float32, device=dev)
         pr = torch.empty(T, dtype=torch.float32, device=dev)
         scalars = torch.empty(SC_W, dtype=torch.float32, device=dev)
-        _lib.call("dlap_row_finish", ws.pp, _ptr(ws.row_part), _ptr(index), _PRECISIONS[precision], int(weighted_loss), None,
+        _timed_call("dlap_row_finish", dev, ws.pp, _ptr(ws.row_part), _ptr(index), _PRECISIONS[precision], int(weighted_loss), None,
                   _ptr(row_stats),
                   _ptr(pr), _ptr(scalars), st)
         w = torch.empty(T, N, dtype=torch.float32, device=dev)
