@@ -58,16 +58,16 @@ SIGNATURES = {
     "dlap_panel_pull": (_PLAN, _P, _P, _P, _P),
     "dlap_cell_fwd": (_PLAN, _P, _P, _P, _P, _TENS, _P, _P, _P, _P, _P, _I, C.c_float, C.c_uint64, _P),
     "dlap_row_finish": (_PLAN, _P, _P, _I, _I, _P, _P, _P, _P, _P),
-    "dlap_col_partial": (_PLAN, _P, _P, _P, _P, _P, _P, _P, _P),
+    "dlap_col_partial": (_PLAN, _P, _P, _P, _P, _P, _P, _P, _P, _P),
     "dlap_loss_finish": (_PLAN, _P, _I, _P, _P, _P, _P, _P, _P),
     "dlap_loss_finish_noalloc": (_PLAN, _P, _I, _P, _P, _P, _P),
     "dlap_loss_coeff": (_PLAN, _P, _P, _P, _P, _P, _P),
-    "dlap_ds_rows": (_PLAN, _P, _P, _P, _P, _P, _P),
+    "dlap_ds_rows": (_PLAN, _P, _P, _P, _P, _P, _P, _P),
     "dlap_cell_bwd": (_PLAN, _P, _P, _P, _P, _TENS, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _P, _P, _I,
                       C.c_float, C.c_uint64, _P),
     "dlap_grad_finish": (_PLAN, _P, _P, _P, _I, _I, _I, _TENS, _P, _P),
     "dlap_macro_bwd": (_PLAN, _P, _TENS, _P, _P, _P, _P, _P, _I, _I, _TENS, _P),
-    "dlap_weights": (_PLAN, _P, _P, _P, _I, _P, _P),
+    "dlap_weights": (_PLAN, _P, _P, _P, _P, _I, _P, _P),
     "dlap_debug_timeline": (_P,),
     "dlap_umma_selftest": (_P, _I, _P, _I, _I, _I, _I, _I, _I, _I, _I, _I, _I, _I, _I, _P, _P),
     "dlap_umma_ts_selftest": (_P, _P, _I, _I, _I, _I, _I, _I, _I, _I, _P, _P, _P),

@@ -16,16 +16,17 @@ cudaError_t launch_row_finish(const double*, int, int, const int*, int, const fl
 cudaError_t launch_panel_index(const uint8_t* mask, int T, int N, int* index, cudaStream_t st);
 cudaError_t launch_panel_pull(const float* x_host, const int* index, int T, int N, int F, float* x_dev, int sms,
                               cudaStream_t st);
-cudaError_t launch_col_partial(const float*, const float*, const uint8_t*, const float*, const float*, int, int,
-                               int, double*, float*, cudaStream_t);
+cudaError_t launch_col_partial(const float*, const float*, const uint8_t*, const float*, const float*, const int*,
+                               int, int, int, double*, float*, cudaStream_t);
 cudaError_t launch_loss_finish(const double*, int, int, int, float*, float*, double*, unsigned int*, float*,
                                cudaStream_t);
 cudaError_t launch_coeff(const float*, const float*, int, const float*, const float*, float*, cudaStream_t);
-cudaError_t launch_ds_rows(const float*, const float*, const uint8_t*, const float*, int, int, int, double*,
-                           cudaStream_t);
+cudaError_t launch_ds_rows(const float*, const float*, const uint8_t*, const float*, const int*, int, int, int,
+                           double*, cudaStream_t);
 cudaError_t launch_grad_finish(const float*, int, int, int, int, const float*, int, int, const int*, float*, int,
                                float*, float*, float*, float*, float*, int, int, float*, cudaStream_t);
-cudaError_t launch_weights(const float*, const uint8_t*, const float*, int, int, int, float*, cudaStream_t);
+cudaError_t launch_weights(const float*, const uint8_t*, const float*, const int*, int, int, int, float*,
+                           cudaStream_t);
 cudaError_t launch_macro_fwd_c(const dlap_plan* plan, const float* macro, const dlap_tensors* p, const float* h0,
                                const float* c0, float* save, float* a_t, float* c_t, float* hn, float* cn,
                                float* xp, cudaStream_t st);
@@ -227,12 +228,12 @@ int dlap_row_finish(const dlap_plan* plan, const double* row_part, const int32_t
 }
 
 int dlap_col_partial(const dlap_plan* plan, const float* g, const float* R, const uint8_t* mask, const float* u,
-                     const float* row_stats, double* col_part, float* w_out, void* stream) {
+                     const float* row_stats, const int32_t* index, double* col_part, float* w_out, void* stream) {
   int rc = check_plan(plan);
   if (rc) return rc;
   REQ(mask); REQ(row_stats); REQ(col_part);
   if (w_out) REQ(u);
-  CU(launch_col_partial(g, R, mask, u, row_stats, plan->dims.T, plan->dims.N, plan->col_splits, col_part, w_out,
+  CU(launch_col_partial(g, R, mask, u, row_stats, index, plan->dims.T, plan->dims.N, plan->col_splits, col_part, w_out,
                         (cudaStream_t)stream));
   return DLAP_OK;
 }
@@ -258,11 +259,12 @@ int dlap_loss_coeff(const dlap_plan* plan, const float* e, const float* t_i, con
 }
 
 int dlap_ds_rows(const dlap_plan* plan, const float* g, const float* R, const uint8_t* mask, const float* G,
-                 double* dS_part, void* stream) {
+                 const int32_t* index, double* dS_part, void* stream) {
   int rc = check_plan(plan);
   if (rc) return rc;
   REQ(R); REQ(mask); REQ(G); REQ(dS_part);
-  CU(launch_ds_rows(g, R, mask, G, plan->dims.T, plan->dims.N, plan->row_splits, dS_part, (cudaStream_t)stream));
+  CU(launch_ds_rows(g, R, mask, G, index, plan->dims.T, plan->dims.N, plan->row_splits, dS_part,
+                    (cudaStream_t)stream));
   return DLAP_OK;
 }
 
@@ -336,11 +338,12 @@ int dlap_macro_bwd(const dlap_plan* plan, const float* macro, const dlap_tensors
 }
 
 int dlap_weights(const dlap_plan* plan, const float* u, const uint8_t* mask, const float* row_stats,
-                 int normalized, float* w_out, void* stream) {
+                 const int32_t* index, int normalized, float* w_out, void* stream) {
   int rc = check_plan(plan);
   if (rc) return rc;
   REQ(u); REQ(mask); REQ(row_stats); REQ(w_out);
-  CU(launch_weights(u, mask, row_stats, plan->dims.T, plan->dims.N, normalized, w_out, (cudaStream_t)stream));
+  CU(launch_weights(u, mask, row_stats, index, plan->dims.T, plan->dims.N, normalized, w_out,
+                    (cudaStream_t)stream));
   return DLAP_OK;
 }
 

@@ -65,11 +65,18 @@ struct CellParams {
 // and gradient.  dlap_panel_index lists, per month, the stocks with mask = 1 in ascending order and cuts
 // each list into tiles of <= 128 cells; the tensor-core kernels walk those tiles only.
 //   int32 index[]:  [0] total tiles | [4, 4+T] tile_start (exclusive prefix, [T] = total) | cnt [T] |
-//                   vidx [T, N] (16-B aligned): row t holds cnt[t] stock numbers, rest undefined
+//                   vidx [T, N] (16-B aligned): row t holds cnt[t] stock numbers, rest undefined |
+//                   rank [T, ceil(N/32)]: unmasked stocks of month t before stock 32 w
+// Per-cell intermediates of the tensor-core path (u, g) are stored "left-packed": the value of the j-th listed
+// stock of month t sits at [t*N + j].  A per-month consumer reads a contiguous run; a per-stock consumer finds
+// its position as rank[t][i / 32] + popc(ballot(mask) below its lane).
 __host__ __device__ inline int idx_off_ts() { return 4; }
 __host__ __device__ inline int idx_off_cnt(int T) { return 4 + T + 1; }
 __host__ __device__ inline long long idx_off_vidx(int T) { return (4 + 2 * T + 1 + 3) & ~3; }
-__host__ __device__ inline long long idx_ints(int T, int N) { return idx_off_vidx(T) + (long long)T * N; }
+__host__ __device__ inline long long idx_off_rank(int T, int N) { return idx_off_vidx(T) + (long long)T * N; }
+__host__ __device__ inline long long idx_ints(int T, int N) {
+  return idx_off_rank(T, N) + (long long)T * ((N + 31) / 32);
+}
 
 __device__ __forceinline__ const int* vidx_row(const CellParams& P, int t) {
   return P.index + idx_off_vidx(P.T) + (size_t)t * P.N;

@@ -150,16 +150,18 @@ __global__ void __launch_bounds__(NT_TC, 1) cell_fwd_tc_kernel(const CellParams 
     const float b3 = __ldg(P.b3);
     MonthCursor mc;
     if (e < my_tiles) mc.init(P, tile_lo + e);
-    int n_nxt = -1, t_nxt = 0;
+    int n_nxt = -1, t_nxt = 0, pos_nxt = 0;
     auto load_row = [&](int tile) {
       mc.seek(P, tile);
       t_nxt = mc.t;
-      n_nxt = (cell < mc.ncell(tile)) ? __ldg(vidx_row(P, mc.t) + mc.j0(tile) + cell) : -1;
+      pos_nxt = mc.j0(tile) + cell;               // position in the month's list: where u, g of this cell go
+      n_nxt = (cell < mc.ncell(tile)) ? __ldg(vidx_row(P, mc.t) + pos_nxt) : -1;
     };
     if (e < my_tiles) load_row(tile_lo + e);
     for (int i = e; i < my_tiles; i += 2) {
       const int tile = tile_lo + i, sl = i & 1, use = i >> 1;
       const int t = t_nxt, n = n_nxt;
+      const size_t pi = (size_t)t * P.N + pos_nxt;
       const uint32_t dA = tbase + lane_base + (sl ? COL_A1 : COL_A0), dB = tbase + lane_base + (sl ? COL_B1 : COL_B0);
       // this cell's return: issued now, consumed after both layers (HBM latency hidden); every listed cell
       // is unmasked, so m = 1 exactly where the row exists
@@ -234,12 +236,12 @@ __global__ void __launch_bounds__(NT_TC, 1) cell_fwd_tc_kernel(const CellParams 
       // -- outputs
       const float m = live ? 1.f : 0.f;
       if (live) {
-        P.u[gi] = u;
+        P.u[pi] = u;
         if (MOM) {
           const size_t plane = (size_t)P.T * P.N;
           const float rm = r * m;
 #pragma unroll
-          for (int k = 0; k < 8; ++k) P.g[(size_t)k * plane + gi] = q[k] * rm;
+          for (int k = 0; k < 8; ++k) P.g[(size_t)k * plane + pi] = q[k] * rm;
         }
       }
       double v0 = 0, v1 = 0, v2 = 0, v3 = 0;

@@ -8,7 +8,8 @@ namespace dlap {
 
 // One CTA per month: stable compaction of the stocks with mask != 0 (ascending stock number).
 __global__ void __launch_bounds__(1024) index_rows_kernel(const uint8_t* __restrict__ mask, int N,
-                                                          int* __restrict__ cnt, int* __restrict__ vidx) {
+                                                          int* __restrict__ cnt, int* __restrict__ vidx,
+                                                          int* __restrict__ rank) {
   __shared__ int wsum[32];
   const int t = blockIdx.x, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const uint8_t* row = mask + (size_t)t * N;
@@ -28,6 +29,7 @@ __global__ void __launch_bounds__(1024) index_rows_kernel(const uint8_t* __restr
       total += c;
     }
     if (v) out[base + before + __popc(b & ((1u << lane) - 1u))] = n;
+    if (lane == 0 && n < N) rank[(size_t)t * ((N + 31) >> 5) + (n >> 5)] = base + before;
     base += total;
     __syncthreads();
   }
@@ -130,7 +132,8 @@ cudaError_t launch_panel_pull(const float* x_host, const int* index, int T, int 
 }
 
 cudaError_t launch_panel_index(const uint8_t* mask, int T, int N, int* index, cudaStream_t st) {
-  index_rows_kernel<<<T, 1024, 0, st>>>(mask, N, index + idx_off_cnt(T), index + idx_off_vidx(T));
+  index_rows_kernel<<<T, 1024, 0, st>>>(mask, N, index + idx_off_cnt(T), index + idx_off_vidx(T),
+                                        index + idx_off_rank(T, N));
   index_tiles_kernel<<<1, 1024, 0, st>>>(T, index);
   return cudaGetLastError();
 }

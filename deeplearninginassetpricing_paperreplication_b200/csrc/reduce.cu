@@ -82,10 +82,11 @@ __global__ void __launch_bounds__(1024) row_finish_kernel(
 // ---- column partial sums + weights ---------------------------------------------------------------
 // per stock i over the months of one T-chunk:  sum_t g_k S_t (k<8), sum_t R m S_t, sum_t m
 // (src/model.py:376,382,428) and, fused, w = m (u - mu_t) (src/model.py:271-279).
+// `index` != null: u and g are left-packed (tensor-core kernels, cell_f32.cuh), else dense [T,N].
 __global__ void __launch_bounds__(256) col_partial_kernel(
     const float* __restrict__ g, const float* __restrict__ R, const uint8_t* __restrict__ mask,
-    const float* __restrict__ u, const float* __restrict__ row_stats, int T, int N, int tchunk,
-    double* __restrict__ col_part, float* __restrict__ w_out) {
+    const float* __restrict__ u, const float* __restrict__ row_stats, const int* __restrict__ index, int T, int N,
+    int tchunk, double* __restrict__ col_part, float* __restrict__ w_out) {
   extern __shared__ float sm[];            // S_t then mu_t for this chunk
   const int t0 = blockIdx.y * tchunk, t1 = min(T, t0 + tchunk);
   for (int t = t0 + threadIdx.x; t < t1; t += blockDim.x) {
@@ -93,8 +94,10 @@ __global__ void __launch_bounds__(256) col_partial_kernel(
     sm[tchunk + t - t0] = row_stats[(size_t)t * RS_W + RS_MU];
   }
   __syncthreads();
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= N) return;
+  const int i = blockIdx.x * blockDim.x + threadIdx.x, lane = threadIdx.x & 31;
+  const bool in = i < N;                   // whole warps stay: the packed position comes from a ballot
+  const int nw = (N + 31) >> 5;
+  const int* rank = index ? index + idx_off_rank(T, N) + (i >> 5) : nullptr;
   const size_t plane = (size_t)T * N;
   double acc[KM + 2];
 #pragma unroll
@@ -104,18 +107,22 @@ __global__ void __launch_bounds__(256) col_partial_kernel(
     const size_t gi = (size_t)t * N + i;
     const float S = sm[t - t0];
     // u and g are defined at unmasked cells only (the tensor-core kernels never visit the others)
-    const bool live = mask[gi] != 0;
-    if (w_out) w_out[gi] = live ? (__ldg(u + gi) - sm[tchunk + t - t0]) : 0.f;
+    const bool live = in && mask[gi] != 0;
+    const unsigned b = __ballot_sync(0xffffffffu, live);
+    size_t vi = gi;
+    if (index) vi = (size_t)t * N + __ldg(rank + (size_t)t * nw) + __popc(b & ((1u << lane) - 1u));
+    if (w_out && in) w_out[gi] = live ? (__ldg(u + vi) - sm[tchunk + t - t0]) : 0.f;
     if (live) {
       const float r = R ? __ldg(R + gi) : 0.f;
       acc[KM] += (double)(r * S);
       acc[KM + 1] += 1.0;
       if (g) {
 #pragma unroll
-        for (int k = 0; k < KM; ++k) acc[k] += (double)(__ldg(g + k * plane + gi) * S);
+        for (int k = 0; k < KM; ++k) acc[k] += (double)(__ldg(g + k * plane + vi) * S);
       }
     }
   }
+  if (!in) return;
   double* out = col_part + (size_t)blockIdx.y * (KM + 2) * N + i;
 #pragma unroll
   for (int k = 0; k < KM + 2; ++k) out[(size_t)k * N] = acc[k];
@@ -200,24 +207,43 @@ __global__ void coeff_kernel(const float* __restrict__ e, const float* __restric
   G[(size_t)KM * N + i] = uu * 2.f * e[(size_t)KM * N + i] * inv;
 }
 
-// dS_t partial = sum_i ( sum_k G_ki g_kti + G0_i R m )
+// dS_t partial = sum_i ( sum_k G_ki g_kti + G0_i R m ).  `index` != null: g is left-packed and the month's
+// list of unmasked stocks is walked (contiguous g, no mask read); else dense.
 __global__ void __launch_bounds__(256) ds_rows_kernel(
     const float* __restrict__ g, const float* __restrict__ R, const uint8_t* __restrict__ mask,
-    const float* __restrict__ G, int T, int N, int nchunk, double* __restrict__ dS_part) {
+    const float* __restrict__ G, const int* __restrict__ index, int T, int N, int nchunk,
+    double* __restrict__ dS_part) {
   __shared__ double red[32];
   const int t = blockIdx.x, sp = blockIdx.y;
-  const int i0 = sp * nchunk, i1 = min(N, i0 + nchunk);
   const size_t plane = (size_t)T * N;
   double acc = 0.0;
-  for (int i = i0 + threadIdx.x; i < i1; i += blockDim.x) {
-    const size_t gi = (size_t)t * N + i;
-    if (!mask[gi]) continue;                         // g is defined at unmasked cells only
-    float v = __ldg(G + (size_t)KM * N + i) * __ldg(R + gi);
-    if (g) {
+  if (index) {
+    const int cnt = index[idx_off_cnt(T) + t];
+    const int chunk = (cnt + (int)gridDim.y - 1) / (int)gridDim.y;
+    const int j0 = sp * chunk, j1 = min(cnt, j0 + chunk);
+    const int* vrow = index + idx_off_vidx(T) + (size_t)t * N;
+    for (int j = j0 + threadIdx.x; j < j1; j += blockDim.x) {
+      const int i = __ldg(vrow + j);
+      const size_t vi = (size_t)t * N + j;
+      float v = __ldg(G + (size_t)KM * N + i) * __ldg(R + (size_t)t * N + i);
+      if (g) {
 #pragma unroll
-      for (int k = 0; k < KM; ++k) v = fmaf(__ldg(G + (size_t)k * N + i), __ldg(g + k * plane + gi), v);
+        for (int k = 0; k < KM; ++k) v = fmaf(__ldg(G + (size_t)k * N + i), __ldg(g + k * plane + vi), v);
+      }
+      acc += (double)v;
     }
-    acc += (double)v;
+  } else {
+    const int i0 = sp * nchunk, i1 = min(N, i0 + nchunk);
+    for (int i = i0 + threadIdx.x; i < i1; i += blockDim.x) {
+      const size_t gi = (size_t)t * N + i;
+      if (!mask[gi]) continue;                         // g is defined at unmasked cells only
+      float v = __ldg(G + (size_t)KM * N + i) * __ldg(R + gi);
+      if (g) {
+#pragma unroll
+        for (int k = 0; k < KM; ++k) v = fmaf(__ldg(G + (size_t)k * N + i), __ldg(g + k * plane + gi), v);
+      }
+      acc += (double)v;
+    }
   }
   acc = block_sum(acc, red);
   if (threadIdx.x == 0) dS_part[(size_t)t * gridDim.y + sp] = acc;
@@ -283,22 +309,38 @@ __global__ void __launch_bounds__(256) grad_finish_kernel(
 // w = m (u - mu_t) ; normalised: w / clamp(sum_i |w| m, 1e-8)          src/model.py:581-592
 __global__ void __launch_bounds__(256) weights_kernel(
     const float* __restrict__ u, const uint8_t* __restrict__ mask, const float* __restrict__ row_stats,
-    int N, int normalized, float* __restrict__ w_out) {
+    const int* __restrict__ index /* != null: u is left-packed */, int T, int N, int normalized,
+    float* __restrict__ w_out) {
   __shared__ double red[32];
-  const int t = blockIdx.x;
+  const int t = blockIdx.x, lane = threadIdx.x & 31;
   const float mu = row_stats[(size_t)t * RS_W + RS_MU];
   const size_t base = (size_t)t * N;
+  const int* rank = index ? index + idx_off_rank(T, N) + (size_t)t * ((N + 31) >> 5) : nullptr;
+  // value of u for stock i (whole warps call it: the packed position comes from a ballot)
+  auto u_at = [&](int i, bool& live) {
+    live = i < N && mask[base + i] != 0;
+    const unsigned b = __ballot_sync(0xffffffffu, live);
+    if (!live) return 0.f;
+    const size_t vi = index ? base + __ldg(rank + (i >> 5)) + __popc(b & ((1u << lane) - 1u)) : base + i;
+    return __ldg(u + vi);
+  };
   float denom = 1.f;
   if (normalized) {
     double s = 0.0;
-    for (int i = threadIdx.x; i < N; i += blockDim.x)
-      if (mask[base + i]) s += (double)fabsf(__ldg(u + base + i) - mu);
+    for (int i0 = 0; i0 < N; i0 += blockDim.x) {
+      bool live;
+      const float v = u_at(i0 + threadIdx.x, live);
+      if (live) s += (double)fabsf(v - mu);
+    }
     s = block_sum(s, red);
     denom = fmaxf((float)s, 1e-8f);
   }
-  for (int i = threadIdx.x; i < N; i += blockDim.x) {
-    const float w = mask[base + i] ? (__ldg(u + base + i) - mu) : 0.f;
-    w_out[base + i] = normalized ? w / denom : w;
+  for (int i0 = 0; i0 < N; i0 += blockDim.x) {
+    const int i = i0 + threadIdx.x;
+    bool live;
+    const float v = u_at(i, live);
+    const float w = live ? (v - mu) : 0.f;
+    if (i < N) w_out[base + i] = normalized ? w / denom : w;
   }
 }
 
@@ -311,11 +353,11 @@ cudaError_t launch_row_finish(const double* row_part, int T, int tpm, const int*
   return cudaGetLastError();
 }
 cudaError_t launch_col_partial(const float* g, const float* R, const uint8_t* mask, const float* u,
-                               const float* row_stats, int T, int N, int nsplit, double* col_part,
-                               float* w_out, cudaStream_t st) {
+                               const float* row_stats, const int* index, int T, int N, int nsplit,
+                               double* col_part, float* w_out, cudaStream_t st) {
   const int tchunk = (T + nsplit - 1) / nsplit;
   dim3 grid((N + 255) / 256, nsplit);
-  col_partial_kernel<<<grid, 256, 2 * tchunk * sizeof(float), st>>>(g, R, mask, u, row_stats, T, N, tchunk,
+  col_partial_kernel<<<grid, 256, 2 * tchunk * sizeof(float), st>>>(g, R, mask, u, row_stats, index, T, N, tchunk,
                                                                     col_part, w_out);
   return cudaGetLastError();
 }
@@ -331,11 +373,11 @@ cudaError_t launch_coeff(const float* e, const float* ti, int N, const float* gc
   coeff_kernel<<<(N + 255) / 256, 256, 0, st>>>(e, ti, N, gc, gu, G);
   return cudaGetLastError();
 }
-cudaError_t launch_ds_rows(const float* g, const float* R, const uint8_t* mask, const float* G, int T, int N,
-                           int nsplit, double* dS_part, cudaStream_t st) {
+cudaError_t launch_ds_rows(const float* g, const float* R, const uint8_t* mask, const float* G, const int* index,
+                           int T, int N, int nsplit, double* dS_part, cudaStream_t st) {
   const int nchunk = (N + nsplit - 1) / nsplit;
   dim3 grid(T, nsplit);
-  ds_rows_kernel<<<grid, 256, 0, st>>>(g, R, mask, G, T, N, nchunk, dS_part);
+  ds_rows_kernel<<<grid, 256, 0, st>>>(g, R, mask, G, index, T, N, nchunk, dS_part);
   return cudaGetLastError();
 }
 cudaError_t launch_grad_finish(const float* wpart, int ncta, int F, int have_sdf, int have_mom,
@@ -349,9 +391,9 @@ cudaError_t launch_grad_finish(const float* wpart, int ncta, int F, int have_sdf
                                                           wq_off, dadc);
   return cudaGetLastError();
 }
-cudaError_t launch_weights(const float* u, const uint8_t* mask, const float* row_stats, int T, int N,
-                           int normalized, float* w_out, cudaStream_t st) {
-  weights_kernel<<<T, 256, 0, st>>>(u, mask, row_stats, N, normalized, w_out);
+cudaError_t launch_weights(const float* u, const uint8_t* mask, const float* row_stats, const int* index, int T,
+                           int N, int normalized, float* w_out, cudaStream_t st) {
+  weights_kernel<<<T, 256, 0, st>>>(u, mask, row_stats, index, T, N, normalized, w_out);
   return cudaGetLastError();
 }
 

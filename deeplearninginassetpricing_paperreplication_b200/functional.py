@@ -282,7 +282,7 @@ class GanStepFn(torch.autograd.Function):
                       _ptr(scalars), st)
             w = torch.empty(T, N, dtype=torch.float32, device=dev)
             _timed_call("dlap_col_partial", dev, ws.pp, _ptr(g), _ptr(R), _ptr(mask), _ptr(u), _ptr(row_stats),
-                      _ptr(ws.col_part), _ptr(w), st)
+                      _ptr(index), _ptr(ws.col_part), _ptr(w), st)
             e = torch.empty(KM + 1, N, dtype=torch.float32, device=dev)
             t_i = torch.empty(N, dtype=torch.float32, device=dev)
             if sh is None:
@@ -330,7 +330,7 @@ class GanStepFn(torch.autograd.Function):
             G = torch.empty(KM + 1, N, dtype=torch.float32, device=dev)
             _timed_call("dlap_loss_coeff", dev, ws.pp, _ptr(e), _ptr(t_i), _ptr(g_lc) if g is not None else None,
                       _ptr(g_lu), _ptr(G), st)
-            _timed_call("dlap_ds_rows", dev, ws.pp, _ptr(g), _ptr(R), _ptr(mask), _ptr(G), _ptr(ws.ds_part), st)
+            _timed_call("dlap_ds_rows", dev, ws.pp, _ptr(g), _ptr(R), _ptr(mask), _ptr(G), _ptr(index), _ptr(ws.ds_part), st)
             if sh is None:
                 a_loc, c_loc = a_t, c_t
             else:
@@ -398,6 +398,6 @@ def sdf_weights(macro, x, mask, params, h0=None, c0=None, normalized=False, prec
                   _ptr(row_stats),
                   _ptr(pr), _ptr(scalars), st)
         w = torch.empty(T, N, dtype=torch.float32, device=dev)
-        _lib.call("dlap_weights", ws.pp, _ptr(u), _ptr(mask), _ptr(row_stats), int(normalized), _ptr(w), st)
+        _lib.call("dlap_weights", ws.pp, _ptr(u), _ptr(mask), _ptr(row_stats), _ptr(index), int(normalized), _ptr(w), st)
         ws.launches += 4
     return w, hn, cn, save

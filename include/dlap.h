@@ -104,7 +104,7 @@ int dlap_macro_fwd(const dlap_plan* plan, const float* macro, const dlap_tensors
  * tiles of <= 128 cells (layout: csrc/cell_f32.cuh).  The reference runs both nets over every cell and
  * multiplies by the mask afterwards (src/model.py:261-279, :363, :376-382, :428), so a masked cell
  * contributes exactly 0 to every weight, loss and gradient; the BF16X3 kernels use this list to skip
- * those cells altogether (u and g are then written at unmasked cells only).  Integer work, bit-exact;
+ * those cells altogether (u and g are then written for unmasked cells only, left-packed per month).  Integer work, bit-exact;
  * the mask contract is src/data_loader.py:50-65.  Rebuild whenever the mask bytes change.  Two launches. */
 int dlap_panel_index(const dlap_plan* plan, const uint8_t* mask, int32_t* index, void* stream);
 
@@ -123,8 +123,9 @@ int dlap_panel_pull(const dlap_plan* plan, const float* x_host, const int32_t* i
  * dropout_p > 0 (model.train(), src/model.py:213, src/train.py:66): each hidden unit of each
  * stock-month is dropped with probability round(p*65536)/65536 by a counter-based generator keyed
  * on (dropout_seed, stock-month, layer, unit); pass the same seed to dlap_cell_bwd.
- * index: dlap_panel_index output, required for BF16X3 (row_part is then per valid-cell tile and u, g are
- * written at unmasked cells only), ignored (may be NULL) for FP32. */
+ * index: dlap_panel_index output, required for BF16X3 (row_part is then per valid-cell tile; u and g are
+ * written for unmasked cells only and left-packed: the j-th unmasked stock of month t at [t*N + j]); ignored
+ * (may be NULL) for FP32 (dense u, g). */
 int dlap_cell_fwd(const dlap_plan* plan, const float* x, const float* R, const uint8_t* mask,
                   const int32_t* index, const dlap_tensors* params, const float* a_t, const float* c_t, float* u,
                   float* g, double* row_part, int precision, float dropout_p, uint64_t dropout_seed,
@@ -142,10 +143,11 @@ int dlap_row_finish(const dlap_plan* plan, const double* row_part, const int32_t
 /* Per-stock sums over the months of each chunk: sum_t g_k S_t, sum_t R m S_t, sum_t m
  * (src/model.py:376, :382, :428) into col_part [col_splits,10,N]; fused: the demeaned weights
  * w = m (u - mu_t) (src/model.py:271-279) into w_out [T,N] when non-NULL.  g may be NULL.  u and g are
- * read at unmasked cells only. */
+ * read at unmasked cells only.  index: the valid-cell index when u and g come from the BF16X3 dlap_cell_fwd
+ * (they are then left-packed: the j-th unmasked stock of month t sits at [t*N + j]); NULL for FP32 (dense). */
 int dlap_col_partial(const dlap_plan* plan, const float* g, const float* R, const uint8_t* mask,
-                     const float* u, const float* row_stats, double* col_part, float* w_out,
-                     void* stream);
+                     const float* u, const float* row_stats, const int32_t* index, double* col_part,
+                     float* w_out, void* stream);
 
 /* e_ki = colsum / T_i, L_c = mean_k mean_i e_ki^2, L_u = mean_i e0_i^2 (src/model.py:382-385,
  * :428-431) -> e [9,N], t_i [N], scalars[0] = L_c, scalars[1] = L_u.  `nsplit` chunks are summed
@@ -175,9 +177,10 @@ int dlap_loss_finish_noalloc(const dlap_plan* plan, const double* col_part, int 
 int dlap_loss_coeff(const dlap_plan* plan, const float* e, const float* t_i, const float* gc,
                     const float* gu, float* G, void* stream);
 
-/* dS_t partials = sum_i (sum_k G_ki g_kti + G0_i R m) -> dS_part [T,row_splits] */
+/* dS_t partials = sum_i (sum_k G_ki g_kti + G0_i R m) -> dS_part [T,row_splits].  index: as for
+ * dlap_col_partial (layout of g). */
 int dlap_ds_rows(const dlap_plan* plan, const float* g, const float* R, const uint8_t* mask,
-                 const float* G, double* dS_part, void* stream);
+                 const float* G, const int32_t* index, double* dS_part, void* stream);
 
 /* Per-cell backward with activation recompute (autograd of src/model.py:261-279
  * and :152-153).  want_sdf / want_mom select the parameter groups (requires_grad semantics of
@@ -206,9 +209,9 @@ int dlap_macro_bwd(const dlap_plan* plan, const float* macro, const dlap_tensors
                    float* dpre, int want_sdf, int want_mom, const dlap_tensors* grads, void* stream);
 
 /* get_weights (src/model.py:565-594): w = m (u - mu_t); normalized != 0 divides each month by
- * clamp(sum_i |w| m, 1e-8) (the Python loop of :586-590). */
+ * clamp(sum_i |w| m, 1e-8) (the Python loop of :586-590).  index: as for dlap_col_partial (layout of u). */
 int dlap_weights(const dlap_plan* plan, const float* u, const uint8_t* mask, const float* row_stats,
-                 int normalized, float* w_out, void* stream);
+                 const int32_t* index, int normalized, float* w_out, void* stream);
 
 /* Diagnostics (no counterpart in the reference): when `stamps` is a device buffer of 3*256*16 int64, every
  * following tensor-core dlap_cell_bwd (first third of the buffer: epilogue and MMA warps per tile; last third:

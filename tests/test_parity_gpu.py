@@ -139,7 +139,7 @@ def test_forward_stages_rand_small():
 def _index_layout(T, N):
     off_ts, off_cnt = 4, 4 + T + 1
     off_vidx = (4 + 2 * T + 1 + 3) & ~3
-    return off_ts, off_cnt, off_vidx
+    return off_ts, off_cnt, off_vidx, off_vidx + T * N
 
 
 @pytest.mark.parametrize("shape,density", [((7, 1000), 0.4), ((5, 130), 0.0), ((3, 257), 1.0), ((240, 3000), 0.35),
@@ -153,7 +153,7 @@ def test_panel_index_bit_exact(shape, density):
         mask[1] = False                              # an empty month in the middle
     ws = Fn.workspace(T, N, 46, 0, 0, dev())
     idx = _np(ws.panel_index(torch.from_numpy(mask).to(dev())))
-    off_ts, off_cnt, off_vidx = _index_layout(T, N)
+    off_ts, off_cnt, off_vidx, off_rank = _index_layout(T, N)
     cnt = mask.sum(axis=1)
     tiles = (cnt + 127) // 128
     ts = np.concatenate([[0], np.cumsum(tiles)])
@@ -163,11 +163,16 @@ def test_panel_index_bit_exact(shape, density):
     vidx = idx[off_vidx:off_vidx + T * N].reshape(T, N)
     for t in range(T):
         assert np.array_equal(vidx[t, :cnt[t]], np.nonzero(mask[t])[0])
+    nw = (N + 31) // 32
+    rank = idx[off_rank:off_rank + T * nw].reshape(T, nw)
+    before = np.concatenate([np.zeros((T, 1), dtype=np.int64), np.cumsum(mask, axis=1)], axis=1)[:, 0:N:32]
+    assert np.array_equal(rank, before)
 
 
 def test_forward_stages_tensor_core_visits_only_unmasked_cells():
-    """BF16X3 forward through the raw ABI: u and g are written at unmasked cells only (poisoned buffers keep
-    their poison elsewhere), and the row partials of the valid-cell tiles add up to the oracle's row sums."""
+    """BF16X3 forward through the raw ABI: u and g are written for unmasked cells only, left-packed per month
+    (poisoned buffers keep their poison elsewhere), and the row partials of the valid-cell tiles add up to the
+    oracle's row sums."""
     g = load_golden("rand_small")
     params = golden_params(g)
     model = _model_from(params, 178).eval()
@@ -186,10 +191,12 @@ def test_forward_stages_tensor_core_visits_only_unmasked_cells():
     torch.cuda.synchronize()
     m = g["mask"]
     un, gn = _np(u), _np(gq)
-    assert np.isnan(un[~m]).all() and np.isnan(gn[:, ~m]).all()
-    assert np.abs(un[m] - s["u"][m]).max() < 1e-5 * max(1.0, np.abs(s["u"]).max())
     gref = np.transpose(s["q"], (2, 0, 1)) * s["rm"][None]
-    assert np.abs(gn[:, m] - gref[:, m]).max() < 2e-6
+    for t in range(T):                                   # the j-th unmasked stock of month t sits at [t, j]
+        c = int(m[t].sum())
+        assert np.isnan(un[t, c:]).all() and np.isnan(gn[:, t, c:]).all()
+        assert np.abs(un[t, :c] - s["u"][t, m[t]]).max(initial=0.0) < 1e-5 * max(1.0, np.abs(s["u"]).max())
+        assert np.abs(gn[:, t, :c] - gref[:, t, m[t]]).max(initial=0.0) < 2e-6
     ntiles = int(index[0])
     ts = _np(index)[4:4 + T + 1]
     rp = _np(ws.row_part)[: ntiles * 16].reshape(ntiles, 4, 4).sum(axis=1)
