@@ -102,25 +102,30 @@ __global__ void __launch_bounds__(256) col_partial_kernel(
   double acc[KM + 2];
 #pragma unroll
   for (int k = 0; k < KM + 2; ++k) acc[k] = 0.0;
+  // The kernel is latency-bound (two dependent round trips per month: mask, then values), so the loop body is
+  // branch-free -- masked lanes load from a clamped in-bounds position and their values are dropped by a
+  // select -- and the unrolled months overlap their loads.
+  const size_t ic = in ? (size_t)i : (size_t)N - 1;
 #pragma unroll 4
   for (int t = t0; t < t1; ++t) {
-    const size_t gi = (size_t)t * N + i;
+    const size_t gi = (size_t)t * N + ic;
     const float S = sm[t - t0];
     // u and g are defined at unmasked cells only (the tensor-core kernels never visit the others)
     const bool live = in && mask[gi] != 0;
     const unsigned b = __ballot_sync(0xffffffffu, live);
     size_t vi = gi;
     if (index) vi = (size_t)t * N + __ldg(rank + (size_t)t * nw) + __popc(b & ((1u << lane) - 1u));
-    if (w_out && in) w_out[gi] = live ? (__ldg(u + vi) - sm[tchunk + t - t0]) : 0.f;
-    if (live) {
-      const float r = R ? __ldg(R + gi) : 0.f;
-      acc[KM] += (double)(r * S);
-      acc[KM + 1] += 1.0;
-      if (g) {
+    if (vi >= plane) vi = plane - 1;       // a masked lane behind the last listed stock of the last month
+    const float uv = (w_out || !g) ? __ldg(u + vi) : 0.f;
+    const float r = R ? __ldg(R + gi) : 0.f;
+    float gv[KM];
 #pragma unroll
-        for (int k = 0; k < KM; ++k) acc[k] += (double)(__ldg(g + k * plane + vi) * S);
-      }
-    }
+    for (int k = 0; k < KM; ++k) gv[k] = g ? __ldg(g + k * plane + vi) : 0.f;
+    if (w_out && in) w_out[gi] = live ? (uv - sm[tchunk + t - t0]) : 0.f;
+    acc[KM] += live ? (double)(r * S) : 0.0;
+    acc[KM + 1] += live ? 1.0 : 0.0;
+#pragma unroll
+    for (int k = 0; k < KM; ++k) acc[k] += live ? (double)(gv[k] * S) : 0.0;
   }
   if (!in) return;
   double* out = col_part + (size_t)blockIdx.y * (KM + 2) * N + i;
