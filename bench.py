@@ -184,14 +184,29 @@ def run_ours(args, rank, world):
     resident = (d_macro, d_x, d_R, d_mask)
     for _ in range(max(args.warmup, 3)):
         step(resident)
+    # roofline leg: the dominant kernel bracketed by CUDA events on its stream, over a short eager run
+    Fn.kernel_timer = Fn.KernelTimer("dlap_cell_bwd")
+    timed(lambda: step(resident), 20)
+    timer, Fn.kernel_timer = Fn.kernel_timer, None
+    # the timed steps: zero_grad + forward + backward of the resident panel.  Enqueuing the ~16 launches of a
+    # step from Python costs about as much host time as they run, so the step is captured once in a CUDA
+    # graph (GraphedStep) and replayed; --eager times the plain Python loop instead.
+    if args.eager:
+        run_step, launches_per_step = (lambda: step(resident)), None
+    else:
+        model.eval()                                   # dropout is 0 anyway; GraphedStep insists on it
+        gs = model.graphed_step(*resident, phase="conditional")
+        run_step, launches_per_step = gs.step, gs.launches
+        for _ in range(3):
+            run_step()
     sampler = ClockSampler(local)
     sampler.start()
     l0 = sum(w.launches for w in Fn._workspaces.values())
-    Fn.kernel_timer = Fn.KernelTimer("dlap_cell_bwd")
-    ms = timed(lambda: step(resident), args.steps)
-    timer, Fn.kernel_timer = Fn.kernel_timer, None
-    launches = sum(w.launches for w in Fn._workspaces.values()) - l0
+    ms = timed(run_step, args.steps)
+    launches = (launches_per_step * args.steps if launches_per_step is not None
+                else sum(w.launches for w in Fn._workspaces.values()) - l0)
     clocks = sampler.stop()
+    model.train()
     cells = T * N * world
     valid_cells = int(mask.sum()) if args.precision != "fp32" else T * N
     value = cells * args.steps / (ms * 1e-3)
@@ -251,7 +266,9 @@ def run_ours(args, rank, world):
                                 f"sharded by month, {T} months x {N} stocks = {T * N} stock-months per GPU "
                                 f"on {world} GPU(s)"),
                    "l2": "inputs (442 MB panel per GPU) larger than the 126 MB L2; no flush needed",
-                   "precision": args.precision},
+                   "precision": args.precision,
+                   "step": ("python loop (eager launches)" if args.eager else
+                            "zero_grad + forward + backward captured once in a CUDA graph (GraphedStep), replayed")},
         "clocks": clocks,
         "e2e": {"value": e2e, "unit": "stock-months/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
                 "ms_per_step": ms2 / k2,
@@ -305,6 +322,7 @@ def main():
                     help="arithmetic of the per-cell contractions: bf16x3 = tcgen05 BF16 MMAs on hi/lo-split "
                          "fp32 operands (3 products per fp32 product, fp32 accumulate); fp32 = CUDA-core FFMA")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--eager", action="store_true", help="time the plain Python loop instead of the CUDA-graph replay")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", 0))
     world = int(os.environ.get("WORLD_SIZE", 1))

@@ -1,5 +1,5 @@
 """B200-native adversarial-SDF training step (drop-in for the reference's ``src.model``)."""
 from .functional import upload_panel  # noqa: F401
-from .model import AssetPricingGAN, MacroLSTM, MomentNetwork, SDFNetwork  # noqa: F401
+from .model import AssetPricingGAN, GraphedStep, MacroLSTM, MomentNetwork, SDFNetwork  # noqa: F401
 
-__all__ = ["AssetPricingGAN", "SDFNetwork", "MomentNetwork", "MacroLSTM", "upload_panel"]
+__all__ = ["AssetPricingGAN", "SDFNetwork", "MomentNetwork", "MacroLSTM", "GraphedStep", "upload_panel"]

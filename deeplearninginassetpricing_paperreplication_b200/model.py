@@ -284,6 +284,11 @@ class AssetPricingGAN(nn.Module):
             'loss_residual': zero, 'sharpe': sharpe, 'portfolio_returns': pr, 'hidden': new_hidden,
         }, moments_fn=moments)
 
+    def graphed_step(self, macro_features, individual_features, returns, mask, hidden=None,
+                     phase: str = 'conditional') -> "GraphedStep":
+        """CUDA-graph capture of zero_grad + forward + backward on a resident panel (see GraphedStep)."""
+        return GraphedStep(self, macro_features, individual_features, returns, mask, hidden, phase)
+
     def get_weights(self, macro_features, individual_features, mask, hidden=None, normalized: bool = False):
         """src/model.py:565-594."""
         return _weights(self.sdf_net, self.moment_net, macro_features, individual_features, mask, hidden,
@@ -294,6 +299,58 @@ class AssetPricingGAN(nn.Module):
         """src/model.py:596-617."""
         w, _ = self.get_weights(macro_features, individual_features, mask, hidden, normalized=normalized)
         return (w * returns * mask.float()).sum(dim=1)
+
+
+class GraphedStep:
+    """One training step -- ``model.zero_grad(); out = model(panel, phase); out['loss'].backward()``
+    (src/train.py:77-84) -- captured once in a CUDA graph and replayed: the ~15 kernel launches of a step cost
+    about as much host time as they run on the device, so a loop over a resident panel is otherwise bound by
+    Python.  ``step()`` replays the graph and returns the forward dict (static tensors, overwritten by the next
+    replay); ``p.grad`` of every parameter is overwritten, not accumulated.
+
+    The panel tensors are the ones passed in (full-batch training on a resident panel, as the reference's
+    loops do); copy new VALUES into them with ``.copy_()`` if needed, but keep the mask: its valid-cell index
+    is part of the capture.  Dropout must be off (a captured seed would repeat the same mask).  A month-sharded
+    model captures its NCCL all-reduces with the kernels; every rank must then replay in lock-step."""
+
+    def __init__(self, model: "AssetPricingGAN", macro_features, individual_features, returns, mask,
+                 hidden=None, phase: str = 'conditional', warmup: int = 3):
+        if model.training and model.sdf_net.dropout_p > 0:
+            raise ValueError("GraphedStep needs dropout off: a captured dropout seed would repeat one mask")
+        self.model, self.args = model, (macro_features, individual_features, returns, mask)
+        self.kw = {"hidden": hidden, "phase": phase}
+        dev = individual_features.device
+        side = torch.cuda.Stream(dev)
+        side.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(side):                      # warm-up off the capture stream (allocator, index)
+            for _ in range(max(warmup, 1)):
+                self._eager()
+        torch.cuda.current_stream(dev).wait_stream(side)
+        torch.cuda.synchronize(dev)
+        ws_launches = lambda: sum(w.launches for w in Fn._workspaces.values())
+        self.graph = torch.cuda.CUDAGraph()
+        model.zero_grad(set_to_none=True)
+        l0 = ws_launches()
+        try:        # the parameters' AccumulateGrad nodes were created on the warm-up stream: harmless here
+            torch.autograd.graph.set_warn_on_accumulate_grad_stream_mismatch(False)
+        except AttributeError:
+            pass
+        with torch.cuda.graph(self.graph):
+            self.out = self._eager(zero=False)
+        self.launches = ws_launches() - l0                # kernels of this library inside one replay
+
+    def _eager(self, zero=True):
+        if zero:
+            self.model.zero_grad(set_to_none=True)
+        out = self.model(*self.args, **self.kw)
+        out['loss'].backward()
+        return out
+
+    def step(self):
+        self.graph.replay()
+        return self.out
+
+    __call__ = step
 
 
 def _gather_months(pr_local, shard):

@@ -240,6 +240,41 @@ def test_upload_panel_pulls_exactly_the_unmasked_rows(shape):
             assert torch.equal(a, b)
 
 
+@pytest.mark.parametrize("precision", ["fp32", "bf16x3"])
+def test_graphed_step_replays_the_eager_step_bit_for_bit(precision):
+    """GraphedStep (zero_grad + forward + backward in one CUDA graph): every replay reproduces the eager step's
+    losses, weights and gradients exactly, also after the parameters changed in place (an optimiser step)."""
+    g = load_golden("rand_small")
+    params = golden_params(g)
+    macro, x, R, mask, _ = _panel(g)
+    model = _model_from(params, 178).eval()
+    model.precision = precision
+
+    def eager():
+        model.zero_grad(set_to_none=True)
+        out = model(macro, x, R, mask)
+        out["loss"].backward()
+        return ([out[k].detach().clone() for k in ("loss", "loss_unconditional", "weights", "portfolio_returns")],
+                {k: p.grad.clone() for k, p in model.named_parameters() if p.grad is not None})
+
+    ref_out, ref_grads = eager()
+    gs = model.graphed_step(macro, x, R, mask)
+    assert gs.launches >= 10
+    for trial in range(3):
+        if trial == 2:                                   # parameters move in place, like optimizer.step()
+            with torch.no_grad():
+                for p in model.parameters():
+                    p.mul_(1.01)
+            ref_out, ref_grads = eager()
+        out = gs.step()
+        torch.cuda.synchronize()
+        for a, key in zip(ref_out, ("loss", "loss_unconditional", "weights", "portfolio_returns")):
+            assert torch.equal(a, out[key]), key
+        for k, p in model.named_parameters():
+            if k in ref_grads:
+                assert torch.equal(ref_grads[k], p.grad), k
+
+
 # ---- full step against the reference's own outputs ---------------------------------------------------
 @pytest.mark.parametrize("phase", PHASES)
 def test_step_matches_reference_goldens(golden, phase):
