@@ -164,87 +164,117 @@ __global__ void __launch_bounds__(MT, 1) macro_fwd_kernel(const MacroParams P) {
   }
 }
 
-// BPTT: one CTA.  dynamic smem: dh[T][H].  Writes dpre[T][4H] (pre-activation gradients) to P.dpre.
+// BPTT: one CTA.  Writes dpre[T][4H] (pre-activation gradients) to P.dpre.
+// The carried state is (dh_rec, dc) per unit and every step is linear in it:
+//   dht = dhe_t + dh_rec ;  dcn = dc + a_c . dht ;  dh_rec' = A_t^T dcn + B_t^T dht ;  dc' = f_t . dcn
+// with  A_t[j][k] = Whh_i[j][k] a_i[j] + Whh_f[j][k] a_f[j] + Whh_g[j][k] a_g[j]  and  B_t[j][k] = Whh_o[j][k] a_o[j]
+// (a_* = the local derivatives of step t).  Everything that does not depend on the carried state -- dhe_t, the
+// a_*, A_t, B_t -- is computed by all threads first; the serial chain on warp 0 is then 2H shuffles + 2H FMAs
+// per step and lane, and the gate gradients d{i,f,g} = dcn a_{i,f,g}, do = dht a_o follow in parallel.
+// dynamic smem: sv[T][6H] (saved states, later S[T][2H] = dht | dcn) | Y[T][H][REC] | W1m[64][H] | Whh[4H][H]
+// record (REC = 8 + 2 HP floats, HP = H rounded up to 4): a_c f dhe . | a_i a_f a_g a_o | A[.][k] | B[.][k]
 template <int H>
 __global__ void __launch_bounds__(MT, 1) macro_bptt_kernel(const MacroParams P) {
   extern __shared__ float sm[];
   const int T = P.T;
   constexpr int G4 = 4 * H;
-  float* dh = sm;
-  float* sv_s = dh + (size_t)T * H;          // saved h,c,i,f,g,o of every month, [T][6H]
+  float* sv_s = sm;                                  // [T][6H]: h, c, i, f, g, o
+  constexpr int HP = (H + 3) & ~3, REC = 8 + 2 * HP;
+  float* Y = sv_s + (size_t)T * 6 * H;               // [T][H][REC]
+  float* w1m = Y + (size_t)T * H * REC;
+  float* whh = w1m + D1 * H;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   for (int i = tid; i < T * 6 * H; i += MT) sv_s[i] = P.save[i];
-  // dh_t = W1[:,F:]^T . da_t   (W1m staged in smem behind the coefficient table)
-  float* w1m = sv_s + (size_t)T * 12 * H;
   for (int i = tid; i < D1 * H; i += MT) w1m[i] = __ldg(P.W1 + (size_t)(i / H) * P.ldw1 + P.F + (i % H));
+  for (int i = tid; i < G4 * H; i += MT) whh[i] = __ldg(P.Whh + i);
   __syncthreads();
+  // pass 1, thread = (month, unit): dhe_t = W1[:,F:]^T . da_t and the local derivatives
   for (int i = tid; i < T * H; i += MT) {
-    const int t = i / H, k = i % H;
+    const int t = i / H, j = i % H;
     const float4* da4 = reinterpret_cast<const float4*>(P.dadc + (size_t)t * 72);
     float v0 = 0.f, v1 = 0.f;
 #pragma unroll 4
     for (int j4 = 0; j4 < D1 / 4; ++j4) {
       const float4 d = __ldg(da4 + j4);
-      v0 = fmaf(w1m[(4 * j4) * H + k], d.x, v0);     v1 = fmaf(w1m[(4 * j4 + 1) * H + k], d.y, v1);
-      v0 = fmaf(w1m[(4 * j4 + 2) * H + k], d.z, v0); v1 = fmaf(w1m[(4 * j4 + 3) * H + k], d.w, v1);
+      v0 = fmaf(w1m[(4 * j4) * H + j], d.x, v0);     v1 = fmaf(w1m[(4 * j4 + 1) * H + j], d.y, v1);
+      v0 = fmaf(w1m[(4 * j4 + 2) * H + j], d.z, v0); v1 = fmaf(w1m[(4 * j4 + 3) * H + j], d.w, v1);
     }
-    dh[i] = v0 + v1;
-  }
-  __syncthreads();
-  // Pre-pass (all threads): everything of step t that does not depend on the carried (dh_rec, dc):
-  //   co[t][j] = { a_c, a_i, a_f, a_g, a_o, f }  with  dc += dh*a_c ; d{i,f,g} = dc*a_{i,f,g} ; do = dh*a_o
-  float* co = sv_s + (size_t)T * 6 * H;
-  for (int i = tid; i < T * H; i += MT) {
-    const int t = i / H, j = i % H;
     const float* sv = sv_s + (size_t)t * 6 * H;
     const float cc = sv[H + j], gi = sv[2 * H + j], gf = sv[3 * H + j], gg = sv[4 * H + j], go = sv[5 * H + j];
     const float cprev = (t > 0) ? sv_s[(size_t)(t - 1) * 6 * H + H + j] : (P.c0 ? __ldg(P.c0 + j) : 0.f);
     const float tc = tanh_fast(cc);
-    float* c6 = co + (size_t)i * 6;
-    c6[0] = go * (1.f - tc * tc);
-    c6[1] = gg * gi * (1.f - gi);
-    c6[2] = cprev * gf * (1.f - gf);
-    c6[3] = gi * (1.f - gg * gg);
-    c6[4] = tc * go * (1.f - go);
-    c6[5] = gf;
+    float* y = Y + (size_t)i * REC;
+    y[0] = go * (1.f - tc * tc);                     // a_c
+    y[1] = gf;
+    y[2] = v0 + v1;                                  // dhe
+    y[4] = gg * gi * (1.f - gi);                     // a_i
+    y[5] = cprev * gf * (1.f - gf);                  // a_f
+    y[6] = gi * (1.f - gg * gg);                     // a_g
+    y[7] = tc * go * (1.f - go);                     // a_o
   }
   __syncthreads();
-  if (warp != 0) return;
-  // lane j < H carries (dh_rec_j, dc_j)
-  float whh_col[G4];           // Whh[r][lane] for every gate row r
+  // pass 2, thread = (month, unit k): column k of A_t and B_t
+  for (int i = tid; i < T * H; i += MT) {
+    const int t = i / H, k = i % H;
+    float* y = Y + (size_t)i * REC;
 #pragma unroll
-  for (int r = 0; r < G4; ++r) whh_col[r] = (lane < H) ? __ldg(P.Whh + r * H + lane) : 0.f;
-  float dh_rec = 0.f, dc = 0.f;
-  const int j = lane < H ? lane : 0;
-  struct Step { float a_c, a_i, a_f, a_g, a_o, gf, dhe; };
-  auto fetch = [&](int t) {
-    Step q;
-    const float* c6 = co + ((size_t)t * H + j) * 6;
-    q.a_c = c6[0]; q.a_i = c6[1]; q.a_f = c6[2]; q.a_g = c6[3]; q.a_o = c6[4]; q.gf = c6[5];
-    q.dhe = dh[t * H + j];
-    return q;
-  };
-  Step nxt = fetch(T - 1);
-  for (int t = T - 1; t >= 0; --t) {
-    const Step q = nxt;
-    if (t > 0) nxt = fetch(t - 1);
-    const float dht = q.dhe + dh_rec;
-    dc = fmaf(dht, q.a_c, dc);
-    const float di = dc * q.a_i, df = dc * q.a_f, dg = dc * q.a_g, d_o = dht * q.a_o;
-    if (lane < H) {
-      float* dp = P.dpre + (size_t)t * G4;
-      dp[lane] = di; dp[H + lane] = df; dp[2 * H + lane] = dg; dp[3 * H + lane] = d_o;
+    for (int j = 0; j < HP; ++j) {
+      float a = 0.f, b = 0.f;
+      if (j < H) {
+        const float* yj = Y + ((size_t)t * H + j) * REC;
+        a = whh[(0 * H + j) * H + k] * yj[4] + whh[(1 * H + j) * H + k] * yj[5] + whh[(2 * H + j) * H + k] * yj[6];
+        b = whh[(3 * H + j) * H + k] * yj[7];
+      }
+      y[8 + j] = a;
+      y[8 + HP + j] = b;
     }
-    float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+  }
+  __syncthreads();
+  // serial chain: lane k < H carries (dh_rec_k, dc_k); S[t] = dht | dcn overwrites the dead saved states
+  float* S = sv_s;
+  if (warp == 0) {
+    const int k = lane < H ? lane : 0;
+    float dh_rec = 0.f, dc = 0.f;
+    constexpr int R4 = REC / 4, NA = HP / 4;
+    const float4* y4 = reinterpret_cast<const float4*>(Y);
+    float4 c0, ca[NA], cb[NA];
+    auto fetch = [&](int t) {
+      const size_t o = ((size_t)t * H + k) * R4;
+      c0 = y4[o];
 #pragma unroll
-    for (int s = 0; s < H; ++s) {
-      a0 = fmaf(whh_col[s], __shfl_sync(0xffffffffu, di, s), a0);
-      a1 = fmaf(whh_col[H + s], __shfl_sync(0xffffffffu, df, s), a1);
-      a2 = fmaf(whh_col[2 * H + s], __shfl_sync(0xffffffffu, dg, s), a2);
-      a3 = fmaf(whh_col[3 * H + s], __shfl_sync(0xffffffffu, d_o, s), a3);
+      for (int u = 0; u < NA; ++u) { ca[u] = y4[o + 2 + u]; cb[u] = y4[o + 2 + NA + u]; }
+    };
+    fetch(T - 1);
+    for (int t = T - 1; t >= 0; --t) {
+      const float4 q0 = c0;
+      float A[HP], B[HP];
+#pragma unroll
+      for (int u = 0; u < NA; ++u) {
+        A[4 * u] = ca[u].x; A[4 * u + 1] = ca[u].y; A[4 * u + 2] = ca[u].z; A[4 * u + 3] = ca[u].w;
+        B[4 * u] = cb[u].x; B[4 * u + 1] = cb[u].y; B[4 * u + 2] = cb[u].z; B[4 * u + 3] = cb[u].w;
+      }
+      if (t > 0) fetch(t - 1);
+      const float dht = q0.z + dh_rec;
+      const float dcn = fmaf(dht, q0.x, dc);
+      if (lane < H) { S[t * 2 * H + lane] = dht; S[t * 2 * H + H + lane] = dcn; }
+      float r0 = 0.f, r1 = 0.f;
+#pragma unroll
+      for (int j = 0; j < H; ++j) {
+        r0 = fmaf(A[j], __shfl_sync(0xffffffffu, dcn, j), r0);
+        r1 = fmaf(B[j], __shfl_sync(0xffffffffu, dht, j), r1);
+      }
+      dh_rec = r0 + r1;
+      dc = dcn * q0.y;
     }
-    dh_rec = (a0 + a1) + (a2 + a3);
-    dc *= q.gf;
+  }
+  __syncthreads();
+  // gate gradients, thread = (month, unit)
+  for (int i = tid; i < T * H; i += MT) {
+    const int t = i / H, j = i % H;
+    const float dht = S[t * 2 * H + j], dcn = S[t * 2 * H + H + j];
+    const float* y = Y + (size_t)i * REC;
+    float* dp = P.dpre + (size_t)t * G4;
+    dp[j] = dcn * y[4]; dp[H + j] = dcn * y[5]; dp[2 * H + j] = dcn * y[6]; dp[3 * H + j] = dht * y[7];
   }
 }
 
@@ -348,7 +378,10 @@ __global__ void __launch_bounds__(256) macro_wgrad_kernel(const MacroParams P) {
 
 size_t macro_fwd_smem(int T, int M, int H) { return (size_t)T * 5 * H * 4 + 0 * (size_t)M; }
 size_t macro_proj_smem(int M, int H) { return ((size_t)4 * H * M + (size_t)KM * M) * 4; }
-size_t macro_bwd_smem(int T, int H) { return ((size_t)T * H + (size_t)T * 12 * H + (size_t)D1 * H) * 4; }
+size_t macro_bwd_smem(int T, int H) {
+  const int rec = 8 + 2 * ((H + 3) & ~3);
+  return ((size_t)T * 6 * H + (size_t)T * H * rec + (size_t)D1 * H + (size_t)4 * H * H) * 4;
+}
 
 template <int H>
 static cudaError_t launch_fwd_h(const MacroParams& P, size_t smem, cudaStream_t st) {
