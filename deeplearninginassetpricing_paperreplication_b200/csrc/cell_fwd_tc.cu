@@ -22,29 +22,30 @@ constexpr int NT_TC = 512;
 constexpr int BR = 32;                                   // rows per gather batch (64 registers in flight per lane)
 constexpr int NB = TILE / BR;                            // batches per tile
 constexpr int NGW = 7;                                   // gather warps: 0, 2 (also TMEM owner), 3, 4..7
+constexpr int NXS = 3;                                   // slots of X image, W1 image and layer-1 accumulator
 struct SmemTc {
   uint8_t* base;
   __device__ uint8_t* xh(int sl) const { return base + sl * 2 * X_IMG; }
   __device__ uint8_t* xl(int sl) const { return xh(sl) + X_IMG; }
-  __device__ uint8_t* w1h(int sl) const { return base + 4 * X_IMG + sl * 2 * W1_IMG; }
+  __device__ uint8_t* w1h(int sl) const { return base + NXS * 2 * X_IMG + sl * 2 * W1_IMG; }
   __device__ uint8_t* w1l(int sl) const { return w1h(sl) + W1_IMG; }
-  __device__ uint8_t* hh(int sl) const { return base + 4 * X_IMG + 4 * W1_IMG + sl * 2 * H_IMG; }
+  __device__ uint8_t* hh(int sl) const { return base + NXS * 2 * (X_IMG + W1_IMG) + sl * 2 * H_IMG; }
   __device__ uint8_t* hl(int sl) const { return hh(sl) + H_IMG; }
-  __device__ uint8_t* w2h() const { return base + 4 * X_IMG + 4 * W1_IMG + 4 * H_IMG; }
+  __device__ uint8_t* w2h() const { return base + NXS * 2 * (X_IMG + W1_IMG) + 4 * H_IMG; }
   __device__ uint8_t* w2l() const { return w2h() + W2_IMG; }
   __device__ float* b2s() const { return reinterpret_cast<float*>(w2l() + W2_IMG); }
   __device__ float* w3s() const { return b2s() + 64; }
   __device__ uint64_t* bars() const { return reinterpret_cast<uint64_t*>(w3s() + 64); }
-  __device__ uint32_t* tmem_slot() const { return reinterpret_cast<uint32_t*>(bars() + 16); }
+  __device__ uint32_t* tmem_slot() const { return reinterpret_cast<uint32_t*>(bars() + 24); }
 };
-enum { F_XOP_FULL = 4, F_XOP_EMPTY = 6, F_D1_FULL = 8, F_H1_FULL = 10,
+enum { F_XOP_FULL = 0, F_XOP_EMPTY = 3, F_D1_FULL = 6, F_H1_FULL = 10,
        F_D2_FULL = 12, F_D2_EMPTY = 14 };
 
-constexpr size_t SMEM_TC_BYTES = (size_t)4 * X_IMG + 4 * W1_IMG + 4 * H_IMG + 2 * W2_IMG +
-                                 128 * 4 + 16 * 8 + 16 + 256;
+constexpr size_t SMEM_TC_BYTES = (size_t)NXS * 2 * (X_IMG + W1_IMG) + 4 * H_IMG + 2 * W2_IMG +
+                                 128 * 4 + 24 * 8 + 16 + 256;
 
-// TMEM columns
-constexpr uint32_t COL_A0 = 0, COL_B0 = 96, COL_A1 = 160, COL_B1 = 256, TMEM_COLS = 512;
+// TMEM columns: three layer-1 accumulators (layer 1 runs two tiles ahead of its epilogue), two layer-2 ones
+constexpr uint32_t COL_A = 0, COL_A_STRIDE = 96, COL_B0 = 288, COL_B1 = 352, TMEM_COLS = 512;
 }  // namespace
 
 // diagnostics: stamp slot k of local tile i (CTA 0 only, one thread per role)
@@ -66,14 +67,17 @@ __global__ void __launch_bounds__(NT_TC, 1) cell_fwd_tc_kernel(const CellParams 
   const int my_tiles = min(ntiles, tile_lo + chunk) - tile_lo;
 
   // ---- one-time set-up ----
-  for (int sl = 0; sl < 2; ++sl) fill_w1_images(P, s.w1h(sl), s.w1l(sl), tid, NT_TC);
+  for (int sl = 0; sl < NXS; ++sl) fill_w1_images(P, s.w1h(sl), s.w1l(sl), tid, NT_TC);
   fill_w2_images(P, s.w2h(), s.w2l(), tid, NT_TC);
-  for (int sl = 0; sl < 2; ++sl) init_x_images(s.xh(sl), s.xl(sl), tid, NT_TC);
+  for (int sl = 0; sl < NXS; ++sl) init_x_images(s.xh(sl), s.xl(sl), tid, NT_TC);
   if (tid < 64) { s.b2s()[tid] = __ldg(P.b2 + tid); s.w3s()[tid] = __ldg(P.W3 + tid); }
   if (tid == 0) {
-    for (int i = 0; i < 2; ++i) {
+    for (int i = 0; i < NXS; ++i) {
       mbar_init(bar + F_XOP_FULL + i, NB);   mbar_init(bar + F_XOP_EMPTY + i, 1);
-      mbar_init(bar + F_D1_FULL + i, 1);     mbar_init(bar + F_H1_FULL + i, 4);
+      mbar_init(bar + F_D1_FULL + i, 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(bar + F_H1_FULL + i, 4);
       mbar_init(bar + F_D2_FULL + i, 1);     mbar_init(bar + F_D2_EMPTY + i, 4);
     }
     fence_mbar_init();
@@ -90,44 +94,48 @@ __global__ void __launch_bounds__(NT_TC, 1) cell_fwd_tc_kernel(const CellParams 
     {
       const uint32_t id1 = tc::idesc_bf16(128, N1, 0, 0), id2 = tc::idesc_bf16(128, 64, 0, 0);
       const uint64_t w2h = tc::smem_desc(smem_u32(s.w2h()), 64 * 16, 128), w2l = tc::smem_desc(smem_u32(s.w2l()), 64 * 16, 128);
-      for (int i = 0; i <= my_tiles; ++i) {
-        if (i < my_tiles) {                          // layer 1 of tile i
-          const int sl = i & 1, use = i >> 1;
-          mbar_wait(bar + F_XOP_FULL + sl, use & 1);
-          tc::fence_after_sync();
-          if (lane == 0) DLAP_STAMP(i, 8);
-          const uint64_t ah = tc::smem_desc(smem_u32(s.xh(sl)), X_LBO, 128), al = tc::smem_desc(smem_u32(s.xl(sl)), X_LBO, 128);
-          const uint64_t bh = tc::smem_desc(smem_u32(s.w1h(sl)), N1 * 16, 128), bl = tc::smem_desc(smem_u32(s.w1l(sl)), N1 * 16, 128);
-          const uint32_t d = tbase + (sl ? COL_A1 : COL_A0);
-          if (tc::elect_one()) {
+      // Layer 1 runs two tiles ahead of its epilogue (three accumulator / X / W1 slots): L1(0) L1(1) | L2(0)
+      // L1(2) | L2(1) L1(3) | ...  so an epilogue group that finishes a tile finds the next one's z1 waiting,
+      // and a late gather delays only layer 1, never layer 2.
+      auto issue_l1 = [&](int i) {
+        const int xs = i % NXS, use = i / NXS;
+        mbar_wait(bar + F_XOP_FULL + xs, use & 1);
+        tc::fence_after_sync();
+        if (lane == 0) DLAP_STAMP(i, 8);
+        const uint64_t ah = tc::smem_desc(smem_u32(s.xh(xs)), X_LBO, 128), al = tc::smem_desc(smem_u32(s.xl(xs)), X_LBO, 128);
+        const uint64_t bh = tc::smem_desc(smem_u32(s.w1h(xs)), N1 * 16, 128), bl = tc::smem_desc(smem_u32(s.w1l(xs)), N1 * 16, 128);
+        const uint32_t d = tbase + COL_A + xs * COL_A_STRIDE;
+        if (tc::elect_one()) {
 #pragma unroll
-            for (int ks = 0; ks < KG1 / 2; ++ks)
-              umma3(d, tc::desc_advance(ah, ks * 2 * X_LBO), tc::desc_advance(al, ks * 2 * X_LBO),
-                    tc::desc_advance(bh, ks * 2 * N1 * 16), tc::desc_advance(bl, ks * 2 * N1 * 16), id1, ks == 0);
-            tc::umma_commit(bar + F_XOP_EMPTY + sl);
-            tc::umma_commit(bar + F_D1_FULL + sl);
-          }
-          __syncwarp();
-          if (lane == 0) DLAP_STAMP(i, 9);
+          for (int ks = 0; ks < KG1 / 2; ++ks)
+            umma3(d, tc::desc_advance(ah, ks * 2 * X_LBO), tc::desc_advance(al, ks * 2 * X_LBO),
+                  tc::desc_advance(bh, ks * 2 * N1 * 16), tc::desc_advance(bl, ks * 2 * N1 * 16), id1, ks == 0);
+          tc::umma_commit(bar + F_XOP_EMPTY + xs);
+          tc::umma_commit(bar + F_D1_FULL + xs);
         }
-        if (i > 0) {                                 // layer 2 of tile i-1
-          const int j = i - 1, sl = j & 1, use = j >> 1;
-          mbar_wait(bar + F_H1_FULL + sl, use & 1);
-          mbar_wait(bar + F_D2_EMPTY + sl, (use & 1) ^ 1);
-          tc::fence_after_sync();
-          if (lane == 0) DLAP_STAMP(j, 10);
-          const uint64_t ah = tc::smem_desc(smem_u32(s.hh(sl)), TILE * 16, 128), al = tc::smem_desc(smem_u32(s.hl(sl)), TILE * 16, 128);
-          const uint32_t d = tbase + (sl ? COL_B1 : COL_B0);
-          if (tc::elect_one()) {
+        __syncwarp();
+        if (lane == 0) DLAP_STAMP(i, 9);
+      };
+      if (my_tiles > 0) issue_l1(0);
+      if (my_tiles > 1) issue_l1(1);
+      for (int j = 0; j < my_tiles; ++j) {           // layer 2 of tile j, then layer 1 of tile j + 2
+        const int sl = j & 1, use = j >> 1;
+        mbar_wait(bar + F_H1_FULL + sl, use & 1);    // also: E1(j) has read the accumulator slot L1(j + 3) will reuse
+        mbar_wait(bar + F_D2_EMPTY + sl, (use & 1) ^ 1);
+        tc::fence_after_sync();
+        if (lane == 0) DLAP_STAMP(j, 10);
+        const uint64_t ah = tc::smem_desc(smem_u32(s.hh(sl)), TILE * 16, 128), al = tc::smem_desc(smem_u32(s.hl(sl)), TILE * 16, 128);
+        const uint32_t d = tbase + (sl ? COL_B1 : COL_B0);
+        if (tc::elect_one()) {
 #pragma unroll
-            for (int ks = 0; ks < KG2 / 2; ++ks)
-              umma3(d, tc::desc_advance(ah, ks * 2 * TILE * 16), tc::desc_advance(al, ks * 2 * TILE * 16),
-                    tc::desc_advance(w2h, ks * 2 * 64 * 16), tc::desc_advance(w2l, ks * 2 * 64 * 16), id2, ks == 0);
-            tc::umma_commit(bar + F_D2_FULL + sl);
-          }
-          __syncwarp();
-          if (lane == 0) DLAP_STAMP(j, 11);
+          for (int ks = 0; ks < KG2 / 2; ++ks)
+            umma3(d, tc::desc_advance(ah, ks * 2 * TILE * 16), tc::desc_advance(al, ks * 2 * TILE * 16),
+                  tc::desc_advance(w2h, ks * 2 * 64 * 16), tc::desc_advance(w2l, ks * 2 * 64 * 16), id2, ks == 0);
+          tc::umma_commit(bar + F_D2_FULL + sl);
         }
+        __syncwarp();
+        if (lane == 0) DLAP_STAMP(j, 11);
+        if (j + 2 < my_tiles) issue_l1(j + 2);
       }
     }
   } else if (warp < 8) {
@@ -136,11 +144,11 @@ __global__ void __launch_bounds__(NT_TC, 1) cell_fwd_tc_kernel(const CellParams 
     const int gw = warp == 0 ? 0 : warp - 1;
     long long* tl = (P.timeline && blockIdx.x == 0 && warp == 4 && lane == 0) ? P.timeline : nullptr;
     if (gather_wide(P))
-      gather_role<BR, NGW, 2, true, MOM>(P, gw, lane, tile_lo, my_tiles, s.xh(0), s.w1h(0) + (KG1 - 1) * N1 * 16,
+      gather_role<BR, NGW, NXS, true, MOM>(P, gw, lane, tile_lo, my_tiles, s.xh(0), s.w1h(0) + (KG1 - 1) * N1 * 16,
                                          2 * W1_IMG, W1_IMG, bar + F_XOP_FULL,
                                       bar + F_XOP_EMPTY, tl, 0, true);
     else
-      gather_role<BR, NGW, 2, false, MOM>(P, gw, lane, tile_lo, my_tiles, s.xh(0), s.w1h(0) + (KG1 - 1) * N1 * 16,
+      gather_role<BR, NGW, NXS, false, MOM>(P, gw, lane, tile_lo, my_tiles, s.xh(0), s.w1h(0) + (KG1 - 1) * N1 * 16,
                                           2 * W1_IMG, W1_IMG, bar + F_XOP_FULL,
                                        bar + F_XOP_EMPTY, tl, 0, true);
   } else if (warp >= 8) {
@@ -162,7 +170,7 @@ __global__ void __launch_bounds__(NT_TC, 1) cell_fwd_tc_kernel(const CellParams 
       const int tile = tile_lo + i, sl = i & 1, use = i >> 1;
       const int t = t_nxt, n = n_nxt;
       const size_t pi = (size_t)t * P.N + pos_nxt;
-      const uint32_t dA = tbase + lane_base + (sl ? COL_A1 : COL_A0), dB = tbase + lane_base + (sl ? COL_B1 : COL_B0);
+      const uint32_t dA = tbase + lane_base + COL_A + (i % NXS) * COL_A_STRIDE, dB = tbase + lane_base + (sl ? COL_B1 : COL_B0);
       // this cell's return: issued now, consumed after both layers (HBM latency hidden); every listed cell
       // is unmasked, so m = 1 exactly where the row exists
       const bool live = n >= 0;
@@ -172,7 +180,7 @@ __global__ void __launch_bounds__(NT_TC, 1) cell_fwd_tc_kernel(const CellParams 
       if (i + 2 < my_tiles) load_row(tile_lo + i + 2);
       // -- after layer 1: h1 = relu(z1) -> bf16 hi/lo image
       const bool stamp = q4 == 0 && lane == 0;
-      mbar_wait(bar + F_D1_FULL + sl, use & 1);
+      mbar_wait(bar + F_D1_FULL + i % NXS, (i / NXS) & 1);
       tc::fence_after_sync();
       if (stamp) DLAP_STAMP(i, 12);
 #pragma unroll
