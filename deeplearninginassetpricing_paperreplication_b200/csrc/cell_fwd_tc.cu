@@ -4,7 +4,10 @@
 // The kernel walks the valid-cell tiles of dlap_panel_index (cell_f32.cuh): a tile is <= 128 unmasked
 // stocks of one month, gathered row by row.
 //
-// Persistent CTA, one per SM, 16 warps with fixed roles; two tiles are in flight (slot = tile & 1):
+// h1 never touches shared memory: the epilogue writes relu(z1), split into bf16 hi/lo, back into the TMEM
+// columns of its own z1 accumulator, and layer 2 takes its A operand from there (tcgen05.mma with A in TMEM).
+//
+// Persistent CTA, one per SM, 16 warps with fixed roles; three tiles are in flight:
 //   warp 1      MMA issuer (one lane): layer 1 of tile i is issued before layer 2 of tile i-1
 //   warps 0, 2-7  gather + convert (warp 2 also owns the TMEM allocation): batches of 32 rows, round-robin over
 //               the seven warps, are fetched with coalesced loads (one row per load, a column pair per lane),
@@ -29,9 +32,7 @@ struct SmemTc {
   __device__ uint8_t* xl(int sl) const { return xh(sl) + X_IMG; }
   __device__ uint8_t* w1h(int sl) const { return base + NXS * 2 * X_IMG + sl * 2 * W1_IMG; }
   __device__ uint8_t* w1l(int sl) const { return w1h(sl) + W1_IMG; }
-  __device__ uint8_t* hh(int sl) const { return base + NXS * 2 * (X_IMG + W1_IMG) + sl * 2 * H_IMG; }
-  __device__ uint8_t* hl(int sl) const { return hh(sl) + H_IMG; }
-  __device__ uint8_t* w2h() const { return base + NXS * 2 * (X_IMG + W1_IMG) + 4 * H_IMG; }
+  __device__ uint8_t* w2h() const { return base + NXS * 2 * (X_IMG + W1_IMG); }
   __device__ uint8_t* w2l() const { return w2h() + W2_IMG; }
   __device__ float* b2s() const { return reinterpret_cast<float*>(w2l() + W2_IMG); }
   __device__ float* w3s() const { return b2s() + 64; }
@@ -41,11 +42,16 @@ struct SmemTc {
 enum { F_XOP_FULL = 0, F_XOP_EMPTY = 3, F_D1_FULL = 6, F_H1_FULL = 10,
        F_D2_FULL = 12, F_D2_EMPTY = 14 };
 
-constexpr size_t SMEM_TC_BYTES = (size_t)NXS * 2 * (X_IMG + W1_IMG) + 4 * H_IMG + 2 * W2_IMG +
+constexpr size_t SMEM_TC_BYTES = (size_t)NXS * 2 * (X_IMG + W1_IMG) + 2 * W2_IMG +
                                  128 * 4 + 24 * 8 + 16 + 256;
 
-// TMEM columns: three layer-1 accumulators (layer 1 runs two tiles ahead of its epilogue), two layer-2 ones
+// TMEM columns: three layer-1 accumulators (layer 1 runs two tiles ahead of its epilogue), two layer-2 ones.
+// After E1 the first 64 columns of a layer-1 slot hold h1 as packed bf16 pairs, in two blocks of 32 units:
+// columns [32b, 32b+16) = hi of units 32b .. 32b+31, [32b+16, 32b+32) = lo  (each block is rewritten in place
+// by the thread that just read it).  K step ks (units 16ks ..) of layer 2 reads 8 columns of each.
 constexpr uint32_t COL_A = 0, COL_A_STRIDE = 96, COL_B0 = 288, COL_B1 = 352, TMEM_COLS = 512;
+__device__ __forceinline__ uint32_t h1_col_hi(int ks) { return (uint32_t)((ks >> 1) * 32 + (ks & 1) * 8); }
+__device__ __forceinline__ uint32_t h1_col_lo(int ks) { return h1_col_hi(ks) + 16; }
 }  // namespace
 
 // diagnostics: stamp slot k of local tile i (CTA 0 only, one thread per role)
@@ -124,13 +130,16 @@ __global__ void __launch_bounds__(NT_TC, 1) cell_fwd_tc_kernel(const CellParams 
         mbar_wait(bar + F_D2_EMPTY + sl, (use & 1) ^ 1);
         tc::fence_after_sync();
         if (lane == 0) DLAP_STAMP(j, 10);
-        const uint64_t ah = tc::smem_desc(smem_u32(s.hh(sl)), TILE * 16, 128), al = tc::smem_desc(smem_u32(s.hl(sl)), TILE * 16, 128);
+        const uint32_t a = tbase + COL_A + (j % NXS) * COL_A_STRIDE;     // h1 of tile j, in its z1 slot
         const uint32_t d = tbase + (sl ? COL_B1 : COL_B0);
         if (tc::elect_one()) {
 #pragma unroll
-          for (int ks = 0; ks < KG2 / 2; ++ks)
-            umma3(d, tc::desc_advance(ah, ks * 2 * TILE * 16), tc::desc_advance(al, ks * 2 * TILE * 16),
-                  tc::desc_advance(w2h, ks * 2 * 64 * 16), tc::desc_advance(w2l, ks * 2 * 64 * 16), id2, ks == 0);
+          for (int ks = 0; ks < KG2 / 2; ++ks) {
+            const uint64_t bh = tc::desc_advance(w2h, ks * 2 * 64 * 16), bl = tc::desc_advance(w2l, ks * 2 * 64 * 16);
+            tc::umma_bf16_ts(d, a + h1_col_hi(ks), bh, id2, ks == 0 ? 0u : 1u);
+            tc::umma_bf16_ts(d, a + h1_col_hi(ks), bl, id2, 1u);
+            tc::umma_bf16_ts(d, a + h1_col_lo(ks), bh, id2, 1u);
+          }
           tc::umma_commit(bar + F_D2_FULL + sl);
         }
         __syncwarp();
@@ -190,21 +199,19 @@ __global__ void __launch_bounds__(NT_TC, 1) cell_fwd_tc_kernel(const CellParams 
 #pragma unroll
         for (int k = 0; k < 32; ++k) v[k] = fmaxf(v[k], 0.f);
         if (DROP) tc_dropout<32>(P, (uint32_t)gi, 0, c * 32, v);
+        uint32_t hi[16], lo[16];
 #pragma unroll
-        for (int g = 0; g < 4; ++g) {
-          uint4 hi, lo;
-          tc::split8(v + 8 * g, hi, lo);
-          *reinterpret_cast<uint4*>(s.hh(sl) + ((4 * c + g) * TILE + cell) * 16) = hi;
-          *reinterpret_cast<uint4*>(s.hl(sl) + ((4 * c + g) * TILE + cell) * 16) = lo;
-        }
+        for (int k = 0; k < 16; ++k) tc::split2(v[2 * k], v[2 * k + 1], hi[k], lo[k]);
+        tc::tmem_st16(dA + c * 32, hi);              // over the z1 columns this thread has just read
+        tc::tmem_st16(dA + c * 32 + 16, lo);
       }
       float q[8];
       if (MOM) {
         tc::tmem_ld8(dA + 64, q);
         tc::tmem_wait_ld();
       }
+      tc::tmem_wait_st();
       tc::fence_before_sync();
-      fence_proxy_async();
       __syncwarp();
       if (lane == 0) mbar_arrive(bar + F_H1_FULL + sl);
       if (stamp) DLAP_STAMP(i, 13);
