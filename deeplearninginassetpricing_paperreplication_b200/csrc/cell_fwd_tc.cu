@@ -215,10 +215,19 @@ __global__ void __launch_bounds__(NT_TC, 1) cell_fwd_tc_kernel(const CellParams 
       __syncwarp();
       if (lane == 0) mbar_arrive(bar + F_H1_FULL + sl);
       if (stamp) DLAP_STAMP(i, 13);
+      // -- while layer 2 runs: everything that does not need u (moments, their stores, the u-free row sums)
+      const float m = live ? 1.f : 0.f;
       if (MOM) {
+        const size_t plane = (size_t)P.T * P.N;
+        const float rm = r * m;
 #pragma unroll
-        for (int k = 0; k < 8; ++k) q[k] = tc::tanh_fast(q[k]);
+        for (int k = 0; k < 8; ++k) {
+          const float gk = tc::tanh_fast(q[k]) * rm;
+          if (live) P.g[(size_t)k * plane + pi] = gk;
+        }
       }
+      double v0 = live ? 1.0 : 0.0, v3 = live ? (double)r : 0.0;
+      v0 = warp_sum(v0); v3 = warp_sum(v3);
       // -- after layer 2: u = b3 + W3 . relu(z2 + b2)
       mbar_wait(bar + F_D2_FULL + sl, use & 1);
       tc::fence_after_sync();
@@ -249,22 +258,13 @@ __global__ void __launch_bounds__(NT_TC, 1) cell_fwd_tc_kernel(const CellParams 
       __syncwarp();
       if (lane == 0) mbar_arrive(bar + F_D2_EMPTY + sl);
       // -- outputs
-      const float m = live ? 1.f : 0.f;
-      if (live) {
-        P.u[pi] = u;
-        if (MOM) {
-          const size_t plane = (size_t)P.T * P.N;
-          const float rm = r * m;
-#pragma unroll
-          for (int k = 0; k < 8; ++k) P.g[(size_t)k * plane + pi] = q[k] * rm;
-        }
-      }
-      double v0 = 0, v1 = 0, v2 = 0, v3 = 0;
+      if (live) P.u[pi] = u;
+      double v1 = 0, v2 = 0;
       if (live) {
         const double mu_ = (double)m * (double)u;
-        v0 = m; v1 = mu_; v2 = mu_ * (double)r; v3 = (double)m * (double)r;
+        v1 = mu_; v2 = mu_ * (double)r;
       }
-      v0 = warp_sum(v0); v1 = warp_sum(v1); v2 = warp_sum(v2); v3 = warp_sum(v3);
+      v1 = warp_sum(v1); v2 = warp_sum(v2);
       if (lane == 0) {
         double* rp = P.row_part + ((size_t)tile * 4 + q4) * 4;
         rp[0] = v0; rp[1] = v1; rp[2] = v2; rp[3] = v3;
