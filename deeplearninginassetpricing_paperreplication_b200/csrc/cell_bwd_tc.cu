@@ -132,6 +132,8 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
   const int Fr = round4(P.F);
 
   // ---- one-time set-up ----
+  if (tid == 0) DLAP_STAMP(255, 0);                          // diagnostics: kernel entry
+  const long long t_entry = (P.timeline && tid == 0) ? clock64() : 0;
   fill_w1_groups(P, s.w1h(), s.w1l(), 0, KG1 - 1, tid, NT_B);
   for (int sl = 0; sl < NXS; ++sl) fill_w1_groups(P, s.g5h(sl), s.g5l(sl), KG1 - 1, 1, tid, NT_B);
   fill_w2_images(P, s.w2h(), s.w2l(), tid, NT_B);
@@ -159,6 +161,7 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
   __syncthreads();
   tc::fence_after_sync();
   const uint32_t tbase = *s.tmem_slot();
+  if (tid == 0) DLAP_STAMP(255, 1);                          // set-up done
 
   if (warp == 1) {
     // ===== MMA issuer (all lanes wait, lane 0 issues) =====
@@ -570,6 +573,9 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
   }
   tc::fence_before_sync();
   __syncthreads();
+  if (tid == 0) DLAP_STAMP(255, 2);                          // every role done
+  if (P.timeline && tid == 0 && blockIdx.x < 2048)           // per-CTA active cycles and tile count
+    P.timeline[2 * 4096 + 2048 + blockIdx.x] = ((clock64() - t_entry) << 8) | (long long)(my_tiles & 255);
   if (warp == 0) tc::tmem_dealloc(tbase, TMEM_COLS);
 }
 

@@ -51,3 +51,17 @@ print("FWD epilogue (even tiles): D1_FULL -> E1 done", fd(12, 13, 0, 2), "| -> D
       "| period per 2 tiles", fd(12, 12, 2, 2))
 print("FWD chain for tile i:", "| L1 issued(9) -> D1_FULL seen(12)", fd(9, 12, 0, 2),
       "| E1 done(13) -> L2 start(10)", fd(13, 10, 0, 2), "| L2 issued(11) -> D2_FULL seen(14)", fd(11, 14, 0, 2))
+nf = int((f[:, 15] > 0).sum())
+first = float(min(x for x in f[0, [8, 9, 12]].tolist() if x > 0))
+print("FWD CTA 0: tiles", nf, "| first stamp -> last epilogue stamp:", float(f[nf - 1, 15]) - first, "cycles | per tile",
+      (float(f[nf - 1, 15]) - first) / max(nf, 1), "| first 6 tile ends:", [float(f[k, 15]) - first for k in range(6)])
+nb_ = int((s[:, 5] > 0).sum())
+print("BWD CTA 0: tiles", nb_, "| first E2 start -> last E3 end:", float(s[nb_ - 1, 5] - s[0, 0]), "cycles | per tile",
+      float(s[nb_ - 1, 5] - s[0, 0]) / max(nb_, 1), "| first 5 tile E3 ends:", [float(s[k, 5] - s[0, 0]) for k in range(5)],
+      "| last 3 periods:", [float(s[k, 0] - s[k - 1, 0]) for k in range(nb_ - 3, nb_)])
+print("BWD CTA 0: entry -> set-up done", float(s[255, 1] - s[255, 0]), "| set-up done -> first E2 start", float(s[0, 0] - s[255, 1]),
+      "| last E3 end -> all roles done", float(s[255, 2] - s[nb_ - 1, 5]), "| entry -> end", float(s[255, 2] - s[255, 0]))
+cta = st[2 * 4096 + 2048:2 * 4096 + 2048 + 148].cpu()
+cyc = (cta >> 8).double(); nt = (cta & 255)
+print("BWD per-CTA active cycles: min", float(cyc.min()), "median", float(cyc.median()), "max", float(cyc.max()),
+      "| tiles per CTA min/max", int(nt.min()), int(nt.max()), "| slowest CTAs", torch.topk(cyc, 5).indices.tolist())
