@@ -140,7 +140,8 @@ static void fill_cell(CellParams& P, const dlap_plan* plan, const float* x, cons
   P.tpm = plan->tpm;
 }
 
-static int set_dropout(CellParams& P, float p, uint64_t seed) {
+static int set_dropout(CellParams& P, float p, uint64_t seed, const uint64_t* seed_dev) {
+  P.seed_ptr = reinterpret_cast<const uint32_t*>(seed_dev);
   if (!(p >= 0.f) || p >= 1.f) return DLAP_E_SHAPE;
   uint32_t thr = (uint32_t)(p * 65536.f + 0.5f);
   if (thr > 65535u) thr = 65535u;
@@ -187,7 +188,8 @@ int dlap_panel_pull(const dlap_plan* plan, const float* x_host, const int32_t* i
 
 int dlap_cell_fwd(const dlap_plan* plan, const float* x, const float* R, const uint8_t* mask, const int32_t* index,
                   const dlap_tensors* params, const float* a_t, const float* c_t, float* u, float* g,
-                  double* row_part, int precision, float dropout_p, uint64_t dropout_seed, void* stream) {
+                  double* row_part, int precision, float dropout_p, uint64_t dropout_seed,
+                  const uint64_t* dropout_seed_dev, void* stream) {
   int rc = check_plan(plan);
   if (rc) return rc;
   REQ(x); REQ(mask); REQ(params); REQ(a_t); REQ(u); REQ(row_part);
@@ -198,7 +200,7 @@ int dlap_cell_fwd(const dlap_plan* plan, const float* x, const float* R, const u
   CellParams P;
   fill_cell(P, plan, x, R, mask, params, a_t, c_t);
   P.u = u; P.g = g; P.row_part = row_part;
-  rc = set_dropout(P, dropout_p, dropout_seed);
+  rc = set_dropout(P, dropout_p, dropout_seed, dropout_seed_dev);
   if (rc) return rc;
   if (precision == DLAP_PREC_BF16X3) {
     if (plan->dims.F > 46) return DLAP_E_SHAPE;      // the ones column lives at k = 46
@@ -272,7 +274,7 @@ int dlap_cell_bwd(const dlap_plan* plan, const float* x, const float* R, const u
                   const dlap_tensors* params, const float* a_t, const float* c_t, const float* row_stats,
                   const double* dS_part, const float* dpr_cot, const float* G, const float* scalars,
                   int weighted_loss, int want_sdf, int want_mom, float* wpart, float* dadc_part, int precision,
-                  float dropout_p, uint64_t dropout_seed, void* stream) {
+                  float dropout_p, uint64_t dropout_seed, const uint64_t* dropout_seed_dev, void* stream) {
   int rc = check_plan(plan);
   if (rc) return rc;
   REQ(x); REQ(R); REQ(mask); REQ(params); REQ(a_t); REQ(c_t); REQ(row_stats); REQ(dS_part); REQ(G); REQ(scalars);
@@ -285,7 +287,7 @@ int dlap_cell_bwd(const dlap_plan* plan, const float* x, const float* R, const u
   P.row_stats = row_stats; P.dS_part = dS_part; P.ds_splits = plan->row_splits; P.dpr_cot = dpr_cot;
   P.G = G; P.scalars = scalars; P.weighted = weighted_loss;
   P.wpart = wpart; P.dadc_part = dadc_part;
-  rc = set_dropout(P, dropout_p, dropout_seed);
+  rc = set_dropout(P, dropout_p, dropout_seed, dropout_seed_dev);
   if (rc) return rc;
   if (precision == DLAP_PREC_BF16X3) {
     if (plan->dims.F > 46) return DLAP_E_SHAPE;

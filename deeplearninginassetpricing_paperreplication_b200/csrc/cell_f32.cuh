@@ -54,6 +54,7 @@ struct CellParams {
   uint32_t drop_thr;         // drop when a 16-bit uniform < drop_thr (0 = off)
   float drop_scale;          // 1 / (1 - drop_thr/65536)
   uint32_t seed_lo, seed_hi; // per-forward seed; the backward pass regenerates the same mask
+  const uint32_t* seed_ptr;  // non-null: the 64-bit seed lives in device memory (a step replayed from a CUDA graph)
   long long* timeline;       // diagnostics (dlap_debug_timeline): per-tile clock64 stamps of CTA 0, or null
   // valid-cell index (dlap_panel_index); tensor-core kernels only, null = not built
   const int* index;
@@ -317,6 +318,8 @@ __device__ __forceinline__ void layer1(const SmemFwd& s, int F, int ty, int tx, 
 }
 
 // ---- dropout: counter-based, keyed on (seed, stock-month, layer, unit) ----------------------------
+__device__ __forceinline__ uint32_t drop_seed_lo(const CellParams& P) { return P.seed_ptr ? __ldg(P.seed_ptr) : P.seed_lo; }
+__device__ __forceinline__ uint32_t drop_seed_hi(const CellParams& P) { return P.seed_ptr ? __ldg(P.seed_ptr + 1) : P.seed_hi; }
 __device__ __forceinline__ uint32_t mix32(uint32_t h) {
   h ^= h >> 16; h *= 0x85ebca6bu; h ^= h >> 13; h *= 0xc2b2ae35u; h ^= h >> 16;
   return h;
@@ -326,7 +329,7 @@ __device__ __forceinline__ void relu_dropout(const CellParams& P, uint32_t cell0
                                              float acc[4][8]) {
 #pragma unroll
   for (int c = 0; c < 4; ++c) {
-    const uint32_t key = mix32((cell0 + c) ^ P.seed_lo) ^ P.seed_hi;
+    const uint32_t key = mix32((cell0 + c) ^ drop_seed_lo(P)) ^ drop_seed_hi(P);
 #pragma unroll
     for (int pr = 0; pr < 4; ++pr) {
       const int j0 = unit_of(tx, 2 * pr);

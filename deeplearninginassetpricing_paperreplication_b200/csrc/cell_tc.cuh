@@ -198,7 +198,7 @@ __device__ __forceinline__ void fill_w2_images(const CellParams& P, uint8_t* hi,
 // two precisions drop exactly the same units for a given seed, forward and backward.
 template <int N>
 __device__ __forceinline__ void tc_dropout(const CellParams& P, uint32_t cell_global, int layer, int U0, float* v) {
-  const uint32_t key = mix32(cell_global ^ P.seed_lo) ^ P.seed_hi;
+  const uint32_t key = mix32(cell_global ^ drop_seed_lo(P)) ^ drop_seed_hi(P);
 #pragma unroll
   for (int k = 0; k < N; k += 2) {
     const uint32_t r = mix32(key + (uint32_t)(layer * 32 + ((U0 + k) >> 1)) * 0x9E3779B9u);

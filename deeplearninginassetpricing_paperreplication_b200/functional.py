@@ -148,6 +148,7 @@ class StepOptions:
     precision: str = "fp32"
     dropout_p: float = 0.0          # > 0 only in train mode (src/model.py:213)
     dropout_seed: int = 0
+    dropout_seed_dev: Optional[torch.Tensor] = None   # int64 [1] on the device: overrides dropout_seed (GraphedStep)
     shard: Optional["MonthShard"] = None
 
 
@@ -272,7 +273,7 @@ class GanStepFn(torch.autograd.Function):
             g = torch.empty(KM, T, N, dtype=torch.float32, device=dev) if opts.need_moments else None
             _timed_call("dlap_cell_fwd", dev, ws.pp, _ptr(x), _ptr(R), _ptr(mask), _ptr(index), C.byref(tens), _ptr(a_loc),
                       _ptr(c_loc), _ptr(u), _ptr(g), _ptr(ws.row_part), prec, float(opts.dropout_p),
-                      int(opts.dropout_seed), st)
+                      int(opts.dropout_seed), _ptr(opts.dropout_seed_dev), st)
             row_stats = torch.empty(T, RS_W, dtype=torch.float32, device=dev)
             pr = torch.empty(T, dtype=torch.float32, device=dev)
             scalars = torch.empty(SC_W, dtype=torch.float32, device=dev)
@@ -338,7 +339,8 @@ class GanStepFn(torch.autograd.Function):
             _timed_call("dlap_cell_bwd", dev, ws.pp, _ptr(x), _ptr(R), _ptr(mask), _ptr(index), C.byref(tens), _ptr(a_loc),
                       _ptr(c_loc), _ptr(row_stats), _ptr(ws.ds_part), _ptr(g_pr), _ptr(G), _ptr(scalars),
                       int(opts.weighted_loss), int(want_sdf), int(want_mom), _ptr(ws.wpart),
-                      _ptr(ws.dadc_part), prec, float(opts.dropout_p), int(opts.dropout_seed), st)
+                      _ptr(ws.dadc_part), prec, float(opts.dropout_p), int(opts.dropout_seed),
+                      _ptr(opts.dropout_seed_dev), st)
             # one zero fill for all twelve gradient tensors (views of one flat buffer)
             sizes = [0 if p is None else p.numel() for p in params]
             flat_g = torch.zeros(sum(sizes), dtype=torch.float32, device=dev)
@@ -390,7 +392,7 @@ def sdf_weights(macro, x, mask, params, h0=None, c0=None, normalized=False, prec
         index = ws.panel_index(mask) if precision == "bf16x3" else None
         u = torch.empty(T, N, dtype=torch.float32, device=dev)
         _lib.call("dlap_cell_fwd", ws.pp, _ptr(x), None, _ptr(mask), _ptr(index), C.byref(tens), _ptr(a_t), _ptr(c_t),
-                  _ptr(u), None, _ptr(ws.row_part), _PRECISIONS[precision], 0.0, 0, st)
+                  _ptr(u), None, _ptr(ws.row_part), _PRECISIONS[precision], 0.0, 0, None, st)
         row_stats = torch.empty(T, RS_W, dtype=torch.float32, device=dev)
         pr = torch.empty(T, dtype=torch.float32, device=dev)
         scalars = torch.empty(SC_W, dtype=torch.float32, device=dev)

@@ -254,10 +254,12 @@ class AssetPricingGAN(nn.Module):
         H = self.sdf_net.macro_lstm.output_dim if with_macro else 0
         h0, c0 = _hidden_pair(hidden, H, dev) if with_macro else (None, None)
         p_drop = self.sdf_net.dropout_p if self.training else 0.0
-        seed = int(torch.randint(0, 2 ** 62, (1,)).item()) if p_drop > 0 else 0   # CPU generator: no sync
+        seed_dev = getattr(self, "_seed_dev", None) if p_drop > 0 else None   # GraphedStep: seed in device memory
+        seed = int(torch.randint(0, 2 ** 62, (1,)).item()) if p_drop > 0 and seed_dev is None else 0   # CPU generator: no sync
         opts = Fn.StepOptions(weighted_loss=bool(self.weighted_loss),
                               need_moments=(phase != 'unconditional'), precision=self.precision,
-                              dropout_p=p_drop, dropout_seed=seed, shard=self.month_shard)
+                              dropout_p=p_drop, dropout_seed=seed, dropout_seed_dev=seed_dev,
+                              shard=self.month_shard)
         l_c, l_u, pr, w, sharpe, hn, cn = Fn.GanStepFn.apply(
             opts, macro_features, x, returns, mask, h0, c0, *params)
         zero = self._zero(dev)
@@ -310,14 +312,23 @@ class GraphedStep:
 
     The panel tensors are the ones passed in (full-batch training on a resident panel, as the reference's
     loops do); copy new VALUES into them with ``.copy_()`` if needed, but keep the mask: its valid-cell index
-    is part of the capture.  Dropout must be off (a captured seed would repeat the same mask).  A month-sharded
-    model captures its NCCL all-reduces with the kernels; every rank must then replay in lock-step."""
+    is part of the capture.  With dropout on (model.train(), p > 0) the seed lives in device memory and the graph
+    itself advances it, so every replay draws a fresh mask; month-sharded ranks start from the same seed.  A
+    month-sharded model captures its NCCL all-reduces with the kernels; every rank must then replay in lock-step."""
 
     def __init__(self, model: "AssetPricingGAN", macro_features, individual_features, returns, mask,
                  hidden=None, phase: str = 'conditional', warmup: int = 3):
-        if model.training and model.sdf_net.dropout_p > 0:
-            raise ValueError("GraphedStep needs dropout off: a captured dropout seed would repeat one mask")
         self.model, self.args = model, (macro_features, individual_features, returns, mask)
+        self.seed = None
+        if model.training and model.sdf_net.dropout_p > 0:
+            s0 = int(torch.randint(0, 2 ** 62, (1,)).item())
+            if model.month_shard is not None:             # the same masks on every rank
+                import torch.distributed as dist
+                t = torch.tensor([s0], dtype=torch.int64, device=individual_features.device)
+                dist.broadcast(t, src=dist.get_global_rank(model.month_shard.group, 0) if model.month_shard.group
+                               is not None else 0, group=model.month_shard.group)
+                s0 = int(t.item())
+            self.seed = torch.tensor([s0], dtype=torch.int64, device=individual_features.device)
         self.kw = {"hidden": hidden, "phase": phase}
         dev = individual_features.device
         side = torch.cuda.Stream(dev)
@@ -342,8 +353,14 @@ class GraphedStep:
     def _eager(self, zero=True):
         if zero:
             self.model.zero_grad(set_to_none=True)
-        out = self.model(*self.args, **self.kw)
-        out['loss'].backward()
+        self.model._seed_dev = self.seed
+        try:
+            if self.seed is not None:
+                self.seed.add_(0x9E3779B97F4A7C15 >> 2)      # next mask; part of the captured graph
+            out = self.model(*self.args, **self.kw)
+            out['loss'].backward()
+        finally:
+            self.model._seed_dev = None
         return out
 
     def step(self):

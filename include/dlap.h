@@ -122,14 +122,16 @@ int dlap_panel_pull(const dlap_plan* plan, const float* x_host, const int32_t* i
  * row_part = per-tile sums of m, m u, m u R, m R.  R may be NULL (weights-only inference).
  * dropout_p > 0 (model.train(), src/model.py:213, src/train.py:66): each hidden unit of each
  * stock-month is dropped with probability round(p*65536)/65536 by a counter-based generator keyed
- * on (dropout_seed, stock-month, layer, unit); pass the same seed to dlap_cell_bwd.
+ * on (dropout_seed, stock-month, layer, unit); pass the same seed to dlap_cell_bwd.  dropout_seed_dev (device,
+ * one uint64, may be NULL) overrides dropout_seed when given: the seed of a step that is replayed from a CUDA
+ * graph has to live in device memory.
  * index: dlap_panel_index output, required for BF16X3 (row_part is then per valid-cell tile; u and g are
  * written for unmasked cells only and left-packed: the j-th unmasked stock of month t at [t*N + j]); ignored
  * (may be NULL) for FP32 (dense u, g). */
 int dlap_cell_fwd(const dlap_plan* plan, const float* x, const float* R, const uint8_t* mask,
                   const int32_t* index, const dlap_tensors* params, const float* a_t, const float* c_t, float* u,
                   float* g, double* row_part, int precision, float dropout_p, uint64_t dropout_seed,
-                  void* stream);
+                  const uint64_t* dropout_seed_dev, void* stream);
 
 /* Per-month statistics: N_t, mu_t (src/model.py:276-278), P_t, portfolio return pr_t and
  * S_t = 1 + pr_t (src/model.py:359-367, :380), Rbar_t; N_bar (src/model.py:360) and the Sharpe
@@ -192,7 +194,7 @@ int dlap_cell_bwd(const dlap_plan* plan, const float* x, const float* R, const u
                   const float* row_stats, const double* dS_part, const float* dpr_cot,
                   const float* G, const float* scalars, int weighted_loss, int want_sdf,
                   int want_mom, float* wpart, float* dadc_part, int precision, float dropout_p,
-                  uint64_t dropout_seed, void* stream);
+                  uint64_t dropout_seed, const uint64_t* dropout_seed_dev, void* stream);
 
 /* Fixed-order sum of the partials into the reference's gradient layouts: grads->w1[:, :F], w2, b2,
  * w3, b3 (= 0, demeaning), wq[:, M:]; and dadc [T,72] = da_t | dc_t summed over stocks.

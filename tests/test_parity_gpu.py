@@ -124,7 +124,7 @@ def test_forward_stages_rand_small():
     u = torch.empty(T, N, device=dev()); gq = torch.empty(8, T, N, device=dev())
     _lib.call("dlap_cell_fwd", ws.pp, x.data_ptr(), R.data_ptr(), mask.data_ptr(), None, C.byref(tens),
               a_t.data_ptr(), c_t.data_ptr(), u.data_ptr(), gq.data_ptr(), ws.row_part.data_ptr(), 0, 0.0, 0,
-              None)
+              None, None)
     torch.cuda.synchronize()
     assert np.abs(_np(u) - s["u"]).max() < 1e-5 * max(1.0, np.abs(s["u"]).max())
     gref = np.transpose(s["q"], (2, 0, 1)) * s["rm"][None]
@@ -187,7 +187,7 @@ def test_forward_stages_tensor_core_visits_only_unmasked_cells():
     u = torch.full((T, N), float("nan"), device=dev()); gq = torch.full((8, T, N), float("nan"), device=dev())
     _lib.call("dlap_cell_fwd", ws.pp, x.data_ptr(), R.data_ptr(), mask.data_ptr(), index.data_ptr(), C.byref(tens),
               a_t.data_ptr(), c_t.data_ptr(), u.data_ptr(), gq.data_ptr(), ws.row_part.data_ptr(), 1, 0.0, 0,
-              None)
+              None, None)
     torch.cuda.synchronize()
     m = g["mask"]
     un, gn = _np(u), _np(gq)
@@ -273,6 +273,36 @@ def test_graphed_step_replays_the_eager_step_bit_for_bit(precision):
         for k, p in model.named_parameters():
             if k in ref_grads:
                 assert torch.equal(ref_grads[k], p.grad), k
+
+
+@pytest.mark.parametrize("precision", ["fp32", "bf16x3"])
+def test_graphed_step_draws_a_fresh_dropout_mask_every_replay(precision):
+    """Train mode: the dropout seed of a GraphedStep lives in device memory and the graph advances it.  A replay
+    equals the eager step run with that same device seed, and consecutive replays differ."""
+    g = load_golden("rand_small")
+    params = golden_params(g)
+    macro, x, R, mask, _ = _panel(g)
+    model = _model_from(params, 178).train()
+    model.precision = precision
+    model.sdf_net.dropout_p = 0.3
+    gs = model.graphed_step(macro, x, R, mask)
+    assert gs.seed is not None
+    out = gs.step()
+    torch.cuda.synchronize()
+    loss1 = out["loss"].detach().clone()
+    grad1 = model.sdf_net.fc_layers[0].weight.grad.clone()
+    model.zero_grad(set_to_none=True)
+    model._seed_dev = gs.seed.clone()                    # the seed that replay used
+    try:
+        ref = model(macro, x, R, mask)
+        ref["loss"].backward()
+    finally:
+        model._seed_dev = None
+    assert torch.equal(ref["loss"].detach(), loss1)
+    assert torch.equal(model.sdf_net.fc_layers[0].weight.grad, grad1)
+    out = gs.step()
+    torch.cuda.synchronize()
+    assert not torch.equal(out["loss"].detach(), loss1)
 
 
 # ---- full step against the reference's own outputs ---------------------------------------------------
