@@ -44,22 +44,52 @@ def synthetic_panel(T, N, F, M, seed, valid=0.4):
 
 
 class ClockSampler(threading.Thread):
-    """nvidia-smi clocks + throttle reasons during the timed region (B200_PROFILING.md)."""
+    """SM clock + throttle reasons during the timed region (B200_PROFILING.md), read through NVML in-process
+    (nvidia_ml_py); falls back to polling `nvidia-smi` when NVML cannot be loaded.  Rank 0 only: eight ranks
+    spawning nvidia-smi every 20 ms compete with the launches they are meant to observe."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index):
         super().__init__(daemon=True)
         self.index, self.rows, self._halt = index, [], threading.Event()
+        self.nvml = self.handle = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            try:
+                uuid = "GPU-" + str(torch.cuda.get_device_properties(index).uuid)
+                self.handle = pynvml.nvmlDeviceGetHandleByUUID(uuid.encode() if hasattr(uuid, "encode") else uuid)
+            except Exception:
+                self.handle = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.nvml = pynvml
+        except Exception:
+            self.nvml = None
+
+    def _sample_nvml(self):
+        n, h = self.nvml, self.handle
+        sm = n.nvmlDeviceGetClockInfo(h, n.NVML_CLOCK_SM)
+        mx = n.nvmlDeviceGetMaxClockInfo(h, n.NVML_CLOCK_SM)
+        try:
+            bits = n.nvmlDeviceGetCurrentClocksEventReasons(h)
+        except Exception:
+            bits = n.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+        flag = lambda name: "Active" if bits & getattr(n, name, 0) else "Not Active"
+        return [str(sm), str(mx), flag("nvmlClocksThrottleReasonHwSlowdown"),
+                flag("nvmlClocksThrottleReasonHwThermalSlowdown"), flag("nvmlClocksThrottleReasonSwThermalSlowdown"),
+                flag("nvmlClocksThrottleReasonSwPowerCap")]
 
     def run(self):
         while not self._halt.is_set():
             try:
-                out = subprocess.run(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
-                                      "--format=csv,noheader,nounits"], capture_output=True, text=True,
-                                     timeout=5).stdout.strip()
-                if out:
-                    self.rows.append([c.strip() for c in out.split(",")])
+                if self.nvml is not None:
+                    self.rows.append(self._sample_nvml())
+                else:
+                    out = subprocess.run(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits"], capture_output=True, text=True,
+                                         timeout=5).stdout.strip()
+                    if out:
+                        self.rows.append([c.strip() for c in out.split(",")])
             except Exception:
                 pass
             self._halt.wait(0.02)
@@ -199,13 +229,14 @@ def run_ours(args, rank, world):
         run_step, launches_per_step = gs.step, gs.launches
         for _ in range(3):
             run_step()
-    sampler = ClockSampler(local)
-    sampler.start()
+    sampler = ClockSampler(local) if rank == 0 else None
+    if sampler is not None:
+        sampler.start()
     l0 = sum(w.launches for w in Fn._workspaces.values())
     ms = timed(run_step, args.steps)
     launches = (launches_per_step * args.steps if launches_per_step is not None
                 else sum(w.launches for w in Fn._workspaces.values()) - l0)
-    clocks = sampler.stop()
+    clocks = sampler.stop() if sampler is not None else None
     model.train()
     cells = T * N * world
     valid_cells = int(mask.sum()) if args.precision != "fp32" else T * N

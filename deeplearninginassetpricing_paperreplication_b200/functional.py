@@ -80,6 +80,21 @@ def _timed_call(name, dev, *args):
         end.record(torch.cuda.current_stream(dev))
 
 
+class _timed_region:
+    """`with _timed_region(name, dev):` -- the enclosed stream work is bracketed like an entry point."""
+
+    def __init__(self, name, dev):
+        self.name, self.dev = name, dev
+
+    def __enter__(self):
+        self.end = kernel_timer.bracket(self.name, self.dev) if kernel_timer is not None else None
+
+    def __exit__(self, *exc):
+        if self.end is not None:
+            self.end.record(torch.cuda.current_stream(self.dev))
+        return False
+
+
 class Workspace:
     """Plan + pure scratch buffers for one (shape, device).  Scratch is reused by every call on
     that shape (single-stream semantics, like the reference); nothing that the backward pass
@@ -289,8 +304,9 @@ class GanStepFn(torch.autograd.Function):
             if sh is None:
                 col, nsplit = ws.col_part, ws.plan.col_splits
             else:   # exchange 1: per-stock sums over ALL months
-                col = ws.col_part.view(ws.plan.col_splits, KM + 2, N).sum(dim=0)
-                torch.distributed.all_reduce(col, group=sh.group)
+                with _timed_region("exchange_fwd", dev):
+                    col = ws.col_part.view(ws.plan.col_splits, KM + 2, N).sum(dim=0)
+                    torch.distributed.all_reduce(col, group=sh.group)
                 nsplit = 1
             _timed_call("dlap_loss_finish", dev, ws.pp, _ptr(col), nsplit, _ptr(e), _ptr(t_i),
                       _ptr(ws.loss_part), _ptr(ws.counter), _ptr(scalars), st)
@@ -357,15 +373,16 @@ class GanStepFn(torch.autograd.Function):
                 wsm, dadc_all = ws, dadc
             else:   # exchange 2: per-cell weight grads + every month's da_t | dc_t row
                 wsm = workspace(sh.T_total, N, F, M, ws.plan.dims.H, dev)
-                dadc_all = torch.zeros(sh.T_total, 72, dtype=torch.float32, device=dev)
-                dadc_all[sh.t0:sh.t1] = dadc
-                flat = [dadc_all] + [grads[i] for i in (4, 6, 7, 8, 9, 10) if grads[i] is not None]
-                buf = torch.cat([f.reshape(-1) for f in flat])
-                torch.distributed.all_reduce(buf, group=sh.group)
-                off = 0
-                for f in flat:
-                    f.copy_(buf[off:off + f.numel()].view_as(f))
-                    off += f.numel()
+                with _timed_region("exchange_bwd", dev):
+                    dadc_all = torch.zeros(sh.T_total, 72, dtype=torch.float32, device=dev)
+                    dadc_all[sh.t0:sh.t1] = dadc
+                    flat = [dadc_all] + [grads[i] for i in (4, 6, 7, 8, 9, 10) if grads[i] is not None]
+                    buf = torch.cat([f.reshape(-1) for f in flat])
+                    torch.distributed.all_reduce(buf, group=sh.group)
+                    off = 0
+                    for f in flat:
+                        f.copy_(buf[off:off + f.numel()].view_as(f))
+                        off += f.numel()
             _timed_call("dlap_macro_bwd", dev, wsm.pp, _ptr(macro), C.byref(tens), _ptr(h0), _ptr(c0), _ptr(save),
                       _ptr(dadc_all), _ptr(wsm.dpre), int(want_sdf), int(want_mom), C.byref(gt), st)
             ws.launches += 2 if (want_sdf and M > 0) else 1

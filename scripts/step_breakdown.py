@@ -28,6 +28,8 @@ if world > 1:
     model.month_shard = Fn.make_month_shard(mask, rank * T, 240, dist.group.WORLD)
 names = ["dlap_macro_fwd", "dlap_cell_fwd", "dlap_row_finish", "dlap_col_partial", "dlap_loss_finish",
          "dlap_loss_coeff", "dlap_ds_rows", "dlap_cell_bwd", "dlap_grad_finish", "dlap_macro_bwd"]
+if world > 1:
+    names += ["exchange_fwd", "exchange_bwd"]
 res = {}
 for name in names:
     for it in range(23):
