@@ -113,3 +113,62 @@ def test_tc_forward_close_to_fp32_path_large():
         assert abs(float(a[key]) - float(b[key])) <= 2e-6 * abs(float(a[key]))
     rerun = mtc(*args)
     assert torch.equal(rerun["weights"], b["weights"]) and torch.equal(rerun["loss"], b["loss"])   # deterministic
+
+
+@pytest.mark.parametrize("F", [45, 13, 46])
+def test_tc_other_feature_counts_and_narrow_gather(F):
+    """F odd (or x only 4-byte aligned) takes the 4-byte gather path; results against the fp64 oracle."""
+    macro, x, R, mask = make_panel(6, 300, 20, F=F, seed=F)
+    x = x * mask[:, :, None]; R = R * mask
+    d = dev()
+    torch.manual_seed(1)
+    model = AssetPricingGAN({"individual_feature_dim": F, "macro_feature_dim": 20, "num_units_rnn": [4],
+                             "b200_precision": "bf16x3"}).to(d).eval()
+    params = {k: _np(v) for k, v in model.state_dict().items()}
+    out = model(macro.to(d), x.to(d), R.to(d), mask.to(d))
+    out["loss"].backward()
+    ref = cf.forward(params, _np(macro), _np(x), _np(R), _np(mask))
+    gref = cf.backward(params, _np(macro), _np(x), _np(R), _np(mask), ref)
+    assert rel_err(_np(out["weights"]), ref["weights"]) < WEIGHT_TOL
+    assert abs(float(out["loss"]) - float(ref["loss"])) <= LOSS_RTOL * abs(float(ref["loss"]))
+    for k, p in model.named_parameters():
+        if p.grad is None or k == "sdf_net.output_proj.bias":
+            continue
+        ok, info = _tc_grad_ok(k, _np(p.grad), gref[k].reshape(p.shape))
+        assert ok, info
+
+
+@pytest.mark.parametrize("offset_floats", [1, 2, 3])
+def test_tc_unaligned_panel_view(offset_floats):
+    """x as a view that starts 4, 8 or 12 bytes past a 16-byte boundary: same bits as the aligned copy."""
+    macro, x, R, mask = make_panel(5, 131, 8, seed=9)
+    x = x * mask[:, :, None]; R = R * mask
+    d = dev()
+    big = torch.zeros(5 * 131 * 46 + offset_floats, device=d)
+    xv = big[offset_floats:].view(5, 131, 46)
+    xv.copy_(x)
+    assert xv.data_ptr() % 16 == 4 * offset_floats
+    torch.manual_seed(2)
+    model = AssetPricingGAN({"macro_feature_dim": 8, "individual_feature_dim": 46,
+                             "b200_precision": "bf16x3"}).to(d).eval()
+    outs = []
+    for xin in (xv, x.to(d)):
+        model.zero_grad(set_to_none=True)
+        o = model(macro.to(d), xin, R.to(d), mask.to(d))
+        o["loss"].backward()
+        outs.append((o["weights"].clone(), o["loss"].detach().clone(), model.sdf_net.fc_layers[0].weight.grad.clone()))
+    for a, b in zip(*outs):
+        assert torch.equal(a, b)
+
+
+def test_tc_all_masked_panel():
+    macro, x, R, mask = make_panel(4, 150, 8, seed=1)
+    mask[:] = False
+    x = x * 0; R = R * 0
+    d = dev()
+    model = AssetPricingGAN({"macro_feature_dim": 8, "individual_feature_dim": 46,
+                             "b200_precision": "bf16x3"}).to(d).eval()
+    out = model(macro.to(d), x.to(d), R.to(d), mask.to(d))
+    out["loss"].backward()
+    assert float(out["loss"]) == 0.0 and float(out["weights"].abs().max()) == 0.0
+    assert all(torch.isfinite(p.grad).all() for p in model.parameters() if p.grad is not None)
