@@ -94,21 +94,6 @@ __device__ __forceinline__ float lane_transpose_sum16(float (&v)[16], int lane) 
   }
   return v[0] + __shfl_xor_sync(0xffffffffu, v[0], 16);
 }
-// Same for 8 per-lane values: every lane L returns sum_lanes v[L & 7].
-__device__ __forceinline__ float lane_transpose_sum8(float (&v)[8], int lane) {
-#pragma unroll
-  for (int s = 4; s >= 1; s >>= 1) {
-    const bool up = (lane & s) != 0;
-#pragma unroll
-    for (int i = 0; i < s; ++i) {
-      const float send = up ? v[i] : v[i + s];
-      const float keep = up ? v[i + s] : v[i];
-      v[i] = keep + __shfl_xor_sync(0xffffffffu, send, s);
-    }
-  }
-  float r = v[0] + __shfl_xor_sync(0xffffffffu, v[0], 8);
-  return r + __shfl_xor_sync(0xffffffffu, r, 16);
-}
 __device__ __forceinline__ void epi_barrier() { asm volatile("bar.sync 1, 512;" ::: "memory"); }
 }  // namespace
 

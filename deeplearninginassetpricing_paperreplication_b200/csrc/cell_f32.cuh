@@ -176,11 +176,10 @@ struct SmemFwd {
 
 __host__ __device__ inline int round4(int v) { return (v + 3) & ~3; }
 
-// Tensor-core kernels give every CTA a CONTIGUOUS range of `chunk` tiles; per-month partial sums are
-// then written once per (month, CTA) "segment": month t is touched by CTAs (t*tpm)/chunk ... and by at
-// most seg_max of them.
+// Tensor-core kernels give every CTA a CONTIGUOUS range of `chunk` valid-cell tiles; per-month partial sums
+// (da_t | dc_t) are then written once per (month, CTA) "segment": month t is touched by the consecutive CTAs
+// tile_start[t] / chunk .. (tile_start[t+1] - 1) / chunk, never more than its tile count.
 __host__ __device__ inline int tc_chunk(long long ntiles, int grid) { return (int)((ntiles + grid - 1) / grid); }
-__host__ __device__ inline int tc_seg_max(int tpm, int chunk) { return (tpm + chunk - 2) / chunk + 1; }
 
 // bytes of dynamic smem for the forward kernel
 __host__ __device__ inline size_t smem_fwd_bytes(int F) {

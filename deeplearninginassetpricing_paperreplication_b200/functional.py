@@ -357,32 +357,32 @@ class GanStepFn(torch.autograd.Function):
                       int(opts.weighted_loss), int(want_sdf), int(want_mom), _ptr(ws.wpart),
                       _ptr(ws.dadc_part), prec, float(opts.dropout_p), int(opts.dropout_seed),
                       _ptr(opts.dropout_seed_dev), st)
-            # one zero fill for all twelve gradient tensors (views of one flat buffer)
+            # one zero fill for all twelve gradient tensors (views of one flat buffer); month-sharded: the same
+            # buffer starts with the [T_total,72] da_t | dc_t rows (this rank fills its slab), so that exchange 2
+            # is ONE all-reduce over it -- gradients that are computed later (LSTM, b1, bq) are still zero
             sizes = [0 if p is None else p.numel() for p in params]
-            flat_g = torch.zeros(sum(sizes), dtype=torch.float32, device=dev)
+            head = 0 if sh is None else sh.T_total * 72
+            buf = torch.zeros(head + sum(sizes), dtype=torch.float32, device=dev)
+            flat_g = buf[head:]
             grads, off = [], 0
             for p, n in zip(params, sizes):
                 grads.append(None if p is None else flat_g[off:off + n].view_as(p))
                 off += n
             gt = _tensors(grads)
-            dadc = torch.empty(T, 72, dtype=torch.float32, device=dev)
+            if sh is None:
+                dadc_all = dadc = torch.empty(T, 72, dtype=torch.float32, device=dev)
+            else:
+                dadc_all = buf[:head].view(sh.T_total, 72)
+                dadc = dadc_all[sh.t0:sh.t1]
             _timed_call("dlap_grad_finish", dev, ws.pp, _ptr(ws.wpart), _ptr(ws.dadc_part), _ptr(index), prec, int(want_sdf),
                       int(want_mom), C.byref(gt), _ptr(dadc), st)
             ws.launches += 4
             if sh is None:
-                wsm, dadc_all = ws, dadc
+                wsm = ws
             else:   # exchange 2: per-cell weight grads + every month's da_t | dc_t row
                 wsm = workspace(sh.T_total, N, F, M, ws.plan.dims.H, dev)
                 with _timed_region("exchange_bwd", dev):
-                    dadc_all = torch.zeros(sh.T_total, 72, dtype=torch.float32, device=dev)
-                    dadc_all[sh.t0:sh.t1] = dadc
-                    flat = [dadc_all] + [grads[i] for i in (4, 6, 7, 8, 9, 10) if grads[i] is not None]
-                    buf = torch.cat([f.reshape(-1) for f in flat])
                     torch.distributed.all_reduce(buf, group=sh.group)
-                    off = 0
-                    for f in flat:
-                        f.copy_(buf[off:off + f.numel()].view_as(f))
-                        off += f.numel()
             _timed_call("dlap_macro_bwd", dev, wsm.pp, _ptr(macro), C.byref(tens), _ptr(h0), _ptr(c0), _ptr(save),
                       _ptr(dadc_all), _ptr(wsm.dpre), int(want_sdf), int(want_mom), C.byref(gt), st)
             ws.launches += 2 if (want_sdf and M > 0) else 1
