@@ -30,6 +30,7 @@ T_MONTHS, N_STOCKS, F_CHARS, M_MACRO = 240, 10_000, 46, 178
 ALGO_BYTES_FWD = 46 * 4 + 4 + 1          # x + R + mask per stock-month
 ALGO_BYTES_STEP = 2 * ALGO_BYTES_FWD     # forward + recomputing backward
 CPU_SAMPLE_N = 2_500                     # stocks in the CPU sample (cost is linear in T*N)
+E2E_RESERVE_SMS = int(os.environ.get("DLAP_E2E_RESERVE", "8"))                      # e2e leg: SMs left to the pull kernel of the next panel
 
 
 def synthetic_panel(T, N, F, M, seed, valid=0.4):
@@ -245,6 +246,9 @@ def run_ours(args, rank, world):
     # end to end: every step's panel comes from pinned host memory and its loss goes back to the host.
     # The way a data loader feeds a training loop: two device buffers, the copy of step k+1 runs on a
     # copy stream while step k computes; every step still pays for its own H2D inside the timed region.
+    # The per-cell kernels leave E2E_RESERVE_SMS SMs to the pull kernel of the next panel (they take one CTA per
+    # SM and all of its registers, so nothing else runs beside them otherwise).
+    Fn.reserve_sms = E2E_RESERVE_SMS
     copy_stream = torch.cuda.Stream(dev)
     bufs = [[torch.empty_like(t, device=dev) for t in host] for _ in range(2)]
     ready = [torch.cuda.Event() for _ in range(2)]
@@ -279,6 +283,7 @@ def run_ours(args, rank, world):
     # bytes that cross the bus per step: macro, returns, mask whole; of x only the rows of unmasked stock-months
     h2d = sum(t.numel() * t.element_size() for t in (host[0], host[2], host[3])) + int(mask.sum()) * F_CHARS * 4
     e2e = cells * k2 / (ms2 * 1e-3)
+    Fn.reserve_sms = 0
 
     if rank != 0:
         return
@@ -305,7 +310,8 @@ def run_ours(args, rank, world):
                 "ms_per_step": ms2 / k2,
                 "note": "every step: upload_panel(pinned host panel) + fwd + bwd + loss.item(); macro, returns and "
                         "mask go by DMA, the characteristic rows of unmasked stock-months (40 %) are read out of "
-                        "pinned host memory by dlap_panel_pull, masked rows never cross the bus"},
+                        "pinned host memory by dlap_panel_pull, masked rows never cross the bus; the pull of "
+                        "panel k+1 runs on 8 SMs beside the step on panel k (the per-cell kernels use the other 140)"},
         "gpu_launches": launches,
         "roofline": {"bound": "hbm", "kernel": "cell_bwd (recomputing per-cell backward, %s)" % args.precision,
                      "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,

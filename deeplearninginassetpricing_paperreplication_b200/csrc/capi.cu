@@ -176,13 +176,15 @@ int dlap_panel_index(const dlap_plan* plan, const uint8_t* mask, int32_t* index,
   return DLAP_OK;
 }
 
-int dlap_panel_pull(const dlap_plan* plan, const float* x_host, const int32_t* index, float* x_dev, void* stream) {
+int dlap_panel_pull(const dlap_plan* plan, const float* x_host, const int32_t* index, float* x_dev, int ctas,
+                    void* stream) {
   int rc = check_plan(plan);
   if (rc) return rc;
   REQ(x_host); REQ(index); REQ(x_dev);
   if ((reinterpret_cast<uintptr_t>(x_host) | reinterpret_cast<uintptr_t>(x_dev)) & 3) return DLAP_E_ALIGN;
-  CU(launch_panel_pull(x_host, index, plan->dims.T, plan->dims.N, plan->dims.F, x_dev, plan->grid_cell,
-                       (cudaStream_t)stream));
+  if (ctas < 0) return DLAP_E_SHAPE;
+  CU(launch_panel_pull(x_host, index, plan->dims.T, plan->dims.N, plan->dims.F, x_dev,
+                       ctas > 0 ? ctas : plan->grid_cell, (cudaStream_t)stream));
   return DLAP_OK;
 }
 

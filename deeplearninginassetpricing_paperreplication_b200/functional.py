@@ -100,13 +100,17 @@ class Workspace:
     that shape (single-stream semantics, like the reference); nothing that the backward pass
     needs from the forward pass lives here."""
 
-    def __init__(self, T: int, N: int, F: int, M: int, H: int, device: torch.device):
+    def __init__(self, T: int, N: int, F: int, M: int, H: int, device: torch.device, reserve: int = 0):
         self.device = device
         dims = DlapDims(T, N, F, M, H if M > 0 else 0)
         self.plan = DlapPlan()
         _lib.call("dlap_make_plan", C.byref(dims), device.index if device.index is not None
                   else torch.cuda.current_device(), C.byref(self.plan))
         p = self.plan
+        # SMs left to a concurrent dlap_panel_pull (reserve_sms): the persistent per-cell kernels take one CTA
+        # per SM and all of its registers, so they only overlap with the ingest if they leave some SMs alone
+        self.reserve = min(int(reserve), p.grid_cell - 1) if reserve > 0 else 0
+        p.grid_cell -= self.reserve
         self.pp = C.byref(p)
         f64 = lambda nbytes: torch.empty(max(nbytes // 8, 1), dtype=torch.float64, device=device)
         f32 = lambda nbytes: torch.empty(max(nbytes // 4, 1), dtype=torch.float32, device=device)
@@ -147,12 +151,16 @@ def panel_index(ws: "Workspace", mask: torch.Tensor) -> torch.Tensor:
 
 _workspaces: Dict[Tuple, Workspace] = {}
 
+# SMs that the per-cell kernels leave free so that upload_panel's pull kernel of the NEXT panel can run beside
+# them (a training loop that double-buffers its panels sets this before its first step; 0 = use every SM)
+reserve_sms = 0
+
 
 def workspace(T, N, F, M, H, device) -> Workspace:
-    key = (T, N, F, M, H if M > 0 else 0, device.index)
+    key = (T, N, F, M, H if M > 0 else 0, device.index, reserve_sms)
     ws = _workspaces.get(key)
     if ws is None:
-        ws = _workspaces[key] = Workspace(T, N, F, M, H, device)
+        ws = _workspaces[key] = Workspace(T, N, F, M, H, device, reserve_sms)
     return ws
 
 
@@ -210,7 +218,8 @@ def upload_panel(macro, x, R, mask, device, out=None):
         if x.is_pinned() and x.dtype == torch.float32 and x.is_contiguous() and mask.dtype == torch.bool:
             ws = workspace(T, N, F, 0, 0, device)
             index = panel_index(ws, d_mask)
-            _lib.call("dlap_panel_pull", ws.pp, x.data_ptr(), _ptr(index), _ptr(d_x), _stream(device))
+            _lib.call("dlap_panel_pull", ws.pp, x.data_ptr(), _ptr(index), _ptr(d_x), int(reserve_sms),
+                      _stream(device))
             ws.launches += 1
         else:
             d_x.copy_(x, non_blocking=True)

@@ -113,8 +113,11 @@ int dlap_panel_index(const dlap_plan* plan, const uint8_t* mask, int32_t* index,
  * (cudaHostAlloc / cudaHostRegister; torch: tensor.pin_memory()), x_dev the device panel.  The rows of unmasked
  * stock-months (index: dlap_panel_index of the mask, already on the device) are read over the bus by the
  * kernel itself; masked rows are not transferred and arrive as zeros (the loader zero-fills them anyway,
- * src/data_loader.py:61-65).  One memset + one launch. */
-int dlap_panel_pull(const dlap_plan* plan, const float* x_host, const int32_t* index, float* x_dev, void* stream);
+ * src/data_loader.py:61-65).  One memset + one launch of `ctas` CTAs of 256 threads (0: plan->grid_cell; a
+ * handful saturates PCIe).  To overlap the pull of the next panel with a step, lower plan->grid_cell of the
+ * plan the per-cell kernels run with by the same number: they take one CTA per SM and all of its registers. */
+int dlap_panel_pull(const dlap_plan* plan, const float* x_host, const int32_t* index, float* x_dev, int ctas,
+                    void* stream);
 
 /* SDFNetwork.forward body on every stock-month (src/model.py:251-271) and MomentNetwork.forward
  * (src/model.py:132-161 with the input of :514-518): u = MLP(x | a_t) [T,N];
