@@ -25,7 +25,8 @@ constexpr int NT_TC = 512;
 constexpr int BR = 32;                                   // rows per gather batch (64 registers in flight per lane)
 constexpr int NB = TILE / BR;                            // batches per tile
 constexpr int NGW = 7;                                   // gather warps: 0, 2 (also TMEM owner), 3, 4..7
-constexpr int NXS = 3;                                   // slots of X image, W1 image and layer-1 accumulator
+constexpr int NXS = 3;                                   // slots of X image and W1 image
+constexpr int NDA = 4;                                   // layer-1 accumulator (then h1) slots in TMEM
 struct SmemTc {
   uint8_t* base;
   __device__ uint8_t* xh(int sl) const { return base + sl * 2 * X_IMG; }
@@ -40,16 +41,17 @@ struct SmemTc {
   __device__ uint32_t* tmem_slot() const { return reinterpret_cast<uint32_t*>(bars() + 24); }
 };
 enum { F_XOP_FULL = 0, F_XOP_EMPTY = 3, F_D1_FULL = 6, F_H1_FULL = 10,
-       F_D2_FULL = 12, F_D2_EMPTY = 14 };
+       F_D2_FULL = 14, F_D2_EMPTY = 16 };
 
 constexpr size_t SMEM_TC_BYTES = (size_t)NXS * 2 * (X_IMG + W1_IMG) + 2 * W2_IMG +
                                  128 * 4 + 24 * 8 + 16 + 256;
 
-// TMEM columns: three layer-1 accumulators (layer 1 runs two tiles ahead of its epilogue), two layer-2 ones.
+// TMEM columns: four layer-1 accumulators (layer 1 runs three tiles ahead of layer 2, and each epilogue group
+// has two tiles in flight), two layer-2 ones.
 // After E1 the first 64 columns of a layer-1 slot hold h1 as packed bf16 pairs, in two blocks of 32 units:
 // columns [32b, 32b+16) = hi of units 32b .. 32b+31, [32b+16, 32b+32) = lo  (each block is rewritten in place
 // by the thread that just read it).  K step ks (units 16ks ..) of layer 2 reads 8 columns of each.
-constexpr uint32_t COL_A = 0, COL_A_STRIDE = 96, COL_B0 = 288, COL_B1 = 352, TMEM_COLS = 512;
+constexpr uint32_t COL_A = 0, COL_A_STRIDE = 96, COL_B0 = 384, COL_B1 = 448, TMEM_COLS = 512;
 __device__ __forceinline__ uint32_t h1_col_hi(int ks) { return (uint32_t)((ks >> 1) * 32 + (ks & 1) * 8); }
 __device__ __forceinline__ uint32_t h1_col_lo(int ks) { return h1_col_hi(ks) + 16; }
 }  // namespace
@@ -78,14 +80,9 @@ __global__ void __launch_bounds__(NT_TC, 1) cell_fwd_tc_kernel(const CellParams 
   for (int sl = 0; sl < NXS; ++sl) init_x_images(s.xh(sl), s.xl(sl), tid, NT_TC);
   if (tid < 64) { s.b2s()[tid] = __ldg(P.b2 + tid); s.w3s()[tid] = __ldg(P.W3 + tid); }
   if (tid == 0) {
-    for (int i = 0; i < NXS; ++i) {
-      mbar_init(bar + F_XOP_FULL + i, NB);   mbar_init(bar + F_XOP_EMPTY + i, 1);
-      mbar_init(bar + F_D1_FULL + i, 1);
-    }
-    for (int i = 0; i < 2; ++i) {
-      mbar_init(bar + F_H1_FULL + i, 4);
-      mbar_init(bar + F_D2_FULL + i, 1);     mbar_init(bar + F_D2_EMPTY + i, 4);
-    }
+    for (int i = 0; i < NXS; ++i) { mbar_init(bar + F_XOP_FULL + i, NB); mbar_init(bar + F_XOP_EMPTY + i, 1); }
+    for (int i = 0; i < NDA; ++i) { mbar_init(bar + F_D1_FULL + i, 1); mbar_init(bar + F_H1_FULL + i, 4); }
+    for (int i = 0; i < 2; ++i) { mbar_init(bar + F_D2_FULL + i, 1); mbar_init(bar + F_D2_EMPTY + i, 4); }
     fence_mbar_init();
   }
   if (warp == 2) tc::tmem_alloc(s.tmem_slot(), TMEM_COLS);
@@ -100,9 +97,9 @@ __global__ void __launch_bounds__(NT_TC, 1) cell_fwd_tc_kernel(const CellParams 
     {
       const uint32_t id1 = tc::idesc_bf16(128, N1, 0, 0), id2 = tc::idesc_bf16(128, 64, 0, 0);
       const uint64_t w2h = tc::smem_desc(smem_u32(s.w2h()), 64 * 16, 128), w2l = tc::smem_desc(smem_u32(s.w2l()), 64 * 16, 128);
-      // Layer 1 runs two tiles ahead of its epilogue (three accumulator / X / W1 slots): L1(0) L1(1) | L2(0)
-      // L1(2) | L2(1) L1(3) | ...  so an epilogue group that finishes a tile finds the next one's z1 waiting,
-      // and a late gather delays only layer 1, never layer 2.
+      // Layer 1 runs three tiles ahead of layer 2 (four accumulator slots, three X / W1 slots): L1(0) L1(1) L1(2)
+      // | L2(0) L1(3) | L2(1) L1(4) | ...  An epilogue group starts E1 of its next tile while layer 2 of its
+      // current one runs, and a late gather delays only layer 1, never layer 2.
       auto issue_l1 = [&](int i) {
         const int xs = i % NXS, use = i / NXS;
         mbar_wait(bar + F_XOP_FULL + xs, use & 1);
@@ -110,27 +107,26 @@ __global__ void __launch_bounds__(NT_TC, 1) cell_fwd_tc_kernel(const CellParams 
         if (lane == 0) DLAP_STAMP(i, 8);
         const uint64_t ah = tc::smem_desc(smem_u32(s.xh(xs)), X_LBO, 128), al = tc::smem_desc(smem_u32(s.xl(xs)), X_LBO, 128);
         const uint64_t bh = tc::smem_desc(smem_u32(s.w1h(xs)), N1 * 16, 128), bl = tc::smem_desc(smem_u32(s.w1l(xs)), N1 * 16, 128);
-        const uint32_t d = tbase + COL_A + xs * COL_A_STRIDE;
+        const uint32_t d = tbase + COL_A + (i % NDA) * COL_A_STRIDE;
         if (tc::elect_one()) {
 #pragma unroll
           for (int ks = 0; ks < KG1 / 2; ++ks)
             umma3(d, tc::desc_advance(ah, ks * 2 * X_LBO), tc::desc_advance(al, ks * 2 * X_LBO),
                   tc::desc_advance(bh, ks * 2 * N1 * 16), tc::desc_advance(bl, ks * 2 * N1 * 16), id1, ks == 0);
           tc::umma_commit(bar + F_XOP_EMPTY + xs);
-          tc::umma_commit(bar + F_D1_FULL + xs);
+          tc::umma_commit(bar + F_D1_FULL + i % NDA);
         }
         __syncwarp();
         if (lane == 0) DLAP_STAMP(i, 9);
       };
-      if (my_tiles > 0) issue_l1(0);
-      if (my_tiles > 1) issue_l1(1);
-      for (int j = 0; j < my_tiles; ++j) {           // layer 2 of tile j, then layer 1 of tile j + 2
+      for (int j = 0; j < 3 && j < my_tiles; ++j) issue_l1(j);
+      for (int j = 0; j < my_tiles; ++j) {           // layer 2 of tile j, then layer 1 of tile j + 3
         const int sl = j & 1, use = j >> 1;
-        mbar_wait(bar + F_H1_FULL + sl, use & 1);    // also: E1(j) has read the accumulator slot L1(j + 3) will reuse
+        mbar_wait(bar + F_H1_FULL + j % NDA, (j / NDA) & 1);
         mbar_wait(bar + F_D2_EMPTY + sl, (use & 1) ^ 1);
         tc::fence_after_sync();
         if (lane == 0) DLAP_STAMP(j, 10);
-        const uint32_t a = tbase + COL_A + (j % NXS) * COL_A_STRIDE;     // h1 of tile j, in its z1 slot
+        const uint32_t a = tbase + COL_A + (j % NDA) * COL_A_STRIDE;     // h1 of tile j, in its z1 slot
         const uint32_t d = tbase + (sl ? COL_B1 : COL_B0);
         if (tc::elect_one()) {
 #pragma unroll
@@ -144,7 +140,7 @@ __global__ void __launch_bounds__(NT_TC, 1) cell_fwd_tc_kernel(const CellParams 
         }
         __syncwarp();
         if (lane == 0) DLAP_STAMP(j, 11);
-        if (j + 2 < my_tiles) issue_l1(j + 2);
+        if (j + 3 < my_tiles) issue_l1(j + 3);
       }
     }
   } else if (warp < 8) {
@@ -179,7 +175,7 @@ __global__ void __launch_bounds__(NT_TC, 1) cell_fwd_tc_kernel(const CellParams 
       const int tile = tile_lo + i, sl = i & 1, use = i >> 1;
       const int t = t_nxt, n = n_nxt;
       const size_t pi = (size_t)t * P.N + pos_nxt;
-      const uint32_t dA = tbase + lane_base + COL_A + (i % NXS) * COL_A_STRIDE, dB = tbase + lane_base + (sl ? COL_B1 : COL_B0);
+      const uint32_t dA = tbase + lane_base + COL_A + (i % NDA) * COL_A_STRIDE, dB = tbase + lane_base + (sl ? COL_B1 : COL_B0);
       // this cell's return: issued now, consumed after both layers (HBM latency hidden); every listed cell
       // is unmasked, so m = 1 exactly where the row exists
       const bool live = n >= 0;
@@ -189,7 +185,7 @@ __global__ void __launch_bounds__(NT_TC, 1) cell_fwd_tc_kernel(const CellParams 
       if (i + 2 < my_tiles) load_row(tile_lo + i + 2);
       // -- after layer 1: h1 = relu(z1) -> bf16 hi/lo image
       const bool stamp = q4 == 0 && lane == 0;
-      mbar_wait(bar + F_D1_FULL + i % NXS, (i / NXS) & 1);
+      mbar_wait(bar + F_D1_FULL + i % NDA, (i / NDA) & 1);
       tc::fence_after_sync();
       if (stamp) DLAP_STAMP(i, 12);
 #pragma unroll
@@ -213,7 +209,7 @@ __global__ void __launch_bounds__(NT_TC, 1) cell_fwd_tc_kernel(const CellParams 
       tc::tmem_wait_st();
       tc::fence_before_sync();
       __syncwarp();
-      if (lane == 0) mbar_arrive(bar + F_H1_FULL + sl);
+      if (lane == 0) mbar_arrive(bar + F_H1_FULL + i % NDA);
       if (stamp) DLAP_STAMP(i, 13);
       // -- while layer 2 runs: everything that does not need u (moments, their stores, the u-free row sums)
       const float m = live ? 1.f : 0.f;
