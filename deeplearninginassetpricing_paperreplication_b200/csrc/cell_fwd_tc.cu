@@ -171,19 +171,22 @@ __global__ void __launch_bounds__(NT_TC, 1) cell_fwd_tc_kernel(const CellParams 
       n_nxt = (cell < mc.ncell(tile)) ? __ldg(vidx_row(P, mc.t) + pos_nxt) : -1;
     };
     if (e < my_tiles) load_row(tile_lo + e);
-    for (int i = e; i < my_tiles; i += 2) {
-      const int tile = tile_lo + i, sl = i & 1, use = i >> 1;
+    // per-tile state that E1 hands to E2 (a group has two tiles in flight: E1 of its next tile runs while layer 2
+    // of the current one is on the tensor core)
+    struct TileState { size_t pi; float r; uint32_t gi; bool live; double v0, v3; };
+    // E1 of local tile i: h1 = relu(z1) -> TMEM, moments and everything else that does not need u
+    auto do_e1 = [&](int i) {
+      TileState S;
       const int t = t_nxt, n = n_nxt;
-      const size_t pi = (size_t)t * P.N + pos_nxt;
-      const uint32_t dA = tbase + lane_base + COL_A + (i % NDA) * COL_A_STRIDE, dB = tbase + lane_base + (sl ? COL_B1 : COL_B0);
-      // this cell's return: issued now, consumed after both layers (HBM latency hidden); every listed cell
-      // is unmasked, so m = 1 exactly where the row exists
-      const bool live = n >= 0;
-      const size_t gi = (size_t)t * P.N + (live ? n : 0);
-      float r = 0.f;
-      if (live && P.R) r = __ldg(P.R + gi);
+      S.pi = (size_t)t * P.N + pos_nxt;
+      const uint32_t dA = tbase + lane_base + COL_A + (i % NDA) * COL_A_STRIDE;
+      // this cell's return; every listed cell is unmasked, so m = 1 exactly where the row exists
+      S.live = n >= 0;
+      const size_t gi = (size_t)t * P.N + (S.live ? n : 0);
+      S.gi = (uint32_t)gi;
+      S.r = 0.f;
+      if (S.live && P.R) S.r = __ldg(P.R + gi);
       if (i + 2 < my_tiles) load_row(tile_lo + i + 2);
-      // -- after layer 1: h1 = relu(z1) -> bf16 hi/lo image
       const bool stamp = q4 == 0 && lane == 0;
       mbar_wait(bar + F_D1_FULL + i % NDA, (i / NDA) & 1);
       tc::fence_after_sync();
@@ -194,7 +197,7 @@ __global__ void __launch_bounds__(NT_TC, 1) cell_fwd_tc_kernel(const CellParams 
         tc::tmem_ld32(dA + c * 32, v);
 #pragma unroll
         for (int k = 0; k < 32; ++k) v[k] = fmaxf(v[k], 0.f);
-        if (DROP) tc_dropout<32>(P, (uint32_t)gi, 0, c * 32, v);
+        if (DROP) tc_dropout<32>(P, S.gi, 0, c * 32, v);
         uint32_t hi[16], lo[16];
 #pragma unroll
         for (int k = 0; k < 16; ++k) tc::split2(v[2 * k], v[2 * k + 1], hi[k], lo[k]);
@@ -211,19 +214,31 @@ __global__ void __launch_bounds__(NT_TC, 1) cell_fwd_tc_kernel(const CellParams 
       __syncwarp();
       if (lane == 0) mbar_arrive(bar + F_H1_FULL + i % NDA);
       if (stamp) DLAP_STAMP(i, 13);
-      // -- while layer 2 runs: everything that does not need u (moments, their stores, the u-free row sums)
-      const float m = live ? 1.f : 0.f;
       if (MOM) {
         const size_t plane = (size_t)P.T * P.N;
-        const float rm = r * m;
+        const float rm = S.live ? S.r : 0.f;
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
           const float gk = tc::tanh_fast(q[k]) * rm;
-          if (live) P.g[(size_t)k * plane + pi] = gk;
+          if (S.live) P.g[(size_t)k * plane + S.pi] = gk;
         }
       }
-      double v0 = live ? 1.0 : 0.0, v3 = live ? (double)r : 0.0;
-      v0 = warp_sum(v0); v3 = warp_sum(v3);
+      S.v0 = warp_sum(S.live ? 1.0 : 0.0);
+      S.v3 = warp_sum(S.live ? (double)S.r : 0.0);
+      return S;
+    };
+    TileState cur{}, nxt{};
+    if (e < my_tiles) cur = do_e1(e);
+    for (int i = e; i < my_tiles; i += 2) {
+      const int tile = tile_lo + i, sl = i & 1, use = i >> 1;
+      const bool stamp = q4 == 0 && lane == 0;
+      const uint32_t dB = tbase + lane_base + (sl ? COL_B1 : COL_B0);
+      if (i + 2 < my_tiles) nxt = do_e1(i + 2);      // while layer 2 of tile i runs
+      const bool live = cur.live;
+      const size_t pi = cur.pi;
+      const float r = cur.r, m = live ? 1.f : 0.f;
+      const uint32_t gi = cur.gi;
+      const double v0 = cur.v0, v3 = cur.v3;
       // -- after layer 2: u = b3 + W3 . relu(z2 + b2)
       mbar_wait(bar + F_D2_FULL + sl, use & 1);
       tc::fence_after_sync();
@@ -241,7 +256,7 @@ __global__ void __launch_bounds__(NT_TC, 1) cell_fwd_tc_kernel(const CellParams 
           v[4 * k] = fmaxf(v[4 * k] + bb.x, 0.f);         v[4 * k + 1] = fmaxf(v[4 * k + 1] + bb.y, 0.f);
           v[4 * k + 2] = fmaxf(v[4 * k + 2] + bb.z, 0.f); v[4 * k + 3] = fmaxf(v[4 * k + 3] + bb.w, 0.f);
         }
-        if (DROP) tc_dropout<32>(P, (uint32_t)gi, 1, c * 32, v);
+        if (DROP) tc_dropout<32>(P, gi, 1, c * 32, v);
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
           const float4 ww = w4[k];
@@ -266,6 +281,7 @@ __global__ void __launch_bounds__(NT_TC, 1) cell_fwd_tc_kernel(const CellParams 
         rp[0] = v0; rp[1] = v1; rp[2] = v2; rp[3] = v3;
       }
       if (stamp) DLAP_STAMP(i, 15);
+      cur = nxt;
     }
   }
   tc::fence_before_sync();
