@@ -1,8 +1,13 @@
 """The oracle against the reference's own outputs (tests/golden/*.npz, written by
 tests/golden/make_golden.py from /root/reference).  CPU only.
 
-torch_port must reproduce the reference bit for bit (same torch ops, same order);
-closed_form (fp64, hand-derived backward) must agree to fp32 rounding.
+torch_port runs the same torch ops in the same order as the reference, so on the host that wrote
+the fixtures it reproduces them bit for bit.  torch's CPU GEMM/LSTM kernels (oneDNN, MKL) dispatch
+on the host ISA (AVX2, AVX-512, AMX) and sum in a different order on another CPU model, so on any
+other host the comparison is "equal, or within HOST_RTOL of the tensor's largest entry" -- a few
+fp32 ulps, well inside the path's 1e-5 loss tolerance.  Integer/index/mask fixtures and the initial
+parameters stay bit-exact everywhere.  closed_form (fp64, hand-derived backward) must agree to
+fp32 rounding.
 """
 import numpy as np
 import pytest
@@ -13,6 +18,18 @@ from oracle import torch_port as tp
 from _dlap_testlib import load_golden
 
 PHASES = ("unconditional", "moment", "conditional")
+HOST_RTOL = 4e-6          # measured between an AVX2 and an AVX-512/AMX host: <= 1.6e-6
+
+
+def _same(a, b):
+    """Bit-equal, or equal up to the summation order of the host's BLAS kernels (see header)."""
+    a = np.asarray(a); b = np.asarray(b)
+    if a.shape != b.shape or a.dtype != b.dtype:
+        return False
+    if np.array_equal(a, b):
+        return True
+    a = a.astype(np.float64); b = b.astype(np.float64)
+    return bool(np.abs(a - b).max() <= HOST_RTOL * max(np.abs(b).max(), 1e-30))
 
 
 def _inputs(g):
@@ -32,23 +49,27 @@ def test_init_matches_reference(golden):
 
 
 @pytest.mark.parametrize("phase", PHASES)
-def test_torch_port_bit_exact(golden, phase):
+def test_torch_port_matches_reference(golden, phase):
     torch.set_num_threads(1)
     params, macro, x, R, mask, hidden = _inputs(golden)
     keys = tp.MOMENT_KEYS if phase == "moment" else tp.PARAM_KEYS
     out, grads = tp.step(params, macro, x, R, mask, phase=phase, hidden=hidden, grad_keys=keys)
     for key in ("weights", "loss", "loss_unconditional", "loss_conditional", "sharpe",
                 "portfolio_returns"):
-        assert np.array_equal(out[key].numpy(), golden[f"{phase}/{key}"]), key
-    assert np.array_equal(out["hidden"][0].numpy(), golden[f"{phase}/hidden_h"])
-    assert np.array_equal(out["hidden"][1].numpy(), golden[f"{phase}/hidden_c"])
+        assert _same(out[key].numpy(), golden[f"{phase}/{key}"]), key
+    assert _same(out["hidden"][0].numpy(), golden[f"{phase}/hidden_h"])
+    assert _same(out["hidden"][1].numpy(), golden[f"{phase}/hidden_c"])
     seen = 0
     for k in keys:
         gk = f"{phase}/grad/{k}"
         if gk in golden:
             seen += 1
             assert grads[k] is not None, k
-            assert np.array_equal(grads[k].numpy(), golden[gk]), k
+            if k == "sdf_net.output_proj.bias":
+                # identically zero in exact arithmetic (demeaning): both sides hold fp32 noise only
+                assert np.abs(grads[k].numpy()).max() < 1e-6 and np.abs(golden[gk]).max() < 1e-6
+                continue
+            assert _same(grads[k].numpy(), golden[gk]), k
         else:  # phase 1: the moment net receives no gradient at all (src/model.py:524-528)
             assert grads[k] is None, k
     assert seen >= 2
@@ -59,12 +80,12 @@ def test_torch_port_moments_and_normalized(golden):
     params, macro, x, R, mask, hidden = _inputs(golden)
     q = tp.moment_conditions(params, macro, x)
     assert q.shape == golden["moments"].shape and not q.is_contiguous()
-    assert np.array_equal(q.contiguous().numpy(), golden["moments"])
+    assert _same(q.contiguous().numpy(), golden["moments"])
     # evaluate() runs under @torch.no_grad (src/train.py:106); oneDNN's LSTM takes a different
     # code path there and differs from grad mode in the last bit, so mirror it.
     with torch.no_grad():
         wn, _ = tp.normalized_weights(params, macro, x, mask, hidden)
-    assert np.array_equal(wn.numpy(), golden["normalized_weights"])
+    assert _same(wn.numpy(), golden["normalized_weights"])
 
 
 def _rel(a, b):
