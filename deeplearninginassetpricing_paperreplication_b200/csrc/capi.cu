@@ -2,6 +2,7 @@
 // kernel launches only.  No allocation, no synchronisation, no torch types.
 #include "../../include/dlap.h"
 #include "cell_f32.cuh"
+#include <cstdlib>
 
 namespace dlap {
 // launchers implemented next to their kernels
@@ -29,7 +30,7 @@ cudaError_t launch_weights(const float*, const uint8_t*, const float*, const int
                            cudaStream_t);
 cudaError_t launch_macro_fwd_c(const dlap_plan* plan, const float* macro, const dlap_tensors* p, const float* h0,
                                const float* c0, float* save, float* a_t, float* c_t, float* hn, float* cn,
-                               float* xp, cudaStream_t st);
+                               float* xp, int* months_ready, cudaStream_t st);
 cudaError_t launch_macro_bwd_c(const dlap_plan* plan, const float* macro, const dlap_tensors* p, const float* h0,
                                const float* c0, const float* save, const float* dadc, float* dpre, int want_sdf,
                                int want_mom, const dlap_tensors* g, cudaStream_t st);
@@ -154,7 +155,7 @@ static int set_dropout(CellParams& P, float p, uint64_t seed, const uint64_t* se
 
 int dlap_macro_fwd(const dlap_plan* plan, const float* macro, const dlap_tensors* params, const float* h0,
                    const float* c0, float* lstm_save, float* a_t, float* c_t, float* hn, float* cn,
-                   float* xproj_scratch, void* stream) {
+                   float* xproj_scratch, int32_t* months_ready, void* stream) {
   int rc = check_plan(plan);
   if (rc) return rc;
   REQ(params); REQ(a_t); REQ(c_t); REQ(params->b1); REQ(params->bq);
@@ -162,7 +163,8 @@ int dlap_macro_fwd(const dlap_plan* plan, const float* macro, const dlap_tensors
     REQ(macro); REQ(lstm_save); REQ(hn); REQ(cn); REQ(xproj_scratch);
     REQ(params->w_ih); REQ(params->w_hh); REQ(params->b_ih); REQ(params->b_hh); REQ(params->w1); REQ(params->wq);
   }
-  CU(launch_macro_fwd_c(plan, macro, params, h0, c0, lstm_save, a_t, c_t, hn, cn, xproj_scratch,
+  if (reinterpret_cast<uintptr_t>(months_ready) & 3) return DLAP_E_ALIGN;
+  CU(launch_macro_fwd_c(plan, macro, params, h0, c0, lstm_save, a_t, c_t, hn, cn, xproj_scratch, months_ready,
                         (cudaStream_t)stream));
   return DLAP_OK;
 }
@@ -191,10 +193,13 @@ int dlap_panel_pull(const dlap_plan* plan, const float* x_host, const int32_t* i
 int dlap_cell_fwd(const dlap_plan* plan, const float* x, const float* R, const uint8_t* mask, const int32_t* index,
                   const dlap_tensors* params, const float* a_t, const float* c_t, float* u, float* g,
                   double* row_part, int precision, float dropout_p, uint64_t dropout_seed,
-                  const uint64_t* dropout_seed_dev, void* stream) {
+                  const uint64_t* dropout_seed_dev, const int32_t* months_ready, int months_base, void* stream) {
   int rc = check_plan(plan);
   if (rc) return rc;
   REQ(x); REQ(mask); REQ(params); REQ(a_t); REQ(u); REQ(row_part);
+  if (months_ready && precision != DLAP_PREC_BF16X3) return DLAP_E_PRECISION;   // only the tensor-core kernel waits
+  if (months_ready && months_base < 0) return DLAP_E_SHAPE;
+  if (reinterpret_cast<uintptr_t>(months_ready) & 3) return DLAP_E_ALIGN;
   REQ(params->w1); REQ(params->w2); REQ(params->b2); REQ(params->w3); REQ(params->b3);
   if (g) { REQ(c_t); REQ(params->wq); }
   if (reinterpret_cast<uintptr_t>(x) & 3) return DLAP_E_ALIGN;
@@ -208,7 +213,21 @@ int dlap_cell_fwd(const dlap_plan* plan, const float* x, const float* R, const u
     if (plan->dims.F > 46) return DLAP_E_SHAPE;      // the ones column lives at k = 46
     REQ(index);
     P.index = index;
-    CU(launch_cell_fwd_tc(P, plan->grid_cell, (cudaStream_t)stream));
+    P.months_ready = months_ready;
+    P.months_base = months_ready ? months_base : 0;
+    static const int cyc_sh = getenv("DLAP_CYC_SH") ? atoi(getenv("DLAP_CYC_SH")) : 2;
+    P.cyc_sh = cyc_sh;
+    int grid = plan->grid_cell;
+    if (months_ready) {
+      // the producer (dlap_macro_fwd's recurrence CTA) must be able to become resident while this kernel spins:
+      // a per-cell CTA takes a whole SM, so one SM stays free
+      int dev = 0, sms = 0;
+      CU(cudaGetDevice(&dev));
+      CU(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+      if (sms < 2) return DLAP_E_NODEVICE;
+      if (grid > sms - 1) grid = sms - 1;
+    }
+    CU(launch_cell_fwd_tc(P, grid, (cudaStream_t)stream));
     return DLAP_OK;
   }
   CU(launch_cell_fwd_f32(P, plan->grid_cell, (cudaStream_t)stream));

@@ -58,6 +58,11 @@ struct CellParams {
   long long* timeline;       // diagnostics (dlap_debug_timeline): per-tile clock64 stamps of CTA 0, or null
   // valid-cell index (dlap_panel_index); tensor-core kernels only, null = not built
   const int* index;
+  // non-null: a_t / c_t are still being written by a concurrent dlap_macro_fwd; months [0, *months_ready) are
+  // complete (tensor-core forward only); month t of this (possibly month-sharded) panel is month months_base + t there
+  const int* months_ready;
+  int months_base;
+  int cyc_sh;                // log2 of the block size of the block-cyclic tile order used with months_ready
 };
 
 // ---- valid-cell index ----------------------------------------------------------------------
@@ -97,11 +102,20 @@ struct MonthCursor {
     t = lo; first = __ldg(ts + t); next = __ldg(ts + t + 1);
     cnt = __ldg(P.index + idx_off_cnt(P.T) + t);
   }
-  // move forward to `tile` (>= the current one, < total tiles)
+  // move forward to `tile` (>= the current one, < total tiles): the next non-empty month as a rule, a new search
+  // when the tile lies further ahead (block-cyclic tile order, TileMap)
   __device__ __forceinline__ void seek(const CellParams& P, int tile) {
     if (tile < next) return;
     const int* ts = P.index + idx_off_ts();
-    do { ++t; first = next; next = __ldg(ts + t + 1); } while (tile >= next);
+    ++t; first = next; next = __ldg(ts + t + 1);
+    if (tile >= next) {
+      int lo = t + 1, hi = P.T - 1;
+      while (lo < hi) {
+        const int mid = (lo + hi + 1) >> 1;
+        if (__ldg(ts + mid) <= tile) lo = mid; else hi = mid - 1;
+      }
+      t = lo; first = __ldg(ts + t); next = __ldg(ts + t + 1);
+    }
     cnt = __ldg(P.index + idx_off_cnt(P.T) + t);
     // consume the load inside this (warp-uniform, once-a-month) branch: its first consumer would otherwise be an
     // instruction on the per-tile path, whose scoreboard wait then also catches every other load in flight
@@ -110,6 +124,44 @@ struct MonthCursor {
   __device__ __forceinline__ int j0(int tile) const { return (tile - first) * TILE; }
   __device__ __forceinline__ int ncell(int tile) const { return min(TILE, cnt - (tile - first) * TILE); }
 };
+
+// Which tiles a persistent CTA works on, in its own order: local tile i -> tile(i).
+//   contiguous (backward kernel): CTA c owns [c * chunk, (c + 1) * chunk), so a month's sums stay in one CTA;
+//   block-cyclic (forward kernel): blocks of 2^sh tiles dealt round-robin to the CTAs, so that every CTA walks
+//   the months from the first to the last -- the order a concurrent LSTM recurrence delivers a_t in.
+struct TileMap {
+  int base, sh, jump, count;
+  __device__ __forceinline__ int tile(int i) const { return base + i + (i >> sh) * jump; }
+  static __device__ __forceinline__ TileMap contiguous(int ntiles, int cta, int ncta) {
+    const int chunk = (ntiles + ncta - 1) / ncta;
+    const int lo = min(ntiles, cta * chunk);
+    return TileMap{lo, 31, 0, min(ntiles, lo + chunk) - lo};
+  }
+  static __device__ __forceinline__ TileMap cyclic(int ntiles, int cta, int ncta, int sh) {
+    const int B = 1 << sh, nblk = (ntiles + B - 1) >> sh;
+    const int mine = cta < nblk ? (nblk - cta + ncta - 1) / ncta : 0;      // blocks cta, cta + ncta, ...
+    int n = mine << sh;
+    if (mine > 0 && cta + (mine - 1) * ncta == nblk - 1) n -= (nblk << sh) - ntiles;   // the last block may be short
+    return TileMap{cta << sh, sh, (ncta - 1) << sh, n};
+  }
+};
+
+// spin until month t of a concurrently produced a_t / c_t is complete (CellParams::months_ready); `seen` caches
+// the last value read.  A producer that never shows up (it could not be scheduled beside this kernel) turns
+// into a trap after ~4 s instead of a hang.
+__device__ __forceinline__ void wait_month(const int* ready, int t, int& seen) {
+  if (t < seen) return;
+  unsigned long long t0 = 0;
+  for (;;) {
+    asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(seen) : "l"(ready) : "memory");
+    if (t < seen) return;
+    __nanosleep(200);
+    unsigned long long now;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+    if (t0 == 0) t0 = now;
+    else if (now - t0 > 4000000000ull) __trap();
+  }
+}
 
 // Gather of characteristic rows by one warp.  Lane l (< ROWS) knows the stock number of row l of the batch
 // (n_lane; a cell past the end of the tile repeats the tile's last row, so only real, finite panel rows are

@@ -70,9 +70,11 @@ __global__ void __launch_bounds__(NT_TC, 1) cell_fwd_tc_kernel(const CellParams 
   uint64_t* bar = s.bars();
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int ntiles = __ldg(P.index);                       // tiles of valid cells (dlap_panel_index)
-  const int chunk = tc_chunk(ntiles, gridDim.x);           // contiguous tile range per CTA
-  const int tile_lo = min(ntiles, (int)blockIdx.x * chunk);
-  const int my_tiles = min(ntiles, tile_lo + chunk) - tile_lo;
+  // A contiguous tile range per CTA as a rule.  When the LSTM recurrence runs beside this kernel (months_ready),
+  // blocks of four tiles are dealt round-robin instead: every CTA then needs the months in the order they are made.
+  const TileMap tm = P.months_ready ? TileMap::cyclic(ntiles, blockIdx.x, gridDim.x, P.cyc_sh)
+                                    : TileMap::contiguous(ntiles, blockIdx.x, gridDim.x);
+  const int my_tiles = tm.count;
 
   // ---- one-time set-up ----
   for (int sl = 0; sl < NXS; ++sl) fill_w1_images(P, s.w1h(sl), s.w1l(sl), tid, NT_TC);
@@ -149,11 +151,11 @@ __global__ void __launch_bounds__(NT_TC, 1) cell_fwd_tc_kernel(const CellParams 
     const int gw = warp == 0 ? 0 : warp - 1;
     long long* tl = (P.timeline && blockIdx.x == 0 && warp == 4 && lane == 0) ? P.timeline : nullptr;
     if (gather_wide(P))
-      gather_role<BR, NGW, NXS, true, MOM>(P, gw, lane, tile_lo, my_tiles, s.xh(0), s.w1h(0) + (KG1 - 1) * N1 * 16,
+      gather_role<BR, NGW, NXS, true, MOM>(P, gw, lane, tm, s.xh(0), s.w1h(0) + (KG1 - 1) * N1 * 16,
                                          2 * W1_IMG, W1_IMG, bar + F_XOP_FULL,
                                       bar + F_XOP_EMPTY, tl, 0, true);
     else
-      gather_role<BR, NGW, NXS, false, MOM>(P, gw, lane, tile_lo, my_tiles, s.xh(0), s.w1h(0) + (KG1 - 1) * N1 * 16,
+      gather_role<BR, NGW, NXS, false, MOM>(P, gw, lane, tm, s.xh(0), s.w1h(0) + (KG1 - 1) * N1 * 16,
                                           2 * W1_IMG, W1_IMG, bar + F_XOP_FULL,
                                        bar + F_XOP_EMPTY, tl, 0, true);
   } else if (warp >= 8) {
@@ -162,7 +164,7 @@ __global__ void __launch_bounds__(NT_TC, 1) cell_fwd_tc_kernel(const CellParams 
     const uint32_t lane_base = (uint32_t)(q4 * 32) << 16;
     const float b3 = __ldg(P.b3);
     MonthCursor mc;
-    if (e < my_tiles) mc.init(P, tile_lo + e);
+    if (e < my_tiles) mc.init(P, tm.tile(e));
     int n_nxt = -1, t_nxt = 0, pos_nxt = 0;
     auto load_row = [&](int tile) {
       mc.seek(P, tile);
@@ -170,7 +172,7 @@ __global__ void __launch_bounds__(NT_TC, 1) cell_fwd_tc_kernel(const CellParams 
       pos_nxt = mc.j0(tile) + cell;               // position in the month's list: where u, g of this cell go
       n_nxt = (cell < mc.ncell(tile)) ? __ldg(vidx_row(P, mc.t) + pos_nxt) : -1;
     };
-    if (e < my_tiles) load_row(tile_lo + e);
+    if (e < my_tiles) load_row(tm.tile(e));
     // per-tile state that E1 hands to E2 (a group has two tiles in flight: E1 of its next tile runs while layer 2
     // of the current one is on the tensor core)
     struct TileState { size_t pi; float r; uint32_t gi; bool live; double v0, v3; };
@@ -186,7 +188,7 @@ __global__ void __launch_bounds__(NT_TC, 1) cell_fwd_tc_kernel(const CellParams 
       S.gi = (uint32_t)gi;
       S.r = 0.f;
       if (S.live && P.R) S.r = __ldg(P.R + gi);
-      if (i + 2 < my_tiles) load_row(tile_lo + i + 2);
+      if (i + 2 < my_tiles) load_row(tm.tile(i + 2));
       const bool stamp = q4 == 0 && lane == 0;
       mbar_wait(bar + F_D1_FULL + i % NDA, (i / NDA) & 1);
       tc::fence_after_sync();
@@ -230,7 +232,7 @@ __global__ void __launch_bounds__(NT_TC, 1) cell_fwd_tc_kernel(const CellParams 
     TileState cur{}, nxt{};
     if (e < my_tiles) cur = do_e1(e);
     for (int i = e; i < my_tiles; i += 2) {
-      const int tile = tile_lo + i, sl = i & 1, use = i >> 1;
+      const int tile = tm.tile(i), sl = i & 1, use = i >> 1;
       const bool stamp = q4 == 0 && lane == 0;
       const uint32_t dB = tbase + lane_base + (sl ? COL_B1 : COL_B0);
       if (i + 2 < my_tiles) nxt = do_e1(i + 2);      // while layer 2 of tile i runs

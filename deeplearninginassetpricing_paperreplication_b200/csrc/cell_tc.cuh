@@ -63,7 +63,7 @@ __device__ __forceinline__ void rows_to_image(const uint64_t (&r)[ROWS], uint8_t
 }
 
 // ---- gather + convert role (forward and backward kernels) -----------------------------------------------
-// The tiles of a CTA are cut into batches of BR rows; batch q = (tile q / NB, rows BR * (q % NB) ..) goes to
+// The tiles of a CTA (tm: local tile i -> tile) are cut into batches of BR rows; batch q = (local tile q / NB, rows BR * (q % NB) ..) goes to
 // gather warp q % NGW.  A batch is fetched with coalesced loads (gather_load), waits in registers, and is
 // written into the X image of its tile's slot (rows_to_image) once the slot is free; the warp that handles
 // the first batch of a tile also writes the per-month bias column (k = 46) of the slot's W1 image:
@@ -78,27 +78,31 @@ __device__ __forceinline__ void rows_to_image(const uint64_t (&r)[ROWS], uint8_t
 // loads: those rows are prefetched to L2 in the meantime.  The loop starts one step early (q < 0: loads only)
 // so that the row registers have a single definition.
 template <int BR, int NGW, int NSLOT, bool WIDE, bool MOM>
-__device__ __forceinline__ void gather_role(const CellParams& P, int gw, int lane, int tile_lo, int my_tiles,
+__device__ __forceinline__ void gather_role(const CellParams& P, int gw, int lane, const TileMap tm,
                                             uint8_t* x0, uint8_t* g5h0, uint32_t g5_stride, uint32_t g5_lo,
                                             uint64_t* xop_full, uint64_t* xop_empty,
                                             long long* tl /* stamps or null */, int tl_slot, bool tl_per_batch) {
   constexpr int NB = TILE / BR;
-  const int nbatch = my_tiles * NB;
+  const int nbatch = tm.count * NB;
   MonthCursor mc;
-  if (my_tiles > 0) mc.init(P, tile_lo);
+  if (tm.count > 0) mc.init(P, tm.tile(0));
   int t_seek = 0;
   // where lane l's stock number of batch q lives (cells past the end of the tile repeat its last row); moves the
   // month cursor, whose rare loads are consumed right here
   auto n_addr = [&](int q) {
-    const int tile = tile_lo + q / NB, cell = (q % NB) * BR + (lane & (BR - 1));
+    const int tile = tm.tile(q / NB), cell = (q % NB) * BR + (lane & (BR - 1));
     mc.seek(P, tile);
     t_seek = mc.t;
     return vidx_row(P, mc.t) + mc.j0(tile) + min(cell, mc.ncell(tile) - 1);
   };
-  auto load_bias = [&](int t, float (&b)[3]) {       // entries lane, lane + 32, lane + 64 of the bias column
-    b[0] = __ldg(P.a_t + (size_t)t * 64 + lane);
-    b[1] = __ldg(P.a_t + (size_t)t * 64 + 32 + lane);
-    b[2] = (MOM && lane < 8) ? __ldg(P.c_t + (size_t)t * 8 + lane) : 0.f;
+  // entries lane, lane + 32, lane + 64 of the bias column.  The recurrence that produces a_t may still be running
+  // (months_ready): wait for the month, and read past L1 (the lines can change during this kernel).
+  int months_seen = 0;
+  auto load_bias = [&](int t, float (&b)[3]) {
+    if (P.months_ready) wait_month(P.months_ready, P.months_base + t, months_seen);
+    b[0] = __ldcg(P.a_t + (size_t)t * 64 + lane);
+    b[1] = __ldcg(P.a_t + (size_t)t * 64 + 32 + lane);
+    b[2] = (MOM && lane < 8) ? __ldcg(P.c_t + (size_t)t * 8 + lane) : 0.f;
   };
   uint64_t rows[BR];
 #pragma unroll

@@ -1,10 +1,11 @@
 // Macro path: everything that is per MONTH rather than per stock-month.
 //
-//   forward  (one persistent CTA): input projection W_ih.macro_t for all months in parallel,
-//            then the serial LSTM recurrence on one warp (one lane per gate row, h broadcast by
-//            shuffles), then the per-month biases that replace the reference's two
-//            tile-over-N concats:  a_t = W1[:,F:].h_t + b1  (src/model.py:253-255, :211)
-//                                  c_t = Wq[:,:M].macro_t + bq (src/model.py:514-516, :152).
+//   forward: input projection W_ih.macro_t for all months in parallel (multi-CTA), then one persistent CTA:
+//            the serial LSTM recurrence on one warp (one lane per unit, h broadcast by shuffles) and, trailing
+//            it on a second warp, the per-month biases that replace the reference's two tile-over-N concats:
+//                                  a_t = W1[:,F:].h_t + b1  (src/model.py:253-255, :211)
+//                                  c_t = Wq[:,:M].macro_t + bq (src/model.py:514-516, :152, by the projection).
+//            The months are published as they complete, so the per-cell forward kernel can run beside it.
 //            LSTM semantics: torch.nn.LSTM, gates i,f,g,o (src/model.py:39-45, :68).
 //   backward (one persistent CTA): dh_t = W1[:,F:]^T.da_t, BPTT on one warp, then the
 //            month-summed weight gradients (LSTM, W1[:,F:], b1, Wq[:,:M], bq).
@@ -28,11 +29,11 @@ struct MacroParams {
   const float* c0;      // [H] or null
   // forward outputs
   float* save;          // [T, 6H]: h(H) c(H) i f g o (4H), post-activation
-  float* xp;            // [T, 4H] scratch: input projection (shares the dpre buffer)
   float* a_t;           // [T,64]
   float* c_t;           // [T,8]
   float* hn;            // [H]
   float* cn;            // [H]
+  int* months_ready;    // null, or a device counter: months [0, *months_ready) of a_t (and all of c_t) are written
   // backward
   const float* dadc;    // [T,72]  da_t (64) | dc_t (8), summed over stocks
   float* dpre;          // [T,4H] scratch: LSTM pre-activation gradients
@@ -52,67 +53,53 @@ __device__ __forceinline__ float tanh_fast(float v) { return fmaf(2.f, sigmoid_f
 
 constexpr int MT = 512;    // threads of the single-CTA macro kernels
 
-// Input projection for every month (multi-CTA, one warp per month):
-//   xp[t][r] = W_ih[r].macro_t + b_ih[r] + b_hh[r]   and   c_t[t][q] = Wq[q,:M].macro_t + bq[q]
-// dynamic smem: Wih[4H][M] | Wqm[8][M]
-template <int H>
-__global__ void __launch_bounds__(256) macro_proj_kernel(const MacroParams P) {
-  extern __shared__ float sm[];
-  const int T = P.T, M = P.M;
-  constexpr int G4 = 4 * H;
-  float* wih = sm;
-  float* wqm = wih + (size_t)G4 * M;
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  for (int i = tid; i < G4 * M; i += 256) wih[i] = __ldg(P.Wih + i);
-  for (int i = tid; i < KM * M; i += 256) wqm[i] = __ldg(P.Wq + (size_t)(i / M) * P.ldwq + (i % M));
-  __syncthreads();
-  const int t = blockIdx.x * 8 + warp;
-  if (t >= T) return;
-  float acc[G4 + KM];
-#pragma unroll
-  for (int r = 0; r < G4 + KM; ++r) acc[r] = 0.f;
-  const float* row = P.macro + (size_t)t * M;
-  for (int k0 = 0; k0 < M; k0 += 128) {              // four independent loads in flight per lane
-    float v[4];
-#pragma unroll
-    for (int u = 0; u < 4; ++u) v[u] = (k0 + u * 32 + lane < M) ? __ldg(row + k0 + u * 32 + lane) : 0.f;
-#pragma unroll
-    for (int u = 0; u < 4; ++u) {
-      const int k = k0 + u * 32 + lane;
-      if (k < M) {
-#pragma unroll
-        for (int r = 0; r < G4; ++r) acc[r] = fmaf(v[u], wih[r * M + k], acc[r]);
-#pragma unroll
-        for (int q = 0; q < KM; ++q) acc[G4 + q] = fmaf(v[u], wqm[q * M + k], acc[G4 + q]);
-      }
-    }
-  }
-#pragma unroll
-  for (int r = 0; r < G4 + KM; ++r) acc[r] = warp_sum(acc[r]);
-  if (lane == 0) {
-#pragma unroll
-    for (int r = 0; r < G4; ++r) P.xp[(size_t)t * G4 + r] = acc[r] + __ldg(P.bih + r) + __ldg(P.bhh + r);
-#pragma unroll
-    for (int q = 0; q < KM; ++q) P.c_t[(size_t)t * KM + q] = acc[G4 + q] + __ldg(P.bq + q);
-  }
+// Forward: ONE CTA of 16 warps.
+// dynamic smem: Wih[4H][M] | Wqm[8][M] | xp[T][4H] | hs[T][6H] | cts[T][8] | xready[T] | group mbarriers
+//   warps 2,3,5,6,7,9,..,15 (eleven; none shares warp 0's scheduler): input projection, a month per warp and
+//             round:  xp[t][r] = W_ih[r].macro_t + b_ih[r] + b_hh[r]  and  c_t[t][q] = Wq[q,:M].macro_t + bq[q],
+//             both into shared memory, the next month's row of the series already in flight.  The first months
+//             are ready a microsecond after the weights are staged, which is what a per-cell kernel waiting
+//             beside this one needs.  (Tried and slower to the first month: a thread per month with transposed
+//             weights; a separate multi-CTA projection kernel costs a launch and ~10 us before the recurrence
+//             starts, but leaves the recurrence alone on its SM -- 56 us for both against 62 us here.)
+//   warp 0    the recurrence, as soon as its month's projection is there; every month's state (h c i f g o) goes
+//             to shared memory and is announced in groups of PUB months, one mbarrier per group (an arrive costs
+//             the serial chain a few cycles; a fence + flag store costs it a memory barrier every time);
+//   warp 1    follows warp 0: copies the states to `save`, the c_t rows to c_t, and turns h_t into a_t rows
+//             (the only warp that writes global memory month by month).  With months_ready the
+//             progress is published device-wide, so that a per-cell forward kernel launched beside this one
+//             (another stream) can start on the first months while the later ones are still being computed.
+constexpr int PUB = 4;
+constexpr int NPROJ = 11;
+__device__ __forceinline__ void st_release_cta(int* p, int v) {
+  asm volatile("st.release.cta.shared.s32 [%0], %1;" ::"r"((uint32_t)__cvta_generic_to_shared(p)), "r"(v) : "memory");
 }
 
-// The serial part: one CTA.  dynamic smem: xp[T][4H]
 template <int H>
 __global__ void __launch_bounds__(MT, 1) macro_fwd_kernel(const MacroParams P) {
-  extern __shared__ float sm[];
-  const int T = P.T;
+  extern __shared__ __align__(16) float sm[];
+  const int T = P.T, M = P.M;
   constexpr int G4 = 4 * H;
-  float* xp = sm;
-  float* hs = xp + (size_t)T * G4;           // h_t of every month, for the a_t pass
+  float* wih = sm;                           // [4H][M]
+  float* wqm = wih + (size_t)G4 * M;         // [8][M]
+  float* xp = wqm + (size_t)KM * M;          // [T][4H]
+  float* hs = xp + (size_t)T * G4;           // [T][6H] states of every month (the layout of `save`)
+  float* cts = hs + (size_t)T * 6 * H;       // [T][8] c_t rows
+  int* xready = reinterpret_cast<int*>(cts + (size_t)T * KM);     // [T] month's projection is in xp / cts
+  const int ngroup = (T + PUB - 1) / PUB;    // group c = months [PUB c, PUB c + PUB): its states are in hs
+  uint64_t* gbar = reinterpret_cast<uint64_t*>(xready + ((T + 1) & ~1));
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  for (int i = tid; i < T * G4; i += MT) xp[i] = P.xp[i];
+  for (int i = tid; i < ngroup; i += MT) mbar_init(gbar + i, 1);
+  if (tid == 0) fence_mbar_init();
+  for (int i = tid; i < T; i += MT) xready[i] = 0;
+  for (int i = tid; i < G4 * M; i += MT) wih[i] = __ldg(P.Wih + i);
+  for (int i = tid; i < KM * M; i += MT) wqm[i] = __ldg(P.Wq + (size_t)(i / M) * P.ldwq + (i % M));
   __syncthreads();
 
-  // phase 2: the recurrence on warp 0.  Lane j < H owns unit j and evaluates its four gates itself
-  // (four independent FMA chains + four independent activations), so one step costs a single round of
-  // shuffles (broadcast of h) instead of two.  The next step's input projection is fetched early.
   if (warp == 0) {
+    // Lane j < H owns unit j and evaluates its four gates itself (four independent FMA chains + four independent
+    // activations), so one step costs a single round of shuffles (broadcast of h) instead of two.  The next
+    // step's input projection is fetched early.
     const int j = lane < H ? lane : 0;
     float whh[4][H];
 #pragma unroll
@@ -121,10 +108,25 @@ __global__ void __launch_bounds__(MT, 1) macro_fwd_kernel(const MacroParams P) {
       for (int k = 0; k < H; ++k) whh[g][k] = __ldg(P.Whh + (g * H + j) * H + k);
     float h = (lane < H && P.h0) ? __ldg(P.h0 + lane) : 0.f;
     float c = (lane < H && P.c0) ? __ldg(P.c0 + lane) : 0.f;
+    // Months [0, xavail) are known to be projected; the flags are looked at only when the recurrence has caught
+    // up with that, 32 months per look, so a step carries no check it would have to wait for as long as the
+    // projection warps stay ahead.
+    int xavail = 0;
+    auto need = [&](int t) {
+      while (xavail <= t) {
+        const int m = xavail + lane;
+        const int f = (m < T) ? *reinterpret_cast<volatile int*>(xready + m) : 0;
+        const unsigned b = __ballot_sync(0xffffffffu, f != 0);
+        xavail += (b == 0xffffffffu) ? 32 : __ffs(~b) - 1;
+      }
+      __threadfence_block();                     // the flags before the xp reads
+    };
+    need(0);
     float xi = xp[j], xf = xp[H + j], xg = xp[2 * H + j], xo = xp[3 * H + j];
     for (int t = 0; t < T; ++t) {
       float pi = xi, pf = xf, pg = xg, po = xo;
       if (t + 1 < T) {
+        if (t + 1 >= xavail) need(t + 1);
         const float* nx = xp + (t + 1) * G4;
         xi = nx[j]; xf = nx[H + j]; xg = nx[2 * H + j]; xo = nx[3 * H + j];
       }
@@ -138,28 +140,91 @@ __global__ void __launch_bounds__(MT, 1) macro_fwd_kernel(const MacroParams P) {
       c = fmaf(gf, c, gi * gg);
       h = go * tanh_fast(c);
       if (lane < H) {
-        float* sv = P.save + (size_t)t * 6 * H;
-        hs[t * H + lane] = h;
+        float* sv = hs + t * 6 * H;
         sv[lane] = h; sv[H + lane] = c;
         sv[2 * H + lane] = gi; sv[3 * H + lane] = gf; sv[4 * H + lane] = gg; sv[5 * H + lane] = go;
       }
+      if ((t % PUB) == PUB - 1 || t == T - 1) {
+        __syncwarp();                            // the lanes' hs stores before lane 0's arrive (release)
+        if (lane == 0) mbar_arrive(gbar + t / PUB);
+      }
     }
     if (lane < H) { P.hn[lane] = h; P.cn[lane] = c; }
-  }
-  __syncthreads();
-
-  // phase 3: a_t = W1[:,F:F+H].h_t + b1 ; thread = (unit j, month slice), weights in registers
-  {
-    const int j = tid % D1;
-    float w[H];
+  } else if (warp == 1) {
+    // a_t = W1[:,F:F+H].h_t + b1 ; lane = units lane and lane + 32, weights in registers
+    float w[2][H], b[2];
 #pragma unroll
-    for (int k = 0; k < H; ++k) w[k] = __ldg(P.W1 + (size_t)j * P.ldw1 + P.F + k);
-    const float b = __ldg(P.b1 + j);
-    for (int t = tid / D1; t < T; t += MT / D1) {
-      float v = b;
+    for (int e = 0; e < 2; ++e) {
+      const int unit = lane + 32 * e;
 #pragma unroll
-      for (int k = 0; k < H; ++k) v = fmaf(w[k], hs[t * H + k], v);
-      P.a_t[(size_t)t * D1 + j] = v;
+      for (int k = 0; k < H; ++k) w[e][k] = __ldg(P.W1 + (size_t)unit * P.ldw1 + P.F + k);
+      b[e] = __ldg(P.b1 + unit);
+    }
+    for (int c = 0; c < ngroup; ++c) {
+      mbar_wait(gbar + c, 0);
+      const int done = c * PUB, avail = min(T, done + PUB);
+      for (int i = done * 6 * H + lane; i < avail * 6 * H; i += 32) P.save[i] = hs[i];
+      for (int i = done * KM + lane; i < avail * KM; i += 32) P.c_t[i] = cts[i];
+      for (int t = done; t < avail; ++t) {
+        float v0 = b[0], v1 = b[1];
+#pragma unroll
+        for (int k = 0; k < H; ++k) {
+          const float hk = hs[t * 6 * H + k];
+          v0 = fmaf(w[0][k], hk, v0); v1 = fmaf(w[1][k], hk, v1);
+        }
+        P.a_t[(size_t)t * D1 + lane] = v0;
+        P.a_t[(size_t)t * D1 + 32 + lane] = v1;
+      }
+      if (P.months_ready) {
+        __syncwarp();                            // the lanes' a_t stores before lane 0's fence + release
+        if (lane == 0) {
+          __threadfence();
+          asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(P.months_ready), "r"(avail) : "memory");
+        }
+      }
+    }
+  } else if ((warp & 3) != 0) {
+    // input projection, month pw, pw + NPROJ, ... ; lanes stride over the macro series' columns.  The first 256
+    // columns of the NEXT month's row are fetched before this month's products start.
+    const int pw = warp - 2 - (warp >> 2);
+    float pre[8];
+    auto fetch = [&](int t) {
+      const float* row = P.macro + (size_t)min(t, T - 1) * M;
+#pragma unroll
+      for (int u = 0; u < 8; ++u) pre[u] = (u * 32 + lane < M) ? __ldg(row + u * 32 + lane) : 0.f;
+    };
+    fetch(pw);
+    for (int t = pw; t < T; t += NPROJ) {
+      float acc[G4 + KM];
+#pragma unroll
+      for (int r = 0; r < G4 + KM; ++r) acc[r] = 0.f;
+      float cur[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) cur[u] = pre[u];
+      fetch(t + NPROJ);
+      const float* row = P.macro + (size_t)t * M;
+      for (int k0 = 0; k0 < M; k0 += 128) {              // products and sums in the order k = k0 + 32 u + lane
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const int k = k0 + u * 32 + lane;
+          if (k < M) {
+            const float v = (k0 == 0) ? cur[u] : (k0 == 128) ? cur[4 + u] : __ldg(row + k);
+#pragma unroll
+            for (int r = 0; r < G4; ++r) acc[r] = fmaf(v, wih[r * M + k], acc[r]);
+#pragma unroll
+            for (int q = 0; q < KM; ++q) acc[G4 + q] = fmaf(v, wqm[q * M + k], acc[G4 + q]);
+          }
+        }
+      }
+#pragma unroll
+      for (int r = 0; r < G4 + KM; ++r) acc[r] = warp_sum(acc[r]);
+      if (lane == 0) {
+#pragma unroll
+        for (int r = 0; r < G4; ++r) xp[t * G4 + r] = acc[r] + __ldg(P.bih + r) + __ldg(P.bhh + r);
+#pragma unroll
+        for (int q = 0; q < KM; ++q) cts[t * KM + q] = acc[G4 + q] + __ldg(P.bq + q);
+        st_release_cta(xready + t, 1);
+      }
     }
   }
 }
@@ -290,10 +355,19 @@ __global__ void __launch_bounds__(256) macro_wgrad_kernel(const MacroParams P) {
   const int T = P.T, M = P.M, H = P.H, G4 = 4 * H, NR = G4 + KM, CP = NR + 1;
   float* coef = sm;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  for (int i = tid; i < T * NR; i += 256) {
-    const int t = i / NR, r = i % NR;
-    coef[t * CP + r] = (r < G4) ? (P.have_sdf ? P.dpre[(size_t)t * G4 + r] : 0.f)
-                                : (P.have_mom ? __ldg(P.dadc + (size_t)t * 72 + 64 + (r - G4)) : 0.f);
+  for (int i0 = tid; i0 < T * NR; i0 += 4 * 256) {         // four independent loads per thread and round
+    float v[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int i = min(i0 + u * 256, T * NR - 1), t = i / NR, r = i % NR;
+      v[u] = (r < G4) ? (P.have_sdf ? __ldcg(P.dpre + (size_t)t * G4 + r) : 0.f)
+                      : (P.have_mom ? __ldg(P.dadc + (size_t)t * 72 + 64 + (r - G4)) : 0.f);
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int i = i0 + u * 256;
+      if (i < T * NR) coef[(i / NR) * CP + i % NR] = v[u];
+    }
   }
   __syncthreads();
   const int task = blockIdx.x * 8 + warp;
@@ -302,12 +376,20 @@ __global__ void __launch_bounds__(256) macro_wgrad_kernel(const MacroParams P) {
     float acc[4 * HMAX + KM];
 #pragma unroll
     for (int r = 0; r < 4 * HMAX + KM; ++r) acc[r] = 0.f;
-    for (int t = lane; t < T; t += 32) {
-      const float v = __ldg(P.macro + (size_t)t * M + m);
-      const float* c = coef + t * CP;
+    for (int t0 = lane; t0 < T; t0 += 4 * 32) {              // four months' loads in flight per lane
+      float v[4];
 #pragma unroll
-      for (int r = 0; r < 4 * HMAX + KM; ++r)
-        if (r < NR) acc[r] = fmaf(c[r], v, acc[r]);
+      for (int u = 0; u < 4; ++u) v[u] = __ldg(P.macro + (size_t)min(t0 + 32 * u, T - 1) * M + m);
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int t = t0 + 32 * u;
+        if (t < T) {
+          const float* c = coef + t * CP;
+#pragma unroll
+          for (int r = 0; r < 4 * HMAX + KM; ++r)
+            if (r < NR) acc[r] = fmaf(c[r], v[u], acc[r]);
+        }
+      }
     }
 #pragma unroll
     for (int r = 0; r < 4 * HMAX + KM; ++r) {
@@ -376,8 +458,10 @@ __global__ void __launch_bounds__(256) macro_wgrad_kernel(const MacroParams P) {
   }
 }
 
-size_t macro_fwd_smem(int T, int M, int H) { return (size_t)T * 5 * H * 4 + 0 * (size_t)M; }
-size_t macro_proj_smem(int M, int H) { return ((size_t)4 * H * M + (size_t)KM * M) * 4; }
+size_t macro_fwd_smem(int T, int M, int H) {
+  return ((size_t)(4 * H + KM) * M + (size_t)T * 10 * H + (size_t)T * KM + ((T + 1) & ~1)) * 4 +
+         (size_t)((T + PUB - 1) / PUB) * 8;
+}
 size_t macro_bwd_smem(int T, int H) {
   const int rec = 8 + 2 * ((H + 3) & ~3);
   return ((size_t)T * 6 * H + (size_t)T * H * rec + (size_t)D1 * H + (size_t)4 * H * H) * 4;
@@ -385,13 +469,7 @@ size_t macro_bwd_smem(int T, int H) {
 
 template <int H>
 static cudaError_t launch_fwd_h(const MacroParams& P, size_t smem, cudaStream_t st) {
-  const size_t psm = macro_proj_smem(P.M, H);
-  cudaError_t e = cudaFuncSetAttribute(macro_proj_kernel<H>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)psm);
-  if (e != cudaSuccess) return e;
-  macro_proj_kernel<H><<<(P.T + 7) / 8, 256, psm, st>>>(P);
-  e = cudaGetLastError();
-  if (e != cudaSuccess) return e;
-  e = cudaFuncSetAttribute(macro_fwd_kernel<H>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  cudaError_t e = cudaFuncSetAttribute(macro_fwd_kernel<H>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
   macro_fwd_kernel<H><<<1, MT, smem, st>>>(P);
   return cudaGetLastError();
@@ -445,6 +523,7 @@ __global__ void const_bias_kernel(const float* __restrict__ b1, const float* __r
   if (i < T * D1) a_t[i] = __ldg(b1 + (i % D1));
   if (i < T * KM) c_t[i] = __ldg(bq + (i % KM));
 }
+__global__ void set_months_kernel(int* months_ready, int T) { *months_ready = T; }
 
 static void fill_macro(MacroParams& P, const dlap_plan* plan, const float* macro, const dlap_tensors* p,
                        const float* h0, const float* c0) {
@@ -458,15 +537,16 @@ static void fill_macro(MacroParams& P, const dlap_plan* plan, const float* macro
 
 cudaError_t launch_macro_fwd_c(const dlap_plan* plan, const float* macro, const dlap_tensors* p, const float* h0,
                                const float* c0, float* save, float* a_t, float* c_t, float* hn, float* cn,
-                               float* xp, cudaStream_t st) {
+                               float* xp, int* months_ready, cudaStream_t st) {
   if (plan->dims.M == 0) {
     const int n = plan->dims.T * D1;
     const_bias_kernel<<<(n + 255) / 256, 256, 0, st>>>(p->b1, p->bq, plan->dims.T, a_t, c_t);
+    if (months_ready) set_months_kernel<<<1, 1, 0, st>>>(months_ready, plan->dims.T);
     return cudaGetLastError();
   }
   MacroParams P;
   fill_macro(P, plan, macro, p, h0, c0);
-  P.save = save; P.a_t = a_t; P.c_t = c_t; P.hn = hn; P.cn = cn; P.xp = xp;
+  P.save = save; P.a_t = a_t; P.c_t = c_t; P.hn = hn; P.cn = cn; (void)xp; P.months_ready = months_ready;
   return launch_macro_fwd(P, st);
 }
 

@@ -265,8 +265,17 @@ __global__ void __launch_bounds__(256) grad_finish_kernel(
   const int Fr = round4(F), stride = wp_stride(Fr);
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx < stride) {
+    // four running sums (CTAs c = u mod 4, ascending), sixteen loads in flight: the kernel is one L2 round trip
+    // per batch of loads and nothing else
     float v4[4] = {0.f, 0.f, 0.f, 0.f};
     int c = 0;
+    for (; c + 16 <= ncta; c += 16) {
+      float ld[16];
+#pragma unroll
+      for (int u = 0; u < 16; ++u) ld[u] = __ldg(wpart + (size_t)(c + u) * stride + idx);
+#pragma unroll
+      for (int u = 0; u < 16; ++u) v4[u & 3] += ld[u];
+    }
     for (; c + 4 <= ncta; c += 4) {
 #pragma unroll
       for (int u = 0; u < 4; ++u) v4[u] += wpart[(size_t)(c + u) * stride + idx];

@@ -3,6 +3,9 @@
 Forward  : macro_fwd -> [panel_index] -> cell_fwd -> row_finish -> col_partial -> loss_finish
 Backward : loss_coeff -> ds_rows -> cell_bwd -> grad_finish -> macro_bwd
 
+With the tensor-core precision the LSTM recurrence of macro_fwd (serial, one warp) runs on a side stream BESIDE
+cell_fwd, which waits month by month for the per-month biases it needs (``overlap_macro``).
+
 Every stage is a kernel launch through ``libdlap_b200.so`` on torch's current stream; torch is
 used for device memory and streams only.  Nothing here synchronises with the host, so a whole
 training step can be captured in a CUDA graph.
@@ -16,6 +19,7 @@ per-cell weight gradients; every rank then runs the (tiny, serial) LSTM BPTT red
 from __future__ import annotations
 
 import ctypes as C
+import os
 import weakref
 from dataclasses import dataclass
 from typing import Dict, Optional, Tuple
@@ -122,6 +126,8 @@ class Workspace:
         self.dadc_part = f32(p.dadc_part_bytes)
         self.dpre = f32(p.dpre_bytes)
         self.counter = torch.zeros(1, dtype=torch.int32, device=device)
+        self.months_ready = torch.zeros(1, dtype=torch.int32, device=device)   # progress of a concurrent dlap_macro_fwd
+        self.side = torch.cuda.Stream(device)                                   # the stream it runs on
         self.launches = 0          # kernels launched through this workspace (bench bookkeeping)
 
     def panel_index(self, mask: torch.Tensor) -> torch.Tensor:
@@ -254,8 +260,16 @@ def _flat_state(h, H, dev):
     return h
 
 
-def macro_forward(ws: Workspace, macro, params, h0, c0):
-    """dlap_macro_fwd: LSTM states + per-month biases.  `macro` covers all months of the panel."""
+# bf16x3 only: dlap_macro_fwd on a side stream, dlap_cell_fwd beside it (False, or DLAP_OVERLAP_MACRO=0 in the
+# environment: one after the other)
+overlap_macro = os.environ.get("DLAP_OVERLAP_MACRO", "1") != "0"
+
+
+def macro_forward(ws: Workspace, macro, params, h0, c0, concurrent: bool = False):
+    """dlap_macro_fwd: LSTM states + per-month biases.  `macro` covers all months of the panel.
+    concurrent: enqueue it on ws.side behind the work already on the current stream and publish its progress in
+    ws.months_ready; the caller hands that counter to the dlap_cell_fwd it enqueues next on the current stream and
+    then joins ws.side (`join_macro`)."""
     dev = ws.device
     T, H = ws.plan.dims.T, max(ws.plan.dims.H, 1)
     save = torch.empty(T, 6 * H, dtype=torch.float32, device=dev)
@@ -264,10 +278,23 @@ def macro_forward(ws: Workspace, macro, params, h0, c0):
     hn = torch.empty(H, dtype=torch.float32, device=dev)
     cn = torch.empty(H, dtype=torch.float32, device=dev)
     tens = _tensors(params)
-    _timed_call("dlap_macro_fwd", dev, ws.pp, _ptr(macro), C.byref(tens), _ptr(h0), _ptr(c0), _ptr(save),
-              _ptr(a_t), _ptr(c_t), _ptr(hn), _ptr(cn), _ptr(ws.dpre), _stream(dev))
-    ws.launches += 2 if ws.plan.dims.M > 0 else 1
+    if concurrent:
+        main = torch.cuda.current_stream(dev)
+        ws.months_ready.zero_()                    # ordered before both the producer and the consumer
+        ws.side.wait_stream(main)
+        _lib.call("dlap_macro_fwd", ws.pp, _ptr(macro), C.byref(tens), _ptr(h0), _ptr(c0), _ptr(save),
+                  _ptr(a_t), _ptr(c_t), _ptr(hn), _ptr(cn), _ptr(ws.dpre), _ptr(ws.months_ready),
+                  ws.side.cuda_stream)
+    else:
+        _timed_call("dlap_macro_fwd", dev, ws.pp, _ptr(macro), C.byref(tens), _ptr(h0), _ptr(c0), _ptr(save),
+                    _ptr(a_t), _ptr(c_t), _ptr(hn), _ptr(cn), _ptr(ws.dpre), None, _stream(dev))
+    ws.launches += 1
     return save, a_t, c_t, hn, cn
+
+
+def join_macro(ws: Workspace) -> None:
+    """The current stream continues only after the concurrent dlap_macro_fwd on ws.side has finished."""
+    torch.cuda.current_stream(ws.device).wait_stream(ws.side)
 
 
 class GanStepFn(torch.autograd.Function):
@@ -285,19 +312,24 @@ class GanStepFn(torch.autograd.Function):
             st = _stream(dev)
             ws = workspace(T, N, F, M, H, dev)
             tens = _tensors(params)
+            index = ws.panel_index(mask) if opts.precision == "bf16x3" else None
+            beside = overlap_macro and opts.precision == "bf16x3" and M > 0
             if sh is None:
-                save, a_t, c_t, hn, cn = macro_forward(ws, macro, params, h0, c0)
+                wsm, t_base = ws, 0
+                save, a_t, c_t, hn, cn = macro_forward(ws, macro, params, h0, c0, beside)
                 a_loc, c_loc = a_t, c_t
             else:   # LSTM replicated over the full series; this rank uses its slab of a_t / c_t
-                wsm = workspace(sh.T_total, N, F, M, H, dev)
-                save, a_t, c_t, hn, cn = macro_forward(wsm, macro, params, h0, c0)
+                wsm, t_base = workspace(sh.T_total, N, F, M, H, dev), sh.t0
+                save, a_t, c_t, hn, cn = macro_forward(wsm, macro, params, h0, c0, beside)
                 a_loc, c_loc = a_t[sh.t0:sh.t1], c_t[sh.t0:sh.t1]
-            index = ws.panel_index(mask) if opts.precision == "bf16x3" else None
             u = torch.empty(T, N, dtype=torch.float32, device=dev)
             g = torch.empty(KM, T, N, dtype=torch.float32, device=dev) if opts.need_moments else None
             _timed_call("dlap_cell_fwd", dev, ws.pp, _ptr(x), _ptr(R), _ptr(mask), _ptr(index), C.byref(tens), _ptr(a_loc),
                       _ptr(c_loc), _ptr(u), _ptr(g), _ptr(ws.row_part), prec, float(opts.dropout_p),
-                      int(opts.dropout_seed), _ptr(opts.dropout_seed_dev), st)
+                      int(opts.dropout_seed), _ptr(opts.dropout_seed_dev),
+                      _ptr(wsm.months_ready) if beside else None, t_base, st)
+            if beside:
+                join_macro(wsm)
             row_stats = torch.empty(T, RS_W, dtype=torch.float32, device=dev)
             pr = torch.empty(T, dtype=torch.float32, device=dev)
             scalars = torch.empty(SC_W, dtype=torch.float32, device=dev)
@@ -414,11 +446,15 @@ def sdf_weights(macro, x, mask, params, h0=None, c0=None, normalized=False, prec
         st = _stream(dev)
         ws = workspace(T, N, F, M, H, dev)
         tens = _tensors(params)
-        save, a_t, c_t, hn, cn = macro_forward(ws, macro, params, h0, c0)
         index = ws.panel_index(mask) if precision == "bf16x3" else None
+        beside = overlap_macro and precision == "bf16x3" and M > 0
+        save, a_t, c_t, hn, cn = macro_forward(ws, macro, params, h0, c0, beside)
         u = torch.empty(T, N, dtype=torch.float32, device=dev)
         _lib.call("dlap_cell_fwd", ws.pp, _ptr(x), None, _ptr(mask), _ptr(index), C.byref(tens), _ptr(a_t), _ptr(c_t),
-                  _ptr(u), None, _ptr(ws.row_part), _PRECISIONS[precision], 0.0, 0, None, st)
+                  _ptr(u), None, _ptr(ws.row_part), _PRECISIONS[precision], 0.0, 0, None,
+                  _ptr(ws.months_ready) if beside else None, 0, st)
+        if beside:
+            join_macro(ws)
         row_stats = torch.empty(T, RS_W, dtype=torch.float32, device=dev)
         pr = torch.empty(T, dtype=torch.float32, device=dev)
         scalars = torch.empty(SC_W, dtype=torch.float32, device=dev)

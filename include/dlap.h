@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define DLAP_ABI_VERSION 2
+#define DLAP_ABI_VERSION 3
 
 enum {
   DLAP_OK = 0,
@@ -93,12 +93,17 @@ int dlap_make_plan(const dlap_dims* dims, int device, dlap_plan* out);
  * replace the tile-over-N concats: a_t = W1[:,F:].h_t + b1 (src/model.py:253-255, :211) and
  * c_t = Wq[:,:M].macro_t + bq (src/model.py:514-516, :152).  h0/c0 [H] may be NULL (zero state).
  * Outputs: lstm_save [T,6H] (h,c,i,f,g,o), a_t [T,64], c_t [T,8], hn/cn [H].  With M = 0 only
- * a_t = b1 and c_t = bq are produced.  xproj_scratch: [T,4H] floats (plan->dpre_bytes; the same buffer
- * may later serve as dlap_macro_bwd's dpre).  Two launches: a multi-CTA input projection, then the
- * single-CTA recurrence. */
+ * a_t = b1 and c_t = bq are produced.  xproj_scratch: kept for ABI stability ([T,4H] floats until ABI 2;
+ * is not used any more, may be NULL).  One launch of a single CTA: eleven warps project the months'
+ * inputs, one warp runs the recurrence behind them, one turns h_t into a_t rows behind that.
+ * months_ready (device, one int32, may be NULL): progress counter of the recurrence.  The caller zeroes it
+ * on a stream ordered before this call AND before the dlap_cell_fwd that is to consume it; the kernel
+ * then keeps *months_ready = number of leading months whose a_t and c_t rows are written.  It lets
+ * dlap_cell_fwd run beside the recurrence on another stream instead of after it (the reference computes
+ * the whole LSTM first, src/model.py:247-255; the result is the same). */
 int dlap_macro_fwd(const dlap_plan* plan, const float* macro, const dlap_tensors* params,
                    const float* h0, const float* c0, float* lstm_save, float* a_t, float* c_t,
-                   float* hn, float* cn, float* xproj_scratch, void* stream);
+                   float* hn, float* cn, float* xproj_scratch, int32_t* months_ready, void* stream);
 
 /* Valid-cell index of the panel: for every month the ascending list of stocks with mask != 0, cut into
  * tiles of <= 128 cells (layout: csrc/cell_f32.cuh).  The reference runs both nets over every cell and
@@ -130,11 +135,18 @@ int dlap_panel_pull(const dlap_plan* plan, const float* x_host, const int32_t* i
  * graph has to live in device memory.
  * index: dlap_panel_index output, required for BF16X3 (row_part is then per valid-cell tile; u and g are
  * written for unmasked cells only and left-packed: the j-th unmasked stock of month t at [t*N + j]); ignored
- * (may be NULL) for FP32 (dense u, g). */
+ * (may be NULL) for FP32 (dense u, g).
+ * months_ready (may be NULL; BF16X3 only, DLAP_E_PRECISION otherwise): the progress counter handed to a
+ * dlap_macro_fwd that was ENQUEUED BEFORE this call on another stream and may still be running: the kernel
+ * waits for a month's a_t / c_t row before it touches the month's first tile, visits the tiles in an
+ * order that follows the months, and leaves one SM to the recurrence.  a_t and c_t must not be written
+ * by anyone else meanwhile.  months_base: month 0 of this panel is month months_base of the series the
+ * recurrence runs over (a month shard passes its first month and its slab of a_t / c_t; 0 otherwise).
+ * With NULL, a_t and c_t are complete when the kernel starts (stream order) and months_base is ignored. */
 int dlap_cell_fwd(const dlap_plan* plan, const float* x, const float* R, const uint8_t* mask,
                   const int32_t* index, const dlap_tensors* params, const float* a_t, const float* c_t, float* u,
                   float* g, double* row_part, int precision, float dropout_p, uint64_t dropout_seed,
-                  const uint64_t* dropout_seed_dev, void* stream);
+                  const uint64_t* dropout_seed_dev, const int32_t* months_ready, int months_base, void* stream);
 
 /* Per-month statistics: N_t, mu_t (src/model.py:276-278), P_t, portfolio return pr_t and
  * S_t = 1 + pr_t (src/model.py:359-367, :380), Rbar_t; N_bar (src/model.py:360) and the Sharpe

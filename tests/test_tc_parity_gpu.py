@@ -172,3 +172,39 @@ def test_tc_all_masked_panel():
     out["loss"].backward()
     assert float(out["loss"]) == 0.0 and float(out["weights"].abs().max()) == 0.0
     assert all(torch.isfinite(p.grad).all() for p in model.parameters() if p.grad is not None)
+
+
+@pytest.mark.parametrize("T,N", [(240, 60), (240, 700), (64, 6000), (3, 129)])
+def test_tc_recurrence_beside_cell_forward_is_bit_identical(T, N):
+    """functional.overlap_macro: the LSTM recurrence on a side stream, dlap_cell_fwd beside it, waiting month by
+    month and walking the tiles block-cyclically.  Same arithmetic per tile, so every output and gradient must
+    equal the one-after-the-other schedule bit for bit -- whether the cells wait for the LSTM (small N) or the
+    LSTM is far ahead (large N)."""
+    from deeplearninginassetpricing_paperreplication_b200 import functional as Fn
+    macro, x, R, mask = make_panel(T, N, 178, seed=5)
+    d = dev()
+    args = (macro.to(d), x.to(d), R.to(d), mask.to(d))
+    torch.manual_seed(11)
+    model = AssetPricingGAN({"macro_feature_dim": 178, "individual_feature_dim": 46, "dropout": 0.0,
+                             "b200_precision": "bf16x3"}).to(d)
+    res = {}
+    old = Fn.overlap_macro
+    try:
+        for beside in (False, True, True):
+            Fn.overlap_macro = beside
+            model.zero_grad(set_to_none=True)
+            out = model(*args, phase="conditional")
+            out["loss"].backward()
+            wn, _ = model.get_weights(args[0], args[1], args[3], normalized=True)
+            torch.cuda.synchronize()
+            got = {k: out[k].detach().clone() for k in ("loss", "loss_unconditional", "weights", "portfolio_returns",
+                                                        "sharpe")}
+            got["wn"] = wn
+            got.update({"grad/" + k: p.grad.clone() for k, p in model.named_parameters()})
+            if not res:
+                res = got
+            else:
+                for k, v in got.items():
+                    assert torch.equal(v, res[k]), (beside, k)
+    finally:
+        Fn.overlap_macro = old
