@@ -260,7 +260,7 @@ def run_ours(args, rank, world):
         # DMA, the characteristic rows of unmasked stock-months pulled out of pinned host memory by a kernel
         with torch.cuda.stream(copy_stream):
             copy_stream.wait_event(consumed[slot])
-            Fn.upload_panel(*host, device=dev, out=bufs[slot])
+            Fn.upload_panel(*host, device=dev, out=bufs[slot], clear=False)    # cleared by e2e_step
             ready[slot].record(copy_stream)
 
     def e2e_step():
@@ -269,9 +269,14 @@ def run_ours(args, rank, world):
         torch.cuda.current_stream(dev).wait_event(ready[slot])
         upload(slot ^ 1)                                   # next step's panel, overlapped with this step
         out = step(bufs[slot])
+        # the loader's zero-fill of masked rows (src/data_loader.py:61-65) for the panel that will land in this
+        # buffer next: done here, straight after the step, when the GPU has SMs to spare, not in front of the pull
+        bufs[slot][1].zero_()
         consumed[slot].record(torch.cuda.current_stream(dev))
         return out["loss"].item()
 
+    for b in bufs:
+        b[1].zero_()
     for ev in consumed:
         ev.record(torch.cuda.current_stream(dev))
     upload(0)
@@ -308,7 +313,7 @@ def run_ours(args, rank, world):
         "clocks": clocks,
         "e2e": {"value": e2e, "unit": "stock-months/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
                 "ms_per_step": ms2 / k2,
-                "note": "every step: upload_panel(pinned host panel) + fwd + bwd + loss.item(); macro, returns and "
+                "note": "every step: upload_panel(pinned host panel) + fwd + bwd + loss.item() + zero-fill of the consumed buffer; macro, returns and "
                         "mask go by DMA, the characteristic rows of unmasked stock-months (40 %) are read out of "
                         "pinned host memory by dlap_panel_pull, masked rows never cross the bus; the pull of "
                         "panel k+1 runs on 8 SMs beside the step on panel k (the per-cell kernels use the other 140)"},

@@ -2,7 +2,6 @@
 // kernel launches only.  No allocation, no synchronisation, no torch types.
 #include "../../include/dlap.h"
 #include "cell_f32.cuh"
-#include <cstdlib>
 
 namespace dlap {
 // launchers implemented next to their kernels
@@ -15,7 +14,7 @@ size_t smem_bwd_bytes(int F);
 cudaError_t launch_row_finish(const double*, int, int, const int*, int, const float*, float*, float*, float*,
                               cudaStream_t);
 cudaError_t launch_panel_index(const uint8_t* mask, int T, int N, int* index, cudaStream_t st);
-cudaError_t launch_panel_pull(const float* x_host, const int* index, int T, int N, int F, float* x_dev, int sms,
+cudaError_t launch_panel_pull(const float* x_host, const int* index, int T, int N, int F, float* x_dev, int sms, bool clear,
                               cudaStream_t st);
 cudaError_t launch_col_partial(const float*, const float*, const uint8_t*, const float*, const float*, const int*,
                                int, int, int, double*, float*, cudaStream_t);
@@ -179,14 +178,14 @@ int dlap_panel_index(const dlap_plan* plan, const uint8_t* mask, int32_t* index,
 }
 
 int dlap_panel_pull(const dlap_plan* plan, const float* x_host, const int32_t* index, float* x_dev, int ctas,
-                    void* stream) {
+                    int clear, void* stream) {
   int rc = check_plan(plan);
   if (rc) return rc;
   REQ(x_host); REQ(index); REQ(x_dev);
   if ((reinterpret_cast<uintptr_t>(x_host) | reinterpret_cast<uintptr_t>(x_dev)) & 3) return DLAP_E_ALIGN;
   if (ctas < 0) return DLAP_E_SHAPE;
   CU(launch_panel_pull(x_host, index, plan->dims.T, plan->dims.N, plan->dims.F, x_dev,
-                       ctas > 0 ? ctas : plan->grid_cell, (cudaStream_t)stream));
+                       ctas > 0 ? ctas : plan->grid_cell, clear != 0, (cudaStream_t)stream));
   return DLAP_OK;
 }
 
@@ -215,8 +214,8 @@ int dlap_cell_fwd(const dlap_plan* plan, const float* x, const float* R, const u
     P.index = index;
     P.months_ready = months_ready;
     P.months_base = months_ready ? months_base : 0;
-    static const int cyc_sh = getenv("DLAP_CYC_SH") ? atoi(getenv("DLAP_CYC_SH")) : 2;
-    P.cyc_sh = cyc_sh;
+    P.cyc_sh = 2;      // blocks of four tiles: measured best of 1, 2, 4, 8 (smaller: more month changes per CTA;
+                       // larger: the last CTAs wait longer for their first month, and the blocks balance worse)
     int grid = plan->grid_cell;
     if (months_ready) {
       // the producer (dlap_macro_fwd's recurrence CTA) must be able to become resident while this kernel spins:

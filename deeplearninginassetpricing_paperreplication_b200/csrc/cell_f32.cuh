@@ -72,7 +72,8 @@ struct CellParams {
 // each list into tiles of <= 128 cells; the tensor-core kernels walk those tiles only.
 //   int32 index[]:  [0] total tiles | [4, 4+T] tile_start (exclusive prefix, [T] = total) | cnt [T] |
 //                   vidx [T, N] (16-B aligned): row t holds cnt[t] stock numbers, rest undefined |
-//                   rank [T, ceil(N/32)]: unmasked stocks of month t before stock 32 w
+//                   rank [T, ceil(N/32)]: unmasked stocks of month t before stock 32 w |
+//                   tmonth [total tiles <= T ceil(N/128)]: month of every tile
 // Per-cell intermediates of the tensor-core path (u, g) are stored "left-packed": the value of the j-th listed
 // stock of month t sits at [t*N + j].  A per-month consumer reads a contiguous run; a per-stock consumer finds
 // its position as rank[t][i / 32] + popc(ballot(mask) below its lane).
@@ -80,8 +81,11 @@ __host__ __device__ inline int idx_off_ts() { return 4; }
 __host__ __device__ inline int idx_off_cnt(int T) { return 4 + T + 1; }
 __host__ __device__ inline long long idx_off_vidx(int T) { return (4 + 2 * T + 1 + 3) & ~3; }
 __host__ __device__ inline long long idx_off_rank(int T, int N) { return idx_off_vidx(T) + (long long)T * N; }
+__host__ __device__ inline long long idx_off_tmonth(int T, int N) {
+  return (idx_off_rank(T, N) + (long long)T * ((N + 31) / 32) + 3) & ~3ll;
+}
 __host__ __device__ inline long long idx_ints(int T, int N) {
-  return idx_off_rank(T, N) + (long long)T * ((N + 31) / 32);
+  return idx_off_tmonth(T, N) + (((long long)T * ((N + TILE - 1) / TILE) + 3) & ~3ll);
 }
 
 __device__ __forceinline__ const int* vidx_row(const CellParams& P, int t) {
@@ -94,27 +98,19 @@ struct MonthCursor {
   // first use: `tile` < total tiles
   __device__ __forceinline__ void init(const CellParams& P, int tile) {
     const int* ts = P.index + idx_off_ts();
-    int lo = 0, hi = P.T - 1;                    // largest t with ts[t] <= tile (lands on a non-empty month)
-    while (lo < hi) {
-      const int mid = (lo + hi + 1) >> 1;
-      if (__ldg(ts + mid) <= tile) lo = mid; else hi = mid - 1;
-    }
-    t = lo; first = __ldg(ts + t); next = __ldg(ts + t + 1);
+    t = __ldg(P.index + idx_off_tmonth(P.T, P.N) + tile);
+    first = __ldg(ts + t); next = __ldg(ts + t + 1);
     cnt = __ldg(P.index + idx_off_cnt(P.T) + t);
   }
-  // move forward to `tile` (>= the current one, < total tiles): the next non-empty month as a rule, a new search
-  // when the tile lies further ahead (block-cyclic tile order, TileMap)
+  // move forward to `tile` (>= the current one, < total tiles): the next month as a rule, a table look-up when
+  // the tile lies further ahead (empty months; block-cyclic tile order, TileMap)
   __device__ __forceinline__ void seek(const CellParams& P, int tile) {
     if (tile < next) return;
     const int* ts = P.index + idx_off_ts();
     ++t; first = next; next = __ldg(ts + t + 1);
     if (tile >= next) {
-      int lo = t + 1, hi = P.T - 1;
-      while (lo < hi) {
-        const int mid = (lo + hi + 1) >> 1;
-        if (__ldg(ts + mid) <= tile) lo = mid; else hi = mid - 1;
-      }
-      t = lo; first = __ldg(ts + t); next = __ldg(ts + t + 1);
+      t = __ldg(P.index + idx_off_tmonth(P.T, P.N) + tile);
+      first = __ldg(ts + t); next = __ldg(ts + t + 1);
     }
     cnt = __ldg(P.index + idx_off_cnt(P.T) + t);
     // consume the load inside this (warp-uniform, once-a-month) branch: its first consumer would otherwise be an

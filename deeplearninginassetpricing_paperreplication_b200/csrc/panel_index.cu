@@ -36,8 +36,8 @@ __global__ void __launch_bounds__(1024) index_rows_kernel(const uint8_t* __restr
   if (tid == 0) cnt[t] = base;
 }
 
-// One CTA: exclusive prefix of the per-month tile counts.
-__global__ void __launch_bounds__(1024) index_tiles_kernel(int T, int* __restrict__ index) {
+// One CTA: exclusive prefix of the per-month tile counts, and the month of every tile.
+__global__ void __launch_bounds__(1024) index_tiles_kernel(int T, int* __restrict__ index, int* __restrict__ tmonth) {
   __shared__ int red[32];
   int* ts = index + idx_off_ts();
   const int* cnt = index + idx_off_cnt(T);
@@ -66,7 +66,10 @@ __global__ void __launch_bounds__(1024) index_tiles_kernel(int T, int* __restric
     }
     __syncthreads();
     const int first = carry + (warp ? red[warp - 1] : 0) + v - nt;
-    if (t < T) ts[t] = first;
+    if (t < T) {
+      ts[t] = first;
+      for (int k = 0; k < nt; ++k) tmonth[first + k] = t;
+    }
     carry += red[31];
     __syncthreads();
   }
@@ -88,12 +91,7 @@ __global__ void __launch_bounds__(256) panel_pull_kernel(const float* __restrict
   const int* cnt = index + idx_off_cnt(T);
   const int* vidx = index + idx_off_vidx(T);
   for (int tile = warp; tile < ntiles; tile += nwarp) {
-    int lo = 0, hi = T - 1;                        // month of the tile: largest t with ts[t] <= tile
-    while (lo < hi) {
-      const int mid = (lo + hi + 1) >> 1;
-      if (ts[mid] <= tile) lo = mid; else hi = mid - 1;
-    }
-    const int t = lo, j0 = (tile - ts[t]) * TILE, ncell = min(TILE, cnt[t] - j0);
+    const int t = index[idx_off_tmonth(T, N) + tile], j0 = (tile - ts[t]) * TILE, ncell = min(TILE, cnt[t] - j0);
     const size_t month = (size_t)t * N * F;
     for (int b = 0; b < ncell; b += 16) {
       const int rows = min(16, ncell - b);
@@ -122,9 +120,11 @@ __global__ void __launch_bounds__(256) panel_pull_kernel(const float* __restrict
 }
 
 cudaError_t launch_panel_pull(const float* x_host, const int* index, int T, int N, int F, float* x_dev, int sms,
-                              cudaStream_t st) {
-  cudaError_t e = cudaMemsetAsync(x_dev, 0, (size_t)T * N * F * 4, st);    // masked rows are delivered as zeros
-  if (e != cudaSuccess) return e;
+                              bool clear, cudaStream_t st) {
+  if (clear) {                                                             // masked rows are delivered as zeros
+    cudaError_t e = cudaMemsetAsync(x_dev, 0, (size_t)T * N * F * 4, st);
+    if (e != cudaSuccess) return e;
+  }
   const bool wide = (F % 2 == 0) && ((reinterpret_cast<uintptr_t>(x_host) | reinterpret_cast<uintptr_t>(x_dev)) & 7) == 0;
   if (wide) panel_pull_kernel<true><<<sms, 256, 0, st>>>(x_host, index, T, N, F, x_dev);
   else panel_pull_kernel<false><<<sms, 256, 0, st>>>(x_host, index, T, N, F, x_dev);
@@ -134,7 +134,7 @@ cudaError_t launch_panel_pull(const float* x_host, const int* index, int T, int 
 cudaError_t launch_panel_index(const uint8_t* mask, int T, int N, int* index, cudaStream_t st) {
   index_rows_kernel<<<T, 1024, 0, st>>>(mask, N, index + idx_off_cnt(T), index + idx_off_vidx(T),
                                         index + idx_off_rank(T, N));
-  index_tiles_kernel<<<1, 1024, 0, st>>>(T, index);
+  index_tiles_kernel<<<1, 1024, 0, st>>>(T, index, index + idx_off_tmonth(T, N));
   return cudaGetLastError();
 }
 

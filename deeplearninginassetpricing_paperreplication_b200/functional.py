@@ -203,12 +203,14 @@ def make_month_shard(mask_local: torch.Tensor, t0: int, T_total: int, group=None
                       n_bar=n_bar)
 
 
-def upload_panel(macro, x, R, mask, device, out=None):
+def upload_panel(macro, x, R, mask, device, out=None, clear=True):
     """`batch = {k: v.to(device) ...}` of src/train.py:69-75 for one panel: (macro, x, R, mask) on `device`,
     enqueued on the current stream.  When x sits in pinned host memory only the rows of unmasked stock-months
     cross the bus (dlap_panel_pull: the kernel reads them straight out of host memory; masked rows arrive as
     zeros, which is what the loader stores there anyway); otherwise x is copied whole.  `out`: device tensors
-    to fill instead of allocating (a training loop that double-buffers its panels)."""
+    to fill instead of allocating (a training loop that double-buffers its panels).  clear=False: the caller has
+    already zeroed out[1] (e.g. right after the step that used it, when the GPU has SMs to spare) or does not need
+    zeros in the masked rows; the pull then starts without a memset of the whole panel in front of it."""
     device = torch.device(device)
     host = (macro, x, R, mask)
     if out is None:
@@ -225,7 +227,7 @@ def upload_panel(macro, x, R, mask, device, out=None):
             ws = workspace(T, N, F, 0, 0, device)
             index = panel_index(ws, d_mask)
             _lib.call("dlap_panel_pull", ws.pp, x.data_ptr(), _ptr(index), _ptr(d_x), int(reserve_sms),
-                      _stream(device))
+                      1 if clear else 0, _stream(device))
             ws.launches += 1
         else:
             d_x.copy_(x, non_blocking=True)
@@ -313,7 +315,9 @@ class GanStepFn(torch.autograd.Function):
             ws = workspace(T, N, F, M, H, dev)
             tens = _tensors(params)
             index = ws.panel_index(mask) if opts.precision == "bf16x3" else None
-            beside = overlap_macro and opts.precision == "bf16x3" and M > 0
+            # not while SMs are set aside for a concurrent panel pull: measured slower there (the recurrence's CTA
+            # ends up beside a pull CTA, and the step is bound by the bus anyway)
+            beside = overlap_macro and opts.precision == "bf16x3" and M > 0 and ws.reserve == 0
             if sh is None:
                 wsm, t_base = ws, 0
                 save, a_t, c_t, hn, cn = macro_forward(ws, macro, params, h0, c0, beside)
@@ -447,7 +451,7 @@ def sdf_weights(macro, x, mask, params, h0=None, c0=None, normalized=False, prec
         ws = workspace(T, N, F, M, H, dev)
         tens = _tensors(params)
         index = ws.panel_index(mask) if precision == "bf16x3" else None
-        beside = overlap_macro and precision == "bf16x3" and M > 0
+        beside = overlap_macro and precision == "bf16x3" and M > 0 and ws.reserve == 0
         save, a_t, c_t, hn, cn = macro_forward(ws, macro, params, h0, c0, beside)
         u = torch.empty(T, N, dtype=torch.float32, device=dev)
         _lib.call("dlap_cell_fwd", ws.pp, _ptr(x), None, _ptr(mask), _ptr(index), C.byref(tens), _ptr(a_t), _ptr(c_t),

@@ -119,9 +119,11 @@ int dlap_panel_index(const dlap_plan* plan, const uint8_t* mask, int32_t* index,
  * stock-months (index: dlap_panel_index of the mask, already on the device) are read over the bus by the
  * kernel itself; masked rows are not transferred and arrive as zeros (the loader zero-fills them anyway,
  * src/data_loader.py:61-65).  One memset + one launch of `ctas` CTAs of 256 threads (0: plan->grid_cell; a
- * handful saturates PCIe).  To overlap the pull of the next panel with a step, lower plan->grid_cell of the
+ * handful saturates PCIe).  clear = 0 skips the memset: the caller has zeroed x_dev itself (a loader that
+ * double-buffers its panels clears a buffer as soon as its step is done, while the GPU has SMs to spare,
+ * instead of in front of the pull), or does not care what the masked rows hold.  To overlap the pull of the next panel with a step, lower plan->grid_cell of the
  * plan the per-cell kernels run with by the same number: they take one CTA per SM and all of its registers. */
-int dlap_panel_pull(const dlap_plan* plan, const float* x_host, const int32_t* index, float* x_dev, int ctas,
+int dlap_panel_pull(const dlap_plan* plan, const float* x_host, const int32_t* index, float* x_dev, int ctas, int clear,
                     void* stream);
 
 /* SDFNetwork.forward body on every stock-month (src/model.py:251-271) and MomentNetwork.forward

@@ -167,6 +167,9 @@ def test_panel_index_bit_exact(shape, density):
     rank = idx[off_rank:off_rank + T * nw].reshape(T, nw)
     before = np.concatenate([np.zeros((T, 1), dtype=np.int64), np.cumsum(mask, axis=1)], axis=1)[:, 0:N:32]
     assert np.array_equal(rank, before)
+    off_tm = (off_rank + T * nw + 3) & ~3                # month of every tile
+    assert np.array_equal(idx[off_tm:off_tm + ts[-1]], np.repeat(np.arange(T), tiles))
+    assert idx.size >= off_tm + T * ((N + 127) // 128)
 
 
 def test_forward_stages_tensor_core_visits_only_unmasked_cells():
