@@ -55,7 +55,7 @@ constexpr int MT = 512;    // threads of the single-CTA macro kernels
 
 // Forward: ONE CTA of 16 warps.
 // dynamic smem: Wih[4H][M] | Wqm[8][M] | xp[T][4H] | hs[T][6H] | cts[T][8] | xready[T] | group mbarriers
-//   warps 2,3,5,6,7,9,..,15 (eleven; none shares warp 0's scheduler): input projection, a month per warp and
+//   warps 2,3,5,6,7,9,..,15 (eleven; none shares warp 0's scheduler): input projection, two months per warp and
 //             round:  xp[t][r] = W_ih[r].macro_t + b_ih[r] + b_hh[r]  and  c_t[t][q] = Wq[q,:M].macro_t + bq[q],
 //             both into shared memory, the next month's row of the series already in flight.  The first months
 //             are ready a microsecond after the weights are staged, which is what a per-cell kernel waiting
@@ -184,45 +184,66 @@ __global__ void __launch_bounds__(MT, 1) macro_fwd_kernel(const MacroParams P) {
       }
     }
   } else if ((warp & 3) != 0) {
-    // input projection, month pw, pw + NPROJ, ... ; lanes stride over the macro series' columns.  The first 256
-    // columns of the NEXT month's row are fetched before this month's products start.
+    // input projection, months in pairs (2 pp, 2 pp + 1), pp = pw, pw + NPROJ, ... ; lanes stride over the macro
+    // series' columns.  Two months per pass: every weight read from shared memory feeds two FMAs (one month per
+    // pass kept the SM's shared-memory pipe busy for the first half of the kernel, and the recurrence warp's own
+    // loads and stores queued behind it).  The first 256 columns of the NEXT pair's rows are fetched before this
+    // pair's products start.
     const int pw = warp - 2 - (warp >> 2);
-    float pre[8];
-    auto fetch = [&](int t) {
-      const float* row = P.macro + (size_t)min(t, T - 1) * M;
+    float pre[2][8];
+    auto fetch = [&](int t0) {
 #pragma unroll
-      for (int u = 0; u < 8; ++u) pre[u] = (u * 32 + lane < M) ? __ldg(row + u * 32 + lane) : 0.f;
+      for (int e = 0; e < 2; ++e) {
+        const float* row = P.macro + (size_t)min(t0 + e, T - 1) * M;
+#pragma unroll
+        for (int u = 0; u < 8; ++u) pre[e][u] = (u * 32 + lane < M) ? __ldg(row + u * 32 + lane) : 0.f;
+      }
     };
-    fetch(pw);
-    for (int t = pw; t < T; t += NPROJ) {
-      float acc[G4 + KM];
+    fetch(2 * pw);
+    for (int t0 = 2 * pw; t0 < T; t0 += 2 * NPROJ) {
+      float acc[2][G4 + KM];
 #pragma unroll
-      for (int r = 0; r < G4 + KM; ++r) acc[r] = 0.f;
-      float cur[8];
+      for (int e = 0; e < 2; ++e)
 #pragma unroll
-      for (int u = 0; u < 8; ++u) cur[u] = pre[u];
-      fetch(t + NPROJ);
-      const float* row = P.macro + (size_t)t * M;
+        for (int r = 0; r < G4 + KM; ++r) acc[e][r] = 0.f;
+      float cur[2][8];
+#pragma unroll
+      for (int e = 0; e < 2; ++e)
+#pragma unroll
+        for (int u = 0; u < 8; ++u) cur[e][u] = pre[e][u];
+      fetch(t0 + 2 * NPROJ);
+      const float* row0 = P.macro + (size_t)t0 * M;
+      const float* row1 = P.macro + (size_t)min(t0 + 1, T - 1) * M;
       for (int k0 = 0; k0 < M; k0 += 128) {              // products and sums in the order k = k0 + 32 u + lane
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
           const int k = k0 + u * 32 + lane;
           if (k < M) {
-            const float v = (k0 == 0) ? cur[u] : (k0 == 128) ? cur[4 + u] : __ldg(row + k);
+            const float v0 = (k0 == 0) ? cur[0][u] : (k0 == 128) ? cur[0][4 + u] : __ldg(row0 + k);
+            const float v1 = (k0 == 0) ? cur[1][u] : (k0 == 128) ? cur[1][4 + u] : __ldg(row1 + k);
 #pragma unroll
-            for (int r = 0; r < G4; ++r) acc[r] = fmaf(v, wih[r * M + k], acc[r]);
+            for (int r = 0; r < G4; ++r) {
+              const float w = wih[r * M + k];
+              acc[0][r] = fmaf(v0, w, acc[0][r]); acc[1][r] = fmaf(v1, w, acc[1][r]);
+            }
 #pragma unroll
-            for (int q = 0; q < KM; ++q) acc[G4 + q] = fmaf(v, wqm[q * M + k], acc[G4 + q]);
+            for (int q = 0; q < KM; ++q) {
+              const float w = wqm[q * M + k];
+              acc[0][G4 + q] = fmaf(v0, w, acc[0][G4 + q]); acc[1][G4 + q] = fmaf(v1, w, acc[1][G4 + q]);
+            }
           }
         }
       }
 #pragma unroll
-      for (int r = 0; r < G4 + KM; ++r) acc[r] = warp_sum(acc[r]);
-      if (lane == 0) {
+      for (int e = 0; e < 2; ++e)
 #pragma unroll
-        for (int r = 0; r < G4; ++r) xp[t * G4 + r] = acc[r] + __ldg(P.bih + r) + __ldg(P.bhh + r);
+        for (int r = 0; r < G4 + KM; ++r) acc[e][r] = warp_sum(acc[e][r]);
+      if (lane < 2 && t0 + lane < T) {                   // lane e finishes month t0 + e
+        const int t = t0 + lane;
 #pragma unroll
-        for (int q = 0; q < KM; ++q) cts[t * KM + q] = acc[G4 + q] + __ldg(P.bq + q);
+        for (int r = 0; r < G4; ++r) xp[t * G4 + r] = (lane ? acc[1][r] : acc[0][r]) + __ldg(P.bih + r) + __ldg(P.bhh + r);
+#pragma unroll
+        for (int q = 0; q < KM; ++q) cts[t * KM + q] = (lane ? acc[1][G4 + q] : acc[0][G4 + q]) + __ldg(P.bq + q);
         st_release_cta(xready + t, 1);
       }
     }
