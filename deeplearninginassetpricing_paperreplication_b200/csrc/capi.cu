@@ -106,9 +106,11 @@ int dlap_make_plan(const dlap_dims* dims, int device, dlap_plan* out) {
   p.tpm = (N + TILE - 1) / TILE;
   const long long ntiles = (long long)T * p.tpm;
   p.grid_cell = (int)(ntiles < sms ? ntiles : sms);
-  // reductions: aim for ~4 CTAs per SM
+  // reductions: aim for ~4 CTAs per SM.  col_partial holds exactly four CTAs of 256 threads per SM (64 registers),
+  // so its grid must not exceed 4 * sms: a few CTAs more would run as a second wave on an otherwise idle GPU and
+  // double the kernel (round down, not up)
   const int nb = (N + 255) / 256, want = 4 * sms;
-  int cs = (want + nb - 1) / nb; if (cs > T) cs = T; if (cs < 1) cs = 1;
+  int cs = want / nb; if (cs > T) cs = T; if (cs < 1) cs = 1;
   p.col_splits = cs;
   int rs = (want + T - 1) / T; if (rs > nb) rs = nb; if (rs < 1) rs = 1;
   p.row_splits = rs;

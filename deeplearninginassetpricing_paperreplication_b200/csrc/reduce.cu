@@ -83,7 +83,7 @@ __global__ void __launch_bounds__(1024) row_finish_kernel(
 // per stock i over the months of one T-chunk:  sum_t g_k S_t (k<8), sum_t R m S_t, sum_t m
 // (src/model.py:376,382,428) and, fused, w = m (u - mu_t) (src/model.py:271-279).
 // `index` != null: u and g are left-packed (tensor-core kernels, cell_f32.cuh), else dense [T,N].
-__global__ void __launch_bounds__(256) col_partial_kernel(
+__global__ void __launch_bounds__(256, 4) col_partial_kernel(
     const float* __restrict__ g, const float* __restrict__ R, const uint8_t* __restrict__ mask,
     const float* __restrict__ u, const float* __restrict__ row_stats, const int* __restrict__ index, int T, int N,
     int tchunk, double* __restrict__ col_part, float* __restrict__ w_out) {
