@@ -402,12 +402,14 @@ class GanStepFn(torch.autograd.Function):
                       int(opts.weighted_loss), int(want_sdf), int(want_mom), _ptr(ws.wpart),
                       _ptr(ws.dadc_part), prec, float(opts.dropout_p), int(opts.dropout_seed),
                       _ptr(opts.dropout_seed_dev), st)
-            # one zero fill for all twelve gradient tensors (views of one flat buffer); month-sharded: the same
-            # buffer starts with the [T_total,72] da_t | dc_t rows (this rank fills its slab), so that exchange 2
-            # is ONE all-reduce over it -- gradients that are computed later (LSTM, b1, bq) are still zero
+            # All twelve gradient tensors are views of one flat buffer.  Month-sharded: the buffer starts with the
+            # [T_total,72] da_t | dc_t rows (this rank fills its slab) and is zero-filled, so that exchange 2 is ONE
+            # all-reduce over it -- gradients that are computed later (LSTM, b1, bq) are still zero.  Otherwise no
+            # fill: dlap_grad_finish and dlap_macro_bwd write every element of every gradient that is handed back
+            # (a fill is one more kernel in a chain of short dependent ones).
             sizes = [0 if p is None else p.numel() for p in params]
             head = 0 if sh is None else sh.T_total * 72
-            buf = torch.zeros(head + sum(sizes), dtype=torch.float32, device=dev)
+            buf = (torch.empty if sh is None else torch.zeros)(head + sum(sizes), dtype=torch.float32, device=dev)
             flat_g = buf[head:]
             grads, off = [], 0
             for p, n in zip(params, sizes):

@@ -320,6 +320,7 @@ class GraphedStep:
                  hidden=None, phase: str = 'conditional', warmup: int = 3):
         self.model, self.args = model, (macro_features, individual_features, returns, mask)
         self.seed = None
+        self._one = None
         if model.training and model.sdf_net.dropout_p > 0:
             s0 = int(torch.randint(0, 2 ** 62, (1,)).item())
             if model.month_shard is not None:             # the same masks on every rank
@@ -358,7 +359,9 @@ class GraphedStep:
             if self.seed is not None:
                 self.seed.add_(0x9E3779B97F4A7C15 >> 2)      # next mask; part of the captured graph
             out = self.model(*self.args, **self.kw)
-            out['loss'].backward()
+            if self._one is None:                       # root gradient: made once, not filled on every replay
+                self._one = torch.ones_like(out['loss'])
+            out['loss'].backward(gradient=self._one)
         finally:
             self.model._seed_dev = None
         return out
