@@ -186,7 +186,8 @@ def run_ours(args, rank, world):
     host = [t.pin_memory() for t in (macro_all, x, R, mask)]
     d_macro, d_x, d_R, d_mask = [t.to(dev) for t in host]
     if world > 1:
-        model.month_shard = Fn.make_month_shard(d_mask, rank * T, T_total, dist.group.WORLD)
+        # months dealt round-robin: rank r owns months r, r + world, ... and follows the LSTM recurrence from month 0
+        model.month_shard = Fn.make_month_shard(d_mask, rank, T_total, dist.group.WORLD, stride=world)
 
     def step(inputs):
         model.zero_grad(set_to_none=True)

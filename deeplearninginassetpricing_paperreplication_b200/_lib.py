@@ -56,7 +56,7 @@ SIGNATURES = {
     "dlap_macro_fwd": (_PLAN, _P, _TENS, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P),
     "dlap_panel_index": (_PLAN, _P, _P, _P),
     "dlap_panel_pull": (_PLAN, _P, _P, _P, _I, _I, _P),
-    "dlap_cell_fwd": (_PLAN, _P, _P, _P, _P, _TENS, _P, _P, _P, _P, _P, _I, C.c_float, C.c_uint64, _P, _P, _I, _P),
+    "dlap_cell_fwd": (_PLAN, _P, _P, _P, _P, _TENS, _P, _P, _P, _P, _P, _I, C.c_float, C.c_uint64, _P, _P, _I, _I, _P),
     "dlap_row_finish": (_PLAN, _P, _P, _I, _I, _P, _P, _P, _P, _P),
     "dlap_col_partial": (_PLAN, _P, _P, _P, _P, _P, _P, _P, _P, _P),
     "dlap_loss_finish": (_PLAN, _P, _I, _P, _P, _P, _P, _P, _P),

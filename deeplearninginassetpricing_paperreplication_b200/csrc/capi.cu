@@ -139,6 +139,7 @@ static void fill_cell(CellParams& P, const dlap_plan* plan, const float* x, cons
   P.W1 = w->w1; P.ldw1 = plan->ldw1; P.W2 = w->w2; P.b2 = w->b2; P.W3 = w->w3; P.b3 = w->b3;
   P.Wq = w->wq; P.ldwq = plan->ldwq; P.wq_off = d.M;
   P.a_t = a_t; P.c_t = c_t;
+  P.months_stride = 1;
   P.tpm = plan->tpm;
 }
 
@@ -194,12 +195,15 @@ int dlap_panel_pull(const dlap_plan* plan, const float* x_host, const int32_t* i
 int dlap_cell_fwd(const dlap_plan* plan, const float* x, const float* R, const uint8_t* mask, const int32_t* index,
                   const dlap_tensors* params, const float* a_t, const float* c_t, float* u, float* g,
                   double* row_part, int precision, float dropout_p, uint64_t dropout_seed,
-                  const uint64_t* dropout_seed_dev, const int32_t* months_ready, int months_base, void* stream) {
+                  const uint64_t* dropout_seed_dev, const int32_t* months_ready, int months_base, int months_stride,
+                  void* stream) {
   int rc = check_plan(plan);
   if (rc) return rc;
   REQ(x); REQ(mask); REQ(params); REQ(a_t); REQ(u); REQ(row_part);
   if (months_ready && precision != DLAP_PREC_BF16X3) return DLAP_E_PRECISION;   // only the tensor-core kernel waits
   if (months_ready && months_base < 0) return DLAP_E_SHAPE;
+  if (months_stride < 1) return DLAP_E_SHAPE;
+  if (months_stride != 1 && precision != DLAP_PREC_BF16X3) return DLAP_E_PRECISION;
   if (reinterpret_cast<uintptr_t>(months_ready) & 3) return DLAP_E_ALIGN;
   REQ(params->w1); REQ(params->w2); REQ(params->b2); REQ(params->w3); REQ(params->b3);
   if (g) { REQ(c_t); REQ(params->wq); }
@@ -216,6 +220,7 @@ int dlap_cell_fwd(const dlap_plan* plan, const float* x, const float* R, const u
     P.index = index;
     P.months_ready = months_ready;
     P.months_base = months_ready ? months_base : 0;
+    P.months_stride = months_stride;
     P.cyc_sh = 2;      // blocks of four tiles: measured best of 1, 2, 4, 8 (smaller: more month changes per CTA;
                        // larger: the last CTAs wait longer for their first month, and the blocks balance worse)
     int grid = plan->grid_cell;

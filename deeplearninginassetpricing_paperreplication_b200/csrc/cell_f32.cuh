@@ -62,6 +62,8 @@ struct CellParams {
   // complete (tensor-core forward only); month t of this (possibly month-sharded) panel is month months_base + t there
   const int* months_ready;
   int months_base;
+  int months_stride;         // rows of a_t / c_t between consecutive months of this panel (1; n for a rank that owns
+                             // every n-th month of the series): tensor-core kernels only
   int cyc_sh;                // log2 of the block size of the block-cyclic tile order used with months_ready
 };
 

@@ -99,10 +99,11 @@ __device__ __forceinline__ void gather_role(const CellParams& P, int gw, int lan
   // (months_ready): wait for the month, and read past L1 (the lines can change during this kernel).
   int months_seen = 0;
   auto load_bias = [&](int t, float (&b)[3]) {
-    if (P.months_ready) wait_month(P.months_ready, P.months_base + t, months_seen);
-    b[0] = __ldcg(P.a_t + (size_t)t * 64 + lane);
-    b[1] = __ldcg(P.a_t + (size_t)t * 64 + 32 + lane);
-    b[2] = (MOM && lane < 8) ? __ldcg(P.c_t + (size_t)t * 8 + lane) : 0.f;
+    const size_t row = (size_t)t * P.months_stride;
+    if (P.months_ready) wait_month(P.months_ready, P.months_base + (int)row, months_seen);
+    b[0] = __ldcg(P.a_t + row * 64 + lane);
+    b[1] = __ldcg(P.a_t + row * 64 + 32 + lane);
+    b[2] = (MOM && lane < 8) ? __ldcg(P.c_t + row * 8 + lane) : 0.f;
   };
   uint64_t rows[BR];
 #pragma unroll

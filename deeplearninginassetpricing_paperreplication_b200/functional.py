@@ -183,24 +183,33 @@ class StepOptions:
 
 @dataclass
 class MonthShard:
-    """This rank's slab of months [t0, t1) of a T_total-month panel (see module docstring)."""
+    """This rank's months t0, t0 + stride, ... (< t1) of a T_total-month panel (see module docstring): a slab
+    (stride 1) or every stride-th month.  Dealing the months round-robin (rank r of n: t0 = r, stride = n) lets every
+    rank follow the LSTM recurrence from the first month on, instead of waiting until it reaches the rank's slab."""
     group: object
     t0: int
     t1: int
     T_total: int
     n_bar: torch.Tensor             # [1] float32, global mean of clamp(N_t, 1)
+    stride: int = 1
+
+    def rows(self, table: torch.Tensor) -> torch.Tensor:
+        """This rank's rows of a per-month table of the whole series (a view)."""
+        return table[self.t0:self.t1:self.stride]
 
 
-def make_month_shard(mask_local: torch.Tensor, t0: int, T_total: int, group=None) -> MonthShard:
-    """MonthShard for this rank's slab `mask_local` = months [t0, t0 + T_local) of a T_total-month panel.
+def make_month_shard(mask_local: torch.Tensor, t0: int, T_total: int, group=None, stride: int = 1) -> MonthShard:
+    """MonthShard for this rank's months `mask_local` = months t0, t0 + stride, ... of a T_total-month panel.
     The only mask-derived global quantity the row stage needs is N_bar = mean_t clamp(N_t, 1)
     (src/model.py:359-360); it is all-reduced here, once per panel, not per step."""
     import torch.distributed as dist
     n_t = mask_local.sum(dim=1).clamp(min=1).to(torch.float32).sum().reshape(1)
     dist.all_reduce(n_t, group=group)
     n_bar = (n_t / float(T_total)).to(torch.float32).contiguous()
-    return MonthShard(group=group, t0=int(t0), t1=int(t0) + int(mask_local.shape[0]), T_total=int(T_total),
-                      n_bar=n_bar)
+    t1 = int(t0) + (int(mask_local.shape[0]) - 1) * int(stride) + 1
+    if stride < 1 or t0 < 0 or t1 > T_total:
+        raise ValueError("month shard outside the series")
+    return MonthShard(group=group, t0=int(t0), t1=t1, T_total=int(T_total), n_bar=n_bar, stride=int(stride))
 
 
 def upload_panel(macro, x, R, mask, device, out=None, clear=True):
@@ -319,19 +328,22 @@ class GanStepFn(torch.autograd.Function):
             # ends up beside a pull CTA, and the step is bound by the bus anyway)
             beside = overlap_macro and opts.precision == "bf16x3" and M > 0 and ws.reserve == 0
             if sh is None:
-                wsm, t_base = ws, 0
+                wsm, t_base, t_stride = ws, 0, 1
                 save, a_t, c_t, hn, cn = macro_forward(ws, macro, params, h0, c0, beside)
                 a_loc, c_loc = a_t, c_t
-            else:   # LSTM replicated over the full series; this rank uses its slab of a_t / c_t
-                wsm, t_base = workspace(sh.T_total, N, F, M, H, dev), sh.t0
+            else:   # LSTM replicated over the full series; this rank uses its rows of a_t / c_t
+                wsm, t_base, t_stride = workspace(sh.T_total, N, F, M, H, dev), sh.t0, sh.stride
                 save, a_t, c_t, hn, cn = macro_forward(wsm, macro, params, h0, c0, beside)
-                a_loc, c_loc = a_t[sh.t0:sh.t1], c_t[sh.t0:sh.t1]
+                if opts.precision == "bf16x3":      # the kernel steps through the full tables itself
+                    a_loc, c_loc = a_t[sh.t0:], c_t[sh.t0:]
+                else:
+                    a_loc, c_loc, t_stride = sh.rows(a_t).contiguous(), sh.rows(c_t).contiguous(), 1
             u = torch.empty(T, N, dtype=torch.float32, device=dev)
             g = torch.empty(KM, T, N, dtype=torch.float32, device=dev) if opts.need_moments else None
             _timed_call("dlap_cell_fwd", dev, ws.pp, _ptr(x), _ptr(R), _ptr(mask), _ptr(index), C.byref(tens), _ptr(a_loc),
                       _ptr(c_loc), _ptr(u), _ptr(g), _ptr(ws.row_part), prec, float(opts.dropout_p),
                       int(opts.dropout_seed), _ptr(opts.dropout_seed_dev),
-                      _ptr(wsm.months_ready) if beside else None, t_base, st)
+                      _ptr(wsm.months_ready) if beside else None, t_base, t_stride, st)
             if beside:
                 join_macro(wsm)
             row_stats = torch.empty(T, RS_W, dtype=torch.float32, device=dev)
@@ -396,7 +408,7 @@ class GanStepFn(torch.autograd.Function):
             if sh is None:
                 a_loc, c_loc = a_t, c_t
             else:
-                a_loc, c_loc = a_t[sh.t0:sh.t1], c_t[sh.t0:sh.t1]
+                a_loc, c_loc = sh.rows(a_t).contiguous(), sh.rows(c_t).contiguous()
             _timed_call("dlap_cell_bwd", dev, ws.pp, _ptr(x), _ptr(R), _ptr(mask), _ptr(index), C.byref(tens), _ptr(a_loc),
                       _ptr(c_loc), _ptr(row_stats), _ptr(ws.ds_part), _ptr(g_pr), _ptr(G), _ptr(scalars),
                       int(opts.weighted_loss), int(want_sdf), int(want_mom), _ptr(ws.wpart),
@@ -420,10 +432,12 @@ class GanStepFn(torch.autograd.Function):
                 dadc_all = dadc = torch.empty(T, 72, dtype=torch.float32, device=dev)
             else:
                 dadc_all = buf[:head].view(sh.T_total, 72)
-                dadc = dadc_all[sh.t0:sh.t1]
+                dadc = sh.rows(dadc_all) if sh.stride == 1 else torch.empty(T, 72, dtype=torch.float32, device=dev)
             _timed_call("dlap_grad_finish", dev, ws.pp, _ptr(ws.wpart), _ptr(ws.dadc_part), _ptr(index), prec, int(want_sdf),
                       int(want_mom), C.byref(gt), _ptr(dadc), st)
             ws.launches += 4
+            if sh is not None and sh.stride != 1:
+                sh.rows(dadc_all).copy_(dadc)
             if sh is None:
                 wsm = ws
             else:   # exchange 2: per-cell weight grads + every month's da_t | dc_t row
@@ -458,7 +472,7 @@ def sdf_weights(macro, x, mask, params, h0=None, c0=None, normalized=False, prec
         u = torch.empty(T, N, dtype=torch.float32, device=dev)
         _lib.call("dlap_cell_fwd", ws.pp, _ptr(x), None, _ptr(mask), _ptr(index), C.byref(tens), _ptr(a_t), _ptr(c_t),
                   _ptr(u), None, _ptr(ws.row_part), _PRECISIONS[precision], 0.0, 0, None,
-                  _ptr(ws.months_ready) if beside else None, 0, st)
+                  _ptr(ws.months_ready) if beside else None, 0, 1, st)
         if beside:
             join_macro(ws)
         row_stats = torch.empty(T, RS_W, dtype=torch.float32, device=dev)

@@ -376,7 +376,7 @@ class GraphedStep:
 def _gather_months(pr_local, shard):
     import torch.distributed as dist
     full = torch.zeros(shard.T_total, dtype=pr_local.dtype, device=pr_local.device)
-    full[shard.t0:shard.t1] = pr_local.detach()
+    full[shard.t0:shard.t1:shard.stride] = pr_local.detach()
     dist.all_reduce(full, group=shard.group)
     sharpe = full.mean() / (full.std() + 1e-8)
     return full, sharpe

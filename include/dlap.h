@@ -144,11 +144,15 @@ int dlap_panel_pull(const dlap_plan* plan, const float* x_host, const int32_t* i
  * order that follows the months, and leaves one SM to the recurrence.  a_t and c_t must not be written
  * by anyone else meanwhile.  months_base: month 0 of this panel is month months_base of the series the
  * recurrence runs over (a month shard passes its first month and its slab of a_t / c_t; 0 otherwise).
- * With NULL, a_t and c_t are complete when the kernel starts (stream order) and months_base is ignored. */
+ * With NULL, a_t and c_t are complete when the kernel starts (stream order) and months_base is ignored.
+ * months_stride (>= 1; BF16X3 only when != 1): month t of this panel uses row t * months_stride of a_t and
+ * c_t (and is month months_base + t * months_stride of the recurrence) -- a rank that owns every n-th
+ * month of a series passes the full tables, offset to its first month, and n. */
 int dlap_cell_fwd(const dlap_plan* plan, const float* x, const float* R, const uint8_t* mask,
                   const int32_t* index, const dlap_tensors* params, const float* a_t, const float* c_t, float* u,
                   float* g, double* row_part, int precision, float dropout_p, uint64_t dropout_seed,
-                  const uint64_t* dropout_seed_dev, const int32_t* months_ready, int months_base, void* stream);
+                  const uint64_t* dropout_seed_dev, const int32_t* months_ready, int months_base, int months_stride,
+                  void* stream);
 
 /* Per-month statistics: N_t, mu_t (src/model.py:276-278), P_t, portfolio return pr_t and
  * S_t = 1 + pr_t (src/model.py:359-367, :380), Rbar_t; N_bar (src/model.py:360) and the Sharpe

@@ -37,7 +37,7 @@ def cell(ready):
     save, a_t, c_t, hn, cn = state["m"]
     _lib.call("dlap_cell_fwd", ws.pp, x.data_ptr(), R.data_ptr(), mask.data_ptr(), index.data_ptr(), C.byref(tens),
               a_t.data_ptr(), c_t.data_ptr(), u.data_ptr(), g.data_ptr(), ws.row_part.data_ptr(), 1, 0.0, 0, None,
-              ready, 0, st())
+              ready, 0, 1, st())
 
 
 def both(beside):

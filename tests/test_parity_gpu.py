@@ -124,7 +124,7 @@ def test_forward_stages_rand_small():
     u = torch.empty(T, N, device=dev()); gq = torch.empty(8, T, N, device=dev())
     _lib.call("dlap_cell_fwd", ws.pp, x.data_ptr(), R.data_ptr(), mask.data_ptr(), None, C.byref(tens),
               a_t.data_ptr(), c_t.data_ptr(), u.data_ptr(), gq.data_ptr(), ws.row_part.data_ptr(), 0, 0.0, 0,
-              None, None, 0, None)
+              None, None, 0, 1, None)
     torch.cuda.synchronize()
     assert np.abs(_np(u) - s["u"]).max() < 1e-5 * max(1.0, np.abs(s["u"]).max())
     gref = np.transpose(s["q"], (2, 0, 1)) * s["rm"][None]
@@ -190,7 +190,7 @@ def test_forward_stages_tensor_core_visits_only_unmasked_cells():
     u = torch.full((T, N), float("nan"), device=dev()); gq = torch.full((8, T, N), float("nan"), device=dev())
     _lib.call("dlap_cell_fwd", ws.pp, x.data_ptr(), R.data_ptr(), mask.data_ptr(), index.data_ptr(), C.byref(tens),
               a_t.data_ptr(), c_t.data_ptr(), u.data_ptr(), gq.data_ptr(), ws.row_part.data_ptr(), 1, 0.0, 0,
-              None, None, 0, None)
+              None, None, 0, 1, None)
     torch.cuda.synchronize()
     m = g["mask"]
     un, gn = _np(u), _np(gq)

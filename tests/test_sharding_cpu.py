@@ -76,6 +76,13 @@ def _worker(rank, world, port, out_q):
         da_all = buf[: T * 64].numpy().reshape(T, 64)
         assert np.allclose(buf[T * 64:].numpy().reshape(64, 64), gfull[cf.K_W2], rtol=1e-4, atol=1e-12)
         assert np.allclose(da_all.sum(axis=0), gfull[cf.K_B1], rtol=1e-4, atol=1e-12)
+        # months dealt round-robin: rank r owns months r, r + 2, ...
+        rr = Fn.make_month_shard(torch.from_numpy(mask[rank::2]), rank, T, None, stride=2)
+        assert abs(float(rr.n_bar) - n_bar_ref) < 1e-4 and rr.stride == 2 and rr.t1 <= T
+        assert torch.equal(rr.rows(torch.arange(T)), torch.arange(T)[rank::2])
+        pr_rr, sharpe_rr = _gather_months(torch.from_numpy(full["portfolio_returns"][rank::2].astype(np.float32)), rr)
+        assert np.allclose(pr_rr.numpy(), full["portfolio_returns"], rtol=1e-5, atol=1e-8)
+        assert abs(float(sharpe_rr) - float(full["sharpe"])) < 1e-4 * abs(float(full["sharpe"]))
         out_q.put((rank, "ok"))
     except Exception:  # pragma: no cover
         import traceback

@@ -27,7 +27,14 @@ def _panel(T, N, M):
     return macro, x, R, mask
 
 
-def _worker(rank, world, port, precision, out_q):
+def _months(rank, T, layout):
+    """Month numbers of a rank: two uneven slabs, or every second month."""
+    if layout == "slabs":
+        return list(range(0, 9)) if rank == 0 else list(range(9, T))
+    return list(range(rank, T, 2))
+
+
+def _worker(rank, world, port, precision, layout, out_q):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     dist.init_process_group("gloo", rank=rank, world_size=world)
     try:
@@ -36,13 +43,14 @@ def _worker(rank, world, port, precision, out_q):
         dev = torch.device("cuda:0")
         T, N, M = 22, 700, 8
         macro, x, R, mask = _panel(T, N, M)
-        t0, t1 = (0, 9) if rank == 0 else (9, T)          # uneven slabs on purpose
+        mine = _months(rank, T, layout)
         torch.manual_seed(4)
         model = AssetPricingGAN({"macro_feature_dim": M, "individual_feature_dim": 46, "dropout": 0.0,
                                  "b200_precision": precision}).to(dev)
-        model.month_shard = Fn.make_month_shard(mask[t0:t1].to(dev), t0, T, None)
-        out = model(macro.to(dev), x[t0:t1].contiguous().to(dev), R[t0:t1].contiguous().to(dev),
-                    mask[t0:t1].contiguous().to(dev), phase="conditional")
+        model.month_shard = Fn.make_month_shard(mask[mine].to(dev), mine[0], T, None,
+                                                stride=1 if layout == "slabs" else 2)
+        out = model(macro.to(dev), x[mine].contiguous().to(dev), R[mine].contiguous().to(dev),
+                    mask[mine].contiguous().to(dev), phase="conditional")
         out["loss"].backward()
         torch.cuda.synchronize()
         res = {"loss": float(out["loss"]), "loss_u": float(out["loss_unconditional"]), "sharpe": float(out["sharpe"]),
@@ -56,13 +64,14 @@ def _worker(rank, world, port, precision, out_q):
         dist.destroy_process_group()
 
 
+@pytest.mark.parametrize("layout", ["slabs", "round_robin"])
 @pytest.mark.parametrize("precision", ["fp32", "bf16x3"])
-def test_two_month_shards_match_single_process(precision):
+def test_two_month_shards_match_single_process(precision, layout):
     from deeplearninginassetpricing_paperreplication_b200 import AssetPricingGAN
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = _free_port()
-    procs = [ctx.Process(target=_worker, args=(r, 2, port, precision, q)) for r in range(2)]
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, precision, layout, q)) for r in range(2)]
     for p in procs:
         p.start()
     res = dict(q.get(timeout=240) for _ in procs)
@@ -82,8 +91,10 @@ def test_two_month_shards_match_single_process(precision):
         assert abs(res[r]["loss_u"] - float(ref["loss_unconditional"])) <= 1e-5 * abs(float(ref["loss_unconditional"]))
         assert np.allclose(res[r]["pr"], ref["portfolio_returns"].detach().cpu().numpy(), rtol=1e-4, atol=1e-7)
         assert abs(res[r]["sharpe"] - float(ref["sharpe"])) <= 1e-4 * abs(float(ref["sharpe"])) + 1e-6
-    w = np.concatenate([res[0]["w"], res[1]["w"]], axis=0)
     wref = ref["weights"].detach().cpu().numpy()
+    w = np.empty_like(wref)
+    for r in (0, 1):
+        w[_months(r, T, layout)] = res[r]["w"]
     assert np.abs(w - wref).max() <= 1e-4 * np.abs(wref).max()
     tol = 2e-4 if precision == "fp32" else 2e-2
     for k, p in model.named_parameters():
