@@ -10,7 +10,7 @@ Every stage is a kernel launch through ``libdlap_b200.so`` on torch's current st
 used for device memory and streams only.  Nothing here synchronises with the host, so a whole
 training step can be captured in a CUDA graph.
 
-Month-sharded multi-GPU runs (``shard`` argument): each rank owns a contiguous slab of months
+Month-sharded multi-GPU runs (``shard`` argument): each rank owns a slab of months, or every n-th month,
 of ``x``/``R``/``mask`` and the full macro series.  The only exchanges are an all-reduce of the
 per-stock column sums ``[10, N]`` in the forward pass and, in the backward pass, an all-reduce
 of the per-month ``da_t | dc_t`` rows (zero outside the rank's slab) together with the
