@@ -362,7 +362,8 @@ class GanStepFn(torch.autograd.Function):
                 col, nsplit = ws.col_part, ws.plan.col_splits
             else:   # exchange 1: per-stock sums over ALL months
                 with _timed_region("exchange_fwd", dev):
-                    col = ws.col_part.view(ws.plan.col_splits, KM + 2, N).sum(dim=0)
+                    col = ws.col_part.view(ws.plan.col_splits, KM + 2, N)
+                    col = col[0] if ws.plan.col_splits == 1 else col.sum(dim=0)   # one split: reduce it in place
                     torch.distributed.all_reduce(col, group=sh.group)
                 nsplit = 1
             _timed_call("dlap_loss_finish", dev, ws.pp, _ptr(col), nsplit, _ptr(e), _ptr(t_i),
