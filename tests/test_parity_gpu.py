@@ -243,6 +243,29 @@ def test_upload_panel_pulls_exactly_the_unmasked_rows(shape):
             assert torch.equal(a, b)
 
 
+def test_upload_panel_into_a_buffer_the_loader_cleared():
+    """upload_panel(out=..., clear=False): no memset in front of the pull -- a loader that double-buffers its panels
+    zeroes a buffer straight after the step that used it.  Unmasked rows arrive, masked rows keep what the buffer
+    held (zeros here; the stale value when nobody cleared it)."""
+    from deeplearninginassetpricing_paperreplication_b200 import upload_panel
+    T, N, F = 9, 700, 46
+    rng = np.random.default_rng(6)
+    mask = torch.from_numpy(rng.random((T, N)) < 0.4)
+    x = torch.from_numpy(rng.standard_normal((T, N, F)).astype(np.float32))
+    R = torch.from_numpy((0.1 * rng.standard_normal((T, N))).astype(np.float32)) * mask
+    macro = torch.from_numpy(rng.standard_normal((T, 178)).astype(np.float32))
+    host = [t.pin_memory() for t in (macro, x, R, mask)]
+    for stale in (0.0, 7.0):
+        out = [torch.empty_like(t, device=dev()) for t in host]
+        out[1].fill_(stale)
+        _, d_x, _, d_mask = upload_panel(*host, device=dev(), out=out, clear=False)
+        torch.cuda.synchronize()
+        xd = d_x.cpu()
+        assert d_x is out[1] and torch.equal(d_mask.cpu(), mask)
+        assert torch.equal(xd[mask], x[mask])
+        assert bool((xd[~mask] == stale).all())
+
+
 @pytest.mark.parametrize("precision", ["fp32", "bf16x3"])
 def test_graphed_step_replays_the_eager_step_bit_for_bit(precision):
     """GraphedStep (zero_grad + forward + backward in one CUDA graph): every replay reproduces the eager step's
