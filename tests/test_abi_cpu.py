@@ -35,6 +35,18 @@ def test_library_builds_and_exports_every_declared_symbol():
     assert _lib.load().dlap_error_string(-2).decode().startswith("dimension")
 
 
+def test_ctypes_signatures_have_the_arity_of_the_header():
+    """Every entry point is bound with as many arguments as include/dlap.h declares (a mismatch would pass garbage
+    pointers to the kernels instead of failing)."""
+    src = re.sub(r"/\*.*?\*/", "", open(HEADER).read(), flags=re.S)
+    decl = {m.group(1): m.group(2) for m in re.finditer(r"\bint\s+(dlap_[a-z0-9_]+)\s*\(([^;]*?)\)\s*;", src, flags=re.S)}
+    for name, sig in _lib.SIGNATURES.items():
+        assert name in decl, name
+        args = decl[name].strip()
+        n = 0 if args in ("", "void") else args.count(",") + 1
+        assert n == len(sig), (name, n, len(sig))
+
+
 def test_plan_without_device_reports_error():
     if torch.cuda.is_available():
         pytest.skip("a device is present")
