@@ -47,7 +47,7 @@ using namespace dlap;
 static int check_dims(const dlap_dims& d) {
   if (d.T < 1 || d.N < 1 || d.F < 1 || d.F > FMAX) return DLAP_E_SHAPE;
   if (d.M < 0 || (d.M > 0 && (d.H < 1 || d.H > HMAX))) return DLAP_E_SHAPE;
-  if ((long long)d.T * d.N >= (1ll << 40)) return DLAP_E_SHAPE;
+  if ((long long)d.T * d.N >= (1ll << 32)) return DLAP_E_SHAPE;      // cell numbers (dropout key, packed offsets) are 32-bit
   if ((long long)d.N * d.F * 4 >= (1ll << 32)) return DLAP_E_SHAPE;   // byte offsets inside a month are 32-bit
   return DLAP_OK;
 }
@@ -162,7 +162,7 @@ int dlap_macro_fwd(const dlap_plan* plan, const float* macro, const dlap_tensors
   if (rc) return rc;
   REQ(params); REQ(a_t); REQ(c_t); REQ(params->b1); REQ(params->bq);
   if (plan->dims.M > 0) {
-    REQ(macro); REQ(lstm_save); REQ(hn); REQ(cn); REQ(xproj_scratch);
+    REQ(macro); REQ(lstm_save); REQ(hn); REQ(cn);
     REQ(params->w_ih); REQ(params->w_hh); REQ(params->b_ih); REQ(params->b_hh); REQ(params->w1); REQ(params->wq);
   }
   if (reinterpret_cast<uintptr_t>(months_ready) & 3) return DLAP_E_ALIGN;

@@ -34,6 +34,7 @@ SC_W = 8      # scalars width
 SC_LC, SC_LU, SC_SHARPE, SC_NBAR = 0, 1, 2, 3
 RS_NT, RS_MU, RS_P, RS_PR, RS_S, RS_RBAR = 0, 1, 2, 3, 4, 5
 KM = 8
+TC_MAX_F = 46   # characteristics the tensor-core kernels take (the ones column of the X image sits at k = 46)
 
 _PRECISIONS = {"fp32": _lib.DLAP_PREC_FP32, "bf16x3": _lib.DLAP_PREC_BF16X3}
 _BWD_PRECISION = {"fp32": "fp32", "bf16x3": "bf16x3"}     # arithmetic of dlap_cell_bwd per model precision
@@ -134,7 +135,7 @@ class Workspace:
         return panel_index(self, mask)
 
 
-_index_cache = []          # up to 4 x (weakref to a mask tensor, its version, index), most recent last
+_index_cache = []          # up to 4 x (weakref to a mask tensor, key, index, build event, build stream), most recent last
 
 
 def panel_index(ws: "Workspace", mask: torch.Tensor) -> torch.Tensor:
@@ -142,17 +143,33 @@ def panel_index(ws: "Workspace", mask: torch.Tensor) -> torch.Tensor:
     the very same tensor object with an unchanged version counter (full-batch training loops do; a loop that
     double-buffers its panels alternates between two); any other mask gets a freshly allocated index, so an
     index captured for a pending backward is never overwritten.  The index depends on T and N only, so one
-    small cache serves every workspace."""
+    small cache serves every workspace.
+    The key is (tensor object, version counter, data pointer, device).  Writes that bypass the version counter
+    (``mask.data = ...``, DLPack / CUDA-array-interface aliases, foreign kernels) are invisible to it: call
+    ``invalidate_panel_index()`` after such a write.  The index is built on the stream that is current at the
+    time; a later call on ANOTHER stream waits for the build event before it hands the index out."""
+    cur = torch.cuda.current_stream(ws.device)
+    key = (mask._version, mask.data_ptr(), mask.device)
     for k, hit in enumerate(_index_cache):
-        if hit[0]() is mask and hit[1] == mask._version:
+        if hit[0]() is mask and hit[1] == key:
             _index_cache.append(_index_cache.pop(k))
+            if hit[4] != cur.cuda_stream and not torch.cuda.is_current_stream_capturing():
+                cur.wait_event(hit[3])
             return hit[2]
     index = torch.empty(max(ws.plan.index_bytes // 4, 4), dtype=torch.int32, device=ws.device)
-    _lib.call("dlap_panel_index", ws.pp, _ptr(mask), _ptr(index), _stream(ws.device))
+    _lib.call("dlap_panel_index", ws.pp, _ptr(mask), _ptr(index), cur.cuda_stream)
     ws.launches += 2
-    _index_cache.append((weakref.ref(mask), mask._version, index))
+    built = torch.cuda.Event()
+    if not torch.cuda.is_current_stream_capturing():
+        built.record(cur)
+    _index_cache.append((weakref.ref(mask), key, index, built, cur.cuda_stream))
     del _index_cache[:-4]
     return index
+
+
+def invalidate_panel_index() -> None:
+    """Forget every cached valid-cell index (see panel_index)."""
+    del _index_cache[:]
 
 
 _workspaces: Dict[Tuple, Workspace] = {}

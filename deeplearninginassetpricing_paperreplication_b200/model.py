@@ -223,8 +223,12 @@ class AssetPricingGAN(nn.Module):
             dropout=dropout)
         self.residual_loss_factor = config.get('residual_loss_factor', 0.0)
         self.weighted_loss = config.get('weighted_loss', True)
-        # kernel arithmetic of the per-cell contractions ("fp32" = exact FFMA)
-        self.precision = config.get('b200_precision', 'fp32')
+        # kernel arithmetic of the per-cell contractions: "bf16x3" = tensor cores on hi/lo-split operands,
+        # "fp32" = exact FFMA on CUDA cores, "auto" (default: the reference's own config dict carries no such
+        # key) = bf16x3 whenever the tensor-core kernels take the shape (F <= 46), fp32 otherwise
+        self.precision = config.get('b200_precision', 'auto')
+        if self.precision not in ('auto', 'fp32', 'bf16x3'):
+            raise ValueError(f"b200_precision must be 'auto', 'fp32' or 'bf16x3', not {self.precision!r}")
         self.month_shard: Optional[Fn.MonthShard] = None
 
     # -- fast-path plumbing -------------------------------------------------------------------
@@ -233,6 +237,11 @@ class AssetPricingGAN(nn.Module):
         if z is None or z.device != dev:
             z = self._zero_cache = torch.zeros((), dtype=torch.float32, device=dev)
         return z
+
+    def _precision(self, F: int) -> str:
+        if self.precision != 'auto':
+            return self.precision
+        return 'bf16x3' if F <= Fn.TC_MAX_F else 'fp32'
 
     def _kernel_params(self, with_macro: bool):
         if self._hidden_dim_moment:
@@ -257,7 +266,7 @@ class AssetPricingGAN(nn.Module):
         seed_dev = getattr(self, "_seed_dev", None) if p_drop > 0 else None   # GraphedStep: seed in device memory
         seed = int(torch.randint(0, 2 ** 62, (1,)).item()) if p_drop > 0 and seed_dev is None else 0   # CPU generator: no sync
         opts = Fn.StepOptions(weighted_loss=bool(self.weighted_loss),
-                              need_moments=(phase != 'unconditional'), precision=self.precision,
+                              need_moments=(phase != 'unconditional'), precision=self._precision(x.shape[2]),
                               dropout_p=p_drop, dropout_seed=seed, dropout_seed_dev=seed_dev,
                               shard=self.month_shard)
         l_c, l_u, pr, w, sharpe, hn, cn = Fn.GanStepFn.apply(
@@ -294,7 +303,7 @@ class AssetPricingGAN(nn.Module):
     def get_weights(self, macro_features, individual_features, mask, hidden=None, normalized: bool = False):
         """src/model.py:565-594."""
         return _weights(self.sdf_net, self.moment_net, macro_features, individual_features, mask, hidden,
-                        normalized, self.precision)
+                        normalized, self._precision(individual_features.shape[2]))
 
     def get_sdf_factor(self, macro_features, individual_features, returns, mask, hidden=None,
                        normalized: bool = True):

@@ -186,7 +186,9 @@ int dlap_loss_finish(const dlap_plan* plan, const double* col_part, int nsplit, 
  * loads the library, for the life of the process.  Limits and rules:
  *   - at most DLAP_NOALLOC_MAX_STOCKS stocks (plan->dims.N); beyond that the call returns DLAP_E_LIMIT;
  *   - the first call on each device looks up the array's device address (one-time set-up with that
- *     device current); make that first call before starting any stream capture;
+ *     device current); make that first call before starting any stream capture.  "That device" is the
+ *     CURRENT device of the calling thread (cudaGetDevice), not the device `stream` belongs to: make the
+ *     device that owns `stream` and the buffers current before the call, as for every entry point here;
  *   - every call on a device shares the one array and it keeps the previous call's contents (the call
  *     itself clears the one word that must start at zero); two calls that overlap on the GPU - different
  *     streams, or different threads - race on it.  Serialise them.

@@ -69,7 +69,7 @@ def macro_lstm(params, macro: torch.Tensor, hidden=None):
     seq = macro.unsqueeze(0)
     hsz = params[K_WHH].shape[1]
     if hidden is None:
-        z = torch.zeros(1, 1, hsz, dtype=macro.dtype)
+        z = torch.zeros(1, 1, hsz, dtype=macro.dtype, device=macro.device)
         hidden = (z, z.clone())
     flat = [params[K_WIH], params[K_WHH], params[K_BIH], params[K_BHH]]
     out, hn, cn = torch._VF.lstm(seq, hidden, flat, True, 1, 0.0, False, False, True)
@@ -151,7 +151,7 @@ def forward(params, macro, x, R, mask, hidden=None, phase: str = "conditional",
     """AssetPricingGAN.forward (src/model.py:485-563) with ``residual_loss_factor == 0``."""
     w, new_hidden = sdf_weights(params, macro, x, mask, hidden, normalize_w)
     q = moment_conditions(params, macro, x)
-    zero = torch.tensor(0.0)
+    zero = torch.zeros((), device=x.device)
     if phase == "unconditional":                                               # :524-528
         l_u, pr = unconditional_loss(w, R, mask, weighted_loss)
         l_c, total = zero, l_u

@@ -23,6 +23,7 @@ def dev():
 
 
 def _model_from(params, M, F=46, **cfg):
+    cfg.setdefault("b200_precision", "fp32")      # this file pins the exact-fp32 path unless a test says otherwise
     model = AssetPricingGAN({"macro_feature_dim": M, "individual_feature_dim": F, **cfg})
     model.load_state_dict({k: torch.as_tensor(v) for k, v in params.items()})
     return model.to(dev())
@@ -403,7 +404,7 @@ def test_step_vs_oracle_shapes(T, N, M, phase):
         mask[:, 2] = False              # a never-valid stock
     x = x * mask[:, :, None]; R = R * mask
     torch.manual_seed(N)
-    model = AssetPricingGAN({"macro_feature_dim": M, "individual_feature_dim": 46}).to(dev()).eval()
+    model = AssetPricingGAN({"b200_precision": "fp32", "macro_feature_dim": M, "individual_feature_dim": 46}).to(dev()).eval()
     _check_against_cf(model, macro, x, R, mask, phase)
 
 
@@ -411,10 +412,10 @@ def test_no_macro_and_other_feature_counts():
     for F in (46, 13, 64):
         _, x, R, mask = make_panel(6, 200, 0, F=F, seed=F)
         torch.manual_seed(1)
-        model = AssetPricingGAN({"individual_feature_dim": F}).to(dev()).eval()
+        model = AssetPricingGAN({"b200_precision": "fp32", "individual_feature_dim": F}).to(dev()).eval()
         _check_against_cf(model, None, x, R, mask, "conditional")
         macro, x, R, mask = make_panel(6, 200, 20, F=F, seed=F)
-        model = AssetPricingGAN({"individual_feature_dim": F, "macro_feature_dim": 20,
+        model = AssetPricingGAN({"b200_precision": "fp32", "individual_feature_dim": F, "macro_feature_dim": 20,
                                  "num_units_rnn": [6]}).to(dev()).eval()
         _check_against_cf(model, macro, x, R, mask, "conditional")
 
@@ -428,7 +429,7 @@ def test_unaligned_panel_view():
     xv.copy_(x)
     assert xv.data_ptr() % 16 == 8
     torch.manual_seed(2)
-    model = AssetPricingGAN({"macro_feature_dim": 8, "individual_feature_dim": 46}).to(d).eval()
+    model = AssetPricingGAN({"b200_precision": "fp32", "macro_feature_dim": 8, "individual_feature_dim": 46}).to(d).eval()
     o1 = model(macro.to(d), xv, R.to(d), mask.to(d))
     o2 = model(macro.to(d), x.to(d), R.to(d), mask.to(d))
     assert torch.equal(o1["weights"], o2["weights"]) and torch.equal(o1["loss"], o2["loss"])
@@ -438,7 +439,7 @@ def test_all_masked_panel():
     macro, x, R, mask = make_panel(4, 150, 8, seed=1)
     mask[:] = False
     x = x * 0; R = R * 0
-    model = AssetPricingGAN({"macro_feature_dim": 8, "individual_feature_dim": 46}).to(dev()).eval()
+    model = AssetPricingGAN({"b200_precision": "fp32", "macro_feature_dim": 8, "individual_feature_dim": 46}).to(dev()).eval()
     out = model(macro.to(dev()), x.to(dev()), R.to(dev()), mask.to(dev()))
     out["loss"].backward()
     assert float(out["loss"]) == 0.0 and float(out["weights"].abs().max()) == 0.0
@@ -449,7 +450,7 @@ def test_bit_reproducible():
     macro, x, R, mask = make_panel(12, 700, 178, seed=4)
     d = dev()
     torch.manual_seed(3)
-    model = AssetPricingGAN({"macro_feature_dim": 178, "individual_feature_dim": 46}).to(d).eval()
+    model = AssetPricingGAN({"b200_precision": "fp32", "macro_feature_dim": 178, "individual_feature_dim": 46}).to(d).eval()
     args = (macro.to(d), x.to(d), R.to(d), mask.to(d))
     res = []
     for _ in range(2):
@@ -466,7 +467,7 @@ def test_grad_accumulates_and_cotangents():
     macro, x, R, mask = make_panel(6, 300, 8, seed=5)
     d = dev()
     torch.manual_seed(3)
-    model = AssetPricingGAN({"macro_feature_dim": 8, "individual_feature_dim": 46}).to(d).eval()
+    model = AssetPricingGAN({"b200_precision": "fp32", "macro_feature_dim": 8, "individual_feature_dim": 46}).to(d).eval()
     args = (macro.to(d), x.to(d), R.to(d), mask.to(d))
     model(*args)["loss"].backward()
     g1 = [p.grad.clone() for p in model.parameters()]
@@ -486,7 +487,7 @@ def test_trajectory_matches_oracle():
     macro, x, R, mask = make_panel(24, 400, 8, seed=6)
     d = dev()
     torch.manual_seed(5)
-    model = AssetPricingGAN({"macro_feature_dim": 8, "individual_feature_dim": 46, "dropout": 0.0}).to(d)
+    model = AssetPricingGAN({"b200_precision": "fp32", "macro_feature_dim": 8, "individual_feature_dim": 46, "dropout": 0.0}).to(d)
     ref = {k: v.detach().cpu().clone().requires_grad_(True) for k, v in model.state_dict().items()}
     opt = torch.optim.Adam(model.sdf_net.parameters(), lr=1e-3)
     ropt = torch.optim.Adam([ref[k] for k in tp.SDF_KEYS], lr=1e-3)
@@ -602,7 +603,7 @@ def test_dropout_mask_is_the_same_in_both_precisions():
     d = dev()
     args = (macro.to(d), x.to(d), R.to(d), mask.to(d))
     torch.manual_seed(5)
-    m32 = AssetPricingGAN({"macro_feature_dim": 8, "individual_feature_dim": 46, "dropout": 0.05}).to(d)
+    m32 = AssetPricingGAN({"b200_precision": "fp32", "macro_feature_dim": 8, "individual_feature_dim": 46, "dropout": 0.05}).to(d)
     mtc = AssetPricingGAN({"macro_feature_dim": 8, "individual_feature_dim": 46, "dropout": 0.05,
                            "b200_precision": "bf16x3"}).to(d)
     mtc.load_state_dict(m32.state_dict())
@@ -618,7 +619,7 @@ def test_dropout_mask_is_the_same_in_both_precisions():
 def test_errors_are_loud():
     d = dev()
     macro, x, R, mask = make_panel(4, 50, 8, seed=8)
-    model = AssetPricingGAN({"macro_feature_dim": 8, "individual_feature_dim": 46}).to(d)
+    model = AssetPricingGAN({"b200_precision": "fp32", "macro_feature_dim": 8, "individual_feature_dim": 46}).to(d)
     with pytest.raises(ValueError):
         model(macro.to(d), x.to(d).double(), R.to(d), mask.to(d))
     with pytest.raises(ValueError):

@@ -1,5 +1,7 @@
-"""Month-sharded step on the GPU: two processes share cuda:0 (gloo carries the all-reduces, so one GPU
-is enough) and must reproduce the single-process losses, weights and gradients."""
+"""Month-sharded step on the GPU: two processes must reproduce the single-process losses, weights and gradients.
+On one GPU the two ranks share cuda:0 and gloo carries the all-reduces; with two GPUs or more the same check
+runs over NCCL, one rank per GPU, eagerly AND as a replay of the captured CUDA graph (GraphedStep, the NCCL
+all-reduces inside the graph) -- the path bench.py times at N > 1."""
 import os
 import socket
 
@@ -40,13 +42,17 @@ def _months(rank, T, layout):
     return list(range(rank, T, 2))
 
 
-def _worker(rank, world, port, precision, layout, out_q):
+def _worker(rank, world, port, precision, layout, out_q, backend="gloo"):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
-    dist.init_process_group("gloo", rank=rank, world_size=world)
+    dev = torch.device("cuda", rank if backend == "nccl" else 0)
+    torch.cuda.set_device(dev)
+    if backend == "nccl":
+        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    else:
+        dist.init_process_group("gloo", rank=rank, world_size=world)
     try:
         from deeplearninginassetpricing_paperreplication_b200 import AssetPricingGAN
         from deeplearninginassetpricing_paperreplication_b200 import functional as Fn
-        dev = torch.device("cuda:0")
         T, N, M = _shape(layout)
         macro, x, R, mask = _panel(T, N, M)
         mine = _months(rank, T, layout)
@@ -55,10 +61,21 @@ def _worker(rank, world, port, precision, layout, out_q):
                                  "b200_precision": precision}).to(dev)
         model.month_shard = Fn.make_month_shard(mask[mine].to(dev), mine[0], T, None,
                                                 stride=1 if layout == "slabs" else 2)
-        out = model(macro.to(dev), x[mine].contiguous().to(dev), R[mine].contiguous().to(dev),
-                    mask[mine].contiguous().to(dev), phase="conditional")
+        panel = (macro.to(dev), x[mine].contiguous().to(dev), R[mine].contiguous().to(dev),
+                 mask[mine].contiguous().to(dev))
+        out = model(*panel, phase="conditional")
         out["loss"].backward()
         torch.cuda.synchronize()
+        if backend == "nccl":          # the same step as a CUDA-graph replay must say the same, to the bit
+            eager = {k: p.grad.clone() for k, p in model.named_parameters()}
+            e_loss, e_w = out["loss"].clone(), out["weights"].clone()
+            model.eval()
+            gs = model.graphed_step(*panel, phase="conditional")
+            out = gs.step(); out = gs.step()
+            torch.cuda.synchronize()
+            assert torch.equal(out["loss"], e_loss) and torch.equal(out["weights"], e_w)
+            for k, p in model.named_parameters():
+                assert torch.equal(p.grad, eager[k]), k
         res = {"loss": float(out["loss"]), "loss_u": float(out["loss_unconditional"]), "sharpe": float(out["sharpe"]),
                "pr": out["portfolio_returns"].cpu().numpy(), "w": out["weights"].cpu().numpy(),
                "grads": {k: p.grad.cpu().numpy() for k, p in model.named_parameters()}}
@@ -70,14 +87,21 @@ def _worker(rank, world, port, precision, layout, out_q):
         dist.destroy_process_group()
 
 
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs (NCCL, one rank per GPU)")
+@pytest.mark.parametrize("precision,layout", [("bf16x3", "round_robin"), ("bf16x3", "slabs"), ("fp32", "round_robin"),
+                                              ("bf16x3", "round_robin_wide")])
+def test_two_month_shards_nccl_eager_and_graph(precision, layout):
+    test_two_month_shards_match_single_process(precision, layout, backend="nccl")
+
+
 @pytest.mark.parametrize("precision,layout", [("fp32", "slabs"), ("bf16x3", "slabs"), ("fp32", "round_robin"),
                                               ("bf16x3", "round_robin"), ("bf16x3", "round_robin_wide")])
-def test_two_month_shards_match_single_process(precision, layout):
+def test_two_month_shards_match_single_process(precision, layout, backend="gloo"):
     from deeplearninginassetpricing_paperreplication_b200 import AssetPricingGAN
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = _free_port()
-    procs = [ctx.Process(target=_worker, args=(r, 2, port, precision, layout, q)) for r in range(2)]
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, precision, layout, q, backend)) for r in range(2)]
     for p in procs:
         p.start()
     res = dict(q.get(timeout=240) for _ in procs)
