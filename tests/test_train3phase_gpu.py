@@ -23,8 +23,12 @@ pytestmark = [pytest.mark.gpu,
               pytest.mark.skipif(not os.path.isdir(os.path.join(REF, "src")), reason="baseline/_ref not staged")]
 
 
-LOSS_TOL = {"fp32": 1e-2, "bf16x3": 2e-2, None: 2e-2}
-SHARPE_TOL = {"fp32": 2e-3, "bf16x3": 5e-3, None: 5e-3}
+# Measured on B200 (96 recorded epochs, 112 Adam steps): exact-fp32 kernels 6e-4 .. 8e-4 on the losses and 6e-4 on the
+# Sharpe ratios -- the floor set by summation order alone, since any two fp32 implementations already take a
+# different side of some ReLUs; tensor-core kernels (pre-activations good to 2^-18 instead of 2^-24, i.e. more such
+# ReLU decisions differ) 5e-3 .. 8e-3 and 4e-3.  The bounds leave a factor ~2.5.
+LOSS_TOL = {"fp32": 2e-3, "bf16x3": 2e-2, None: 2e-2}
+SHARPE_TOL = {"fp32": 2e-3, "bf16x3": 1e-2, None: 1e-2}      # relative to max(|Sharpe|, 0.2)
 
 
 def _reference():
@@ -106,8 +110,8 @@ def test_reference_train_3phase_on_the_drop_in(cpu_run, precision):
         assert err <= tol, (key, err)
     for key in ("train_sharpe", "valid_sharpe", "test_sharpe"):
         a, b = hist[key], ref[key]
-        err = np.abs(a - b).max()
-        print(f"[{precision}] {key}: worst absolute deviation {err:.2e} (values up to {np.abs(b).max():.3f})")
+        err = (np.abs(a - b) / np.maximum(np.abs(b), 0.2)).max()
+        print(f"[{precision}] {key}: worst relative deviation {err:.2e} (values up to {np.abs(b).max():.3f})")
         assert err <= SHARPE_TOL[precision], (key, err)
     # the trained parameters themselves
     sd, rsd = model.state_dict(), cpu_run["model"].state_dict()

@@ -1,0 +1,358 @@
+// Macro path: everything that is per MONTH rather than per stock-month.
+//
+//   forward: input projection W_ih.macro_t for all months in parallel (multi-CTA), then one persistent CTA:
+//            the serial LSTM recurrence on one warp (one lane per unit, h broadcast by shuffles) and, trailing
+//            it on a second warp, the per-month biases that replace the reference's two tile-over-N concats:
+//                                  a_t = W1[:,F:].h_t + b1  (src/model.py:253-255, :211)
+//                                  c_t = Wq[:,:M].macro_t + bq (src/model.py:514-516, :152, by the projection).
+//            The months are published as they complete, so the per-cell forward kernel can run beside it.
+//            LSTM semantics: torch.nn.LSTM, gates i,f,g,o (src/model.py:39-45, :68).
+//   backward (one persistent CTA): dh_t = W1[:,F:]^T.da_t, BPTT on one warp, then the
+//            month-summed weight gradients (LSTM, W1[:,F:], b1, Wq[:,:M], bq).
+#include "../../include/dlap.h"
+#include "dlap_common.cuh"
+#include "macro_role.cuh"
+#include "grad_finish.cuh"
+
+namespace dlap {
+
+template <int H>
+__global__ void __launch_bounds__(MT, 1) macro_fwd_kernel(const MacroParams P) {
+  extern __shared__ __align__(16) float sm[];
+  macro_fwd_role<H>(P, sm);
+}
+
+// BPTT: one CTA.  Writes dpre[T][4H] (pre-activation gradients) to P.dpre.
+// The carried state is (dh_rec, dc) per unit and every step is linear in it:
+//   dht = dhe_t + dh_rec ;  dcn = dc + a_c . dht ;  dh_rec' = A_t^T dcn + B_t^T dht ;  dc' = f_t . dcn
+// with  A_t[j][k] = Whh_i[j][k] a_i[j] + Whh_f[j][k] a_f[j] + Whh_g[j][k] a_g[j]  and  B_t[j][k] = Whh_o[j][k] a_o[j]
+// (a_* = the local derivatives of step t).  Everything that does not depend on the carried state -- dhe_t, the
+// a_*, A_t, B_t -- is computed by all threads first; the serial chain on warp 0 is then 2H shuffles + 2H FMAs
+// per step and lane, and the gate gradients d{i,f,g} = dcn a_{i,f,g}, do = dht a_o follow in parallel.
+// dynamic smem: sv[T][6H] (saved states, later S[T][2H] = dht | dcn) | Y[T][H][REC] | W1m[64][H] | Whh[4H][H]
+// record (REC = 8 + 2 HP floats, HP = H rounded up to 4): a_c f dhe . | a_i a_f a_g a_o | A[.][k] | B[.][k]
+template <int H>
+__global__ void __launch_bounds__(MT, 1) macro_bptt_kernel(const MacroParams P) {
+  extern __shared__ float sm[];
+  const int T = P.T;
+  constexpr int G4 = 4 * H;
+  float* sv_s = sm;                                  // [T][6H]: h, c, i, f, g, o
+  constexpr int HP = (H + 3) & ~3, REC = 8 + 2 * HP;
+  float* Y = sv_s + (size_t)T * 6 * H;               // [T][H][REC]
+  float* w1m = Y + (size_t)T * H * REC;
+  float* whh = w1m + D1 * H;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  for (int i = tid; i < T * 6 * H; i += MT) sv_s[i] = P.save[i];
+  for (int i = tid; i < D1 * H; i += MT) w1m[i] = __ldg(P.W1 + (size_t)(i / H) * P.ldw1 + P.F + (i % H));
+  for (int i = tid; i < G4 * H; i += MT) whh[i] = __ldg(P.Whh + i);
+  __syncthreads();
+  // pass 1, thread = (month, unit): dhe_t = W1[:,F:]^T . da_t and the local derivatives
+  for (int i = tid; i < T * H; i += MT) {
+    const int t = i / H, j = i % H;
+    const float4* da4 = reinterpret_cast<const float4*>(P.dadc + (size_t)t * 72);
+    float v0 = 0.f, v1 = 0.f;
+#pragma unroll 4
+    for (int j4 = 0; j4 < D1 / 4; ++j4) {
+      const float4 d = __ldg(da4 + j4);
+      v0 = fmaf(w1m[(4 * j4) * H + j], d.x, v0);     v1 = fmaf(w1m[(4 * j4 + 1) * H + j], d.y, v1);
+      v0 = fmaf(w1m[(4 * j4 + 2) * H + j], d.z, v0); v1 = fmaf(w1m[(4 * j4 + 3) * H + j], d.w, v1);
+    }
+    const float* sv = sv_s + (size_t)t * 6 * H;
+    const float cc = sv[H + j], gi = sv[2 * H + j], gf = sv[3 * H + j], gg = sv[4 * H + j], go = sv[5 * H + j];
+    const float cprev = (t > 0) ? sv_s[(size_t)(t - 1) * 6 * H + H + j] : (P.c0 ? __ldg(P.c0 + j) : 0.f);
+    const float tc = tanh_fast(cc);
+    float* y = Y + (size_t)i * REC;
+    y[0] = go * (1.f - tc * tc);                     // a_c
+    y[1] = gf;
+    y[2] = v0 + v1;                                  // dhe
+    y[4] = gg * gi * (1.f - gi);                     // a_i
+    y[5] = cprev * gf * (1.f - gf);                  // a_f
+    y[6] = gi * (1.f - gg * gg);                     // a_g
+    y[7] = tc * go * (1.f - go);                     // a_o
+  }
+  __syncthreads();
+  // pass 2, thread = (month, unit k): column k of A_t and B_t
+  for (int i = tid; i < T * H; i += MT) {
+    const int t = i / H, k = i % H;
+    float* y = Y + (size_t)i * REC;
+#pragma unroll
+    for (int j = 0; j < HP; ++j) {
+      float a = 0.f, b = 0.f;
+      if (j < H) {
+        const float* yj = Y + ((size_t)t * H + j) * REC;
+        a = whh[(0 * H + j) * H + k] * yj[4] + whh[(1 * H + j) * H + k] * yj[5] + whh[(2 * H + j) * H + k] * yj[6];
+        b = whh[(3 * H + j) * H + k] * yj[7];
+      }
+      y[8 + j] = a;
+      y[8 + HP + j] = b;
+    }
+  }
+  __syncthreads();
+  // serial chain: lane k < H carries (dh_rec_k, dc_k); S[t] = dht | dcn overwrites the dead saved states
+  float* S = sv_s;
+  if (warp == 0) {
+    const int k = lane < H ? lane : 0;
+    float dh_rec = 0.f, dc = 0.f;
+    constexpr int R4 = REC / 4, NA = HP / 4;
+    const float4* y4 = reinterpret_cast<const float4*>(Y);
+    float4 c0, ca[NA], cb[NA];
+    auto fetch = [&](int t) {
+      const size_t o = ((size_t)t * H + k) * R4;
+      c0 = y4[o];
+#pragma unroll
+      for (int u = 0; u < NA; ++u) { ca[u] = y4[o + 2 + u]; cb[u] = y4[o + 2 + NA + u]; }
+    };
+    fetch(T - 1);
+    for (int t = T - 1; t >= 0; --t) {
+      const float4 q0 = c0;
+      float A[HP], B[HP];
+#pragma unroll
+      for (int u = 0; u < NA; ++u) {
+        A[4 * u] = ca[u].x; A[4 * u + 1] = ca[u].y; A[4 * u + 2] = ca[u].z; A[4 * u + 3] = ca[u].w;
+        B[4 * u] = cb[u].x; B[4 * u + 1] = cb[u].y; B[4 * u + 2] = cb[u].z; B[4 * u + 3] = cb[u].w;
+      }
+      if (t > 0) fetch(t - 1);
+      const float dht = q0.z + dh_rec;
+      const float dcn = fmaf(dht, q0.x, dc);
+      if (lane < H) { S[t * 2 * H + lane] = dht; S[t * 2 * H + H + lane] = dcn; }
+      float r0 = 0.f, r1 = 0.f;
+#pragma unroll
+      for (int j = 0; j < H; ++j) {
+        r0 = fmaf(A[j], __shfl_sync(0xffffffffu, dcn, j), r0);
+        r1 = fmaf(B[j], __shfl_sync(0xffffffffu, dht, j), r1);
+      }
+      dh_rec = r0 + r1;
+      dc = dcn * q0.y;
+    }
+  }
+  __syncthreads();
+  // gate gradients, thread = (month, unit)
+  for (int i = tid; i < T * H; i += MT) {
+    const int t = i / H, j = i % H;
+    const float dht = S[t * 2 * H + j], dcn = S[t * 2 * H + H + j];
+    const float* y = Y + (size_t)i * REC;
+    float* dp = P.dpre + (size_t)t * G4;
+    dp[j] = dcn * y[4]; dp[H + j] = dcn * y[5]; dp[2 * H + j] = dcn * y[6]; dp[3 * H + j] = dht * y[7];
+  }
+}
+
+// Month-summed gradients, one warp per output row ("task"), lanes striding over the months, fixed-tree warp
+// sums; eight tasks per CTA, the coefficients (dpre | dc_t) staged in shared memory once per CTA:
+//   task m < M           dW_ih[r][m] = sum_t dpre[t][r] macro[t][m]  (r < 4H) ; dWq[k][m] = sum_t dc_t[k] macro[t][m]
+//   task M + j, j < 64   dW1[j][F+k] = sum_t da_t[j] h_t[k] ; db1[j] = sum_t da_t[j]
+//   task M + 64 + r      dW_hh[r][k] = sum_t dpre[t][r] h_{t-1}[k] ; db_ih[r] = db_hh[r] = sum_t dpre[t][r]
+//   task M + 64 + 4H + q dbq[q] = sum_t dc_t[q]
+// dynamic smem: coef[T][NR + 1]   (NR = 4H + 8; the odd pitch keeps the month-strided reads conflict-free)
+__global__ void __launch_bounds__(256) macro_wgrad_kernel(const MacroParams P) {
+  extern __shared__ float sm[];
+  const int T = P.T, M = P.M, H = P.H, G4 = 4 * H, NR = G4 + KM, CP = NR + 1;
+  float* coef = sm;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  for (int i0 = tid; i0 < T * NR; i0 += 4 * 256) {         // four independent loads per thread and round
+    float v[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int i = min(i0 + u * 256, T * NR - 1), t = i / NR, r = i % NR;
+      v[u] = (r < G4) ? (P.have_sdf ? __ldcg(P.dpre + (size_t)t * G4 + r) : 0.f)
+                      : (P.have_mom ? __ldg(P.dadc + (size_t)t * 72 + 64 + (r - G4)) : 0.f);
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int i = i0 + u * 256;
+      if (i < T * NR) coef[(i / NR) * CP + i % NR] = v[u];
+    }
+  }
+  __syncthreads();
+  const int task = blockIdx.x * 8 + warp;
+  if (task < M) {
+    const int m = task;
+    float acc[4 * HMAX + KM];
+#pragma unroll
+    for (int r = 0; r < 4 * HMAX + KM; ++r) acc[r] = 0.f;
+    for (int t0 = lane; t0 < T; t0 += 4 * 32) {              // four months' loads in flight per lane
+      float v[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) v[u] = __ldg(P.macro + (size_t)min(t0 + 32 * u, T - 1) * M + m);
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int t = t0 + 32 * u;
+        if (t < T) {
+          const float* c = coef + t * CP;
+#pragma unroll
+          for (int r = 0; r < 4 * HMAX + KM; ++r)
+            if (r < NR) acc[r] = fmaf(c[r], v[u], acc[r]);
+        }
+      }
+    }
+#pragma unroll
+    for (int r = 0; r < 4 * HMAX + KM; ++r) {
+      if (r < NR) {
+        const float v = warp_sum(acc[r]);
+        if (lane == 0) {
+          if (r < G4) { if (P.have_sdf) P.gWih[(size_t)r * M + m] = v; }
+          else if (P.have_mom) P.gWq[(size_t)(r - G4) * P.ldwq + m] = v;
+        }
+      }
+    }
+  } else if (task < M + D1) {
+    if (!P.have_sdf) return;
+    const int j = task - M;
+    float a[HMAX], b = 0.f;
+#pragma unroll
+    for (int k = 0; k < HMAX; ++k) a[k] = 0.f;
+    for (int t = lane; t < T; t += 32) {
+      const float d = __ldg(P.dadc + (size_t)t * 72 + j);
+      b += d;
+#pragma unroll
+      for (int k = 0; k < HMAX; ++k)
+        if (k < H) a[k] = fmaf(d, __ldg(P.save + (size_t)t * 6 * H + k), a[k]);
+    }
+    b = warp_sum(b);
+#pragma unroll
+    for (int k = 0; k < HMAX; ++k) a[k] = warp_sum(a[k]);
+    if (lane == 0) {
+      P.gb1[j] = b;
+#pragma unroll
+      for (int k = 0; k < HMAX; ++k)
+        if (k < H) P.gW1[(size_t)j * P.ldw1 + P.F + k] = a[k];
+    }
+  } else if (task < M + D1 + G4) {
+    if (!P.have_sdf) return;
+    const int r = task - M - D1;
+    float a[HMAX], b = 0.f;
+#pragma unroll
+    for (int k = 0; k < HMAX; ++k) a[k] = 0.f;
+    for (int t = lane; t < T; t += 32) {
+      const float d = coef[t * CP + r];
+      b += d;
+#pragma unroll
+      for (int k = 0; k < HMAX; ++k)
+        if (k < H) {
+          const float hp = (t > 0) ? __ldg(P.save + (size_t)(t - 1) * 6 * H + k) : (P.h0 ? __ldg(P.h0 + k) : 0.f);
+          a[k] = fmaf(d, hp, a[k]);
+        }
+    }
+    b = warp_sum(b);
+#pragma unroll
+    for (int k = 0; k < HMAX; ++k) a[k] = warp_sum(a[k]);
+    if (lane == 0) {
+      P.gbih[r] = b; P.gbhh[r] = b;
+#pragma unroll
+      for (int k = 0; k < HMAX; ++k)
+        if (k < H) P.gWhh[r * H + k] = a[k];
+    }
+  } else if (task < M + D1 + G4 + KM) {
+    if (!P.have_mom) return;
+    const int q = task - M - D1 - G4;
+    float b = 0.f;
+    for (int t = lane; t < T; t += 32) b += coef[t * CP + G4 + q];
+    b = warp_sum(b);
+    if (lane == 0) P.gbq[q] = b;
+  }
+}
+
+size_t macro_fwd_smem(int T, int M, int H) {
+  return ((size_t)(4 * H + KM) * M + (size_t)T * 10 * H + (size_t)T * KM + ((T + 1) & ~1)) * 4 +
+         (size_t)((T + PUB - 1) / PUB) * 8;
+}
+size_t macro_bwd_smem(int T, int H) {
+  const int rec = 8 + 2 * ((H + 3) & ~3);
+  return ((size_t)T * 6 * H + (size_t)T * H * rec + (size_t)D1 * H + (size_t)4 * H * H) * 4;
+}
+
+template <int H>
+static cudaError_t launch_fwd_h(const MacroParams& P, size_t smem, cudaStream_t st) {
+  cudaError_t e = cudaFuncSetAttribute(macro_fwd_kernel<H>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return e;
+  macro_fwd_kernel<H><<<1, MT, smem, st>>>(P);
+  return cudaGetLastError();
+}
+template <int H>
+static cudaError_t launch_bptt_h(const MacroParams& P, size_t smem, cudaStream_t st) {
+  cudaError_t e = cudaFuncSetAttribute(macro_bptt_kernel<H>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return e;
+  macro_bptt_kernel<H><<<1, MT, smem, st>>>(P);
+  return cudaGetLastError();
+}
+#define DLAP_H_SWITCH(FN, ...)                       \
+  switch (P.H) {                                     \
+    case 1: return FN<1>(__VA_ARGS__);               \
+    case 2: return FN<2>(__VA_ARGS__);               \
+    case 3: return FN<3>(__VA_ARGS__);               \
+    case 4: return FN<4>(__VA_ARGS__);               \
+    case 5: return FN<5>(__VA_ARGS__);               \
+    case 6: return FN<6>(__VA_ARGS__);               \
+    case 7: return FN<7>(__VA_ARGS__);               \
+    case 8: return FN<8>(__VA_ARGS__);               \
+    default: return cudaErrorInvalidValue;           \
+  }
+
+cudaError_t launch_macro_fwd(const MacroParams& P, cudaStream_t st) {
+  const size_t smem = macro_fwd_smem(P.T, P.M, P.H);
+  DLAP_H_SWITCH(launch_fwd_h, P, smem, st)
+}
+static cudaError_t launch_bptt(const MacroParams& P, cudaStream_t st) {
+  const size_t smem = macro_bwd_smem(P.T, P.H);
+  DLAP_H_SWITCH(launch_bptt_h, P, smem, st)
+}
+cudaError_t launch_macro_bwd(const MacroParams& P, cudaStream_t st) {
+  if (P.have_sdf && P.H > 0) {
+    cudaError_t e = launch_bptt(P, st);
+    if (e != cudaSuccess) return e;
+  }
+  const int NR = 4 * P.H + KM;
+  const size_t smem = (size_t)P.T * (NR + 1) * 4;
+  cudaError_t e = cudaFuncSetAttribute(macro_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return e;
+  const int tasks = P.M + D1 + 4 * P.H + KM;
+  macro_wgrad_kernel<<<(tasks + 7) / 8, 256, smem, st>>>(P);
+  return cudaGetLastError();
+}
+
+// M = 0 (macro_features=None, src/model.py:247-257, :517-518): the per-month biases are just b1 / bq.
+__global__ void const_bias_kernel(const float* __restrict__ b1, const float* __restrict__ bq, int T,
+                                  float* __restrict__ a_t, float* __restrict__ c_t) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < T * D1) a_t[i] = __ldg(b1 + (i % D1));
+  if (i < T * KM) c_t[i] = __ldg(bq + (i % KM));
+}
+__global__ void set_months_kernel(int* months_ready, int T) { *months_ready = T; }
+
+static void fill_macro(MacroParams& P, const dlap_plan* plan, const float* macro, const dlap_tensors* p,
+                       const float* h0, const float* c0) {
+  P = MacroParams{};
+  P.macro = macro; P.T = plan->dims.T; P.M = plan->dims.M; P.H = plan->dims.M > 0 ? plan->dims.H : 0;
+  P.F = plan->dims.F;
+  P.Wih = p->w_ih; P.Whh = p->w_hh; P.bih = p->b_ih; P.bhh = p->b_hh;
+  P.W1 = p->w1; P.ldw1 = plan->ldw1; P.b1 = p->b1; P.Wq = p->wq; P.ldwq = plan->ldwq; P.bq = p->bq;
+  P.h0 = h0; P.c0 = c0;
+}
+
+cudaError_t launch_macro_fwd_c(const dlap_plan* plan, const float* macro, const dlap_tensors* p, const float* h0,
+                               const float* c0, float* save, float* a_t, float* c_t, float* hn, float* cn,
+                               float* xp, int* months_ready, cudaStream_t st) {
+  if (plan->dims.M == 0) {
+    const int n = plan->dims.T * D1;
+    const_bias_kernel<<<(n + 255) / 256, 256, 0, st>>>(p->b1, p->bq, plan->dims.T, a_t, c_t);
+    if (months_ready) set_months_kernel<<<1, 1, 0, st>>>(months_ready, plan->dims.T);
+    return cudaGetLastError();
+  }
+  MacroParams P;
+  fill_macro(P, plan, macro, p, h0, c0);
+  P.save = save; P.a_t = a_t; P.c_t = c_t; P.hn = hn; P.cn = cn; (void)xp; P.months_ready = months_ready;
+  return launch_macro_fwd(P, st);
+}
+
+cudaError_t launch_macro_bwd_c(const dlap_plan* plan, const float* macro, const dlap_tensors* p, const float* h0,
+                               const float* c0, const float* save, const float* dadc, float* dpre, int want_sdf,
+                               int want_mom, const dlap_tensors* g, cudaStream_t st) {
+  MacroParams P;
+  fill_macro(P, plan, macro, p, h0, c0);
+  P.save = const_cast<float*>(save); P.dadc = dadc; P.dpre = dpre;
+  P.have_sdf = want_sdf; P.have_mom = want_mom;
+  P.gWih = g->w_ih; P.gWhh = g->w_hh; P.gbih = g->b_ih; P.gbhh = g->b_hh;
+  P.gW1 = g->w1; P.gb1 = g->b1; P.gWq = g->wq; P.gbq = g->bq;
+  return launch_macro_bwd(P, st);
+}
+
+}  // namespace dlap

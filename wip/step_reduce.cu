@@ -1,0 +1,318 @@
+// Everything of the step that is a sum over stocks (per month) or over months (per stock), in ONE kernel whose
+// grid is co-resident and steps through its phases with grid-wide barriers:
+//   phase 0  per month:  N_t, mu_t, P_t, Rbar_t from u and R          src/model.py:276-278, :363-367
+//   phase 1  N_bar, pr_t, S_t, Sharpe (CTA 0 writes them; every CTA recomputes the S_t it needs);
+//            per stock over the months of one chunk: sum_t q_k R S_t, sum_t R m S_t, sum_t m     :376, :382, :428
+//            and, fused, the demeaned weights w = m (u - mu_t)                                     :271-279
+//   phase 2  the month chunks summed into chunk 0 (all CTAs; with month shards this is what gets all-reduced)
+//   phase 3  per stock: e_ki = colsum / T_i, per-block partial sums of e^2, and the UNIT loss coefficients
+//            Gc_ki = 2 e_ki / (K N T_i), Gu_i = 2 e0_i / (N T_i)        :382-385, :428-431, autograd of them
+//   phase 4  L_c, L_u; per month the two sums the backward pass needs:
+//            dSc_t = sum_i R sum_k Gc_ki q_kti,  dSu_t = sum_i Gu_i R m   (dL/dS_t = g_c dSc_t + g_u dSu_t)
+// A launch runs a contiguous set of phases (a month-sharded step exchanges the per-stock sums between 2 and 3).
+// Replaces six launches of round 1 (row_sum, row_finish, col_partial, loss_finish, coeff, ds_rows).
+// Every cross-CTA sum has a fixed order (no float atomics): results are reproducible run to run.
+// Data written in one phase and read in a later one is read with ld.cg / ld.acquire, never through the
+// read-only (nc) path.
+#include "../../include/dlap.h"
+#include "dlap_common.cuh"
+#include "cell_f32.cuh"
+
+namespace dlap {
+
+struct ReduceParams {
+  const float* u;            // packed (index != null) or dense [T,N]
+  const float* q;            // [8] planes like u: tanh outputs of the moment net, or null
+  const float* R;            // [T,N]
+  const uint8_t* mask;       // [T,N]
+  const int* index;          // valid-cell index or null (dense u, q)
+  int T, N;
+  int weighted;
+  const float* n_bar_in;     // month shards: the series' N_bar; else null
+  int n_total;               // stocks in the loss means
+  float* row_stats;          // [T,RS_W]
+  float* pr;                 // [T]
+  float* scalars;            // [SC_W]
+  float* w_out;              // [T,N] or null
+  double* col_part;          // [nsplit,10,N]
+  int nsplit, tchunk;        // month chunks of phase 1; phase 2 sums them into chunk 0, which phase 3 reads
+  float* e; float* t_i; float* G;      // [9,N], [N], [9,N]
+  double* loss_part;         // [ceil(N/64), 2]
+  double* dS2;               // [T,2] or null (no backward pass will follow)
+  unsigned int* bar;         // grid barrier word, zero between launches
+  int phase_lo, phase_hi;    // inclusive
+};
+
+namespace {
+constexpr int RT = 256;
+
+__device__ __forceinline__ float S_of(const float* rs, int weighted, float n_bar, float* pr_out) {
+  const float P = __ldcg(rs + RS_P), nt = __ldcg(rs + RS_NT);
+  const float pr = weighted ? (float)((double)P / (double)nt * (double)n_bar) : P;
+  if (pr_out) *pr_out = pr;
+  return 1.f + pr;
+}
+
+// four doubles summed over the CTA in a fixed tree; result in every thread (two barriers)
+__device__ __forceinline__ void block_sum4(double (&v)[4], double* red /* [4][8] */) {
+  const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+#pragma unroll
+  for (int k = 0; k < 4; ++k) v[k] = warp_sum(v[k]);
+  __syncthreads();
+  if (l == 0) {
+#pragma unroll
+    for (int k = 0; k < 4; ++k) red[k * 8 + w] = v[k];
+  }
+  __syncthreads();
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    double s = 0.0;
+#pragma unroll
+    for (int i = 0; i < RT / 32; ++i) s += red[k * 8 + i];
+    v[k] = s;
+  }
+}
+}  // namespace
+
+__global__ void __launch_bounds__(RT, 4) step_reduce_kernel(const ReduceParams P) {
+  extern __shared__ float sm[];            // phase 1: S_t then mu_t of this CTA's month chunk
+  __shared__ double red[32];
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int T = P.T, N = P.N;
+  const size_t plane = (size_t)T * N;
+  unsigned int nsync = 0;
+
+  // ---------------------------------------------------------------- phase 0: row sums
+  if (P.phase_lo <= 0 && P.phase_hi >= 0) {
+    for (int t = blockIdx.x; t < T; t += gridDim.x) {
+      double v[4] = {0.0, 0.0, 0.0, 0.0};          // count, sum u, sum u R, sum R
+      const size_t base = (size_t)t * N;
+      if (P.index) {
+        const int cnt = __ldg(P.index + idx_off_cnt(T) + t);
+        const int* vrow = P.index + idx_off_vidx(T) + base;
+        for (int j = tid; j < cnt; j += RT) {
+          const float uv = __ldcg(P.u + base + j), r = __ldg(P.R + base + __ldg(vrow + j));
+          v[1] += (double)uv; v[2] += (double)uv * (double)r; v[3] += (double)r;
+        }
+        v[0] = tid == 0 ? (double)cnt : 0.0;
+      } else {
+        for (int i = tid; i < N; i += RT) {
+          if (P.mask[base + i]) {
+            const float uv = __ldcg(P.u + base + i), r = __ldg(P.R + base + i);
+            v[0] += 1.0; v[1] += (double)uv; v[2] += (double)uv * (double)r; v[3] += (double)r;
+          }
+        }
+      }
+      block_sum4(v, red);
+      if (tid == 0) {
+        const double nt = fmax(v[0], 1.0);
+        const float mu = (float)(v[1] / nt);
+        float* rs = P.row_stats + (size_t)t * RS_W;
+        rs[RS_NT] = (float)nt;
+        rs[RS_MU] = mu;
+        rs[RS_P] = (float)(v[2] - (double)mu * v[3]);
+        rs[RS_RBAR] = (float)(v[3] / nt);
+      }
+    }
+    if (P.phase_hi >= 1) grid_sync(P.bar, ++nsync);
+  }
+
+  // ---------------------------------------------------------------- phase 1: N_bar, S_t; column partial sums
+  if (P.phase_lo <= 1 && P.phase_hi >= 1) {
+    double nsum = 0.0;
+    for (int t = tid; t < T; t += RT) nsum += (double)__ldcg(P.row_stats + (size_t)t * RS_W + RS_NT);
+    nsum = block_sum(nsum, red);
+    const float n_bar = P.n_bar_in ? __ldg(P.n_bar_in) : (float)(nsum / (double)T);
+    if (blockIdx.x == 0) {               // pr_t, S_t, Sharpe (src/model.py:360, :367, :380, :551)
+      double s1 = 0.0;
+      for (int t = tid; t < T; t += RT) {
+        float* rs = P.row_stats + (size_t)t * RS_W;
+        float pr;
+        const float S = S_of(rs, P.weighted, n_bar, &pr);
+        rs[RS_PR] = pr; rs[RS_S] = S;
+        P.pr[t] = pr;
+        s1 += (double)pr;
+      }
+      s1 = block_sum(s1, red);
+      const double mean = s1 / (double)T;
+      double s2 = 0.0;
+      for (int t = tid; t < T; t += RT) {
+        float pr;
+        S_of(P.row_stats + (size_t)t * RS_W, P.weighted, n_bar, &pr);
+        const double d = (double)pr - mean;
+        s2 += d * d;
+      }
+      s2 = block_sum(s2, red);
+      if (tid == 0) {
+        P.scalars[SC_NBAR] = n_bar;
+        P.scalars[SC_SHARPE] = (T > 1) ? (float)(mean / (sqrt(s2 / (double)(T - 1)) + 1e-8)) : nanf("");
+      }
+    }
+    const int nb = (N + RT - 1) / RT, nw = (N + 31) >> 5;
+    const int tchunk = P.tchunk;
+    for (int unit = blockIdx.x; unit < nb * P.nsplit; unit += gridDim.x) {
+      const int bx = unit % nb, by = unit / nb;
+      const int t0 = by * tchunk, t1 = min(T, t0 + tchunk);
+      __syncthreads();
+      for (int t = t0 + tid; t < t1; t += RT) {
+        const float* rs = P.row_stats + (size_t)t * RS_W;
+        sm[t - t0] = S_of(rs, P.weighted, n_bar, nullptr);
+        sm[tchunk + t - t0] = __ldcg(rs + RS_MU);
+      }
+      __syncthreads();
+      const int i = bx * RT + tid;
+      const bool in = i < N;                   // whole warps stay: the packed position comes from a ballot
+      const int* rank = P.index ? P.index + idx_off_rank(T, N) + (i >> 5) : nullptr;
+      double acc[KM + 2];
+#pragma unroll
+      for (int k = 0; k < KM + 2; ++k) acc[k] = 0.0;
+      // latency-bound (two dependent round trips per month: mask, then values): branch-free body, masked lanes
+      // load from a clamped in-bounds position and drop the values, the unrolled months overlap their loads
+      const size_t ic = in ? (size_t)i : (size_t)N - 1;
+#pragma unroll 4
+      for (int t = t0; t < t1; ++t) {
+        const size_t gi = (size_t)t * N + ic;
+        const float S = sm[t - t0];
+        const bool live = in && P.mask[gi] != 0;
+        const unsigned b = __ballot_sync(0xffffffffu, live);
+        size_t vi = gi;
+        if (P.index) vi = (size_t)t * N + __ldg(rank + (size_t)t * nw) + __popc(b & ((1u << lane) - 1u));
+        if (vi >= plane) vi = plane - 1;       // a masked lane behind the last listed stock of the last month
+        const float uv = P.w_out ? __ldcg(P.u + vi) : 0.f;
+        const float r = __ldg(P.R + gi);
+        float qv[KM];
+#pragma unroll
+        for (int k = 0; k < KM; ++k) qv[k] = P.q ? __ldcg(P.q + k * plane + vi) : 0.f;
+        if (P.w_out && in) P.w_out[gi] = live ? (uv - sm[tchunk + t - t0]) : 0.f;
+        acc[KM] += live ? (double)(r * S) : 0.0;
+        acc[KM + 1] += live ? 1.0 : 0.0;
+#pragma unroll
+        for (int k = 0; k < KM; ++k) acc[k] += live ? (double)((qv[k] * r) * S) : 0.0;
+      }
+      if (in) {
+        double* out = P.col_part + (size_t)by * (KM + 2) * N + i;
+#pragma unroll
+        for (int k = 0; k < KM + 2; ++k) out[(size_t)k * N] = acc[k];
+      }
+    }
+    if (P.phase_hi >= 2) grid_sync(P.bar, ++nsync);
+  }
+
+  // ---------------------------------------------------------------- phase 2: month chunks -> chunk 0
+  if (P.phase_lo <= 2 && P.phase_hi >= 2 && P.nsplit > 1) {
+    const size_t n10 = (size_t)(KM + 2) * N;
+    for (size_t idx = (size_t)blockIdx.x * RT + tid; idx < n10; idx += (size_t)gridDim.x * RT) {
+      double s = __ldcg(P.col_part + idx);
+      for (int sp = 1; sp < P.nsplit; ++sp) s += __ldcg(P.col_part + (size_t)sp * n10 + idx);
+      P.col_part[idx] = s;
+    }
+  }
+  if (P.phase_lo <= 2 && P.phase_hi >= 3 && P.nsplit > 1) grid_sync(P.bar, ++nsync);
+
+  // ---------------------------------------------------------------- phase 3: e, T_i, unit coefficients, sum e^2
+  if (P.phase_lo <= 3 && P.phase_hi >= 3) {
+    const int nblk = (N + RT - 1) / RT;
+    for (int blk = blockIdx.x; blk < nblk; blk += gridDim.x) {
+      const int i = blk * RT + tid;
+      double sc = 0.0, su = 0.0;
+      if (i < N) {
+        double v[KM + 2];
+#pragma unroll
+        for (int k = 0; k < KM + 2; ++k) v[k] = __ldcg(P.col_part + (size_t)k * N + i);
+        const double ti = fmax(v[KM + 1], 1.0);
+        const float tif = (float)ti;
+        P.t_i[i] = tif;
+        const float inv = 1.f / ((float)P.n_total * tif);
+#pragma unroll
+        for (int k = 0; k <= KM; ++k) {
+          const float e = (float)(v[k] / ti);
+          P.e[(size_t)k * N + i] = e;
+          // autograd of mean_k mean_i e^2 and of mean_i e0^2 for a unit cotangent
+          P.G[(size_t)k * N + i] = k < KM ? ((2.f / KM) * e) * inv : (2.f * e) * inv;
+          if (k < KM) sc += (double)e * (double)e; else su += (double)e * (double)e;
+        }
+      }
+      __syncthreads();
+      sc = block_sum(sc, red);
+      su = block_sum(su, red);
+      if (tid == 0) { P.loss_part[2 * blk] = sc; P.loss_part[2 * blk + 1] = su; }
+    }
+    if (P.phase_hi >= 4) grid_sync(P.bar, ++nsync);
+  }
+
+  // ---------------------------------------------------------------- phase 4: losses; per-month dS sums
+  if (P.phase_lo <= 4 && P.phase_hi >= 4) {
+    if (blockIdx.x == gridDim.x - 1) {
+      const int nblk = (N + RT - 1) / RT;
+      double a = 0.0, b = 0.0;
+      for (int j = tid; j < nblk; j += RT) { a += __ldcg(P.loss_part + 2 * j); b += __ldcg(P.loss_part + 2 * j + 1); }
+      __syncthreads();
+      a = block_sum(a, red);
+      b = block_sum(b, red);
+      if (tid == 0) {
+        // means run over ALL columns, dead ones included (src/model.py:385)
+        P.scalars[SC_LC] = (float)(a / ((double)KM * (double)P.n_total));
+        P.scalars[SC_LU] = (float)(b / (double)P.n_total);
+      }
+    }
+    if (P.dS2) {
+      for (int t = blockIdx.x; t < T; t += gridDim.x) {
+        const size_t base = (size_t)t * N;
+        double v[4] = {0.0, 0.0, 0.0, 0.0};
+        auto cell = [&](int i, size_t vi) {
+          const float r = __ldg(P.R + base + i);
+          float c = 0.f;
+          if (P.q) {
+#pragma unroll
+            for (int k = 0; k < KM; ++k) c = fmaf(__ldcg(P.G + (size_t)k * N + i), __ldcg(P.q + k * plane + vi) * r, c);
+          }
+          v[0] += (double)c;
+          v[1] += (double)(__ldcg(P.G + (size_t)KM * N + i) * r);
+        };
+        if (P.index) {
+          const int cnt = __ldg(P.index + idx_off_cnt(T) + t);
+          const int* vrow = P.index + idx_off_vidx(T) + base;
+          for (int j = tid; j < cnt; j += RT) cell(__ldg(vrow + j), base + j);
+        } else {
+          for (int i = tid; i < N; i += RT)
+            if (P.mask[base + i]) cell(i, base + i);
+        }
+        block_sum4(v, red);
+        if (tid == 0) { P.dS2[2 * t] = v[0]; P.dS2[2 * t + 1] = v[1]; }
+      }
+    }
+  }
+  grid_exit(P.bar, nsync);
+}
+
+// co-resident CTAs of the kernel on `device` with `sms` SMs in use and this much dynamic shared memory
+static int reduce_ctas_per_sm(size_t smem) {
+  int per_sm = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, step_reduce_kernel, RT, smem) != cudaSuccess) per_sm = 0;
+  return per_sm;
+}
+
+cudaError_t launch_step_reduce(ReduceParams P, int sms, bool cooperative, cudaStream_t st) {
+  const size_t smem = 2 * (size_t)P.tchunk * sizeof(float);
+  if (smem > 48 * 1024) {
+    cudaError_t e = cudaFuncSetAttribute(step_reduce_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+  }
+  int per_sm = reduce_ctas_per_sm(smem);
+  if (per_sm < 1) return cudaErrorLaunchOutOfResources;
+  if (per_sm > 4) per_sm = 4;
+  // no more CTAs than any phase has work for
+  const int nb = (P.N + RT - 1) / RT;
+  int want = nb * P.nsplit;
+  if (want < P.T) want = P.T;
+  int grid = per_sm * sms;
+  if (grid > want) grid = want;
+  if (grid < 1) grid = 1;
+  void* args[] = {(void*)&P};
+  if (cooperative)
+    return cudaLaunchCooperativeKernel((const void*)step_reduce_kernel, dim3(grid), dim3(RT), args, smem, st);
+  step_reduce_kernel<<<grid, RT, smem, st>>>(P);
+  return cudaGetLastError();
+}
+
+}  // namespace dlap
