@@ -17,8 +17,8 @@ ROOT = os.path.dirname(PKG_DIR)
 CSRC = os.path.join(PKG_DIR, "csrc")
 LIB_PATH = os.path.join(PKG_DIR, "libdlap_b200.so")
 OBJ_DIR = os.path.join(PKG_DIR, "build")          # objects: git- and gpurun-ignored
-SOURCES = ("capi.cu", "cell_fwd.cu", "cell_bwd.cu", "reduce.cu", "macro_lstm.cu", "tc_selftest.cu", "cell_fwd_tc.cu", "cell_bwd_tc.cu",
-           "panel_index.cu")
+SOURCES = ("capi.cu", "cell_fwd.cu", "cell_bwd.cu", "reduce.cu", "step_reduce.cu", "macro_lstm.cu", "tc_selftest.cu",
+           "cell_fwd_tc.cu", "cell_bwd_tc.cu", "panel_index.cu")
 NVCC_FLAGS = ("-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-shared", "-Xcompiler", "-fPIC")
 
@@ -32,10 +32,9 @@ class DlapDims(C.Structure):
 
 
 class DlapPlan(C.Structure):
-    _fields_ = [("dims", DlapDims), ("tpm", C.c_int32), ("grid_cell", C.c_int32),
-                ("col_splits", C.c_int32), ("row_splits", C.c_int32), ("ldw1", C.c_int32),
-                ("ldwq", C.c_int32), ("row_part_bytes", C.c_int64), ("col_part_bytes", C.c_int64),
-                ("loss_part_bytes", C.c_int64), ("ds_part_bytes", C.c_int64),
+    _fields_ = [("dims", DlapDims), ("tpm", C.c_int32), ("sms", C.c_int32), ("grid_cell", C.c_int32),
+                ("cooperative", C.c_int32), ("col_splits", C.c_int32), ("ldw1", C.c_int32), ("ldwq", C.c_int32),
+                ("col_part_bytes", C.c_int64), ("loss_part_bytes", C.c_int64),
                 ("wpart_bytes", C.c_int64), ("dadc_part_bytes", C.c_int64),
                 ("lstm_save_bytes", C.c_int64), ("dpre_bytes", C.c_int64), ("index_bytes", C.c_int64)]
 
@@ -46,7 +45,15 @@ class DlapTensors(C.Structure):
     _fields_ = [(n, C.c_void_p) for n in FIELDS]
 
 
+class DlapMacroIO(C.Structure):
+    """dlap_macro_io: the macro side of a per-cell call (include/dlap.h)."""
+    _fields_ = [("macro", C.c_void_p), ("series_T", C.c_int32), ("month0", C.c_int32), ("month_stride", C.c_int32),
+                ("h0", C.c_void_p), ("c0", C.c_void_p), ("lstm_save", C.c_void_p), ("a_t", C.c_void_p),
+                ("c_t", C.c_void_p), ("hn", C.c_void_p), ("cn", C.c_void_p), ("sync", C.c_void_p)]
+
+
 _P = C.c_void_p
+_MIO = C.POINTER(DlapMacroIO)
 _PLAN = C.POINTER(DlapPlan)
 _TENS = C.POINTER(DlapTensors)
 _I = C.c_int
@@ -54,21 +61,18 @@ _I = C.c_int
 # name -> argtypes; every function returns int status (except the two introspection calls)
 SIGNATURES = {
     "dlap_make_plan": (C.POINTER(DlapDims), _I, _PLAN),
-    "dlap_macro_fwd": (_PLAN, _P, _TENS, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P),
+    "dlap_macro_fwd": (_PLAN, _P, _TENS, _P, _P, _P, _P, _P, _P, _P, _P),
     "dlap_panel_index": (_PLAN, _P, _P, _P),
     "dlap_panel_pull": (_PLAN, _P, _P, _P, _I, _I, _P),
-    "dlap_cell_fwd": (_PLAN, _P, _P, _P, _P, _TENS, _P, _P, _P, _P, _P, _I, C.c_float, C.c_uint64, _P, _P, _I, _I, _P),
-    "dlap_row_finish": (_PLAN, _P, _P, _I, _I, _P, _P, _P, _P, _P),
-    "dlap_col_partial": (_PLAN, _P, _P, _P, _P, _P, _P, _P, _P, _P),
+    "dlap_cell_fwd": (_PLAN, _P, _P, _P, _TENS, _MIO, _P, _P, _I, C.c_float, C.c_uint64, _P, _P),
+    "dlap_step_reduce": (_PLAN, _P, _P, _P, _P, _P, _I, _P, _I, _I, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P),
     "dlap_loss_finish": (_PLAN, _P, _I, _P, _P, _P, _P, _P, _P),
     "dlap_loss_finish_noalloc": (_PLAN, _P, _I, _P, _P, _P, _P),
-    "dlap_loss_coeff": (_PLAN, _P, _P, _P, _P, _P, _P),
-    "dlap_ds_rows": (_PLAN, _P, _P, _P, _P, _P, _P, _P),
-    "dlap_cell_bwd": (_PLAN, _P, _P, _P, _P, _TENS, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _P, _P, _I,
+    "dlap_cell_bwd": (_PLAN, _P, _P, _P, _P, _TENS, _MIO, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _P, _P, _I,
                       C.c_float, C.c_uint64, _P, _P),
-    "dlap_grad_finish": (_PLAN, _P, _P, _P, _I, _I, _I, _TENS, _P, _P),
-    "dlap_macro_bwd": (_PLAN, _P, _TENS, _P, _P, _P, _P, _P, _I, _I, _TENS, _P),
-    "dlap_weights": (_PLAN, _P, _P, _P, _P, _I, _P, _P),
+    "dlap_grad_finish": (_PLAN, _P, _P, _P, _I, _I, _I, _TENS, _P, _I, _P),
+    "dlap_macro_bwd": (_PLAN, _P, _TENS, _P, _P, _P, _P, _P, _I, _I, _TENS, _P, _P, _P, _I, _P),
+    "dlap_weights": (_PLAN, _P, _P, _P, _I, _P, _P),
     "dlap_debug_timeline": (_P,),
     "dlap_umma_selftest": (_P, _I, _P, _I, _I, _I, _I, _I, _I, _I, _I, _I, _I, _I, _I, _P, _P),
     "dlap_umma_ts_selftest": (_P, _P, _I, _I, _I, _I, _I, _I, _I, _I, _P, _P, _P),

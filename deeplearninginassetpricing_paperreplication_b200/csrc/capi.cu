@@ -2,37 +2,32 @@
 // kernel launches only.  No allocation, no synchronisation, no torch types.
 #include "../../include/dlap.h"
 #include "cell_f32.cuh"
+#include "grad_finish.cuh"
+#include "macro_role.cuh"
 
 namespace dlap {
 // launchers implemented next to their kernels
-struct MacroParams;
 cudaError_t launch_cell_fwd_f32(const CellParams& P, int grid, cudaStream_t st);
 cudaError_t launch_cell_bwd_f32(const CellParams& P, int grid, bool sdf, bool mom, cudaStream_t st);
-cudaError_t launch_cell_fwd_tc(const CellParams& P, int grid, cudaStream_t st);
+cudaError_t launch_cell_fwd_tc(const CellParams& P, const MacroParams* MP, int grid, bool cooperative, cudaStream_t st);
 cudaError_t launch_cell_bwd_tc(const CellParams& P, int grid, bool sdf, bool mom, cudaStream_t st);
 size_t smem_bwd_bytes(int F);
-cudaError_t launch_row_finish(const double*, int, int, const int*, int, const float*, float*, float*, float*,
-                              cudaStream_t);
 cudaError_t launch_panel_index(const uint8_t* mask, int T, int N, int* index, cudaStream_t st);
 cudaError_t launch_panel_pull(const float* x_host, const int* index, int T, int N, int F, float* x_dev, int sms, bool clear,
                               cudaStream_t st);
-cudaError_t launch_col_partial(const float*, const float*, const uint8_t*, const float*, const float*, const int*,
-                               int, int, int, double*, float*, cudaStream_t);
+cudaError_t launch_step_reduce_c(const dlap_plan* plan, const float* u, const float* q, const float* R, const uint8_t* mask,
+                                 const int* index, int weighted, const float* n_bar_in, int phase_lo, int phase_hi,
+                                 float* row_stats, float* pr, float* scalars, float* w_out, double* col_part, float* e,
+                                 float* t_i, float* G, double* loss_part, double* dS2, unsigned int* bar, cudaStream_t st);
 cudaError_t launch_loss_finish(const double*, int, int, int, float*, float*, double*, unsigned int*, float*,
                                cudaStream_t);
-cudaError_t launch_coeff(const float*, const float*, int, const float*, const float*, float*, cudaStream_t);
-cudaError_t launch_ds_rows(const float*, const float*, const uint8_t*, const float*, const int*, int, int, int,
-                           double*, cudaStream_t);
-cudaError_t launch_grad_finish(const float*, int, int, int, int, const float*, int, int, const int*, float*, int,
-                               float*, float*, float*, float*, float*, int, int, float*, cudaStream_t);
-cudaError_t launch_weights(const float*, const uint8_t*, const float*, const int*, int, int, int, float*,
-                           cudaStream_t);
-cudaError_t launch_macro_fwd_c(const dlap_plan* plan, const float* macro, const dlap_tensors* p, const float* h0,
-                               const float* c0, float* save, float* a_t, float* c_t, float* hn, float* cn,
-                               float* xp, int* months_ready, cudaStream_t st);
-cudaError_t launch_macro_bwd_c(const dlap_plan* plan, const float* macro, const dlap_tensors* p, const float* h0,
-                               const float* c0, const float* save, const float* dadc, float* dpre, int want_sdf,
-                               int want_mom, const dlap_tensors* g, cudaStream_t st);
+cudaError_t launch_grad_finish(const FinishParams& P, cudaStream_t st);
+cudaError_t launch_weights(const float*, const uint8_t*, const int*, int, int, int, float*, cudaStream_t);
+void fill_macro(MacroParams& P, const dlap_plan* plan, int T, const float* macro, const dlap_tensors* p, const float* h0,
+                const float* c0);
+cudaError_t launch_macro_fwd(const MacroParams& P, cudaStream_t st);
+cudaError_t launch_macro_bwd(const MacroParams& P, const FinishParams& FIN, cudaStream_t st);
+cudaError_t launch_const_bias(const dlap_tensors* p, int T, float* a_t, float* c_t, cudaStream_t st);
 size_t macro_fwd_smem(int T, int M, int H);
 void set_bwd_tc_timeline(long long* p);
 void set_fwd_tc_timeline(long long* p);
@@ -56,7 +51,8 @@ static int check_plan(const dlap_plan* p) {
   REQ(p);
   int rc = check_dims(p->dims);
   if (rc) return rc;
-  if (p->tpm != (p->dims.N + TILE - 1) / TILE || p->grid_cell < 1 || p->col_splits < 1 || p->row_splits < 1)
+  if (p->tpm != (p->dims.N + TILE - 1) / TILE || p->grid_cell < 1 || p->sms < 1 || p->grid_cell > p->sms ||
+      p->col_splits < 1 || p->col_splits > p->dims.T)
     return DLAP_E_PLAN;
   return DLAP_OK;
 }
@@ -105,21 +101,19 @@ int dlap_make_plan(const dlap_dims* dims, int device, dlap_plan* out) {
   const int T = dims->T, N = dims->N, F = dims->F;
   p.tpm = (N + TILE - 1) / TILE;
   const long long ntiles = (long long)T * p.tpm;
+  p.sms = sms;
   p.grid_cell = (int)(ntiles < sms ? ntiles : sms);
+  p.cooperative = 1;
   // reductions: aim for ~4 CTAs per SM.  col_partial holds exactly four CTAs of 256 threads per SM (64 registers),
   // so its grid must not exceed 4 * sms: a few CTAs more would run as a second wave on an otherwise idle GPU and
   // double the kernel (round down, not up)
   const int nb = (N + 255) / 256, want = 4 * sms;
   int cs = want / nb; if (cs > T) cs = T; if (cs < 1) cs = 1;
   p.col_splits = cs;
-  int rs = (want + T - 1) / T; if (rs > nb) rs = nb; if (rs < 1) rs = 1;
-  p.row_splits = rs;
   p.ldw1 = F + (dims->M > 0 ? dims->H : 0);
   p.ldwq = dims->M + F;
-  p.row_part_bytes = (int64_t)T * p.tpm * 4 * 4 * 8;
   p.col_part_bytes = (int64_t)p.col_splits * (KM + 2) * N * 8;
   p.loss_part_bytes = (int64_t)((N + 63) / 64) * 2 * 8;
-  p.ds_part_bytes = (int64_t)T * p.row_splits * 8;
   p.wpart_bytes = (int64_t)p.grid_cell * wp_stride(round4(F)) * 4;
   p.dadc_part_bytes = (int64_t)T * (p.tpm > 4 ? p.tpm : 4) * 72 * 4;
   p.index_bytes = (int64_t)idx_ints(T, N) * 4;
@@ -129,8 +123,8 @@ int dlap_make_plan(const dlap_dims* dims, int device, dlap_plan* out) {
   return DLAP_OK;
 }
 
-static void fill_cell(CellParams& P, const dlap_plan* plan, const float* x, const float* R, const uint8_t* mask,
-                      const dlap_tensors* w, const float* a_t, const float* c_t) {
+static int fill_cell(CellParams& P, const dlap_plan* plan, const float* x, const float* R, const uint8_t* mask,
+                     const dlap_tensors* w, const dlap_macro_io* mio) {
   const dlap_dims& d = plan->dims;
   P = CellParams{};
   P.x = x; P.R = R; P.mask = mask;
@@ -138,9 +132,16 @@ static void fill_cell(CellParams& P, const dlap_plan* plan, const float* x, cons
   P.x_bytes = (long long)d.T * d.N * d.F * 4;
   P.W1 = w->w1; P.ldw1 = plan->ldw1; P.W2 = w->w2; P.b2 = w->b2; P.W3 = w->w3; P.b3 = w->b3;
   P.Wq = w->wq; P.ldwq = plan->ldwq; P.wq_off = d.M;
-  P.a_t = a_t; P.c_t = c_t;
-  P.months_stride = 1;
+  // month t of the panel is month month0 + t * month_stride of the series the tables run over
+  const int stride = mio->month_stride > 0 ? mio->month_stride : 1;
+  const int series = mio->series_T > 0 ? mio->series_T : d.T;
+  if (mio->month0 < 0 || (long long)mio->month0 + (long long)(d.T - 1) * stride >= series) return DLAP_E_SHAPE;
+  P.a_t = mio->a_t + (size_t)mio->month0 * D1;
+  P.c_t = mio->c_t ? mio->c_t + (size_t)mio->month0 * KM : nullptr;
+  P.months_base = mio->month0;
+  P.months_stride = stride;
   P.tpm = plan->tpm;
+  return DLAP_OK;
 }
 
 static int set_dropout(CellParams& P, float p, uint64_t seed, const uint64_t* seed_dev) {
@@ -156,18 +157,20 @@ static int set_dropout(CellParams& P, float p, uint64_t seed, const uint64_t* se
 }
 
 int dlap_macro_fwd(const dlap_plan* plan, const float* macro, const dlap_tensors* params, const float* h0,
-                   const float* c0, float* lstm_save, float* a_t, float* c_t, float* hn, float* cn,
-                   float* xproj_scratch, int32_t* months_ready, void* stream) {
+                   const float* c0, float* lstm_save, float* a_t, float* c_t, float* hn, float* cn, void* stream) {
   int rc = check_plan(plan);
   if (rc) return rc;
   REQ(params); REQ(a_t); REQ(c_t); REQ(params->b1); REQ(params->bq);
-  if (plan->dims.M > 0) {
-    REQ(macro); REQ(lstm_save); REQ(hn); REQ(cn);
-    REQ(params->w_ih); REQ(params->w_hh); REQ(params->b_ih); REQ(params->b_hh); REQ(params->w1); REQ(params->wq);
+  if (plan->dims.M == 0) {
+    CU(launch_const_bias(params, plan->dims.T, a_t, c_t, (cudaStream_t)stream));
+    return DLAP_OK;
   }
-  if (reinterpret_cast<uintptr_t>(months_ready) & 3) return DLAP_E_ALIGN;
-  CU(launch_macro_fwd_c(plan, macro, params, h0, c0, lstm_save, a_t, c_t, hn, cn, xproj_scratch, months_ready,
-                        (cudaStream_t)stream));
+  REQ(macro); REQ(lstm_save); REQ(hn); REQ(cn);
+  REQ(params->w_ih); REQ(params->w_hh); REQ(params->b_ih); REQ(params->b_hh); REQ(params->w1); REQ(params->wq);
+  MacroParams P;
+  fill_macro(P, plan, plan->dims.T, macro, params, h0, c0);
+  P.save = lstm_save; P.a_t = a_t; P.c_t = c_t; P.hn = hn; P.cn = cn;
+  CU(launch_macro_fwd(P, (cudaStream_t)stream));
   return DLAP_OK;
 }
 
@@ -192,78 +195,82 @@ int dlap_panel_pull(const dlap_plan* plan, const float* x_host, const int32_t* i
   return DLAP_OK;
 }
 
-int dlap_cell_fwd(const dlap_plan* plan, const float* x, const float* R, const uint8_t* mask, const int32_t* index,
-                  const dlap_tensors* params, const float* a_t, const float* c_t, float* u, float* g,
-                  double* row_part, int precision, float dropout_p, uint64_t dropout_seed,
-                  const uint64_t* dropout_seed_dev, const int32_t* months_ready, int months_base, int months_stride,
-                  void* stream) {
+int dlap_cell_fwd(const dlap_plan* plan, const float* x, const uint8_t* mask, const int32_t* index,
+                  const dlap_tensors* params, const dlap_macro_io* mio, float* u, float* q, int precision,
+                  float dropout_p, uint64_t dropout_seed, const uint64_t* dropout_seed_dev, void* stream) {
   int rc = check_plan(plan);
   if (rc) return rc;
-  REQ(x); REQ(mask); REQ(params); REQ(a_t); REQ(u); REQ(row_part);
-  if (months_ready && precision != DLAP_PREC_BF16X3) return DLAP_E_PRECISION;   // only the tensor-core kernel waits
-  if (months_ready && months_base < 0) return DLAP_E_SHAPE;
-  if (months_stride < 1) return DLAP_E_SHAPE;
-  if (months_stride != 1 && precision != DLAP_PREC_BF16X3) return DLAP_E_PRECISION;
-  if (reinterpret_cast<uintptr_t>(months_ready) & 3) return DLAP_E_ALIGN;
+  REQ(x); REQ(mask); REQ(params); REQ(mio); REQ(mio->a_t); REQ(u);
   REQ(params->w1); REQ(params->w2); REQ(params->b2); REQ(params->w3); REQ(params->b3);
-  if (g) { REQ(c_t); REQ(params->wq); }
+  if (q) { REQ(mio->c_t); REQ(params->wq); }
   if (reinterpret_cast<uintptr_t>(x) & 3) return DLAP_E_ALIGN;
   if (precision != DLAP_PREC_FP32 && precision != DLAP_PREC_BF16X3) return DLAP_E_PRECISION;
-  CellParams P;
-  fill_cell(P, plan, x, R, mask, params, a_t, c_t);
-  P.u = u; P.g = g; P.row_part = row_part;
-  rc = set_dropout(P, dropout_p, dropout_seed, dropout_seed_dev);
-  if (rc) return rc;
-  if (precision == DLAP_PREC_BF16X3) {
+  const bool tc = precision == DLAP_PREC_BF16X3;
+  if (tc) {
     if (plan->dims.F > 46) return DLAP_E_SHAPE;      // the ones column lives at k = 46
     REQ(index);
-    P.index = index;
-    P.months_ready = months_ready;
-    P.months_base = months_ready ? months_base : 0;
-    P.months_stride = months_stride;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  const dlap_dims& d = plan->dims;
+  CellParams P;
+  rc = fill_cell(P, plan, x, nullptr, mask, params, mio);
+  if (rc) return rc;
+  P.u = u; P.q = q;
+  rc = set_dropout(P, dropout_p, dropout_seed, dropout_seed_dev);
+  if (rc) return rc;
+  P.index = tc ? index : nullptr;
+  const int series = mio->series_T > 0 ? mio->series_T : d.T;
+  // ---- the macro side
+  MacroParams MP;
+  bool fused = false;
+  if (d.M == 0) {
+    REQ(params->b1);
+    if (q) REQ(params->bq);
+    REQ(mio->c_t);
+    CU(launch_const_bias(params, series, mio->a_t, mio->c_t, st));
+  } else if (mio->macro) {
+    REQ(mio->lstm_save); REQ(mio->c_t); REQ(mio->hn); REQ(mio->cn); REQ(params->b1); REQ(params->bq);
+    REQ(params->w_ih); REQ(params->w_hh); REQ(params->b_ih); REQ(params->b_hh); REQ(params->wq);
+    fill_macro(MP, plan, series, mio->macro, params, mio->h0, mio->c0);
+    MP.save = mio->lstm_save; MP.a_t = mio->a_t; MP.c_t = mio->c_t; MP.hn = mio->hn; MP.cn = mio->cn;
+    // the recurrence as a CTA of the per-cell grid: tensor-core kernel, H = 4 (the reference's default and every
+    // shipped configuration), and a second SM to run it on
+    fused = tc && d.H == 4 && plan->sms >= 2 && mio->sync != nullptr;
+    if (fused) {
+      if (reinterpret_cast<uintptr_t>(mio->sync) & 3) return DLAP_E_ALIGN;
+      MP.months_ready = mio->sync;
+    } else {
+      CU(launch_macro_fwd(MP, st));
+    }
+  }
+  if (tc) {
     P.cyc_sh = 2;      // blocks of four tiles: measured best of 1, 2, 4, 8 (smaller: more month changes per CTA;
                        // larger: the last CTAs wait longer for their first month, and the blocks balance worse)
     int grid = plan->grid_cell;
-    if (months_ready) {
-      // the producer (dlap_macro_fwd's recurrence CTA) must be able to become resident while this kernel spins:
-      // a per-cell CTA takes a whole SM, so one SM stays free
-      int dev = 0, sms = 0;
-      CU(cudaGetDevice(&dev));
-      CU(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-      if (sms < 2) return DLAP_E_NODEVICE;
-      if (grid > sms - 1) grid = sms - 1;
+    if (fused) {
+      P.months_ready = mio->sync;
+      if (grid > plan->sms - 1) grid = plan->sms - 1;      // one SM is the recurrence's
     }
-    CU(launch_cell_fwd_tc(P, grid, (cudaStream_t)stream));
+    CU(launch_cell_fwd_tc(P, fused ? &MP : nullptr, grid, plan->cooperative != 0, st));
     return DLAP_OK;
   }
-  CU(launch_cell_fwd_f32(P, plan->grid_cell, (cudaStream_t)stream));
+  CU(launch_cell_fwd_f32(P, plan->grid_cell, st));
   return DLAP_OK;
 }
 
-int dlap_row_finish(const dlap_plan* plan, const double* row_part, const int32_t* index, int precision,
-                    int weighted_loss, const float* n_bar_in, float* row_stats, float* pr, float* scalars,
-                    void* stream) {
+int dlap_step_reduce(const dlap_plan* plan, const float* u, const float* q, const float* R, const uint8_t* mask,
+                     const int32_t* index, int weighted_loss, const float* n_bar_in, int phase_lo, int phase_hi,
+                     float* row_stats, float* pr, float* scalars, float* w_out, double* col_part, float* e,
+                     float* t_i, float* G, double* loss_part, double* dS2, uint32_t* bar, void* stream) {
   int rc = check_plan(plan);
   if (rc) return rc;
-  REQ(row_part); REQ(row_stats); REQ(pr); REQ(scalars);
-  if (precision != DLAP_PREC_FP32 && precision != DLAP_PREC_BF16X3) return DLAP_E_PRECISION;
-  // fp32 kernel: one row-sum partial per dense tile; tensor-core kernel: one per valid-cell tile and TMEM
-  // lane quarter
-  const bool tc = precision == DLAP_PREC_BF16X3;
-  if (tc) REQ(index);
-  CU(launch_row_finish(row_part, plan->dims.T, plan->tpm, tc ? index : nullptr, weighted_loss, n_bar_in, row_stats,
-                       pr, scalars, (cudaStream_t)stream));
-  return DLAP_OK;
-}
-
-int dlap_col_partial(const dlap_plan* plan, const float* g, const float* R, const uint8_t* mask, const float* u,
-                     const float* row_stats, const int32_t* index, double* col_part, float* w_out, void* stream) {
-  int rc = check_plan(plan);
-  if (rc) return rc;
-  REQ(mask); REQ(row_stats); REQ(col_part);
-  if (w_out) REQ(u);
-  CU(launch_col_partial(g, R, mask, u, row_stats, index, plan->dims.T, plan->dims.N, plan->col_splits, col_part, w_out,
-                        (cudaStream_t)stream));
+  if (phase_lo < 0 || phase_hi > 4 || phase_lo > phase_hi) return DLAP_E_SHAPE;
+  REQ(mask); REQ(R); REQ(row_stats); REQ(scalars); REQ(col_part); REQ(bar);
+  if (reinterpret_cast<uintptr_t>(bar) & 3) return DLAP_E_ALIGN;
+  if (phase_lo <= 1) { REQ(u); REQ(pr); }
+  if (phase_hi >= 3) { REQ(e); REQ(t_i); REQ(G); REQ(loss_part); }
+  CU(launch_step_reduce_c(plan, u, q, R, mask, index, weighted_loss, n_bar_in, phase_lo, phase_hi, row_stats, pr,
+                          scalars, w_out, col_part, e, t_i, G, loss_part, dS2, bar, (cudaStream_t)stream));
   return DLAP_OK;
 }
 
@@ -278,40 +285,22 @@ int dlap_loss_finish(const dlap_plan* plan, const double* col_part, int nsplit, 
   return DLAP_OK;
 }
 
-int dlap_loss_coeff(const dlap_plan* plan, const float* e, const float* t_i, const float* gc, const float* gu,
-                    float* G, void* stream) {
-  int rc = check_plan(plan);
-  if (rc) return rc;
-  REQ(e); REQ(t_i); REQ(G);
-  CU(launch_coeff(e, t_i, plan->dims.N, gc, gu, G, (cudaStream_t)stream));
-  return DLAP_OK;
-}
-
-int dlap_ds_rows(const dlap_plan* plan, const float* g, const float* R, const uint8_t* mask, const float* G,
-                 const int32_t* index, double* dS_part, void* stream) {
-  int rc = check_plan(plan);
-  if (rc) return rc;
-  REQ(R); REQ(mask); REQ(G); REQ(dS_part);
-  CU(launch_ds_rows(g, R, mask, G, index, plan->dims.T, plan->dims.N, plan->row_splits, dS_part,
-                    (cudaStream_t)stream));
-  return DLAP_OK;
-}
-
 int dlap_cell_bwd(const dlap_plan* plan, const float* x, const float* R, const uint8_t* mask, const int32_t* index,
-                  const dlap_tensors* params, const float* a_t, const float* c_t, const float* row_stats,
-                  const double* dS_part, const float* dpr_cot, const float* G, const float* scalars,
+                  const dlap_tensors* params, const dlap_macro_io* mio, const float* row_stats, const double* dS2,
+                  const float* gc, const float* gu, const float* dpr_cot, const float* G, const float* scalars,
                   int weighted_loss, int want_sdf, int want_mom, float* wpart, float* dadc_part, int precision,
                   float dropout_p, uint64_t dropout_seed, const uint64_t* dropout_seed_dev, void* stream) {
   int rc = check_plan(plan);
   if (rc) return rc;
-  REQ(x); REQ(R); REQ(mask); REQ(params); REQ(a_t); REQ(c_t); REQ(row_stats); REQ(dS_part); REQ(G); REQ(scalars);
-  REQ(wpart); REQ(dadc_part);
+  REQ(x); REQ(R); REQ(mask); REQ(params); REQ(mio); REQ(mio->a_t); REQ(mio->c_t); REQ(row_stats); REQ(dS2); REQ(G);
+  REQ(scalars); REQ(wpart); REQ(dadc_part);
   REQ(params->w1); REQ(params->w2); REQ(params->b2); REQ(params->w3); REQ(params->b3); REQ(params->wq);
   if (!want_sdf && !want_mom) return DLAP_E_SHAPE;
   if (precision != DLAP_PREC_FP32 && precision != DLAP_PREC_BF16X3) return DLAP_E_PRECISION;
   CellParams P;
-  fill_cell(P, plan, x, R, mask, params, a_t, c_t);
-  P.row_stats = row_stats; P.dS_part = dS_part; P.ds_splits = plan->row_splits; P.dpr_cot = dpr_cot;
+  rc = fill_cell(P, plan, x, R, mask, params, mio);
+  if (rc) return rc;
+  P.row_stats = row_stats; P.dS2 = dS2; P.gc = gc; P.gu = gu; P.dpr_cot = dpr_cot;
   P.G = G; P.scalars = scalars; P.weighted = weighted_loss;
   P.wpart = wpart; P.dadc_part = dadc_part;
   rc = set_dropout(P, dropout_p, dropout_seed, dropout_seed_dev);
@@ -327,27 +316,43 @@ int dlap_cell_bwd(const dlap_plan* plan, const float* x, const float* R, const u
   return DLAP_OK;
 }
 
-int dlap_grad_finish(const dlap_plan* plan, const float* wpart, const float* dadc_part, const int32_t* index,
-                     int precision, int want_sdf, int want_mom, const dlap_tensors* grads, float* dadc,
-                     void* stream) {
-  int rc = check_plan(plan);
-  if (rc) return rc;
+// what the per-cell backward kernel left behind, and where its sums go
+static int fill_finish(FinishParams& F, const dlap_plan* plan, const float* wpart, const float* dadc_part,
+                       const int32_t* index, int precision, int want_sdf, int want_mom, const dlap_tensors* grads,
+                       float* dadc, int dadc_row_stride) {
   if (precision != DLAP_PREC_FP32 && precision != DLAP_PREC_BF16X3) return DLAP_E_PRECISION;
   // fp32 kernel: one da_t|dc_t partial per dense tile; tensor-core kernel: one per (month, CTA) segment
   const bool tc = precision == DLAP_PREC_BF16X3;
   if (tc) REQ(index);
   REQ(wpart); REQ(dadc_part); REQ(grads); REQ(dadc);
+  if (dadc_row_stride < 1) return DLAP_E_SHAPE;
   if (want_sdf) { REQ(grads->w1); REQ(grads->w2); REQ(grads->b2); REQ(grads->w3); REQ(grads->b3); }
   if (want_mom) REQ(grads->wq);
-  CU(launch_grad_finish(wpart, plan->grid_cell, plan->dims.F, want_sdf, want_mom, dadc_part, plan->dims.T,
-                        plan->tpm, tc ? index : nullptr, grads->w1, plan->ldw1, grads->w2, grads->b2, grads->w3, grads->b3, grads->wq,
-                        plan->ldwq, plan->dims.M, dadc, (cudaStream_t)stream));
+  F = FinishParams{};
+  F.wpart = wpart; F.ncta = plan->grid_cell; F.F = plan->dims.F; F.have_sdf = want_sdf; F.have_mom = want_mom;
+  F.dadc_part = dadc_part; F.T = plan->dims.T; F.tpm = plan->tpm; F.index = tc ? index : nullptr;
+  F.gW1 = grads->w1; F.ldw1 = plan->ldw1; F.gW2 = grads->w2; F.gb2 = grads->b2; F.gW3 = grads->w3; F.gb3 = grads->b3;
+  F.gWq = grads->wq; F.ldwq = plan->ldwq; F.wq_off = plan->dims.M;
+  F.dadc = dadc; F.dadc_stride = dadc_row_stride;
+  return DLAP_OK;
+}
+
+int dlap_grad_finish(const dlap_plan* plan, const float* wpart, const float* dadc_part, const int32_t* index,
+                     int precision, int want_sdf, int want_mom, const dlap_tensors* grads, float* dadc,
+                     int dadc_row_stride, void* stream) {
+  int rc = check_plan(plan);
+  if (rc) return rc;
+  FinishParams F;
+  rc = fill_finish(F, plan, wpart, dadc_part, index, precision, want_sdf, want_mom, grads, dadc, dadc_row_stride);
+  if (rc) return rc;
+  CU(launch_grad_finish(F, (cudaStream_t)stream));
   return DLAP_OK;
 }
 
 int dlap_macro_bwd(const dlap_plan* plan, const float* macro, const dlap_tensors* params, const float* h0,
-                   const float* c0, const float* lstm_save, const float* dadc, float* dpre, int want_sdf,
-                   int want_mom, const dlap_tensors* grads, void* stream) {
+                   const float* c0, const float* lstm_save, float* dadc, float* dpre, int want_sdf, int want_mom,
+                   const dlap_tensors* grads, const float* wpart, const float* dadc_part, const int32_t* index,
+                   int precision, void* stream) {
   int rc = check_plan(plan);
   if (rc) return rc;
   REQ(params); REQ(dadc); REQ(grads);
@@ -361,18 +366,27 @@ int dlap_macro_bwd(const dlap_plan* plan, const float* macro, const dlap_tensors
     }
     if (want_mom) REQ(grads->wq);
   }
-  CU(launch_macro_bwd_c(plan, macro, params, h0, c0, lstm_save, dadc, dpre, want_sdf, want_mom, grads,
-                        (cudaStream_t)stream));
+  FinishParams F{};
+  if (wpart || dadc_part) {
+    rc = fill_finish(F, plan, wpart, dadc_part, index, precision, want_sdf, want_mom, grads, dadc, 1);
+    if (rc) return rc;
+  }
+  MacroParams P;
+  fill_macro(P, plan, plan->dims.T, macro, params, h0, c0);
+  P.save = const_cast<float*>(lstm_save); P.dadc = dadc; P.dpre = dpre;
+  P.have_sdf = want_sdf; P.have_mom = want_mom;
+  P.gWih = grads->w_ih; P.gWhh = grads->w_hh; P.gbih = grads->b_ih; P.gbhh = grads->b_hh;
+  P.gW1 = grads->w1; P.gb1 = grads->b1; P.gWq = grads->wq; P.gbq = grads->bq;
+  CU(launch_macro_bwd(P, F, (cudaStream_t)stream));
   return DLAP_OK;
 }
 
-int dlap_weights(const dlap_plan* plan, const float* u, const uint8_t* mask, const float* row_stats,
-                 const int32_t* index, int normalized, float* w_out, void* stream) {
+int dlap_weights(const dlap_plan* plan, const float* u, const uint8_t* mask, const int32_t* index, int normalized,
+                 float* w_out, void* stream) {
   int rc = check_plan(plan);
   if (rc) return rc;
-  REQ(u); REQ(mask); REQ(row_stats); REQ(w_out);
-  CU(launch_weights(u, mask, row_stats, index, plan->dims.T, plan->dims.N, normalized, w_out,
-                    (cudaStream_t)stream));
+  REQ(u); REQ(mask); REQ(w_out);
+  CU(launch_weights(u, mask, index, plan->dims.T, plan->dims.N, normalized, w_out, (cudaStream_t)stream));
   return DLAP_OK;
 }
 

@@ -108,18 +108,14 @@ __global__ void __launch_bounds__(NT, 1) cell_bwd_f32_kernel(const CellParams P)
     const int t = tile / P.tpm, jt = tile % P.tpm, n0 = jt * TILE;
     if (L.bytes) { mbar_wait(s.bar, phase); phase ^= 1; } else { __syncthreads(); }
     transpose_tile(L, F, s.stage, s.xs);
-    if (tid < 64) s.as[tid] = __ldg(P.a_t + (size_t)t * 64 + tid);
-    if (tid >= 64 && tid < 72) s.cs[tid - 64] = __ldg(P.c_t + (size_t)t * 8 + tid - 64);
+    if (tid < 64) s.as[tid] = __ldg(P.a_t + (size_t)t * P.months_stride * 64 + tid);
+    if (tid >= 64 && tid < 72) s.cs[tid - 64] = __ldg(P.c_t + (size_t)t * P.months_stride * 8 + tid - 64);
     if (tid == 96) {
-      // dL/dP_t from the row partials of dL/dS_t (fixed order), src/model.py:367
-      double dS = 0.0;
-      for (int i = 0; i < P.ds_splits; ++i) dS += P.dS_part[(size_t)t * P.ds_splits + i];
-      if (P.dpr_cot) dS += (double)__ldg(P.dpr_cot + t);
       const float* rs = P.row_stats + (size_t)t * RS_W;
-      const double scale = P.weighted ? (double)P.scalars[SC_NBAR] / (double)rs[RS_NT] : 1.0;
-      s.sc[0] = (float)(dS * scale);
+      s.sc[0] = month_dP(P, t);
       s.sc[1] = rs[RS_RBAR];
       s.sc[2] = rs[RS_S];
+      s.sc[3] = P.gc ? __ldg(P.gc) : 0.f;
     }
     __syncthreads();
     const int ncell = L.ncell;
@@ -158,7 +154,7 @@ __global__ void __launch_bounds__(NT, 1) cell_bwd_f32_kernel(const CellParams P)
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
         const float q = tanhf(qp[i]);
-        const float gk = live ? __ldg(P.G + (size_t)(4 * half + i) * P.N + n0 + cell) : 0.f;
+        const float gk = live ? s.sc[3] * __ldg(P.G + (size_t)(4 * half + i) * P.N + n0 + cell) : 0.f;
         dp[i] = gk * cq * (1.f - q * q);
         b.dps[(4 * half + i) * TILE + cell] = dp[i];
       }

@@ -9,8 +9,8 @@
 //     (reference: src/model.py:208-219, 261-268; the tile-over-N concat of :253-255 is the
 //     per-month bias a_t) as register-tiled fp32 GEMMs, weights resident in smem;
 //   * runs the moment net  q = tanh(Wqx.x + c_t)  (src/model.py:132-161, :514-516).
-// The forward kernel emits u, g = q*R*m and the four row sums of the month; the backward
-// kernel recomputes the activations instead of reading saved ones and produces per-CTA
+// The forward kernel emits u and q (everything that sums over stocks or months happens in step_reduce.cu);
+// the backward kernel recomputes the activations instead of reading saved ones and produces per-CTA
 // weight-gradient partials plus per-tile da_t / dc_t partials.
 #pragma once
 #include "dlap_common.cuh"
@@ -20,7 +20,7 @@ namespace dlap {
 struct CellParams {
   // panel (caller-owned, read-only)
   const float* x;            // [T,N,F]
-  const float* R;            // [T,N]      (may be null in weights-only inference)
+  const float* R;            // [T,N]      backward kernels only
   const uint8_t* mask;       // [T,N]      torch.bool bytes
   int T, N, F;
   long long x_bytes;         // T*N*F*4, to keep the bulk copy inside the tensor
@@ -36,14 +36,14 @@ struct CellParams {
   const float* c_t;          // [T,8]   Wqm.macro_t + bq
   // forward outputs
   float* u;                  // [T,N]
-  float* g;                  // [8,T,N]  q*R*m            (null: skip the moment net)
-  double* row_part;          // [T,tpm,4] sum m, m*u, m*u*R, m*R
+  float* q;                  // [8,T,N]  tanh outputs of the moment net   (null: skip the moment net)
   // backward inputs
   const float* row_stats;    // [T,RS_W]
-  const double* dS_part;     // [T,ds_splits]
-  int ds_splits;
+  const double* dS2;         // [T,2]  dS_t for unit cotangents of L_c and of L_u (step_reduce.cu, phase 4)
+  const float* gc;           // device scalars dL/dL_c, dL/dL_u (null = 0): dS_t = gc dS2[t][0] + gu dS2[t][1]
+  const float* gu;
   const float* dpr_cot;      // [T] cotangent of portfolio_returns, or null
-  const float* G;            // [9,N]   rows 0..7: G_k, row 8: G0
+  const float* G;            // [9,N]   unit coefficients; rows 0..7 (times gc): G_k, row 8: Gu
   const float* scalars;      // [SC_W]  (n_bar)
   int weighted;              // weighted_loss flag
   // backward outputs
@@ -63,9 +63,18 @@ struct CellParams {
   const int* months_ready;
   int months_base;
   int months_stride;         // rows of a_t / c_t between consecutive months of this panel (1; n for a rank that owns
-                             // every n-th month of the series): tensor-core kernels only
+                             // every n-th month of the series)
   int cyc_sh;                // log2 of the block size of the block-cyclic tile order used with months_ready
 };
+
+// dL/dP_t of month t from the two unit sums and the loss cotangents (src/model.py:367 backwards)
+__device__ __forceinline__ float month_dP(const CellParams& P, int t) {
+  const float gc = P.gc ? __ldg(P.gc) : 0.f, gu = P.gu ? __ldg(P.gu) : 0.f;
+  double dS = (double)gc * P.dS2[2 * (size_t)t] + (double)gu * P.dS2[2 * (size_t)t + 1];
+  if (P.dpr_cot) dS += (double)__ldg(P.dpr_cot + t);
+  const float* rs = P.row_stats + (size_t)t * RS_W;
+  return (float)(dS * (P.weighted ? (double)P.scalars[SC_NBAR] / (double)rs[RS_NT] : 1.0));
+}
 
 // ---- valid-cell index ----------------------------------------------------------------------
 // The reference pushes every cell through both nets and multiplies by the mask afterwards

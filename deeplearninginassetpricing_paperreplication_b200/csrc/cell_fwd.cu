@@ -1,6 +1,6 @@
 // Forward per-cell kernel (exact fp32).  See cell_f32.cuh for the tile scheme.
-// Replaces, for one [T,N,F] panel: src/model.py:251-271 (SDF MLP on every cell),
-// :514-521 + :132-161 (moment net), and the per-month sums behind :276-278 and :363-367.
+// Replaces, for one [T,N,F] panel: src/model.py:251-271 (SDF MLP on every cell) and
+// :514-521 + :132-161 (moment net).  Dense outputs: u [T,N], q [8,T,N].
 #include "cell_f32.cuh"
 
 namespace dlap {
@@ -32,8 +32,8 @@ __global__ void __launch_bounds__(NT, 1) cell_fwd_f32_kernel(const CellParams P)
     const int t = tile / P.tpm, jt = tile % P.tpm, n0 = jt * TILE;
     if (L.bytes) { mbar_wait(s.bar, phase); phase ^= 1; } else { __syncthreads(); }
     transpose_tile(L, F, s.stage, s.xs);
-    if (tid < 64) s.as[tid] = __ldg(P.a_t + (size_t)t * 64 + tid);
-    if (MOM && tid < 8) s.cs[tid] = __ldg(P.c_t + (size_t)t * 8 + tid);
+    if (tid < 64) s.as[tid] = __ldg(P.a_t + (size_t)t * P.months_stride * 64 + tid);
+    if (MOM && tid < 8) s.cs[tid] = __ldg(P.c_t + (size_t)t * P.months_stride * 8 + tid);
     __syncthreads();
     const int ncell = L.ncell;
     const int nxt = tile + gridDim.x;
@@ -77,35 +77,13 @@ __global__ void __launch_bounds__(NT, 1) cell_fwd_f32_kernel(const CellParams P)
     const int cell = tid & (TILE - 1), half = tid >> 7;
     const bool live = cell < ncell;
     const size_t gi = (size_t)t * P.N + n0 + cell;
-    float m = 0.f, r = 0.f, uu = 0.f;
-    if (live) {
-      m = P.mask[gi] ? 1.f : 0.f;
-      r = P.R ? __ldg(P.R + gi) : 0.f;
-      uu = s.us[cell];
-    }
     if (MOM && live) {
       const size_t plane = (size_t)P.T * P.N;
-      const float rm = r * m;
 #pragma unroll
-      for (int i = 0; i < 4; ++i) P.g[(size_t)(4 * half + i) * plane + gi] = tanhf(qp[i]) * rm;
+      for (int i = 0; i < 4; ++i) P.q[(size_t)(4 * half + i) * plane + gi] = tanhf(qp[i]);
     }
-    double v0 = 0, v1 = 0, v2 = 0, v3 = 0;
-    if (half == 0 && live) {
-      P.u[gi] = uu;
-      const double mu_ = (double)m * (double)uu;
-      v0 = m; v1 = mu_; v2 = mu_ * (double)r; v3 = (double)m * (double)r;
-    }
-    v0 = warp_sum(v0); v1 = warp_sum(v1); v2 = warp_sum(v2); v3 = warp_sum(v3);
-    if ((tid & 31) == 0 && tid < TILE) {
-      double* rr = s.red + (tid >> 5) * 4;
-      rr[0] = v0; rr[1] = v1; rr[2] = v2; rr[3] = v3;
-    }
-    __syncthreads();
-    if (tid < 4) {
-      const double tot = s.red[tid] + s.red[4 + tid] + s.red[8 + tid] + s.red[12 + tid];
-      P.row_part[((size_t)t * P.tpm + jt) * 4 + tid] = tot;
-    }
-    __syncthreads();   // xs/hs/us/red are rewritten by the next tile
+    if (half == 0 && live) P.u[gi] = s.us[cell];
+    __syncthreads();   // xs/hs/us are rewritten by the next tile
   }
 }
 
@@ -121,7 +99,7 @@ static cudaError_t launch_fwd_variant(const CellParams& P, int grid, size_t smem
 cudaError_t launch_cell_fwd_f32(const CellParams& P, int grid, cudaStream_t st) {
   const size_t smem = smem_fwd_bytes(P.F);
   const bool drop = P.drop_thr != 0;
-  if (P.g) return drop ? launch_fwd_variant<true, true>(P, grid, smem, st)
+  if (P.q) return drop ? launch_fwd_variant<true, true>(P, grid, smem, st)
                        : launch_fwd_variant<true, false>(P, grid, smem, st);
   return drop ? launch_fwd_variant<false, true>(P, grid, smem, st)
               : launch_fwd_variant<false, false>(P, grid, smem, st);

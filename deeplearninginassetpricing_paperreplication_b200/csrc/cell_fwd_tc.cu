@@ -7,6 +7,13 @@
 // h1 never touches shared memory: the epilogue writes relu(z1), split into bf16 hi/lo, back into the TMEM
 // columns of its own z1 accumulator, and layer 2 takes its A operand from there (tcgen05.mma with A in TMEM).
 //
+// The LSTM beside it.  With FUSED the LAST CTA of the grid does not work on cells: it runs the macro path
+// (macro_role.cuh: input projection, the serial recurrence, a_t / c_t rows) and publishes the months as they
+// complete; the other CTAs wait for a month's row before they touch the month's first tile and walk the tiles
+// in month order.  Producer and consumers are CTAs of ONE grid that is launched co-resident (cooperative
+// launch, one CTA per SM), so the wait cannot outlive the producer's start.  The progress word is put back to
+// zero by the last CTA that leaves the kernel.
+//
 // Persistent CTA, one per SM, 16 warps with fixed roles; three tiles are in flight:
 //   warp 1      MMA issuer (one lane): layer 1 of tile i is issued before layer 2 of tile i-1
 //   warps 0, 2-7  gather + convert (warp 2 also owns the TMEM allocation): batches of 32 rows, round-robin over
@@ -14,8 +21,9 @@
 //               split into bf16 hi/lo and stored straight into the X image; the warp that handles the first
 //               batch of a tile also writes the per-month bias column of W1
 //   warps 8-11  epilogue of even tiles   } z1 -> relu -> split -> H1 image ; tanh(q) ;
-//   warps 12-15 epilogue of odd tiles    } z2 -> relu -> .W3 -> u ; g = q R m ; row sums
+//   warps 12-15 epilogue of odd tiles    } z2 -> relu -> .W3 -> u
 #include "cell_tc.cuh"
+#include "macro_role.cuh"
 
 namespace dlap {
 using namespace tcl;
@@ -62,9 +70,29 @@ __device__ __forceinline__ uint32_t h1_col_lo(int ks) { return h1_col_hi(ks) + 1
     if (P.timeline && blockIdx.x == 0 && (i) < 256) P.timeline[(i) * 16 + (k)] = clock64(); \
   } while (0)
 
-template <bool MOM, bool DROP>
-__global__ void __launch_bounds__(NT_TC, 1) cell_fwd_tc_kernel(const CellParams P) {
+// every CTA's last act when the macro role runs in this grid: the last one out zeroes both words of `sync`
+// (sync[0]: months published so far, sync[1]: CTAs that have left)
+__device__ __forceinline__ void fused_exit(int* sync) {
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    if (atomicAdd(sync + 1, 1) == (int)gridDim.x - 1) {
+      atomicExch(sync, 0);
+      atomicExch(sync + 1, 0);
+    }
+  }
+}
+
+template <bool MOM, bool DROP, bool FUSED>
+__global__ void __launch_bounds__(NT_TC, 1) cell_fwd_tc_kernel(const CellParams P, const MacroParams MP) {
   extern __shared__ __align__(128) uint8_t smem_raw[];
+  static_assert(MT == NT_TC, "the macro role is written for the per-cell kernel's CTA size");
+  if (FUSED && blockIdx.x == gridDim.x - 1) {
+    macro_fwd_role<4>(MP, reinterpret_cast<float*>(smem_raw));
+    fused_exit(MP.months_ready);
+    return;
+  }
+  const int ncta = FUSED ? (int)gridDim.x - 1 : (int)gridDim.x;     // CTAs that work on cells
   SmemTc s;
   s.base = tc::smem_align128(smem_raw);
   uint64_t* bar = s.bars();
@@ -72,8 +100,8 @@ __global__ void __launch_bounds__(NT_TC, 1) cell_fwd_tc_kernel(const CellParams 
   const int ntiles = __ldg(P.index);                       // tiles of valid cells (dlap_panel_index)
   // A contiguous tile range per CTA as a rule.  When the LSTM recurrence runs beside this kernel (months_ready),
   // blocks of four tiles are dealt round-robin instead: every CTA then needs the months in the order they are made.
-  const TileMap tm = P.months_ready ? TileMap::cyclic(ntiles, blockIdx.x, gridDim.x, P.cyc_sh)
-                                    : TileMap::contiguous(ntiles, blockIdx.x, gridDim.x);
+  const TileMap tm = P.months_ready ? TileMap::cyclic(ntiles, blockIdx.x, ncta, P.cyc_sh)
+                                    : TileMap::contiguous(ntiles, blockIdx.x, ncta);
   const int my_tiles = tm.count;
 
   // ---- one-time set-up ----
@@ -166,28 +194,26 @@ __global__ void __launch_bounds__(NT_TC, 1) cell_fwd_tc_kernel(const CellParams 
     MonthCursor mc;
     if (e < my_tiles) mc.init(P, tm.tile(e));
     int n_nxt = -1, t_nxt = 0, pos_nxt = 0;
+    bool live_nxt = false;
     auto load_row = [&](int tile) {
       mc.seek(P, tile);
       t_nxt = mc.t;
-      pos_nxt = mc.j0(tile) + cell;               // position in the month's list: where u, g of this cell go
-      n_nxt = (cell < mc.ncell(tile)) ? __ldg(vidx_row(P, mc.t) + pos_nxt) : -1;
+      pos_nxt = mc.j0(tile) + cell;               // position in the month's list: where u, q of this cell go
+      live_nxt = cell < mc.ncell(tile);
+      if (DROP) n_nxt = live_nxt ? __ldg(vidx_row(P, mc.t) + pos_nxt) : -1;     // the dropout key is the DENSE cell number
     };
     if (e < my_tiles) load_row(tm.tile(e));
     // per-tile state that E1 hands to E2 (a group has two tiles in flight: E1 of its next tile runs while layer 2
     // of the current one is on the tensor core)
-    struct TileState { size_t pi; float r; uint32_t gi; bool live; double v0, v3; };
-    // E1 of local tile i: h1 = relu(z1) -> TMEM, moments and everything else that does not need u
+    struct TileState { size_t pi; uint32_t gi; bool live; };
+    // E1 of local tile i: h1 = relu(z1) -> TMEM, and the moment outputs
     auto do_e1 = [&](int i) {
       TileState S;
       const int t = t_nxt, n = n_nxt;
       S.pi = (size_t)t * P.N + pos_nxt;
       const uint32_t dA = tbase + lane_base + COL_A + (i % NDA) * COL_A_STRIDE;
-      // this cell's return; every listed cell is unmasked, so m = 1 exactly where the row exists
-      S.live = n >= 0;
-      const size_t gi = (size_t)t * P.N + (S.live ? n : 0);
-      S.gi = (uint32_t)gi;
-      S.r = 0.f;
-      if (S.live && P.R) S.r = __ldg(P.R + gi);
+      S.live = live_nxt;
+      S.gi = (uint32_t)((size_t)t * P.N + (DROP && S.live ? n : 0));
       if (i + 2 < my_tiles) load_row(tm.tile(i + 2));
       const bool stamp = q4 == 0 && lane == 0;
       mbar_wait(bar + F_D1_FULL + i % NDA, (i / NDA) & 1);
@@ -216,17 +242,11 @@ __global__ void __launch_bounds__(NT_TC, 1) cell_fwd_tc_kernel(const CellParams 
       __syncwarp();
       if (lane == 0) mbar_arrive(bar + F_H1_FULL + i % NDA);
       if (stamp) DLAP_STAMP(i, 13);
-      if (MOM) {
+      if (MOM && S.live) {
         const size_t plane = (size_t)P.T * P.N;
-        const float rm = S.live ? S.r : 0.f;
 #pragma unroll
-        for (int k = 0; k < 8; ++k) {
-          const float gk = tc::tanh_fast(q[k]) * rm;
-          if (S.live) P.g[(size_t)k * plane + S.pi] = gk;
-        }
+        for (int k = 0; k < 8; ++k) P.q[(size_t)k * plane + S.pi] = tc::tanh_fast(q[k]);
       }
-      S.v0 = warp_sum(S.live ? 1.0 : 0.0);
-      S.v3 = warp_sum(S.live ? (double)S.r : 0.0);
       return S;
     };
     TileState cur{}, nxt{};
@@ -238,9 +258,7 @@ __global__ void __launch_bounds__(NT_TC, 1) cell_fwd_tc_kernel(const CellParams 
       if (i + 2 < my_tiles) nxt = do_e1(i + 2);      // while layer 2 of tile i runs
       const bool live = cur.live;
       const size_t pi = cur.pi;
-      const float r = cur.r, m = live ? 1.f : 0.f;
       const uint32_t gi = cur.gi;
-      const double v0 = cur.v0, v3 = cur.v3;
       // -- after layer 2: u = b3 + W3 . relu(z2 + b2)
       mbar_wait(bar + F_D2_FULL + sl, use & 1);
       tc::fence_after_sync();
@@ -270,18 +288,7 @@ __global__ void __launch_bounds__(NT_TC, 1) cell_fwd_tc_kernel(const CellParams 
       tc::fence_before_sync();
       __syncwarp();
       if (lane == 0) mbar_arrive(bar + F_D2_EMPTY + sl);
-      // -- outputs
       if (live) P.u[pi] = u;
-      double v1 = 0, v2 = 0;
-      if (live) {
-        const double mu_ = (double)m * (double)u;
-        v1 = mu_; v2 = mu_ * (double)r;
-      }
-      v1 = warp_sum(v1); v2 = warp_sum(v2);
-      if (lane == 0) {
-        double* rp = P.row_part + ((size_t)tile * 4 + q4) * 4;
-        rp[0] = v0; rp[1] = v1; rp[2] = v2; rp[3] = v3;
-      }
       if (stamp) DLAP_STAMP(i, 15);
       cur = nxt;
     }
@@ -289,26 +296,50 @@ __global__ void __launch_bounds__(NT_TC, 1) cell_fwd_tc_kernel(const CellParams 
   tc::fence_before_sync();
   __syncthreads();
   if (warp == 2) tc::tmem_dealloc(tbase, TMEM_COLS);
+  if (FUSED) fused_exit(MP.months_ready);
 }
 
-template <bool MOM, bool DROP>
-static cudaError_t launch_fwd_tc_variant(const CellParams& P, int grid, cudaStream_t st) {
-  cudaError_t e = cudaFuncSetAttribute(cell_fwd_tc_kernel<MOM, DROP>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       (int)SMEM_TC_BYTES);
+template <bool MOM, bool DROP, bool FUSED>
+static cudaError_t launch_fwd_tc_variant(const CellParams& P, const MacroParams& MP, int grid, bool cooperative,
+                                         cudaStream_t st) {
+  size_t smem = SMEM_TC_BYTES;
+  if (FUSED) {
+    const size_t need = macro_fwd_smem_bytes(MP.T, MP.M, 4) + 128;
+    if (need > smem) smem = need;
+  }
+  auto kern = cell_fwd_tc_kernel<MOM, DROP, FUSED>;
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
-  cell_fwd_tc_kernel<MOM, DROP><<<grid, NT_TC, SMEM_TC_BYTES, st>>>(P);
+  if (cooperative) {
+    void* args[] = {(void*)&P, (void*)&MP};
+    return cudaLaunchCooperativeKernel((const void*)kern, dim3(grid), dim3(NT_TC), args, smem, st);
+  }
+  kern<<<grid, NT_TC, smem, st>>>(P, MP);
   return cudaGetLastError();
 }
 
 static long long* g_timeline_fwd = nullptr;
 void set_fwd_tc_timeline(long long* p) { g_timeline_fwd = p; }
 
-cudaError_t launch_cell_fwd_tc(const CellParams& P0, int grid, cudaStream_t st) {
+// grid: CTAs that work on cells.  MP0 non-null: one more CTA runs the macro path beside them (H = 4 only; the caller
+// has put MP0->months_ready into P0.months_ready as well), and the grid is launched co-resident when `cooperative`.
+cudaError_t launch_cell_fwd_tc(const CellParams& P0, const MacroParams* MP0, int grid, bool cooperative,
+                               cudaStream_t st) {
   CellParams P = P0;
   P.timeline = g_timeline_fwd;
-  const bool drop = P.drop_thr != 0;
-  if (P.g) return drop ? launch_fwd_tc_variant<true, true>(P, grid, st) : launch_fwd_tc_variant<true, false>(P, grid, st);
-  return drop ? launch_fwd_tc_variant<false, true>(P, grid, st) : launch_fwd_tc_variant<false, false>(P, grid, st);
+  const bool drop = P.drop_thr != 0, mom = P.q != nullptr;
+  if (MP0) {
+    const MacroParams& MP = *MP0;
+    if (mom) return drop ? launch_fwd_tc_variant<true, true, true>(P, MP, grid + 1, cooperative, st)
+                         : launch_fwd_tc_variant<true, false, true>(P, MP, grid + 1, cooperative, st);
+    return drop ? launch_fwd_tc_variant<false, true, true>(P, MP, grid + 1, cooperative, st)
+                : launch_fwd_tc_variant<false, false, true>(P, MP, grid + 1, cooperative, st);
+  }
+  MacroParams MP{};
+  if (mom) return drop ? launch_fwd_tc_variant<true, true, false>(P, MP, grid, false, st)
+                       : launch_fwd_tc_variant<true, false, false>(P, MP, grid, false, st);
+  return drop ? launch_fwd_tc_variant<false, true, false>(P, MP, grid, false, st)
+              : launch_fwd_tc_variant<false, false, false>(P, MP, grid, false, st);
 }
 
 }  // namespace dlap

@@ -102,4 +102,32 @@ __device__ __forceinline__ T block_sum(T v, T* red) {
 
 __device__ __forceinline__ float ld_nc(const float* p) { return __ldg(p); }
 
+// ---- grid-wide barrier ---------------------------------------------------------------------
+// For kernels whose whole grid is co-resident (cooperative launch, or a grid no larger than what the device
+// holds at once).  *bar is zero when the kernel starts; the k-th barrier of the launch (k = 1, 2, ...) opens
+// when the word reaches k * gridDim.x.  Data written before the barrier is visible after it to loads that do
+// not go through the read-only path (plain, ld.cg, ld.acquire).
+__device__ __forceinline__ void grid_sync(unsigned int* bar, unsigned int k) {
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    atomicAdd(bar, 1u);
+    const unsigned int target = k * gridDim.x;
+    unsigned int v;
+    do {
+      asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(bar) : "memory");
+    } while (v < target);
+  }
+  __syncthreads();
+}
+// The last thing such a kernel does (nsync = barriers it has passed): the last CTA to get here puts the word back
+// to zero for the next launch on the stream.
+__device__ __forceinline__ void grid_exit(unsigned int* bar, unsigned int nsync) {
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned int old = atomicAdd(bar, 1u);
+    if (old == (nsync + 1u) * gridDim.x - 1u) atomicExch(bar, 0u);
+  }
+}
+
 }  // namespace dlap

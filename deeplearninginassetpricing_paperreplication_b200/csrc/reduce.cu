@@ -1,137 +1,15 @@
-// Row (per month over N) and column (per stock over T) reductions, loss and gradient finishing
-// kernels.  All HBM-bound or tiny; every cross-CTA sum is done in a fixed order (no float
-// atomics) so that results are run-to-run reproducible like the reference's CPU path.
+// Stage-level kernels next to the fused reduction of step_reduce.cu: the loss stage on its own (per-stock sums ->
+// e, T_i, L_c, L_u; also behind the no-allocation entry point), the stand-alone sum of the backward kernels'
+// partials (month shards exchange right after it), and the inference weights.  Every cross-CTA sum is done in a
+// fixed order (no float atomics) so that results are run-to-run reproducible like the reference's CPU path.
 #include <mutex>
 
 #include "../../include/dlap.h"
 #include "dlap_common.cuh"
 #include "cell_f32.cuh"
+#include "grad_finish.cuh"
 
 namespace dlap {
-
-// ---- row finish ------------------------------------------------------------------------------
-// N_t = clamp(sum m, 1), mu_t = sum(m u)/N_t                      src/model.py:276-278
-// P_t = sum m (u - mu_t) R = sum(m u R) - mu_t sum(m R)           src/model.py:363,367
-// pr_t = P_t / N_t * N_bar (weighted_loss) ; S_t = 1 + pr_t       src/model.py:360,367,380
-// sharpe = mean(pr) / (std_unbiased(pr) + 1e-8)                   src/model.py:551
-// stage 1 (multi-CTA): one warp per month sums the per-tile partial slots in a fixed tree
-// `index` != null (tensor-core kernels): the partials of month t are the 4 slots of each of its valid-cell
-// tiles, tile_start[t] .. tile_start[t+1]; otherwise `tpm` slots per month.
-__global__ void __launch_bounds__(256) row_sum_kernel(const double* __restrict__ row_part, int T, int tpm,
-                                                      const int* __restrict__ index, float* __restrict__ row_stats) {
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int t = blockIdx.x * 8 + warp;
-  if (t >= T) return;
-  size_t first = (size_t)t * tpm;
-  if (index) {
-    const int* ts = index + idx_off_ts();
-    first = (size_t)ts[t] * 4;
-    tpm = (ts[t + 1] - ts[t]) * 4;
-  }
-  double c = 0, su = 0, sur = 0, sr = 0;
-  const double4* p = reinterpret_cast<const double4*>(row_part) + first;
-  for (int j = lane; j < tpm; j += 32) {
-    const double4 v = p[j];
-    c += v.x; su += v.y; sur += v.z; sr += v.w;
-  }
-  c = warp_sum(c); su = warp_sum(su); sur = warp_sum(sur); sr = warp_sum(sr);
-  if (lane == 0) {
-    const double nt = fmax(c, 1.0);
-    const float mu = (float)(su / nt);
-    float* rs = row_stats + (size_t)t * RS_W;
-    rs[RS_NT] = (float)nt;
-    rs[RS_MU] = mu;
-    rs[RS_P] = (float)(sur - (double)mu * sr);
-    rs[RS_RBAR] = (float)(sr / nt);
-  }
-}
-
-// stage 2 (one CTA): N_bar, pr_t, S_t, Sharpe from the T per-month rows
-__global__ void __launch_bounds__(1024) row_finish_kernel(
-    int T, int weighted, const float* __restrict__ n_bar_in, float* __restrict__ row_stats,
-    float* __restrict__ pr_out, float* __restrict__ scalars) {
-  __shared__ double red[32];
-  const int tid = threadIdx.x;
-  double nsum = 0.0;
-  for (int t = tid; t < T; t += blockDim.x) nsum += (double)row_stats[(size_t)t * RS_W + RS_NT];
-  nsum = block_sum(nsum, red);
-  const float n_bar = n_bar_in ? *n_bar_in : (float)(nsum / (double)T);
-  double s1 = 0.0;
-  for (int t = tid; t < T; t += blockDim.x) {
-    float* rs = row_stats + (size_t)t * RS_W;
-    const float pr = weighted ? (float)((double)rs[RS_P] / (double)rs[RS_NT] * (double)n_bar) : rs[RS_P];
-    rs[RS_PR] = pr;
-    rs[RS_S] = 1.f + pr;
-    pr_out[t] = pr;
-    s1 += pr;
-  }
-  s1 = block_sum(s1, red);
-  const double mean = s1 / (double)T;
-  double s2 = 0.0;
-  for (int t = tid; t < T; t += blockDim.x) {
-    const double d = (double)pr_out[t] - mean;
-    s2 += d * d;
-  }
-  s2 = block_sum(s2, red);
-  if (tid == 0) {
-    scalars[SC_NBAR] = n_bar;
-    scalars[SC_SHARPE] = (T > 1) ? (float)(mean / (sqrt(s2 / (double)(T - 1)) + 1e-8)) : nanf("");
-  }
-}
-
-// ---- column partial sums + weights ---------------------------------------------------------------
-// per stock i over the months of one T-chunk:  sum_t g_k S_t (k<8), sum_t R m S_t, sum_t m
-// (src/model.py:376,382,428) and, fused, w = m (u - mu_t) (src/model.py:271-279).
-// `index` != null: u and g are left-packed (tensor-core kernels, cell_f32.cuh), else dense [T,N].
-__global__ void __launch_bounds__(256, 4) col_partial_kernel(
-    const float* __restrict__ g, const float* __restrict__ R, const uint8_t* __restrict__ mask,
-    const float* __restrict__ u, const float* __restrict__ row_stats, const int* __restrict__ index, int T, int N,
-    int tchunk, double* __restrict__ col_part, float* __restrict__ w_out) {
-  extern __shared__ float sm[];            // S_t then mu_t for this chunk
-  const int t0 = blockIdx.y * tchunk, t1 = min(T, t0 + tchunk);
-  for (int t = t0 + threadIdx.x; t < t1; t += blockDim.x) {
-    sm[t - t0] = row_stats[(size_t)t * RS_W + RS_S];
-    sm[tchunk + t - t0] = row_stats[(size_t)t * RS_W + RS_MU];
-  }
-  __syncthreads();
-  const int i = blockIdx.x * blockDim.x + threadIdx.x, lane = threadIdx.x & 31;
-  const bool in = i < N;                   // whole warps stay: the packed position comes from a ballot
-  const int nw = (N + 31) >> 5;
-  const int* rank = index ? index + idx_off_rank(T, N) + (i >> 5) : nullptr;
-  const size_t plane = (size_t)T * N;
-  double acc[KM + 2];
-#pragma unroll
-  for (int k = 0; k < KM + 2; ++k) acc[k] = 0.0;
-  // The kernel is latency-bound (two dependent round trips per month: mask, then values), so the loop body is
-  // branch-free -- masked lanes load from a clamped in-bounds position and their values are dropped by a
-  // select -- and the unrolled months overlap their loads.
-  const size_t ic = in ? (size_t)i : (size_t)N - 1;
-#pragma unroll 4
-  for (int t = t0; t < t1; ++t) {
-    const size_t gi = (size_t)t * N + ic;
-    const float S = sm[t - t0];
-    // u and g are defined at unmasked cells only (the tensor-core kernels never visit the others)
-    const bool live = in && mask[gi] != 0;
-    const unsigned b = __ballot_sync(0xffffffffu, live);
-    size_t vi = gi;
-    if (index) vi = (size_t)t * N + __ldg(rank + (size_t)t * nw) + __popc(b & ((1u << lane) - 1u));
-    if (vi >= plane) vi = plane - 1;       // a masked lane behind the last listed stock of the last month
-    const float uv = (w_out || !g) ? __ldg(u + vi) : 0.f;
-    const float r = R ? __ldg(R + gi) : 0.f;
-    float gv[KM];
-#pragma unroll
-    for (int k = 0; k < KM; ++k) gv[k] = g ? __ldg(g + k * plane + vi) : 0.f;
-    if (w_out && in) w_out[gi] = live ? (uv - sm[tchunk + t - t0]) : 0.f;
-    acc[KM] += live ? (double)(r * S) : 0.0;
-    acc[KM + 1] += live ? 1.0 : 0.0;
-#pragma unroll
-    for (int k = 0; k < KM; ++k) acc[k] += live ? (double)(gv[k] * S) : 0.0;
-  }
-  if (!in) return;
-  double* out = col_part + (size_t)blockIdx.y * (KM + 2) * N + i;
-#pragma unroll
-  for (int k = 0; k < KM + 2; ++k) out[(size_t)k * N] = acc[k];
-}
 
 // ---- loss finish -----------------------------------------------------------------------------
 // e_ki = colsum / T_i ; L_c = mean_k mean_i e_ki^2 ; L_u = mean_i e0_i^2   src/model.py:382-385,428-431
@@ -198,136 +76,25 @@ __global__ void __launch_bounds__(256) loss_finish_kernel(
   }
 }
 
-// ---- backward: loss cotangents -> per-stock coefficients -------------------------------------------
-// G_ki = gc * 2 e_ki / (K N T_i) ; G0_i = gu * 2 e0_i / (N T_i)          
-__global__ void coeff_kernel(const float* __restrict__ e, const float* __restrict__ ti, int N,
-                             const float* __restrict__ gc, const float* __restrict__ gu,
-                             float* __restrict__ G) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= N) return;
-  const float c = gc ? *gc : 0.f, uu = gu ? *gu : 0.f;
-  const float inv = 1.f / ((float)N * ti[i]);
-#pragma unroll
-  for (int k = 0; k < KM; ++k) G[(size_t)k * N + i] = c * (2.f / KM) * e[(size_t)k * N + i] * inv;
-  G[(size_t)KM * N + i] = uu * 2.f * e[(size_t)KM * N + i] * inv;
-}
-
-// dS_t partial = sum_i ( sum_k G_ki g_kti + G0_i R m ).  `index` != null: g is left-packed and the month's
-// list of unmasked stocks is walked (contiguous g, no mask read); else dense.
-__global__ void __launch_bounds__(256) ds_rows_kernel(
-    const float* __restrict__ g, const float* __restrict__ R, const uint8_t* __restrict__ mask,
-    const float* __restrict__ G, const int* __restrict__ index, int T, int N, int nchunk,
-    double* __restrict__ dS_part) {
-  __shared__ double red[32];
-  const int t = blockIdx.x, sp = blockIdx.y;
-  const size_t plane = (size_t)T * N;
-  double acc = 0.0;
-  if (index) {
-    const int cnt = index[idx_off_cnt(T) + t];
-    const int chunk = (cnt + (int)gridDim.y - 1) / (int)gridDim.y;
-    const int j0 = sp * chunk, j1 = min(cnt, j0 + chunk);
-    const int* vrow = index + idx_off_vidx(T) + (size_t)t * N;
-    for (int j = j0 + threadIdx.x; j < j1; j += blockDim.x) {
-      const int i = __ldg(vrow + j);
-      const size_t vi = (size_t)t * N + j;
-      float v = __ldg(G + (size_t)KM * N + i) * __ldg(R + (size_t)t * N + i);
-      if (g) {
-#pragma unroll
-        for (int k = 0; k < KM; ++k) v = fmaf(__ldg(G + (size_t)k * N + i), __ldg(g + k * plane + vi), v);
-      }
-      acc += (double)v;
-    }
-  } else {
-    const int i0 = sp * nchunk, i1 = min(N, i0 + nchunk);
-    for (int i = i0 + threadIdx.x; i < i1; i += blockDim.x) {
-      const size_t gi = (size_t)t * N + i;
-      if (!mask[gi]) continue;                         // g is defined at unmasked cells only
-      float v = __ldg(G + (size_t)KM * N + i) * __ldg(R + gi);
-      if (g) {
-#pragma unroll
-        for (int k = 0; k < KM; ++k) v = fmaf(__ldg(G + (size_t)k * N + i), __ldg(g + k * plane + gi), v);
-      }
-      acc += (double)v;
-    }
-  }
-  acc = block_sum(acc, red);
-  if (threadIdx.x == 0) dS_part[(size_t)t * gridDim.y + sp] = acc;
-}
-
-// ---- backward: sum per-CTA / per-tile partials into the reference's gradient layouts ----------------
-__global__ void __launch_bounds__(256) grad_finish_kernel(
-    const float* __restrict__ wpart, int ncta, int F, int have_sdf, int have_mom,
-    const float* __restrict__ dadc_part, int T, int tpm /* partial slots per month */,
-    const int* __restrict__ index /* != null: (month, CTA) segment layout of the tensor-core kernel */,
-    float* __restrict__ gW1, int ldw1, float* __restrict__ gW2, float* __restrict__ gb2,
-    float* __restrict__ gW3, float* __restrict__ gb3, float* __restrict__ gWq, int ldwq, int wq_off,
-    float* __restrict__ dadc) {
-  const int Fr = round4(F), stride = wp_stride(Fr);
+// ---- backward: sum per-CTA / per-tile partials into the reference's gradient layouts (grad_finish.cuh) --------
+__global__ void __launch_bounds__(256) grad_finish_kernel(const FinishParams P) {
+  const int stride = wp_stride(round4(P.F));
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx < stride) {
-    // four running sums (CTAs c = u mod 4, ascending), sixteen loads in flight: the kernel is one L2 round trip
-    // per batch of loads and nothing else
-    float v4[4] = {0.f, 0.f, 0.f, 0.f};
-    int c = 0;
-    for (; c + 16 <= ncta; c += 16) {
-      float ld[16];
-#pragma unroll
-      for (int u = 0; u < 16; ++u) ld[u] = __ldg(wpart + (size_t)(c + u) * stride + idx);
-#pragma unroll
-      for (int u = 0; u < 16; ++u) v4[u & 3] += ld[u];
-    }
-    for (; c + 4 <= ncta; c += 4) {
-#pragma unroll
-      for (int u = 0; u < 4; ++u) v4[u] += wpart[(size_t)(c + u) * stride + idx];
-    }
-    for (; c < ncta; ++c) v4[0] += wpart[(size_t)c * stride + idx];
-    const float v = (v4[0] + v4[1]) + (v4[2] + v4[3]);
-    if (idx < wp_off_w1()) {
-      if (have_sdf) gW2[idx] = v;
-    } else if (idx < wp_off_wq(Fr)) {
-      const int j = (idx - wp_off_w1()) / Fr, f = (idx - wp_off_w1()) % Fr;
-      if (have_sdf && f < F) gW1[(size_t)j * ldw1 + f] = v;
-    } else if (idx < wp_off_w3(Fr)) {
-      const int k = (idx - wp_off_wq(Fr)) / Fr, f = (idx - wp_off_wq(Fr)) % Fr;
-      if (have_mom && f < F) gWq[(size_t)k * ldwq + wq_off + f] = v;
-    } else if (idx < wp_off_b2(Fr)) {
-      if (have_sdf) gW3[idx - wp_off_w3(Fr)] = v;
-    } else if (idx < wp_off_b2(Fr) + 64) {
-      if (have_sdf) gb2[idx - wp_off_b2(Fr)] = v;
-    }
-    // d b3 = sum du = dP_t * sum m (R - Rbar_t) = 0 identically (demeaning, src/model.py:279)
-    if (idx == 0 && have_sdf) gb3[0] = 0.f;
-  } else {
-    const int r = idx - stride;
-    if (r < T * 72) {
-      const int t = r / 72, c = r % 72;
-      float v8[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-      const float* p = dadc_part + (size_t)t * tpm * 72 + c;
-      if (index) {             // one partial per CTA that owns tiles of this month (consecutive CTAs)
-        const int* ts = index + idx_off_ts();
-        const int chunk = tc_chunk(index[0], ncta), a = ts[t], b = ts[t + 1];
-        tpm = b > a ? (b - 1) / chunk - a / chunk + 1 : 0;
-      }
-      int j = 0;
-      for (; j + 8 <= tpm; j += 8) {
-#pragma unroll
-        for (int u = 0; u < 8; ++u) v8[u] += p[(size_t)(j + u) * 72];
-      }
-      for (; j < tpm; ++j) v8[0] += p[(size_t)j * 72];
-      dadc[r] = ((v8[0] + v8[1]) + (v8[2] + v8[3])) + ((v8[4] + v8[5]) + (v8[6] + v8[7]));
-    }
+    if (P.wpart) finish_wpart(P, idx);
+  } else if (idx - stride < P.T * 72) {
+    finish_dadc(P, idx - stride);
   }
 }
 
 // ---- inference: weights, optionally per-month |w|-normalised -----------------------------------------
-// w = m (u - mu_t) ; normalised: w / clamp(sum_i |w| m, 1e-8)          src/model.py:581-592
+// w = m (u - mu_t), mu_t = sum_i m u / clamp(sum_i m, 1); normalised: w / clamp(sum_i |w| m, 1e-8)
+// (src/model.py:271-279, :581-592).  One CTA per month; `index` != null: u is left-packed.
 __global__ void __launch_bounds__(256) weights_kernel(
-    const float* __restrict__ u, const uint8_t* __restrict__ mask, const float* __restrict__ row_stats,
-    const int* __restrict__ index /* != null: u is left-packed */, int T, int N, int normalized,
-    float* __restrict__ w_out) {
+    const float* __restrict__ u, const uint8_t* __restrict__ mask, const int* __restrict__ index, int T, int N,
+    int normalized, float* __restrict__ w_out) {
   __shared__ double red[32];
   const int t = blockIdx.x, lane = threadIdx.x & 31;
-  const float mu = row_stats[(size_t)t * RS_W + RS_MU];
   const size_t base = (size_t)t * N;
   const int* rank = index ? index + idx_off_rank(T, N) + (size_t)t * ((N + 31) >> 5) : nullptr;
   // value of u for stock i (whole warps call it: the packed position comes from a ballot)
@@ -338,6 +105,21 @@ __global__ void __launch_bounds__(256) weights_kernel(
     const size_t vi = index ? base + __ldg(rank + (i >> 5)) + __popc(b & ((1u << lane) - 1u)) : base + i;
     return __ldg(u + vi);
   };
+  double su = 0.0, cnt = 0.0;
+  if (index) {                                   // the month's listed cells are contiguous in u
+    const int c = index[idx_off_cnt(T) + t];
+    for (int j = threadIdx.x; j < c; j += blockDim.x) su += (double)__ldg(u + base + j);
+    cnt = threadIdx.x == 0 ? (double)c : 0.0;
+  } else {
+    for (int i0 = 0; i0 < N; i0 += blockDim.x) {
+      bool live;
+      const float v = u_at(i0 + threadIdx.x, live);
+      if (live) { su += (double)v; cnt += 1.0; }
+    }
+  }
+  su = block_sum(su, red);
+  cnt = block_sum(cnt, red);
+  const float mu = (float)(su / fmax(cnt, 1.0));
   float denom = 1.f;
   if (normalized) {
     double s = 0.0;
@@ -359,22 +141,6 @@ __global__ void __launch_bounds__(256) weights_kernel(
 }
 
 // ---- launchers ---------------------------------------------------------------------------------------
-cudaError_t launch_row_finish(const double* row_part, int T, int tpm, const int* index, int weighted,
-                              const float* n_bar_in, float* row_stats, float* pr_out, float* scalars,
-                              cudaStream_t st) {
-  row_sum_kernel<<<(T + 7) / 8, 256, 0, st>>>(row_part, T, tpm, index, row_stats);
-  row_finish_kernel<<<1, T < 1024 ? ((T + 31) / 32) * 32 : 1024, 0, st>>>(T, weighted, n_bar_in, row_stats, pr_out, scalars);
-  return cudaGetLastError();
-}
-cudaError_t launch_col_partial(const float* g, const float* R, const uint8_t* mask, const float* u,
-                               const float* row_stats, const int* index, int T, int N, int nsplit,
-                               double* col_part, float* w_out, cudaStream_t st) {
-  const int tchunk = (T + nsplit - 1) / nsplit;
-  dim3 grid((N + 255) / 256, nsplit);
-  col_partial_kernel<<<grid, 256, 2 * tchunk * sizeof(float), st>>>(g, R, mask, u, row_stats, index, T, N, tchunk,
-                                                                    col_part, w_out);
-  return cudaGetLastError();
-}
 cudaError_t launch_loss_finish(const double* col_part, int nsplit, int N, int n_total, float* e_out,
                                float* ti_out, double* loss_part, unsigned int* counter, float* scalars,
                                cudaStream_t st) {
@@ -382,32 +148,14 @@ cudaError_t launch_loss_finish(const double* col_part, int nsplit, int N, int n_
                                                       loss_part, counter, scalars);
   return cudaGetLastError();
 }
-cudaError_t launch_coeff(const float* e, const float* ti, int N, const float* gc, const float* gu, float* G,
-                         cudaStream_t st) {
-  coeff_kernel<<<(N + 255) / 256, 256, 0, st>>>(e, ti, N, gc, gu, G);
+cudaError_t launch_grad_finish(const FinishParams& P, cudaStream_t st) {
+  const int total = wp_stride(round4(P.F)) + P.T * 72;
+  grad_finish_kernel<<<(total + 255) / 256, 256, 0, st>>>(P);
   return cudaGetLastError();
 }
-cudaError_t launch_ds_rows(const float* g, const float* R, const uint8_t* mask, const float* G, const int* index,
-                           int T, int N, int nsplit, double* dS_part, cudaStream_t st) {
-  const int nchunk = (N + nsplit - 1) / nsplit;
-  dim3 grid(T, nsplit);
-  ds_rows_kernel<<<grid, 256, 0, st>>>(g, R, mask, G, index, T, N, nchunk, dS_part);
-  return cudaGetLastError();
-}
-cudaError_t launch_grad_finish(const float* wpart, int ncta, int F, int have_sdf, int have_mom,
-                               const float* dadc_part, int T, int tpm, const int* index, float* gW1,
-                               int ldw1, float* gW2,
-                               float* gb2, float* gW3, float* gb3, float* gWq, int ldwq, int wq_off,
-                               float* dadc, cudaStream_t st) {
-  const int total = wp_stride(round4(F)) + T * 72;
-  grad_finish_kernel<<<(total + 255) / 256, 256, 0, st>>>(wpart, ncta, F, have_sdf, have_mom, dadc_part, T,
-                                                          tpm, index, gW1, ldw1, gW2, gb2, gW3, gb3, gWq, ldwq,
-                                                          wq_off, dadc);
-  return cudaGetLastError();
-}
-cudaError_t launch_weights(const float* u, const uint8_t* mask, const float* row_stats, const int* index, int T,
-                           int N, int normalized, float* w_out, cudaStream_t st) {
-  weights_kernel<<<T, 256, 0, st>>>(u, mask, row_stats, index, T, N, normalized, w_out);
+cudaError_t launch_weights(const float* u, const uint8_t* mask, const int* index, int T, int N, int normalized,
+                           float* w_out, cudaStream_t st) {
+  weights_kernel<<<T, 256, 0, st>>>(u, mask, index, T, N, normalized, w_out);
   return cudaGetLastError();
 }
 

@@ -315,4 +315,19 @@ cudaError_t launch_step_reduce(ReduceParams P, int sms, bool cooperative, cudaSt
   return cudaGetLastError();
 }
 
+cudaError_t launch_step_reduce_c(const dlap_plan* plan, const float* u, const float* q, const float* R, const uint8_t* mask,
+                                 const int* index, int weighted, const float* n_bar_in, int phase_lo, int phase_hi,
+                                 float* row_stats, float* pr, float* scalars, float* w_out, double* col_part, float* e,
+                                 float* t_i, float* G, double* loss_part, double* dS2, unsigned int* bar, cudaStream_t st) {
+  ReduceParams P{};
+  P.u = u; P.q = q; P.R = R; P.mask = mask; P.index = index;
+  P.T = plan->dims.T; P.N = plan->dims.N;
+  P.weighted = weighted; P.n_bar_in = n_bar_in; P.n_total = plan->dims.N;
+  P.row_stats = row_stats; P.pr = pr; P.scalars = scalars; P.w_out = w_out;
+  P.col_part = col_part; P.nsplit = plan->col_splits; P.tchunk = (plan->dims.T + plan->col_splits - 1) / plan->col_splits;
+  P.e = e; P.t_i = t_i; P.G = G; P.loss_part = loss_part; P.dS2 = dS2; P.bar = bar;
+  P.phase_lo = phase_lo; P.phase_hi = phase_hi;
+  return launch_step_reduce(P, plan->sms, plan->cooperative != 0, st);
+}
+
 }  // namespace dlap

@@ -1,20 +1,17 @@
 """The adversarial-SDF step as one ``torch.autograd.Function`` over the C ABI.
 
-Forward  : macro_fwd -> [panel_index] -> cell_fwd -> row_finish -> col_partial -> loss_finish
-Backward : loss_coeff -> ds_rows -> cell_bwd -> grad_finish -> macro_bwd
+Forward  : [panel_index] -> cell_fwd (the macro LSTM runs on one CTA of its grid) -> step_reduce
+Backward : cell_bwd -> macro_bwd (sums the per-cell partials, BPTT, month-level gradients)
 
-With the tensor-core precision the LSTM recurrence of macro_fwd (serial, one warp) runs on a side stream BESIDE
-cell_fwd, which waits month by month for the per-month biases it needs (``overlap_macro``).
-
-Every stage is a kernel launch through ``libdlap_b200.so`` on torch's current stream; torch is
-used for device memory and streams only.  Nothing here synchronises with the host, so a whole
+Five launches per step.  Every stage is a kernel launch through ``libdlap_b200.so`` on torch's current stream;
+torch is used for device memory and streams only.  Nothing here synchronises with the host, so a whole
 training step can be captured in a CUDA graph.
 
 Month-sharded multi-GPU runs (``shard`` argument): each rank owns a slab of months, or every n-th month,
 of ``x``/``R``/``mask`` and the full macro series.  The only exchanges are an all-reduce of the
-per-stock column sums ``[10, N]`` in the forward pass and, in the backward pass, an all-reduce
-of the per-month ``da_t | dc_t`` rows (zero outside the rank's slab) together with the
-per-cell weight gradients; every rank then runs the (tiny, serial) LSTM BPTT redundantly.
+per-stock column sums ``[10, N]`` in the forward pass (between phases 2 and 3 of step_reduce) and, in the
+backward pass, an all-reduce of the per-month ``da_t | dc_t`` rows (zero outside the rank's months) together
+with the per-cell weight gradients; every rank then runs the (tiny, serial) LSTM BPTT redundantly.
 """
 from __future__ import annotations
 
@@ -27,7 +24,7 @@ from typing import Dict, Optional, Tuple
 import torch
 
 from . import _lib
-from ._lib import DlapDims, DlapPlan, DlapTensors
+from ._lib import DlapDims, DlapMacroIO, DlapPlan, DlapTensors
 
 RS_W = 8      # row_stats row width  (csrc/dlap_common.cuh)
 SC_W = 8      # scalars width
@@ -113,22 +110,25 @@ class Workspace:
                   else torch.cuda.current_device(), C.byref(self.plan))
         p = self.plan
         # SMs left to a concurrent dlap_panel_pull (reserve_sms): the persistent per-cell kernels take one CTA
-        # per SM and all of its registers, so they only overlap with the ingest if they leave some SMs alone
-        self.reserve = min(int(reserve), p.grid_cell - 1) if reserve > 0 else 0
-        p.grid_cell -= self.reserve
+        # per SM and all of its registers, so they only overlap with the ingest if they leave some SMs alone; the
+        # grid-synchronising kernels are then launched plainly (a cooperative grid does not share the device)
+        self.reserve = min(int(reserve), p.sms - 2) if reserve > 0 else 0
+        if self.reserve > 0:
+            p.sms -= self.reserve
+            p.grid_cell = min(p.grid_cell, p.sms)
+            p.cooperative = 0
+        if os.environ.get("DLAP_COOPERATIVE", "1") == "0":
+            p.cooperative = 0
         self.pp = C.byref(p)
         f64 = lambda nbytes: torch.empty(max(nbytes // 8, 1), dtype=torch.float64, device=device)
         f32 = lambda nbytes: torch.empty(max(nbytes // 4, 1), dtype=torch.float32, device=device)
-        self.row_part = f64(p.row_part_bytes)
         self.col_part = f64(p.col_part_bytes)
         self.loss_part = f64(p.loss_part_bytes)
-        self.ds_part = f64(p.ds_part_bytes)
         self.wpart = f32(p.wpart_bytes)
         self.dadc_part = f32(p.dadc_part_bytes)
         self.dpre = f32(p.dpre_bytes)
-        self.counter = torch.zeros(1, dtype=torch.int32, device=device)
-        self.months_ready = torch.zeros(1, dtype=torch.int32, device=device)   # progress of a concurrent dlap_macro_fwd
-        self.side = torch.cuda.Stream(device)                                   # the stream it runs on
+        self.bar = torch.zeros(1, dtype=torch.int32, device=device)      # barrier word of dlap_step_reduce
+        self.sync = torch.zeros(2, dtype=torch.int32, device=device)     # progress words of the fused dlap_cell_fwd
         self.launches = 0          # kernels launched through this workspace (bench bookkeeping)
 
     def panel_index(self, mask: torch.Tensor) -> torch.Tensor:
@@ -288,16 +288,16 @@ def _flat_state(h, H, dev):
     return h
 
 
-# bf16x3 only: dlap_macro_fwd on a side stream, dlap_cell_fwd beside it (False, or DLAP_OVERLAP_MACRO=0 in the
-# environment: one after the other)
-overlap_macro = os.environ.get("DLAP_OVERLAP_MACRO", "1") != "0"
 
 
-def macro_forward(ws: Workspace, macro, params, h0, c0, concurrent: bool = False):
-    """dlap_macro_fwd: LSTM states + per-month biases.  `macro` covers all months of the panel.
-    concurrent: enqueue it on ws.side behind the work already on the current stream and publish its progress in
-    ws.months_ready; the caller hands that counter to the dlap_cell_fwd it enqueues next on the current stream and
-    then joins ws.side (`join_macro`)."""
+# bf16x3, H = 4: the macro LSTM runs on one CTA of dlap_cell_fwd's own grid, beside the per-cell work (False, or
+# DLAP_FUSE_MACRO=0 in the environment: a launch of its own in front of it; same results bit for bit)
+fuse_macro = os.environ.get("DLAP_FUSE_MACRO", "1") != "0"
+
+
+def macro_forward(ws: Workspace, macro, params, h0, c0):
+    """dlap_macro_fwd on its own (MacroLSTM.forward as a stand-alone call): LSTM states + per-month biases of the
+    plan's T months."""
     dev = ws.device
     T, H = ws.plan.dims.T, max(ws.plan.dims.H, 1)
     save = torch.empty(T, 6 * H, dtype=torch.float32, device=dev)
@@ -306,108 +306,141 @@ def macro_forward(ws: Workspace, macro, params, h0, c0, concurrent: bool = False
     hn = torch.empty(H, dtype=torch.float32, device=dev)
     cn = torch.empty(H, dtype=torch.float32, device=dev)
     tens = _tensors(params)
-    if concurrent:
-        main = torch.cuda.current_stream(dev)
-        ws.months_ready.zero_()                    # ordered before both the producer and the consumer
-        ws.side.wait_stream(main)
-        _lib.call("dlap_macro_fwd", ws.pp, _ptr(macro), C.byref(tens), _ptr(h0), _ptr(c0), _ptr(save),
-                  _ptr(a_t), _ptr(c_t), _ptr(hn), _ptr(cn), _ptr(ws.dpre), _ptr(ws.months_ready),
-                  ws.side.cuda_stream)
-    else:
-        _timed_call("dlap_macro_fwd", dev, ws.pp, _ptr(macro), C.byref(tens), _ptr(h0), _ptr(c0), _ptr(save),
-                    _ptr(a_t), _ptr(c_t), _ptr(hn), _ptr(cn), _ptr(ws.dpre), None, _stream(dev))
+    _timed_call("dlap_macro_fwd", dev, ws.pp, _ptr(macro), C.byref(tens), _ptr(h0), _ptr(c0), _ptr(save),
+                _ptr(a_t), _ptr(c_t), _ptr(hn), _ptr(cn), _stream(dev))
     ws.launches += 1
     return save, a_t, c_t, hn, cn
 
 
-def join_macro(ws: Workspace) -> None:
-    """The current stream continues only after the concurrent dlap_macro_fwd on ws.side has finished."""
-    torch.cuda.current_stream(ws.device).wait_stream(ws.side)
+@dataclass
+class CellPass:
+    """What one per-cell forward pass leaves behind (dlap_cell_fwd): u, the moment outputs q (or None), the macro
+    tables over the series, the final LSTM state, the valid-cell index the tensor-core kernels ran with (or None),
+    and the dlap_macro_io that describes the tables to later calls."""
+    u: torch.Tensor
+    q: Optional[torch.Tensor]
+    save: torch.Tensor
+    a_t: torch.Tensor
+    c_t: torch.Tensor
+    hn: torch.Tensor
+    cn: torch.Tensor
+    index: Optional[torch.Tensor]
+    mio: DlapMacroIO
+    precision: str
+
+
+def cell_forward(ws: Workspace, macro, x, mask, params, h0, c0, precision: str, need_moments: bool,
+                 dropout_p: float = 0.0, dropout_seed: int = 0, dropout_seed_dev=None,
+                 shard: Optional["MonthShard"] = None) -> CellPass:
+    """dlap_cell_fwd: the macro LSTM over the (whole) series and both nets on every stock-month of the panel."""
+    dev = x.device
+    T, N, F = x.shape
+    M, H = ws.plan.dims.M, max(ws.plan.dims.H, 1)
+    series_T = T if shard is None else shard.T_total
+    month0, stride = (0, 1) if shard is None else (shard.t0, shard.stride)
+    index = ws.panel_index(mask) if precision == "bf16x3" else None
+    save = torch.empty(series_T, 6 * H, dtype=torch.float32, device=dev)
+    a_t = torch.empty(series_T, 64, dtype=torch.float32, device=dev)
+    c_t = torch.empty(series_T, KM, dtype=torch.float32, device=dev)
+    hn = torch.empty(H, dtype=torch.float32, device=dev)
+    cn = torch.empty(H, dtype=torch.float32, device=dev)
+    fused = fuse_macro and precision == "bf16x3" and M > 0 and ws.plan.dims.H == 4 and ws.plan.sms >= 2
+    mio = DlapMacroIO(_ptr(macro) if M > 0 else None, series_T, month0, stride, _ptr(h0), _ptr(c0), _ptr(save),
+                      _ptr(a_t), _ptr(c_t), _ptr(hn), _ptr(cn), _ptr(ws.sync) if fused else None)
+    u = torch.empty(T, N, dtype=torch.float32, device=dev)
+    q = torch.empty(KM, T, N, dtype=torch.float32, device=dev) if need_moments else None
+    tens = _tensors(params)
+    _timed_call("dlap_cell_fwd", dev, ws.pp, _ptr(x), _ptr(mask), _ptr(index), C.byref(tens), C.byref(mio), _ptr(u),
+                _ptr(q), _PRECISIONS[precision], float(dropout_p), int(dropout_seed), _ptr(dropout_seed_dev),
+                _stream(dev))
+    ws.launches += 1 if fused else 2
+    return CellPass(u, q, save, a_t, c_t, hn, cn, index, mio, precision)
+
+
+@dataclass
+class Reduced:
+    """Outputs of dlap_step_reduce: per-month statistics, portfolio returns, [L_c, L_u, Sharpe, N_bar, ...], the
+    demeaned weights, and what the backward pass needs (unit loss coefficients G, the two dS sums)."""
+    row_stats: torch.Tensor
+    pr: torch.Tensor
+    scalars: torch.Tensor
+    w: torch.Tensor
+    G: Optional[torch.Tensor]
+    dS2: Optional[torch.Tensor]
+
+
+def step_reduce(ws: Workspace, cp: CellPass, R, mask, weighted_loss: bool, want_backward: bool,
+                shard: Optional["MonthShard"] = None) -> Reduced:
+    """dlap_step_reduce: every sum over stocks and over months, one launch (two around the all-reduce of the
+    per-stock sums when the panel is a month shard)."""
+    dev = R.device
+    T, N = R.shape
+    row_stats = torch.empty(T, RS_W, dtype=torch.float32, device=dev)
+    pr = torch.empty(T, dtype=torch.float32, device=dev)
+    scalars = torch.empty(SC_W, dtype=torch.float32, device=dev)
+    w = torch.empty(T, N, dtype=torch.float32, device=dev)
+    e = torch.empty(KM + 1, N, dtype=torch.float32, device=dev)
+    t_i = torch.empty(N, dtype=torch.float32, device=dev)
+    G = torch.empty(KM + 1, N, dtype=torch.float32, device=dev)
+    dS2 = torch.empty(T, 2, dtype=torch.float64, device=dev) if want_backward else None
+
+    def launch(lo, hi):
+        _timed_call("dlap_step_reduce", dev, ws.pp, _ptr(cp.u), _ptr(cp.q), _ptr(R), _ptr(mask), _ptr(cp.index),
+                    int(weighted_loss), _ptr(shard.n_bar) if shard is not None else None, lo, hi, _ptr(row_stats),
+                    _ptr(pr), _ptr(scalars), _ptr(w), _ptr(ws.col_part), _ptr(e), _ptr(t_i), _ptr(G),
+                    _ptr(ws.loss_part), _ptr(dS2), _ptr(ws.bar), _stream(dev))
+        ws.launches += 1
+
+    if shard is None:
+        launch(0, 4)
+    else:       # exchange 1: per-stock sums over ALL months
+        launch(0, 2)
+        with _timed_region("exchange_fwd", dev):
+            torch.distributed.all_reduce(ws.col_part[:(KM + 2) * N], group=shard.group)
+        launch(3, 4)
+    return Reduced(row_stats, pr, scalars, w, G, dS2)
 
 
 class GanStepFn(torch.autograd.Function):
-    """(L_c, L_u, pr, weights, sharpe, h_n, c_n) = step(panel, params)."""
+    """(L_c, L_u, pr, weights, sharpe, h_n, c_n) = step(panel, params).  `cells`: a CellPass of the same panel and
+    parameters made earlier (the evaluation cache of AssetPricingGAN), or None."""
 
     @staticmethod
-    def forward(ctx, opts: StepOptions, macro, x, R, mask, h0, c0, *params):
+    def forward(ctx, opts: StepOptions, cells: Optional[CellPass], macro, x, R, mask, h0, c0, *params):
         dev = x.device
         T, N, F = x.shape
         M = 0 if macro is None else macro.shape[1]
         H = 0 if macro is None else params[1].shape[1]
-        prec = _PRECISIONS[opts.precision]
         sh = opts.shard
+        want_backward = any(ctx.needs_input_grad)
         with torch.cuda.device(dev):
-            st = _stream(dev)
             ws = workspace(T, N, F, M, H, dev)
-            tens = _tensors(params)
-            index = ws.panel_index(mask) if opts.precision == "bf16x3" else None
-            # not while SMs are set aside for a concurrent panel pull: measured slower there (the recurrence's CTA
-            # ends up beside a pull CTA, and the step is bound by the bus anyway)
-            beside = overlap_macro and opts.precision == "bf16x3" and M > 0 and ws.reserve == 0
-            if sh is None:
-                wsm, t_base, t_stride = ws, 0, 1
-                save, a_t, c_t, hn, cn = macro_forward(ws, macro, params, h0, c0, beside)
-                a_loc, c_loc = a_t, c_t
-            else:   # LSTM replicated over the full series; this rank uses its rows of a_t / c_t
-                wsm, t_base, t_stride = workspace(sh.T_total, N, F, M, H, dev), sh.t0, sh.stride
-                save, a_t, c_t, hn, cn = macro_forward(wsm, macro, params, h0, c0, beside)
-                if opts.precision == "bf16x3":      # the kernel steps through the full tables itself
-                    a_loc, c_loc = a_t[sh.t0:], c_t[sh.t0:]
-                else:
-                    a_loc, c_loc, t_stride = sh.rows(a_t).contiguous(), sh.rows(c_t).contiguous(), 1
-            u = torch.empty(T, N, dtype=torch.float32, device=dev)
-            g = torch.empty(KM, T, N, dtype=torch.float32, device=dev) if opts.need_moments else None
-            _timed_call("dlap_cell_fwd", dev, ws.pp, _ptr(x), _ptr(R), _ptr(mask), _ptr(index), C.byref(tens), _ptr(a_loc),
-                      _ptr(c_loc), _ptr(u), _ptr(g), _ptr(ws.row_part), prec, float(opts.dropout_p),
-                      int(opts.dropout_seed), _ptr(opts.dropout_seed_dev),
-                      _ptr(wsm.months_ready) if beside else None, t_base, t_stride, st)
-            if beside:
-                join_macro(wsm)
-            row_stats = torch.empty(T, RS_W, dtype=torch.float32, device=dev)
-            pr = torch.empty(T, dtype=torch.float32, device=dev)
-            scalars = torch.empty(SC_W, dtype=torch.float32, device=dev)
-            _timed_call("dlap_row_finish", dev, ws.pp, _ptr(ws.row_part), _ptr(index), prec,
-                      int(opts.weighted_loss),
-                      _ptr(sh.n_bar) if sh is not None else None, _ptr(row_stats), _ptr(pr),
-                      _ptr(scalars), st)
-            w = torch.empty(T, N, dtype=torch.float32, device=dev)
-            _timed_call("dlap_col_partial", dev, ws.pp, _ptr(g), _ptr(R), _ptr(mask), _ptr(u), _ptr(row_stats),
-                      _ptr(index), _ptr(ws.col_part), _ptr(w), st)
-            e = torch.empty(KM + 1, N, dtype=torch.float32, device=dev)
-            t_i = torch.empty(N, dtype=torch.float32, device=dev)
-            if sh is None:
-                col, nsplit = ws.col_part, ws.plan.col_splits
-            else:   # exchange 1: per-stock sums over ALL months
-                with _timed_region("exchange_fwd", dev):
-                    col = ws.col_part.view(ws.plan.col_splits, KM + 2, N)
-                    col = col[0] if ws.plan.col_splits == 1 else col.sum(dim=0)   # one split: reduce it in place
-                    torch.distributed.all_reduce(col, group=sh.group)
-                nsplit = 1
-            _timed_call("dlap_loss_finish", dev, ws.pp, _ptr(col), nsplit, _ptr(e), _ptr(t_i),
-                      _ptr(ws.loss_part), _ptr(ws.counter), _ptr(scalars), st)
-            ws.launches += 5
+            cp = cells
+            if cp is None:
+                cp = cell_forward(ws, macro, x, mask, params, h0, c0, opts.precision, opts.need_moments,
+                                  opts.dropout_p, opts.dropout_seed, opts.dropout_seed_dev, sh)
+            red = step_reduce(ws, cp, R, mask, opts.weighted_loss, want_backward, sh)
         ctx.set_materialize_grads(False)      # unused outputs come back as None, not as zero tensors (fill kernels)
         ctx.save_for_backward(x, R, mask, macro, h0, c0, *params)
-        ctx.opts, ctx.ws = opts, ws
-        ctx.inter = (save, a_t, c_t, row_stats, scalars, g, e, t_i, index)
+        ctx.opts, ctx.ws, ctx.cp, ctx.red = opts, ws, cp, red
+        scalars = red.scalars
         l_c, l_u, sharpe = scalars[SC_LC], scalars[SC_LU], scalars[SC_SHARPE]
-        ctx.mark_non_differentiable(w, sharpe, hn, cn)
-        return l_c, l_u, pr, w, sharpe, hn, cn
+        ctx.mark_non_differentiable(red.w, sharpe, cp.hn, cp.cn)
+        return l_c, l_u, red.pr, red.w, sharpe, cp.hn, cp.cn
 
     @staticmethod
     def backward(ctx, g_lc, g_lu, g_pr, *_unused):
         x, R, mask, macro, h0, c0, *params = ctx.saved_tensors
-        save, a_t, c_t, row_stats, scalars, g, e, t_i, index = ctx.inter
-        opts, ws = ctx.opts, ctx.ws
+        opts, ws, cp, red = ctx.opts, ctx.ws, ctx.cp, ctx.red
         sh = opts.shard
         dev = x.device
         T, N, F = x.shape
         M = 0 if macro is None else macro.shape[1]
-        need = ctx.needs_input_grad[7:]
+        need = ctx.needs_input_grad[8:]
         want_sdf = any(need[:10])
-        want_mom = any(need[10:]) and g is not None
+        want_mom = any(need[10:]) and cp.q is not None
         if not (want_sdf or want_mom):
-            return (None,) * (7 + len(params))
+            return (None,) * (8 + len(params))
         prec = _PRECISIONS[_BWD_PRECISION[opts.precision]]
 
         def scalar(t):
@@ -419,24 +452,16 @@ class GanStepFn(torch.autograd.Function):
         with torch.cuda.device(dev):
             st = _stream(dev)
             tens = _tensors(params)
-            G = torch.empty(KM + 1, N, dtype=torch.float32, device=dev)
-            _timed_call("dlap_loss_coeff", dev, ws.pp, _ptr(e), _ptr(t_i), _ptr(g_lc) if g is not None else None,
-                      _ptr(g_lu), _ptr(G), st)
-            _timed_call("dlap_ds_rows", dev, ws.pp, _ptr(g), _ptr(R), _ptr(mask), _ptr(G), _ptr(index), _ptr(ws.ds_part), st)
-            if sh is None:
-                a_loc, c_loc = a_t, c_t
-            else:
-                a_loc, c_loc = sh.rows(a_t).contiguous(), sh.rows(c_t).contiguous()
-            _timed_call("dlap_cell_bwd", dev, ws.pp, _ptr(x), _ptr(R), _ptr(mask), _ptr(index), C.byref(tens), _ptr(a_loc),
-                      _ptr(c_loc), _ptr(row_stats), _ptr(ws.ds_part), _ptr(g_pr), _ptr(G), _ptr(scalars),
-                      int(opts.weighted_loss), int(want_sdf), int(want_mom), _ptr(ws.wpart),
-                      _ptr(ws.dadc_part), prec, float(opts.dropout_p), int(opts.dropout_seed),
-                      _ptr(opts.dropout_seed_dev), st)
+            _timed_call("dlap_cell_bwd", dev, ws.pp, _ptr(x), _ptr(R), _ptr(mask), _ptr(cp.index), C.byref(tens),
+                        C.byref(cp.mio), _ptr(red.row_stats), _ptr(red.dS2), _ptr(g_lc) if cp.q is not None else None,
+                        _ptr(g_lu), _ptr(g_pr), _ptr(red.G), _ptr(red.scalars), int(opts.weighted_loss), int(want_sdf),
+                        int(want_mom), _ptr(ws.wpart), _ptr(ws.dadc_part), prec, float(opts.dropout_p),
+                        int(opts.dropout_seed), _ptr(opts.dropout_seed_dev), st)
+            ws.launches += 1
             # All twelve gradient tensors are views of one flat buffer.  Month-sharded: the buffer starts with the
-            # [T_total,72] da_t | dc_t rows (this rank fills its slab) and is zero-filled, so that exchange 2 is ONE
+            # [T_total,72] da_t | dc_t rows (this rank fills its months) and is zero-filled, so that exchange 2 is ONE
             # all-reduce over it -- gradients that are computed later (LSTM, b1, bq) are still zero.  Otherwise no
-            # fill: dlap_grad_finish and dlap_macro_bwd write every element of every gradient that is handed back
-            # (a fill is one more kernel in a chain of short dependent ones).
+            # fill: the kernels write every element of every gradient that is handed back.
             sizes = [0 if p is None else p.numel() for p in params]
             head = 0 if sh is None else sh.T_total * 72
             buf = (torch.empty if sh is None else torch.zeros)(head + sum(sizes), dtype=torch.float32, device=dev)
@@ -447,59 +472,42 @@ class GanStepFn(torch.autograd.Function):
                 off += n
             gt = _tensors(grads)
             if sh is None:
-                dadc_all = dadc = torch.empty(T, 72, dtype=torch.float32, device=dev)
-            else:
-                dadc_all = buf[:head].view(sh.T_total, 72)
-                dadc = sh.rows(dadc_all) if sh.stride == 1 else torch.empty(T, 72, dtype=torch.float32, device=dev)
-            _timed_call("dlap_grad_finish", dev, ws.pp, _ptr(ws.wpart), _ptr(ws.dadc_part), _ptr(index), prec, int(want_sdf),
-                      int(want_mom), C.byref(gt), _ptr(dadc), st)
-            ws.launches += 4
-            if sh is not None and sh.stride != 1:
-                sh.rows(dadc_all).copy_(dadc)
-            if sh is None:
-                wsm = ws
+                dadc = torch.empty(T, 72, dtype=torch.float32, device=dev)
+                _timed_call("dlap_macro_bwd", dev, ws.pp, _ptr(macro), C.byref(tens), _ptr(h0), _ptr(c0), _ptr(cp.save),
+                            _ptr(dadc), _ptr(ws.dpre), int(want_sdf), int(want_mom), C.byref(gt), _ptr(ws.wpart),
+                            _ptr(ws.dadc_part), _ptr(cp.index), prec, st)
+                ws.launches += 2
             else:   # exchange 2: per-cell weight grads + every month's da_t | dc_t row
+                dadc_all = buf[:head].view(sh.T_total, 72)
+                _timed_call("dlap_grad_finish", dev, ws.pp, _ptr(ws.wpart), _ptr(ws.dadc_part), _ptr(cp.index), prec,
+                            int(want_sdf), int(want_mom), C.byref(gt), _ptr(dadc_all[sh.t0:]), int(sh.stride), st)
                 wsm = workspace(sh.T_total, N, F, M, ws.plan.dims.H, dev)
                 with _timed_region("exchange_bwd", dev):
                     torch.distributed.all_reduce(buf, group=sh.group)
-            _timed_call("dlap_macro_bwd", dev, wsm.pp, _ptr(macro), C.byref(tens), _ptr(h0), _ptr(c0), _ptr(save),
-                      _ptr(dadc_all), _ptr(wsm.dpre), int(want_sdf), int(want_mom), C.byref(gt), st)
-            ws.launches += 2 if (want_sdf and M > 0) else 1
+                _timed_call("dlap_macro_bwd", dev, wsm.pp, _ptr(macro), C.byref(tens), _ptr(h0), _ptr(c0),
+                            _ptr(cp.save), _ptr(dadc_all), _ptr(wsm.dpre), int(want_sdf), int(want_mom), C.byref(gt),
+                            None, None, None, prec, st)
+                ws.launches += 3 if (want_sdf and M > 0) else 2
         out = []
         for i, gr in enumerate(grads):
             live = need[i] and ((i < 10 and want_sdf) or (i >= 10 and want_mom))
             out.append(gr if live else None)
-        return (None,) * 7 + tuple(out)
+        return (None,) * 8 + tuple(out)
 
 
 def sdf_weights(macro, x, mask, params, h0=None, c0=None, normalized=False, precision="fp32",
-                weighted_loss=True):
+                with_moments=False):
     """Inference path of SDFNetwork.forward / get_weights (src/model.py:221-281, :565-594):
-    weights [T,N] (demeaned, optionally |w|-normalised per month) and the final LSTM state."""
+    weights [T,N] (demeaned, optionally |w|-normalised per month) and the per-cell pass they came from
+    (with_moments: the moment outputs are computed too, for a forward() of the same panel that may follow)."""
     dev = x.device
     T, N, F = x.shape
     M = 0 if macro is None else macro.shape[1]
     H = 0 if macro is None else params[1].shape[1]
     with torch.cuda.device(dev):
-        st = _stream(dev)
         ws = workspace(T, N, F, M, H, dev)
-        tens = _tensors(params)
-        index = ws.panel_index(mask) if precision == "bf16x3" else None
-        beside = overlap_macro and precision == "bf16x3" and M > 0 and ws.reserve == 0
-        save, a_t, c_t, hn, cn = macro_forward(ws, macro, params, h0, c0, beside)
-        u = torch.empty(T, N, dtype=torch.float32, device=dev)
-        _lib.call("dlap_cell_fwd", ws.pp, _ptr(x), None, _ptr(mask), _ptr(index), C.byref(tens), _ptr(a_t), _ptr(c_t),
-                  _ptr(u), None, _ptr(ws.row_part), _PRECISIONS[precision], 0.0, 0, None,
-                  _ptr(ws.months_ready) if beside else None, 0, 1, st)
-        if beside:
-            join_macro(ws)
-        row_stats = torch.empty(T, RS_W, dtype=torch.float32, device=dev)
-        pr = torch.empty(T, dtype=torch.float32, device=dev)
-        scalars = torch.empty(SC_W, dtype=torch.float32, device=dev)
-        _timed_call("dlap_row_finish", dev, ws.pp, _ptr(ws.row_part), _ptr(index), _PRECISIONS[precision], int(weighted_loss), None,
-                  _ptr(row_stats),
-                  _ptr(pr), _ptr(scalars), st)
+        cp = cell_forward(ws, macro, x, mask, params, h0, c0, precision, with_moments)
         w = torch.empty(T, N, dtype=torch.float32, device=dev)
-        _lib.call("dlap_weights", ws.pp, _ptr(u), _ptr(mask), _ptr(row_stats), _ptr(index), int(normalized), _ptr(w), st)
-        ws.launches += 4
-    return w, hn, cn, save
+        _lib.call("dlap_weights", ws.pp, _ptr(cp.u), _ptr(mask), _ptr(cp.index), int(normalized), _ptr(w), _stream(dev))
+        ws.launches += 1
+    return w, cp

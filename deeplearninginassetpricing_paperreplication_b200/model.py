@@ -151,24 +151,29 @@ class SDFNetwork(nn.Module):
     def forward(self, macro_features, individual_features, mask, hidden=None):
         """-> (weights [T,N], new_hidden).  Stand-alone use is the inference path (no autograd
         graph is attached to the returned weights)."""
-        return _weights(self, None, macro_features, individual_features, mask, hidden, False)
+        return _weights(self, None, macro_features, individual_features, mask, hidden, False)[:2]
 
 
-def _weights(sdf: SDFNetwork, moment: Optional[MomentNetwork], macro, x, mask, hidden, normalized,
-             precision="fp32"):
+def _weights(sdf: SDFNetwork, moment_params, macro, x, mask, hidden, normalized, precision="fp32"):
+    """-> (weights, new_hidden, CellPass).  moment_params: [Wq, bq] to have the moment outputs computed in the same
+    per-cell pass (for a forward() on the same panel that may follow), or None."""
     Fn.check_panel(macro, x, None, mask)
     with_macro = macro is not None
     params = [p.detach() if p is not None else None for p in sdf.kernel_params(with_macro)]
     dev = x.device
     T, N, F = x.shape
     M = macro.shape[1] if with_macro else 0
-    # the moment net takes no part in the weights; the kernel ABI still wants its two tensors
-    z = torch.zeros(8, M + F, dtype=torch.float32, device=dev), torch.zeros(8, dtype=torch.float32, device=dev)
+    if moment_params is None:
+        # the moment net takes no part in the weights; the kernel ABI still wants its two tensors
+        mp = [torch.zeros(8, M + F, dtype=torch.float32, device=dev), torch.zeros(8, dtype=torch.float32, device=dev)]
+    else:
+        mp = [p.detach() for p in moment_params]
     H = sdf.macro_lstm.output_dim if with_macro else 0
     h0, c0 = _hidden_pair(hidden, H, dev) if with_macro else (None, None)
-    w, hn, cn, _ = Fn.sdf_weights(macro, x, mask, params + list(z), h0, c0, normalized, precision)
-    new_hidden = (hn.view(1, 1, H), cn.view(1, 1, H)) if with_macro else None
-    return w, new_hidden
+    w, cp = Fn.sdf_weights(macro, x, mask, params + mp, h0, c0, normalized, precision,
+                           with_moments=moment_params is not None)
+    new_hidden = (cp.hn.view(1, 1, H), cp.cn.view(1, 1, H)) if with_macro else None
+    return w, new_hidden, cp
 
 
 class StepOutputs(dict):
@@ -269,8 +274,9 @@ class AssetPricingGAN(nn.Module):
                               need_moments=(phase != 'unconditional'), precision=self._precision(x.shape[2]),
                               dropout_p=p_drop, dropout_seed=seed, dropout_seed_dev=seed_dev,
                               shard=self.month_shard)
+        cells = self._cached_cells(macro_features, x, mask, hidden, params, opts)
         l_c, l_u, pr, w, sharpe, hn, cn = Fn.GanStepFn.apply(
-            opts, macro_features, x, returns, mask, h0, c0, *params)
+            opts, cells, macro_features, x, returns, mask, h0, c0, *params)
         zero = self._zero(dev)
         if phase == 'unconditional':            # src/model.py:524-528
             loss_unc, loss_cond, total = l_u, zero, l_u
@@ -300,10 +306,55 @@ class AssetPricingGAN(nn.Module):
         """CUDA-graph capture of zero_grad + forward + backward on a resident panel (see GraphedStep)."""
         return GraphedStep(self, macro_features, individual_features, returns, mask, hidden, phase)
 
+    # -- evaluation cache (SURVEY.md §8f row 1) ---------------------------------------------------------
+    # evaluate() of src/train.py:106-153 calls get_weights(normalized=True) and then forward(phase='conditional') on
+    # the same panel with the same parameters, i.e. two full passes over every stock-month.  Under no_grad in eval
+    # mode, get_weights therefore also computes the moment outputs in its per-cell pass and keeps (u, q, LSTM state)
+    # keyed on the identity and version counters of panel and parameters; the forward() that follows finds them and
+    # runs only the reductions.  Anything else -- another panel, an optimiser step, train mode, grad mode -- misses.
+    eval_cache = True
+
+    @staticmethod
+    def _cache_key(macro, x, mask, hidden, params, precision):
+        """(scalars, tensors): version counters and data pointers of panel and parameters, and the tensor objects
+        themselves -- the cache keeps weak references to those and matches by identity, so a recycled id() or
+        address of a dead tensor can never hit."""
+        tensors = [t for t in (macro, x, mask) + (tuple(hidden) if hidden is not None else ()) + tuple(params)
+                   if t is not None]
+        return (tuple((t._version, t.data_ptr()) for t in tensors), macro is None, hidden is None, precision), tensors
+
+    def _cached_cells(self, macro, x, mask, hidden, params, opts):
+        hit = getattr(self, "_cells", None)
+        self._cells = None                        # one use: the cache never outlives the evaluate() it was made for
+        if hit is None or torch.is_grad_enabled() or self.training or opts.shard is not None:
+            return None
+        scalars, refs, cp = hit
+        now, tensors = self._cache_key(macro, x, mask, hidden, params, opts.precision)
+        if now != scalars or len(refs) != len(tensors) or any(r() is not t for r, t in zip(refs, tensors)):
+            return None
+        if opts.need_moments and cp.q is None:
+            return None
+        return cp
+
     def get_weights(self, macro_features, individual_features, mask, hidden=None, normalized: bool = False):
         """src/model.py:565-594."""
-        return _weights(self.sdf_net, self.moment_net, macro_features, individual_features, mask, hidden,
-                        normalized, self._precision(individual_features.shape[2]))
+        precision = self._precision(individual_features.shape[2])
+        keep = (self.eval_cache and not torch.is_grad_enabled() and not self.training and self.month_shard is None)
+        mom = None
+        if keep:
+            try:
+                params = self._kernel_params(macro_features is not None)
+                mom = params[-2:]
+            except NotImplementedError:
+                keep = False
+        w, new_hidden, cp = _weights(self.sdf_net, mom, macro_features, individual_features, mask, hidden,
+                                     normalized, precision)
+        self._cells = None
+        if keep:
+            import weakref
+            scalars, tensors = self._cache_key(macro_features, individual_features, mask, hidden, params, precision)
+            self._cells = (scalars, [weakref.ref(t) for t in tensors], cp)
+        return w, new_hidden
 
     def get_sdf_factor(self, macro_features, individual_features, returns, mask, hidden=None,
                        normalized: bool = True):

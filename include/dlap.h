@@ -7,7 +7,8 @@
  * (deeplearninginassetpricing_paperreplication_b200/model.py) is a thin ctypes caller of these.
  *
  * Conventions
- *   - every pointer is a DEVICE pointer on the current CUDA device unless it says "host";
+ *   - every pointer is a DEVICE pointer on the current CUDA device unless it says "host" (structs that are
+ *     passed by pointer -- plan, tensors, macro_io -- are host structs holding device pointers);
  *     all floating-point data is fp32, row-major, contiguous; `mask` is torch.bool bytes (0/1);
  *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream); calls only
  *     enqueue work, they never synchronise and never allocate;
@@ -27,7 +28,7 @@
 extern "C" {
 #endif
 
-#define DLAP_ABI_VERSION 3
+#define DLAP_ABI_VERSION 4
 
 enum {
   DLAP_OK = 0,
@@ -43,10 +44,10 @@ enum {
 
 /* arithmetic of the per-cell contractions */
 enum {
-  DLAP_PREC_FP32 = 0,     /* exact fp32 FFMA on CUDA cores */
+  DLAP_PREC_FP32 = 0,     /* exact fp32 FFMA on CUDA cores; dense u / q */
   DLAP_PREC_BF16X3 = 1    /* tcgen05 BF16 MMAs on hi/lo-split operands, 3 products per fp32 product,
                              fp32 accumulation in TMEM; needs F <= 46 and the valid-cell index of
-                             dlap_panel_index: only unmasked stock-months are visited */
+                             dlap_panel_index: only unmasked stock-months are visited; u / q left-packed */
 };
 
 typedef struct dlap_dims {
@@ -57,15 +58,18 @@ typedef struct dlap_dims {
 typedef struct dlap_plan {
   dlap_dims dims;
   int32_t tpm;            /* tiles (128 stocks) per month */
-  int32_t grid_cell;      /* persistent CTAs of the per-cell kernels (= SM count) */
-  int32_t col_splits;     /* month chunks of the per-stock (column) reduction */
-  int32_t row_splits;     /* stock chunks of the per-month (row) reduction of dS */
+  int32_t sms;            /* SMs the kernels of this plan spread over (the device's; a caller that overlaps another
+                             kernel, e.g. dlap_panel_pull, lowers it together with grid_cell) */
+  int32_t grid_cell;      /* persistent CTAs of the per-cell kernels (<= sms) */
+  int32_t cooperative;    /* 1: kernels that synchronise across their grid (dlap_step_reduce, the fused dlap_cell_fwd)
+                             are launched with cudaLaunchCooperativeKernel, which refuses a grid that cannot be
+                             co-resident; 0: plain launches of the same grids (needed when another kernel is meant to
+                             run beside them on the SMs left free: a cooperative grid does not share the device) */
+  int32_t col_splits;     /* month chunks of the per-stock (column) sums */
   int32_t ldw1;           /* row pitch of fc_layers.0.weight  = F + H (F when M = 0) */
   int32_t ldwq;           /* row pitch of moment output_proj.weight = M + F */
-  int64_t row_part_bytes;   /* double [T, tpm, 4 slots, 4]  */
   int64_t col_part_bytes;   /* double [col_splits, 10, N]   */
   int64_t loss_part_bytes;  /* double [ceil(N/64), 2]       */
-  int64_t ds_part_bytes;    /* double [T, row_splits]       */
   int64_t wpart_bytes;      /* float  [grid_cell, wstride]  */
   int64_t dadc_part_bytes;  /* float  [T, max(tpm,4), 72]   */
   int64_t lstm_save_bytes;  /* float  [T, 6H]               */
@@ -83,33 +87,48 @@ typedef struct dlap_tensors {
   float *wq, *bq;                     /* moment_net.output_proj.{weight [8,M+F], bias [8]} */
 } dlap_tensors;
 
+/* The macro side of a per-cell call.  The per-month biases that replace the reference's two tile-over-N concats,
+ * a_t = W1[:,F:].h_t + b1 (src/model.py:253-255, :211) and c_t = Wq[:,:M].macro_t + bq (src/model.py:514-516, :152),
+ * live in tables over a SERIES of series_T months; month t of the panel is month month0 + t * month_stride of that
+ * series (a month shard that owns every n-th month passes its first month and n; otherwise 0 and 1, and series_T =
+ * the plan's T).
+ *   dlap_cell_fwd: macro != NULL: the call also runs MacroLSTM.forward (src/model.py:50-73) over the whole series
+ *     and fills lstm_save [series_T,6H] (h,c,i,f,g,o), a_t [series_T,64], c_t [series_T,8], hn, cn [H] (h0 / c0 [H]
+ *     may be NULL: zero state).  macro == NULL: a_t and c_t are inputs (with M = 0 the call fills them with b1 / bq).
+ *   dlap_cell_bwd: reads a_t, c_t, month0, month_stride only.
+ * sync (device, two int32, zero when the call starts and zero again when it has finished; may be NULL): BF16X3 with
+ * macro and H = 4 only.  When given, the LSTM runs on one CTA of the per-cell kernel's own grid, beside the per-cell
+ * work, and publishes the months as they complete (the reference computes the whole LSTM first, src/model.py:247-255;
+ * the result is the same, bit for bit); sync[0] counts the published months.  NULL: the LSTM is a launch of its own
+ * in front of the per-cell kernel. */
+typedef struct dlap_macro_io {
+  const float* macro;
+  int32_t series_T, month0, month_stride;
+  const float *h0, *c0;
+  float *lstm_save, *a_t, *c_t, *hn, *cn;
+  int32_t* sync;
+} dlap_macro_io;
+
 int dlap_abi_version(void);
 const char* dlap_error_string(int code);
 
 /* Geometry for a panel shape on CUDA device `device` (host-side, no GPU work). */
 int dlap_make_plan(const dlap_dims* dims, int device, dlap_plan* out);
 
-/* MacroLSTM.forward (src/model.py:50-73, nn.LSTM at :39-45) plus the two per-month biases that
- * replace the tile-over-N concats: a_t = W1[:,F:].h_t + b1 (src/model.py:253-255, :211) and
- * c_t = Wq[:,:M].macro_t + bq (src/model.py:514-516, :152).  h0/c0 [H] may be NULL (zero state).
- * Outputs: lstm_save [T,6H] (h,c,i,f,g,o), a_t [T,64], c_t [T,8], hn/cn [H].  With M = 0 only
- * a_t = b1 and c_t = bq are produced.  xproj_scratch: kept for ABI stability ([T,4H] floats until ABI 2;
- * is not used any more, may be NULL).  One launch of a single CTA: eleven warps project the months'
- * inputs, one warp runs the recurrence behind them, one turns h_t into a_t rows behind that.
- * months_ready (device, one int32, may be NULL): progress counter of the recurrence.  The caller zeroes it
- * on a stream ordered before this call AND before the dlap_cell_fwd that is to consume it; the kernel
- * then keeps *months_ready = number of leading months whose a_t and c_t rows are written.  It lets
- * dlap_cell_fwd run beside the recurrence on another stream instead of after it (the reference computes
- * the whole LSTM first, src/model.py:247-255; the result is the same). */
+/* MacroLSTM.forward on its own (src/model.py:50-73, nn.LSTM at :39-45) plus the two per-month bias tables; the
+ * series is the plan's T months.  h0/c0 [H] may be NULL (zero state).  Outputs: lstm_save [T,6H] (h,c,i,f,g,o),
+ * a_t [T,64], c_t [T,8], hn/cn [H].  With M = 0 only a_t = b1 and c_t = bq are produced.  One launch of a single
+ * CTA: eleven warps project the months' inputs, one warp runs the recurrence behind them, one turns h_t into a_t
+ * rows behind that. */
 int dlap_macro_fwd(const dlap_plan* plan, const float* macro, const dlap_tensors* params,
                    const float* h0, const float* c0, float* lstm_save, float* a_t, float* c_t,
-                   float* hn, float* cn, float* xproj_scratch, int32_t* months_ready, void* stream);
+                   float* hn, float* cn, void* stream);
 
 /* Valid-cell index of the panel: for every month the ascending list of stocks with mask != 0, cut into
  * tiles of <= 128 cells (layout: csrc/cell_f32.cuh).  The reference runs both nets over every cell and
  * multiplies by the mask afterwards (src/model.py:261-279, :363, :376-382, :428), so a masked cell
  * contributes exactly 0 to every weight, loss and gradient; the BF16X3 kernels use this list to skip
- * those cells altogether (u and g are then written for unmasked cells only, left-packed per month).  Integer work, bit-exact;
+ * those cells altogether (u and q are then written for unmasked cells only, left-packed per month).  Integer work, bit-exact;
  * the mask contract is src/data_loader.py:50-65.  Rebuild whenever the mask bytes change.  Two launches. */
 int dlap_panel_index(const dlap_plan* plan, const uint8_t* mask, int32_t* index, void* stream);
 
@@ -121,60 +140,55 @@ int dlap_panel_index(const dlap_plan* plan, const uint8_t* mask, int32_t* index,
  * src/data_loader.py:61-65).  One memset + one launch of `ctas` CTAs of 256 threads (0: plan->grid_cell; a
  * handful saturates PCIe).  clear = 0 skips the memset: the caller has zeroed x_dev itself (a loader that
  * double-buffers its panels clears a buffer as soon as its step is done, while the GPU has SMs to spare,
- * instead of in front of the pull), or does not care what the masked rows hold.  To overlap the pull of the next panel with a step, lower plan->grid_cell of the
- * plan the per-cell kernels run with by the same number: they take one CTA per SM and all of its registers. */
+ * instead of in front of the pull), or does not care what the masked rows hold.  To overlap the pull of the next
+ * panel with a step, lower plan->sms and plan->grid_cell of the plan the step runs with by the same number and
+ * clear plan->cooperative: the per-cell kernels take one CTA per SM and all of its registers. */
 int dlap_panel_pull(const dlap_plan* plan, const float* x_host, const int32_t* index, float* x_dev, int ctas, int clear,
                     void* stream);
 
 /* SDFNetwork.forward body on every stock-month (src/model.py:251-271) and MomentNetwork.forward
- * (src/model.py:132-161 with the input of :514-518): u = MLP(x | a_t) [T,N];
- * g = tanh(Wqx.x + c_t) * R * m [8,T,N] (g NULL: moment net skipped, phase 'unconditional');
- * row_part = per-tile sums of m, m u, m u R, m R.  R may be NULL (weights-only inference).
+ * (src/model.py:132-161 with the input of :514-518), and -- see dlap_macro_io -- the macro LSTM in front of them:
+ * u = MLP(x | a_t) [T,N];  q = tanh(Wqx.x + c_t) [8,T,N] (q NULL: moment net skipped, phase 'unconditional').
+ * Everything that sums over stocks or months is dlap_step_reduce's.
  * dropout_p > 0 (model.train(), src/model.py:213, src/train.py:66): each hidden unit of each
  * stock-month is dropped with probability round(p*65536)/65536 by a counter-based generator keyed
  * on (dropout_seed, stock-month, layer, unit); pass the same seed to dlap_cell_bwd.  dropout_seed_dev (device,
  * one uint64, may be NULL) overrides dropout_seed when given: the seed of a step that is replayed from a CUDA
  * graph has to live in device memory.
- * index: dlap_panel_index output, required for BF16X3 (row_part is then per valid-cell tile; u and g are
- * written for unmasked cells only and left-packed: the j-th unmasked stock of month t at [t*N + j]); ignored
- * (may be NULL) for FP32 (dense u, g).
- * months_ready (may be NULL; BF16X3 only, DLAP_E_PRECISION otherwise): the progress counter handed to a
- * dlap_macro_fwd that was ENQUEUED BEFORE this call on another stream and may still be running: the kernel
- * waits for a month's a_t / c_t row before it touches the month's first tile, visits the tiles in an
- * order that follows the months, and leaves one SM to the recurrence.  a_t and c_t must not be written
- * by anyone else meanwhile.  months_base: month 0 of this panel is month months_base of the series the
- * recurrence runs over (a month shard passes its first month and its slab of a_t / c_t; 0 otherwise).
- * With NULL, a_t and c_t are complete when the kernel starts (stream order) and months_base is ignored.
- * months_stride (>= 1; BF16X3 only when != 1): month t of this panel uses row t * months_stride of a_t and
- * c_t (and is month months_base + t * months_stride of the recurrence) -- a rank that owns every n-th
- * month of a series passes the full tables, offset to its first month, and n. */
-int dlap_cell_fwd(const dlap_plan* plan, const float* x, const float* R, const uint8_t* mask,
-                  const int32_t* index, const dlap_tensors* params, const float* a_t, const float* c_t, float* u,
-                  float* g, double* row_part, int precision, float dropout_p, uint64_t dropout_seed,
-                  const uint64_t* dropout_seed_dev, const int32_t* months_ready, int months_base, int months_stride,
-                  void* stream);
+ * index: dlap_panel_index output, required for BF16X3 (u and q are then written for unmasked cells only and
+ * left-packed: the j-th unmasked stock of month t at [t*N + j]); ignored (may be NULL) for FP32 (dense u, q).
+ * Launches: BF16X3 with macro, H = 4 and mio->sync: ONE (the recurrence is a CTA of the per-cell grid); otherwise the
+ * macro kernel (or the constant-bias fill when M = 0), then the per-cell kernel. */
+int dlap_cell_fwd(const dlap_plan* plan, const float* x, const uint8_t* mask, const int32_t* index,
+                  const dlap_tensors* params, const dlap_macro_io* mio, float* u, float* q, int precision,
+                  float dropout_p, uint64_t dropout_seed, const uint64_t* dropout_seed_dev, void* stream);
 
-/* Per-month statistics: N_t, mu_t (src/model.py:276-278), P_t, portfolio return pr_t and
- * S_t = 1 + pr_t (src/model.py:359-367, :380), Rbar_t; N_bar (src/model.py:360) and the Sharpe
- * ratio of pr (src/model.py:551) into scalars[3], scalars[2].  n_bar_in (device, 1 float) overrides
- * N_bar when the panel is one month-shard of a larger one; NULL otherwise.  precision: the selector
- * and index dlap_cell_fwd ran with (they fix the layout of row_part). */
-int dlap_row_finish(const dlap_plan* plan, const double* row_part, const int32_t* index, int precision,
-                    int weighted_loss, const float* n_bar_in, float* row_stats, float* pr, float* scalars,
-                    void* stream);
+/* Every sum of the step over stocks (per month) and over months (per stock), one launch whose CTAs step through
+ * the phases phase_lo .. phase_hi with grid-wide barriers in between (csrc/step_reduce.cu):
+ *   0  N_t, mu_t (src/model.py:276-278), P_t, Rbar_t from u and R                          -> row_stats [T,8]
+ *   1  N_bar (src/model.py:360; n_bar_in, device, overrides it when the panel is a month shard), portfolio return
+ *      pr_t and S_t = 1 + pr_t (src/model.py:359-367, :380), Sharpe ratio of pr (src/model.py:551)
+ *                                                      -> row_stats, pr [T], scalars[2] = Sharpe, scalars[3] = N_bar;
+ *      per stock and month chunk: sum_t q_k R S_t, sum_t R m S_t, sum_t m (src/model.py:376, :382, :428)
+ *                                                      -> col_part [col_splits,10,N]
+ *      and the demeaned weights w = m (u - mu_t) (src/model.py:271-279)      -> w_out [T,N] when non-NULL
+ *   2  the month chunks summed into chunk 0 of col_part (month shards all-reduce col_part[0] after this phase)
+ *   3  e_ki = colsum / T_i (src/model.py:382, :428) -> e [9,N], t_i [N]; the loss coefficients for UNIT cotangents,
+ *      G_ki = 2 e_ki / (K N T_i), G_8i = 2 e0_i / (N T_i) (autograd at src/train.py:84)  -> G [9,N]
+ *   4  L_c = mean_k mean_i e_ki^2, L_u = mean_i e0_i^2 (src/model.py:385, :429-431) -> scalars[0], scalars[1];
+ *      dS2 [T,2] (double): dS_t for unit cotangents of L_c and of L_u; dS2 NULL: no backward pass will follow
+ * Single device: phases 0..4 in one launch.  q may be NULL (phase 'unconditional').  index: the valid-cell index
+ * when u and q come from the BF16X3 dlap_cell_fwd, NULL for FP32.  bar (device, one uint32, zero when the call
+ * starts, zero again when it has finished): the barrier word. */
+int dlap_step_reduce(const dlap_plan* plan, const float* u, const float* q, const float* R, const uint8_t* mask,
+                     const int32_t* index, int weighted_loss, const float* n_bar_in, int phase_lo, int phase_hi,
+                     float* row_stats, float* pr, float* scalars, float* w_out, double* col_part, float* e,
+                     float* t_i, float* G, double* loss_part, double* dS2, uint32_t* bar, void* stream);
 
-/* Per-stock sums over the months of each chunk: sum_t g_k S_t, sum_t R m S_t, sum_t m
- * (src/model.py:376, :382, :428) into col_part [col_splits,10,N]; fused: the demeaned weights
- * w = m (u - mu_t) (src/model.py:271-279) into w_out [T,N] when non-NULL.  g may be NULL.  u and g are
- * read at unmasked cells only.  index: the valid-cell index when u and g come from the BF16X3 dlap_cell_fwd
- * (they are then left-packed: the j-th unmasked stock of month t sits at [t*N + j]); NULL for FP32 (dense). */
-int dlap_col_partial(const dlap_plan* plan, const float* g, const float* R, const uint8_t* mask,
-                     const float* u, const float* row_stats, const int32_t* index, double* col_part,
-                     float* w_out, void* stream);
-
-/* e_ki = colsum / T_i, L_c = mean_k mean_i e_ki^2, L_u = mean_i e0_i^2 (src/model.py:382-385,
- * :428-431) -> e [9,N], t_i [N], scalars[0] = L_c, scalars[1] = L_u.  `nsplit` chunks are summed
- * in order (1 after an all-reduce across month shards).  counter: one zero-initialised uint32. */
+/* The loss stage on its own, for a caller that holds per-stock sums from elsewhere: e_ki = colsum / T_i,
+ * L_c = mean_k mean_i e_ki^2, L_u = mean_i e0_i^2 (src/model.py:382-385, :428-431) -> e [9,N], t_i [N],
+ * scalars[0] = L_c, scalars[1] = L_u.  `nsplit` chunks [nsplit,10,N] are summed in order.  counter: one
+ * zero-initialised uint32. */
 int dlap_loss_finish(const dlap_plan* plan, const double* col_part, int nsplit, float* e, float* t_i,
                      double* loss_part, uint32_t* counter, float* scalars, void* stream);
 
@@ -197,46 +211,46 @@ int dlap_loss_finish(const dlap_plan* plan, const double* col_part, int nsplit, 
 int dlap_loss_finish_noalloc(const dlap_plan* plan, const double* col_part, int nsplit, float* e,
                              float* t_i, float* scalars, void* stream);
 
-/* Backward of the two losses (autograd at src/train.py:84): G_ki = gc 2 e_ki/(K N T_i),
- * G0_i = gu 2 e0_i/(N T_i); gc/gu are device scalars = dL/dL_c, dL/dL_u (NULL = 0). -> G [9,N] */
-int dlap_loss_coeff(const dlap_plan* plan, const float* e, const float* t_i, const float* gc,
-                    const float* gu, float* G, void* stream);
-
-/* dS_t partials = sum_i (sum_k G_ki g_kti + G0_i R m) -> dS_part [T,row_splits].  index: as for
- * dlap_col_partial (layout of g). */
-int dlap_ds_rows(const dlap_plan* plan, const float* g, const float* R, const uint8_t* mask,
-                 const float* G, const int32_t* index, double* dS_part, void* stream);
-
 /* Per-cell backward with activation recompute (autograd of src/model.py:261-279
- * and :152-153).  want_sdf / want_mom select the parameter groups (requires_grad semantics of
- * src/train.py:309-312).  dpr_cot [T] = extra cotangent of portfolio_returns or NULL.
+ * and :152-153).  gc / gu (device scalars, NULL = 0) = dL/dL_c, dL/dL_u: dS_t = gc dS2[t][0] + gu dS2[t][1]
+ * (+ dpr_cot[t], the extra cotangent of portfolio_returns, or NULL), and the moment side uses gc G_k.
+ * want_sdf / want_mom select the parameter groups (requires_grad semantics of src/train.py:309-312).
+ * mio: a_t, c_t, month0, month_stride as for dlap_cell_fwd (nothing else is read).
  * Outputs: wpart (per-CTA weight-gradient partials), dadc_part (per-tile da_t | dc_t).
  * index: as for dlap_cell_fwd. */
 int dlap_cell_bwd(const dlap_plan* plan, const float* x, const float* R, const uint8_t* mask,
-                  const int32_t* index, const dlap_tensors* params, const float* a_t, const float* c_t,
-                  const float* row_stats, const double* dS_part, const float* dpr_cot,
-                  const float* G, const float* scalars, int weighted_loss, int want_sdf,
+                  const int32_t* index, const dlap_tensors* params, const dlap_macro_io* mio,
+                  const float* row_stats, const double* dS2, const float* gc, const float* gu,
+                  const float* dpr_cot, const float* G, const float* scalars, int weighted_loss, int want_sdf,
                   int want_mom, float* wpart, float* dadc_part, int precision, float dropout_p,
                   uint64_t dropout_seed, const uint64_t* dropout_seed_dev, void* stream);
 
 /* Fixed-order sum of the partials into the reference's gradient layouts: grads->w1[:, :F], w2, b2,
- * w3, b3 (= 0, demeaning), wq[:, M:]; and dadc [T,72] = da_t | dc_t summed over stocks.
- * precision, index: what dlap_cell_bwd ran with (they fix the layout of dadc_part: one partial per
- * tile for FP32, one per (month, CTA) segment for BF16X3). */
+ * w3, b3 (= 0, demeaning), wq[:, M:]; and da_t | dc_t summed over stocks: row t of the panel goes to row
+ * t * dadc_row_stride of dadc [.,72].  precision, index: what dlap_cell_bwd ran with (they fix the layout of
+ * dadc_part: one partial per tile for FP32, one per (month, CTA) segment for BF16X3).  A launch of its own for
+ * callers that exchange the sums before the month-level backward (month shards); otherwise hand the partials to
+ * dlap_macro_bwd. */
 int dlap_grad_finish(const dlap_plan* plan, const float* wpart, const float* dadc_part, const int32_t* index,
                      int precision, int want_sdf, int want_mom, const dlap_tensors* grads, float* dadc,
-                     void* stream);
+                     int dadc_row_stride, void* stream);
 
 /* Month-level backward: dh_t = W1[:,F:]^T da_t, LSTM BPTT, and the month-summed gradients
- * grads->{w_ih,w_hh,b_ih,b_hh}, w1[:, F:], b1, wq[:, :M], bq.  dpre [T,4H] is scratch. */
-int dlap_macro_bwd(const dlap_plan* plan, const float* macro, const dlap_tensors* params,
-                   const float* h0, const float* c0, const float* lstm_save, const float* dadc,
-                   float* dpre, int want_sdf, int want_mom, const dlap_tensors* grads, void* stream);
+ * grads->{w_ih,w_hh,b_ih,b_hh}, w1[:, F:], b1, wq[:, :M], bq.  dpre [T,4H] is scratch.
+ * wpart / dadc_part non-NULL (with the index and precision dlap_cell_bwd ran with; the plan is then also the
+ * per-cell plan): the call first does dlap_grad_finish's work -- dadc [T,72] becomes an output -- and hides most
+ * of it behind the serial recurrence: CTA 0 of the BPTT kernel sums the da_t | dc_t partials, its other CTAs the
+ * weight-gradient partials.  Two launches. */
+int dlap_macro_bwd(const dlap_plan* plan, const float* macro, const dlap_tensors* params, const float* h0,
+                   const float* c0, const float* lstm_save, float* dadc, float* dpre, int want_sdf,
+                   int want_mom, const dlap_tensors* grads, const float* wpart, const float* dadc_part,
+                   const int32_t* index, int precision, void* stream);
 
-/* get_weights (src/model.py:565-594): w = m (u - mu_t); normalized != 0 divides each month by
- * clamp(sum_i |w| m, 1e-8) (the Python loop of :586-590).  index: as for dlap_col_partial (layout of u). */
-int dlap_weights(const dlap_plan* plan, const float* u, const uint8_t* mask, const float* row_stats,
-                 const int32_t* index, int normalized, float* w_out, void* stream);
+/* get_weights (src/model.py:565-594): w = m (u - mu_t), mu_t the month's mean of u over unmasked stocks;
+ * normalized != 0 divides each month by clamp(sum_i |w| m, 1e-8) (the Python loop of :586-590).
+ * index: the layout of u (as for dlap_step_reduce). */
+int dlap_weights(const dlap_plan* plan, const float* u, const uint8_t* mask, const int32_t* index, int normalized,
+                 float* w_out, void* stream);
 
 /* Diagnostics (no counterpart in the reference): when `stamps` is a device buffer of 3*256*16 int64, every
  * following tensor-core dlap_cell_bwd (first third of the buffer: epilogue and MMA warps per tile; last third:

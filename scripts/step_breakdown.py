@@ -25,14 +25,11 @@ if world > 1:
     import torch.distributed as dist
     os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
     dist.init_process_group("nccl", device_id=dev)
-    model.month_shard = Fn.make_month_shard(mask, rank * T, 240, dist.group.WORLD)
-names = ["dlap_macro_fwd", "dlap_cell_fwd", "dlap_row_finish", "dlap_col_partial", "dlap_loss_finish",
-         "dlap_loss_coeff", "dlap_ds_rows", "dlap_cell_bwd", "dlap_grad_finish", "dlap_macro_bwd"]
+    model.month_shard = Fn.make_month_shard(mask, rank, 240, dist.group.WORLD, stride=world)
+names = ["dlap_cell_fwd", "dlap_step_reduce", "dlap_cell_bwd", "dlap_macro_bwd"]
 if world > 1:
-    names += ["exchange_fwd", "exchange_bwd"]
+    names += ["dlap_grad_finish", "exchange_fwd", "exchange_bwd"]
 res = {}
-overlap = Fn.overlap_macro
-Fn.overlap_macro = False          # per-entry-point times: one kernel after the other (macro_fwd is otherwise hidden)
 for name in names:
     for it in range(23):
         if it == 3:
@@ -42,7 +39,6 @@ for name in names:
     torch.cuda.synchronize()
     res[name] = round(Fn.kernel_timer.mean_ms() * 1e3, 1)
     Fn.kernel_timer = None
-Fn.overlap_macro = overlap
 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
 e0.record()
 for _ in range(50):

@@ -108,6 +108,30 @@ def test_macro_fwd_stage():
     assert np.abs(_np(cn).reshape(-1) - saved["cn"]).max() < 2e-6
 
 
+def _check_reduce_stage(red, ref, s, T, N):
+    """dlap_step_reduce against the closed form: per-month statistics, losses, unit loss coefficients, dS sums."""
+    rs = _np(red.row_stats)
+    m = s["m"]
+    assert np.array_equal(rs[:, Fn.RS_NT], np.maximum(m.sum(axis=1), 1))           # counts are exact integers
+    assert np.abs(rs[:, Fn.RS_MU] - s["mu"]).max() < 1e-6 * max(1.0, np.abs(s["mu"]).max())
+    assert np.abs(rs[:, Fn.RS_S] - s["S"]).max() < 1e-6
+    assert np.abs(_np(red.pr) - ref["portfolio_returns"]).max() < 1e-4 * np.abs(ref["portfolio_returns"]).max()
+    sc = _np(red.scalars)
+    assert abs(sc[Fn.SC_LC] - ref["loss_conditional"]) <= LOSS_RTOL * ref["loss_conditional"]
+    assert abs(sc[Fn.SC_LU] - ref["loss_unconditional"]) <= LOSS_RTOL * ref["loss_unconditional"]
+    assert abs(sc[Fn.SC_NBAR] - s["n_bar"]) <= 1e-6 * s["n_bar"]
+    assert abs(sc[Fn.SC_SHARPE] - ref["sharpe"]) <= 1e-4 * abs(ref["sharpe"]) + 1e-7
+    assert rel_err(_np(red.w), ref["weights"]) < WEIGHT_TOL
+    K = 8
+    Gc = 2.0 * s["e"] / (K * N * s["t_i"]); Gu = 2.0 * s["e0"] / (N * s["t_i"])
+    G = _np(red.G)
+    assert np.abs(G[:8] - Gc).max() < 1e-5 * np.abs(Gc).max() and np.abs(G[8] - Gu).max() < 1e-5 * np.abs(Gu).max()
+    dSc = (s["rm"] * np.einsum("kn,tnk->tn", Gc, s["q"])).sum(axis=1)
+    dSu = (s["rm"] * Gu[None, :]).sum(axis=1)
+    dS2 = _np(red.dS2)
+    assert np.abs(dS2[:, 0] - dSc).max() < 2e-5 * np.abs(dSc).max() and np.abs(dS2[:, 1] - dSu).max() < 2e-5 * np.abs(dSu).max()
+
+
 def test_forward_stages_rand_small():
     g = load_golden("rand_small")
     params = golden_params(g)
@@ -118,23 +142,16 @@ def test_forward_stages_rand_small():
     s = ref["_saved"]
     kp = [p.detach() for p in model._kernel_params(True)]
     ws = Fn.workspace(T, N, F, 178, 4, dev())
-    save, a_t, c_t, hn, cn = Fn.macro_forward(ws, macro, kp, None, None)
-    assert np.abs(_np(a_t) - s["a"]).max() < 5e-6
-    assert np.abs(_np(c_t) - s["c"]).max() < 2e-5
-    tens = Fn._tensors(kp)
-    u = torch.empty(T, N, device=dev()); gq = torch.empty(8, T, N, device=dev())
-    _lib.call("dlap_cell_fwd", ws.pp, x.data_ptr(), R.data_ptr(), mask.data_ptr(), None, C.byref(tens),
-              a_t.data_ptr(), c_t.data_ptr(), u.data_ptr(), gq.data_ptr(), ws.row_part.data_ptr(), 0, 0.0, 0,
-              None, None, 0, 1, None)
+    cp = Fn.cell_forward(ws, macro, x, mask, kp, None, None, "fp32", True)
     torch.cuda.synchronize()
-    assert np.abs(_np(u) - s["u"]).max() < 1e-5 * max(1.0, np.abs(s["u"]).max())
-    gref = np.transpose(s["q"], (2, 0, 1)) * s["rm"][None]
-    assert np.abs(_np(gq) - gref).max() < 1e-6
-    rp = _np(ws.row_part)[: T * ws.plan.tpm * 4].reshape(T, ws.plan.tpm, 4).sum(axis=1)
-    m = s["m"]
-    assert np.array_equal(rp[:, 0], m.sum(axis=1))          # counts are exact integers
-    assert np.abs(rp[:, 1] - (m * s["u"]).sum(axis=1)).max() < 1e-4
-    assert np.abs(rp[:, 3] - s["rm"].sum(axis=1)).max() < 1e-6
+    assert np.abs(_np(cp.a_t) - s["a"]).max() < 5e-6
+    assert np.abs(_np(cp.c_t) - s["c"]).max() < 2e-5
+    assert np.abs(_np(cp.u) - s["u"]).max() < 1e-5 * max(1.0, np.abs(s["u"]).max())
+    assert np.abs(_np(cp.q) - np.transpose(s["q"], (2, 0, 1))).max() < 1e-6          # dense, masked cells included
+    red = Fn.step_reduce(ws, cp, R, mask, True, True)
+    torch.cuda.synchronize()
+    _check_reduce_stage(red, ref, s, T, N)
+    assert int(ws.bar) == 0                                   # the barrier word is back to zero
 
 
 def _index_layout(T, N):
@@ -174,40 +191,40 @@ def test_panel_index_bit_exact(shape, density):
 
 
 def test_forward_stages_tensor_core_visits_only_unmasked_cells():
-    """BF16X3 forward through the raw ABI: u and g are written for unmasked cells only, left-packed per month
-    (poisoned buffers keep their poison elsewhere), and the row partials of the valid-cell tiles add up to the
-    oracle's row sums."""
+    """BF16X3 forward through the ABI: u and q are written for unmasked cells only, left-packed per month
+    (poisoned buffers keep their poison elsewhere); the LSTM that runs on one CTA of the same grid leaves the same
+    tables as the stand-alone macro kernel; the reductions on the packed layout match the closed form."""
     g = load_golden("rand_small")
     params = golden_params(g)
     model = _model_from(params, 178).eval()
     macro, x, R, mask, _ = _panel(g)
     T, N, F = x.shape
-    s = cf.forward(params, g["macro"], g["x"], g["R"], g["mask"])["_saved"]
+    ref = cf.forward(params, g["macro"], g["x"], g["R"], g["mask"])
+    s = ref["_saved"]
     kp = [p.detach() for p in model._kernel_params(True)]
     ws = Fn.workspace(T, N, F, 178, 4, dev())
-    save, a_t, c_t, hn, cn = Fn.macro_forward(ws, macro, kp, None, None)
-    tens = Fn._tensors(kp)
-    index = ws.panel_index(mask)
-    u = torch.full((T, N), float("nan"), device=dev()); gq = torch.full((8, T, N), float("nan"), device=dev())
-    _lib.call("dlap_cell_fwd", ws.pp, x.data_ptr(), R.data_ptr(), mask.data_ptr(), index.data_ptr(), C.byref(tens),
-              a_t.data_ptr(), c_t.data_ptr(), u.data_ptr(), gq.data_ptr(), ws.row_part.data_ptr(), 1, 0.0, 0,
-              None, None, 0, 1, None)
+    save, a_t, c_t, hn, cn = Fn.macro_forward(ws, macro, kp, None, None)            # stand-alone macro kernel
+    real_empty = torch.empty
+    try:                                                      # poison what cell_forward allocates
+        torch.empty = lambda *a, **k: real_empty(*a, **k).fill_(float("nan")) if k.get("dtype") == torch.float32 else real_empty(*a, **k)
+        cp = Fn.cell_forward(ws, macro, x, mask, kp, None, None, "bf16x3", True)
+    finally:
+        torch.empty = real_empty
     torch.cuda.synchronize()
+    assert torch.equal(cp.a_t, a_t) and torch.equal(cp.c_t, c_t) and torch.equal(cp.save, save)
+    assert torch.equal(cp.hn, hn) and torch.equal(cp.cn, cn)
+    assert [int(v) for v in ws.sync] == [0, 0]                # progress words are back to zero
     m = g["mask"]
-    un, gn = _np(u), _np(gq)
-    gref = np.transpose(s["q"], (2, 0, 1)) * s["rm"][None]
+    un, qn = _np(cp.u), _np(cp.q)
+    qref = np.transpose(s["q"], (2, 0, 1))
     for t in range(T):                                   # the j-th unmasked stock of month t sits at [t, j]
         c = int(m[t].sum())
-        assert np.isnan(un[t, c:]).all() and np.isnan(gn[:, t, c:]).all()
+        assert np.isnan(un[t, c:]).all() and np.isnan(qn[:, t, c:]).all()
         assert np.abs(un[t, :c] - s["u"][t, m[t]]).max(initial=0.0) < 1e-5 * max(1.0, np.abs(s["u"]).max())
-        assert np.abs(gn[:, t, :c] - gref[:, t, m[t]]).max(initial=0.0) < 2e-6
-    ntiles = int(index[0])
-    ts = _np(index)[4:4 + T + 1]
-    rp = _np(ws.row_part)[: ntiles * 16].reshape(ntiles, 4, 4).sum(axis=1)
-    rows = np.stack([rp[ts[t]:ts[t + 1]].sum(axis=0) for t in range(T)])
-    assert np.array_equal(rows[:, 0], s["m"].sum(axis=1))
-    assert np.abs(rows[:, 1] - (s["m"] * s["u"]).sum(axis=1)).max() < 1e-4
-    assert np.abs(rows[:, 3] - s["rm"].sum(axis=1)).max() < 1e-6
+        assert np.abs(qn[:, t, :c] - qref[:, t, m[t]]).max(initial=0.0) < 2e-6
+    red = Fn.step_reduce(ws, cp, R, mask, True, True)
+    torch.cuda.synchronize()
+    _check_reduce_stage(red, ref, s, T, N)
 
 
 @pytest.mark.parametrize("shape", [(7, 1000, 46), (3, 130, 45), (2, 257, 46)])

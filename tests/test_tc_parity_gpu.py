@@ -176,9 +176,9 @@ def test_tc_all_masked_panel():
 
 @pytest.mark.parametrize("T,N", [(240, 60), (240, 700), (64, 6000), (3, 129)])
 def test_tc_recurrence_beside_cell_forward_is_bit_identical(T, N):
-    """functional.overlap_macro: the LSTM recurrence on a side stream, dlap_cell_fwd beside it, waiting month by
-    month and walking the tiles block-cyclically.  Same arithmetic per tile, so every output and gradient must
-    equal the one-after-the-other schedule bit for bit -- whether the cells wait for the LSTM (small N) or the
+    """functional.fuse_macro: the LSTM recurrence on one CTA of dlap_cell_fwd's own grid, the other CTAs waiting
+    month by month and walking the tiles block-cyclically.  Same arithmetic per tile, so every output and gradient
+    must equal the one-after-the-other schedule bit for bit -- whether the cells wait for the LSTM (small N) or the
     LSTM is far ahead (large N)."""
     from deeplearninginassetpricing_paperreplication_b200 import functional as Fn
     macro, x, R, mask = make_panel(T, N, 178, seed=5)
@@ -188,10 +188,10 @@ def test_tc_recurrence_beside_cell_forward_is_bit_identical(T, N):
     model = AssetPricingGAN({"macro_feature_dim": 178, "individual_feature_dim": 46, "dropout": 0.0,
                              "b200_precision": "bf16x3"}).to(d)
     res = {}
-    old = Fn.overlap_macro
+    old = Fn.fuse_macro
     try:
         for beside in (False, True, True):
-            Fn.overlap_macro = beside
+            Fn.fuse_macro = beside
             model.zero_grad(set_to_none=True)
             out = model(*args, phase="conditional")
             out["loss"].backward()
@@ -207,4 +207,4 @@ def test_tc_recurrence_beside_cell_forward_is_bit_identical(T, N):
                 for k, v in got.items():
                     assert torch.equal(v, res[k]), (beside, k)
     finally:
-        Fn.overlap_macro = old
+        Fn.fuse_macro = old
