@@ -422,7 +422,12 @@ class GanStepFn(torch.autograd.Function):
             red = step_reduce(ws, cp, R, mask, opts.weighted_loss, want_backward, sh)
         ctx.set_materialize_grads(False)      # unused outputs come back as None, not as zero tensors (fill kernels)
         ctx.save_for_backward(x, R, mask, macro, h0, c0, *params)
-        ctx.opts, ctx.ws, ctx.cp, ctx.red = opts, ws, cp, red
+        # What the backward pass reads -- and nothing that is an OUTPUT of this function: an output held by ctx is a
+        # reference cycle (output -> grad_fn -> ctx -> output) that keeps the graph, and with it the parameters'
+        # AccumulateGrad nodes and their stream, alive until the garbage collector runs.  u and q are dead here.
+        ctx.opts, ctx.ws = opts, ws
+        ctx.keep = (cp.save, cp.a_t, cp.c_t, cp.index, cp.mio, cp.q is not None, red.row_stats, red.scalars, red.G,
+                    red.dS2)
         scalars = red.scalars
         l_c, l_u, sharpe = scalars[SC_LC], scalars[SC_LU], scalars[SC_SHARPE]
         ctx.mark_non_differentiable(red.w, sharpe, cp.hn, cp.cn)
@@ -431,14 +436,15 @@ class GanStepFn(torch.autograd.Function):
     @staticmethod
     def backward(ctx, g_lc, g_lu, g_pr, *_unused):
         x, R, mask, macro, h0, c0, *params = ctx.saved_tensors
-        opts, ws, cp, red = ctx.opts, ctx.ws, ctx.cp, ctx.red
+        opts, ws = ctx.opts, ctx.ws
+        save, a_t, c_t, index, mio, has_q, row_stats, scalars, G, dS2 = ctx.keep
         sh = opts.shard
         dev = x.device
         T, N, F = x.shape
         M = 0 if macro is None else macro.shape[1]
         need = ctx.needs_input_grad[8:]
         want_sdf = any(need[:10])
-        want_mom = any(need[10:]) and cp.q is not None
+        want_mom = any(need[10:]) and has_q
         if not (want_sdf or want_mom):
             return (None,) * (8 + len(params))
         prec = _PRECISIONS[_BWD_PRECISION[opts.precision]]
@@ -452,9 +458,9 @@ class GanStepFn(torch.autograd.Function):
         with torch.cuda.device(dev):
             st = _stream(dev)
             tens = _tensors(params)
-            _timed_call("dlap_cell_bwd", dev, ws.pp, _ptr(x), _ptr(R), _ptr(mask), _ptr(cp.index), C.byref(tens),
-                        C.byref(cp.mio), _ptr(red.row_stats), _ptr(red.dS2), _ptr(g_lc) if cp.q is not None else None,
-                        _ptr(g_lu), _ptr(g_pr), _ptr(red.G), _ptr(red.scalars), int(opts.weighted_loss), int(want_sdf),
+            _timed_call("dlap_cell_bwd", dev, ws.pp, _ptr(x), _ptr(R), _ptr(mask), _ptr(index), C.byref(tens),
+                        C.byref(mio), _ptr(row_stats), _ptr(dS2), _ptr(g_lc) if has_q else None,
+                        _ptr(g_lu), _ptr(g_pr), _ptr(G), _ptr(scalars), int(opts.weighted_loss), int(want_sdf),
                         int(want_mom), _ptr(ws.wpart), _ptr(ws.dadc_part), prec, float(opts.dropout_p),
                         int(opts.dropout_seed), _ptr(opts.dropout_seed_dev), st)
             ws.launches += 1
@@ -473,19 +479,19 @@ class GanStepFn(torch.autograd.Function):
             gt = _tensors(grads)
             if sh is None:
                 dadc = torch.empty(T, 72, dtype=torch.float32, device=dev)
-                _timed_call("dlap_macro_bwd", dev, ws.pp, _ptr(macro), C.byref(tens), _ptr(h0), _ptr(c0), _ptr(cp.save),
+                _timed_call("dlap_macro_bwd", dev, ws.pp, _ptr(macro), C.byref(tens), _ptr(h0), _ptr(c0), _ptr(save),
                             _ptr(dadc), _ptr(ws.dpre), int(want_sdf), int(want_mom), C.byref(gt), _ptr(ws.wpart),
-                            _ptr(ws.dadc_part), _ptr(cp.index), prec, st)
+                            _ptr(ws.dadc_part), _ptr(index), prec, st)
                 ws.launches += 2
             else:   # exchange 2: per-cell weight grads + every month's da_t | dc_t row
                 dadc_all = buf[:head].view(sh.T_total, 72)
-                _timed_call("dlap_grad_finish", dev, ws.pp, _ptr(ws.wpart), _ptr(ws.dadc_part), _ptr(cp.index), prec,
+                _timed_call("dlap_grad_finish", dev, ws.pp, _ptr(ws.wpart), _ptr(ws.dadc_part), _ptr(index), prec,
                             int(want_sdf), int(want_mom), C.byref(gt), _ptr(dadc_all[sh.t0:]), int(sh.stride), st)
                 wsm = workspace(sh.T_total, N, F, M, ws.plan.dims.H, dev)
                 with _timed_region("exchange_bwd", dev):
                     torch.distributed.all_reduce(buf, group=sh.group)
                 _timed_call("dlap_macro_bwd", dev, wsm.pp, _ptr(macro), C.byref(tens), _ptr(h0), _ptr(c0),
-                            _ptr(cp.save), _ptr(dadc_all), _ptr(wsm.dpre), int(want_sdf), int(want_mom), C.byref(gt),
+                            _ptr(save), _ptr(dadc_all), _ptr(wsm.dpre), int(want_sdf), int(want_mom), C.byref(gt),
                             None, None, None, prec, st)
                 ws.launches += 3 if (want_sdf and M > 0) else 2
         out = []

@@ -22,7 +22,7 @@ from test_parity_gpu import LOSS_RTOL, WEIGHT_TOL, _np, dev, make_panel
 pytestmark = pytest.mark.gpu
 
 PAPER = dict(T=240, N=10_000, M=178, F=46)
-TRAJ_TOL = {"fp32": 2e-2, "bf16x3": 1e-1}     # provisional: tightened to ~2.5x the measured values
+TRAJ_TOL = {"fp32": 5e-2, "bf16x3": 2e-1}     # provisional: to be set to ~2.5x the measured values
 
 
 @pytest.fixture(scope="module")
@@ -171,10 +171,11 @@ def test_adam_trajectory_200_steps(precision):
         torch.nn.utils.clip_grad_norm_([ref[k] for k in tp.SDF_KEYS], 1.0)
         ropt.step()
         a, b = float(out["loss"]), float(rout["loss"])
-        if abs(a - b) / abs(b) > worst:
-            worst, at = abs(a - b) / abs(b), step
         first = b if first is None else first
         last = b
+        dev_ = abs(a - b) / max(abs(b), 1e-3 * first)     # relative; below 0.1 % of the initial loss: to that floor
+        if dev_ > worst:
+            worst, at = dev_, step
     with torch.no_grad():
         model.eval()
         wn, _ = model.get_weights(args[0], args[1], args[3], normalized=True)

@@ -221,7 +221,7 @@ def test_forward_stages_tensor_core_visits_only_unmasked_cells():
         c = int(m[t].sum())
         assert np.isnan(un[t, c:]).all() and np.isnan(qn[:, t, c:]).all()
         assert np.abs(un[t, :c] - s["u"][t, m[t]]).max(initial=0.0) < 1e-5 * max(1.0, np.abs(s["u"]).max())
-        assert np.abs(qn[:, t, :c] - qref[:, t, m[t]]).max(initial=0.0) < 2e-6
+        assert np.abs(qn[:, t, :c] - qref[:, t, m[t]]).max(initial=0.0) < 1e-5
     red = Fn.step_reduce(ws, cp, R, mask, True, True)
     torch.cuda.synchronize()
     _check_reduce_stage(red, ref, s, T, N)
@@ -303,7 +303,7 @@ def test_graphed_step_replays_the_eager_step_bit_for_bit(precision):
 
     ref_out, ref_grads = eager()
     gs = model.graphed_step(macro, x, R, mask)
-    assert gs.launches >= 10
+    assert gs.launches == (5 if precision == "bf16x3" else 6)      # fp32: the macro LSTM is a launch of its own
     for trial in range(3):
         if trial == 2:                                   # parameters move in place, like optimizer.step()
             with torch.no_grad():

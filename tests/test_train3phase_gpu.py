@@ -28,7 +28,9 @@ pytestmark = [pytest.mark.gpu,
 # different side of some ReLUs; tensor-core kernels (pre-activations good to 2^-18 instead of 2^-24, i.e. more such
 # ReLU decisions differ) 5e-3 .. 8e-3 and 4e-3.  The bounds leave a factor ~2.5.
 LOSS_TOL = {"fp32": 2e-3, "bf16x3": 2e-2, None: 2e-2}
-SHARPE_TOL = {"fp32": 2e-3, "bf16x3": 1e-2, None: 1e-2}      # relative to max(|Sharpe|, 0.2)
+# Sharpe ratios (normalised-weight portfolio over 30 .. 120 months): |a - b| <= abs + rel |b|.  Measured: fp32 5e-4
+# absolute at 0.26, 6e-4 at 3.0; tensor-core path 5.5e-3 at 0.18, 1.2e-2 at 3.0.
+SHARPE_TOL = {"fp32": (1.5e-3, 1e-3), "bf16x3": (1.2e-2, 8e-3), None: (1.2e-2, 8e-3)}
 
 
 def _reference():
@@ -110,9 +112,9 @@ def test_reference_train_3phase_on_the_drop_in(cpu_run, precision):
         assert err <= tol, (key, err)
     for key in ("train_sharpe", "valid_sharpe", "test_sharpe"):
         a, b = hist[key], ref[key]
-        err = (np.abs(a - b) / np.maximum(np.abs(b), 0.2)).max()
-        print(f"[{precision}] {key}: worst relative deviation {err:.2e} (values up to {np.abs(b).max():.3f})")
-        assert err <= SHARPE_TOL[precision], (key, err)
+        tol_abs, tol_rel = SHARPE_TOL[precision]
+        print(f"[{precision}] {key}: worst absolute deviation {np.abs(a - b).max():.2e} (values up to {np.abs(b).max():.3f})")
+        assert np.all(np.abs(a - b) <= tol_abs + tol_rel * np.abs(b)), (key, np.abs(a - b).max())
     # the trained parameters themselves
     sd, rsd = model.state_dict(), cpu_run["model"].state_dict()
     assert list(sd.keys()) == list(rsd.keys())
