@@ -34,7 +34,8 @@ class DlapDims(C.Structure):
 class DlapPlan(C.Structure):
     _fields_ = [("dims", DlapDims), ("tpm", C.c_int32), ("sms", C.c_int32), ("grid_cell", C.c_int32),
                 ("cooperative", C.c_int32), ("col_splits", C.c_int32), ("ldw1", C.c_int32), ("ldwq", C.c_int32),
-                ("col_part_bytes", C.c_int64), ("loss_part_bytes", C.c_int64),
+                ("col_part_bytes", C.c_int64), ("loss_part_bytes", C.c_int64), ("row_part_bytes", C.c_int64),
+                ("bar_bytes", C.c_int64),
                 ("wpart_bytes", C.c_int64), ("dadc_part_bytes", C.c_int64),
                 ("lstm_save_bytes", C.c_int64), ("dpre_bytes", C.c_int64), ("index_bytes", C.c_int64)]
 
@@ -65,13 +66,13 @@ SIGNATURES = {
     "dlap_panel_index": (_PLAN, _P, _P, _P),
     "dlap_panel_pull": (_PLAN, _P, _P, _P, _I, _I, _P),
     "dlap_cell_fwd": (_PLAN, _P, _P, _P, _TENS, _MIO, _P, _P, _I, C.c_float, C.c_uint64, _P, _P),
-    "dlap_step_reduce": (_PLAN, _P, _P, _P, _P, _P, _I, _P, _I, _I, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P),
+    "dlap_step_reduce": (_PLAN, _P, _P, _P, _P, _P, _I, _P, _I, _I, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P),
     "dlap_loss_finish": (_PLAN, _P, _I, _P, _P, _P, _P, _P, _P),
     "dlap_loss_finish_noalloc": (_PLAN, _P, _I, _P, _P, _P, _P),
     "dlap_cell_bwd": (_PLAN, _P, _P, _P, _P, _TENS, _MIO, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _P, _P, _I,
                       C.c_float, C.c_uint64, _P, _P),
     "dlap_grad_finish": (_PLAN, _P, _P, _P, _I, _I, _I, _TENS, _P, _I, _P),
-    "dlap_macro_bwd": (_PLAN, _P, _TENS, _P, _P, _P, _P, _P, _I, _I, _TENS, _P, _P, _P, _I, _P),
+    "dlap_macro_bwd": (_PLAN, _P, _TENS, _P, _P, _P, _P, _P, _I, _I, _TENS, _P, _P, _P, _I, _P, _P),
     "dlap_weights": (_PLAN, _P, _P, _P, _I, _P, _P),
     "dlap_debug_timeline": (_P,),
     "dlap_umma_selftest": (_P, _I, _P, _I, _I, _I, _I, _I, _I, _I, _I, _I, _I, _I, _I, _P, _P),

@@ -18,7 +18,8 @@ cudaError_t launch_panel_pull(const float* x_host, const int* index, int T, int 
 cudaError_t launch_step_reduce_c(const dlap_plan* plan, const float* u, const float* q, const float* R, const uint8_t* mask,
                                  const int* index, int weighted, const float* n_bar_in, int phase_lo, int phase_hi,
                                  float* row_stats, float* pr, float* scalars, float* w_out, double* col_part, float* e,
-                                 float* t_i, float* G, double* loss_part, double* dS2, unsigned int* bar, cudaStream_t st);
+                                 float* t_i, float* G, double* loss_part, double* dS2, double* row_part,
+                                 unsigned int* bar, cudaStream_t st);
 cudaError_t launch_loss_finish(const double*, int, int, int, float*, float*, double*, unsigned int*, float*,
                                cudaStream_t);
 cudaError_t launch_grad_finish(const FinishParams& P, cudaStream_t st);
@@ -114,6 +115,8 @@ int dlap_make_plan(const dlap_dims* dims, int device, dlap_plan* out) {
   p.ldwq = dims->M + F;
   p.col_part_bytes = (int64_t)p.col_splits * (KM + 2) * N * 8;
   p.loss_part_bytes = (int64_t)((N + 63) / 64) * 2 * 8;
+  p.row_part_bytes = (int64_t)T * 8 * 4 * 8;
+  p.bar_bytes = (int64_t)(1 + T) * 4;
   p.wpart_bytes = (int64_t)p.grid_cell * wp_stride(round4(F)) * 4;
   p.dadc_part_bytes = (int64_t)T * (p.tpm > 4 ? p.tpm : 4) * 72 * 4;
   p.index_bytes = (int64_t)idx_ints(T, N) * 4;
@@ -261,7 +264,8 @@ int dlap_cell_fwd(const dlap_plan* plan, const float* x, const uint8_t* mask, co
 int dlap_step_reduce(const dlap_plan* plan, const float* u, const float* q, const float* R, const uint8_t* mask,
                      const int32_t* index, int weighted_loss, const float* n_bar_in, int phase_lo, int phase_hi,
                      float* row_stats, float* pr, float* scalars, float* w_out, double* col_part, float* e,
-                     float* t_i, float* G, double* loss_part, double* dS2, uint32_t* bar, void* stream) {
+                     float* t_i, float* G, double* loss_part, double* dS2, double* row_part, uint32_t* bar,
+                     void* stream) {
   int rc = check_plan(plan);
   if (rc) return rc;
   if (phase_lo < 0 || phase_hi > 4 || phase_lo > phase_hi) return DLAP_E_SHAPE;
@@ -270,7 +274,7 @@ int dlap_step_reduce(const dlap_plan* plan, const float* u, const float* q, cons
   if (phase_lo <= 1) { REQ(u); REQ(pr); }
   if (phase_hi >= 3) { REQ(e); REQ(t_i); REQ(G); REQ(loss_part); }
   CU(launch_step_reduce_c(plan, u, q, R, mask, index, weighted_loss, n_bar_in, phase_lo, phase_hi, row_stats, pr,
-                          scalars, w_out, col_part, e, t_i, G, loss_part, dS2, bar, (cudaStream_t)stream));
+                          scalars, w_out, col_part, e, t_i, G, loss_part, dS2, row_part, bar, (cudaStream_t)stream));
   return DLAP_OK;
 }
 
@@ -300,7 +304,8 @@ int dlap_cell_bwd(const dlap_plan* plan, const float* x, const float* R, const u
   CellParams P;
   rc = fill_cell(P, plan, x, R, mask, params, mio);
   if (rc) return rc;
-  P.row_stats = row_stats; P.dS2 = dS2; P.gc = gc; P.gu = gu; P.dpr_cot = dpr_cot;
+  P.row_stats = row_stats; P.dS2 = dS2; P.dpr_cot = dpr_cot;
+  P.cot[0] = gc ? gc : scalars + SC_ZERO; P.cot[1] = gu ? gu : scalars + SC_ZERO; P.ncot = 2;
   P.G = G; P.scalars = scalars; P.weighted = weighted_loss;
   P.wpart = wpart; P.dadc_part = dadc_part;
   rc = set_dropout(P, dropout_p, dropout_seed, dropout_seed_dev);
@@ -352,7 +357,7 @@ int dlap_grad_finish(const dlap_plan* plan, const float* wpart, const float* dad
 int dlap_macro_bwd(const dlap_plan* plan, const float* macro, const dlap_tensors* params, const float* h0,
                    const float* c0, const float* lstm_save, float* dadc, float* dpre, int want_sdf, int want_mom,
                    const dlap_tensors* grads, const float* wpart, const float* dadc_part, const int32_t* index,
-                   int precision, void* stream) {
+                   int precision, uint32_t* counter, void* stream) {
   int rc = check_plan(plan);
   if (rc) return rc;
   REQ(params); REQ(dadc); REQ(grads);
@@ -370,6 +375,9 @@ int dlap_macro_bwd(const dlap_plan* plan, const float* macro, const dlap_tensors
   if (wpart || dadc_part) {
     rc = fill_finish(F, plan, wpart, dadc_part, index, precision, want_sdf, want_mom, grads, dadc, 1);
     if (rc) return rc;
+    REQ(counter);
+    if (reinterpret_cast<uintptr_t>(counter) & 3) return DLAP_E_ALIGN;
+    F.counter = counter; F.cooperative = plan->cooperative;
   }
   MacroParams P;
   fill_macro(P, plan, plan->dims.T, macro, params, h0, c0);

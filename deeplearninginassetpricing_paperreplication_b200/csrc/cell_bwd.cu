@@ -115,7 +115,7 @@ __global__ void __launch_bounds__(NT, 1) cell_bwd_f32_kernel(const CellParams P)
       s.sc[0] = month_dP(P, t);
       s.sc[1] = rs[RS_RBAR];
       s.sc[2] = rs[RS_S];
-      s.sc[3] = P.gc ? __ldg(P.gc) : 0.f;
+      s.sc[3] = __ldg(P.cot[0]);
     }
     __syncthreads();
     const int ncell = L.ncell;

@@ -302,7 +302,6 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
     for (int k = 0; k < 8; ++k) pf_g[k] = 0.f;
     int ms_month = -1;
     float ms_dP = 0.f, ms_rbar = 0.f, ms_S = 0.f;
-    const float gc_cot = (mom_warp && P.gc) ? __ldg(P.gc) : 0.f;      // dL/dL_c: scales the unit coefficients G_k
     auto load_n = [&](int i) {
       const int tile = tile_lo + i;
       mc.seek(P, tile);
@@ -316,14 +315,15 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
       pf_r = pf_live ? __ldg(P.R + gi) : 0.f;            // consumed one phase later: no stall here
       if (mom_warp) {
 #pragma unroll
-        for (int k = 0; k < 8; ++k) pf_g[k] = pf_live ? gc_cot * __ldg(P.G + (size_t)k * P.N + n) : 0.f;
+        for (int k = 0; k < 8; ++k) pf_g[k] = pf_live ? __ldg(P.G + (size_t)k * P.N + n) : 0.f;
       }
       if (t != ms_month) {
         ms_month = t;
         const float* rs = P.row_stats + (size_t)t * RS_W;
         ms_dP = month_dP(P, t);
         ms_rbar = rs[RS_RBAR];
-        ms_S = rs[RS_S];
+        // S_t only ever multiplies the moment-side cotangent: carry dL/dL_c with it (G holds UNIT coefficients)
+        ms_S = rs[RS_S] * __ldg(P.cot[0]);
       }
       if (i + 1 < my_tiles) load_n(i + 1);
     };

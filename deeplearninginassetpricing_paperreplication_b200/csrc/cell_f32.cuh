@@ -40,8 +40,8 @@ struct CellParams {
   // backward inputs
   const float* row_stats;    // [T,RS_W]
   const double* dS2;         // [T,2]  dS_t for unit cotangents of L_c and of L_u (step_reduce.cu, phase 4)
-  const float* gc;           // device scalars dL/dL_c, dL/dL_u (null = 0): dS_t = gc dS2[t][0] + gu dS2[t][1]
-  const float* gu;
+  const float* cot[2];       // device scalars dL/dL_c, dL/dL_u: dS_t = cot[0] dS2[t][0] + cot[1] dS2[t][1]
+  int ncot;                  // 2
   const float* dpr_cot;      // [T] cotangent of portfolio_returns, or null
   const float* G;            // [9,N]   unit coefficients; rows 0..7 (times gc): G_k, row 8: Gu
   const float* scalars;      // [SC_W]  (n_bar)
@@ -67,10 +67,14 @@ struct CellParams {
   int cyc_sh;                // log2 of the block size of the block-cyclic tile order used with months_ready
 };
 
-// dL/dP_t of month t from the two unit sums and the loss cotangents (src/model.py:367 backwards)
+// dL/dP_t of month t from the two unit sums and the loss cotangents (src/model.py:367 backwards):
+// dS_t = gc dS2[t][0] + gu dS2[t][1] (+ the cotangent of portfolio_returns).  Written as a loop over P.ncot = 2
+// terms on purpose: straight-line code lets ptxas hoist these once-a-month loads to the top of the per-tile path,
+// where the tensor-core backward kernel has no register to spare (measured: 40 bytes of spills, +18 us).
 __device__ __forceinline__ float month_dP(const CellParams& P, int t) {
-  const float gc = P.gc ? __ldg(P.gc) : 0.f, gu = P.gu ? __ldg(P.gu) : 0.f;
-  double dS = (double)gc * P.dS2[2 * (size_t)t] + (double)gu * P.dS2[2 * (size_t)t + 1];
+  double dS = 0.0;
+#pragma unroll 1
+  for (int k = 0; k < P.ncot; ++k) dS += (double)__ldg(P.cot[k]) * P.dS2[2 * (size_t)t + k];
   if (P.dpr_cot) dS += (double)__ldg(P.dpr_cot + t);
   const float* rs = P.row_stats + (size_t)t * RS_W;
   return (float)(dS * (P.weighted ? (double)P.scalars[SC_NBAR] / (double)rs[RS_NT] : 1.0));

@@ -21,7 +21,7 @@ constexpr int HMAX = 8;       // LSTM units: 4*H gate rows must fit one warp
 // row_stats[t][*] written by row_finish
 enum { RS_NT = 0, RS_MU = 1, RS_P = 2, RS_PR = 3, RS_S = 4, RS_RBAR = 5, RS_W = 8 };
 // scalars[*] written by row_finish / loss_finish
-enum { SC_LC = 0, SC_LU = 1, SC_SHARPE = 2, SC_NBAR = 3, SC_W = 8 };
+enum { SC_LC = 0, SC_LU = 1, SC_SHARPE = 2, SC_NBAR = 3, SC_ZERO = 7 /* always 0.0 */, SC_W = 8 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));

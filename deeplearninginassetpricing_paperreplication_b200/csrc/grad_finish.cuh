@@ -12,6 +12,8 @@ struct FinishParams {
   const int* index;                        // != null: (month, CTA) segment layout of the tensor-core kernel
   float* gW1; int ldw1; float* gW2; float* gb2; float* gW3; float* gb3; float* gWq; int ldwq, wq_off;
   float* dadc; int dadc_stride;            // row t of this panel goes to row t * dadc_stride of dadc
+  // BPTT kernel only (macro_lstm.cu): CTAs that sum da_t | dc_t elements count themselves off here
+  unsigned int* counter; int dadc_ctas; int cooperative;
 };
 
 // element idx < wp_stride(round4(F)) of the per-CTA weight-gradient partials, summed over the CTAs

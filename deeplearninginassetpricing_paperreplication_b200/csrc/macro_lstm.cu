@@ -32,19 +32,23 @@ __global__ void __launch_bounds__(MT, 1) macro_fwd_kernel(const MacroParams P) {
 // dynamic smem: sv[T][6H] (saved states, later S[T][2H] = dht | dcn) | Y[T][H][REC] | W1m[64][H] | Whh[4H][H]
 // record (REC = 8 + 2 HP floats, HP = H rounded up to 4): a_c f dhe . | a_i a_f a_g a_o | A[.][k] | B[.][k]
 // With FIN.dadc_part (an unsharded step) the kernel also finishes the per-cell backward kernel's partials, which
-// used to be a launch of its own in front of this one: CTA 0 first sums the da_t | dc_t partials of every month
-// into FIN.dadc (= P.dadc), CTAs 1.. sum the per-CTA weight-gradient partials beside the serial recurrence.
+// used to be a launch of its own in front of this one: the first gridDim.x - 1 CTAs sum the per-CTA weight-gradient
+// partials and the da_t | dc_t partials of every month (grad_finish.cuh) and count themselves off in *FIN.counter;
+// the LAST CTA is the recurrence: it stages its tables, waits until the da_t | dc_t rows are complete (the grid is
+// co-resident: a cooperative launch, ~50 CTAs), and puts the counter back to zero.
 template <int H>
 __global__ void __launch_bounds__(MT, 1) macro_bptt_kernel(const MacroParams P, const FinishParams FIN) {
   extern __shared__ float sm[];
-  if (blockIdx.x > 0) {
-    const int idx = (blockIdx.x - 1) * MT + threadIdx.x;
-    if (idx < wp_stride(round4(FIN.F))) finish_wpart(FIN, idx);
+  if (blockIdx.x + 1 < gridDim.x) {
+    const int stride = wp_stride(round4(FIN.F));
+    const int idx = blockIdx.x * MT + threadIdx.x;
+    if (idx < stride) finish_wpart(FIN, idx);
+    else if (idx - stride < FIN.T * 72) finish_dadc(FIN, idx - stride);
+    if ((int)(blockIdx.x + 1) * MT > stride) {            // this CTA wrote da_t | dc_t elements
+      __syncthreads();
+      if (threadIdx.x == 0) { __threadfence(); atomicAdd(FIN.counter, 1u); }
+    }
     return;
-  }
-  if (FIN.dadc_part) {
-    for (int r = threadIdx.x; r < FIN.T * 72; r += MT) finish_dadc(FIN, r);
-    __syncthreads();
   }
   const int T = P.T;
   constexpr int G4 = 4 * H;
@@ -57,6 +61,13 @@ __global__ void __launch_bounds__(MT, 1) macro_bptt_kernel(const MacroParams P, 
   for (int i = tid; i < T * 6 * H; i += MT) sv_s[i] = P.save[i];
   for (int i = tid; i < D1 * H; i += MT) w1m[i] = __ldg(P.W1 + (size_t)(i / H) * P.ldw1 + P.F + (i % H));
   for (int i = tid; i < G4 * H; i += MT) whh[i] = __ldg(P.Whh + i);
+  if (FIN.dadc_part && tid == 0) {                          // the da_t | dc_t rows are being summed by the other CTAs
+    unsigned int v;
+    do {
+      asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(FIN.counter) : "memory");
+    } while (v < (unsigned int)FIN.dadc_ctas);
+    atomicExch(FIN.counter, 0u);
+  }
   __syncthreads();
   // pass 1, thread = (month, unit): dhe_t = W1[:,F:]^T . da_t and the local derivatives
   for (int i = tid; i < T * H; i += MT) {
@@ -65,7 +76,7 @@ __global__ void __launch_bounds__(MT, 1) macro_bptt_kernel(const MacroParams P, 
     float v0 = 0.f, v1 = 0.f;
 #pragma unroll 4
     for (int j4 = 0; j4 < D1 / 4; ++j4) {
-      const float4 d = __ldcg(da4 + j4);                 // may have been written by this CTA a moment ago
+      const float4 d = __ldcg(da4 + j4);                 // may have been written by this grid a moment ago
       v0 = fmaf(w1m[(4 * j4) * H + j], d.x, v0);     v1 = fmaf(w1m[(4 * j4 + 1) * H + j], d.y, v1);
       v0 = fmaf(w1m[(4 * j4 + 2) * H + j], d.z, v0); v1 = fmaf(w1m[(4 * j4 + 3) * H + j], d.w, v1);
     }
@@ -280,8 +291,18 @@ template <int H>
 static cudaError_t launch_bptt_h(const MacroParams& P, const FinishParams& FIN, size_t smem, cudaStream_t st) {
   cudaError_t e = cudaFuncSetAttribute(macro_bptt_kernel<H>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
-  const int extra = FIN.wpart ? (wp_stride(round4(FIN.F)) + MT - 1) / MT : 0;
-  macro_bptt_kernel<H><<<1 + extra, MT, smem, st>>>(P, FIN);
+  FinishParams F2 = FIN;
+  int extra = 0;
+  if (FIN.dadc_part) {
+    const int stride = wp_stride(round4(FIN.F)), total = stride + FIN.T * 72;
+    extra = (total + MT - 1) / MT;
+    F2.dadc_ctas = extra - stride / MT;                     // CTAs whose range reaches past the weight partials
+  }
+  if (extra > 0 && FIN.cooperative) {
+    void* args[] = {(void*)&P, (void*)&F2};
+    return cudaLaunchCooperativeKernel((const void*)macro_bptt_kernel<H>, dim3(1 + extra), dim3(MT), args, smem, st);
+  }
+  macro_bptt_kernel<H><<<1 + extra, MT, smem, st>>>(P, F2);
   return cudaGetLastError();
 }
 #define DLAP_H_SWITCH(FN, ...)                       \

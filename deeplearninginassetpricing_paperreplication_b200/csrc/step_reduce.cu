@@ -39,7 +39,9 @@ struct ReduceParams {
   float* e; float* t_i; float* G;      // [9,N], [N], [9,N]
   double* loss_part;         // [ceil(N/64), 2]
   double* dS2;               // [T,2] or null (no backward pass will follow)
-  unsigned int* bar;         // grid barrier word, zero between launches
+  double* row_part;          // [T,nseg,4] partial sums of the per-month phases
+  int nseg;                  // segments a month's cells are cut into in phases 0 and 4
+  unsigned int* bar;         // [1 + T], zero between launches: the grid barrier word, then one counter per month
   int phase_lo, phase_hi;    // inclusive
 };
 
@@ -83,35 +85,61 @@ __global__ void __launch_bounds__(RT, 4) step_reduce_kernel(const ReduceParams P
   unsigned int nsync = 0;
 
   // ---------------------------------------------------------------- phase 0: row sums
+  // A month is cut into nseg segments of its cells so that every CTA has work; the CTA that finishes a month's
+  // last segment (a counter per month) adds the segments' partial sums in segment order.
   if (P.phase_lo <= 0 && P.phase_hi >= 0) {
-    for (int t = blockIdx.x; t < T; t += gridDim.x) {
+    const int nseg = P.nseg;
+    for (int unit = blockIdx.x; unit < T * nseg; unit += gridDim.x) {
+      const int t = unit / nseg, seg = unit % nseg;
       double v[4] = {0.0, 0.0, 0.0, 0.0};          // count, sum u, sum u R, sum R
       const size_t base = (size_t)t * N;
       if (P.index) {
         const int cnt = __ldg(P.index + idx_off_cnt(T) + t);
+        const int per = (cnt + nseg - 1) / nseg, j0 = seg * per, j1 = min(cnt, j0 + per);
         const int* vrow = P.index + idx_off_vidx(T) + base;
-        for (int j = tid; j < cnt; j += RT) {
+#pragma unroll 4
+        for (int j = j0 + tid; j < j1; j += RT) {
           const float uv = __ldcg(P.u + base + j), r = __ldg(P.R + base + __ldg(vrow + j));
           v[1] += (double)uv; v[2] += (double)uv * (double)r; v[3] += (double)r;
         }
-        v[0] = tid == 0 ? (double)cnt : 0.0;
+        v[0] = tid == 0 ? (double)max(j1 - j0, 0) : 0.0;
       } else {
-        for (int i = tid; i < N; i += RT) {
-          if (P.mask[base + i]) {
-            const float uv = __ldcg(P.u + base + i), r = __ldg(P.R + base + i);
-            v[0] += 1.0; v[1] += (double)uv; v[2] += (double)uv * (double)r; v[3] += (double)r;
-          }
+        const int per = (N + nseg - 1) / nseg, i0 = seg * per, i1 = min(N, i0 + per);
+#pragma unroll 4
+        for (int i = i0 + tid; i < i1; i += RT) {
+          const bool live = P.mask[base + i] != 0;
+          const float uv = __ldcg(P.u + base + i), r = __ldg(P.R + base + i);
+          v[0] += live ? 1.0 : 0.0; v[1] += live ? (double)uv : 0.0;
+          v[2] += live ? (double)uv * (double)r : 0.0; v[3] += live ? (double)r : 0.0;
         }
       }
       block_sum4(v, red);
       if (tid == 0) {
-        const double nt = fmax(v[0], 1.0);
-        const float mu = (float)(v[1] / nt);
-        float* rs = P.row_stats + (size_t)t * RS_W;
-        rs[RS_NT] = (float)nt;
-        rs[RS_MU] = mu;
-        rs[RS_P] = (float)(v[2] - (double)mu * v[3]);
-        rs[RS_RBAR] = (float)(v[3] / nt);
+        bool last = true;
+        if (nseg > 1) {
+          double* mine = P.row_part + ((size_t)t * nseg + seg) * 4;
+          mine[0] = v[0]; mine[1] = v[1]; mine[2] = v[2]; mine[3] = v[3];
+          __threadfence();
+          last = atomicAdd(P.bar + 1 + t, 1u) == (unsigned int)(nseg - 1);
+          if (last) {
+            __threadfence();
+            v[0] = v[1] = v[2] = v[3] = 0.0;
+            for (int sg = 0; sg < nseg; ++sg) {
+              const double* pp = P.row_part + ((size_t)t * nseg + sg) * 4;
+              v[0] += __ldcg(pp); v[1] += __ldcg(pp + 1); v[2] += __ldcg(pp + 2); v[3] += __ldcg(pp + 3);
+            }
+            atomicExch(P.bar + 1 + t, 0u);
+          }
+        }
+        if (last) {
+          const double nt = fmax(v[0], 1.0);
+          const float mu = (float)(v[1] / nt);
+          float* rs = P.row_stats + (size_t)t * RS_W;
+          rs[RS_NT] = (float)nt;
+          rs[RS_MU] = mu;
+          rs[RS_P] = (float)(v[2] - (double)mu * v[3]);
+          rs[RS_RBAR] = (float)(v[3] / nt);
+        }
       }
     }
     if (P.phase_hi >= 1) grid_sync(P.bar, ++nsync);
@@ -145,6 +173,7 @@ __global__ void __launch_bounds__(RT, 4) step_reduce_kernel(const ReduceParams P
       s2 = block_sum(s2, red);
       if (tid == 0) {
         P.scalars[SC_NBAR] = n_bar;
+        P.scalars[SC_ZERO] = 0.f;          // what a NULL loss cotangent points at in dlap_cell_bwd
         P.scalars[SC_SHARPE] = (T > 1) ? (float)(mean / (sqrt(s2 / (double)(T - 1)) + 1e-8)) : nanf("");
       }
     }
@@ -256,29 +285,53 @@ __global__ void __launch_bounds__(RT, 4) step_reduce_kernel(const ReduceParams P
       }
     }
     if (P.dS2) {
-      for (int t = blockIdx.x; t < T; t += gridDim.x) {
+      const int nseg = P.nseg;
+      for (int unit = blockIdx.x; unit < T * nseg; unit += gridDim.x) {
+        const int t = unit / nseg, seg = unit % nseg;
         const size_t base = (size_t)t * N;
         double v[4] = {0.0, 0.0, 0.0, 0.0};
-        auto cell = [&](int i, size_t vi) {
+        auto cell = [&](int i, size_t vi, bool live) {
           const float r = __ldg(P.R + base + i);
           float c = 0.f;
           if (P.q) {
 #pragma unroll
             for (int k = 0; k < KM; ++k) c = fmaf(__ldcg(P.G + (size_t)k * N + i), __ldcg(P.q + k * plane + vi) * r, c);
           }
-          v[0] += (double)c;
-          v[1] += (double)(__ldcg(P.G + (size_t)KM * N + i) * r);
+          const float uu = __ldcg(P.G + (size_t)KM * N + i) * r;
+          v[0] += live ? (double)c : 0.0;
+          v[1] += live ? (double)uu : 0.0;
         };
         if (P.index) {
           const int cnt = __ldg(P.index + idx_off_cnt(T) + t);
+          const int per = (cnt + nseg - 1) / nseg, j0 = seg * per, j1 = min(cnt, j0 + per);
           const int* vrow = P.index + idx_off_vidx(T) + base;
-          for (int j = tid; j < cnt; j += RT) cell(__ldg(vrow + j), base + j);
+#pragma unroll 2
+          for (int j = j0 + tid; j < j1; j += RT) cell(__ldg(vrow + j), base + j, true);
         } else {
-          for (int i = tid; i < N; i += RT)
-            if (P.mask[base + i]) cell(i, base + i);
+          const int per = (N + nseg - 1) / nseg, i0 = seg * per, i1 = min(N, i0 + per);
+#pragma unroll 2
+          for (int i = i0 + tid; i < i1; i += RT) cell(i, base + i, P.mask[base + i] != 0);
         }
         block_sum4(v, red);
-        if (tid == 0) { P.dS2[2 * t] = v[0]; P.dS2[2 * t + 1] = v[1]; }
+        if (tid == 0) {
+          bool last = true;
+          if (nseg > 1) {
+            double* mine = P.row_part + ((size_t)t * nseg + seg) * 4;
+            mine[0] = v[0]; mine[1] = v[1];
+            __threadfence();
+            last = atomicAdd(P.bar + 1 + t, 1u) == (unsigned int)(nseg - 1);
+            if (last) {
+              __threadfence();
+              v[0] = v[1] = 0.0;
+              for (int sg = 0; sg < nseg; ++sg) {
+                const double* pp = P.row_part + ((size_t)t * nseg + sg) * 4;
+                v[0] += __ldcg(pp); v[1] += __ldcg(pp + 1);
+              }
+              atomicExch(P.bar + 1 + t, 0u);
+            }
+          }
+          if (last) { P.dS2[2 * t] = v[0]; P.dS2[2 * t + 1] = v[1]; }
+        }
       }
     }
   }
@@ -306,6 +359,12 @@ cudaError_t launch_step_reduce(ReduceParams P, int sms, bool cooperative, cudaSt
   int want = nb * P.nsplit;
   if (want < P.T) want = P.T;
   int grid = per_sm * sms;
+  // months cut into segments so that the per-month phases fill the grid (at most 8: the scratch is sized for that)
+  int nseg = P.row_part ? grid / (P.T > 0 ? P.T : 1) : 1;
+  if (nseg > 8) nseg = 8;
+  if (nseg < 1) nseg = 1;
+  P.nseg = nseg;
+  if (want < P.T * nseg) want = P.T * nseg;
   if (grid > want) grid = want;
   if (grid < 1) grid = 1;
   void* args[] = {(void*)&P};
@@ -318,8 +377,10 @@ cudaError_t launch_step_reduce(ReduceParams P, int sms, bool cooperative, cudaSt
 cudaError_t launch_step_reduce_c(const dlap_plan* plan, const float* u, const float* q, const float* R, const uint8_t* mask,
                                  const int* index, int weighted, const float* n_bar_in, int phase_lo, int phase_hi,
                                  float* row_stats, float* pr, float* scalars, float* w_out, double* col_part, float* e,
-                                 float* t_i, float* G, double* loss_part, double* dS2, unsigned int* bar, cudaStream_t st) {
+                                 float* t_i, float* G, double* loss_part, double* dS2, double* row_part,
+                                 unsigned int* bar, cudaStream_t st) {
   ReduceParams P{};
+  P.row_part = row_part;
   P.u = u; P.q = q; P.R = R; P.mask = mask; P.index = index;
   P.T = plan->dims.T; P.N = plan->dims.N;
   P.weighted = weighted; P.n_bar_in = n_bar_in; P.n_total = plan->dims.N;

@@ -127,8 +127,10 @@ class Workspace:
         self.wpart = f32(p.wpart_bytes)
         self.dadc_part = f32(p.dadc_part_bytes)
         self.dpre = f32(p.dpre_bytes)
-        self.bar = torch.zeros(1, dtype=torch.int32, device=device)      # barrier word of dlap_step_reduce
+        self.row_part = f64(p.row_part_bytes)
+        self.bar = torch.zeros(max(p.bar_bytes // 4, 1), dtype=torch.int32, device=device)   # dlap_step_reduce's barrier words
         self.sync = torch.zeros(2, dtype=torch.int32, device=device)     # progress words of the fused dlap_cell_fwd
+        self.counter = torch.zeros(1, dtype=torch.int32, device=device)  # dlap_macro_bwd's (finished da_t | dc_t rows)
         self.launches = 0          # kernels launched through this workspace (bench bookkeeping)
 
     def panel_index(self, mask: torch.Tensor) -> torch.Tensor:
@@ -388,7 +390,7 @@ def step_reduce(ws: Workspace, cp: CellPass, R, mask, weighted_loss: bool, want_
         _timed_call("dlap_step_reduce", dev, ws.pp, _ptr(cp.u), _ptr(cp.q), _ptr(R), _ptr(mask), _ptr(cp.index),
                     int(weighted_loss), _ptr(shard.n_bar) if shard is not None else None, lo, hi, _ptr(row_stats),
                     _ptr(pr), _ptr(scalars), _ptr(w), _ptr(ws.col_part), _ptr(e), _ptr(t_i), _ptr(G),
-                    _ptr(ws.loss_part), _ptr(dS2), _ptr(ws.bar), _stream(dev))
+                    _ptr(ws.loss_part), _ptr(dS2), _ptr(ws.row_part), _ptr(ws.bar), _stream(dev))
         ws.launches += 1
 
     if shard is None:
@@ -481,7 +483,7 @@ class GanStepFn(torch.autograd.Function):
                 dadc = torch.empty(T, 72, dtype=torch.float32, device=dev)
                 _timed_call("dlap_macro_bwd", dev, ws.pp, _ptr(macro), C.byref(tens), _ptr(h0), _ptr(c0), _ptr(save),
                             _ptr(dadc), _ptr(ws.dpre), int(want_sdf), int(want_mom), C.byref(gt), _ptr(ws.wpart),
-                            _ptr(ws.dadc_part), _ptr(index), prec, st)
+                            _ptr(ws.dadc_part), _ptr(index), prec, _ptr(ws.counter), st)
                 ws.launches += 2
             else:   # exchange 2: per-cell weight grads + every month's da_t | dc_t row
                 dadc_all = buf[:head].view(sh.T_total, 72)
@@ -492,7 +494,7 @@ class GanStepFn(torch.autograd.Function):
                     torch.distributed.all_reduce(buf, group=sh.group)
                 _timed_call("dlap_macro_bwd", dev, wsm.pp, _ptr(macro), C.byref(tens), _ptr(h0), _ptr(c0),
                             _ptr(save), _ptr(dadc_all), _ptr(wsm.dpre), int(want_sdf), int(want_mom), C.byref(gt),
-                            None, None, None, prec, st)
+                            None, None, None, prec, None, st)
                 ws.launches += 3 if (want_sdf and M > 0) else 2
         out = []
         for i, gr in enumerate(grads):

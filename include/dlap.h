@@ -70,6 +70,8 @@ typedef struct dlap_plan {
   int32_t ldwq;           /* row pitch of moment output_proj.weight = M + F */
   int64_t col_part_bytes;   /* double [col_splits, 10, N]   */
   int64_t loss_part_bytes;  /* double [ceil(N/64), 2]       */
+  int64_t row_part_bytes;   /* double [T, 8, 4]: partial sums of dlap_step_reduce's per-month phases */
+  int64_t bar_bytes;        /* uint32 [1 + T]: dlap_step_reduce's barrier word and per-month counters */
   int64_t wpart_bytes;      /* float  [grid_cell, wstride]  */
   int64_t dadc_part_bytes;  /* float  [T, max(tpm,4), 72]   */
   int64_t lstm_save_bytes;  /* float  [T, 6H]               */
@@ -168,7 +170,7 @@ int dlap_cell_fwd(const dlap_plan* plan, const float* x, const uint8_t* mask, co
  *   0  N_t, mu_t (src/model.py:276-278), P_t, Rbar_t from u and R                          -> row_stats [T,8]
  *   1  N_bar (src/model.py:360; n_bar_in, device, overrides it when the panel is a month shard), portfolio return
  *      pr_t and S_t = 1 + pr_t (src/model.py:359-367, :380), Sharpe ratio of pr (src/model.py:551)
- *                                                      -> row_stats, pr [T], scalars[2] = Sharpe, scalars[3] = N_bar;
+ *                                -> row_stats, pr [T], scalars[2] = Sharpe, scalars[3] = N_bar, scalars[7] = 0;
  *      per stock and month chunk: sum_t q_k R S_t, sum_t R m S_t, sum_t m (src/model.py:376, :382, :428)
  *                                                      -> col_part [col_splits,10,N]
  *      and the demeaned weights w = m (u - mu_t) (src/model.py:271-279)      -> w_out [T,N] when non-NULL
@@ -178,12 +180,14 @@ int dlap_cell_fwd(const dlap_plan* plan, const float* x, const uint8_t* mask, co
  *   4  L_c = mean_k mean_i e_ki^2, L_u = mean_i e0_i^2 (src/model.py:385, :429-431) -> scalars[0], scalars[1];
  *      dS2 [T,2] (double): dS_t for unit cotangents of L_c and of L_u; dS2 NULL: no backward pass will follow
  * Single device: phases 0..4 in one launch.  q may be NULL (phase 'unconditional').  index: the valid-cell index
- * when u and q come from the BF16X3 dlap_cell_fwd, NULL for FP32.  bar (device, one uint32, zero when the call
- * starts, zero again when it has finished): the barrier word. */
+ * when u and q come from the BF16X3 dlap_cell_fwd, NULL for FP32.  row_part: scratch (row_part_bytes; NULL: the
+ * per-month phases run one CTA per month).  bar (device, bar_bytes, all zero when the call starts and all zero
+ * again when it has finished): the barrier word and one counter per month. */
 int dlap_step_reduce(const dlap_plan* plan, const float* u, const float* q, const float* R, const uint8_t* mask,
                      const int32_t* index, int weighted_loss, const float* n_bar_in, int phase_lo, int phase_hi,
                      float* row_stats, float* pr, float* scalars, float* w_out, double* col_part, float* e,
-                     float* t_i, float* G, double* loss_part, double* dS2, uint32_t* bar, void* stream);
+                     float* t_i, float* G, double* loss_part, double* dS2, double* row_part, uint32_t* bar,
+                     void* stream);
 
 /* The loss stage on its own, for a caller that holds per-stock sums from elsewhere: e_ki = colsum / T_i,
  * L_c = mean_k mean_i e_ki^2, L_u = mean_i e0_i^2 (src/model.py:382-385, :428-431) -> e [9,N], t_i [N],
@@ -238,13 +242,14 @@ int dlap_grad_finish(const dlap_plan* plan, const float* wpart, const float* dad
 /* Month-level backward: dh_t = W1[:,F:]^T da_t, LSTM BPTT, and the month-summed gradients
  * grads->{w_ih,w_hh,b_ih,b_hh}, w1[:, F:], b1, wq[:, :M], bq.  dpre [T,4H] is scratch.
  * wpart / dadc_part non-NULL (with the index and precision dlap_cell_bwd ran with; the plan is then also the
- * per-cell plan): the call first does dlap_grad_finish's work -- dadc [T,72] becomes an output -- and hides most
- * of it behind the serial recurrence: CTA 0 of the BPTT kernel sums the da_t | dc_t partials, its other CTAs the
- * weight-gradient partials.  Two launches. */
+ * per-cell plan): the call also does dlap_grad_finish's work -- dadc [T,72] becomes an output -- on extra CTAs of
+ * the BPTT kernel: the recurrence's CTA stages its tables meanwhile and waits for the da_t | dc_t rows, the
+ * weight-gradient sums run beside the serial chain.  counter (device, one uint32, zero when the call starts and
+ * zero again when it has finished; required with partials).  Two launches. */
 int dlap_macro_bwd(const dlap_plan* plan, const float* macro, const dlap_tensors* params, const float* h0,
                    const float* c0, const float* lstm_save, float* dadc, float* dpre, int want_sdf,
                    int want_mom, const dlap_tensors* grads, const float* wpart, const float* dadc_part,
-                   const int32_t* index, int precision, void* stream);
+                   const int32_t* index, int precision, uint32_t* counter, void* stream);
 
 /* get_weights (src/model.py:565-594): w = m (u - mu_t), mu_t the month's mean of u over unmasked stocks;
  * normalized != 0 divides each month by clamp(sum_i |w| m, 1e-8) (the Python loop of :586-590).
