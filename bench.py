@@ -486,6 +486,27 @@ def single_gpu_legs(args, dev, model, new_model, resident, graphed, timed, kerne
         k3 = max(3, min(k, 10))
         out["fp32_path"] = rate(timed(s32, k3), k3)
         del m32
+    # a whole epoch of src/train.py:45-103 -- zero_grad, forward, backward, clip_grad_norm_, Adam -- as one graph replay
+    # (device time), and through training.train_epoch with its one device-to-host read per epoch (host wall clock)
+    from deeplearninginassetpricing_paperreplication_b200 import FusedClipAdam, train_epoch
+    m_ep = new_model()
+    opt = FusedClipAdam(m_ep.sdf_net.parameters(), lr=1e-3)
+    gs = m_ep.train().graphed_step(*resident, phase="conditional", optimizer=opt, max_norm=1.0)
+    for _ in range(3):
+        gs.step()
+    legs["epoch_graph_clip_adam"] = dict(rate(timed(gs.step, k), k), launches=gs.launches)
+    data = {"macro_features": resident[0], "individual_features": resident[1], "returns": resident[2], "mask": resident[3]}
+    for _ in range(3):
+        train_epoch(m_ep, opt, data, dev, phase="conditional", scope="sdf")
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(k):
+        train_epoch(m_ep, opt, data, dev, phase="conditional", scope="sdf")
+    wall = (time.perf_counter() - t0) / k
+    legs["train_epoch_wall"] = {"value": cells / wall, "unit": "stock-months/s", "ms_per_epoch": wall * 1e3,
+                                "what": "training.train_epoch(): graph replay + one D2H copy of the epoch's numbers + sync"}
+    out["epoch_ms"] = legs["epoch_graph_clip_adam"]["ms_per_step"]
+    del gs, m_ep, opt
     out["legs"] = legs
 
     # "the Blackwell kernel to beat" (SURVEY.md §8d): the reference's own eager torch ops on this GPU

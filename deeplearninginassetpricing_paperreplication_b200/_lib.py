@@ -17,7 +17,7 @@ ROOT = os.path.dirname(PKG_DIR)
 CSRC = os.path.join(PKG_DIR, "csrc")
 LIB_PATH = os.path.join(PKG_DIR, "libdlap_b200.so")
 OBJ_DIR = os.path.join(PKG_DIR, "build")          # objects: git- and gpurun-ignored
-SOURCES = ("capi.cu", "cell_fwd.cu", "cell_bwd.cu", "reduce.cu", "step_reduce.cu", "macro_lstm.cu", "tc_selftest.cu",
+SOURCES = ("capi.cu", "cell_fwd.cu", "cell_bwd.cu", "reduce.cu", "step_reduce.cu", "macro_lstm.cu", "adam.cu", "tc_selftest.cu",
            "cell_fwd_tc.cu", "cell_bwd_tc.cu", "panel_index.cu")
 NVCC_FLAGS = ("-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-shared", "-Xcompiler", "-fPIC")
@@ -53,6 +53,16 @@ class DlapMacroIO(C.Structure):
                 ("c_t", C.c_void_p), ("hn", C.c_void_p), ("cn", C.c_void_p), ("sync", C.c_void_p)]
 
 
+ADAM_MAX_TENSORS = 16
+
+
+class DlapAdamTensors(C.Structure):
+    """dlap_adam_tensors: parameter / gradient / moment pointers of one optimiser step."""
+    _fields_ = [("count", C.c_int32), ("param", C.c_void_p * ADAM_MAX_TENSORS), ("grad", C.c_void_p * ADAM_MAX_TENSORS),
+                ("exp_avg", C.c_void_p * ADAM_MAX_TENSORS), ("exp_avg_sq", C.c_void_p * ADAM_MAX_TENSORS),
+                ("numel", C.c_int64 * ADAM_MAX_TENSORS)]
+
+
 _P = C.c_void_p
 _MIO = C.POINTER(DlapMacroIO)
 _PLAN = C.POINTER(DlapPlan)
@@ -74,6 +84,7 @@ SIGNATURES = {
     "dlap_grad_finish": (_PLAN, _P, _P, _P, _I, _I, _I, _TENS, _P, _I, _P),
     "dlap_macro_bwd": (_PLAN, _P, _TENS, _P, _P, _P, _P, _P, _I, _I, _TENS, _P, _P, _P, _I, _P, _P),
     "dlap_weights": (_PLAN, _P, _P, _P, _I, _P, _P),
+    "dlap_clip_adam": (C.POINTER(DlapAdamTensors), C.c_float, C.c_float, C.c_float, C.c_float, C.c_float, _P, _P, _P),
     "dlap_debug_timeline": (_P,),
     "dlap_umma_selftest": (_P, _I, _P, _I, _I, _I, _I, _I, _I, _I, _I, _I, _I, _I, _I, _P, _P),
     "dlap_umma_ts_selftest": (_P, _P, _I, _I, _I, _I, _I, _I, _I, _I, _P, _P, _P),

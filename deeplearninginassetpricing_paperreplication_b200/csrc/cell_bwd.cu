@@ -154,7 +154,7 @@ __global__ void __launch_bounds__(NT, 1) cell_bwd_f32_kernel(const CellParams P)
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
         const float q = tanhf(qp[i]);
-        const float gk = live ? s.sc[3] * __ldg(P.G + (size_t)(4 * half + i) * P.N + n0 + cell) : 0.f;
+        const float gk = live ? s.sc[3] * __ldg(P.G + (size_t)(n0 + cell) * GS + 4 * half + i) : 0.f;
         dp[i] = gk * cq * (1.f - q * q);
         b.dps[(4 * half + i) * TILE + cell] = dp[i];
       }

@@ -313,9 +313,15 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
       const size_t gi = (size_t)t * P.N + (pf_live ? n : 0);
       pf_gi = (uint32_t)gi;
       pf_r = pf_live ? __ldg(P.R + gi) : 0.f;            // consumed one phase later: no stall here
-      if (mom_warp) {
+      if (mom_warp) {                                    // the stock's eight coefficients: one 32-byte piece of its G row
+        const float4* gr = reinterpret_cast<const float4*>(P.G + (size_t)(pf_live ? n : 0) * GS);
+        const float4 ga = __ldg(gr), gb = __ldg(gr + 1);
+        pf_g[0] = ga.x; pf_g[1] = ga.y; pf_g[2] = ga.z; pf_g[3] = ga.w;
+        pf_g[4] = gb.x; pf_g[5] = gb.y; pf_g[6] = gb.z; pf_g[7] = gb.w;
+        if (!pf_live) {
 #pragma unroll
-        for (int k = 0; k < 8; ++k) pf_g[k] = pf_live ? __ldg(P.G + (size_t)k * P.N + n) : 0.f;
+          for (int k = 0; k < 8; ++k) pf_g[k] = 0.f;
+        }
       }
       if (t != ms_month) {
         ms_month = t;

@@ -43,7 +43,7 @@ struct CellParams {
   const float* cot[2];       // device scalars dL/dL_c, dL/dL_u: dS_t = cot[0] dS2[t][0] + cot[1] dS2[t][1]
   int ncot;                  // 2
   const float* dpr_cot;      // [T] cotangent of portfolio_returns, or null
-  const float* G;            // [9,N]   unit coefficients; rows 0..7 (times gc): G_k, row 8: Gu
+  const float* G;            // [N,GS]  unit loss coefficients per stock: G_0..G_7 (times the L_c cotangent), G_u
   const float* scalars;      // [SC_W]  (n_bar)
   int weighted;              // weighted_loss flag
   // backward outputs

@@ -13,6 +13,7 @@ namespace dlap {
 constexpr int D1 = 64;        // first hidden width   (hidden_dim[0])
 constexpr int D2 = 64;        // second hidden width  (hidden_dim[1])
 constexpr int KM = 8;         // moments              (num_condition_moment)
+constexpr int GS = 12;        // row pitch of the per-stock loss coefficients G [N,GS]: G_0..G_7, G_u, 3 floats of padding
 constexpr int TILE = 128;     // stock-months per tile; a tile never straddles a month
 constexpr int NT = 256;       // threads per CTA of the per-cell kernels
 constexpr int FMAX = 64;      // characteristics supported by the smem layout

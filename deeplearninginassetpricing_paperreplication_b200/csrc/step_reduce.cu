@@ -36,7 +36,7 @@ struct ReduceParams {
   float* w_out;              // [T,N] or null
   double* col_part;          // [nsplit,10,N]
   int nsplit, tchunk;        // month chunks of phase 1; phase 2 sums them into chunk 0, which phase 3 reads
-  float* e; float* t_i; float* G;      // [9,N], [N], [9,N]
+  float* e; float* t_i; float* G;      // [9,N], [N], [N,GS] (stock-major rows: G_0..G_7, G_u, padding)
   double* loss_part;         // [ceil(N/64), 2]
   double* dS2;               // [T,2] or null (no backward pass will follow)
   double* row_part;          // [T,nseg,4] partial sums of the per-month phases
@@ -224,10 +224,12 @@ __global__ void __launch_bounds__(RT, 4) step_reduce_kernel(const ReduceParams P
         for (int k = 0; k < KM + 2; ++k) out[(size_t)k * N] = acc[k];
       }
     }
-    if (P.phase_hi >= 2) grid_sync(P.bar, ++nsync);
+    if (P.phase_hi >= 2 && !(P.phase_hi == 2 && P.nsplit == 1)) grid_sync(P.bar, ++nsync);
   }
 
   // ---------------------------------------------------------------- phase 2: month chunks -> chunk 0
+  // (every CTA takes part: 10 N sums of nsplit terms.  Measured against letting phase 3 add the chunks itself, one
+  // thread per stock and one barrier less: 66 us against 71 for the whole kernel at the paper shape)
   if (P.phase_lo <= 2 && P.phase_hi >= 2 && P.nsplit > 1) {
     const size_t n10 = (size_t)(KM + 2) * N;
     for (size_t idx = (size_t)blockIdx.x * RT + tid; idx < n10; idx += (size_t)gridDim.x * RT) {
@@ -236,6 +238,7 @@ __global__ void __launch_bounds__(RT, 4) step_reduce_kernel(const ReduceParams P
       P.col_part[idx] = s;
     }
   }
+
   if (P.phase_lo <= 2 && P.phase_hi >= 3 && P.nsplit > 1) grid_sync(P.bar, ++nsync);
 
   // ---------------------------------------------------------------- phase 3: e, T_i, unit coefficients, sum e^2
@@ -252,14 +255,20 @@ __global__ void __launch_bounds__(RT, 4) step_reduce_kernel(const ReduceParams P
         const float tif = (float)ti;
         P.t_i[i] = tif;
         const float inv = 1.f / ((float)P.n_total * tif);
+        float g[GS];
 #pragma unroll
         for (int k = 0; k <= KM; ++k) {
           const float e = (float)(v[k] / ti);
           P.e[(size_t)k * N + i] = e;
           // autograd of mean_k mean_i e^2 and of mean_i e0^2 for a unit cotangent
-          P.G[(size_t)k * N + i] = k < KM ? ((2.f / KM) * e) * inv : (2.f * e) * inv;
+          g[k] = k < KM ? ((2.f / KM) * e) * inv : (2.f * e) * inv;
           if (k < KM) sc += (double)e * (double)e; else su += (double)e * (double)e;
         }
+        g[9] = g[10] = g[11] = 0.f;
+        float4* go = reinterpret_cast<float4*>(P.G + (size_t)i * GS);
+        go[0] = make_float4(g[0], g[1], g[2], g[3]);
+        go[1] = make_float4(g[4], g[5], g[6], g[7]);
+        go[2] = make_float4(g[8], g[9], g[10], g[11]);
       }
       __syncthreads();
       sc = block_sum(sc, red);
@@ -292,12 +301,15 @@ __global__ void __launch_bounds__(RT, 4) step_reduce_kernel(const ReduceParams P
         double v[4] = {0.0, 0.0, 0.0, 0.0};
         auto cell = [&](int i, size_t vi, bool live) {
           const float r = __ldg(P.R + base + i);
+          const float4* gi = reinterpret_cast<const float4*>(P.G + (size_t)i * GS);
           float c = 0.f;
           if (P.q) {
+            const float4 ga = __ldcg(gi), gb = __ldcg(gi + 1);
+            const float gk[KM] = {ga.x, ga.y, ga.z, ga.w, gb.x, gb.y, gb.z, gb.w};
 #pragma unroll
-            for (int k = 0; k < KM; ++k) c = fmaf(__ldcg(P.G + (size_t)k * N + i), __ldcg(P.q + k * plane + vi) * r, c);
+            for (int k = 0; k < KM; ++k) c = fmaf(gk[k], __ldcg(P.q + k * plane + vi) * r, c);
           }
-          const float uu = __ldcg(P.G + (size_t)KM * N + i) * r;
+          const float uu = __ldcg(P.G + (size_t)i * GS + KM) * r;
           v[0] += live ? (double)c : 0.0;
           v[1] += live ? (double)uu : 0.0;
         };

@@ -31,6 +31,7 @@ SC_W = 8      # scalars width
 SC_LC, SC_LU, SC_SHARPE, SC_NBAR = 0, 1, 2, 3
 RS_NT, RS_MU, RS_P, RS_PR, RS_S, RS_RBAR = 0, 1, 2, 3, 4, 5
 KM = 8
+GS = 12        # row pitch of the per-stock loss coefficients G [N, GS]
 TC_MAX_F = 46   # characteristics the tensor-core kernels take (the ones column of the X image sits at k = 46)
 
 _PRECISIONS = {"fp32": _lib.DLAP_PREC_FP32, "bf16x3": _lib.DLAP_PREC_BF16X3}
@@ -383,7 +384,7 @@ def step_reduce(ws: Workspace, cp: CellPass, R, mask, weighted_loss: bool, want_
     w = torch.empty(T, N, dtype=torch.float32, device=dev)
     e = torch.empty(KM + 1, N, dtype=torch.float32, device=dev)
     t_i = torch.empty(N, dtype=torch.float32, device=dev)
-    G = torch.empty(KM + 1, N, dtype=torch.float32, device=dev)
+    G = torch.empty(N, GS, dtype=torch.float32, device=dev)
     dS2 = torch.empty(T, 2, dtype=torch.float64, device=dev) if want_backward else None
 
     def launch(lo, hi):

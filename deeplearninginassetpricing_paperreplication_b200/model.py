@@ -302,9 +302,10 @@ class AssetPricingGAN(nn.Module):
         }, moments_fn=moments)
 
     def graphed_step(self, macro_features, individual_features, returns, mask, hidden=None,
-                     phase: str = 'conditional') -> "GraphedStep":
-        """CUDA-graph capture of zero_grad + forward + backward on a resident panel (see GraphedStep)."""
-        return GraphedStep(self, macro_features, individual_features, returns, mask, hidden, phase)
+                     phase: str = 'conditional', optimizer=None, max_norm: Optional[float] = None) -> "GraphedStep":
+        """CUDA-graph capture of zero_grad + forward + backward (+ clip + Adam) on a resident panel (see GraphedStep)."""
+        return GraphedStep(self, macro_features, individual_features, returns, mask, hidden, phase,
+                           optimizer=optimizer, max_norm=max_norm)
 
     # -- evaluation cache (SURVEY.md §8f row 1) ---------------------------------------------------------
     # evaluate() of src/train.py:106-153 calls get_weights(normalized=True) and then forward(phase='conditional') on
@@ -374,13 +375,22 @@ class GraphedStep:
     loops do); copy new VALUES into them with ``.copy_()`` if needed, but keep the mask: its valid-cell index
     is part of the capture.  With dropout on (model.train(), p > 0) the seed lives in device memory and the graph
     itself advances it, so every replay draws a fresh mask; month-sharded ranks start from the same seed.  A
-    month-sharded model captures its NCCL all-reduces with the kernels; every rank must then replay in lock-step."""
+    month-sharded model captures its NCCL all-reduces with the kernels; every rank must then replay in lock-step.
+
+    ``optimizer`` (a training.FusedClipAdam): the graph ends with ``clip_grad_norm_(its parameters, max_norm)`` +
+    ``optimizer.step()`` (src/train.py:87-94) as one more launch, i.e. a replay is a whole training epoch of the
+    reference's full-batch loop; ``optimizer.grad_norm`` then holds the gradient norm of the last replay.  The warm-up
+    steps before the capture do not touch the parameters or the optimiser state."""
 
     def __init__(self, model: "AssetPricingGAN", macro_features, individual_features, returns, mask,
-                 hidden=None, phase: str = 'conditional', warmup: int = 3):
+                 hidden=None, phase: str = 'conditional', warmup: int = 3, optimizer=None,
+                 max_norm: Optional[float] = None):
         self.model, self.args = model, (macro_features, individual_features, returns, mask)
         self.seed = None
         self._one = None
+        self.optimizer, self.max_norm = optimizer, max_norm
+        if optimizer is not None:
+            optimizer.ensure_state()          # allocations with a fill must not be part of the capture
         if model.training and model.sdf_net.dropout_p > 0:
             s0 = int(torch.randint(0, 2 ** 62, (1,)).item())
             if model.month_shard is not None:             # the same masks on every rank
@@ -407,11 +417,13 @@ class GraphedStep:
             torch.autograd.graph.set_warn_on_accumulate_grad_stream_mismatch(False)
         except AttributeError:
             pass
+        o0 = optimizer.launches if optimizer is not None else 0
         with torch.cuda.graph(self.graph):
-            self.out = self._eager(zero=False)
-        self.launches = ws_launches() - l0                # kernels of this library inside one replay
+            self.out = self._eager(zero=False, apply=True)
+        # kernels of this library inside one replay
+        self.launches = ws_launches() - l0 + ((optimizer.launches - o0) if optimizer is not None else 0)
 
-    def _eager(self, zero=True):
+    def _eager(self, zero=True, apply=False):
         if zero:
             self.model.zero_grad(set_to_none=True)
         self.model._seed_dev = self.seed
@@ -422,12 +434,24 @@ class GraphedStep:
             if self._one is None:                       # root gradient: made once, not filled on every replay
                 self._one = torch.ones_like(out['loss'])
             out['loss'].backward(gradient=self._one)
+            if apply and self.optimizer is not None:
+                self.optimizer.step(self.max_norm)
+                # what an epoch reports (src/train.py:96-103), packed for ONE device-to-host copy:
+                # loss, L_u, L_c, gradient norm, then the T portfolio returns
+                with torch.no_grad():
+                    self.report = torch.cat([torch.stack([out['loss'], out['loss_unconditional'],
+                                                          out['loss_conditional'], self.optimizer.grad_norm[0]]),
+                                             out['portfolio_returns']])
         finally:
             self.model._seed_dev = None
         return out
 
     def step(self):
         self.graph.replay()
+        if self.optimizer is not None:      # the replay moved the parameters behind torch's back
+            from .training import bump_versions
+            bump_versions([p for p in self.optimizer.params if p.grad is not None])
+            self.model._cells = None
         return self.out
 
     __call__ = step

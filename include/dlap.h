@@ -176,7 +176,8 @@ int dlap_cell_fwd(const dlap_plan* plan, const float* x, const uint8_t* mask, co
  *      and the demeaned weights w = m (u - mu_t) (src/model.py:271-279)      -> w_out [T,N] when non-NULL
  *   2  the month chunks summed into chunk 0 of col_part (month shards all-reduce col_part[0] after this phase)
  *   3  e_ki = colsum / T_i (src/model.py:382, :428) -> e [9,N], t_i [N]; the loss coefficients for UNIT cotangents,
- *      G_ki = 2 e_ki / (K N T_i), G_8i = 2 e0_i / (N T_i) (autograd at src/train.py:84)  -> G [9,N]
+ *      G_ki = 2 e_ki / (K N T_i), G_8i = 2 e0_i / (N T_i) (autograd at src/train.py:84)
+ *                              -> G [N,12], one row per stock: G_0i .. G_7i, G_8i, three floats of padding
  *   4  L_c = mean_k mean_i e_ki^2, L_u = mean_i e0_i^2 (src/model.py:385, :429-431) -> scalars[0], scalars[1];
  *      dS2 [T,2] (double): dS_t for unit cotangents of L_c and of L_u; dS2 NULL: no backward pass will follow
  * Single device: phases 0..4 in one launch.  q may be NULL (phase 'unconditional').  index: the valid-cell index
@@ -256,6 +257,25 @@ int dlap_macro_bwd(const dlap_plan* plan, const float* macro, const dlap_tensors
  * index: the layout of u (as for dlap_step_reduce). */
 int dlap_weights(const dlap_plan* plan, const float* u, const uint8_t* mask, const int32_t* index, int normalized,
                  float* w_out, void* stream);
+
+/* clip_grad_norm_ + optimizer.step() of the training loop (src/train.py:87-94: torch.nn.utils.clip_grad_norm_ over
+ * the scope's parameters, then torch.optim.Adam with its defaults: no weight decay, no amsgrad) over up to
+ * DLAP_ADAM_MAX_TENSORS tensors in ONE launch: the 2-norm of all gradients -> *grad_norm (device, may be NULL); with
+ * max_norm > 0 every gradient is scaled IN PLACE by min(max_norm / (norm + 1e-6), 1); then exp_avg, exp_avg_sq and
+ * the parameters are updated with Adam's arithmetic, op for op.  *step (device, one int64: the number of updates so
+ * far) is incremented, so the call can be replayed from a CUDA graph.  The training step's twelve tensors are
+ * 12,233 numbers: one CTA. */
+#define DLAP_ADAM_MAX_TENSORS 16
+typedef struct dlap_adam_tensors {
+  int32_t count;
+  float* param[DLAP_ADAM_MAX_TENSORS];
+  float* grad[DLAP_ADAM_MAX_TENSORS];
+  float* exp_avg[DLAP_ADAM_MAX_TENSORS];
+  float* exp_avg_sq[DLAP_ADAM_MAX_TENSORS];
+  int64_t numel[DLAP_ADAM_MAX_TENSORS];
+} dlap_adam_tensors;
+int dlap_clip_adam(const dlap_adam_tensors* tensors, float max_norm, float lr, float beta1, float beta2, float eps,
+                   int64_t* step, float* grad_norm, void* stream);
 
 /* Diagnostics (no counterpart in the reference): when `stamps` is a device buffer of 3*256*16 int64, every
  * following tensor-core dlap_cell_bwd (first third of the buffer: epilogue and MMA warps per tile; last third:

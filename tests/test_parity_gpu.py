@@ -124,8 +124,9 @@ def _check_reduce_stage(red, ref, s, T, N):
     assert rel_err(_np(red.w), ref["weights"]) < WEIGHT_TOL
     K = 8
     Gc = 2.0 * s["e"] / (K * N * s["t_i"]); Gu = 2.0 * s["e0"] / (N * s["t_i"])
-    G = _np(red.G)
+    G = _np(red.G).T                                           # [N,12] stock-major rows -> [12,N]
     assert np.abs(G[:8] - Gc).max() < 1e-5 * np.abs(Gc).max() and np.abs(G[8] - Gu).max() < 1e-5 * np.abs(Gu).max()
+    assert not G[9:].any()
     dSc = (s["rm"] * np.einsum("kn,tnk->tn", Gc, s["q"])).sum(axis=1)
     dSu = (s["rm"] * Gu[None, :]).sum(axis=1)
     dS2 = _np(red.dS2)

@@ -67,16 +67,21 @@ def _config(train, **extra):
     return cfg
 
 
-def _run(rt, model_cls, cfg, data, device, **kw):
+def _run(rt, model_cls, cfg, data, device, fused_epoch=False, **kw):
     torch.manual_seed(42)
     np.random.seed(42)
-    saved = rt.AssetPricingGAN
+    saved = rt.AssetPricingGAN, rt.train_epoch, rt.optim
     rt.AssetPricingGAN = model_cls                      # the import swap, and nothing else
+    if fused_epoch:                                     # ... or, second swap: the epoch as one CUDA graph
+        import types
+        from deeplearninginassetpricing_paperreplication_b200 import FusedClipAdam, train_epoch
+        rt.train_epoch = train_epoch
+        rt.optim = types.SimpleNamespace(Adam=FusedClipAdam)
     try:
         with contextlib.redirect_stdout(io.StringIO()):
             model, history = rt.train_3phase(cfg, data[0], data[1], data[2], device=device, **kw)
     finally:
-        rt.AssetPricingGAN = saved
+        rt.AssetPricingGAN, rt.train_epoch, rt.optim = saved
     return model, {k: np.asarray(v) for k, v in history.items()}
 
 
@@ -90,13 +95,17 @@ def cpu_run():
     return dict(rt=rt, sets=sets, data=data, kw=kw, model=model, hist=hist)
 
 
-@pytest.mark.parametrize("precision", [None, "fp32", "bf16x3"])
-def test_reference_train_3phase_on_the_drop_in(cpu_run, precision):
-    """precision None: the reference's config dict as it is (no b200_* key) -- must reach the tensor-core kernels."""
+@pytest.mark.parametrize("precision,fused_epoch", [(None, False), ("fp32", False), ("bf16x3", False), ("fp32", True),
+                                                   ("bf16x3", True)])
+def test_reference_train_3phase_on_the_drop_in(cpu_run, precision, fused_epoch):
+    """precision None: the reference's config dict as it is (no b200_* key) -- must reach the tensor-core kernels.
+    fused_epoch: train_epoch and optim.Adam of src/train.py are swapped too (training.train_epoch, FusedClipAdam): every
+    epoch is one CUDA-graph replay and one device-to-host copy; evaluate() and the loop stay the reference's."""
     from deeplearninginassetpricing_paperreplication_b200 import AssetPricingGAN
     rt, sets, data = cpu_run["rt"], cpu_run["sets"], cpu_run["data"]
     extra = {} if precision is None else {"b200_precision": precision}
-    model, hist = _run(rt, AssetPricingGAN, _config(sets[0], **extra), data, torch.device("cuda:0"), **cpu_run["kw"])
+    model, hist = _run(rt, AssetPricingGAN, _config(sets[0], **extra), data, torch.device("cuda:0"),
+                       fused_epoch=fused_epoch, **cpu_run["kw"])
     if precision is None:
         assert model._precision(sets[0].individual_feature_dim) == "bf16x3"
     ref = cpu_run["hist"]

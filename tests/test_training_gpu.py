@@ -1,0 +1,122 @@
+"""clip_grad_norm_ + Adam as one launch, and the whole epoch of src/train.py:45-103 as one CUDA
+graph -- against torch.optim.Adam + torch.nn.utils.clip_grad_norm_ themselves."""
+import numpy as np
+import pytest
+import torch
+
+from deeplearninginassetpricing_paperreplication_b200 import AssetPricingGAN, FusedClipAdam, train_epoch
+from test_parity_gpu import dev, make_panel
+
+pytestmark = pytest.mark.gpu
+
+SHAPES = [(16, 178), (16, 4), (16,), (16,), (64, 50), (64,), (64, 64), (64,), (1, 64), (1,), (8, 224), (8,)]
+
+
+@pytest.mark.parametrize("max_norm", [0.0, 1.0])
+def test_fused_clip_adam_matches_torch_over_100_steps(max_norm):
+    d = dev()
+    g = torch.Generator(device=d).manual_seed(5)
+    ours = [torch.nn.Parameter(torch.randn(*s, generator=g, device=d)) for s in SHAPES]
+    ref = [torch.nn.Parameter(p.detach().clone()) for p in ours]
+    opt = FusedClipAdam(ours, lr=1e-3, max_norm=max_norm)
+    ropt = torch.optim.Adam(ref, lr=1e-3)
+    for step in range(100):
+        scale = 10.0 ** float(torch.randint(-4, 1, (1,)))          # gradient norms on both sides of the clip
+        for p, r in zip(ours, ref):
+            gr = scale * torch.randn(p.shape, generator=g, device=d)
+            p.grad = gr.clone(); r.grad = gr.clone()
+        if step % 7 == 3:                                            # a parameter without gradient is skipped
+            ours[3].grad = None; ref[3].grad = None
+        if max_norm > 0:
+            rn = torch.nn.utils.clip_grad_norm_(ref, max_norm)
+        ropt.step()
+        versions = [p._version for p in ours]
+        opt.step()
+        assert all(p._version > v for p, v in zip(ours, versions) if p.grad is not None)
+        if max_norm > 0:
+            assert abs(float(opt.grad_norm) - float(rn)) <= 2e-6 * float(rn)
+            for p, r in zip(ours, ref):                              # clip_grad_norm_ scales the gradients in place
+                if p.grad is not None:
+                    assert torch.allclose(p.grad, r.grad, rtol=2e-6, atol=0)
+    for p, r in zip(ours, ref):
+        err = float((p - r).abs().max() / r.abs().max())
+        assert err < 1e-6, err
+    sd = opt.state_dict()
+    rsd = ropt.state_dict()
+    assert float(sd["state"][0]["step"]) == float(rsd["state"][0]["step"]) == 100.0
+    assert torch.allclose(sd["state"][4]["exp_avg_sq"], rsd["state"][4]["exp_avg_sq"], rtol=1e-5, atol=1e-30)
+
+
+@pytest.mark.parametrize("precision,phase,dropout", [("bf16x3", "conditional", 0.0), ("fp32", "unconditional", 0.0),
+                                                     ("bf16x3", "moment", 0.0)])
+def test_graphed_epoch_matches_the_eager_torch_loop(precision, phase, dropout):
+    """zero_grad + forward + backward + clip + Adam replayed from one CUDA graph against the same model stepped
+    eagerly with torch.optim.Adam and clip_grad_norm_ (src/train.py:77-94): 40 epochs."""
+    d = dev()
+    macro, x, R, mask = [t.to(d) for t in make_panel(20, 600, 8, seed=3)]
+    cfg = {"macro_feature_dim": 8, "individual_feature_dim": 46, "dropout": dropout, "b200_precision": precision}
+    torch.manual_seed(9)
+    a = AssetPricingGAN(cfg).to(d)
+    b = AssetPricingGAN(cfg).to(d)
+    b.load_state_dict(a.state_dict())
+    scope = "moment" if phase == "moment" else "sdf"
+    for m in (a, b):
+        for p in m.sdf_net.parameters():
+            p.requires_grad = phase != "moment"
+    pa = list(a.moment_net.parameters() if scope == "moment" else a.sdf_net.parameters())
+    pb = list(b.moment_net.parameters() if scope == "moment" else b.sdf_net.parameters())
+    ropt = torch.optim.Adam(pa, lr=1e-3)
+    opt = FusedClipAdam(pb, lr=1e-3)
+    before = [p.detach().clone() for p in pb]
+    gs = b.train().graphed_step(macro, x, R, mask, phase=phase, optimizer=opt, max_norm=1.0)
+    assert all(torch.equal(p, q) for p, q in zip(pb, before))          # warm-up and capture moved nothing
+    assert gs.launches == (6 if precision == "bf16x3" else 7)
+    a.train()
+    for epoch in range(40):
+        ropt.zero_grad()
+        out = a(macro, x, R, mask, phase=phase)
+        out["loss"].backward()
+        rn = torch.nn.utils.clip_grad_norm_(pa, 1.0)
+        ropt.step()
+        got = gs.step()
+        torch.cuda.synchronize()
+        assert abs(float(got["loss"]) - float(out["loss"])) <= 2e-5 * abs(float(out["loss"])), epoch
+        assert abs(float(opt.grad_norm) - float(rn)) <= 2e-5 * float(rn)
+        rep = gs.report.cpu().numpy()
+        assert rep[0] == float(got["loss"]) and rep[3] == float(opt.grad_norm)
+        assert np.array_equal(rep[4:], got["portfolio_returns"].cpu().numpy())
+    for (k, p), q in zip(a.named_parameters(), b.parameters()):
+        if k == "sdf_net.output_proj.bias":
+            continue
+        assert float((p - q).abs().max()) <= 2e-5 * float(p.abs().max()), k
+
+
+def test_train_epoch_signature_and_report():
+    """train_epoch(model, optimizer, data, device, phase, grad_clip, scope) -> the reference's dict, from host tensors
+    that are uploaded once."""
+    d = dev()
+    macro, x, R, mask = make_panel(12, 300, 8, seed=4)
+    data = {"macro_features": macro, "individual_features": x, "returns": R, "mask": mask}
+    torch.manual_seed(2)
+    model = AssetPricingGAN({"macro_feature_dim": 8, "individual_feature_dim": 46, "dropout": 0.0}).to(d)
+    ref = AssetPricingGAN({"macro_feature_dim": 8, "individual_feature_dim": 46, "dropout": 0.0}).to(d)
+    ref.load_state_dict(model.state_dict())
+    opt = FusedClipAdam(model.sdf_net.parameters(), lr=1e-3)
+    ropt = torch.optim.Adam(ref.sdf_net.parameters(), lr=1e-3)
+    for epoch in range(5):
+        m = train_epoch(model, opt, data, d, phase="unconditional", scope="sdf")
+        assert sorted(m) == ["grad_norm", "loss", "loss_cond", "loss_residual", "loss_unc", "sharpe"]
+        ref.train(); ropt.zero_grad()
+        out = ref(macro.to(d), x.to(d), R.to(d), mask.to(d), phase="unconditional")
+        out["loss"].backward()
+        rn = torch.nn.utils.clip_grad_norm_(ref.sdf_net.parameters(), 1.0)
+        ropt.step()
+        pr = out["portfolio_returns"].detach()
+        assert abs(m["loss"] - float(out["loss"])) <= 2e-5 * abs(float(out["loss"]))
+        assert abs(m["sharpe"] - float(pr.mean() / pr.std())) <= 1e-4 * abs(float(pr.mean() / pr.std())) + 1e-6
+        assert abs(m["grad_norm"] - float(rn)) <= 2e-5 * float(rn) and m["loss_cond"] == 0.0
+    assert len(model._epoch_graphs) == 1                              # one capture, five replays
+    with pytest.raises(NotImplementedError):
+        train_epoch(model, opt, data, d, phase="conditional", scope="all")
+    with pytest.raises(TypeError):
+        train_epoch(model, ropt, data, d)
