@@ -24,6 +24,8 @@ NVCC_FLAGS = ("-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", 
 
 DLAP_PREC_FP32 = 0
 DLAP_PREC_BF16X3 = 1
+DLAP_REDUCE_NO_DEMEAN = 1
+DLAP_REDUCE_Q_DENSE = 2
 
 
 class DlapDims(C.Structure):
@@ -49,7 +51,7 @@ class DlapTensors(C.Structure):
 class DlapMacroIO(C.Structure):
     """dlap_macro_io: the macro side of a per-cell call (include/dlap.h)."""
     _fields_ = [("macro", C.c_void_p), ("series_T", C.c_int32), ("month0", C.c_int32), ("month_stride", C.c_int32),
-                ("h0", C.c_void_p), ("c0", C.c_void_p), ("lstm_save", C.c_void_p), ("a_t", C.c_void_p),
+                ("tables_ready", C.c_int32), ("h0", C.c_void_p), ("c0", C.c_void_p), ("lstm_save", C.c_void_p), ("a_t", C.c_void_p),
                 ("c_t", C.c_void_p), ("hn", C.c_void_p), ("cn", C.c_void_p), ("sync", C.c_void_p)]
 
 
@@ -60,7 +62,7 @@ class DlapAdamTensors(C.Structure):
     """dlap_adam_tensors: parameter / gradient / moment pointers of one optimiser step."""
     _fields_ = [("count", C.c_int32), ("param", C.c_void_p * ADAM_MAX_TENSORS), ("grad", C.c_void_p * ADAM_MAX_TENSORS),
                 ("exp_avg", C.c_void_p * ADAM_MAX_TENSORS), ("exp_avg_sq", C.c_void_p * ADAM_MAX_TENSORS),
-                ("numel", C.c_int64 * ADAM_MAX_TENSORS)]
+                ("step", C.c_void_p * ADAM_MAX_TENSORS), ("numel", C.c_int64 * ADAM_MAX_TENSORS)]
 
 
 _P = C.c_void_p
@@ -76,15 +78,15 @@ SIGNATURES = {
     "dlap_panel_index": (_PLAN, _P, _P, _P),
     "dlap_panel_pull": (_PLAN, _P, _P, _P, _I, _I, _P),
     "dlap_cell_fwd": (_PLAN, _P, _P, _P, _TENS, _MIO, _P, _P, _I, C.c_float, C.c_uint64, _P, _P),
-    "dlap_step_reduce": (_PLAN, _P, _P, _P, _P, _P, _I, _P, _I, _I, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P),
+    "dlap_step_reduce": (_PLAN, _P, _P, _P, _P, _P, _I, _I, _P, _I, _I, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P),
     "dlap_loss_finish": (_PLAN, _P, _I, _P, _P, _P, _P, _P, _P),
     "dlap_loss_finish_noalloc": (_PLAN, _P, _I, _P, _P, _P, _P),
     "dlap_cell_bwd": (_PLAN, _P, _P, _P, _P, _TENS, _MIO, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _P, _P, _I,
                       C.c_float, C.c_uint64, _P, _P),
     "dlap_grad_finish": (_PLAN, _P, _P, _P, _I, _I, _I, _TENS, _P, _I, _P),
     "dlap_macro_bwd": (_PLAN, _P, _TENS, _P, _P, _P, _P, _P, _I, _I, _TENS, _P, _P, _P, _I, _P, _P),
-    "dlap_weights": (_PLAN, _P, _P, _P, _I, _P, _P),
-    "dlap_clip_adam": (C.POINTER(DlapAdamTensors), C.c_float, C.c_float, C.c_float, C.c_float, C.c_float, _P, _P, _P),
+    "dlap_weights": (_PLAN, _P, _P, _P, _I, _I, _P, _P),
+    "dlap_clip_adam": (C.POINTER(DlapAdamTensors), C.c_float, C.c_float, C.c_float, C.c_float, C.c_float, _P, _P),
     "dlap_debug_timeline": (_P,),
     "dlap_umma_selftest": (_P, _I, _P, _I, _I, _I, _I, _I, _I, _I, _I, _I, _I, _I, _I, _P, _P),
     "dlap_umma_ts_selftest": (_P, _P, _I, _I, _I, _I, _I, _I, _I, _I, _P, _P, _P),

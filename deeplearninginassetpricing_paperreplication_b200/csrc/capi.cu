@@ -16,14 +16,14 @@ cudaError_t launch_panel_index(const uint8_t* mask, int T, int N, int* index, cu
 cudaError_t launch_panel_pull(const float* x_host, const int* index, int T, int N, int F, float* x_dev, int sms, bool clear,
                               cudaStream_t st);
 cudaError_t launch_step_reduce_c(const dlap_plan* plan, const float* u, const float* q, const float* R, const uint8_t* mask,
-                                 const int* index, int weighted, const float* n_bar_in, int phase_lo, int phase_hi,
+                                 const int* index, int weighted, int flags, const float* n_bar_in, int phase_lo, int phase_hi,
                                  float* row_stats, float* pr, float* scalars, float* w_out, double* col_part, float* e,
                                  float* t_i, float* G, double* loss_part, double* dS2, double* row_part,
                                  unsigned int* bar, cudaStream_t st);
 cudaError_t launch_loss_finish(const double*, int, int, int, float*, float*, double*, unsigned int*, float*,
                                cudaStream_t);
 cudaError_t launch_grad_finish(const FinishParams& P, cudaStream_t st);
-cudaError_t launch_weights(const float*, const uint8_t*, const int*, int, int, int, float*, cudaStream_t);
+cudaError_t launch_weights(const float*, const uint8_t*, const int*, int, int, int, int, float*, cudaStream_t);
 void fill_macro(MacroParams& P, const dlap_plan* plan, int T, const float* macro, const dlap_tensors* p, const float* h0,
                 const float* c0);
 cudaError_t launch_macro_fwd(const MacroParams& P, cudaStream_t st);
@@ -226,7 +226,9 @@ int dlap_cell_fwd(const dlap_plan* plan, const float* x, const uint8_t* mask, co
   // ---- the macro side
   MacroParams MP;
   bool fused = false;
-  if (d.M == 0) {
+  if (!mio->macro && mio->tables_ready) {
+    // a_t / c_t are the caller's
+  } else if (d.M == 0) {
     REQ(params->b1);
     if (q) REQ(params->bq);
     REQ(mio->c_t);
@@ -245,6 +247,8 @@ int dlap_cell_fwd(const dlap_plan* plan, const float* x, const uint8_t* mask, co
     } else {
       CU(launch_macro_fwd(MP, st));
     }
+  } else {
+    return DLAP_E_NULL;       // macro input expected, or tables that are ready
   }
   if (tc) {
     P.cyc_sh = 2;      // blocks of four tiles: measured best of 1, 2, 4, 8 (smaller: more month changes per CTA;
@@ -262,7 +266,7 @@ int dlap_cell_fwd(const dlap_plan* plan, const float* x, const uint8_t* mask, co
 }
 
 int dlap_step_reduce(const dlap_plan* plan, const float* u, const float* q, const float* R, const uint8_t* mask,
-                     const int32_t* index, int weighted_loss, const float* n_bar_in, int phase_lo, int phase_hi,
+                     const int32_t* index, int weighted_loss, int flags, const float* n_bar_in, int phase_lo, int phase_hi,
                      float* row_stats, float* pr, float* scalars, float* w_out, double* col_part, float* e,
                      float* t_i, float* G, double* loss_part, double* dS2, double* row_part, uint32_t* bar,
                      void* stream) {
@@ -273,7 +277,7 @@ int dlap_step_reduce(const dlap_plan* plan, const float* u, const float* q, cons
   if (reinterpret_cast<uintptr_t>(bar) & 3) return DLAP_E_ALIGN;
   if (phase_lo <= 1) { REQ(u); REQ(pr); }
   if (phase_hi >= 3) { REQ(e); REQ(t_i); REQ(G); REQ(loss_part); }
-  CU(launch_step_reduce_c(plan, u, q, R, mask, index, weighted_loss, n_bar_in, phase_lo, phase_hi, row_stats, pr,
+  CU(launch_step_reduce_c(plan, u, q, R, mask, index, weighted_loss, flags, n_bar_in, phase_lo, phase_hi, row_stats, pr,
                           scalars, w_out, col_part, e, t_i, G, loss_part, dS2, row_part, bar, (cudaStream_t)stream));
   return DLAP_OK;
 }
@@ -298,7 +302,8 @@ int dlap_cell_bwd(const dlap_plan* plan, const float* x, const float* R, const u
   if (rc) return rc;
   REQ(x); REQ(R); REQ(mask); REQ(params); REQ(mio); REQ(mio->a_t); REQ(mio->c_t); REQ(row_stats); REQ(dS2); REQ(G);
   REQ(scalars); REQ(wpart); REQ(dadc_part);
-  REQ(params->w1); REQ(params->w2); REQ(params->b2); REQ(params->w3); REQ(params->b3); REQ(params->wq);
+  REQ(params->w1); REQ(params->w2); REQ(params->b2); REQ(params->w3); REQ(params->b3);
+  if (want_mom) REQ(params->wq);
   if (!want_sdf && !want_mom) return DLAP_E_SHAPE;
   if (precision != DLAP_PREC_FP32 && precision != DLAP_PREC_BF16X3) return DLAP_E_PRECISION;
   CellParams P;
@@ -390,11 +395,11 @@ int dlap_macro_bwd(const dlap_plan* plan, const float* macro, const dlap_tensors
 }
 
 int dlap_weights(const dlap_plan* plan, const float* u, const uint8_t* mask, const int32_t* index, int normalized,
-                 float* w_out, void* stream) {
+                 int demean, float* w_out, void* stream) {
   int rc = check_plan(plan);
   if (rc) return rc;
   REQ(u); REQ(mask); REQ(w_out);
-  CU(launch_weights(u, mask, index, plan->dims.T, plan->dims.N, normalized, w_out, (cudaStream_t)stream));
+  CU(launch_weights(u, mask, index, plan->dims.T, plan->dims.N, normalized, demean, w_out, (cudaStream_t)stream));
   return DLAP_OK;
 }
 

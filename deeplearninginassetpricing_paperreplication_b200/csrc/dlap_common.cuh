@@ -20,7 +20,7 @@ constexpr int FMAX = 64;      // characteristics supported by the smem layout
 constexpr int HMAX = 8;       // LSTM units: 4*H gate rows must fit one warp
 
 // row_stats[t][*] written by row_finish
-enum { RS_NT = 0, RS_MU = 1, RS_P = 2, RS_PR = 3, RS_S = 4, RS_RBAR = 5, RS_W = 8 };
+enum { RS_NT = 0, RS_MU = 1, RS_P = 2, RS_PR = 3, RS_S = 4, RS_RBAR = 5, RS_SR = 6 /* sum_i m R */, RS_W = 8 };
 // scalars[*] written by row_finish / loss_finish
 enum { SC_LC = 0, SC_LU = 1, SC_SHARPE = 2, SC_NBAR = 3, SC_ZERO = 7 /* always 0.0 */, SC_W = 8 };
 

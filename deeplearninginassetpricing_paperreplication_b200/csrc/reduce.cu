@@ -92,7 +92,7 @@ __global__ void __launch_bounds__(256) grad_finish_kernel(const FinishParams P) 
 // (src/model.py:271-279, :581-592).  One CTA per month; `index` != null: u is left-packed.
 __global__ void __launch_bounds__(256) weights_kernel(
     const float* __restrict__ u, const uint8_t* __restrict__ mask, const int* __restrict__ index, int T, int N,
-    int normalized, float* __restrict__ w_out) {
+    int normalized, int demean, float* __restrict__ w_out) {
   __shared__ double red[32];
   const int t = blockIdx.x, lane = threadIdx.x & 31;
   const size_t base = (size_t)t * N;
@@ -119,7 +119,7 @@ __global__ void __launch_bounds__(256) weights_kernel(
   }
   su = block_sum(su, red);
   cnt = block_sum(cnt, red);
-  const float mu = (float)(su / fmax(cnt, 1.0));
+  const float mu = demean ? (float)(su / fmax(cnt, 1.0)) : 0.f;
   float denom = 1.f;
   if (normalized) {
     double s = 0.0;
@@ -154,8 +154,8 @@ cudaError_t launch_grad_finish(const FinishParams& P, cudaStream_t st) {
   return cudaGetLastError();
 }
 cudaError_t launch_weights(const float* u, const uint8_t* mask, const int* index, int T, int N, int normalized,
-                           float* w_out, cudaStream_t st) {
-  weights_kernel<<<T, 256, 0, st>>>(u, mask, index, T, N, normalized, w_out);
+                           int demean, float* w_out, cudaStream_t st) {
+  weights_kernel<<<T, 256, 0, st>>>(u, mask, index, T, N, normalized, demean, w_out);
   return cudaGetLastError();
 }
 

@@ -28,6 +28,8 @@ struct ReduceParams {
   const int* index;          // valid-cell index or null (dense u, q)
   int T, N;
   int weighted;
+  int no_demean;             // normalize_w = False (src/model.py:274): w = m u; mu_t and Rbar_t reported as 0
+  int q_dense;               // q is dense [8,T,N] although u is left-packed
   const float* n_bar_in;     // month shards: the series' N_bar; else null
   int n_total;               // stocks in the loss means
   float* row_stats;          // [T,RS_W]
@@ -132,13 +134,14 @@ __global__ void __launch_bounds__(RT, 4) step_reduce_kernel(const ReduceParams P
           }
         }
         if (last) {
-          const double nt = fmax(v[0], 1.0);
-          const float mu = (float)(v[1] / nt);
+            const double nt = fmax(v[0], 1.0);
+          const float mu = P.no_demean ? 0.f : (float)(v[1] / nt);
           float* rs = P.row_stats + (size_t)t * RS_W;
           rs[RS_NT] = (float)nt;
           rs[RS_MU] = mu;
           rs[RS_P] = (float)(v[2] - (double)mu * v[3]);
-          rs[RS_RBAR] = (float)(v[3] / nt);
+          rs[RS_RBAR] = P.no_demean ? 0.f : (float)(v[3] / nt);      // what the backward subtracts from R
+          rs[RS_SR] = (float)v[3];
         }
       }
     }
@@ -211,7 +214,7 @@ __global__ void __launch_bounds__(RT, 4) step_reduce_kernel(const ReduceParams P
         const float r = __ldg(P.R + gi);
         float qv[KM];
 #pragma unroll
-        for (int k = 0; k < KM; ++k) qv[k] = P.q ? __ldcg(P.q + k * plane + vi) : 0.f;
+        for (int k = 0; k < KM; ++k) qv[k] = P.q ? __ldcg(P.q + k * plane + (P.q_dense ? gi : vi)) : 0.f;
         if (P.w_out && in) P.w_out[gi] = live ? (uv - sm[tchunk + t - t0]) : 0.f;
         acc[KM] += live ? (double)(r * S) : 0.0;
         acc[KM + 1] += live ? 1.0 : 0.0;
@@ -318,7 +321,10 @@ __global__ void __launch_bounds__(RT, 4) step_reduce_kernel(const ReduceParams P
           const int per = (cnt + nseg - 1) / nseg, j0 = seg * per, j1 = min(cnt, j0 + per);
           const int* vrow = P.index + idx_off_vidx(T) + base;
 #pragma unroll 2
-          for (int j = j0 + tid; j < j1; j += RT) cell(__ldg(vrow + j), base + j, true);
+          for (int j = j0 + tid; j < j1; j += RT) {
+            const int i = __ldg(vrow + j);
+            cell(i, P.q_dense ? base + i : base + j, true);
+          }
         } else {
           const int per = (N + nseg - 1) / nseg, i0 = seg * per, i1 = min(N, i0 + per);
 #pragma unroll 2
@@ -387,7 +393,7 @@ cudaError_t launch_step_reduce(ReduceParams P, int sms, bool cooperative, cudaSt
 }
 
 cudaError_t launch_step_reduce_c(const dlap_plan* plan, const float* u, const float* q, const float* R, const uint8_t* mask,
-                                 const int* index, int weighted, const float* n_bar_in, int phase_lo, int phase_hi,
+                                 const int* index, int weighted, int flags, const float* n_bar_in, int phase_lo, int phase_hi,
                                  float* row_stats, float* pr, float* scalars, float* w_out, double* col_part, float* e,
                                  float* t_i, float* G, double* loss_part, double* dS2, double* row_part,
                                  unsigned int* bar, cudaStream_t st) {
@@ -396,6 +402,7 @@ cudaError_t launch_step_reduce_c(const dlap_plan* plan, const float* u, const fl
   P.u = u; P.q = q; P.R = R; P.mask = mask; P.index = index;
   P.T = plan->dims.T; P.N = plan->dims.N;
   P.weighted = weighted; P.n_bar_in = n_bar_in; P.n_total = plan->dims.N;
+  P.no_demean = (flags & DLAP_REDUCE_NO_DEMEAN) != 0; P.q_dense = (flags & DLAP_REDUCE_Q_DENSE) != 0;
   P.row_stats = row_stats; P.pr = pr; P.scalars = scalars; P.w_out = w_out;
   P.col_part = col_part; P.nsplit = plan->col_splits; P.tchunk = (plan->dims.T + plan->col_splits - 1) / plan->col_splits;
   P.e = e; P.t_i = t_i; P.G = G; P.loss_part = loss_part; P.dS2 = dS2; P.bar = bar;

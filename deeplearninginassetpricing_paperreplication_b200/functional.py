@@ -199,6 +199,7 @@ class StepOptions:
     dropout_seed: int = 0
     dropout_seed_dev: Optional[torch.Tensor] = None   # int64 [1] on the device: overrides dropout_seed (GraphedStep)
     shard: Optional["MonthShard"] = None
+    demean: bool = True             # normalize_w (src/model.py:274): False = the weights are m u, not demeaned
 
 
 @dataclass
@@ -334,8 +335,10 @@ class CellPass:
 
 def cell_forward(ws: Workspace, macro, x, mask, params, h0, c0, precision: str, need_moments: bool,
                  dropout_p: float = 0.0, dropout_seed: int = 0, dropout_seed_dev=None,
-                 shard: Optional["MonthShard"] = None) -> CellPass:
-    """dlap_cell_fwd: the macro LSTM over the (whole) series and both nets on every stock-month of the panel."""
+                 shard: Optional["MonthShard"] = None, tables=None) -> CellPass:
+    """dlap_cell_fwd: the macro LSTM over the (whole) series and both nets on every stock-month of the panel.
+    tables = (a_t [T,64], c_t [T,8] or None): the per-month biases are the caller's (no LSTM in this call; the
+    workspace is one without macro input)."""
     dev = x.device
     T, N, F = x.shape
     M, H = ws.plan.dims.M, max(ws.plan.dims.H, 1)
@@ -343,12 +346,21 @@ def cell_forward(ws: Workspace, macro, x, mask, params, h0, c0, precision: str, 
     month0, stride = (0, 1) if shard is None else (shard.t0, shard.stride)
     index = ws.panel_index(mask) if precision == "bf16x3" else None
     save = torch.empty(series_T, 6 * H, dtype=torch.float32, device=dev)
-    a_t = torch.empty(series_T, 64, dtype=torch.float32, device=dev)
-    c_t = torch.empty(series_T, KM, dtype=torch.float32, device=dev)
     hn = torch.empty(H, dtype=torch.float32, device=dev)
     cn = torch.empty(H, dtype=torch.float32, device=dev)
-    fused = fuse_macro and precision == "bf16x3" and M > 0 and ws.plan.dims.H == 4 and ws.plan.sms >= 2
-    mio = DlapMacroIO(_ptr(macro) if M > 0 else None, series_T, month0, stride, _ptr(h0), _ptr(c0), _ptr(save),
+    if tables is None:
+        a_t = torch.empty(series_T, 64, dtype=torch.float32, device=dev)
+        c_t = torch.empty(series_T, KM, dtype=torch.float32, device=dev)
+    else:
+        a_t = tables[0].detach().contiguous()
+        c_t = (tables[1].detach().contiguous() if tables[1] is not None
+               else torch.zeros(series_T, KM, dtype=torch.float32, device=dev))
+        if tuple(a_t.shape) != (series_T, 64) or tuple(c_t.shape) != (series_T, KM) or M != 0:
+            raise ValueError("per-month bias tables must be [T,64] and [T,8], on a workspace without macro input")
+    fused = (tables is None and fuse_macro and precision == "bf16x3" and M > 0 and ws.plan.dims.H == 4
+             and ws.plan.sms >= 2)
+    mio = DlapMacroIO(_ptr(macro) if (M > 0 and tables is None) else None, series_T, month0, stride,
+                      0 if tables is None else 1, _ptr(h0), _ptr(c0), _ptr(save),
                       _ptr(a_t), _ptr(c_t), _ptr(hn), _ptr(cn), _ptr(ws.sync) if fused else None)
     u = torch.empty(T, N, dtype=torch.float32, device=dev)
     q = torch.empty(KM, T, N, dtype=torch.float32, device=dev) if need_moments else None
@@ -356,7 +368,7 @@ def cell_forward(ws: Workspace, macro, x, mask, params, h0, c0, precision: str, 
     _timed_call("dlap_cell_fwd", dev, ws.pp, _ptr(x), _ptr(mask), _ptr(index), C.byref(tens), C.byref(mio), _ptr(u),
                 _ptr(q), _PRECISIONS[precision], float(dropout_p), int(dropout_seed), _ptr(dropout_seed_dev),
                 _stream(dev))
-    ws.launches += 1 if fused else 2
+    ws.launches += 1 if (fused or tables is not None) else 2
     return CellPass(u, q, save, a_t, c_t, hn, cn, index, mio, precision)
 
 
@@ -373,9 +385,12 @@ class Reduced:
 
 
 def step_reduce(ws: Workspace, cp: CellPass, R, mask, weighted_loss: bool, want_backward: bool,
-                shard: Optional["MonthShard"] = None) -> Reduced:
+                shard: Optional["MonthShard"] = None, demean: bool = True, q_dense=None) -> Reduced:
     """dlap_step_reduce: every sum over stocks and over months, one launch (two around the all-reduce of the
-    per-stock sums when the panel is a month shard)."""
+    per-stock sums when the panel is a month shard).  q_dense: moment outputs [8,T,N] that did not come from the
+    per-cell kernel (they replace cp.q)."""
+    flags = (0 if demean else _lib.DLAP_REDUCE_NO_DEMEAN) | (_lib.DLAP_REDUCE_Q_DENSE if q_dense is not None else 0)
+    q = cp.q if q_dense is None else q_dense
     dev = R.device
     T, N = R.shape
     row_stats = torch.empty(T, RS_W, dtype=torch.float32, device=dev)
@@ -388,8 +403,8 @@ def step_reduce(ws: Workspace, cp: CellPass, R, mask, weighted_loss: bool, want_
     dS2 = torch.empty(T, 2, dtype=torch.float64, device=dev) if want_backward else None
 
     def launch(lo, hi):
-        _timed_call("dlap_step_reduce", dev, ws.pp, _ptr(cp.u), _ptr(cp.q), _ptr(R), _ptr(mask), _ptr(cp.index),
-                    int(weighted_loss), _ptr(shard.n_bar) if shard is not None else None, lo, hi, _ptr(row_stats),
+        _timed_call("dlap_step_reduce", dev, ws.pp, _ptr(cp.u), _ptr(q), _ptr(R), _ptr(mask), _ptr(cp.index),
+                    int(weighted_loss), flags, _ptr(shard.n_bar) if shard is not None else None, lo, hi, _ptr(row_stats),
                     _ptr(pr), _ptr(scalars), _ptr(w), _ptr(ws.col_part), _ptr(e), _ptr(t_i), _ptr(G),
                     _ptr(ws.loss_part), _ptr(dS2), _ptr(ws.row_part), _ptr(ws.bar), _stream(dev))
         ws.launches += 1
@@ -404,25 +419,42 @@ def step_reduce(ws: Workspace, cp: CellPass, R, mask, weighted_loss: bool, want_
     return Reduced(row_stats, pr, scalars, w, G, dS2)
 
 
+RS_SR = 6     # row_stats: sum_i m R of the month
+
+
 class GanStepFn(torch.autograd.Function):
-    """(L_c, L_u, pr, weights, sharpe, h_n, c_n) = step(panel, params).  `cells`: a CellPass of the same panel and
-    parameters made earlier (the evaluation cache of AssetPricingGAN), or None."""
+    """(L_c, L_u, pr, weights, sharpe, h_n, c_n) = step(panel, params).
+
+    `cells`: a CellPass of the same panel and parameters made earlier (the evaluation cache of AssetPricingGAN), or
+    None.  Three optional tensor inputs widen the fast path to the reference's other configurations:
+      a_in [T,64], c_in [T,8] (or None)  the per-month biases come from the caller (a model without the LSTM,
+                 src/model.py:200-205: a_t = W1[:,F:].macro_t + b1 by a plain matmul); `macro` is then None and the
+                 parameter list holds the characteristics' columns of W1 / Wq only; their gradients are returned;
+      q_in [8,T,N] dense                 the moment outputs come from the caller (a moment network with hidden layers,
+                 src/model.py:119-127, evaluated with torch ops); its gradient is returned."""
 
     @staticmethod
-    def forward(ctx, opts: StepOptions, cells: Optional[CellPass], macro, x, R, mask, h0, c0, *params):
+    def forward(ctx, opts: StepOptions, cells: Optional[CellPass], macro, x, R, mask, h0, c0, a_in, c_in, q_in,
+                *params):
         dev = x.device
         T, N, F = x.shape
-        M = 0 if macro is None else macro.shape[1]
-        H = 0 if macro is None else params[1].shape[1]
+        tables = a_in is not None
+        M = 0 if (macro is None or tables) else macro.shape[1]
+        H = 0 if M == 0 else params[1].shape[1]
         sh = opts.shard
+        if (tables or q_in is not None) and sh is not None:
+            raise NotImplementedError("month shards with caller-made bias tables / moment outputs")
         want_backward = any(ctx.needs_input_grad)
+        kernel_moments = opts.need_moments and q_in is None
         with torch.cuda.device(dev):
             ws = workspace(T, N, F, M, H, dev)
             cp = cells
             if cp is None:
-                cp = cell_forward(ws, macro, x, mask, params, h0, c0, opts.precision, opts.need_moments,
-                                  opts.dropout_p, opts.dropout_seed, opts.dropout_seed_dev, sh)
-            red = step_reduce(ws, cp, R, mask, opts.weighted_loss, want_backward, sh)
+                cp = cell_forward(ws, None if tables else macro, x, mask, params, h0, c0, opts.precision, kernel_moments,
+                                  opts.dropout_p, opts.dropout_seed, opts.dropout_seed_dev, sh,
+                                  tables=(a_in, c_in) if tables else None)
+            q_dense = q_in.detach().contiguous() if (q_in is not None and opts.need_moments) else None
+            red = step_reduce(ws, cp, R, mask, opts.weighted_loss, want_backward, sh, opts.demean, q_dense)
         ctx.set_materialize_grads(False)      # unused outputs come back as None, not as zero tensors (fill kernels)
         ctx.save_for_backward(x, R, mask, macro, h0, c0, *params)
         # What the backward pass reads -- and nothing that is an OUTPUT of this function: an output held by ctx is a
@@ -430,7 +462,7 @@ class GanStepFn(torch.autograd.Function):
         # AccumulateGrad nodes and their stream, alive until the garbage collector runs.  u and q are dead here.
         ctx.opts, ctx.ws = opts, ws
         ctx.keep = (cp.save, cp.a_t, cp.c_t, cp.index, cp.mio, cp.q is not None, red.row_stats, red.scalars, red.G,
-                    red.dS2)
+                    red.dS2, tables, q_dense is not None)
         scalars = red.scalars
         l_c, l_u, sharpe = scalars[SC_LC], scalars[SC_LU], scalars[SC_SHARPE]
         ctx.mark_non_differentiable(red.w, sharpe, cp.hn, cp.cn)
@@ -440,16 +472,18 @@ class GanStepFn(torch.autograd.Function):
     def backward(ctx, g_lc, g_lu, g_pr, *_unused):
         x, R, mask, macro, h0, c0, *params = ctx.saved_tensors
         opts, ws = ctx.opts, ctx.ws
-        save, a_t, c_t, index, mio, has_q, row_stats, scalars, G, dS2 = ctx.keep
+        save, a_t, c_t, index, mio, has_q, row_stats, scalars, G, dS2, tables, q_given = ctx.keep
         sh = opts.shard
         dev = x.device
         T, N, F = x.shape
-        M = 0 if macro is None else macro.shape[1]
-        need = ctx.needs_input_grad[8:]
-        want_sdf = any(need[:10])
-        want_mom = any(need[10:]) and has_q
-        if not (want_sdf or want_mom):
-            return (None,) * (8 + len(params))
+        M = ws.plan.dims.M
+        NP = 11                                             # inputs in front of the parameters
+        need_a, need_c, need_q = ctx.needs_input_grad[8:11]
+        need = ctx.needs_input_grad[NP:]
+        want_sdf = any(need[:10]) or need_a
+        want_mom = (any(need[10:]) or need_c) and has_q
+        if not (want_sdf or want_mom or (need_q and q_given)):
+            return (None,) * (NP + len(params))
         prec = _PRECISIONS[_BWD_PRECISION[opts.precision]]
 
         def scalar(t):
@@ -458,65 +492,101 @@ class GanStepFn(torch.autograd.Function):
         g_lc, g_lu = scalar(g_lc), scalar(g_lu)
         if g_pr is not None:
             g_pr = g_pr.detach().to(torch.float32).contiguous()
+        grad_a = grad_c = grad_q = None
+        grads = [None] * len(params)
         with torch.cuda.device(dev):
             st = _stream(dev)
-            tens = _tensors(params)
-            _timed_call("dlap_cell_bwd", dev, ws.pp, _ptr(x), _ptr(R), _ptr(mask), _ptr(index), C.byref(tens),
-                        C.byref(mio), _ptr(row_stats), _ptr(dS2), _ptr(g_lc) if has_q else None,
-                        _ptr(g_lu), _ptr(g_pr), _ptr(G), _ptr(scalars), int(opts.weighted_loss), int(want_sdf),
-                        int(want_mom), _ptr(ws.wpart), _ptr(ws.dadc_part), prec, float(opts.dropout_p),
-                        int(opts.dropout_seed), _ptr(opts.dropout_seed_dev), st)
-            ws.launches += 1
-            # All twelve gradient tensors are views of one flat buffer.  Month-sharded: the buffer starts with the
-            # [T_total,72] da_t | dc_t rows (this rank fills its months) and is zero-filled, so that exchange 2 is ONE
-            # all-reduce over it -- gradients that are computed later (LSTM, b1, bq) are still zero.  Otherwise no
-            # fill: the kernels write every element of every gradient that is handed back.
-            sizes = [0 if p is None else p.numel() for p in params]
-            head = 0 if sh is None else sh.T_total * 72
-            buf = (torch.empty if sh is None else torch.zeros)(head + sum(sizes), dtype=torch.float32, device=dev)
-            flat_g = buf[head:]
-            grads, off = [], 0
-            for p, n in zip(params, sizes):
-                grads.append(None if p is None else flat_g[off:off + n].view_as(p))
-                off += n
-            gt = _tensors(grads)
-            if sh is None:
-                dadc = torch.empty(T, 72, dtype=torch.float32, device=dev)
-                _timed_call("dlap_macro_bwd", dev, ws.pp, _ptr(macro), C.byref(tens), _ptr(h0), _ptr(c0), _ptr(save),
-                            _ptr(dadc), _ptr(ws.dpre), int(want_sdf), int(want_mom), C.byref(gt), _ptr(ws.wpart),
-                            _ptr(ws.dadc_part), _ptr(index), prec, _ptr(ws.counter), st)
-                ws.launches += 2
-            else:   # exchange 2: per-cell weight grads + every month's da_t | dc_t row
-                dadc_all = buf[:head].view(sh.T_total, 72)
-                _timed_call("dlap_grad_finish", dev, ws.pp, _ptr(ws.wpart), _ptr(ws.dadc_part), _ptr(index), prec,
-                            int(want_sdf), int(want_mom), C.byref(gt), _ptr(dadc_all[sh.t0:]), int(sh.stride), st)
-                wsm = workspace(sh.T_total, N, F, M, ws.plan.dims.H, dev)
-                with _timed_region("exchange_bwd", dev):
-                    torch.distributed.all_reduce(buf, group=sh.group)
-                _timed_call("dlap_macro_bwd", dev, wsm.pp, _ptr(macro), C.byref(tens), _ptr(h0), _ptr(c0),
-                            _ptr(save), _ptr(dadc_all), _ptr(wsm.dpre), int(want_sdf), int(want_mom), C.byref(gt),
-                            None, None, None, prec, None, st)
-                ws.launches += 3 if (want_sdf and M > 0) else 2
+            if want_sdf or want_mom:
+                tens = _tensors(params)
+                _timed_call("dlap_cell_bwd", dev, ws.pp, _ptr(x), _ptr(R), _ptr(mask), _ptr(index), C.byref(tens),
+                            C.byref(mio), _ptr(row_stats), _ptr(dS2), _ptr(g_lc) if has_q else None,
+                            _ptr(g_lu), _ptr(g_pr), _ptr(G), _ptr(scalars), int(opts.weighted_loss), int(want_sdf),
+                            int(want_mom), _ptr(ws.wpart), _ptr(ws.dadc_part), prec, float(opts.dropout_p),
+                            int(opts.dropout_seed), _ptr(opts.dropout_seed_dev), st)
+                ws.launches += 1
+                # All gradient tensors are views of one flat buffer.  Month-sharded: the buffer starts with the
+                # [T_total,72] da_t | dc_t rows (this rank fills its months) and is zero-filled, so that exchange 2 is
+                # ONE all-reduce over it -- gradients that are computed later (LSTM, b1, bq) are still zero.
+                # Otherwise no fill: the kernels write every element of every gradient that is handed back.
+                sizes = [0 if p is None else p.numel() for p in params]
+                head = 0 if sh is None else sh.T_total * 72
+                buf = (torch.empty if sh is None else torch.zeros)(head + sum(sizes), dtype=torch.float32, device=dev)
+                flat_g = buf[head:]
+                grads, off = [], 0
+                for p, n in zip(params, sizes):
+                    grads.append(None if p is None else flat_g[off:off + n].view_as(p))
+                    off += n
+                gt = _tensors(grads)
+                if tables:           # the month-level backward is the caller's (autograd of how it made a_t / c_t)
+                    dadc = torch.empty(T, 72, dtype=torch.float32, device=dev)
+                    _timed_call("dlap_grad_finish", dev, ws.pp, _ptr(ws.wpart), _ptr(ws.dadc_part), _ptr(index), prec,
+                                int(want_sdf), int(want_mom), C.byref(gt), _ptr(dadc), 1, st)
+                    ws.launches += 1
+                    grad_a = dadc[:, :64] if (need_a and want_sdf) else None
+                    grad_c = dadc[:, 64:] if (need_c and want_mom) else None
+                elif sh is None:
+                    dadc = torch.empty(T, 72, dtype=torch.float32, device=dev)
+                    _timed_call("dlap_macro_bwd", dev, ws.pp, _ptr(macro), C.byref(tens), _ptr(h0), _ptr(c0), _ptr(save),
+                                _ptr(dadc), _ptr(ws.dpre), int(want_sdf), int(want_mom), C.byref(gt), _ptr(ws.wpart),
+                                _ptr(ws.dadc_part), _ptr(index), prec, _ptr(ws.counter), st)
+                    ws.launches += 2
+                else:   # exchange 2: per-cell weight grads + every month's da_t | dc_t row
+                    dadc_all = buf[:head].view(sh.T_total, 72)
+                    _timed_call("dlap_grad_finish", dev, ws.pp, _ptr(ws.wpart), _ptr(ws.dadc_part), _ptr(index), prec,
+                                int(want_sdf), int(want_mom), C.byref(gt), _ptr(dadc_all[sh.t0:]), int(sh.stride), st)
+                    if not opts.demean and want_sdf:
+                        grads[9].copy_(_bias3_grad(opts, row_stats, scalars, dS2, g_lc if has_q or q_given else None, g_lu, g_pr))
+                    wsm = workspace(sh.T_total, N, F, M, ws.plan.dims.H, dev)
+                    with _timed_region("exchange_bwd", dev):
+                        torch.distributed.all_reduce(buf, group=sh.group)
+                    _timed_call("dlap_macro_bwd", dev, wsm.pp, _ptr(macro), C.byref(tens), _ptr(h0), _ptr(c0),
+                                _ptr(save), _ptr(dadc_all), _ptr(wsm.dpre), int(want_sdf), int(want_mom), C.byref(gt),
+                                None, None, None, prec, None, st)
+                    ws.launches += 3 if (want_sdf and M > 0) else 2
+                if not opts.demean and want_sdf and sh is None and grads[9] is not None:
+                    grads[9].copy_(_bias3_grad(opts, row_stats, scalars, dS2, g_lc if has_q or q_given else None, g_lu, g_pr))
+            if need_q and q_given and g_lc is not None:
+                # dL/dq_kti = dL/dL_c * G_ki R_ti m_ti S_t  (autograd of src/model.py:425-431; G holds unit coefficients)
+                rms = (R * mask) * row_stats[:, RS_S].unsqueeze(1)
+                grad_q = (G[:, :KM].t().unsqueeze(1) * rms.unsqueeze(0)) * g_lc
         out = []
         for i, gr in enumerate(grads):
-            live = need[i] and ((i < 10 and want_sdf) or (i >= 10 and want_mom))
+            live = need[i] and gr is not None and ((i < 10 and want_sdf) or (i >= 10 and want_mom))
             out.append(gr if live else None)
-        return (None,) * 8 + tuple(out)
+        return (None,) * 8 + (grad_a, grad_c, grad_q) + tuple(out)
+
+
+def _bias3_grad(opts, row_stats, scalars, dS2, g_lc, g_lu, g_pr):
+    """d loss / d output_proj.bias when the weights are not demeaned (normalize_w = False): every u shifts by db3, so
+    it is sum_t dP_t sum_i m R -- a month-level sum, done with a handful of [T]-sized torch ops (with demeaning it is
+    identically zero and the kernels write that)."""
+    dS = torch.zeros(dS2.shape[0], dtype=torch.float64, device=dS2.device)
+    if g_lc is not None:
+        dS = dS + g_lc.double() * dS2[:, 0]
+    if g_lu is not None:
+        dS = dS + g_lu.double() * dS2[:, 1]
+    if g_pr is not None:
+        dS = dS + g_pr.double()
+    if opts.weighted_loss:
+        dS = dS * (scalars[SC_NBAR].double() / row_stats[:, RS_NT].double())
+    return (dS * row_stats[:, RS_SR].double()).sum().to(torch.float32).reshape(1)
 
 
 def sdf_weights(macro, x, mask, params, h0=None, c0=None, normalized=False, precision="fp32",
-                with_moments=False):
+                with_moments=False, tables=None, demean=True):
     """Inference path of SDFNetwork.forward / get_weights (src/model.py:221-281, :565-594):
-    weights [T,N] (demeaned, optionally |w|-normalised per month) and the per-cell pass they came from
-    (with_moments: the moment outputs are computed too, for a forward() of the same panel that may follow)."""
+    weights [T,N] (demeaned unless demean=False, optionally |w|-normalised per month) and the per-cell pass they
+    came from (with_moments: the moment outputs are computed too, for a forward() of the same panel that may follow)."""
     dev = x.device
     T, N, F = x.shape
-    M = 0 if macro is None else macro.shape[1]
-    H = 0 if macro is None else params[1].shape[1]
+    M = 0 if (macro is None or tables is not None) else macro.shape[1]
+    H = 0 if M == 0 else params[1].shape[1]
     with torch.cuda.device(dev):
         ws = workspace(T, N, F, M, H, dev)
-        cp = cell_forward(ws, macro, x, mask, params, h0, c0, precision, with_moments)
+        cp = cell_forward(ws, None if tables is not None else macro, x, mask, params, h0, c0, precision, with_moments,
+                          tables=tables)
         w = torch.empty(T, N, dtype=torch.float32, device=dev)
-        _lib.call("dlap_weights", ws.pp, _ptr(cp.u), _ptr(mask), _ptr(cp.index), int(normalized), _ptr(w), _stream(dev))
+        _lib.call("dlap_weights", ws.pp, _ptr(cp.u), _ptr(mask), _ptr(cp.index), int(normalized), int(demean), _ptr(w),
+                  _stream(dev))
         ws.launches += 1
     return w, cp

@@ -99,6 +99,20 @@ class MomentNetwork(nn.Module):
             h = self.fc_layers(h)
         return torch.tanh(self.output_proj(h)).view(T, N, -1).permute(2, 0, 1)
 
+    def moments_by_month_bias(self, macro: Optional[torch.Tensor], x: torch.Tensor) -> torch.Tensor:
+        """forward(cat([macro tiled over the stocks, x])) of src/model.py:514-521 for a network WITH hidden layers,
+        without the [T,N,M+F] concatenation: the first Linear is split into its characteristics' columns (a GEMM
+        over the cells) and its macro columns (a per-month bias).  Library GEMMs and elementwise torch ops: this
+        variant of the moment network is not fused into the per-cell kernels.  -> contiguous [K,T,N]."""
+        first, rest = self.fc_layers[0], self.fc_layers[1:]
+        M = 0 if macro is None else macro.shape[1]
+        if first.in_features != M + x.shape[2]:
+            raise ValueError("the moment network's input width does not match the panel")
+        h = x @ first.weight[:, M:].t()
+        h = h + (first.bias if macro is None else torch.addmm(first.bias, macro, first.weight[:, :M].t())[:, None, :])
+        h = rest(h)
+        return torch.tanh(self.output_proj(h)).permute(2, 0, 1).contiguous()
+
 
 class SDFNetwork(nn.Module):
     """src/model.py:164-281."""
@@ -128,25 +142,28 @@ class SDFNetwork(nn.Module):
         self._hidden_dims = list(hidden_dims)
 
     # -- fast-path plumbing -------------------------------------------------------------------
-    def _mlp_params(self, with_macro: bool):
-        if self._hidden_dims != [64, 64]:
-            _unsupported(f"hidden_dim={self._hidden_dims} (only [64, 64])")
-        if not self.normalize_weights:
-            _unsupported("normalize_w=False")
-        if with_macro and self.macro_lstm is None:
-            _unsupported("macro features without the LSTM (use_rnn=False)")
+    def _check(self):
+        if len(self._hidden_dims) != 2 or max(self._hidden_dims) > 64 or min(self._hidden_dims) < 1:
+            _unsupported(f"hidden_dim={self._hidden_dims} (two hidden layers of at most 64 units)")
         if self.individual_dim > 64:
             _unsupported("more than 64 characteristics")
-        fc0, fc3 = self.fc_layers[0], self.fc_layers[3]
-        exp_in = self.individual_dim + (self.macro_lstm.output_dim if with_macro else 0)
-        if fc0.in_features != exp_in:
-            raise ValueError("macro_features=None needs a model built with macro_feature_dim=0")
-        return [fc0.weight, fc0.bias, fc3.weight, fc3.bias, self.output_proj.weight, self.output_proj.bias]
 
-    def kernel_params(self, with_macro: bool):
-        mlp = self._mlp_params(with_macro)          # raises for configurations off the fast path
-        lstm = self.macro_lstm._params() if with_macro else [None] * 4
-        return lstm + mlp
+    def mlp_tensors(self):
+        """(W1 [64, in], b1 [64], W2 [64,64], b2 [64], W3 [1,64], b3 [1]): the MLP's parameters as the kernels want
+        them.  Hidden layers narrower than 64 units (the notebooks' [64, 32]) are padded with zero units by
+        differentiable torch ops: a unit with zero weights and zero bias outputs relu(0) = 0, passes nothing on
+        (zero outgoing weights) and receives zero gradient, so the padded network IS the narrow one, and autograd
+        cuts the kernels' gradients back to the parameters' shapes."""
+        self._check()
+        d1, d2 = self._hidden_dims
+        fc0, fc3, out = self.fc_layers[0], self.fc_layers[3], self.output_proj
+        pad = torch.nn.functional.pad
+        w1 = fc0.weight if d1 == 64 else pad(fc0.weight, (0, 0, 0, 64 - d1))
+        b1 = fc0.bias if d1 == 64 else pad(fc0.bias, (0, 64 - d1))
+        w2 = fc3.weight if (d1, d2) == (64, 64) else pad(fc3.weight, (0, 64 - d1, 0, 64 - d2))
+        b2 = fc3.bias if d2 == 64 else pad(fc3.bias, (0, 64 - d2))
+        w3 = out.weight if d2 == 64 else pad(out.weight, (0, 64 - d2))
+        return w1, b1, w2, b2, w3, out.bias
 
     def forward(self, macro_features, individual_features, mask, hidden=None):
         """-> (weights [T,N], new_hidden).  Stand-alone use is the inference path (no autograd
@@ -154,25 +171,70 @@ class SDFNetwork(nn.Module):
         return _weights(self, None, macro_features, individual_features, mask, hidden, False)[:2]
 
 
-def _weights(sdf: SDFNetwork, moment_params, macro, x, mask, hidden, normalized, precision="fp32"):
-    """-> (weights, new_hidden, CellPass).  moment_params: [Wq, bq] to have the moment outputs computed in the same
+class KernelInputs:
+    """How one configuration of the reference's model reaches the kernels (GanStepFn's arguments)."""
+    __slots__ = ("macro", "a_in", "c_in", "q_in", "params", "H")
+
+
+def _kernel_inputs(sdf: SDFNetwork, moment: Optional[MomentNetwork], macro, x, want_q: bool) -> KernelInputs:
+    """moment None: the moment network takes no part (weights-only inference); the kernel ABI still gets neutral
+    tensors where it wants some.  want_q: the moment outputs are needed (phase != 'unconditional')."""
+    k = KernelInputs()
+    dev = x.device
+    F = x.shape[2]
+    w1, b1, w2, b2, w3, b3 = sdf.mlp_tensors()
+    M = macro.shape[1] if macro is not None else 0
+    lstm_mode = macro is not None and sdf.macro_lstm is not None
+    tables_mode = macro is not None and sdf.macro_lstm is None          # use_rnn=False, src/model.py:200-205
+    exp_in = F + (sdf.macro_lstm.output_dim if lstm_mode else M)
+    if sdf.fc_layers[0].in_features != exp_in:
+        raise ValueError(f"the SDF network expects {sdf.fc_layers[0].in_features} inputs per stock-month, the panel "
+                         f"provides {exp_in} (macro_features=None needs a model built with macro_feature_dim=0)")
+    k.macro, k.a_in, k.c_in, k.q_in = (macro if lstm_mode else None), None, None, None
+    k.H = sdf.macro_lstm.output_dim if lstm_mode else 0
+    lstm = sdf.macro_lstm._params() if lstm_mode else [None] * 4
+    if tables_mode:
+        # x first, then the macro series (src/model.py:253-255): a_t = W1[:, F:] macro_t + b1 by one small matmul
+        k.a_in = torch.addmm(b1, macro, w1[:, F:].t())
+        w1 = w1[:, :F].contiguous()
+        b1 = None
+    mom_hidden = moment is not None and not isinstance(moment.fc_layers, nn.Identity)
+    wq = bq = None
+    if moment is not None and moment.num_moments != 8:
+        _unsupported("num_condition_moment != 8")
+    if moment is not None and not mom_hidden:
+        mp = moment.output_proj
+        if mp.in_features != M + F:
+            raise ValueError("the moment network's input width does not match the panel")
+        if tables_mode:          # macro first, then x (src/model.py:514-516)
+            k.c_in = torch.addmm(mp.bias, macro, mp.weight[:, :M].t())
+            wq = mp.weight[:, M:].contiguous()
+        else:
+            wq, bq = mp.weight, mp.bias
+    elif mom_hidden and want_q:
+        k.q_in = moment.moments_by_month_bias(macro, x)
+    if wq is None and not tables_mode:
+        # the macro kernel fills c_t whatever happens: neutral moment parameters
+        wq = torch.zeros(8, M + F, dtype=torch.float32, device=dev)
+        bq = torch.zeros(8, dtype=torch.float32, device=dev)
+    k.params = lstm + [w1, b1, w2, b2, w3, b3, wq, bq]
+    return k
+
+
+def _weights(sdf: SDFNetwork, moment, macro, x, mask, hidden, normalized, precision="fp32"):
+    """-> (weights, new_hidden, CellPass).  moment: the moment network, to have its outputs computed in the same
     per-cell pass (for a forward() on the same panel that may follow), or None."""
     Fn.check_panel(macro, x, None, mask)
-    with_macro = macro is not None
-    params = [p.detach() if p is not None else None for p in sdf.kernel_params(with_macro)]
+    with torch.no_grad():
+        k = _kernel_inputs(sdf, moment, macro, x, want_q=False)
+    params = [p.detach() if p is not None else None for p in k.params]
     dev = x.device
-    T, N, F = x.shape
-    M = macro.shape[1] if with_macro else 0
-    if moment_params is None:
-        # the moment net takes no part in the weights; the kernel ABI still wants its two tensors
-        mp = [torch.zeros(8, M + F, dtype=torch.float32, device=dev), torch.zeros(8, dtype=torch.float32, device=dev)]
-    else:
-        mp = [p.detach() for p in moment_params]
-    H = sdf.macro_lstm.output_dim if with_macro else 0
-    h0, c0 = _hidden_pair(hidden, H, dev) if with_macro else (None, None)
-    w, cp = Fn.sdf_weights(macro, x, mask, params + mp, h0, c0, normalized, precision,
-                           with_moments=moment_params is not None)
-    new_hidden = (cp.hn.view(1, 1, H), cp.cn.view(1, 1, H)) if with_macro else None
+    h0, c0 = _hidden_pair(hidden, k.H, dev) if k.H else (None, None)
+    with_moments = moment is not None and isinstance(moment.fc_layers, nn.Identity)
+    tables = None if k.a_in is None else (k.a_in, k.c_in)
+    w, cp = Fn.sdf_weights(macro, x, mask, params, h0, c0, normalized, precision, with_moments=with_moments,
+                           tables=tables, demean=sdf.normalize_weights)
+    new_hidden = (cp.hn.view(1, 1, k.H), cp.cn.view(1, 1, k.H)) if k.H else None
     return w, new_hidden, cp
 
 
@@ -248,24 +310,22 @@ class AssetPricingGAN(nn.Module):
             return self.precision
         return 'bf16x3' if F <= Fn.TC_MAX_F else 'fp32'
 
-    def _kernel_params(self, with_macro: bool):
-        if self._hidden_dim_moment:
-            _unsupported("hidden layers in the moment network (hidden_dim_moment != [])")
-        if self.moment_net.num_moments != 8:
-            _unsupported("num_condition_moment != 8")
+    def _inputs(self, macro, x, want_q: bool) -> "KernelInputs":
         if self.residual_loss_factor > 0:
             _unsupported("residual_loss_factor > 0")
-        mp = self.moment_net.output_proj
-        return self.sdf_net.kernel_params(with_macro) + [mp.weight, mp.bias]
+        return _kernel_inputs(self.sdf_net, self.moment_net, macro, x, want_q)
 
     def forward(self, macro_features, individual_features, returns, mask, hidden=None,
                 phase: str = 'conditional'):
+        """src/model.py:485-563.  Differentiable outputs: ``loss``, the two loss terms and ``portfolio_returns``;
+        ``weights``, ``sharpe`` and ``hidden`` carry no autograd history (nothing in the reference's loops
+        differentiates through them; a loss term built on them would get no gradient)."""
         Fn.check_panel(macro_features, individual_features, returns, mask)
-        with_macro = macro_features is not None
-        params = self._kernel_params(with_macro)
         x = individual_features
         dev = x.device
-        H = self.sdf_net.macro_lstm.output_dim if with_macro else 0
+        k = self._inputs(macro_features, x, want_q=(phase != 'unconditional'))
+        H = k.H
+        with_macro = H > 0
         h0, c0 = _hidden_pair(hidden, H, dev) if with_macro else (None, None)
         p_drop = self.sdf_net.dropout_p if self.training else 0.0
         seed_dev = getattr(self, "_seed_dev", None) if p_drop > 0 else None   # GraphedStep: seed in device memory
@@ -273,10 +333,10 @@ class AssetPricingGAN(nn.Module):
         opts = Fn.StepOptions(weighted_loss=bool(self.weighted_loss),
                               need_moments=(phase != 'unconditional'), precision=self._precision(x.shape[2]),
                               dropout_p=p_drop, dropout_seed=seed, dropout_seed_dev=seed_dev,
-                              shard=self.month_shard)
-        cells = self._cached_cells(macro_features, x, mask, hidden, params, opts)
+                              shard=self.month_shard, demean=bool(self.sdf_net.normalize_weights))
+        cells = self._cached_cells(macro_features, x, mask, hidden, opts)
         l_c, l_u, pr, w, sharpe, hn, cn = Fn.GanStepFn.apply(
-            opts, cells, macro_features, x, returns, mask, h0, c0, *params)
+            opts, cells, k.macro, x, returns, mask, h0, c0, k.a_in, k.c_in, k.q_in, *k.params)
         zero = self._zero(dev)
         if phase == 'unconditional':            # src/model.py:524-528
             loss_unc, loss_cond, total = l_u, zero, l_u
@@ -289,11 +349,13 @@ class AssetPricingGAN(nn.Module):
         new_hidden = (hn.view(1, 1, H), cn.view(1, 1, H)) if with_macro else None
 
         def moments():
+            if k.q_in is not None:
+                return k.q_in
             mp = self.moment_net.output_proj
-            M = macro_features.shape[1] if with_macro else 0
+            M = macro_features.shape[1] if macro_features is not None else 0
             pre = x @ mp.weight[:, M:].t()
-            bias = mp.bias if not with_macro else macro_features @ mp.weight[:, :M].t() + mp.bias
-            pre = pre + (bias[:, None, :] if with_macro else bias)
+            bias = mp.bias if M == 0 else macro_features @ mp.weight[:, :M].t() + mp.bias
+            pre = pre + (bias[:, None, :] if M else bias)
             return torch.tanh(pre).permute(2, 0, 1)
 
         return StepOutputs({
@@ -315,22 +377,21 @@ class AssetPricingGAN(nn.Module):
     # runs only the reductions.  Anything else -- another panel, an optimiser step, train mode, grad mode -- misses.
     eval_cache = True
 
-    @staticmethod
-    def _cache_key(macro, x, mask, hidden, params, precision):
+    def _cache_key(self, macro, x, mask, hidden, precision):
         """(scalars, tensors): version counters and data pointers of panel and parameters, and the tensor objects
         themselves -- the cache keeps weak references to those and matches by identity, so a recycled id() or
         address of a dead tensor can never hit."""
-        tensors = [t for t in (macro, x, mask) + (tuple(hidden) if hidden is not None else ()) + tuple(params)
-                   if t is not None]
+        tensors = [t for t in (macro, x, mask) + (tuple(hidden) if hidden is not None else ())
+                   + tuple(self.parameters()) if t is not None]
         return (tuple((t._version, t.data_ptr()) for t in tensors), macro is None, hidden is None, precision), tensors
 
-    def _cached_cells(self, macro, x, mask, hidden, params, opts):
+    def _cached_cells(self, macro, x, mask, hidden, opts):
         hit = getattr(self, "_cells", None)
         self._cells = None                        # one use: the cache never outlives the evaluate() it was made for
         if hit is None or torch.is_grad_enabled() or self.training or opts.shard is not None:
             return None
         scalars, refs, cp = hit
-        now, tensors = self._cache_key(macro, x, mask, hidden, params, opts.precision)
+        now, tensors = self._cache_key(macro, x, mask, hidden, opts.precision)
         if now != scalars or len(refs) != len(tensors) or any(r() is not t for r, t in zip(refs, tensors)):
             return None
         if opts.need_moments and cp.q is None:
@@ -340,20 +401,14 @@ class AssetPricingGAN(nn.Module):
     def get_weights(self, macro_features, individual_features, mask, hidden=None, normalized: bool = False):
         """src/model.py:565-594."""
         precision = self._precision(individual_features.shape[2])
-        keep = (self.eval_cache and not torch.is_grad_enabled() and not self.training and self.month_shard is None)
-        mom = None
-        if keep:
-            try:
-                params = self._kernel_params(macro_features is not None)
-                mom = params[-2:]
-            except NotImplementedError:
-                keep = False
-        w, new_hidden, cp = _weights(self.sdf_net, mom, macro_features, individual_features, mask, hidden,
-                                     normalized, precision)
+        keep = (self.eval_cache and not torch.is_grad_enabled() and not self.training and self.month_shard is None
+                and not self._hidden_dim_moment and self.residual_loss_factor == 0)
+        w, new_hidden, cp = _weights(self.sdf_net, self.moment_net if keep else None, macro_features,
+                                     individual_features, mask, hidden, normalized, precision)
         self._cells = None
         if keep:
             import weakref
-            scalars, tensors = self._cache_key(macro_features, individual_features, mask, hidden, params, precision)
+            scalars, tensors = self._cache_key(macro_features, individual_features, mask, hidden, precision)
             self._cells = (scalars, [weakref.ref(t) for t in tensors], cp)
         return w, new_hidden
 

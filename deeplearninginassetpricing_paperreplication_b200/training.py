@@ -43,9 +43,10 @@ class FusedClipAdam:
         self.defaults = {"lr": lr, "betas": tuple(betas), "eps": eps, "max_norm": float(max_norm)}
         self.param_groups = [dict(self.defaults, params=self.params)]
         self.state: Dict[torch.nn.Parameter, Dict[str, torch.Tensor]] = {}
-        self._step = None          # int64 [1] on the device: updates so far
+        self._step = None          # int64 [len(params)] on the device: updates so far, per tensor (as torch counts)
         self.grad_norm = None      # float32 [1] on the device
         self.launches = 0
+        self._slot = {p: i for i, p in enumerate(self.params)}
 
     # -- state ------------------------------------------------------------------------------------------
     def ensure_state(self) -> None:
@@ -59,7 +60,7 @@ class FusedClipAdam:
                                  "exp_avg_sq": torch.zeros_like(p, memory_format=torch.contiguous_format)}
         dev = self.params[0].device
         if self._step is None:
-            self._step = torch.zeros(1, dtype=torch.int64, device=dev)
+            self._step = torch.zeros(len(self.params), dtype=torch.int64, device=dev)
             self.grad_norm = torch.zeros(1, dtype=torch.float32, device=dev)
 
     def zero_grad(self, set_to_none: bool = True) -> None:
@@ -85,20 +86,21 @@ class FusedClipAdam:
             st = self.state[p]
             t.param[k], t.grad[k] = p.data_ptr(), p.grad.data_ptr()
             t.exp_avg[k], t.exp_avg_sq[k] = st["exp_avg"].data_ptr(), st["exp_avg_sq"].data_ptr()
+            t.step[k] = self._step.data_ptr() + 8 * self._slot[p]
             t.numel[k] = p.numel()
         dev = live[0].device
         with torch.cuda.device(dev):
             _lib.call("dlap_clip_adam", C.byref(t), float(g["max_norm"] if max_norm is None else max_norm),
                       float(g["lr"]), float(g["betas"][0]), float(g["betas"][1]), float(g["eps"]),
-                      self._step.data_ptr(), self.grad_norm.data_ptr(), torch.cuda.current_stream(dev).cuda_stream)
+                      self.grad_norm.data_ptr(), torch.cuda.current_stream(dev).cuda_stream)
         bump_versions(live)
         self.launches += 1
 
     # -- torch.optim.Adam-shaped checkpoints -------------------------------------------------------------------
     def state_dict(self) -> dict:
         self.ensure_state()
-        step = self._step.clone()
-        return {"state": {i: {"step": step.to(torch.float32).reshape(()).cpu(), "exp_avg": self.state[p]["exp_avg"].clone(),
+        step = self._step.to(torch.float32).cpu()
+        return {"state": {i: {"step": step[i].clone(), "exp_avg": self.state[p]["exp_avg"].clone(),
                               "exp_avg_sq": self.state[p]["exp_avg_sq"].clone()} for i, p in enumerate(self.params)},
                 "param_groups": [{k: v for k, v in self.param_groups[0].items() if k != "params"}
                                  | {"params": list(range(len(self.params)))}]}
@@ -111,7 +113,7 @@ class FusedClipAdam:
                 continue
             self.state[p]["exp_avg"].copy_(s["exp_avg"])
             self.state[p]["exp_avg_sq"].copy_(s["exp_avg_sq"])
-            self._step.fill_(int(float(s["step"])))
+            self._step[i] = int(float(s["step"]))
         for k in ("lr", "betas", "eps", "max_norm"):
             if k in sd["param_groups"][0]:
                 self.param_groups[0][k] = sd["param_groups"][0][k]

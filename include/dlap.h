@@ -96,7 +96,10 @@ typedef struct dlap_tensors {
  * the plan's T).
  *   dlap_cell_fwd: macro != NULL: the call also runs MacroLSTM.forward (src/model.py:50-73) over the whole series
  *     and fills lstm_save [series_T,6H] (h,c,i,f,g,o), a_t [series_T,64], c_t [series_T,8], hn, cn [H] (h0 / c0 [H]
- *     may be NULL: zero state).  macro == NULL: a_t and c_t are inputs (with M = 0 the call fills them with b1 / bq).
+ *     may be NULL: zero state).  macro == NULL: with tables_ready != 0, a_t and c_t are INPUTS, complete when the
+ *     call starts (a caller that builds the per-month biases itself, e.g. a model without the LSTM:
+ *     a_t = W1[:,F:].macro_t + b1, src/model.py:200-205; the plan then has M = 0, and w1 / wq hold the
+ *     characteristics' columns only); otherwise M must be 0 and the call fills them with b1 / bq.
  *   dlap_cell_bwd: reads a_t, c_t, month0, month_stride only.
  * sync (device, two int32, zero when the call starts and zero again when it has finished; may be NULL): BF16X3 with
  * macro and H = 4 only.  When given, the LSTM runs on one CTA of the per-cell kernel's own grid, beside the per-cell
@@ -105,7 +108,7 @@ typedef struct dlap_tensors {
  * in front of the per-cell kernel. */
 typedef struct dlap_macro_io {
   const float* macro;
-  int32_t series_T, month0, month_stride;
+  int32_t series_T, month0, month_stride, tables_ready;
   const float *h0, *c0;
   float *lstm_save, *a_t, *c_t, *hn, *cn;
   int32_t* sync;
@@ -180,12 +183,17 @@ int dlap_cell_fwd(const dlap_plan* plan, const float* x, const uint8_t* mask, co
  *                              -> G [N,12], one row per stock: G_0i .. G_7i, G_8i, three floats of padding
  *   4  L_c = mean_k mean_i e_ki^2, L_u = mean_i e0_i^2 (src/model.py:385, :429-431) -> scalars[0], scalars[1];
  *      dS2 [T,2] (double): dS_t for unit cotangents of L_c and of L_u; dS2 NULL: no backward pass will follow
+ * flags: DLAP_REDUCE_NO_DEMEAN: normalize_w = False (src/model.py:274): w = m u, mu_t and Rbar_t are reported as 0;
+ * DLAP_REDUCE_Q_DENSE: q is a dense [8,T,N] tensor even though u is left-packed (moment outputs that did not come
+ * from dlap_cell_fwd: a moment network with hidden layers, evaluated by the caller).
  * Single device: phases 0..4 in one launch.  q may be NULL (phase 'unconditional').  index: the valid-cell index
  * when u and q come from the BF16X3 dlap_cell_fwd, NULL for FP32.  row_part: scratch (row_part_bytes; NULL: the
  * per-month phases run one CTA per month).  bar (device, bar_bytes, all zero when the call starts and all zero
  * again when it has finished): the barrier word and one counter per month. */
+#define DLAP_REDUCE_NO_DEMEAN 1
+#define DLAP_REDUCE_Q_DENSE 2
 int dlap_step_reduce(const dlap_plan* plan, const float* u, const float* q, const float* R, const uint8_t* mask,
-                     const int32_t* index, int weighted_loss, const float* n_bar_in, int phase_lo, int phase_hi,
+                     const int32_t* index, int weighted_loss, int flags, const float* n_bar_in, int phase_lo, int phase_hi,
                      float* row_stats, float* pr, float* scalars, float* w_out, double* col_part, float* e,
                      float* t_i, float* G, double* loss_part, double* dS2, double* row_part, uint32_t* bar,
                      void* stream);
@@ -252,19 +260,20 @@ int dlap_macro_bwd(const dlap_plan* plan, const float* macro, const dlap_tensors
                    int want_mom, const dlap_tensors* grads, const float* wpart, const float* dadc_part,
                    const int32_t* index, int precision, uint32_t* counter, void* stream);
 
-/* get_weights (src/model.py:565-594): w = m (u - mu_t), mu_t the month's mean of u over unmasked stocks;
- * normalized != 0 divides each month by clamp(sum_i |w| m, 1e-8) (the Python loop of :586-590).
- * index: the layout of u (as for dlap_step_reduce). */
+/* get_weights (src/model.py:565-594): w = m (u - mu_t), mu_t the month's mean of u over unmasked stocks (demean = 0:
+ * w = m u, normalize_w = False, src/model.py:274); normalized != 0 divides each month by clamp(sum_i |w| m, 1e-8)
+ * (the Python loop of :586-590).  index: the layout of u (as for dlap_step_reduce). */
 int dlap_weights(const dlap_plan* plan, const float* u, const uint8_t* mask, const int32_t* index, int normalized,
-                 float* w_out, void* stream);
+                 int demean, float* w_out, void* stream);
 
 /* clip_grad_norm_ + optimizer.step() of the training loop (src/train.py:87-94: torch.nn.utils.clip_grad_norm_ over
  * the scope's parameters, then torch.optim.Adam with its defaults: no weight decay, no amsgrad) over up to
  * DLAP_ADAM_MAX_TENSORS tensors in ONE launch: the 2-norm of all gradients -> *grad_norm (device, may be NULL); with
  * max_norm > 0 every gradient is scaled IN PLACE by min(max_norm / (norm + 1e-6), 1); then exp_avg, exp_avg_sq and
- * the parameters are updated with Adam's arithmetic, op for op.  *step (device, one int64: the number of updates so
- * far) is incremented, so the call can be replayed from a CUDA graph.  The training step's twelve tensors are
- * 12,233 numbers: one CTA. */
+ * the parameters are updated with Adam's arithmetic, op for op.  step[k] (device, one int64 per tensor: the number of
+ * updates that tensor has had -- torch counts per parameter, and one without a gradient in some step lags behind)
+ * is incremented, so the call can be replayed from a CUDA graph.  The training step's twelve tensors are 12,233
+ * numbers: one CTA. */
 #define DLAP_ADAM_MAX_TENSORS 16
 typedef struct dlap_adam_tensors {
   int32_t count;
@@ -272,10 +281,11 @@ typedef struct dlap_adam_tensors {
   float* grad[DLAP_ADAM_MAX_TENSORS];
   float* exp_avg[DLAP_ADAM_MAX_TENSORS];
   float* exp_avg_sq[DLAP_ADAM_MAX_TENSORS];
+  int64_t* step[DLAP_ADAM_MAX_TENSORS];
   int64_t numel[DLAP_ADAM_MAX_TENSORS];
 } dlap_adam_tensors;
 int dlap_clip_adam(const dlap_adam_tensors* tensors, float max_norm, float lr, float beta1, float beta2, float eps,
-                   int64_t* step, float* grad_norm, void* stream);
+                   float* grad_norm, void* stream);
 
 /* Diagnostics (no counterpart in the reference): when `stamps` is a device buffer of 3*256*16 int64, every
  * following tensor-core dlap_cell_bwd (first third of the buffer: epilogue and MMA warps per tile; last third:

@@ -23,6 +23,9 @@ Cases
   mask_raw      raw returns/features with -99.99 sentinels and NaNs -> mask, zero-filled
                 arrays (``src/data_loader.py:50-65``).  Bit-exact contract.
   anchors       scalars of the full shipped training panel.
+  v_*           config variants: the notebooks' [64,32] / use_rnn=False / hidden_dim_moment=[32],
+                normalize_w=False, narrow hidden layers with weighted_loss=False -- `python make_golden.py variants`
+                writes only these.
 """
 import json
 import os
@@ -40,13 +43,16 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 PHASES = ("unconditional", "moment", "conditional")
 
 
-def run_case(name, macro, x, R, mask, seed, hidden=None):
+def run_case(name, macro, x, R, mask, seed, hidden=None, cfg_extra=None):
     cfg = {"macro_feature_dim": int(macro.shape[1]), "individual_feature_dim": int(x.shape[2])}
+    cfg.update(cfg_extra or {})
     torch.manual_seed(seed)
     model = AssetPricingGAN(cfg)
     model.eval()
     blob = {"macro": macro.numpy(), "x": x.numpy(), "R": R.numpy(), "mask": mask.numpy(),
             "seed": np.int64(seed)}
+    if cfg_extra:
+        blob["cfg_json"] = np.array(json.dumps(cfg_extra))
     if hidden is not None:
         blob["h0"] = hidden[0].numpy(); blob["c0"] = hidden[1].numpy()
     for k, v in model.state_dict().items():
@@ -61,8 +67,9 @@ def run_case(name, macro, x, R, mask, seed, hidden=None):
         for key in ("weights", "loss", "loss_unconditional", "loss_conditional", "sharpe",
                     "portfolio_returns"):
             blob[f"{phase}/{key}"] = out[key].detach().numpy().copy()
-        blob[f"{phase}/hidden_h"] = out["hidden"][0].detach().numpy().copy()
-        blob[f"{phase}/hidden_c"] = out["hidden"][1].detach().numpy().copy()
+        if out["hidden"] is not None:
+            blob[f"{phase}/hidden_h"] = out["hidden"][0].detach().numpy().copy()
+            blob[f"{phase}/hidden_c"] = out["hidden"][1].detach().numpy().copy()
         if phase == "conditional":
             blob["moments"] = out["moments"].detach().contiguous().numpy().copy()
         for k, prm in model.named_parameters():
@@ -90,6 +97,30 @@ def rand_small():
     R = 0.1 * torch.randn(T, N, generator=g) * mask
     macro = torch.randn(T, M, generator=g)
     run_case("rand_small", macro, x, R, mask, seed=42)
+
+
+VARIANTS = {
+    "v_notebook": {"hidden_dim": [64, 32], "hidden_dim_moment": [32], "use_rnn": False},   # notebooks/demo*.ipynb
+    "v_6432": {"hidden_dim": [64, 32]},
+    "v_norm_off": {"normalize_w": False},
+    "v_no_rnn": {"use_rnn": False},
+    "v_mom_hidden": {"hidden_dim_moment": [32]},
+    "v_narrow": {"hidden_dim": [32, 16], "weighted_loss": False},
+}
+
+
+def variants():
+    """The configurations of SURVEY.md §8f row 3 (the notebooks' among them) on one small panel."""
+    g = torch.Generator().manual_seed(77)
+    T, N, F, M = 10, 150, 46, 8
+    mask = torch.rand(T, N, generator=g) < 0.45
+    mask[6, :] = False
+    mask[:, 11] = False
+    x = torch.randn(T, N, F, generator=g).clamp_(-2, 2) * mask[:, :, None]
+    R = 0.1 * torch.randn(T, N, generator=g) * mask
+    macro = torch.randn(T, M, generator=g)
+    for i, (name, extra) in enumerate(VARIANTS.items()):
+        run_case(name, macro, x, R, mask, seed=100 + i, cfg_extra=extra)
 
 
 def shipped():
@@ -142,5 +173,9 @@ def shipped():
 
 if __name__ == "__main__":
     torch.set_num_threads(1)        # bit-reproducible regardless of the host
-    rand_small()
-    shipped()
+    if sys.argv[1:] == ["variants"]:
+        variants()
+    else:
+        rand_small()
+        shipped()
+        variants()

@@ -1,0 +1,99 @@
+"""the reference's other configurations on the drop-in, against goldens written by the reference
+itself (tests/golden/make_golden.py `variants`): the notebooks' hidden_dim=[64,32] + use_rnn=False +
+hidden_dim_moment=[32] (notebooks/demo.ipynb, demo_synthetic.ipynb), each of those alone, normalize_w=False, and
+narrow hidden layers with weighted_loss=False.  All three phases, both arithmetic paths, losses / weights /
+portfolio returns / normalised weights / every gradient."""
+import json
+
+import numpy as np
+import pytest
+import torch
+
+from _dlap_testlib import PHASES, golden_params, load_golden, rel_err
+from deeplearninginassetpricing_paperreplication_b200 import AssetPricingGAN
+from test_parity_gpu import LOSS_RTOL, WEIGHT_TOL, _np, dev
+
+pytestmark = pytest.mark.gpu
+VARIANTS = ["v_notebook", "v_6432", "v_norm_off", "v_no_rnn", "v_mom_hidden", "v_narrow"]
+
+
+def _model(g, precision):
+    cfg = json.loads(str(g["cfg_json"]))
+    model = AssetPricingGAN({"macro_feature_dim": int(g["macro"].shape[1]), "individual_feature_dim": 46,
+                             "b200_precision": precision, **cfg})
+    model.load_state_dict({k: torch.as_tensor(v) for k, v in golden_params(g).items()})     # same keys, same shapes
+    return model.to(dev()).eval(), cfg
+
+
+@pytest.mark.parametrize("precision", ["fp32", "bf16x3"])
+@pytest.mark.parametrize("phase", PHASES)
+@pytest.mark.parametrize("name", VARIANTS)
+def test_variant_step_matches_the_reference(name, phase, precision):
+    g = load_golden(name)
+    model, cfg = _model(g, precision)
+    d = dev()
+    macro, x, R, mask = [torch.from_numpy(g[k]).to(d) for k in ("macro", "x", "R", "mask")]
+    for p in model.sdf_net.parameters():
+        p.requires_grad = phase != "moment"
+    out = model(macro, x, R, mask, phase=phase)
+    out["loss"].backward()
+    torch.cuda.synchronize()
+    for key in ("loss", "loss_unconditional", "loss_conditional"):
+        a, b = float(out[key]), float(g[f"{phase}/{key}"])
+        assert abs(a - b) <= LOSS_RTOL * abs(b) + 1e-30, (key, a, b)
+    w = _np(out["weights"])
+    assert np.all(w[~g["mask"]] == 0.0)
+    assert rel_err(w, g[f"{phase}/weights"]) < WEIGHT_TOL
+    assert rel_err(_np(out["portfolio_returns"]), g[f"{phase}/portfolio_returns"]) < WEIGHT_TOL
+    assert abs(float(out["sharpe"]) - float(g[f"{phase}/sharpe"])) <= 1e-4 * abs(float(g[f"{phase}/sharpe"])) + 1e-7
+    if f"{phase}/hidden_h" in g:
+        assert np.abs(_np(out["hidden"][0]) - g[f"{phase}/hidden_h"]).max() < 2e-6
+    else:
+        assert out["hidden"] is None
+    tol_max, tol_norm = (2e-4, 2e-4) if precision == "fp32" else (4e-2, 1e-2)
+    seen = 0
+    for k, p in model.named_parameters():
+        gk = f"{phase}/grad/{k}"
+        if gk not in g:
+            assert p.grad is None or float(p.grad.abs().max()) == 0.0, k
+            continue
+        assert p.grad is not None, k
+        ref = g[gk]
+        assert tuple(p.grad.shape) == ref.shape, k
+        if k == "sdf_net.output_proj.bias" and cfg.get("normalize_w", True):
+            assert float(p.grad.abs().max()) < 1e-9          # identically zero with demeaning
+            continue
+        got = _np(p.grad)
+        emax = np.abs(got - ref).max() / max(np.abs(ref).max(), 1e-30)
+        enorm = np.linalg.norm(got - ref) / max(np.linalg.norm(ref), 1e-30)
+        assert emax < tol_max and enorm < tol_norm, (k, emax, enorm)
+        seen += 1
+    assert seen >= 2
+
+
+@pytest.mark.parametrize("precision", ["fp32", "bf16x3"])
+@pytest.mark.parametrize("name", VARIANTS)
+def test_variant_inference_matches_the_reference(name, precision):
+    g = load_golden(name)
+    model, _ = _model(g, precision)
+    d = dev()
+    macro, x, R, mask = [torch.from_numpy(g[k]).to(d) for k in ("macro", "x", "R", "mask")]
+    with torch.no_grad():
+        wn, _ = model.get_weights(macro, x, mask, normalized=True)
+        out = model(macro, x, R, mask, phase="conditional")              # evaluate(): the same panel right after
+        f = model.get_sdf_factor(macro, x, R, mask)
+    assert rel_err(_np(wn), g["normalized_weights"]) < WEIGHT_TOL
+    assert rel_err(_np(f), g["sdf_factor"]) < WEIGHT_TOL
+    assert abs(float(out["loss"]) - float(g["conditional/loss"])) <= LOSS_RTOL * abs(float(g["conditional/loss"]))
+    assert rel_err(_np(out["moments"]), g["moments"]) < 1e-4
+
+
+def test_still_unsupported_configurations_raise():
+    d = dev()
+    g = load_golden("v_6432")
+    macro, x, R, mask = [torch.from_numpy(g[k]).to(d) for k in ("macro", "x", "R", "mask")]
+    for cfg in ({"hidden_dim": [64, 64, 64]}, {"hidden_dim": [128, 64]}, {"residual_loss_factor": 0.1},
+                {"num_units_rnn": [4, 4]}, {"num_condition_moment": 4}):
+        bad = AssetPricingGAN({"macro_feature_dim": 8, "individual_feature_dim": 46, **cfg}).to(d)
+        with pytest.raises(NotImplementedError):
+            bad(macro, x, R, mask)
