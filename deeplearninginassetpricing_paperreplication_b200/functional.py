@@ -499,7 +499,7 @@ class GanStepFn(torch.autograd.Function):
             if want_sdf or want_mom:
                 tens = _tensors(params)
                 _timed_call("dlap_cell_bwd", dev, ws.pp, _ptr(x), _ptr(R), _ptr(mask), _ptr(index), C.byref(tens),
-                            C.byref(mio), _ptr(row_stats), _ptr(dS2), _ptr(g_lc) if has_q else None,
+                            C.byref(mio), _ptr(row_stats), _ptr(dS2), _ptr(g_lc) if (has_q or q_given) else None,
                             _ptr(g_lu), _ptr(g_pr), _ptr(G), _ptr(scalars), int(opts.weighted_loss), int(want_sdf),
                             int(want_mom), _ptr(ws.wpart), _ptr(ws.dadc_part), prec, float(opts.dropout_p),
                             int(opts.dropout_seed), _ptr(opts.dropout_seed_dev), st)

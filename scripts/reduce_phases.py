@@ -18,7 +18,7 @@ macro, x, R, mask = [t.to(dev) for t in bench.synthetic_panel(T, N, 46, 178, see
 torch.manual_seed(42)
 model = AssetPricingGAN({"macro_feature_dim": 178, "individual_feature_dim": 46, "dropout": 0.0,
                          "b200_precision": "bf16x3"}).to(dev).eval()
-kp = [p.detach() for p in model._kernel_params(True)]
+kp = [p.detach() for p in model._inputs(macro, x, True).params]
 ws = Fn.workspace(T, N, 46, 178, 4, dev)
 cp = Fn.cell_forward(ws, macro, x, mask, kp, None, None, "bf16x3", True)
 red = Fn.step_reduce(ws, cp, R, mask, True, True)

@@ -141,7 +141,7 @@ def test_forward_stages_rand_small():
     T, N, F = x.shape
     ref = cf.forward(params, g["macro"], g["x"], g["R"], g["mask"])
     s = ref["_saved"]
-    kp = [p.detach() for p in model._kernel_params(True)]
+    kp = [p.detach() for p in model._inputs(macro, x, True).params]
     ws = Fn.workspace(T, N, F, 178, 4, dev())
     cp = Fn.cell_forward(ws, macro, x, mask, kp, None, None, "fp32", True)
     torch.cuda.synchronize()
@@ -202,7 +202,7 @@ def test_forward_stages_tensor_core_visits_only_unmasked_cells():
     T, N, F = x.shape
     ref = cf.forward(params, g["macro"], g["x"], g["R"], g["mask"])
     s = ref["_saved"]
-    kp = [p.detach() for p in model._kernel_params(True)]
+    kp = [p.detach() for p in model._inputs(macro, x, True).params]
     ws = Fn.workspace(T, N, F, 178, 4, dev())
     save, a_t, c_t, hn, cn = Fn.macro_forward(ws, macro, kp, None, None)            # stand-alone macro kernel
     real_empty = torch.empty

