@@ -19,7 +19,8 @@ cudaError_t launch_step_reduce_c(const dlap_plan* plan, const float* u, const fl
                                  const int* index, int weighted, int flags, const float* n_bar_in, int phase_lo, int phase_hi,
                                  float* row_stats, float* pr, float* scalars, float* w_out, double* col_part, float* e,
                                  float* t_i, float* G, double* loss_part, double* dS2, double* row_part,
-                                 unsigned int* bar, cudaStream_t st);
+                                 unsigned int* bar, float* xbuf, int T_series, int month0, int month_stride,
+                                 cudaStream_t st);
 cudaError_t launch_loss_finish(const double*, int, int, int, float*, float*, double*, unsigned int*, float*,
                                cudaStream_t);
 cudaError_t launch_grad_finish(const FinishParams& P, cudaStream_t st);
@@ -269,16 +270,27 @@ int dlap_step_reduce(const dlap_plan* plan, const float* u, const float* q, cons
                      const int32_t* index, int weighted_loss, int flags, const float* n_bar_in, int phase_lo, int phase_hi,
                      float* row_stats, float* pr, float* scalars, float* w_out, double* col_part, float* e,
                      float* t_i, float* G, double* loss_part, double* dS2, double* row_part, uint32_t* bar,
-                     void* stream) {
+                     const dlap_macro_io* series, float* xbuf, void* stream) {
   int rc = check_plan(plan);
   if (rc) return rc;
   if (phase_lo < 0 || phase_hi > 4 || phase_lo > phase_hi) return DLAP_E_SHAPE;
   REQ(mask); REQ(R); REQ(row_stats); REQ(scalars); REQ(col_part); REQ(bar);
   if (reinterpret_cast<uintptr_t>(bar) & 3) return DLAP_E_ALIGN;
-  if (phase_lo <= 1) { REQ(u); REQ(pr); }
+  if (phase_lo <= 1) REQ(u);
+  if (phase_lo <= 1 || xbuf) REQ(pr);
+  int T_series = plan->dims.T, month0 = 0, month_stride = 1;
+  if (xbuf) {
+    REQ(series);
+    month_stride = series->month_stride > 0 ? series->month_stride : 1;
+    T_series = series->series_T > 0 ? series->series_T : plan->dims.T;
+    month0 = series->month0;
+    if (month0 < 0 || (long long)month0 + (long long)(plan->dims.T - 1) * month_stride >= T_series) return DLAP_E_SHAPE;
+    if (reinterpret_cast<uintptr_t>(xbuf) & 3) return DLAP_E_ALIGN;
+  }
   if (phase_hi >= 3) { REQ(e); REQ(t_i); REQ(G); REQ(loss_part); }
   CU(launch_step_reduce_c(plan, u, q, R, mask, index, weighted_loss, flags, n_bar_in, phase_lo, phase_hi, row_stats, pr,
-                          scalars, w_out, col_part, e, t_i, G, loss_part, dS2, row_part, bar, (cudaStream_t)stream));
+                          scalars, w_out, col_part, e, t_i, G, loss_part, dS2, row_part, bar, xbuf, T_series, month0,
+                          month_stride, (cudaStream_t)stream));
   return DLAP_OK;
 }
 

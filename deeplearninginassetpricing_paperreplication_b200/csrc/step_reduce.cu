@@ -44,6 +44,10 @@ struct ReduceParams {
   double* row_part;          // [T,nseg,4] partial sums of the per-month phases
   int nseg;                  // segments a month's cells are cut into in phases 0 and 4
   unsigned int* bar;         // [1 + T], zero between launches: the grid barrier word, then one counter per month
+  // month shards: what crosses the wire between phases 2 and 3, in fp32: [10,N] per-stock sums, then the series'
+  // portfolio returns (this rank fills its own months, the rest is zero, so that the all-reduce assembles them)
+  float* xbuf;               // [10 N + T_series] or null (single device)
+  int T_series, month0, month_stride;
   int phase_lo, phase_hi;    // inclusive
 };
 
@@ -91,6 +95,8 @@ __global__ void __launch_bounds__(RT, 4) step_reduce_kernel(const ReduceParams P
   // last segment (a counter per month) adds the segments' partial sums in segment order.
   if (P.phase_lo <= 0 && P.phase_hi >= 0) {
     const int nseg = P.nseg;
+    if (P.xbuf && blockIdx.x == gridDim.x - 1)
+      for (int t = tid; t < P.T_series; t += RT) P.xbuf[(size_t)(KM + 2) * N + t] = 0.f;
     for (int unit = blockIdx.x; unit < T * nseg; unit += gridDim.x) {
       const int t = unit / nseg, seg = unit % nseg;
       double v[4] = {0.0, 0.0, 0.0, 0.0};          // count, sum u, sum u R, sum R
@@ -161,7 +167,8 @@ __global__ void __launch_bounds__(RT, 4) step_reduce_kernel(const ReduceParams P
         float pr;
         const float S = S_of(rs, P.weighted, n_bar, &pr);
         rs[RS_PR] = pr; rs[RS_S] = S;
-        P.pr[t] = pr;
+        if (P.xbuf) P.xbuf[(size_t)(KM + 2) * N + P.month0 + (size_t)t * P.month_stride] = pr;
+        else P.pr[t] = pr;
         s1 += (double)pr;
       }
       s1 = block_sum(s1, red);
@@ -177,7 +184,8 @@ __global__ void __launch_bounds__(RT, 4) step_reduce_kernel(const ReduceParams P
       if (tid == 0) {
         P.scalars[SC_NBAR] = n_bar;
         P.scalars[SC_ZERO] = 0.f;          // what a NULL loss cotangent points at in dlap_cell_bwd
-        P.scalars[SC_SHARPE] = (T > 1) ? (float)(mean / (sqrt(s2 / (double)(T - 1)) + 1e-8)) : nanf("");
+        // (a month shard only knows its own months here: the series' Sharpe ratio follows the exchange, phase 3)
+        if (!P.xbuf) P.scalars[SC_SHARPE] = (T > 1) ? (float)(mean / (sqrt(s2 / (double)(T - 1)) + 1e-8)) : nanf("");
       }
     }
     const int nb = (N + RT - 1) / RT, nw = (N + 31) >> 5;
@@ -227,22 +235,22 @@ __global__ void __launch_bounds__(RT, 4) step_reduce_kernel(const ReduceParams P
         for (int k = 0; k < KM + 2; ++k) out[(size_t)k * N] = acc[k];
       }
     }
-    if (P.phase_hi >= 2 && !(P.phase_hi == 2 && P.nsplit == 1)) grid_sync(P.bar, ++nsync);
+    if (P.phase_hi >= 2 && !(P.phase_hi == 2 && P.nsplit == 1 && !P.xbuf)) grid_sync(P.bar, ++nsync);
   }
 
   // ---------------------------------------------------------------- phase 2: month chunks -> chunk 0
   // (every CTA takes part: 10 N sums of nsplit terms.  Measured against letting phase 3 add the chunks itself, one
   // thread per stock and one barrier less: 66 us against 71 for the whole kernel at the paper shape)
-  if (P.phase_lo <= 2 && P.phase_hi >= 2 && P.nsplit > 1) {
+  if (P.phase_lo <= 2 && P.phase_hi >= 2 && (P.nsplit > 1 || P.xbuf)) {
     const size_t n10 = (size_t)(KM + 2) * N;
     for (size_t idx = (size_t)blockIdx.x * RT + tid; idx < n10; idx += (size_t)gridDim.x * RT) {
       double s = __ldcg(P.col_part + idx);
       for (int sp = 1; sp < P.nsplit; ++sp) s += __ldcg(P.col_part + (size_t)sp * n10 + idx);
-      P.col_part[idx] = s;
+      if (P.xbuf) P.xbuf[idx] = (float)s; else P.col_part[idx] = s;
     }
   }
 
-  if (P.phase_lo <= 2 && P.phase_hi >= 3 && P.nsplit > 1) grid_sync(P.bar, ++nsync);
+  if (P.phase_lo <= 2 && P.phase_hi >= 3 && (P.nsplit > 1 || P.xbuf)) grid_sync(P.bar, ++nsync);
 
   // ---------------------------------------------------------------- phase 3: e, T_i, unit coefficients, sum e^2
   if (P.phase_lo <= 3 && P.phase_hi >= 3) {
@@ -253,7 +261,8 @@ __global__ void __launch_bounds__(RT, 4) step_reduce_kernel(const ReduceParams P
       if (i < N) {
         double v[KM + 2];
 #pragma unroll
-        for (int k = 0; k < KM + 2; ++k) v[k] = __ldcg(P.col_part + (size_t)k * N + i);
+        for (int k = 0; k < KM + 2; ++k)
+          v[k] = P.xbuf ? (double)__ldcg(P.xbuf + (size_t)k * N + i) : __ldcg(P.col_part + (size_t)k * N + i);
         const double ti = fmax(v[KM + 1], 1.0);
         const float tif = (float)ti;
         P.t_i[i] = tif;
@@ -277,6 +286,19 @@ __global__ void __launch_bounds__(RT, 4) step_reduce_kernel(const ReduceParams P
       sc = block_sum(sc, red);
       su = block_sum(su, red);
       if (tid == 0) { P.loss_part[2 * blk] = sc; P.loss_part[2 * blk + 1] = su; }
+    }
+    if (P.xbuf && blockIdx.x == gridDim.x - 1) {        // the series' portfolio returns are complete now: Sharpe ratio
+      const float* prs = P.xbuf + (size_t)(KM + 2) * N;
+      const int Ts = P.T_series;
+      double s1 = 0.0;
+      for (int t = tid; t < Ts; t += RT) { const float pr = __ldcg(prs + t); P.pr[t] = pr; s1 += (double)pr; }
+      __syncthreads();
+      s1 = block_sum(s1, red);
+      const double mean = s1 / (double)Ts;
+      double s2 = 0.0;
+      for (int t = tid; t < Ts; t += RT) { const double d = (double)__ldcg(prs + t) - mean; s2 += d * d; }
+      s2 = block_sum(s2, red);
+      if (tid == 0) P.scalars[SC_SHARPE] = (Ts > 1) ? (float)(mean / (sqrt(s2 / (double)(Ts - 1)) + 1e-8)) : nanf("");
     }
     if (P.phase_hi >= 4) grid_sync(P.bar, ++nsync);
   }
@@ -396,9 +418,11 @@ cudaError_t launch_step_reduce_c(const dlap_plan* plan, const float* u, const fl
                                  const int* index, int weighted, int flags, const float* n_bar_in, int phase_lo, int phase_hi,
                                  float* row_stats, float* pr, float* scalars, float* w_out, double* col_part, float* e,
                                  float* t_i, float* G, double* loss_part, double* dS2, double* row_part,
-                                 unsigned int* bar, cudaStream_t st) {
+                                 unsigned int* bar, float* xbuf, int T_series, int month0, int month_stride,
+                                 cudaStream_t st) {
   ReduceParams P{};
   P.row_part = row_part;
+  P.xbuf = xbuf; P.T_series = T_series; P.month0 = month0; P.month_stride = month_stride;
   P.u = u; P.q = q; P.R = R; P.mask = mask; P.index = index;
   P.T = plan->dims.T; P.N = plan->dims.N;
   P.weighted = weighted; P.n_bar_in = n_bar_in; P.n_total = plan->dims.N;

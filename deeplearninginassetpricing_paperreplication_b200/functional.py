@@ -394,7 +394,8 @@ def step_reduce(ws: Workspace, cp: CellPass, R, mask, weighted_loss: bool, want_
     dev = R.device
     T, N = R.shape
     row_stats = torch.empty(T, RS_W, dtype=torch.float32, device=dev)
-    pr = torch.empty(T, dtype=torch.float32, device=dev)
+    pr = torch.empty(T if shard is None else shard.T_total, dtype=torch.float32, device=dev)   # a shard: the whole series'
+    xbuf = None if shard is None else torch.empty((KM + 2) * N + shard.T_total, dtype=torch.float32, device=dev)
     scalars = torch.empty(SC_W, dtype=torch.float32, device=dev)
     w = torch.empty(T, N, dtype=torch.float32, device=dev)
     e = torch.empty(KM + 1, N, dtype=torch.float32, device=dev)
@@ -406,15 +407,16 @@ def step_reduce(ws: Workspace, cp: CellPass, R, mask, weighted_loss: bool, want_
         _timed_call("dlap_step_reduce", dev, ws.pp, _ptr(cp.u), _ptr(q), _ptr(R), _ptr(mask), _ptr(cp.index),
                     int(weighted_loss), flags, _ptr(shard.n_bar) if shard is not None else None, lo, hi, _ptr(row_stats),
                     _ptr(pr), _ptr(scalars), _ptr(w), _ptr(ws.col_part), _ptr(e), _ptr(t_i), _ptr(G),
-                    _ptr(ws.loss_part), _ptr(dS2), _ptr(ws.row_part), _ptr(ws.bar), _stream(dev))
+                    _ptr(ws.loss_part), _ptr(dS2), _ptr(ws.row_part), _ptr(ws.bar),
+                    C.byref(cp.mio) if shard is not None else None, _ptr(xbuf), _stream(dev))
         ws.launches += 1
 
     if shard is None:
         launch(0, 4)
-    else:       # exchange 1: per-stock sums over ALL months
+    else:       # exchange 1 (the only one of the forward pass): per-stock sums over ALL months + the series' returns
         launch(0, 2)
         with _timed_region("exchange_fwd", dev):
-            torch.distributed.all_reduce(ws.col_part[:(KM + 2) * N], group=shard.group)
+            torch.distributed.all_reduce(xbuf, group=shard.group)
         launch(3, 4)
     return Reduced(row_stats, pr, scalars, w, G, dS2)
 

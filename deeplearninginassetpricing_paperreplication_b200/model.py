@@ -344,8 +344,6 @@ class AssetPricingGAN(nn.Module):
             loss_unc, loss_cond, total = zero, l_c, -l_c
         else:                                   # src/model.py:537-541
             loss_unc, loss_cond, total = l_u, l_c, l_c
-        if self.month_shard is not None:
-            pr, sharpe = _gather_months(pr, self.month_shard)
         new_hidden = (hn.view(1, 1, H), cn.view(1, 1, H)) if with_macro else None
 
         def moments():
@@ -425,6 +423,10 @@ class GraphedStep:
     about as much host time as they run on the device, so a loop over a resident panel is otherwise bound by
     Python.  ``step()`` replays the graph and returns the forward dict (static tensors, overwritten by the next
     replay); ``p.grad`` of every parameter is overwritten, not accumulated.
+
+    Drop every reference to the outputs of earlier eager steps (``out``, ``loss``) before constructing one: an
+    autograd graph that is still alive keeps the parameters' AccumulateGrad nodes on the stream it ran on, and the
+    capture then fails with a stream-dependency error.
 
     The panel tensors are the ones passed in (full-batch training on a resident panel, as the reference's
     loops do); copy new VALUES into them with ``.copy_()`` if needed, but keep the mask: its valid-cell index
@@ -510,12 +512,3 @@ class GraphedStep:
         return self.out
 
     __call__ = step
-
-
-def _gather_months(pr_local, shard):
-    import torch.distributed as dist
-    full = torch.zeros(shard.T_total, dtype=pr_local.dtype, device=pr_local.device)
-    full[shard.t0:shard.t1:shard.stride] = pr_local.detach()
-    dist.all_reduce(full, group=shard.group)
-    sharpe = full.mean() / (full.std() + 1e-8)
-    return full, sharpe

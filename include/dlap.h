@@ -177,7 +177,7 @@ int dlap_cell_fwd(const dlap_plan* plan, const float* x, const uint8_t* mask, co
  *      per stock and month chunk: sum_t q_k R S_t, sum_t R m S_t, sum_t m (src/model.py:376, :382, :428)
  *                                                      -> col_part [col_splits,10,N]
  *      and the demeaned weights w = m (u - mu_t) (src/model.py:271-279)      -> w_out [T,N] when non-NULL
- *   2  the month chunks summed into chunk 0 of col_part (month shards all-reduce col_part[0] after this phase)
+ *   2  the month chunks summed into chunk 0 of col_part (month shards: into xbuf, see below)
  *   3  e_ki = colsum / T_i (src/model.py:382, :428) -> e [9,N], t_i [N]; the loss coefficients for UNIT cotangents,
  *      G_ki = 2 e_ki / (K N T_i), G_8i = 2 e0_i / (N T_i) (autograd at src/train.py:84)
  *                              -> G [N,12], one row per stock: G_0i .. G_7i, G_8i, three floats of padding
@@ -186,6 +186,11 @@ int dlap_cell_fwd(const dlap_plan* plan, const float* x, const uint8_t* mask, co
  * flags: DLAP_REDUCE_NO_DEMEAN: normalize_w = False (src/model.py:274): w = m u, mu_t and Rbar_t are reported as 0;
  * DLAP_REDUCE_Q_DENSE: q is a dense [8,T,N] tensor even though u is left-packed (moment outputs that did not come
  * from dlap_cell_fwd: a moment network with hidden layers, evaluated by the caller).
+ * Month shards (xbuf != NULL; series: the shard's place in the series -- series_T, month0, month_stride, nothing
+ * else is read): phase 2 writes what has to cross the wire into xbuf, fp32 [10 N + series_T]: the per-stock sums
+ * of this rank's months, then the series' portfolio returns with this rank's months filled in and zeros elsewhere.
+ * The caller sum-all-reduces xbuf between a call for phases 0..2 and a call for phases 3..4; phase 3 then reads the
+ * per-stock sums from it and writes the whole series' pr [series_T] and its Sharpe ratio.
  * Single device: phases 0..4 in one launch.  q may be NULL (phase 'unconditional').  index: the valid-cell index
  * when u and q come from the BF16X3 dlap_cell_fwd, NULL for FP32.  row_part: scratch (row_part_bytes; NULL: the
  * per-month phases run one CTA per month).  bar (device, bar_bytes, all zero when the call starts and all zero
@@ -196,7 +201,7 @@ int dlap_step_reduce(const dlap_plan* plan, const float* u, const float* q, cons
                      const int32_t* index, int weighted_loss, int flags, const float* n_bar_in, int phase_lo, int phase_hi,
                      float* row_stats, float* pr, float* scalars, float* w_out, double* col_part, float* e,
                      float* t_i, float* G, double* loss_part, double* dS2, double* row_part, uint32_t* bar,
-                     void* stream);
+                     const dlap_macro_io* series, float* xbuf, void* stream);
 
 /* The loss stage on its own, for a caller that holds per-stock sums from elsewhere: e_ki = colsum / T_i,
  * L_c = mean_k mean_i e_ki^2, L_u = mean_i e0_i^2 (src/model.py:382-385, :428-431) -> e [9,N], t_i [N],

@@ -29,9 +29,9 @@ w = torch.empty(T, N, device=dev)
 
 def launch(lo, hi):
     _lib.call("dlap_step_reduce", ws.pp, cp.u.data_ptr(), cp.q.data_ptr(), R.data_ptr(), mask.data_ptr(),
-              cp.index.data_ptr(), 1, None, lo, hi, red.row_stats.data_ptr(), red.pr.data_ptr(), red.scalars.data_ptr(),
+              cp.index.data_ptr(), 1, 0, None, lo, hi, red.row_stats.data_ptr(), red.pr.data_ptr(), red.scalars.data_ptr(),
               w.data_ptr(), ws.col_part.data_ptr(), e.data_ptr(), t_i.data_ptr(), red.G.data_ptr(),
-              ws.loss_part.data_ptr(), red.dS2.data_ptr(), ws.row_part.data_ptr(), ws.bar.data_ptr(),
+              ws.loss_part.data_ptr(), red.dS2.data_ptr(), ws.row_part.data_ptr(), ws.bar.data_ptr(), None, None,
               torch.cuda.current_stream().cuda_stream)
 
 

@@ -1,8 +1,9 @@
 """Month-sharding algebra and its host-side plumbing on CPU: two gloo ranks, each owning half of the
 months.  The per-shard arithmetic is the fp64 oracle; what is under test is that the two exchanges of
 DESIGN.md §5 (per-stock column sums forward; da_t|dc_t rows + per-cell weight gradients backward, N_bar
-once) reproduce the unsharded result, and that functional.make_month_shard / model._gather_months move the
-right numbers."""
+once) reproduce the unsharded result -- with exchange 1 laid out and rounded as the kernels do it: ONE fp32 buffer,
+the [10,N] per-stock sums followed by the series' portfolio returns (own months filled in, zeros elsewhere) -- and
+that functional.make_month_shard moves the right numbers."""
 import os
 import socket
 
@@ -27,7 +28,6 @@ def _worker(rank, world, port, out_q):
     dist.init_process_group("gloo", rank=rank, world_size=world)
     try:
         from deeplearninginassetpricing_paperreplication_b200 import functional as Fn
-        from deeplearninginassetpricing_paperreplication_b200.model import _gather_months
         g = load_golden("shipped_sub")
         params = {k: v.astype(np.float64) for k, v in golden_params(g).items()}
         macro, x, R, mask = g["macro"], g["x"], g["R"], g["mask"]
@@ -47,17 +47,27 @@ def _worker(rank, world, port, out_q):
         col = np.concatenate([np.einsum("tnk,tn->kn", s["q"][sl], rm * S_loc[:, None]),
                               (rm * S_loc[:, None]).sum(axis=0, keepdims=True),
                               mask[sl].sum(axis=0, keepdims=True).astype(np.float64)], axis=0)
-        colt = torch.from_numpy(col)
-        dist.all_reduce(colt)
-        t_i = np.maximum(colt[9].numpy(), 1.0)
-        e = colt[:8].numpy() / t_i
-        e0 = colt[8].numpy() / t_i
+        N = x.shape[1]
+
+        def exchange(col_local, pr_local, months):
+            """dlap_step_reduce's xbuf: fp32 [10 N + T], summed over the ranks"""
+            xb = np.zeros(10 * N + T, dtype=np.float32)
+            xb[:10 * N] = col_local.reshape(-1).astype(np.float32)
+            xb[10 * N + np.asarray(months)] = pr_local.astype(np.float32)
+            xt = torch.from_numpy(xb)
+            dist.all_reduce(xt)
+            return xt.numpy()[:10 * N].reshape(10, N).astype(np.float64), xt.numpy()[10 * N:]
+
+        colt, pr_full = exchange(col, full["portfolio_returns"][sl], np.arange(t0, t1))
+        t_i = np.maximum(colt[9], 1.0)
+        e = colt[:8] / t_i
+        e0 = colt[8] / t_i
         assert np.allclose(e, s["e"], rtol=1e-5, atol=1e-9) and np.allclose(e0, s["e0"], rtol=1e-5, atol=1e-9)
         l_c = (e ** 2).mean(axis=1).mean()
         assert abs(l_c - full["loss_conditional"]) < 1e-5 * abs(full["loss_conditional"])
-        # month gather (portfolio returns + Sharpe of the whole series)
-        pr_full, sharpe = _gather_months(torch.from_numpy(full["portfolio_returns"][sl].astype(np.float32)), shard)
-        assert np.allclose(pr_full.numpy(), full["portfolio_returns"], rtol=1e-5, atol=1e-8)
+        # the series' portfolio returns rode along; Sharpe of the whole series (src/model.py:551)
+        assert np.allclose(pr_full, full["portfolio_returns"], rtol=1e-5, atol=1e-8)
+        sharpe = pr_full.astype(np.float64).mean() / (pr_full.astype(np.float64).std(ddof=1) + 1e-8)
         assert abs(float(sharpe) - float(full["sharpe"])) < 1e-4 * abs(float(full["sharpe"]))
         # exchange 2: da_t rows (zero outside the slab) summed over ranks == the full table
         gfull = cf.backward(params, macro, x, R, mask, full)
@@ -80,9 +90,8 @@ def _worker(rank, world, port, out_q):
         rr = Fn.make_month_shard(torch.from_numpy(mask[rank::2]), rank, T, None, stride=2)
         assert abs(float(rr.n_bar) - n_bar_ref) < 1e-4 and rr.stride == 2 and rr.t1 <= T
         assert torch.equal(rr.rows(torch.arange(T)), torch.arange(T)[rank::2])
-        pr_rr, sharpe_rr = _gather_months(torch.from_numpy(full["portfolio_returns"][rank::2].astype(np.float32)), rr)
-        assert np.allclose(pr_rr.numpy(), full["portfolio_returns"], rtol=1e-5, atol=1e-8)
-        assert abs(float(sharpe_rr) - float(full["sharpe"])) < 1e-4 * abs(float(full["sharpe"]))
+        _, pr_rr = exchange(np.zeros((10, N)), full["portfolio_returns"][rank::2], np.arange(rank, T, 2))
+        assert np.allclose(pr_rr, full["portfolio_returns"], rtol=1e-5, atol=1e-8)
         out_q.put((rank, "ok"))
     except Exception:  # pragma: no cover
         import traceback

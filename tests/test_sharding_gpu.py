@@ -68,7 +68,8 @@ def _worker(rank, world, port, precision, layout, out_q, backend="gloo"):
         torch.cuda.synchronize()
         if backend == "nccl":          # the same step as a CUDA-graph replay must say the same, to the bit
             eager = {k: p.grad.clone() for k, p in model.named_parameters()}
-            e_loss, e_w = out["loss"].clone(), out["weights"].clone()
+            e_loss, e_w = out["loss"].detach().clone(), out["weights"].clone()
+            del out             # an earlier graph that is still alive pins the parameters' AccumulateGrad stream
             model.eval()
             gs = model.graphed_step(*panel, phase="conditional")
             out = gs.step(); out = gs.step()
