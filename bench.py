@@ -55,8 +55,8 @@ def workload_config(world):
     return {"workload": (f"paper-shape panel T={T_MONTHS} N={N} F={F_CHARS} M={M_MACRO} "
                          f"(BASELINE.json configs[1]" + ("" if world == 1 else f", stocks x{world}") +
                          f"); phase 'conditional' fwd+bwd, dropout 0, hidden [64,64], rnn [4], 8 moments; "
-                         f"sharded by month, {T} months x {N} stocks = {T * N} stock-months per GPU "
-                         f"on {world} GPU(s)"),
+                         f"{T * N} stock-months per GPU on {world} GPU(s) (how the panel is dealt over the ranks: "
+                         f"`how.parallelism`)"),
             "l2": "inputs (442 MB panel per GPU) larger than the 126 MB L2; no flush needed"}
 
 
@@ -401,6 +401,15 @@ def run_ours(args, rank, world):
                              "step_frac_per_gpu = whole step at 378 B per stock-month, per GPU"},
     }
     line.update(extra)
+    if world > 1 and "by_stock" in extra and extra["by_stock"].get("value", 0) > value:
+        bs = extra["by_stock"]
+        line["alt_sharding"] = {"parallelism": how["parallelism"], "value": value, "ms_per_step": ms / args.steps,
+                                "gpu_launches": launches}
+        line["value"], line["ms_per_step"] = bs["value"], bs["ms_per_step"]
+        line["gpu_launches"] = bs["launches_per_step"] * args.steps
+        how["parallelism"] = bs["parallelism"]
+        line["roofline"]["step_frac_per_gpu"] = bs["value"] / world * ALGO_BYTES_STEP / 1e9 / hbm_peak
+        line["roofline"]["kernel_share_of_step"] = k_ms / bs["ms_per_step"]
     if not args.no_cpu and world == 1:
         r = cpu_step_rate()
         line["cpu_baseline"] = {"value": r["rate_mean"], "unit": "stock-months/s", "cores": r["cores"],
@@ -546,9 +555,9 @@ def multi_gpu_legs(args, dev, rank, world, new_model, graphed, timed, k):
     so = gs.step()
     torch.cuda.synchronize()
     rel = lambda a, b: float((a - b).abs().max() / b.abs().max().clamp_min(1e-30))
-    errs = torch.tensor([abs(float(so["loss"]) - float(o["loss"])) / abs(float(o["loss"])),
+    errs = torch.tensor([abs(float(so["loss"].detach()) - float(o["loss"].detach())) / abs(float(o["loss"].detach())),
                          rel(so["weights"], o["weights"][mine]),
-                         rel(so["portfolio_returns"], o["portfolio_returns"]),
+                         rel(so["portfolio_returns"].detach(), o["portfolio_returns"].detach()),
                          max(float((p.grad - q.grad).norm() / q.grad.norm().clamp_min(1e-30))
                              for (n, p), q in zip(part.named_parameters(), full.parameters())
                              if n != "sdf_net.output_proj.bias")], device=dev, dtype=torch.float64)
@@ -559,7 +568,9 @@ def multi_gpu_legs(args, dev, rank, world, new_model, graphed, timed, k):
                             "loss_rel": e[0], "weights_rel": e[1], "portfolio_returns_rel": e[2], "grad_norm_rel": e[3]}
     if not (e[0] < 1e-5 and e[1] < 1e-4 and e[2] < 1e-4 and e[3] < 2e-2):
         raise SystemExit(f"sharded step disagrees with the unsharded one: {out['sharded_check']}")
-    del gs, part, full, o, so
+    del gs, part, o, so
+    full.zero_grad(set_to_none=True)
+    del full
 
     # (2) configs[4]
     T5, N5 = 600, 100_000
@@ -579,6 +590,57 @@ def multi_gpu_legs(args, dev, rank, world, new_model, graphed, timed, k):
                                "scaling": "strong (fixed 60 M stock-months)", "loss": float(gs.out["loss"])}
         del gs, big, x5, R5, m5
         torch.cuda.empty_cache()
+
+    # (3) the same two workloads sharded BY STOCK (SURVEY.md §8e's alternative): every rank keeps all months of its
+    # own stocks; three all-reduces of a few kilobytes (per-month sums forward, dS + loss sums, gradients backward)
+    bs = {}
+    lo = rank * (Ns // world)
+    hi = Ns if rank == world - 1 else lo + Ns // world
+    full = new_model()
+    o = full(macro, x, R, mask, phase="conditional")
+    o["loss"].backward()
+    part = new_model()
+    part.month_shard = Fn.StockShard(dist.group.WORLD, Ns)
+    gs = graphed(part, (macro, x[:, lo:hi].contiguous(), R[:, lo:hi].contiguous(), mask[:, lo:hi].contiguous()))
+    so = gs.step()
+    torch.cuda.synchronize()
+    errs = torch.tensor([abs(float(so["loss"].detach()) - float(o["loss"].detach())) / abs(float(o["loss"].detach())),
+                         rel(so["weights"], o["weights"][:, lo:hi]),
+                         rel(so["portfolio_returns"].detach(), o["portfolio_returns"].detach()),
+                         max(float((p.grad - q.grad).norm() / q.grad.norm().clamp_min(1e-30))
+                             for (n, p), q in zip(part.named_parameters(), full.parameters())
+                             if n != "sdf_net.output_proj.bias")], device=dev, dtype=torch.float64)
+    dist.all_reduce(errs, op=dist.ReduceOp.MAX)
+    e = [float(v) for v in errs]
+    bs["sharded_check"] = {"loss_rel": e[0], "weights_rel": e[1], "portfolio_returns_rel": e[2], "grad_norm_rel": e[3]}
+    if not (e[0] < 1e-5 and e[1] < 1e-4 and e[2] < 1e-4 and e[3] < 2e-2):
+        raise SystemExit(f"stock-sharded step disagrees with the unsharded one: {bs['sharded_check']}")
+    del gs, part, full, o, so
+    # weak scaling: every rank the paper-shape panel of its own 10,000 stocks
+    _, xs, Rs, ms_ = synthetic_panel(T_MONTHS, N_STOCKS, F_CHARS, M_MACRO, seed=1234 + rank, device=dev)
+    macro_w = torch.randn(T_MONTHS, M_MACRO, generator=torch.Generator().manual_seed(99)).to(dev)
+    wk = new_model()
+    wk.month_shard = Fn.StockShard(dist.group.WORLD, N_STOCKS * world)
+    gs = graphed(wk, (macro_w, xs, Rs, ms_))
+    ms = timed(gs.step, args.steps)
+    bs.update({"value": T_MONTHS * N_STOCKS * world * args.steps / (ms * 1e-3), "unit": "stock-months/s",
+               "ms_per_step": ms / args.steps, "launches_per_step": gs.launches,
+               "parallelism": f"stocks dealt over {world} ranks (all months each), NCCL all-reduces of [T,4], [T,2]+2 "
+                              "doubles and the gradients inside the CUDA graph"})
+    del gs, wk, xs, Rs, ms_
+    torch.cuda.empty_cache()
+    if N5 % world == 0:
+        macro5 = torch.randn(T5, M_MACRO, generator=torch.Generator().manual_seed(98)).to(dev)
+        _, x5, R5, m5 = synthetic_panel(T5, N5 // world, F_CHARS, M_MACRO, seed=8765 + rank, device=dev)
+        big = new_model()
+        big.month_shard = Fn.StockShard(dist.group.WORLD, N5)
+        gs = graphed(big, (macro5, x5, R5, m5))
+        ms = timed(gs.step, k)
+        bs["scaled_panel"] = {"value": T5 * N5 * k / (ms * 1e-3), "unit": "stock-months/s", "ms_per_step": ms / k,
+                              "workload": f"T={T5} N={N5}: {N5 // world} stocks x {T5} months per GPU"}
+        del gs, big, x5, R5, m5
+        torch.cuda.empty_cache()
+    out["by_stock"] = bs
     return out
 
 

@@ -26,6 +26,7 @@ DLAP_PREC_FP32 = 0
 DLAP_PREC_BF16X3 = 1
 DLAP_REDUCE_NO_DEMEAN = 1
 DLAP_REDUCE_Q_DENSE = 2
+DLAP_REDUCE_STOCK_SHARD = 4
 
 
 class DlapDims(C.Structure):
@@ -78,7 +79,7 @@ SIGNATURES = {
     "dlap_panel_index": (_PLAN, _P, _P, _P),
     "dlap_panel_pull": (_PLAN, _P, _P, _P, _I, _I, _P),
     "dlap_cell_fwd": (_PLAN, _P, _P, _P, _TENS, _MIO, _P, _P, _I, C.c_float, C.c_uint64, _P, _P),
-    "dlap_step_reduce": (_PLAN, _P, _P, _P, _P, _P, _I, _I, _P, _I, _I, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _MIO, _P, _P),
+    "dlap_step_reduce": (_PLAN, _P, _P, _P, _P, _P, _I, _I, _P, _I, _I, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _MIO, _P, _P, _I, _P),
     "dlap_loss_finish": (_PLAN, _P, _I, _P, _P, _P, _P, _P, _P),
     "dlap_loss_finish_noalloc": (_PLAN, _P, _I, _P, _P, _P, _P),
     "dlap_cell_bwd": (_PLAN, _P, _P, _P, _P, _TENS, _MIO, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _P, _P, _I,

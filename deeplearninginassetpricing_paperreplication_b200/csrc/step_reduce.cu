@@ -48,6 +48,12 @@ struct ReduceParams {
   // portfolio returns (this rank fills its own months, the rest is zero, so that the all-reduce assembles them)
   float* xbuf;               // [10 N + T_series] or null (single device)
   int T_series, month0, month_stride;
+  // stock shards (this rank owns a slice of the stocks, all months): the per-month sums are partial sums.  Phase 0
+  // leaves the raw sums in row_sums [T,4] (all-reduced by the caller); a launch that starts at phase 1 first turns
+  // them into row_stats; phase 4 leaves the sums of e^2 behind the dS sums, dS2 [T,2] + [2] (all-reduced by the
+  // caller); phase 5 turns those two into L_c and L_u.
+  int stock_shard;
+  double* row_sums;
   int phase_lo, phase_hi;    // inclusive
 };
 
@@ -156,6 +162,20 @@ __global__ void __launch_bounds__(RT, 4) step_reduce_kernel(const ReduceParams P
 
   // ---------------------------------------------------------------- phase 1: N_bar, S_t; column partial sums
   if (P.phase_lo <= 1 && P.phase_hi >= 1) {
+    if (P.stock_shard && P.phase_lo == 1) {       // the months' sums over ALL stocks are in: row_stats from them
+      for (int t = blockIdx.x * RT + tid; t < T; t += gridDim.x * RT) {
+        const double* v = P.row_sums + (size_t)t * 4;
+        const double nt = fmax(v[0], 1.0);
+        const float mu = P.no_demean ? 0.f : (float)(v[1] / nt);
+        float* rs = P.row_stats + (size_t)t * RS_W;
+        rs[RS_NT] = (float)nt;
+        rs[RS_MU] = mu;
+        rs[RS_P] = (float)(v[2] - (double)mu * v[3]);
+        rs[RS_RBAR] = P.no_demean ? 0.f : (float)(v[3] / nt);
+        rs[RS_SR] = (float)v[3];
+      }
+      grid_sync(P.bar, ++nsync);
+    }
     double nsum = 0.0;
     for (int t = tid; t < T; t += RT) nsum += (double)__ldcg(P.row_stats + (size_t)t * RS_W + RS_NT);
     nsum = block_sum(nsum, red);
@@ -312,7 +332,9 @@ __global__ void __launch_bounds__(RT, 4) step_reduce_kernel(const ReduceParams P
       __syncthreads();
       a = block_sum(a, red);
       b = block_sum(b, red);
-      if (tid == 0) {
+      if (tid == 0 && P.stock_shard) {       // this rank's stocks only: the sums travel behind the dS sums
+        P.dS2[2 * (size_t)T] = a; P.dS2[2 * (size_t)T + 1] = b;
+      } else if (tid == 0) {
         // means run over ALL columns, dead ones included (src/model.py:385)
         P.scalars[SC_LC] = (float)(a / ((double)KM * (double)P.n_total));
         P.scalars[SC_LU] = (float)(b / (double)P.n_total);
@@ -375,6 +397,11 @@ __global__ void __launch_bounds__(RT, 4) step_reduce_kernel(const ReduceParams P
       }
     }
   }
+  // ---------------------------------------------------------------- phase 5 (stock shards): L_c, L_u
+  if (P.phase_lo <= 5 && P.phase_hi >= 5 && P.stock_shard && blockIdx.x == 0 && tid == 0) {
+    P.scalars[SC_LC] = (float)(P.dS2[2 * (size_t)T] / ((double)KM * (double)P.n_total));
+    P.scalars[SC_LU] = (float)(P.dS2[2 * (size_t)T + 1] / (double)P.n_total);
+  }
   grid_exit(P.bar, nsync);
 }
 
@@ -395,6 +422,10 @@ cudaError_t launch_step_reduce(ReduceParams P, int sms, bool cooperative, cudaSt
   if (per_sm < 1) return cudaErrorLaunchOutOfResources;
   if (per_sm > 4) per_sm = 4;
   // no more CTAs than any phase has work for
+  if (P.phase_lo == 5) {          // two divisions
+    step_reduce_kernel<<<1, RT, smem, st>>>(P);
+    return cudaGetLastError();
+  }
   const int nb = (P.N + RT - 1) / RT;
   int want = nb * P.nsplit;
   if (want < P.T) want = P.T;
@@ -419,13 +450,14 @@ cudaError_t launch_step_reduce_c(const dlap_plan* plan, const float* u, const fl
                                  float* row_stats, float* pr, float* scalars, float* w_out, double* col_part, float* e,
                                  float* t_i, float* G, double* loss_part, double* dS2, double* row_part,
                                  unsigned int* bar, float* xbuf, int T_series, int month0, int month_stride,
-                                 cudaStream_t st) {
+                                 double* row_sums, int n_total, cudaStream_t st) {
   ReduceParams P{};
+  P.stock_shard = (flags & DLAP_REDUCE_STOCK_SHARD) != 0; P.row_sums = row_sums;
   P.row_part = row_part;
   P.xbuf = xbuf; P.T_series = T_series; P.month0 = month0; P.month_stride = month_stride;
   P.u = u; P.q = q; P.R = R; P.mask = mask; P.index = index;
   P.T = plan->dims.T; P.N = plan->dims.N;
-  P.weighted = weighted; P.n_bar_in = n_bar_in; P.n_total = plan->dims.N;
+  P.weighted = weighted; P.n_bar_in = n_bar_in; P.n_total = n_total > 0 ? n_total : plan->dims.N;
   P.no_demean = (flags & DLAP_REDUCE_NO_DEMEAN) != 0; P.q_dense = (flags & DLAP_REDUCE_Q_DENSE) != 0;
   P.row_stats = row_stats; P.pr = pr; P.scalars = scalars; P.w_out = w_out;
   P.col_part = col_part; P.nsplit = plan->col_splits; P.tchunk = (plan->dims.T + plan->col_splits - 1) / plan->col_splits;

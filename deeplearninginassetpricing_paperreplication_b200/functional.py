@@ -198,7 +198,7 @@ class StepOptions:
     dropout_p: float = 0.0          # > 0 only in train mode (src/model.py:213)
     dropout_seed: int = 0
     dropout_seed_dev: Optional[torch.Tensor] = None   # int64 [1] on the device: overrides dropout_seed (GraphedStep)
-    shard: Optional["MonthShard"] = None
+    shard: Optional["MonthShard"] = None            # a MonthShard or a StockShard
     demean: bool = True             # normalize_w (src/model.py:274): False = the weights are m u, not demeaned
 
 
@@ -231,6 +231,17 @@ def make_month_shard(mask_local: torch.Tensor, t0: int, T_total: int, group=None
     if stride < 1 or t0 < 0 or t1 > T_total:
         raise ValueError("month shard outside the series")
     return MonthShard(group=group, t0=int(t0), t1=t1, T_total=int(T_total), n_bar=n_bar, stride=int(stride))
+
+
+@dataclass
+class StockShard:
+    """This rank's slice of the STOCKS (all months) of a panel with n_total stocks.  Per-stock sums are then local
+    and complete; per-month sums are partial: the forward pass all-reduces the months' four raw sums ([T,4] doubles)
+    and, at its end, the two dS sums per month plus the two sums of e^2 ([T,2] + [2] doubles); the backward pass
+    all-reduces the da_t | dc_t rows and the per-cell weight gradients, as month shards do.  A few kilobytes each,
+    whatever the number of ranks -- and the per-stock stage does not grow with it."""
+    group: object
+    n_total: int
 
 
 def upload_panel(macro, x, R, mask, device, out=None, clear=True):
@@ -342,8 +353,9 @@ def cell_forward(ws: Workspace, macro, x, mask, params, h0, c0, precision: str, 
     dev = x.device
     T, N, F = x.shape
     M, H = ws.plan.dims.M, max(ws.plan.dims.H, 1)
-    series_T = T if shard is None else shard.T_total
-    month0, stride = (0, 1) if shard is None else (shard.t0, shard.stride)
+    months = shard if isinstance(shard, MonthShard) else None
+    series_T = T if months is None else months.T_total
+    month0, stride = (0, 1) if months is None else (months.t0, months.stride)
     index = ws.panel_index(mask) if precision == "bf16x3" else None
     save = torch.empty(series_T, 6 * H, dtype=torch.float32, device=dev)
     hn = torch.empty(H, dtype=torch.float32, device=dev)
@@ -391,27 +403,43 @@ def step_reduce(ws: Workspace, cp: CellPass, R, mask, weighted_loss: bool, want_
     per-cell kernel (they replace cp.q)."""
     flags = (0 if demean else _lib.DLAP_REDUCE_NO_DEMEAN) | (_lib.DLAP_REDUCE_Q_DENSE if q_dense is not None else 0)
     q = cp.q if q_dense is None else q_dense
+    stocks = shard if isinstance(shard, StockShard) else None
+    if stocks is not None:
+        flags |= _lib.DLAP_REDUCE_STOCK_SHARD
+        shard = None
     dev = R.device
     T, N = R.shape
     row_stats = torch.empty(T, RS_W, dtype=torch.float32, device=dev)
-    pr = torch.empty(T if shard is None else shard.T_total, dtype=torch.float32, device=dev)   # a shard: the whole series'
+    pr = torch.empty(T if shard is None else shard.T_total, dtype=torch.float32, device=dev)   # month shard: the whole series'
     xbuf = None if shard is None else torch.empty((KM + 2) * N + shard.T_total, dtype=torch.float32, device=dev)
+    row_sums = torch.empty(T, 4, dtype=torch.float64, device=dev) if stocks is not None else None
     scalars = torch.empty(SC_W, dtype=torch.float32, device=dev)
     w = torch.empty(T, N, dtype=torch.float32, device=dev)
     e = torch.empty(KM + 1, N, dtype=torch.float32, device=dev)
     t_i = torch.empty(N, dtype=torch.float32, device=dev)
     G = torch.empty(N, GS, dtype=torch.float32, device=dev)
     dS2 = torch.empty(T, 2, dtype=torch.float64, device=dev) if want_backward else None
+    if stocks is not None:          # [T,2] dS sums, then the two sums of e^2: one buffer, one all-reduce
+        dS2 = torch.empty(2 * T + 2, dtype=torch.float64, device=dev)
 
     def launch(lo, hi):
         _timed_call("dlap_step_reduce", dev, ws.pp, _ptr(cp.u), _ptr(q), _ptr(R), _ptr(mask), _ptr(cp.index),
                     int(weighted_loss), flags, _ptr(shard.n_bar) if shard is not None else None, lo, hi, _ptr(row_stats),
                     _ptr(pr), _ptr(scalars), _ptr(w), _ptr(ws.col_part), _ptr(e), _ptr(t_i), _ptr(G),
                     _ptr(ws.loss_part), _ptr(dS2), _ptr(ws.row_part), _ptr(ws.bar),
-                    C.byref(cp.mio) if shard is not None else None, _ptr(xbuf), _stream(dev))
+                    C.byref(cp.mio) if shard is not None else None, _ptr(xbuf), _ptr(row_sums),
+                    stocks.n_total if stocks is not None else 0, _stream(dev))
         ws.launches += 1
 
-    if shard is None:
+    if stocks is not None:
+        launch(0, 0)
+        with _timed_region("exchange_fwd", dev):
+            torch.distributed.all_reduce(row_sums, group=stocks.group)
+        launch(1, 4)
+        with _timed_region("exchange_fwd2", dev):
+            torch.distributed.all_reduce(dS2, group=stocks.group)
+        launch(5, 5)
+    elif shard is None:
         launch(0, 4)
     else:       # exchange 1 (the only one of the forward pass): per-stock sums over ALL months + the series' returns
         launch(0, 2)
@@ -445,7 +473,7 @@ class GanStepFn(torch.autograd.Function):
         H = 0 if M == 0 else params[1].shape[1]
         sh = opts.shard
         if (tables or q_in is not None) and sh is not None:
-            raise NotImplementedError("month shards with caller-made bias tables / moment outputs")
+            raise NotImplementedError("shards with caller-made bias tables / moment outputs")
         want_backward = any(ctx.needs_input_grad)
         kernel_moments = opts.need_moments and q_in is None
         with torch.cuda.device(dev):
@@ -476,6 +504,9 @@ class GanStepFn(torch.autograd.Function):
         opts, ws = ctx.opts, ctx.ws
         save, a_t, c_t, index, mio, has_q, row_stats, scalars, G, dS2, tables, q_given = ctx.keep
         sh = opts.shard
+        stocks = isinstance(sh, StockShard)
+        # rows of the da_t | dc_t table that is exchanged: the whole series' (month shards) / this panel's (stock shards)
+        T_rows = 0 if sh is None else (x.shape[0] if stocks else sh.T_total)
         dev = x.device
         T, N, F = x.shape
         M = ws.plan.dims.M
@@ -511,7 +542,7 @@ class GanStepFn(torch.autograd.Function):
                 # ONE all-reduce over it -- gradients that are computed later (LSTM, b1, bq) are still zero.
                 # Otherwise no fill: the kernels write every element of every gradient that is handed back.
                 sizes = [0 if p is None else p.numel() for p in params]
-                head = 0 if sh is None else sh.T_total * 72
+                head = T_rows * 72
                 buf = (torch.empty if sh is None else torch.zeros)(head + sum(sizes), dtype=torch.float32, device=dev)
                 flat_g = buf[head:]
                 grads, off = [], 0
@@ -533,12 +564,13 @@ class GanStepFn(torch.autograd.Function):
                                 _ptr(ws.dadc_part), _ptr(index), prec, _ptr(ws.counter), st)
                     ws.launches += 2
                 else:   # exchange 2: per-cell weight grads + every month's da_t | dc_t row
-                    dadc_all = buf[:head].view(sh.T_total, 72)
+                    dadc_all = buf[:head].view(T_rows, 72)
+                    t0, stride = (0, 1) if stocks else (sh.t0, sh.stride)
                     _timed_call("dlap_grad_finish", dev, ws.pp, _ptr(ws.wpart), _ptr(ws.dadc_part), _ptr(index), prec,
-                                int(want_sdf), int(want_mom), C.byref(gt), _ptr(dadc_all[sh.t0:]), int(sh.stride), st)
+                                int(want_sdf), int(want_mom), C.byref(gt), _ptr(dadc_all[t0:]), int(stride), st)
                     if not opts.demean and want_sdf:
                         grads[9].copy_(_bias3_grad(opts, row_stats, scalars, dS2, g_lc if has_q or q_given else None, g_lu, g_pr))
-                    wsm = workspace(sh.T_total, N, F, M, ws.plan.dims.H, dev)
+                    wsm = workspace(T_rows, N, F, M, ws.plan.dims.H, dev)
                     with _timed_region("exchange_bwd", dev):
                         torch.distributed.all_reduce(buf, group=sh.group)
                     _timed_call("dlap_macro_bwd", dev, wsm.pp, _ptr(macro), C.byref(tens), _ptr(h0), _ptr(c0),

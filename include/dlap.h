@@ -191,17 +191,24 @@ int dlap_cell_fwd(const dlap_plan* plan, const float* x, const uint8_t* mask, co
  * of this rank's months, then the series' portfolio returns with this rank's months filled in and zeros elsewhere.
  * The caller sum-all-reduces xbuf between a call for phases 0..2 and a call for phases 3..4; phase 3 then reads the
  * per-stock sums from it and writes the whole series' pr [series_T] and its Sharpe ratio.
+ * Stock shards (flags & DLAP_REDUCE_STOCK_SHARD: this rank owns a slice of the stocks and all months; every sum
+ * over stocks is a partial sum, every sum over months is complete): three calls with two small all-reduces in
+ * between.  Phases 0..0 leave the months' raw sums in row_sums (double [T,4]: count, sum u, sum u R, sum R); the
+ * caller sum-all-reduces it; phases 1..4 turn it into row_stats and go on as usual with n_stocks_total stocks in
+ * the loss means, and leave the sums of e^2 behind the dS sums: dS2 is double [T,2] + [2] (required); the caller
+ * sum-all-reduces it; phase 5 writes L_c and L_u.
  * Single device: phases 0..4 in one launch.  q may be NULL (phase 'unconditional').  index: the valid-cell index
  * when u and q come from the BF16X3 dlap_cell_fwd, NULL for FP32.  row_part: scratch (row_part_bytes; NULL: the
  * per-month phases run one CTA per month).  bar (device, bar_bytes, all zero when the call starts and all zero
  * again when it has finished): the barrier word and one counter per month. */
 #define DLAP_REDUCE_NO_DEMEAN 1
 #define DLAP_REDUCE_Q_DENSE 2
+#define DLAP_REDUCE_STOCK_SHARD 4
 int dlap_step_reduce(const dlap_plan* plan, const float* u, const float* q, const float* R, const uint8_t* mask,
                      const int32_t* index, int weighted_loss, int flags, const float* n_bar_in, int phase_lo, int phase_hi,
                      float* row_stats, float* pr, float* scalars, float* w_out, double* col_part, float* e,
                      float* t_i, float* G, double* loss_part, double* dS2, double* row_part, uint32_t* bar,
-                     const dlap_macro_io* series, float* xbuf, void* stream);
+                     const dlap_macro_io* series, float* xbuf, double* row_sums, int n_stocks_total, void* stream);
 
 /* The loss stage on its own, for a caller that holds per-stock sums from elsewhere: e_ki = colsum / T_i,
  * L_c = mean_k mean_i e_ki^2, L_u = mean_i e0_i^2 (src/model.py:382-385, :428-431) -> e [9,N], t_i [N],

@@ -35,6 +35,12 @@ def _shape(layout):
     return (6, 76100, 8) if layout == "round_robin_wide" else (22, 700, 8)
 
 
+def _stocks(rank, N):
+    """Stock numbers of a rank (layout "stocks"): two uneven slices."""
+    cut = (3 * N) // 7
+    return slice(0, cut) if rank == 0 else slice(cut, N)
+
+
 def _months(rank, T, layout):
     """Month numbers of a rank: two uneven slabs, or every second month."""
     if layout == "slabs":
@@ -55,14 +61,20 @@ def _worker(rank, world, port, precision, layout, out_q, backend="gloo"):
         from deeplearninginassetpricing_paperreplication_b200 import functional as Fn
         T, N, M = _shape(layout)
         macro, x, R, mask = _panel(T, N, M)
-        mine = _months(rank, T, layout)
         torch.manual_seed(4)
         model = AssetPricingGAN({"macro_feature_dim": M, "individual_feature_dim": 46, "dropout": 0.0,
                                  "b200_precision": precision}).to(dev)
-        model.month_shard = Fn.make_month_shard(mask[mine].to(dev), mine[0], T, None,
-                                                stride=1 if layout == "slabs" else 2)
-        panel = (macro.to(dev), x[mine].contiguous().to(dev), R[mine].contiguous().to(dev),
-                 mask[mine].contiguous().to(dev))
+        if layout == "stocks":
+            mine = _stocks(rank, N)
+            model.month_shard = Fn.StockShard(None, N)
+            panel = (macro.to(dev), x[:, mine].contiguous().to(dev), R[:, mine].contiguous().to(dev),
+                     mask[:, mine].contiguous().to(dev))
+        else:
+            mine = _months(rank, T, layout)
+            model.month_shard = Fn.make_month_shard(mask[mine].to(dev), mine[0], T, None,
+                                                    stride=1 if layout == "slabs" else 2)
+            panel = (macro.to(dev), x[mine].contiguous().to(dev), R[mine].contiguous().to(dev),
+                     mask[mine].contiguous().to(dev))
         out = model(*panel, phase="conditional")
         out["loss"].backward()
         torch.cuda.synchronize()
@@ -91,13 +103,14 @@ def _worker(rank, world, port, precision, layout, out_q, backend="gloo"):
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs (NCCL, one rank per GPU)")
 @pytest.mark.parametrize("precision,layout", [("bf16x3", "round_robin"), ("bf16x3", "slabs"), ("fp32", "round_robin"),
-                                              ("bf16x3", "round_robin_wide")])
+                                              ("bf16x3", "round_robin_wide"), ("bf16x3", "stocks")])
 def test_two_month_shards_nccl_eager_and_graph(precision, layout):
     test_two_month_shards_match_single_process(precision, layout, backend="nccl")
 
 
 @pytest.mark.parametrize("precision,layout", [("fp32", "slabs"), ("bf16x3", "slabs"), ("fp32", "round_robin"),
-                                              ("bf16x3", "round_robin"), ("bf16x3", "round_robin_wide")])
+                                              ("bf16x3", "round_robin"), ("bf16x3", "round_robin_wide"),
+                                              ("fp32", "stocks"), ("bf16x3", "stocks")])
 def test_two_month_shards_match_single_process(precision, layout, backend="gloo"):
     from deeplearninginassetpricing_paperreplication_b200 import AssetPricingGAN
     ctx = mp.get_context("spawn")
@@ -128,7 +141,10 @@ def test_two_month_shards_match_single_process(precision, layout, backend="gloo"
     wref = ref["weights"].detach().cpu().numpy()
     w = np.empty_like(wref)
     for r in (0, 1):
-        w[_months(r, T, layout)] = res[r]["w"]
+        if layout == "stocks":
+            w[:, _stocks(r, N)] = res[r]["w"]
+        else:
+            w[_months(r, T, layout)] = res[r]["w"]
     assert np.abs(w - wref).max() <= 1e-4 * np.abs(wref).max()
     tol = 2e-4 if precision == "fp32" else 2e-2
     for k, p in model.named_parameters():
