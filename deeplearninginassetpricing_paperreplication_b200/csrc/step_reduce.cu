@@ -145,8 +145,11 @@ __global__ void __launch_bounds__(RT, 4) step_reduce_kernel(const ReduceParams P
             atomicExch(P.bar + 1 + t, 0u);
           }
         }
-        if (last) {
-            const double nt = fmax(v[0], 1.0);
+        if (last && P.stock_shard) {             // partial sums of this rank's stocks: the caller all-reduces them
+          double* o = P.row_sums + (size_t)t * 4;
+          o[0] = v[0]; o[1] = v[1]; o[2] = v[2]; o[3] = v[3];
+        } else if (last) {
+          const double nt = fmax(v[0], 1.0);
           const float mu = P.no_demean ? 0.f : (float)(v[1] / nt);
           float* rs = P.row_stats + (size_t)t * RS_W;
           rs[RS_NT] = (float)nt;
