@@ -600,7 +600,7 @@ def multi_gpu_legs(args, dev, rank, world, new_model, graphed, timed, k):
     o = full(macro, x, R, mask, phase="conditional")
     o["loss"].backward()
     part = new_model()
-    part.month_shard = Fn.StockShard(dist.group.WORLD, Ns)
+    part.month_shard = Fn.make_stock_shard(dist.group.WORLD, Ns, Ts, dev)
     gs = graphed(part, (macro, x[:, lo:hi].contiguous(), R[:, lo:hi].contiguous(), mask[:, lo:hi].contiguous()))
     so = gs.step()
     torch.cuda.synchronize()
@@ -620,20 +620,24 @@ def multi_gpu_legs(args, dev, rank, world, new_model, graphed, timed, k):
     _, xs, Rs, ms_ = synthetic_panel(T_MONTHS, N_STOCKS, F_CHARS, M_MACRO, seed=1234 + rank, device=dev)
     macro_w = torch.randn(T_MONTHS, M_MACRO, generator=torch.Generator().manual_seed(99)).to(dev)
     wk = new_model()
-    wk.month_shard = Fn.StockShard(dist.group.WORLD, N_STOCKS * world)
+    wk.month_shard = Fn.make_stock_shard(dist.group.WORLD, N_STOCKS * world, T_MONTHS, dev)
     gs = graphed(wk, (macro_w, xs, Rs, ms_))
     ms = timed(gs.step, args.steps)
     bs.update({"value": T_MONTHS * N_STOCKS * world * args.steps / (ms * 1e-3), "unit": "stock-months/s",
                "ms_per_step": ms / args.steps, "launches_per_step": gs.launches,
-               "parallelism": f"stocks dealt over {world} ranks (all months each), NCCL all-reduces of [T,4], [T,2]+2 "
-                              "doubles and the gradients inside the CUDA graph"})
+               "parallelism": (f"stocks dealt over {world} ranks (all months each); per-month sums and dS / loss sums "
+                               "exchanged INSIDE the reduction kernel over NVLink peer memory (flag barrier + P2P loads), "
+                               "gradients by one NCCL all-reduce; all inside the CUDA graph"
+                               if wk.month_shard.peers is not None else
+                               f"stocks dealt over {world} ranks (all months each), NCCL all-reduces of [T,4], [T,2]+2 "
+                               "doubles and the gradients inside the CUDA graph")})
     del gs, wk, xs, Rs, ms_
     torch.cuda.empty_cache()
     if N5 % world == 0:
         macro5 = torch.randn(T5, M_MACRO, generator=torch.Generator().manual_seed(98)).to(dev)
         _, x5, R5, m5 = synthetic_panel(T5, N5 // world, F_CHARS, M_MACRO, seed=8765 + rank, device=dev)
         big = new_model()
-        big.month_shard = Fn.StockShard(dist.group.WORLD, N5)
+        big.month_shard = Fn.make_stock_shard(dist.group.WORLD, N5, T5, dev)
         gs = graphed(big, (macro5, x5, R5, m5))
         ms = timed(gs.step, k)
         bs["scaled_panel"] = {"value": T5 * N5 * k / (ms * 1e-3), "unit": "stock-months/s", "ms_per_step": ms / k,
@@ -665,12 +669,16 @@ def main():
         import torch.distributed as dist
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", int(os.environ.get("LOCAL_RANK", 0))))
-    try:
-        run_ours(args, rank, world)
-    finally:
-        if world > 1:
-            import torch.distributed as dist
-            dist.destroy_process_group()
+    run_ours(args, rank, world)
+    if world > 1:
+        # the process group is not torn down: with symmetric-memory buffers alive destroy_process_group() does not
+        # return (seen on this image); every rank has finished its work and rank 0 has printed the line
+        import torch.distributed as dist
+        torch.cuda.synchronize()
+        dist.barrier()
+        sys.stdout.flush()
+        sys.stderr.flush()
+        os._exit(0)
 
 
 if __name__ == "__main__":

@@ -66,6 +66,12 @@ class DlapAdamTensors(C.Structure):
                 ("step", C.c_void_p * ADAM_MAX_TENSORS), ("numel", C.c_int64 * ADAM_MAX_TENSORS)]
 
 
+class DlapPeers(C.Structure):
+    """dlap_peers: every rank's exchange buffer as this device addresses it (stock shards over NVLink peer memory)."""
+    _fields_ = [("world", C.c_int32), ("rank", C.c_int32), ("months", C.c_int32), ("buf", C.c_void_p * 8),
+                ("epoch", C.c_void_p)]
+
+
 _P = C.c_void_p
 _MIO = C.POINTER(DlapMacroIO)
 _PLAN = C.POINTER(DlapPlan)
@@ -79,7 +85,8 @@ SIGNATURES = {
     "dlap_panel_index": (_PLAN, _P, _P, _P),
     "dlap_panel_pull": (_PLAN, _P, _P, _P, _I, _I, _P),
     "dlap_cell_fwd": (_PLAN, _P, _P, _P, _TENS, _MIO, _P, _P, _I, C.c_float, C.c_uint64, _P, _P),
-    "dlap_step_reduce": (_PLAN, _P, _P, _P, _P, _P, _I, _I, _P, _I, _I, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _MIO, _P, _P, _I, _P),
+    "dlap_step_reduce": (_PLAN, _P, _P, _P, _P, _P, _I, _I, _P, _I, _I, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _MIO, _P, _P, _I,
+                         C.POINTER(DlapPeers), _P),
     "dlap_loss_finish": (_PLAN, _P, _I, _P, _P, _P, _P, _P, _P),
     "dlap_loss_finish_noalloc": (_PLAN, _P, _I, _P, _P, _P, _P),
     "dlap_cell_bwd": (_PLAN, _P, _P, _P, _P, _TENS, _MIO, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _P, _P, _I,

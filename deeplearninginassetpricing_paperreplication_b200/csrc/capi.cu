@@ -20,7 +20,7 @@ cudaError_t launch_step_reduce_c(const dlap_plan* plan, const float* u, const fl
                                  float* row_stats, float* pr, float* scalars, float* w_out, double* col_part, float* e,
                                  float* t_i, float* G, double* loss_part, double* dS2, double* row_part,
                                  unsigned int* bar, float* xbuf, int T_series, int month0, int month_stride,
-                                 double* row_sums, int n_total, cudaStream_t st);
+                                 double* row_sums, int n_total, const dlap_peers* peers, cudaStream_t st);
 cudaError_t launch_loss_finish(const double*, int, int, int, float*, float*, double*, unsigned int*, float*,
                                cudaStream_t);
 cudaError_t launch_grad_finish(const FinishParams& P, cudaStream_t st);
@@ -270,17 +270,27 @@ int dlap_step_reduce(const dlap_plan* plan, const float* u, const float* q, cons
                      const int32_t* index, int weighted_loss, int flags, const float* n_bar_in, int phase_lo, int phase_hi,
                      float* row_stats, float* pr, float* scalars, float* w_out, double* col_part, float* e,
                      float* t_i, float* G, double* loss_part, double* dS2, double* row_part, uint32_t* bar,
-                     const dlap_macro_io* series, float* xbuf, double* row_sums, int n_stocks_total, void* stream) {
+                     const dlap_macro_io* series, float* xbuf, double* row_sums, int n_stocks_total,
+                     const dlap_peers* peers, void* stream) {
   int rc = check_plan(plan);
   if (rc) return rc;
   const bool stock_shard = (flags & DLAP_REDUCE_STOCK_SHARD) != 0;
   if (phase_lo < 0 || phase_hi > (stock_shard ? 5 : 4) || phase_lo > phase_hi) return DLAP_E_SHAPE;
+  if (peers && !stock_shard) return DLAP_E_SHAPE;
   if (stock_shard) {
-    REQ(row_sums); REQ(dS2);
+    REQ(dS2);
     if (xbuf || n_stocks_total < plan->dims.N) return DLAP_E_SHAPE;
-    // the all-reduces sit between phases 0 | 1..4 | 5
-    if (!((phase_lo == 0 && phase_hi == 0) || (phase_lo == 1 && phase_hi == 4) || (phase_lo == 5 && phase_hi == 5)))
-      return DLAP_E_SHAPE;
+    if (peers && peers->world > 1) {        // both exchanges inside the one launch
+      if (peers->world > 8 || peers->rank < 0 || peers->rank >= peers->world || peers->months < plan->dims.T)
+        return DLAP_E_SHAPE;
+      REQ(peers->epoch);
+      for (int r = 0; r < peers->world; ++r) REQ(peers->buf[r]);
+      if (phase_lo != 0 || phase_hi != 5) return DLAP_E_SHAPE;
+    } else {                                // the caller's all-reduces sit between phases 0 | 1..4 | 5
+      REQ(row_sums);
+      if (!((phase_lo == 0 && phase_hi == 0) || (phase_lo == 1 && phase_hi == 4) || (phase_lo == 5 && phase_hi == 5)))
+        return DLAP_E_SHAPE;
+    }
   }
   REQ(mask); REQ(R); REQ(row_stats); REQ(scalars); REQ(col_part); REQ(bar);
   if (reinterpret_cast<uintptr_t>(bar) & 3) return DLAP_E_ALIGN;
@@ -298,7 +308,8 @@ int dlap_step_reduce(const dlap_plan* plan, const float* u, const float* q, cons
   if (phase_hi >= 3) { REQ(e); REQ(t_i); REQ(G); REQ(loss_part); }
   CU(launch_step_reduce_c(plan, u, q, R, mask, index, weighted_loss, flags, n_bar_in, phase_lo, phase_hi, row_stats, pr,
                           scalars, w_out, col_part, e, t_i, G, loss_part, dS2, row_part, bar, xbuf, T_series, month0,
-                          month_stride, row_sums, n_stocks_total, (cudaStream_t)stream));
+                          month_stride, row_sums, n_stocks_total, (peers && peers->world > 1) ? peers : nullptr,
+                          (cudaStream_t)stream));
   return DLAP_OK;
 }
 

@@ -54,6 +54,12 @@ struct ReduceParams {
   // caller); phase 5 turns those two into L_c and L_u.
   int stock_shard;
   double* row_sums;
+  // stock shards over peer memory (NVLink): every rank's partial sums sit in a buffer all ranks can address,
+  // peer[r] = rank r's, laid out as doubles [4 T | 2 T + 2] and then 2 x 8 uint32 flags.  The two all-reduces become
+  // "write mine, barrier across the GPUs, add everybody's in rank order" inside this one launch (phases 0..5).
+  int world, rank, Tcap;     // Tcap: months the buffers were laid out for (>= T)
+  double* peer[8];
+  unsigned int* epoch;       // launches so far (device, this rank's own): the value the flags are raised to
   int phase_lo, phase_hi;    // inclusive
 };
 
@@ -86,6 +92,35 @@ __device__ __forceinline__ void block_sum4(double (&v)[4], double* red /* [4][8]
     v[k] = s;
   }
 }
+// Barrier across the GPUs of a stock-sharded step, called by CTA 0 between two grid barriers: slot `b` of every
+// peer's flag block gets this launch's number from this rank, then this rank waits for everybody's.  Flags only ever
+// grow, so a rank that is one launch ahead cannot be mistaken for one that has arrived.  A peer that never shows up
+// (its process died) turns into a trap after 2 s instead of a hang.
+__device__ __forceinline__ void peer_barrier(const ReduceParams& P, int b, unsigned int value) {
+  const int r = threadIdx.x;
+  if (r < P.world) {
+    const size_t flag_off = (size_t)(6 * P.Tcap + 2) * sizeof(double) + (size_t)b * 8 * sizeof(unsigned int);
+    __threadfence_system();
+    unsigned int* theirs = reinterpret_cast<unsigned int*>(reinterpret_cast<char*>(P.peer[r]) + flag_off) + P.rank;
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(theirs), "r"(value) : "memory");
+    const unsigned int* mine = reinterpret_cast<const unsigned int*>(reinterpret_cast<const char*>(P.peer[P.rank]) + flag_off) + r;
+    unsigned int v;
+    unsigned long long t0 = 0;
+    for (;;) {
+      asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(mine) : "memory");
+      if ((int)(v - value) >= 0) break;
+      unsigned long long now;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+      if (t0 == 0) t0 = now;
+      else if (now - t0 > 2000000000ull) __trap();
+    }
+  }
+}
+__device__ __forceinline__ double ld_peer(const double* p) {
+  double v;
+  asm volatile("ld.relaxed.sys.global.f64 %0, [%1];" : "=d"(v) : "l"(p) : "memory");
+  return v;
+}
 }  // namespace
 
 __global__ void __launch_bounds__(RT, 4) step_reduce_kernel(const ReduceParams P) {
@@ -95,6 +130,8 @@ __global__ void __launch_bounds__(RT, 4) step_reduce_kernel(const ReduceParams P
   const int T = P.T, N = P.N;
   const size_t plane = (size_t)T * N;
   unsigned int nsync = 0;
+  const bool peers = P.stock_shard && P.world > 1;
+  const unsigned int launch_no = peers ? __ldcg(P.epoch) + 1u : 0u;
 
   // ---------------------------------------------------------------- phase 0: row sums
   // A month is cut into nseg segments of its cells so that every CTA has work; the CTA that finishes a month's
@@ -145,8 +182,8 @@ __global__ void __launch_bounds__(RT, 4) step_reduce_kernel(const ReduceParams P
             atomicExch(P.bar + 1 + t, 0u);
           }
         }
-        if (last && P.stock_shard) {             // partial sums of this rank's stocks: the caller all-reduces them
-          double* o = P.row_sums + (size_t)t * 4;
+        if (last && P.stock_shard) {             // partial sums of this rank's stocks: all-reduced by the caller, or
+          double* o = (peers ? P.peer[P.rank] : P.row_sums) + (size_t)t * 4;       // added up over peer memory below
           o[0] = v[0]; o[1] = v[1]; o[2] = v[2]; o[3] = v[3];
         } else if (last) {
           const double nt = fmax(v[0], 1.0);
@@ -165,9 +202,23 @@ __global__ void __launch_bounds__(RT, 4) step_reduce_kernel(const ReduceParams P
 
   // ---------------------------------------------------------------- phase 1: N_bar, S_t; column partial sums
   if (P.phase_lo <= 1 && P.phase_hi >= 1) {
-    if (P.stock_shard && P.phase_lo == 1) {       // the months' sums over ALL stocks are in: row_stats from them
+    if (peers) {                                  // everybody's partial sums are written: barrier across the GPUs
+      if (blockIdx.x == 0) peer_barrier(P, 0, launch_no);
+      grid_sync(P.bar, ++nsync);
+    }
+    if (P.stock_shard && (P.phase_lo == 1 || peers)) {     // the months' sums over ALL stocks: row_stats from them
       for (int t = blockIdx.x * RT + tid; t < T; t += gridDim.x * RT) {
-        const double* v = P.row_sums + (size_t)t * 4;
+        double v[4];
+        if (peers) {
+          v[0] = v[1] = v[2] = v[3] = 0.0;
+          for (int r = 0; r < P.world; ++r) {            // rank order: every rank gets the same bits
+            const double* q = P.peer[r] + (size_t)t * 4;
+            v[0] += ld_peer(q); v[1] += ld_peer(q + 1); v[2] += ld_peer(q + 2); v[3] += ld_peer(q + 3);
+          }
+        } else {
+          const double* q = P.row_sums + (size_t)t * 4;
+          v[0] = q[0]; v[1] = q[1]; v[2] = q[2]; v[3] = q[3];
+        }
         const double nt = fmax(v[0], 1.0);
         const float mu = P.no_demean ? 0.f : (float)(v[1] / nt);
         float* rs = P.row_stats + (size_t)t * RS_W;
@@ -336,7 +387,8 @@ __global__ void __launch_bounds__(RT, 4) step_reduce_kernel(const ReduceParams P
       a = block_sum(a, red);
       b = block_sum(b, red);
       if (tid == 0 && P.stock_shard) {       // this rank's stocks only: the sums travel behind the dS sums
-        P.dS2[2 * (size_t)T] = a; P.dS2[2 * (size_t)T + 1] = b;
+        double* ds = peers ? P.peer[P.rank] + 4 * (size_t)P.Tcap : P.dS2;
+        ds[2 * (size_t)T] = a; ds[2 * (size_t)T + 1] = b;
       } else if (tid == 0) {
         // means run over ALL columns, dead ones included (src/model.py:385)
         P.scalars[SC_LC] = (float)(a / ((double)KM * (double)P.n_total));
@@ -395,18 +447,35 @@ __global__ void __launch_bounds__(RT, 4) step_reduce_kernel(const ReduceParams P
               atomicExch(P.bar + 1 + t, 0u);
             }
           }
-          if (last) { P.dS2[2 * t] = v[0]; P.dS2[2 * t + 1] = v[1]; }
+          if (last) {
+            double* ds = peers ? P.peer[P.rank] + 4 * (size_t)P.Tcap : P.dS2;
+            ds[2 * t] = v[0]; ds[2 * t + 1] = v[1];
+          }
         }
       }
     }
   }
   // ---------------------------------------------------------------- phase 5 (stock shards): L_c, L_u
-  if (P.phase_lo <= 5 && P.phase_hi >= 5 && P.stock_shard && blockIdx.x == 0 && tid == 0) {
+  if (peers && P.phase_hi >= 5) {                 // the second exchange: dS sums and sums of e^2, over peer memory
+    grid_sync(P.bar, ++nsync);
+    if (blockIdx.x == 0) peer_barrier(P, 1, launch_no);
+    grid_sync(P.bar, ++nsync);
+    for (int i = blockIdx.x * RT + tid; i < 2 * T + 2; i += gridDim.x * RT) {
+      double v = 0.0;
+      for (int r = 0; r < P.world; ++r) v += ld_peer(P.peer[r] + 4 * (size_t)P.Tcap + i);
+      P.dS2[i] = v;
+      if (i == 2 * T) P.scalars[SC_LC] = (float)(v / ((double)KM * (double)P.n_total));
+      if (i == 2 * T + 1) P.scalars[SC_LU] = (float)(v / (double)P.n_total);
+    }
+  } else if (P.phase_lo <= 5 && P.phase_hi >= 5 && P.stock_shard && blockIdx.x == 0 && tid == 0) {
     P.scalars[SC_LC] = (float)(P.dS2[2 * (size_t)T] / ((double)KM * (double)P.n_total));
     P.scalars[SC_LU] = (float)(P.dS2[2 * (size_t)T + 1] / (double)P.n_total);
   }
+  if (peers && blockIdx.x == 0 && tid == 0) *P.epoch = launch_no;      // read by every CTA at its start, long ago
   grid_exit(P.bar, nsync);
 }
+
+static bool peers_in_use(const ReduceParams& P) { return P.stock_shard && P.world > 1; }
 
 // co-resident CTAs of the kernel on `device` with `sms` SMs in use and this much dynamic shared memory
 static int reduce_ctas_per_sm(size_t smem) {
@@ -425,7 +494,7 @@ cudaError_t launch_step_reduce(ReduceParams P, int sms, bool cooperative, cudaSt
   if (per_sm < 1) return cudaErrorLaunchOutOfResources;
   if (per_sm > 4) per_sm = 4;
   // no more CTAs than any phase has work for
-  if (P.phase_lo == 5) {          // two divisions
+  if (P.phase_lo == 5 && !peers_in_use(P)) {          // two divisions
     step_reduce_kernel<<<1, RT, smem, st>>>(P);
     return cudaGetLastError();
   }
@@ -453,8 +522,12 @@ cudaError_t launch_step_reduce_c(const dlap_plan* plan, const float* u, const fl
                                  float* row_stats, float* pr, float* scalars, float* w_out, double* col_part, float* e,
                                  float* t_i, float* G, double* loss_part, double* dS2, double* row_part,
                                  unsigned int* bar, float* xbuf, int T_series, int month0, int month_stride,
-                                 double* row_sums, int n_total, cudaStream_t st) {
+                                 double* row_sums, int n_total, const dlap_peers* peers, cudaStream_t st) {
   ReduceParams P{};
+  if (peers) {
+    P.world = peers->world; P.rank = peers->rank; P.epoch = peers->epoch; P.Tcap = peers->months;
+    for (int r = 0; r < peers->world && r < 8; ++r) P.peer[r] = static_cast<double*>(peers->buf[r]);
+  }
   P.stock_shard = (flags & DLAP_REDUCE_STOCK_SHARD) != 0; P.row_sums = row_sums;
   P.row_part = row_part;
   P.xbuf = xbuf; P.T_series = T_series; P.month0 = month0; P.month_stride = month_stride;

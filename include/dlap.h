@@ -114,6 +114,18 @@ typedef struct dlap_macro_io {
   int32_t* sync;
 } dlap_macro_io;
 
+/* Stock shards on GPUs that can address each other's memory (NVLink / NVSwitch; torch: symmetric memory).  buf[r]:
+ * rank r's exchange buffer as THIS device addresses it, (6 months + 2) doubles followed by 16 uint32 (months: the
+ * capacity the buffers were laid out for, >= the plan's T), all zero before the first call; epoch: one zero-initialised uint32 in this rank's own memory.  dlap_step_reduce then does its two
+ * exchanges inside its one launch: every rank writes its partial sums into its own buffer, a flag barrier across the
+ * GPUs, and every rank adds everybody's sums in rank order (so all ranks hold the same bits).  All ranks must make
+ * the same calls in the same order; a rank that waits for more than 2 s for a peer traps. */
+typedef struct dlap_peers {
+  int32_t world, rank, months; /* 2 .. 8 ranks */
+  void* buf[8];
+  uint32_t* epoch;
+} dlap_peers;
+
 int dlap_abi_version(void);
 const char* dlap_error_string(int code);
 
@@ -196,7 +208,8 @@ int dlap_cell_fwd(const dlap_plan* plan, const float* x, const uint8_t* mask, co
  * between.  Phases 0..0 leave the months' raw sums in row_sums (double [T,4]: count, sum u, sum u R, sum R); the
  * caller sum-all-reduces it; phases 1..4 turn it into row_stats and go on as usual with n_stocks_total stocks in
  * the loss means, and leave the sums of e^2 behind the dS sums: dS2 is double [T,2] + [2] (required); the caller
- * sum-all-reduces it; phase 5 writes L_c and L_u.
+ * sum-all-reduces it; phase 5 writes L_c and L_u.  With `peers` (see dlap_peers) ONE call for phases 0..5 does it all,
+ * the two exchanges over peer memory; row_sums is then not used and dS2 is an output only.
  * Single device: phases 0..4 in one launch.  q may be NULL (phase 'unconditional').  index: the valid-cell index
  * when u and q come from the BF16X3 dlap_cell_fwd, NULL for FP32.  row_part: scratch (row_part_bytes; NULL: the
  * per-month phases run one CTA per month).  bar (device, bar_bytes, all zero when the call starts and all zero
@@ -208,7 +221,8 @@ int dlap_step_reduce(const dlap_plan* plan, const float* u, const float* q, cons
                      const int32_t* index, int weighted_loss, int flags, const float* n_bar_in, int phase_lo, int phase_hi,
                      float* row_stats, float* pr, float* scalars, float* w_out, double* col_part, float* e,
                      float* t_i, float* G, double* loss_part, double* dS2, double* row_part, uint32_t* bar,
-                     const dlap_macro_io* series, float* xbuf, double* row_sums, int n_stocks_total, void* stream);
+                     const dlap_macro_io* series, float* xbuf, double* row_sums, int n_stocks_total,
+                     const dlap_peers* peers, void* stream);
 
 /* The loss stage on its own, for a caller that holds per-stock sums from elsewhere: e_ki = colsum / T_i,
  * L_c = mean_k mean_i e_ki^2, L_u = mean_i e0_i^2 (src/model.py:382-385, :428-431) -> e [9,N], t_i [N],

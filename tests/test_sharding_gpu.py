@@ -66,7 +66,10 @@ def _worker(rank, world, port, precision, layout, out_q, backend="gloo"):
                                  "b200_precision": precision}).to(dev)
         if layout == "stocks":
             mine = _stocks(rank, N)
-            model.month_shard = Fn.StockShard(None, N)
+            # NCCL, one rank per GPU: both forward exchanges run inside the reduction kernel over peer memory
+            model.month_shard = (Fn.make_stock_shard(None, N, T, dev) if backend == "nccl" else Fn.StockShard(None, N))
+            if backend == "nccl":
+                assert model.month_shard.peers is not None
             panel = (macro.to(dev), x[:, mine].contiguous().to(dev), R[:, mine].contiguous().to(dev),
                      mask[:, mine].contiguous().to(dev))
         else:
@@ -94,6 +97,10 @@ def _worker(rank, world, port, precision, layout, out_q, backend="gloo"):
                "pr": out["portfolio_returns"].detach().cpu().numpy(), "w": out["weights"].detach().cpu().numpy(),
                "grads": {k: p.grad.cpu().numpy() for k, p in model.named_parameters()}}
         out_q.put((rank, res))
+        if backend == "nccl" and layout == "stocks":      # tearing the group down hangs with symmetric memory alive
+            out_q.close(); out_q.join_thread()
+            torch.cuda.synchronize()
+            os._exit(0)
     except Exception as exc:  # pragma: no cover
         import traceback
         out_q.put((rank, "ERR " + traceback.format_exc()))
