@@ -68,7 +68,7 @@ class DlapAdamTensors(C.Structure):
 
 class DlapPeers(C.Structure):
     """dlap_peers: every rank's exchange buffer as this device addresses it (stock shards over NVLink peer memory)."""
-    _fields_ = [("world", C.c_int32), ("rank", C.c_int32), ("months", C.c_int32), ("buf", C.c_void_p * 8),
+    _fields_ = [("world", C.c_int32), ("rank", C.c_int32), ("capacity", C.c_int32), ("buf", C.c_void_p * 8),
                 ("epoch", C.c_void_p)]
 
 
@@ -92,7 +92,7 @@ SIGNATURES = {
     "dlap_cell_bwd": (_PLAN, _P, _P, _P, _P, _TENS, _MIO, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _P, _P, _I,
                       C.c_float, C.c_uint64, _P, _P),
     "dlap_grad_finish": (_PLAN, _P, _P, _P, _I, _I, _I, _TENS, _P, _I, _P),
-    "dlap_macro_bwd": (_PLAN, _P, _TENS, _P, _P, _P, _P, _P, _I, _I, _TENS, _P, _P, _P, _I, _P, _P),
+    "dlap_macro_bwd": (_PLAN, _P, _TENS, _P, _P, _P, _P, _P, _I, _I, _TENS, _P, _P, _P, _I, _P, C.POINTER(DlapPeers), _P),
     "dlap_weights": (_PLAN, _P, _P, _P, _I, _I, _P, _P),
     "dlap_clip_adam": (C.POINTER(DlapAdamTensors), C.c_float, C.c_float, C.c_float, C.c_float, C.c_float, _P, _P),
     "dlap_debug_timeline": (_P,),

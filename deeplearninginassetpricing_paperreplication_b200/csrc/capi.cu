@@ -281,7 +281,7 @@ int dlap_step_reduce(const dlap_plan* plan, const float* u, const float* q, cons
     REQ(dS2);
     if (xbuf || n_stocks_total < plan->dims.N) return DLAP_E_SHAPE;
     if (peers && peers->world > 1) {        // both exchanges inside the one launch
-      if (peers->world > 8 || peers->rank < 0 || peers->rank >= peers->world || peers->months < plan->dims.T)
+      if (peers->world > 8 || peers->rank < 0 || peers->rank >= peers->world || peers->capacity < plan->dims.T)
         return DLAP_E_SHAPE;
       REQ(peers->epoch);
       for (int r = 0; r < peers->world; ++r) REQ(peers->buf[r]);
@@ -393,7 +393,7 @@ int dlap_grad_finish(const dlap_plan* plan, const float* wpart, const float* dad
 int dlap_macro_bwd(const dlap_plan* plan, const float* macro, const dlap_tensors* params, const float* h0,
                    const float* c0, const float* lstm_save, float* dadc, float* dpre, int want_sdf, int want_mom,
                    const dlap_tensors* grads, const float* wpart, const float* dadc_part, const int32_t* index,
-                   int precision, uint32_t* counter, void* stream) {
+                   int precision, uint32_t* counter, const dlap_peers* peers, void* stream) {
   int rc = check_plan(plan);
   if (rc) return rc;
   REQ(params); REQ(dadc); REQ(grads);
@@ -414,6 +414,16 @@ int dlap_macro_bwd(const dlap_plan* plan, const float* macro, const dlap_tensors
     REQ(counter);
     if (reinterpret_cast<uintptr_t>(counter) & 3) return DLAP_E_ALIGN;
     F.counter = counter; F.cooperative = plan->cooperative;
+    if (peers && peers->world > 1) {
+      if (!wpart || !dadc_part) return DLAP_E_NULL;
+      if (peers->world > 8 || peers->rank < 0 || peers->rank >= peers->world || peers->capacity < 1) return DLAP_E_SHAPE;
+      if (!(want_sdf && plan->dims.M > 0)) return DLAP_E_SHAPE;      // the exchange lives in the BPTT kernel
+      REQ(peers->epoch);
+      F.world = peers->world; F.rank = peers->rank; F.gcap = peers->capacity; F.gepoch = peers->epoch;
+      for (int r = 0; r < peers->world; ++r) { REQ(peers->buf[r]); F.gpeer[r] = static_cast<float*>(peers->buf[r]); }
+    }
+  } else if (peers && peers->world > 1) {
+    return DLAP_E_NULL;
   }
   MacroParams P;
   fill_macro(P, plan, plan->dims.T, macro, params, h0, c0);

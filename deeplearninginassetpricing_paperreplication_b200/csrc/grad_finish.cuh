@@ -14,11 +14,18 @@ struct FinishParams {
   float* dadc; int dadc_stride;            // row t of this panel goes to row t * dadc_stride of dadc
   // BPTT kernel only (macro_lstm.cu): CTAs that sum da_t | dc_t elements count themselves off here
   unsigned int* counter; int dadc_ctas; int cooperative;
+  // stock shards over peer memory (BPTT kernel only): the sums of this rank's partials are this rank's share; every
+  // rank writes its shares into gpeer[rank] (two halves of gcap floats, used alternately, then 8 uint32 flags), a flag
+  // barrier across the GPUs, and every rank adds everybody's shares in rank order.  gepoch[0]: launches so far,
+  // gepoch[1]: the "go" word the summing CTAs wait on.
+  int world, rank, gcap, nfin;
+  float* gpeer[8];
+  unsigned int* gepoch;
 };
 
 // element idx < wp_stride(round4(F)) of the per-CTA weight-gradient partials, summed over the CTAs
-__device__ __forceinline__ void finish_wpart(const FinishParams& P, int idx) {
-  const int Fr = round4(P.F), stride = wp_stride(Fr), ncta = P.ncta, F = P.F;
+__device__ __forceinline__ float wpart_sum(const FinishParams& P, int idx) {
+  const int Fr = round4(P.F), stride = wp_stride(Fr), ncta = P.ncta;
   // four running sums (CTAs c = u mod 4, ascending), sixteen loads in flight: one L2 round trip per batch of loads
   float v4[4] = {0.f, 0.f, 0.f, 0.f};
   int c = 0;
@@ -34,7 +41,11 @@ __device__ __forceinline__ void finish_wpart(const FinishParams& P, int idx) {
     for (int u = 0; u < 4; ++u) v4[u] += P.wpart[(size_t)(c + u) * stride + idx];
   }
   for (; c < ncta; ++c) v4[0] += P.wpart[(size_t)c * stride + idx];
-  const float v = (v4[0] + v4[1]) + (v4[2] + v4[3]);
+  return (v4[0] + v4[1]) + (v4[2] + v4[3]);
+}
+// ... and stored where the reference keeps that gradient
+__device__ __forceinline__ void wpart_store(const FinishParams& P, int idx, float v) {
+  const int Fr = round4(P.F), F = P.F;
   if (idx < wp_off_w1()) {
     if (P.have_sdf) P.gW2[idx] = v;
   } else if (idx < wp_off_wq(Fr)) {
@@ -51,9 +62,10 @@ __device__ __forceinline__ void finish_wpart(const FinishParams& P, int idx) {
   // d b3 = sum du = dP_t * sum m (R - Rbar_t) = 0 identically (demeaning, src/model.py:279)
   if (idx == 0 && P.have_sdf) P.gb3[0] = 0.f;
 }
+__device__ __forceinline__ void finish_wpart(const FinishParams& P, int idx) { wpart_store(P, idx, wpart_sum(P, idx)); }
 
-// element r < T * 72 of da_t | dc_t, summed over the month's partial slots; returns the sum (also stored)
-__device__ __forceinline__ float finish_dadc(const FinishParams& P, int r) {
+// element r < T * 72 of da_t | dc_t, summed over the month's partial slots
+__device__ __forceinline__ float dadc_sum(const FinishParams& P, int r) {
   const int t = r / 72, c = r % 72;
   int tpm = P.tpm;
   float v8[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
@@ -69,9 +81,11 @@ __device__ __forceinline__ float finish_dadc(const FinishParams& P, int r) {
     for (int u = 0; u < 8; ++u) v8[u] += p[(size_t)(j + u) * 72];
   }
   for (; j < tpm; ++j) v8[0] += p[(size_t)j * 72];
-  const float v = ((v8[0] + v8[1]) + (v8[2] + v8[3])) + ((v8[4] + v8[5]) + (v8[6] + v8[7]));
-  P.dadc[(size_t)t * P.dadc_stride * 72 + c] = v;
-  return v;
+  return ((v8[0] + v8[1]) + (v8[2] + v8[3])) + ((v8[4] + v8[5]) + (v8[6] + v8[7]));
 }
+__device__ __forceinline__ void dadc_store(const FinishParams& P, int r, float v) {
+  P.dadc[(size_t)(r / 72) * P.dadc_stride * 72 + r % 72] = v;
+}
+__device__ __forceinline__ void finish_dadc(const FinishParams& P, int r) { dadc_store(P, r, dadc_sum(P, r)); }
 
 }  // namespace dlap

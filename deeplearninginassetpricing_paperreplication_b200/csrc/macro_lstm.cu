@@ -36,14 +36,59 @@ __global__ void __launch_bounds__(MT, 1) macro_fwd_kernel(const MacroParams P) {
 // partials and the da_t | dc_t partials of every month (grad_finish.cuh) and count themselves off in *FIN.counter;
 // the LAST CTA is the recurrence: it stages its tables, waits until the da_t | dc_t rows are complete (the grid is
 // co-resident: a cooperative launch, ~50 CTAs), and puts the counter back to zero.
+//
+// Stock shards over peer memory (FIN.world > 1): what the summing CTAs compute is only this rank's share.  They write
+// it into this rank's exchange buffer and count off; the recurrence's CTA waits for all of them, raises this launch's
+// flag at every peer and waits for everybody's (the backward pass' one exchange), then releases the summing CTAs,
+// which add all ranks' shares in rank order and store the result; the da_t | dc_t ones count off a second time.
+__device__ __forceinline__ float ld_peer_f32(const float* p) {
+  float v;
+  asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void spin_until(const unsigned int* word, unsigned int value, bool sys) {
+  unsigned int v;
+  unsigned long long t0 = 0;
+  for (;;) {
+    if (sys) asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(word) : "memory");
+    else asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(word) : "memory");
+    if ((int)(v - value) >= 0) return;
+    unsigned long long now;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+    if (t0 == 0) t0 = now;
+    else if (now - t0 > 2000000000ull) __trap();      // a peer (or a CTA) that never shows up: no hang
+  }
+}
+
 template <int H>
 __global__ void __launch_bounds__(MT, 1) macro_bptt_kernel(const MacroParams P, const FinishParams FIN) {
   extern __shared__ float sm[];
+  const bool peers = FIN.world > 1;
+  const unsigned int launch_no = peers ? __ldcg(FIN.gepoch) + 1u : 0u;
   if (blockIdx.x + 1 < gridDim.x) {
     const int stride = wp_stride(round4(FIN.F));
     const int idx = blockIdx.x * MT + threadIdx.x;
-    if (idx < stride) finish_wpart(FIN, idx);
-    else if (idx - stride < FIN.T * 72) finish_dadc(FIN, idx - stride);
+    if (peers) {
+      float* mine = FIN.gpeer[FIN.rank] + (size_t)(launch_no & 1u) * FIN.gcap;
+      const bool w = idx < stride, d = !w && idx - stride < FIN.T * 72;
+      if (w) mine[idx] = wpart_sum(FIN, idx);
+      else if (d) mine[idx] = dadc_sum(FIN, idx - stride);
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        __threadfence();
+        atomicAdd(FIN.counter, 1u);
+        spin_until(FIN.gepoch + 1, launch_no, false);          // every rank's shares are in place
+      }
+      __syncthreads();
+      if (w || d) {
+        float v = 0.f;
+        for (int r = 0; r < FIN.world; ++r) v += ld_peer_f32(FIN.gpeer[r] + (size_t)(launch_no & 1u) * FIN.gcap + idx);
+        if (w) wpart_store(FIN, idx, v); else dadc_store(FIN, idx - stride, v);
+      }
+    } else {
+      if (idx < stride) finish_wpart(FIN, idx);
+      else if (idx - stride < FIN.T * 72) finish_dadc(FIN, idx - stride);
+    }
     if ((int)(blockIdx.x + 1) * MT > stride) {            // this CTA wrote da_t | dc_t elements
       __syncthreads();
       if (threadIdx.x == 0) { __threadfence(); atomicAdd(FIN.counter, 1u); }
@@ -61,12 +106,29 @@ __global__ void __launch_bounds__(MT, 1) macro_bptt_kernel(const MacroParams P, 
   for (int i = tid; i < T * 6 * H; i += MT) sv_s[i] = P.save[i];
   for (int i = tid; i < D1 * H; i += MT) w1m[i] = __ldg(P.W1 + (size_t)(i / H) * P.ldw1 + P.F + (i % H));
   for (int i = tid; i < G4 * H; i += MT) whh[i] = __ldg(P.Whh + i);
+  if (peers) {
+    if (tid == 0) {                                         // every summing CTA has written this rank's shares
+      spin_until(FIN.counter, (unsigned int)FIN.nfin, false);
+      atomicExch(FIN.counter, 0u);
+    }
+    __syncthreads();
+    if (tid < FIN.world) {                                  // the exchange: raise our flag at every peer, wait for theirs
+      unsigned int* flags_theirs = reinterpret_cast<unsigned int*>(FIN.gpeer[tid] + 2 * (size_t)FIN.gcap) + FIN.rank;
+      const unsigned int* flags_mine = reinterpret_cast<const unsigned int*>(FIN.gpeer[FIN.rank] + 2 * (size_t)FIN.gcap) + tid;
+      __threadfence_system();
+      asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(flags_theirs), "r"(launch_no) : "memory");
+      spin_until(flags_mine, launch_no, true);
+    }
+    __syncthreads();
+    if (tid == 0) {
+      __threadfence();
+      asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(FIN.gepoch + 1), "r"(launch_no) : "memory");
+    }
+  }
   if (FIN.dadc_part && tid == 0) {                          // the da_t | dc_t rows are being summed by the other CTAs
-    unsigned int v;
-    do {
-      asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(FIN.counter) : "memory");
-    } while (v < (unsigned int)FIN.dadc_ctas);
+    spin_until(FIN.counter, (unsigned int)FIN.dadc_ctas, false);
     atomicExch(FIN.counter, 0u);
+    if (peers) *FIN.gepoch = launch_no;
   }
   __syncthreads();
   // pass 1, thread = (month, unit): dhe_t = W1[:,F:]^T . da_t and the local derivatives
@@ -297,6 +359,8 @@ static cudaError_t launch_bptt_h(const MacroParams& P, const FinishParams& FIN, 
     const int stride = wp_stride(round4(FIN.F)), total = stride + FIN.T * 72;
     extra = (total + MT - 1) / MT;
     F2.dadc_ctas = extra - stride / MT;                     // CTAs whose range reaches past the weight partials
+    F2.nfin = extra;
+    if (F2.world > 1 && total > F2.gcap) return cudaErrorInvalidValue;
   }
   if (extra > 0 && FIN.cooperative) {
     void* args[] = {(void*)&P, (void*)&F2};

@@ -525,7 +525,7 @@ cudaError_t launch_step_reduce_c(const dlap_plan* plan, const float* u, const fl
                                  double* row_sums, int n_total, const dlap_peers* peers, cudaStream_t st) {
   ReduceParams P{};
   if (peers) {
-    P.world = peers->world; P.rank = peers->rank; P.epoch = peers->epoch; P.Tcap = peers->months;
+    P.world = peers->world; P.rank = peers->rank; P.epoch = peers->epoch; P.Tcap = peers->capacity;
     for (int r = 0; r < peers->world && r < 8; ++r) P.peer[r] = static_cast<double*>(peers->buf[r]);
   }
   P.stock_shard = (flags & DLAP_REDUCE_STOCK_SHARD) != 0; P.row_sums = row_sums;

@@ -263,10 +263,24 @@ class PeerExchange:
         self.handle.barrier()
         torch.cuda.synchronize(device)
         self.c = _lib.DlapPeers()
-        self.c.world, self.c.rank, self.c.months = self.handle.world_size, self.handle.rank, self.T_max
+        self.c.world, self.c.rank, self.c.capacity = self.handle.world_size, self.handle.rank, self.T_max
         for r, ptr in enumerate(self.handle.buffer_ptrs):
             self.c.buf[r] = ptr
         self.c.epoch = self.epoch.data_ptr()
+        # the backward pass' exchange (dlap_macro_bwd): per-cell weight gradients + every month's da_t | dc_t row
+        self.gcap = 64 * 64 + 72 * 64 + 128 + 72 * self.T_max
+        self.gbuf = symm.empty(2 * self.gcap + 8, dtype=torch.float32, device=device)
+        self.gbuf.zero_()
+        self.ghandle = symm.rendezvous(self.gbuf, group if group is not None else dist.group.WORLD)
+        self.gepoch = torch.zeros(2, dtype=torch.int32, device=device)
+        torch.cuda.synchronize(device)
+        self.ghandle.barrier()
+        torch.cuda.synchronize(device)
+        self.g = _lib.DlapPeers()
+        self.g.world, self.g.rank, self.g.capacity = self.ghandle.world_size, self.ghandle.rank, self.gcap
+        for r, ptr in enumerate(self.ghandle.buffer_ptrs):
+            self.g.buf[r] = ptr
+        self.g.epoch = self.gepoch.data_ptr()
 
 
 def make_stock_shard(group, n_total: int, T: int, device, peer_memory: bool = True) -> StockShard:
@@ -520,6 +534,8 @@ class GanStepFn(torch.autograd.Function):
         sh = opts.shard
         if (tables or q_in is not None) and sh is not None:
             raise NotImplementedError("shards with caller-made bias tables / moment outputs")
+        if isinstance(sh, StockShard) and not opts.demean:
+            raise NotImplementedError("stock shards with normalize_w=False")
         want_backward = any(ctx.needs_input_grad)
         kernel_moments = opts.need_moments and q_in is None
         with torch.cuda.device(dev):
@@ -588,8 +604,10 @@ class GanStepFn(torch.autograd.Function):
                 # ONE all-reduce over it -- gradients that are computed later (LSTM, b1, bq) are still zero.
                 # Otherwise no fill: the kernels write every element of every gradient that is handed back.
                 sizes = [0 if p is None else p.numel() for p in params]
-                head = T_rows * 72
-                buf = (torch.empty if sh is None else torch.zeros)(head + sum(sizes), dtype=torch.float32, device=dev)
+                peer_bwd = stocks and sh.peers is not None and want_sdf and M > 0
+                head = 0 if peer_bwd else T_rows * 72
+                buf = (torch.empty if (sh is None or peer_bwd) else torch.zeros)(head + sum(sizes), dtype=torch.float32,
+                                                                                device=dev)
                 flat_g = buf[head:]
                 grads, off = [], 0
                 for p, n in zip(params, sizes):
@@ -603,11 +621,13 @@ class GanStepFn(torch.autograd.Function):
                     ws.launches += 1
                     grad_a = dadc[:, :64] if (need_a and want_sdf) else None
                     grad_c = dadc[:, 64:] if (need_c and want_mom) else None
-                elif sh is None:
+                elif sh is None or (stocks and sh.peers is not None and want_sdf and M > 0):
+                    # one device -- or stock shards over peer memory: the exchange is inside the BPTT kernel
                     dadc = torch.empty(T, 72, dtype=torch.float32, device=dev)
                     _timed_call("dlap_macro_bwd", dev, ws.pp, _ptr(macro), C.byref(tens), _ptr(h0), _ptr(c0), _ptr(save),
                                 _ptr(dadc), _ptr(ws.dpre), int(want_sdf), int(want_mom), C.byref(gt), _ptr(ws.wpart),
-                                _ptr(ws.dadc_part), _ptr(index), prec, _ptr(ws.counter), st)
+                                _ptr(ws.dadc_part), _ptr(index), prec, _ptr(ws.counter),
+                                C.byref(sh.peers.g) if sh is not None else None, st)
                     ws.launches += 2
                 else:   # exchange 2: per-cell weight grads + every month's da_t | dc_t row
                     dadc_all = buf[:head].view(T_rows, 72)
@@ -621,7 +641,7 @@ class GanStepFn(torch.autograd.Function):
                         torch.distributed.all_reduce(buf, group=sh.group)
                     _timed_call("dlap_macro_bwd", dev, wsm.pp, _ptr(macro), C.byref(tens), _ptr(h0), _ptr(c0),
                                 _ptr(save), _ptr(dadc_all), _ptr(wsm.dpre), int(want_sdf), int(want_mom), C.byref(gt),
-                                None, None, None, prec, None, st)
+                                None, None, None, prec, None, None, st)
                     ws.launches += 3 if (want_sdf and M > 0) else 2
                 if not opts.demean and want_sdf and sh is None and grads[9] is not None:
                     grads[9].copy_(_bias3_grad(opts, row_stats, scalars, dS2, g_lc if has_q or q_given else None, g_lu, g_pr))

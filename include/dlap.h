@@ -114,14 +114,19 @@ typedef struct dlap_macro_io {
   int32_t* sync;
 } dlap_macro_io;
 
-/* Stock shards on GPUs that can address each other's memory (NVLink / NVSwitch; torch: symmetric memory).  buf[r]:
- * rank r's exchange buffer as THIS device addresses it, (6 months + 2) doubles followed by 16 uint32 (months: the
- * capacity the buffers were laid out for, >= the plan's T), all zero before the first call; epoch: one zero-initialised uint32 in this rank's own memory.  dlap_step_reduce then does its two
- * exchanges inside its one launch: every rank writes its partial sums into its own buffer, a flag barrier across the
- * GPUs, and every rank adds everybody's sums in rank order (so all ranks hold the same bits).  All ranks must make
- * the same calls in the same order; a rank that waits for more than 2 s for a peer traps. */
+/* Stock shards on GPUs that can address each other's memory (NVLink / NVSwitch; torch: symmetric memory): the
+ * exchanges of a step happen INSIDE the kernels instead of in collectives between them.  Every rank writes its
+ * partial sums into its own exchange buffer, raises a flag at every peer and waits for everybody's (flags carry the
+ * launch number and only ever grow), then adds all ranks' partial sums in rank order -- so every rank holds the same
+ * bits.  buf[r]: rank r's exchange buffer as THIS device addresses it, all zero before the first call; epoch: zero-
+ * initialised uint32 words in this rank's own memory.  All ranks must make the same calls in the same order; a rank
+ * that waits more than 2 s for a peer traps.  One dlap_peers per entry point:
+ *   dlap_step_reduce  buf: (6 capacity + 2) doubles then 16 uint32, capacity >= the plan's T months; epoch: 1 word;
+ *   dlap_macro_bwd    buf: 2 capacity floats then 8 uint32, capacity >= the number of gradient elements the per-cell
+ *                     kernel leaves (64*64 + 72*round4(F) + 128 + 72 T); epoch: 2 words.
+ * (TMA multicast is not involved: plain loads and stores to peer addresses.) */
 typedef struct dlap_peers {
-  int32_t world, rank, months; /* 2 .. 8 ranks */
+  int32_t world, rank, capacity;   /* 2 .. 8 ranks */
   void* buf[8];
   uint32_t* epoch;
 } dlap_peers;
@@ -280,11 +285,13 @@ int dlap_grad_finish(const dlap_plan* plan, const float* wpart, const float* dad
  * per-cell plan): the call also does dlap_grad_finish's work -- dadc [T,72] becomes an output -- on extra CTAs of
  * the BPTT kernel: the recurrence's CTA stages its tables meanwhile and waits for the da_t | dc_t rows, the
  * weight-gradient sums run beside the serial chain.  counter (device, one uint32, zero when the call starts and
- * zero again when it has finished; required with partials).  Two launches. */
+ * zero again when it has finished; required with partials).  peers (stock shards over peer memory, see dlap_peers;
+ * NULL otherwise; needs the partials): the sums of the partials are this rank's share only, and the same kernel adds
+ * all ranks' shares -- the backward pass' one exchange -- before the recurrence starts.  Two launches. */
 int dlap_macro_bwd(const dlap_plan* plan, const float* macro, const dlap_tensors* params, const float* h0,
                    const float* c0, const float* lstm_save, float* dadc, float* dpre, int want_sdf,
                    int want_mom, const dlap_tensors* grads, const float* wpart, const float* dadc_part,
-                   const int32_t* index, int precision, uint32_t* counter, void* stream);
+                   const int32_t* index, int precision, uint32_t* counter, const dlap_peers* peers, void* stream);
 
 /* get_weights (src/model.py:565-594): w = m (u - mu_t), mu_t the month's mean of u over unmasked stocks (demean = 0:
  * w = m u, normalize_w = False, src/model.py:274); normalized != 0 divides each month by clamp(sum_i |w| m, 1e-8)
