@@ -92,17 +92,20 @@ __device__ __forceinline__ void block_sum4(double (&v)[4], double* red /* [4][8]
     v[k] = s;
   }
 }
-// Barrier across the GPUs of a stock-sharded step, called by CTA 0 between two grid barriers: slot `b` of every
-// peer's flag block gets this launch's number from this rank, then this rank waits for everybody's.  Flags only ever
-// grow, so a rank that is one launch ahead cannot be mistaken for one that has arrived.  A peer that never shows up
-// (its process died) turns into a trap after 2 s instead of a hang.
+// Barrier across the GPUs of a stock-sharded step, entered right after a grid barrier (this rank's partial sums are
+// written): CTA 0 raises slot `b` of every peer's flag block to this launch's number, and EVERY CTA waits until all
+// peers have raised this rank's flags (they sit in this rank's own memory, so the polling is local) -- no second
+// grid barrier.  Flags only ever grow, so a rank that is one launch ahead cannot be mistaken for one that has
+// arrived.  A peer that never shows up (its process died) turns into a trap after 2 s instead of a hang.
 __device__ __forceinline__ void peer_barrier(const ReduceParams& P, int b, unsigned int value) {
   const int r = threadIdx.x;
   if (r < P.world) {
     const size_t flag_off = (size_t)(6 * P.Tcap + 2) * sizeof(double) + (size_t)b * 8 * sizeof(unsigned int);
-    __threadfence_system();
-    unsigned int* theirs = reinterpret_cast<unsigned int*>(reinterpret_cast<char*>(P.peer[r]) + flag_off) + P.rank;
-    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(theirs), "r"(value) : "memory");
+    if (blockIdx.x == 0) {
+      __threadfence_system();
+      unsigned int* theirs = reinterpret_cast<unsigned int*>(reinterpret_cast<char*>(P.peer[r]) + flag_off) + P.rank;
+      asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(theirs), "r"(value) : "memory");
+    }
     const unsigned int* mine = reinterpret_cast<const unsigned int*>(reinterpret_cast<const char*>(P.peer[P.rank]) + flag_off) + r;
     unsigned int v;
     unsigned long long t0 = 0;
@@ -115,6 +118,7 @@ __device__ __forceinline__ void peer_barrier(const ReduceParams& P, int b, unsig
       else if (now - t0 > 2000000000ull) __trap();
     }
   }
+  __syncthreads();
 }
 __device__ __forceinline__ double ld_peer(const double* p) {
   double v;
@@ -202,10 +206,7 @@ __global__ void __launch_bounds__(RT, 4) step_reduce_kernel(const ReduceParams P
 
   // ---------------------------------------------------------------- phase 1: N_bar, S_t; column partial sums
   if (P.phase_lo <= 1 && P.phase_hi >= 1) {
-    if (peers) {                                  // everybody's partial sums are written: barrier across the GPUs
-      if (blockIdx.x == 0) peer_barrier(P, 0, launch_no);
-      grid_sync(P.bar, ++nsync);
-    }
+    if (peers) peer_barrier(P, 0, launch_no);     // this rank's partial sums are written: wait for everybody's
     if (P.stock_shard && (P.phase_lo == 1 || peers)) {     // the months' sums over ALL stocks: row_stats from them
       for (int t = blockIdx.x * RT + tid; t < T; t += gridDim.x * RT) {
         double v[4];
@@ -458,8 +459,7 @@ __global__ void __launch_bounds__(RT, 4) step_reduce_kernel(const ReduceParams P
   // ---------------------------------------------------------------- phase 5 (stock shards): L_c, L_u
   if (peers && P.phase_hi >= 5) {                 // the second exchange: dS sums and sums of e^2, over peer memory
     grid_sync(P.bar, ++nsync);
-    if (blockIdx.x == 0) peer_barrier(P, 1, launch_no);
-    grid_sync(P.bar, ++nsync);
+    peer_barrier(P, 1, launch_no);
     for (int i = blockIdx.x * RT + tid; i < 2 * T + 2; i += gridDim.x * RT) {
       double v = 0.0;
       for (int r = 0; r < P.world; ++r) v += ld_peer(P.peer[r] + 4 * (size_t)P.Tcap + i);
