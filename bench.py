@@ -26,6 +26,7 @@ import time
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
+import numpy as np  # noqa: E402
 import torch  # noqa: E402
 
 T_MONTHS, N_STOCKS, F_CHARS, M_MACRO = 240, 10_000, 46, 178
@@ -517,6 +518,40 @@ def single_gpu_legs(args, dev, model, new_model, resident, graphed, timed, kerne
     out["epoch_ms"] = legs["epoch_graph_clip_adam"]["ms_per_step"]
     del gs, m_ep, opt
     out["legs"] = legs
+
+    # the loader stage on the device (src/data_loader.py:42-66): raw [T,N,F+1] -> mask, R, x.
+    # HBM-bound byte work: 4(F+1) B read + 4(F+1)+1 B written per stock-month; the raw panel (451 MB) exceeds the L2.
+    try:
+        from deeplearninginassetpricing_paperreplication_b200 import data as D
+        raw = torch.randn(T_MONTHS, N_STOCKS, F_CHARS + 1, device=dev)
+        raw[torch.rand(T_MONTHS, N_STOCKS, device=dev) < 0.6] = -99.99
+        for _ in range(3):
+            D.ingest_panel(raw, dev)
+        ms = timed(lambda: D.ingest_panel(raw, dev), 10) / 10
+        moved = cells * (8 * (F_CHARS + 1) + 1)
+        raw_host = raw.cpu().pin_memory()
+        D.ingest_panel(raw_host, dev)
+        t0 = time.perf_counter()
+        for _ in range(3):
+            D.ingest_panel(raw_host, dev)                                     # synchronises: the kernel reads host memory
+        host_ms = (time.perf_counter() - t0) / 3 * 1e3
+        t0 = time.perf_counter()
+        rn = raw_host.numpy()
+        m_ref = (rn[:, :, 0] > -98.99) & ~np.isnan(rn[:, :, 0]) & np.all(rn[:, :, 1:] > -98.99, axis=2)
+        np.where(m_ref, rn[:, :, 0], 0.0); np.where(m_ref[:, :, None], rn[:, :, 1:], 0.0)
+        numpy_ms = (time.perf_counter() - t0) * 1e3
+        out["loader"] = {"ingest_ms": ms, "GB/s": moved / (ms * 1e-3) / 1e9, "hbm_frac": moved / (ms * 1e-3) / 1e9 / peaks()[0],
+                         "bytes_per_stock_month": 8 * (F_CHARS + 1) + 1,
+                         "from_pinned_host_ms": host_ms, "from_pinned_host_GB/s": cells * 4 * (F_CHARS + 1) / (host_ms * 1e-3) / 1e9,
+                         "numpy_same_arrays_ms": numpy_ms,
+                         "what": "dlap_panel_ingest on the paper-shape raw array: mask from the -99.99 sentinel, zero-filled "
+                                 "returns and characteristics, one launch; from_pinned_host: the same kernel reading the raw "
+                                 "array over PCIe (upload + mask + zero-fill in one pass, wall clock); numpy_same_arrays: the "
+                                 "loader's numpy expressions (src/data_loader.py:53-65) on this host"}
+        del raw, raw_host, rn
+        torch.cuda.empty_cache()
+    except Exception as exc:                                                  # pragma: no cover
+        out["loader"] = {"error": repr(exc)[:200]}
 
     # "the Blackwell kernel to beat" (SURVEY.md §8d): the reference's own eager torch ops on this GPU
     try:

@@ -15,6 +15,10 @@ size_t smem_bwd_bytes(int F);
 cudaError_t launch_panel_index(const uint8_t* mask, int T, int N, int* index, cudaStream_t st);
 cudaError_t launch_panel_pull(const float* x_host, const int* index, int T, int N, int F, float* x_dev, int sms, bool clear,
                               cudaStream_t st);
+cudaError_t launch_panel_ingest(const void* raw, int raw_f64, long long cells, int F, float thr, float* x, float* R,
+                                uint8_t* mask, int ctas, cudaStream_t st);
+cudaError_t launch_macro_zscore(const float* raw, int T, int M, float* mean, float* stdv, int stats_given, int pairwise,
+                                float* out, cudaStream_t st);
 cudaError_t launch_step_reduce_c(const dlap_plan* plan, const float* u, const float* q, const float* R, const uint8_t* mask,
                                  const int* index, int weighted, int flags, const float* n_bar_in, int phase_lo, int phase_hi,
                                  float* row_stats, float* pr, float* scalars, float* w_out, double* col_part, float* e,
@@ -196,6 +200,28 @@ int dlap_panel_pull(const dlap_plan* plan, const float* x_host, const int32_t* i
   if (ctas < 0) return DLAP_E_SHAPE;
   CU(launch_panel_pull(x_host, index, plan->dims.T, plan->dims.N, plan->dims.F, x_dev,
                        ctas > 0 ? ctas : plan->grid_cell, clear != 0, (cudaStream_t)stream));
+  return DLAP_OK;
+}
+
+int dlap_panel_ingest(const dlap_plan* plan, const void* raw, int raw_f64, float valid_above, float* x, float* R,
+                      uint8_t* mask, int ctas, void* stream) {
+  int rc = check_plan(plan);
+  if (rc) return rc;
+  REQ(raw); REQ(x); REQ(R); REQ(mask);
+  if ((reinterpret_cast<uintptr_t>(raw) | reinterpret_cast<uintptr_t>(x)) & 15) return DLAP_E_ALIGN;   // float4 chunks
+  if (reinterpret_cast<uintptr_t>(R) & 3) return DLAP_E_ALIGN;
+  if (ctas < 0 || (raw_f64 != 0 && raw_f64 != 1)) return DLAP_E_SHAPE;
+  CU(launch_panel_ingest(raw, raw_f64, (long long)plan->dims.T * plan->dims.N, plan->dims.F, valid_above, x, R, mask,
+                         ctas > 0 ? ctas : plan->sms * 8, (cudaStream_t)stream));
+  return DLAP_OK;
+}
+
+int dlap_macro_zscore(const float* macro_raw, int T, int M, float* mean, float* std, int stats_given, int pairwise,
+                      float* out, void* stream) {
+  if (T < 0 || M < 0) return DLAP_E_SHAPE;
+  if (T == 0 || M == 0) return DLAP_OK;
+  REQ(macro_raw); REQ(mean); REQ(std); REQ(out);
+  CU(launch_macro_zscore(macro_raw, T, M, mean, std, stats_given != 0, pairwise != 0, out, (cudaStream_t)stream));
   return DLAP_OK;
 }
 

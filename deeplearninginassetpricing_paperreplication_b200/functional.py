@@ -138,6 +138,19 @@ class Workspace:
         return panel_index(self, mask)
 
 
+class PlanOnly:
+    """A plan without the step's scratch buffers: what the loader-side calls (dlap_panel_ingest, dlap_panel_index)
+    need.  Quacks like a Workspace for `panel_index`."""
+
+    def __init__(self, T: int, N: int, F: int, device: torch.device):
+        self.device = device
+        self.plan = DlapPlan()
+        _lib.call("dlap_make_plan", C.byref(DlapDims(T, N, F, 0, 0)), device.index if device.index is not None
+                  else torch.cuda.current_device(), C.byref(self.plan))
+        self.pp = C.byref(self.plan)
+        self.launches = 0
+
+
 _index_cache = []          # up to 4 x (weakref to a mask tensor, key, index, build event, build stream), most recent last
 
 

@@ -168,6 +168,30 @@ int dlap_panel_index(const dlap_plan* plan, const uint8_t* mask, int32_t* index,
 int dlap_panel_pull(const dlap_plan* plan, const float* x_host, const int32_t* index, float* x_dev, int ctas, int clear,
                     void* stream);
 
+/* The loader's array work on the device (AssetPricingDataset.__init__, src/data_loader.py:42-66), one launch:
+ * raw is the `data` array of the characteristics file, [T,N,F+1] with column 0 the return (src/data_loader.py:45-46),
+ * fp32 (raw_f64 = 0) or fp64 (raw_f64 = 1: rounded to fp32 first, the `.astype(np.float32)` of :45-46), 16-B aligned,
+ * in device memory OR in page-locked host memory the device can address (the kernel then reads it over the bus: the
+ * upload, the mask and the zero-fill are one pass, nothing is staged).  Outputs, all on the device:
+ *   mask[t,n] = R > valid_above and every characteristic > valid_above   (src/data_loader.py:50-57; a NaN fails '>';
+ *               the reference's threshold is the fp32 value of -99.99 + 1)
+ *   R[t,n], x[t,n,:] = the raw values where mask, +0.0 elsewhere          (src/data_loader.py:60-65)
+ * Bit-exact (comparisons and copies only).  4(F+1) B read and 4(F+1)+1 B written per stock-month, coalesced on both
+ * sides through shared memory.  ctas: CTAs of 256 threads (0: 8 per SM of the plan). */
+int dlap_panel_ingest(const dlap_plan* plan, const void* raw, int raw_f64, float valid_above, float* x, float* R,
+                      uint8_t* mask, int ctas, void* stream);
+
+/* Macro z-score of the loader (src/data_loader.py:76-86): macro_raw [T,M] fp32 on the device, row-major (after the
+ * macro_idx selection of :72-73).  stats_given = 0 (training file): mean[m] = sum_t x / T, std[m] = sqrt(sum_t
+ * (x-mean)^2 / T) + 1e-8 are computed and stored (:78-79); stats_given = 1 (validation / test file): mean, std are
+ * read (:81-82).  out = (x - mean) / std (:84).  fp32, each operation rounded separately, the sums in numpy's order
+ * for the array the loader holds: pairwise = 0, the file's own C-contiguous array: row after row; pairwise = 1, the
+ * column-major result of `macro_features[:, macro_idx]`: numpy's pairwise scheme down each column (8 interleaved
+ * accumulators up to 128 terms, recursive halves beyond).  Bit-identical to the reference's arrays either way.
+ * One launch, one thread per column. */
+int dlap_macro_zscore(const float* macro_raw, int T, int M, float* mean, float* std, int stats_given, int pairwise,
+                      float* out, void* stream);
+
 /* SDFNetwork.forward body on every stock-month (src/model.py:251-271) and MomentNetwork.forward
  * (src/model.py:132-161 with the input of :514-518), and -- see dlap_macro_io -- the macro LSTM in front of them:
  * u = MLP(x | a_t) [T,N];  q = tanh(Wqx.x + c_t) [8,T,N] (q NULL: moment net skipped, phase 'unconditional').

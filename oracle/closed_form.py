@@ -205,3 +205,65 @@ def mask_from_raw(ret, feat, missing: float = -99.99):
     mask = (ret > thr) & ~np.isnan(ret) & np.all(feat > thr, axis=2)
     return mask, np.where(mask, ret, 0.0).astype(np.float32), \
         np.where(mask[:, :, None], feat, 0.0).astype(np.float32)
+
+
+def _numpy_pairwise(col):
+    """numpy's pairwise summation of one contiguous fp32 run (the scalar loop behind add.reduce along the contiguous
+    axis): fewer than 8 terms one after the other; up to 128 terms eight interleaved accumulators, combined as
+    ((r0+r1)+(r2+r3))+((r4+r5)+(r6+r7)), then the remainder; longer runs split at n/2 rounded down to a multiple of 8."""
+    f = np.float32
+    n = len(col)
+    if n < 8:
+        r = f(0)
+        for v in col:
+            r = f(r + v)
+        return r
+    if n <= 128:
+        r = [f(col[j]) for j in range(8)]
+        i = 8
+        while i < n - (n % 8):
+            for j in range(8):
+                r[j] = f(r[j] + col[i + j])
+            i += 8
+        res = f(f(f(r[0] + r[1]) + f(r[2] + r[3])) + f(f(r[4] + r[5]) + f(r[6] + r[7])))
+        while i < n:
+            res = f(res + col[i]); i += 1
+        return res
+    n2 = n // 2
+    n2 -= n2 % 8
+    return f(_numpy_pairwise(col[:n2]) + _numpy_pairwise(col[n2:]))
+
+
+def macro_zscore(macro, mean=None, std=None, pairwise=False):
+    """Macro normalisation of the loader (src/data_loader.py:76-86) with the summation order written out.
+    pairwise=False: the file's array as loaded, C-contiguous [T, M]; numpy reduces it along axis 0 by adding the rows
+    one after the other in fp32.  pairwise=True: after ``macro_features[:, macro_idx]`` (src/data_loader.py:72-73)
+    the array is COLUMN-major (fancy indexing on the last axis), axis 0 is the contiguous one, and numpy sums each
+    column with its pairwise scheme.  `std` subtracts the mean, squares, sums the same way, divides by T and takes the
+    root; the loader adds 1e-8.  Returns (normalized, mean [1,M], std [1,M]), all fp32, bit-identical to the
+    reference's arrays (tests/test_oracle_golden.py) -- which is what the device kernel is held to."""
+    a = np.ascontiguousarray(macro, dtype=np.float32)
+    T, M = a.shape
+
+    def colsum(v):
+        if pairwise:
+            return np.array([_numpy_pairwise(v[:, m]) for m in range(M)], np.float32)
+        s = np.zeros(M, np.float32)
+        for t in range(T):
+            s = s + v[t]
+        return s
+
+    if mean is None:
+        mean = (colsum(a) / np.float32(T))[None]
+        d = a - mean
+        std = (np.sqrt(colsum(d * d) / np.float32(T)) + np.float32(1e-8))[None]
+    mean = np.asarray(mean, np.float32).reshape(1, M); std = np.asarray(std, np.float32).reshape(1, M)
+    return (a - mean) / std, mean, std
+
+
+def small_sample(mask, n_periods, n_stocks):
+    """Row/column selection of create_small_sample (src/data_loader.py:212-237): months [0, T'), the N' stocks with
+    the most valid months in numpy's argsort order.  Returns (T', stock indices)."""
+    T = min(n_periods, mask.shape[0]); N = min(n_stocks, mask.shape[1])
+    return T, np.argsort(mask.sum(axis=0))[-N:]
+

@@ -22,6 +22,11 @@ Cases
                 initial LSTM state.
   mask_raw      raw returns/features with -99.99 sentinels and NaNs -> mask, zero-filled
                 arrays (``src/data_loader.py:50-65``).  Bit-exact contract.
+  loader        the reference's loader (``src/data_loader.py:42-99, 157-237``) on a raw panel with sentinels, NaNs and
+                a wide-range macro series written to temporary .npz files: mask, zero-filled arrays, macro mean / std /
+                z-scores of a training file and of a validation file normalised with the training statistics,
+                ``get_date_count_list`` and ``create_small_sample`` -- `python make_golden.py loader` writes only this.
+                Bit-exact contract for the device-side loader.
   anchors       scalars of the full shipped training panel.
   v_*           config variants: the notebooks' [64,32] / use_rnn=False / hidden_dim_moment=[32],
                 normalize_w=False, narrow hidden layers with weighted_loss=False -- `python make_golden.py variants`
@@ -171,11 +176,71 @@ def shipped():
     print("mask_raw: valid", int(ds.mask.sum()), "of", ds.mask.size)
 
 
+def loader():
+    """Raw files -> the reference's AssetPricingDataset / create_data_loaders / create_small_sample."""
+    from src.data_loader import create_data_loaders, create_small_sample
+    rng = np.random.default_rng(20240611)
+    files = {}
+    for split, (T, N) in {"train": (24, 157), "valid": (7, 157)}.items():
+        F = 46
+        raw = rng.standard_normal((T, N, F + 1)).astype(np.float32)
+        raw[..., 0] *= 0.1
+        raw[rng.random((T, N)) < 0.30] = -99.99              # whole stock-month missing
+        raw[rng.random((T, N)) < 0.05, 0] = -99.99            # return missing only
+        hit = rng.random((T, N)) < 0.05                       # one characteristic missing
+        raw[hit, rng.integers(1, F + 1, size=int(hit.sum()))] = -99.99
+        raw[1, 2, 0] = np.nan; raw[2, 5, 17] = np.nan         # NaNs fail the comparison
+        raw[3, 1, 0] = -98.99; raw[3, 4, 9] = -98.99           # on the threshold: strict '>' says missing
+        raw[3, 6, 0] = -98.98; raw[4, 0, 0] = -0.0             # just above; a negative zero survives where valid
+        raw[5, :, :] = -99.99                                  # an empty month
+        macro = (rng.standard_normal((T, 11)) * rng.uniform(1e-3, 1e3, (1, 11)) + rng.uniform(-50, 50, (1, 11))).astype(np.float32)
+        macro[:, 7] = 3.25                                     # a constant column: std = 1e-8
+        files[split] = (raw, macro)
+        np.savez(f"/tmp/_dlap_loader_char_{split}.npz", data=raw)
+        np.savez(f"/tmp/_dlap_loader_macro_{split}.npz", data=macro)
+    idx = [0, 2, 3, 7, 10]
+    tr, va, _ = create_data_loaders("/tmp/_dlap_loader_char_train.npz", "/tmp/_dlap_loader_macro_train.npz",
+                                    "/tmp/_dlap_loader_char_valid.npz", "/tmp/_dlap_loader_macro_valid.npz",
+                                    macro_idx=idx)
+    blob = {"macro_idx": np.array(idx)}
+    for split, ds in (("train", tr), ("valid", va)):
+        raw, macro = files[split]
+        blob.update({f"{split}/raw": raw, f"{split}/macro_raw": macro, f"{split}/mask": ds.mask,
+                     f"{split}/returns": ds.returns, f"{split}/features": ds.individual_features,
+                     f"{split}/macro": ds.macro_features, f"{split}/mean": ds.mean_macro, f"{split}/std": ds.std_macro,
+                     f"{split}/date_count": ds.get_date_count_list()})
+    full = AssetPricingDataset("/tmp/_dlap_loader_char_valid.npz", "/tmp/_dlap_loader_macro_train.npz")   # no macro_idx
+    blob.update({"train/macro_all": full.macro_features, "train/mean_all": full.mean_macro, "train/std_all": full.std_macro})
+    # a series longer than numpy's pairwise block (128) and than two of them: the recursive split of the column sums
+    long_raw = (rng.standard_normal((300, 6)) * rng.uniform(1e-2, 1e2, (1, 6)) + rng.uniform(-20, 20, (1, 6))).astype(np.float32)
+    np.savez("/tmp/_dlap_loader_macro_long.npz", data=long_raw)
+    lg = AssetPricingDataset("/tmp/_dlap_loader_char_valid.npz", "/tmp/_dlap_loader_macro_long.npz", macro_idx=[5, 1, 2])
+    la = AssetPricingDataset("/tmp/_dlap_loader_char_valid.npz", "/tmp/_dlap_loader_macro_long.npz")
+    blob.update({"long/macro_raw": long_raw, "long/idx": np.array([5, 1, 2]), "long/macro": lg.macro_features,
+                 "long/mean": lg.mean_macro, "long/std": lg.std_macro, "long/macro_all": la.macro_features,
+                 "long/mean_all": la.mean_macro, "long/std_all": la.std_macro})
+    small = create_small_sample(tr, n_periods=12, n_stocks=40)
+    for k, v in small.items():
+        blob["small/" + k] = v.numpy()
+    # fp64 raw file: the loader rounds to fp32 first (src/data_loader.py:45-46)
+    raw64 = files["valid"][0].astype(np.float64) * (1.0 + 1e-9)
+    raw64[files["valid"][0] == np.float32(-99.99)] = -99.99
+    np.savez("/tmp/_dlap_loader_char64.npz", data=raw64)
+    d64 = AssetPricingDataset("/tmp/_dlap_loader_char64.npz")
+    blob.update({"f64/raw": raw64, "f64/mask": d64.mask, "f64/returns": d64.returns, "f64/features": d64.individual_features})
+    np.savez_compressed(os.path.join(HERE, "loader.npz"), **blob)
+    print("loader: train valid", int(tr.mask.sum()), "of", tr.mask.size, "| mean/std dtype", tr.mean_macro.dtype,
+          "| min std", float(tr.std_macro.min()))
+
+
 if __name__ == "__main__":
     torch.set_num_threads(1)        # bit-reproducible regardless of the host
     if sys.argv[1:] == ["variants"]:
         variants()
+    elif sys.argv[1:] == ["loader"]:
+        loader()
     else:
+        loader()
         rand_small()
         shipped()
         variants()

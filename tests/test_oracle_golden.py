@@ -140,3 +140,38 @@ def test_mask_contract_bit_exact():
     assert np.array_equal(ret, g["returns"])
     assert np.array_equal(feat, g["features"])
     assert not mask[2, 3] and not mask[4, 7] and not mask[5, 1]
+
+
+def test_loader_contract_bit_exact():
+    """src/data_loader.py:42-99, :212-237 on raw files written by make_golden.py `loader`: mask, zero-fill (fp32 and
+    fp64 files), macro statistics and z-scores in numpy's summation order, validation file with training statistics."""
+    g = load_golden("loader")
+    idx = g["macro_idx"]
+    stats = None
+    for split in ("train", "valid"):
+        raw = g[f"{split}/raw"]
+        mask, ret, feat = cf.mask_from_raw(raw[:, :, 0], raw[:, :, 1:])
+        assert np.array_equal(mask, g[f"{split}/mask"])
+        assert ret.tobytes() == g[f"{split}/returns"].tobytes()            # bytes: -0.0 and +0.0 differ
+        assert feat.tobytes() == g[f"{split}/features"].tobytes()
+        z, mean, std = cf.macro_zscore(g[f"{split}/macro_raw"][:, idx], *(stats or (None, None)), pairwise=True)
+        assert z.tobytes() == g[f"{split}/macro"].tobytes()
+        assert mean.tobytes() == g[f"{split}/mean"].tobytes() and std.tobytes() == g[f"{split}/std"].tobytes()
+        assert np.array_equal(mask.sum(axis=1).astype(np.float32), g[f"{split}/date_count"])
+        stats = stats or (mean, std)
+    z, mean, std = cf.macro_zscore(g["train/macro_raw"])                      # no macro_idx: row-after-row sums
+    assert z.tobytes() == g["train/macro_all"].tobytes() and std.tobytes() == g["train/std_all"].tobytes()
+    z, mean, std = cf.macro_zscore(g["long/macro_raw"][:, g["long/idx"]], pairwise=True)      # 300 months: recursive split
+    assert z.tobytes() == g["long/macro"].tobytes() and mean.tobytes() == g["long/mean"].tobytes()
+    assert std.tobytes() == g["long/std"].tobytes()
+    z, mean, std = cf.macro_zscore(g["long/macro_raw"])
+    assert z.tobytes() == g["long/macro_all"].tobytes() and mean.tobytes() == g["long/mean_all"].tobytes()
+    assert not g["train/mask"][5].any() and g["train/mask"].any()
+    raw64 = g["f64/raw"]
+    mask, ret, feat = cf.mask_from_raw(raw64[:, :, 0].astype(np.float32), raw64[:, :, 1:].astype(np.float32))
+    assert np.array_equal(mask, g["f64/mask"]) and ret.tobytes() == g["f64/returns"].tobytes()
+    assert feat.tobytes() == g["f64/features"].tobytes()
+    T, cols = cf.small_sample(g["train/mask"], 12, 40)
+    assert np.array_equal(g["train/mask"][:T][:, cols], g["small/mask"])
+    assert np.array_equal(g["train/features"][:T][:, cols], g["small/individual_features"])
+
