@@ -308,7 +308,9 @@ def run_ours(args, rank, world):
     ksteps = max(5, min(args.steps, 50))
 
     extra = {}
-    if world == 1:
+    if args.no_legs:
+        pass
+    elif world == 1:
         extra.update(single_gpu_legs(args, dev, model, new_model, resident, graphed, timed, kernel_ms, step_of, ksteps))
     else:
         extra.update(multi_gpu_legs(args, dev, rank, world, new_model, graphed, timed, ksteps))
@@ -369,7 +371,12 @@ def run_ours(args, rank, world):
     how = {"precision": args.precision,
            "parallelism": "single GPU" if world == 1 else f"months dealt round-robin over {world} ranks (NCCL)",
            "step": ("python loop (eager launches)" if args.eager else
-                    "zero_grad + forward + backward captured once in a CUDA graph (GraphedStep), replayed")}
+                    "zero_grad + forward + backward captured once in a CUDA graph (GraphedStep), replayed"),
+           "panel": ("resident in HBM: x [T,N,F] fp32 as the reference holds it" + (
+               "" if args.precision == "fp32" or not Fn.use_x_image else
+               ", plus its X images (dlap_panel_image: the listed rows split into bf16 hi/lo in the tensor-core operand "
+               "layout), made once per panel like the valid-cell index -- `panel_image.build_ms`; `gather_path` is the "
+               "step without them"))}
     line = {
         "metric": METRIC, "value": value, "unit": "stock-months/s",
         "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps,
@@ -422,6 +429,7 @@ def single_gpu_legs(args, dev, model, new_model, resident, graphed, timed, kerne
     """What SURVEY.md §8d asks for beside the headline: the other phases, the forward-only evaluation, dropout on,
     a fully listed panel (rate per VISITED stock-month), the exact-fp32 path, and the eager-torch step on the same
     GPU (the reference moved to `cuda`, src/train.py:193-199)."""
+    from deeplearninginassetpricing_paperreplication_b200 import functional as Fn
     cells = T_MONTHS * N_STOCKS
     rate = lambda ms_total, n: {"value": cells * n / (ms_total * 1e-3), "unit": "stock-months/s", "ms_per_step": ms_total / n}
     out = {}
@@ -496,6 +504,28 @@ def single_gpu_legs(args, dev, model, new_model, resident, graphed, timed, kerne
         k3 = max(3, min(k, 10))
         out["fp32_path"] = rate(timed(s32, k3), k3)
         del m32
+    if args.precision != "fp32":
+        # X images (dlap_panel_image): the resident panel is converted ONCE to the tensor-core operand format (like the
+        # valid-cell index it is not part of a step).  What that pass costs, and the step WITHOUT it -- every step
+        # gathering and converting the rows of x itself, as a loop that sees each panel once would run.
+        try:
+            ws0 = Fn.PlanOnly(T_MONTHS, N_STOCKS, F_CHARS, dev)
+            idx0 = Fn.panel_index(ws0, resident[3])
+            hit = Fn.cached_panel_image(resident[1])
+            if hit is not None:
+                img_ms = timed(lambda: Fn.rebuild_panel_image(resident[1], hit[0], hit[1]), 5) / 5
+                out["panel_image"] = {"build_ms": img_ms, "bytes": int(hit[1].numel()),
+                                      "bytes_per_listed_stock_month": hit[1].numel() / float(resident[3].sum().item()),
+                                      "what": "dlap_panel_image: once per resident panel, outside the timed steps"}
+            Fn.use_x_image = False
+            mg = new_model()
+            gg = graphed(mg, resident)
+            out["gather_path"] = dict(rate(timed(gg.step, k), k), launches=gg.launches,
+                                      what="the same step with DLAP_X_IMAGE=0: no X images, every step gathers the 184-byte "
+                                           "rows of x and splits them to bf16 hi/lo itself (bit-identical results)")
+            del gg, mg
+        finally:
+            Fn.use_x_image = True
     # a whole epoch of src/train.py:45-103 -- zero_grad, forward, backward, clip_grad_norm_, Adam -- as one graph replay
     # (device time), and through training.train_epoch with its one device-to-host read per epoch (host wall clock)
     from deeplearninginassetpricing_paperreplication_b200 import FusedClipAdam, train_epoch
@@ -693,6 +723,7 @@ def main():
                     help="arithmetic of the per-cell contractions: bf16x3 = tcgen05 BF16 MMAs on hi/lo-split "
                          "fp32 operands (3 products per fp32 product, fp32 accumulate); fp32 = CUDA-core FFMA")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-legs", action="store_true", help="headline, e2e and roofline only (development runs)")
     ap.add_argument("--eager", action="store_true", help="time the plain Python loop instead of the CUDA-graph replay")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", 0))

@@ -17,7 +17,7 @@ ROOT = os.path.dirname(PKG_DIR)
 CSRC = os.path.join(PKG_DIR, "csrc")
 LIB_PATH = os.path.join(PKG_DIR, "libdlap_b200.so")
 OBJ_DIR = os.path.join(PKG_DIR, "build")          # objects: git- and gpurun-ignored
-SOURCES = ("capi.cu", "cell_fwd.cu", "cell_bwd.cu", "reduce.cu", "step_reduce.cu", "macro_lstm.cu", "adam.cu", "ingest.cu", "tc_selftest.cu",
+SOURCES = ("capi.cu", "cell_fwd.cu", "cell_bwd.cu", "reduce.cu", "step_reduce.cu", "macro_lstm.cu", "adam.cu", "ingest.cu", "panel_image.cu", "tc_selftest.cu",
            "cell_fwd_tc.cu", "cell_bwd_tc.cu", "panel_index.cu")
 NVCC_FLAGS = ("-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-shared", "-Xcompiler", "-fPIC")
@@ -40,7 +40,8 @@ class DlapPlan(C.Structure):
                 ("col_part_bytes", C.c_int64), ("loss_part_bytes", C.c_int64), ("row_part_bytes", C.c_int64),
                 ("bar_bytes", C.c_int64),
                 ("wpart_bytes", C.c_int64), ("dadc_part_bytes", C.c_int64),
-                ("lstm_save_bytes", C.c_int64), ("dpre_bytes", C.c_int64), ("index_bytes", C.c_int64)]
+                ("lstm_save_bytes", C.c_int64), ("dpre_bytes", C.c_int64), ("index_bytes", C.c_int64),
+                ("image_bytes", C.c_int64)]
 
 
 class DlapTensors(C.Structure):
@@ -86,12 +87,13 @@ SIGNATURES = {
     "dlap_panel_pull": (_PLAN, _P, _P, _P, _I, _I, _P),
     "dlap_panel_ingest": (_PLAN, _P, _I, C.c_float, _P, _P, _P, _I, _P),
     "dlap_macro_zscore": (_P, _I, _I, _P, _P, _I, _I, _P, _P),
-    "dlap_cell_fwd": (_PLAN, _P, _P, _P, _TENS, _MIO, _P, _P, _I, C.c_float, C.c_uint64, _P, _P),
+    "dlap_panel_image": (_PLAN, _P, _P, _P, _P),
+    "dlap_cell_fwd": (_PLAN, _P, _P, _P, _P, _TENS, _MIO, _P, _P, _I, C.c_float, C.c_uint64, _P, _P),
     "dlap_step_reduce": (_PLAN, _P, _P, _P, _P, _P, _I, _I, _P, _I, _I, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _MIO, _P, _P, _I,
                          C.POINTER(DlapPeers), _P),
     "dlap_loss_finish": (_PLAN, _P, _I, _P, _P, _P, _P, _P, _P),
     "dlap_loss_finish_noalloc": (_PLAN, _P, _I, _P, _P, _P, _P),
-    "dlap_cell_bwd": (_PLAN, _P, _P, _P, _P, _TENS, _MIO, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _P, _P, _I,
+    "dlap_cell_bwd": (_PLAN, _P, _P, _P, _P, _P, _TENS, _MIO, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _P, _P, _I,
                       C.c_float, C.c_uint64, _P, _P),
     "dlap_grad_finish": (_PLAN, _P, _P, _P, _I, _I, _I, _TENS, _P, _I, _P),
     "dlap_macro_bwd": (_PLAN, _P, _TENS, _P, _P, _P, _P, _P, _I, _I, _TENS, _P, _P, _P, _I, _P, C.POINTER(DlapPeers), _P),

@@ -13,6 +13,8 @@ cudaError_t launch_cell_fwd_tc(const CellParams& P, const MacroParams* MP, int g
 cudaError_t launch_cell_bwd_tc(const CellParams& P, int grid, bool sdf, bool mom, cudaStream_t st);
 size_t smem_bwd_bytes(int F);
 cudaError_t launch_panel_index(const uint8_t* mask, int T, int N, int* index, cudaStream_t st);
+cudaError_t launch_panel_image(const CellParams& P, uint8_t* image, int sms, cudaStream_t st);
+size_t panel_image_tile_bytes();
 cudaError_t launch_panel_pull(const float* x_host, const int* index, int T, int N, int F, float* x_dev, int sms, bool clear,
                               cudaStream_t st);
 cudaError_t launch_panel_ingest(const void* raw, int raw_f64, long long cells, int F, float thr, float* x, float* R,
@@ -125,6 +127,7 @@ int dlap_make_plan(const dlap_dims* dims, int device, dlap_plan* out) {
   p.wpart_bytes = (int64_t)p.grid_cell * wp_stride(round4(F)) * 4;
   p.dadc_part_bytes = (int64_t)T * (p.tpm > 4 ? p.tpm : 4) * 72 * 4;
   p.index_bytes = (int64_t)idx_ints(T, N) * 4;
+  p.image_bytes = F <= 46 ? (int64_t)T * p.tpm * (int64_t)panel_image_tile_bytes() : 0;
   p.lstm_save_bytes = (int64_t)T * 6 * (dims->H > 0 ? dims->H : 1) * 4;
   p.dpre_bytes = (int64_t)T * 4 * (dims->H > 0 ? dims->H : 1) * 4;
   *out = p;
@@ -225,7 +228,19 @@ int dlap_macro_zscore(const float* macro_raw, int T, int M, float* mean, float* 
   return DLAP_OK;
 }
 
-int dlap_cell_fwd(const dlap_plan* plan, const float* x, const uint8_t* mask, const int32_t* index,
+int dlap_panel_image(const dlap_plan* plan, const float* x, const int32_t* index, void* image, void* stream) {
+  int rc = check_plan(plan);
+  if (rc) return rc;
+  REQ(x); REQ(index); REQ(image);
+  if (plan->dims.F > 46) return DLAP_E_SHAPE;
+  if ((reinterpret_cast<uintptr_t>(x) & 3) || (reinterpret_cast<uintptr_t>(image) & 15)) return DLAP_E_ALIGN;
+  CellParams P{};
+  P.x = x; P.T = plan->dims.T; P.N = plan->dims.N; P.F = plan->dims.F; P.index = index;
+  CU(launch_panel_image(P, static_cast<uint8_t*>(image), plan->sms, (cudaStream_t)stream));
+  return DLAP_OK;
+}
+
+int dlap_cell_fwd(const dlap_plan* plan, const float* x, const uint8_t* mask, const int32_t* index, const void* x_image,
                   const dlap_tensors* params, const dlap_macro_io* mio, float* u, float* q, int precision,
                   float dropout_p, uint64_t dropout_seed, const uint64_t* dropout_seed_dev, void* stream) {
   int rc = check_plan(plan);
@@ -249,6 +264,8 @@ int dlap_cell_fwd(const dlap_plan* plan, const float* x, const uint8_t* mask, co
   rc = set_dropout(P, dropout_p, dropout_seed, dropout_seed_dev);
   if (rc) return rc;
   P.index = tc ? index : nullptr;
+  if (x_image && (reinterpret_cast<uintptr_t>(x_image) & 15)) return DLAP_E_ALIGN;
+  P.ximg = tc ? static_cast<const uint8_t*>(x_image) : nullptr;
   const int series = mio->series_T > 0 ? mio->series_T : d.T;
   // ---- the macro side
   MacroParams MP;
@@ -351,7 +368,7 @@ int dlap_loss_finish(const dlap_plan* plan, const double* col_part, int nsplit, 
 }
 
 int dlap_cell_bwd(const dlap_plan* plan, const float* x, const float* R, const uint8_t* mask, const int32_t* index,
-                  const dlap_tensors* params, const dlap_macro_io* mio, const float* row_stats, const double* dS2,
+                  const void* x_image, const dlap_tensors* params, const dlap_macro_io* mio, const float* row_stats, const double* dS2,
                   const float* gc, const float* gu, const float* dpr_cot, const float* G, const float* scalars,
                   int weighted_loss, int want_sdf, int want_mom, float* wpart, float* dadc_part, int precision,
                   float dropout_p, uint64_t dropout_seed, const uint64_t* dropout_seed_dev, void* stream) {
@@ -376,6 +393,8 @@ int dlap_cell_bwd(const dlap_plan* plan, const float* x, const float* R, const u
     if (plan->dims.F > 46) return DLAP_E_SHAPE;
     REQ(index);
     P.index = index;
+    if (x_image && (reinterpret_cast<uintptr_t>(x_image) & 15)) return DLAP_E_ALIGN;
+    P.ximg = static_cast<const uint8_t*>(x_image);
     CU(launch_cell_bwd_tc(P, plan->grid_cell, want_sdf != 0, want_mom != 0, (cudaStream_t)stream));
     return DLAP_OK;
   }

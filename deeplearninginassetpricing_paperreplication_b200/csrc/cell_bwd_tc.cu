@@ -271,7 +271,11 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
     // ===== gather + convert (cell_tc.cuh); stamps 4-7 of row q / NGW: loop top, slot free, converted, loads issued
     const int gw = warp == 0 ? 0 : (warp < 4 ? warp - 1 : warp - 17);
     long long* tl = (P.timeline && blockIdx.x == 0 && gw == 1 && lane == 0) ? P.timeline + 256 * 16 * 2 : nullptr;
-    if (gather_wide(P))
+    if (P.ximg) {                   // the panel's X images exist (dlap_panel_image): one warp, one bulk copy per tile
+      if (warp == 0)
+        image_role<NB, NXS, true>(P, lane, TileMap{tile_lo, 31, 0, my_tiles}, s.xh(0), s.g5h(0), G5_BLK, NXS * G5_BLK,
+                                  bar + B_XOP_FULL, bar + B_XOP_EMPTY);
+    } else if (gather_wide(P))
       gather_role<BR, NGW, NXS, true, true>(P, gw, lane, TileMap{tile_lo, 31, 0, my_tiles}, s.xh(0), s.g5h(0), G5_BLK, NXS * G5_BLK, bar + B_XOP_FULL,
                                        bar + B_XOP_EMPTY, tl, 0, true);
     else

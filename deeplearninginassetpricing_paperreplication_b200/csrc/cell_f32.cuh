@@ -58,6 +58,8 @@ struct CellParams {
   long long* timeline;       // diagnostics (dlap_debug_timeline): per-tile clock64 stamps of CTA 0, or null
   // valid-cell index (dlap_panel_index); tensor-core kernels only, null = not built
   const int* index;
+  // X images of every tile of the index (dlap_panel_image; cell_tc.cuh), or null: gather the rows of x instead
+  const uint8_t* ximg;
   // non-null: a_t / c_t are still being written by a concurrent dlap_macro_fwd; months [0, *months_ready) are
   // complete (tensor-core forward only); month t of this (possibly month-sharded) panel is month months_base + t there
   const int* months_ready;

@@ -178,7 +178,11 @@ __global__ void __launch_bounds__(NT_TC, 1) cell_fwd_tc_kernel(const CellParams 
     // loads issued
     const int gw = warp == 0 ? 0 : warp - 1;
     long long* tl = (P.timeline && blockIdx.x == 0 && warp == 4 && lane == 0) ? P.timeline : nullptr;
-    if (gather_wide(P))
+    if (P.ximg) {                   // the panel's X images exist: one warp feeds the slots with bulk copies
+      if (warp == 0)
+        image_role<NB, NXS, MOM>(P, lane, tm, s.xh(0), s.w1h(0) + (KG1 - 1) * N1 * 16, 2 * W1_IMG, W1_IMG,
+                                 bar + F_XOP_FULL, bar + F_XOP_EMPTY);
+    } else if (gather_wide(P))
       gather_role<BR, NGW, NXS, true, MOM>(P, gw, lane, tm, s.xh(0), s.w1h(0) + (KG1 - 1) * N1 * 16,
                                          2 * W1_IMG, W1_IMG, bar + F_XOP_FULL,
                                       bar + F_XOP_EMPTY, tl, 0, true);

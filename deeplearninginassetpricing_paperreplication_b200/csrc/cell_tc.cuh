@@ -159,6 +159,55 @@ __device__ __forceinline__ void gather_role(const CellParams& P, int gw, int lan
   }
 }
 
+// ---- the same role when the panel's X images already exist in HBM (CellParams::ximg, dlap_panel_image) -----------
+// The characteristics do not change from one step to the next (full-batch training re-reads the same panel every
+// epoch, src/train.py:45-103), so gathering 184-byte rows and splitting them into bf16 hi/lo pairs can be done once
+// per panel instead of twice per step: dlap_panel_image stores, for every tile of the valid-cell index, exactly the
+// bytes the gather warps would have put into shared memory (hi image, then lo image: 2 * X_IMG contiguous bytes).
+// ONE warp then feeds the tensor core: per tile one 1-D bulk copy (TMA engine) of 24 KB into the free slot,
+// completing on the slot's `full` barrier, and the per-month bias column of the slot's W1 image as before.  The
+// barrier still counts NB arrivals per tile (the gather role's batches): lane 0 makes all of them.
+template <int NB, int NSLOT, bool MOM>
+__device__ __forceinline__ void image_role(const CellParams& P, int lane, const TileMap tm, uint8_t* x0, uint8_t* g5h0,
+                                           uint32_t g5_stride, uint32_t g5_lo, uint64_t* xop_full, uint64_t* xop_empty) {
+  static_assert(NB >= 2, "the arrivals that follow the bias column publish it");
+  MonthCursor mc;
+  if (tm.count > 0) mc.init(P, tm.tile(0));
+  int months_seen = 0;
+  for (int i = 0; i < tm.count; ++i) {
+    const int tile = tm.tile(i), sl = i % NSLOT, use = i / NSLOT;
+    mc.seek(P, tile);
+    mbar_wait(xop_empty + sl, (use & 1) ^ 1);
+    if (lane == 0) {
+      mbar_expect_tx(xop_full + sl, 2 * X_IMG);                         // arrival 1 of NB, and the bytes to come
+      bulk_g2s(x0 + (size_t)sl * 2 * X_IMG, P.ximg + (size_t)tile * (2 * X_IMG), 2 * X_IMG, xop_full + sl);
+    }
+    // bias column a_t | c_t | 0 of this tile's month (the recurrence that makes a_t may still be running)
+    const size_t row = (size_t)mc.t * P.months_stride;
+    if (P.months_ready) wait_month(P.months_ready, P.months_base + (int)row, months_seen);
+    const float b[3] = {__ldcg(P.a_t + row * 64 + lane), __ldcg(P.a_t + row * 64 + 32 + lane),
+                        (MOM && lane < 8) ? __ldcg(P.c_t + row * 8 + lane) : 0.f};
+    uint8_t* g5h = g5h0 + sl * g5_stride;
+#pragma unroll
+    for (int e = 0; e < 3; ++e) {
+      const int unit = lane + 32 * e;
+      if (unit < N1) {
+        const __nv_bfloat16 bh = __float2bfloat16_rn(b[e]);
+        const __nv_bfloat16 bl = __float2bfloat16_rn(b[e] - __bfloat162float(bh));
+        const int off = unit * 16 + (ONES_K - 8 * (KG1 - 1)) * 2;
+        *reinterpret_cast<__nv_bfloat16*>(g5h + off) = bh;
+        *reinterpret_cast<__nv_bfloat16*>(g5h + g5_lo + off) = bl;
+      }
+    }
+    fence_proxy_async();
+    __syncwarp();
+    if (lane == 0) {
+#pragma unroll
+      for (int k = 1; k < NB; ++k) mbar_arrive(xop_full + sl);
+    }
+  }
+}
+
 // fill k-groups g0 .. g0+ng-1 of a W1 image pair (hi, lo: contiguous [ng][N1][8] blocks) from global
 // parameters; the bias column k = 46 is left zero (the gather warps write it per tile)
 __device__ __forceinline__ void fill_w1_groups(const CellParams& P, uint8_t* hi, uint8_t* lo, int g0, int ng, int tid,

@@ -184,8 +184,83 @@ def panel_index(ws: "Workspace", mask: torch.Tensor) -> torch.Tensor:
 
 
 def invalidate_panel_index() -> None:
-    """Forget every cached valid-cell index (see panel_index)."""
+    """Forget every cached valid-cell index (see panel_index) and every X image built on one."""
     del _index_cache[:]
+    del _image_cache[:]
+
+
+# ---- X images (dlap_panel_image): the characteristics in the tensor-core kernels' operand format, once per panel ----
+# DLAP_X_IMAGE=0 in the environment: never build them (the kernels gather and convert the rows of x every step; same
+# results bit for bit)
+use_x_image = os.environ.get("DLAP_X_IMAGE", "1") != "0"
+force_x_image = False      # set by GraphedStep around its warm-up: the panel it captures is stepped on many times
+IMAGE_TILE_BYTES = 24768
+_image_cache = []          # up to 3 x [weakref to x, key, index, image or None, build event, build stream]
+
+
+def forget_panel_image(x: torch.Tensor) -> None:
+    """Drop the X image of `x` (its values were changed by something the version counter does not see)."""
+    _image_cache[:] = [e for e in _image_cache if e[0]() is not None and e[0]() is not x]
+
+
+def panel_image(ws: "Workspace", x: torch.Tensor, index: torch.Tensor, force: bool = False) -> Optional[torch.Tensor]:
+    """The X images of panel `x` for the valid-cell `index`, or None (the kernels then gather the rows of x).
+    A panel that is seen ONCE (a loop that uploads a fresh panel every step) is not worth a pass of its own: the
+    image is built when the same tensor object comes back with an unchanged version counter -- the full-batch loops
+    of the reference step on the same resident panel thousands of times -- or at once with `force`.  Never built
+    during a stream capture.  Keyed like the valid-cell index: (tensor object, version counter, data pointer, index);
+    a write that bypasses the version counter needs forget_panel_image(x)."""
+    if not use_x_image or ws.plan.image_bytes == 0:
+        return None
+    _image_cache[:] = [e for e in _image_cache if e[0]() is not None]
+    cur = torch.cuda.current_stream(ws.device)
+    capturing = torch.cuda.is_current_stream_capturing()
+    key = (x._version, x.data_ptr(), x.device)
+    entry = None
+    for k, e in enumerate(_image_cache):
+        if e[0]() is x:
+            if e[1] == key and e[2] is index:
+                entry = e
+                _image_cache.append(_image_cache.pop(k))
+            else:
+                del _image_cache[k]            # the panel's values or its mask changed
+            break
+    if entry is None:
+        entry = [weakref.ref(x), key, index, None, None, None]
+        _image_cache.append(entry)
+        del _image_cache[:-3]
+        if not force:
+            return None
+    if entry[3] is None:
+        if capturing:
+            return None
+        ntiles = int(index[0].item())          # one read-back per panel: the image is sized by the tiles that exist
+        image = torch.empty(max(ntiles, 1) * IMAGE_TILE_BYTES, dtype=torch.uint8, device=ws.device)
+        _lib.call("dlap_panel_image", ws.pp, _ptr(x), _ptr(index), _ptr(image), cur.cuda_stream)
+        ws.launches += 1
+        built = torch.cuda.Event()
+        built.record(cur)
+        entry[3:6] = [image, built, cur.cuda_stream]
+    elif entry[5] != cur.cuda_stream and not capturing:
+        cur.wait_event(entry[4])
+    return entry[3]
+
+
+def cached_panel_image(x: torch.Tensor):
+    """(index, image) of the X images currently held for `x`, or None."""
+    for e in _image_cache:
+        if e[0]() is x and e[3] is not None:
+            return e[2], e[3]
+    return None
+
+
+def rebuild_panel_image(x: torch.Tensor, index: torch.Tensor, image: torch.Tensor) -> None:
+    """dlap_panel_image into an existing buffer (a captured graph holds its address) after x was given new values."""
+    T, N, F = x.shape
+    _lib.call("dlap_panel_image", PlanOnly(T, N, F, x.device).pp, _ptr(x), _ptr(index), _ptr(image), _stream(x.device))
+    for e in _image_cache:
+        if e[0]() is x and e[3] is image:
+            e[1] = (x._version, x.data_ptr(), x.device)
 
 
 _workspaces: Dict[Tuple, Workspace] = {}
@@ -338,6 +413,7 @@ def upload_panel(macro, x, R, mask, device, out=None, clear=True):
             _lib.call("dlap_panel_pull", ws.pp, x.data_ptr(), _ptr(index), _ptr(d_x), int(reserve_sms),
                       1 if clear else 0, _stream(device))
             ws.launches += 1
+            forget_panel_image(d_x)            # the kernel wrote d_x behind the version counter's back
         else:
             d_x.copy_(x, non_blocking=True)
     return d_macro, d_x, d_R, d_mask
@@ -410,6 +486,7 @@ class CellPass:
     index: Optional[torch.Tensor]
     mio: DlapMacroIO
     precision: str
+    ximg: Optional[torch.Tensor] = None        # X images the kernels fetched their operands from (dlap_panel_image)
 
 
 def cell_forward(ws: Workspace, macro, x, mask, params, h0, c0, precision: str, need_moments: bool,
@@ -425,6 +502,7 @@ def cell_forward(ws: Workspace, macro, x, mask, params, h0, c0, precision: str, 
     series_T = T if months is None else months.T_total
     month0, stride = (0, 1) if months is None else (months.t0, months.stride)
     index = ws.panel_index(mask) if precision == "bf16x3" else None
+    ximg = panel_image(ws, x, index, force_x_image) if index is not None else None
     save = torch.empty(series_T, 6 * H, dtype=torch.float32, device=dev)
     hn = torch.empty(H, dtype=torch.float32, device=dev)
     cn = torch.empty(H, dtype=torch.float32, device=dev)
@@ -445,11 +523,11 @@ def cell_forward(ws: Workspace, macro, x, mask, params, h0, c0, precision: str, 
     u = torch.empty(T, N, dtype=torch.float32, device=dev)
     q = torch.empty(KM, T, N, dtype=torch.float32, device=dev) if need_moments else None
     tens = _tensors(params)
-    _timed_call("dlap_cell_fwd", dev, ws.pp, _ptr(x), _ptr(mask), _ptr(index), C.byref(tens), C.byref(mio), _ptr(u),
+    _timed_call("dlap_cell_fwd", dev, ws.pp, _ptr(x), _ptr(mask), _ptr(index), _ptr(ximg), C.byref(tens), C.byref(mio), _ptr(u),
                 _ptr(q), _PRECISIONS[precision], float(dropout_p), int(dropout_seed), _ptr(dropout_seed_dev),
                 _stream(dev))
     ws.launches += 1 if (fused or tables is not None) else 2
-    return CellPass(u, q, save, a_t, c_t, hn, cn, index, mio, precision)
+    return CellPass(u, q, save, a_t, c_t, hn, cn, index, mio, precision, ximg)
 
 
 @dataclass
@@ -567,7 +645,7 @@ class GanStepFn(torch.autograd.Function):
         # AccumulateGrad nodes and their stream, alive until the garbage collector runs.  u and q are dead here.
         ctx.opts, ctx.ws = opts, ws
         ctx.keep = (cp.save, cp.a_t, cp.c_t, cp.index, cp.mio, cp.q is not None, red.row_stats, red.scalars, red.G,
-                    red.dS2, tables, q_dense is not None)
+                    red.dS2, tables, q_dense is not None, cp.ximg)
         scalars = red.scalars
         l_c, l_u, sharpe = scalars[SC_LC], scalars[SC_LU], scalars[SC_SHARPE]
         ctx.mark_non_differentiable(red.w, sharpe, cp.hn, cp.cn)
@@ -577,7 +655,7 @@ class GanStepFn(torch.autograd.Function):
     def backward(ctx, g_lc, g_lu, g_pr, *_unused):
         x, R, mask, macro, h0, c0, *params = ctx.saved_tensors
         opts, ws = ctx.opts, ctx.ws
-        save, a_t, c_t, index, mio, has_q, row_stats, scalars, G, dS2, tables, q_given = ctx.keep
+        save, a_t, c_t, index, mio, has_q, row_stats, scalars, G, dS2, tables, q_given, ximg = ctx.keep
         sh = opts.shard
         stocks = isinstance(sh, StockShard)
         # rows of the da_t | dc_t table that is exchanged: the whole series' (month shards) / this panel's (stock shards)
@@ -606,7 +684,7 @@ class GanStepFn(torch.autograd.Function):
             st = _stream(dev)
             if want_sdf or want_mom:
                 tens = _tensors(params)
-                _timed_call("dlap_cell_bwd", dev, ws.pp, _ptr(x), _ptr(R), _ptr(mask), _ptr(index), C.byref(tens),
+                _timed_call("dlap_cell_bwd", dev, ws.pp, _ptr(x), _ptr(R), _ptr(mask), _ptr(index), _ptr(ximg), C.byref(tens),
                             C.byref(mio), _ptr(row_stats), _ptr(dS2), _ptr(g_lc) if (has_q or q_given) else None,
                             _ptr(g_lu), _ptr(g_pr), _ptr(G), _ptr(scalars), int(opts.weighted_loss), int(want_sdf),
                             int(want_mom), _ptr(ws.wpart), _ptr(ws.dadc_part), prec, float(opts.dropout_p),

@@ -429,8 +429,8 @@ class GraphedStep:
     capture then fails with a stream-dependency error.
 
     The panel tensors are the ones passed in (full-batch training on a resident panel, as the reference's
-    loops do); copy new VALUES into them with ``.copy_()`` if needed, but keep the mask: its valid-cell index
-    is part of the capture.  With dropout on (model.train(), p > 0) the seed lives in device memory and the graph
+    loops do); copy new VALUES into them with ``.copy_()`` if needed (``step()`` notices a new version of the
+    characteristics and rebuilds their X images in place), but keep the mask: its valid-cell index is part of the capture.  With dropout on (model.train(), p > 0) the seed lives in device memory and the graph
     itself advances it, so every replay draws a fresh mask; month-sharded ranks start from the same seed.  A
     month-sharded model captures its NCCL all-reduces with the kernels; every rank must then replay in lock-step.
 
@@ -461,9 +461,13 @@ class GraphedStep:
         dev = individual_features.device
         side = torch.cuda.Stream(dev)
         side.wait_stream(torch.cuda.current_stream(dev))
-        with torch.cuda.stream(side):                      # warm-up off the capture stream (allocator, index)
-            for _ in range(max(warmup, 1)):
-                self._eager()
+        Fn.force_x_image = True                            # this panel is stepped on many times: X images at once
+        try:
+            with torch.cuda.stream(side):                  # warm-up off the capture stream (allocator, index, images)
+                for _ in range(max(warmup, 1)):
+                    self._eager()
+        finally:
+            Fn.force_x_image = False
         torch.cuda.current_stream(dev).wait_stream(side)
         torch.cuda.synchronize(dev)
         ws_launches = lambda: sum(w.launches for w in Fn._workspaces.values())
@@ -479,6 +483,9 @@ class GraphedStep:
             self.out = self._eager(zero=False, apply=True)
         # kernels of this library inside one replay
         self.launches = ws_launches() - l0 + ((optimizer.launches - o0) if optimizer is not None else 0)
+        # the capture holds the address of the panel's X images: new values copied into x need them rebuilt in place
+        self._ximg = Fn.cached_panel_image(individual_features)
+        self._x_version = individual_features._version
 
     def _eager(self, zero=True, apply=False):
         if zero:
@@ -504,6 +511,10 @@ class GraphedStep:
         return out
 
     def step(self):
+        x = self.args[1]
+        if self._ximg is not None and x._version != self._x_version:
+            Fn.rebuild_panel_image(x, *self._ximg)
+            self._x_version = x._version
         self.graph.replay()
         if self.optimizer is not None:      # the replay moved the parameters behind torch's back
             from .training import bump_versions

@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define DLAP_ABI_VERSION 4
+#define DLAP_ABI_VERSION 5
 
 enum {
   DLAP_OK = 0,
@@ -77,6 +77,8 @@ typedef struct dlap_plan {
   int64_t lstm_save_bytes;  /* float  [T, 6H]               */
   int64_t dpre_bytes;       /* float  [T, 4H]               */
   int64_t index_bytes;      /* int32  valid-cell index (dlap_panel_index), 16-B aligned */
+  int64_t image_bytes;      /* bytes  X images of every tile the index can hold (dlap_panel_image), 16-B aligned;
+                               0 when F > 46 (no tensor-core path) */
 } dlap_plan;
 
 /* The twelve parameter tensors in the reference's state_dict order.
@@ -154,6 +156,15 @@ int dlap_macro_fwd(const dlap_plan* plan, const float* macro, const dlap_tensors
  * the mask contract is src/data_loader.py:50-65.  Rebuild whenever the mask bytes change.  Two launches. */
 int dlap_panel_index(const dlap_plan* plan, const uint8_t* mask, int32_t* index, void* stream);
 
+/* The panel's characteristics in the tensor-core kernels' operand format, once per panel (the reference re-reads
+ * the same x every epoch, src/train.py:45-103; SURVEY.md 8 f4 "a bf16-split copy of x").  For every tile of the
+ * valid-cell index (<= 128 listed stocks of one month) `image` receives, at [tile * 24768), the 24,768 bytes the
+ * BF16X3 kernels otherwise build in shared memory per tile and step: the rows of x split into bf16 hi + lo
+ * (x = hi + lo up to 2^-18 |x|) in the no-swizzle canonical K-major layout, a ones column for the first-layer
+ * biases, rows past the end of a tile repeating its last row.  image: plan->image_bytes, 16-B aligned.  Requires
+ * F <= 46.  Rebuild whenever x or the index changes.  One launch; reads x once (listed rows only), HBM-bound. */
+int dlap_panel_image(const dlap_plan* plan, const float* x, const int32_t* index, void* image, void* stream);
+
 /* Panel ingest without a staging copy (the per-epoch `batch[k].to(device)` of src/train.py:69-75 for the
  * characteristics): x_host is the [T,N,F] panel in page-locked host memory that the device can address
  * (cudaHostAlloc / cudaHostRegister; torch: tensor.pin_memory()), x_dev the device panel.  The rows of unmasked
@@ -203,10 +214,13 @@ int dlap_macro_zscore(const float* macro_raw, int T, int M, float* mean, float* 
  * graph has to live in device memory.
  * index: dlap_panel_index output, required for BF16X3 (u and q are then written for unmasked cells only and
  * left-packed: the j-th unmasked stock of month t at [t*N + j]); ignored (may be NULL) for FP32 (dense u, q).
+ * x_image: dlap_panel_image output for this x and index, or NULL (BF16X3 only; ignored for FP32).  With it the
+ * kernel fetches each tile's operand image with one bulk copy instead of gathering and converting 128 rows of x
+ * (x is then not read at all); the results are bit-identical either way.
  * Launches: BF16X3 with macro, H = 4 and mio->sync: ONE (the recurrence is a CTA of the per-cell grid); otherwise the
  * macro kernel (or the constant-bias fill when M = 0), then the per-cell kernel. */
 int dlap_cell_fwd(const dlap_plan* plan, const float* x, const uint8_t* mask, const int32_t* index,
-                  const dlap_tensors* params, const dlap_macro_io* mio, float* u, float* q, int precision,
+                  const void* x_image, const dlap_tensors* params, const dlap_macro_io* mio, float* u, float* q, int precision,
                   float dropout_p, uint64_t dropout_seed, const uint64_t* dropout_seed_dev, void* stream);
 
 /* Every sum of the step over stocks (per month) and over months (per stock), one launch whose CTAs step through
@@ -285,9 +299,9 @@ int dlap_loss_finish_noalloc(const dlap_plan* plan, const double* col_part, int 
  * want_sdf / want_mom select the parameter groups (requires_grad semantics of src/train.py:309-312).
  * mio: a_t, c_t, month0, month_stride as for dlap_cell_fwd (nothing else is read).
  * Outputs: wpart (per-CTA weight-gradient partials), dadc_part (per-tile da_t | dc_t).
- * index: as for dlap_cell_fwd. */
+ * index, x_image: as for dlap_cell_fwd. */
 int dlap_cell_bwd(const dlap_plan* plan, const float* x, const float* R, const uint8_t* mask,
-                  const int32_t* index, const dlap_tensors* params, const dlap_macro_io* mio,
+                  const int32_t* index, const void* x_image, const dlap_tensors* params, const dlap_macro_io* mio,
                   const float* row_stats, const double* dS2, const float* gc, const float* gu,
                   const float* dpr_cot, const float* G, const float* scalars, int weighted_loss, int want_sdf,
                   int want_mom, float* wpart, float* dadc_part, int precision, float dropout_p,

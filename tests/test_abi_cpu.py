@@ -31,7 +31,7 @@ def test_library_builds_and_exports_every_declared_symbol():
     for n in names:
         assert hasattr(lib, n), f"{n} declared in include/dlap.h but not exported"
     assert set(_lib.EXPORTS) == set(names)
-    assert _lib.load().dlap_abi_version() == 4
+    assert _lib.load().dlap_abi_version() == 5
     assert _lib.load().dlap_error_string(-2).decode().startswith("dimension")
 
 
