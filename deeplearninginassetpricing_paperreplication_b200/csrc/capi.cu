@@ -39,6 +39,7 @@ cudaError_t launch_const_bias(const dlap_tensors* p, int T, float* a_t, float* c
 size_t macro_fwd_smem(int T, int M, int H);
 void set_bwd_tc_timeline(long long* p);
 void set_fwd_tc_timeline(long long* p);
+void set_bptt_timeline(long long* p);
 size_t macro_bwd_smem(int T, int H);
 }  // namespace dlap
 
@@ -72,6 +73,7 @@ int dlap_abi_version(void) { return DLAP_ABI_VERSION; }
 int dlap_debug_timeline(long long* stamps) {
   set_bwd_tc_timeline(stamps);
   set_fwd_tc_timeline(stamps ? stamps + 256 * 16 : nullptr);
+  set_bptt_timeline(stamps ? stamps + 3 * 256 * 16 : nullptr);
   return DLAP_OK;
 }
 

@@ -13,7 +13,9 @@ struct FinishParams {
   float* gW1; int ldw1; float* gW2; float* gb2; float* gW3; float* gb3; float* gWq; int ldwq, wq_off;
   float* dadc; int dadc_stride;            // row t of this panel goes to row t * dadc_stride of dadc
   // BPTT kernel only (macro_lstm.cu): CTAs that sum da_t | dc_t elements count themselves off here
-  unsigned int* counter; int dadc_ctas; int cooperative;
+  unsigned int* counter; int dadc_ctas; int cooperative;      // counter: four words, zero between launches
+  long long* tl;                           // diagnostics (dlap_debug_timeline): globaltimer stamps, or null
+  int fold_wgrad;                          // the summing CTAs go on to the month-summed gradients (macro_lstm.cu)
   // stock shards over peer memory (BPTT kernel only): the sums of this rank's partials are this rank's share; every
   // rank writes its shares into gpeer[rank] (two halves of gcap floats, used alternately, then 8 uint32 flags), a flag
   // barrier across the GPUs, and every rank adds everybody's shares in rank order.  gepoch[0]: launches so far,

@@ -9,6 +9,7 @@
 //            LSTM semantics: torch.nn.LSTM, gates i,f,g,o (src/model.py:39-45, :68).
 //   backward (one persistent CTA): dh_t = W1[:,F:]^T.da_t, BPTT on one warp, then the
 //            month-summed weight gradients (LSTM, W1[:,F:], b1, Wq[:,:M], bq).
+#include <cstdlib>
 #include "../../include/dlap.h"
 #include "dlap_common.cuh"
 #include "macro_role.cuh"
@@ -20,6 +21,200 @@ template <int H>
 __global__ void __launch_bounds__(MT, 1) macro_fwd_kernel(const MacroParams P) {
   extern __shared__ __align__(16) float sm[];
   macro_fwd_role<H>(P, sm);
+}
+
+// ---- month-summed gradients ------------------------------------------------------------------------------------
+// One warp per output row ("task"), lanes striding over the months, sums in a fixed order:
+//   task m < M           dW_ih[r][m] = sum_t dpre[t][r] macro[t][m]  (r < 4H) ; dWq[k][m] = sum_t dc_t[k] macro[t][m]
+//   task M + j, j < 64   dW1[j][F+k] = sum_t da_t[j] h_t[k] ; db1[j] = sum_t da_t[j]
+//   task M + 64 + r      dW_hh[r][k] = sum_t dpre[t][r] h_{t-1}[k] ; db_ih[r] = db_hh[r] = sum_t dpre[t][r]
+//   task M + 64 + 4H + q dbq[q] = sum_t dc_t[q]
+// Two acts.  What needs only da_t | dc_t (dWq, dW1's macro-state columns, db1, dbq) is finished in the first, and the
+// operands of the second (the task's macro column, h_{t-1}) are fetched into registers; the second act needs the
+// LSTM's pre-activation gradients dpre: it stages them in shared memory and is left with FMAs and one reduction.
+// As a kernel of its own (macro_wgrad_kernel) the acts simply follow each other; as the second job of the BPTT
+// kernel's summing CTAs each act waits for the recurrence CTA's word, so that only the short second act is left
+// when the serial chain is through.  da_t | dc_t and dpre are read past L1, never through the read-only path: the
+// same grid may have written them a moment ago.
+// dynamic smem: dc[T][9] | dpre[T][4H + 1]   (odd pitches: the month-strided reads are conflict-free)
+__host__ __device__ constexpr int pow2ceil(int v) { return v <= 1 ? 1 : v <= 2 ? 2 : v <= 4 ? 4 : v <= 8 ? 8 : v <= 16 ? 16 : 32; }
+__host__ __device__ constexpr int log2i(int v) { return v <= 1 ? 0 : 1 + log2i(v >> 1); }
+
+// K running sums per lane (K a power of two <= 32) -> their totals over the warp, with K + log2(32/K) shuffles
+// instead of 5 K: at every step a lane hands half of its values to its partner and adds the partner's other half.
+// Afterwards v[0] of lane l is the total of value number l >> (5 - log2 K).  Fixed order.
+template <int K>
+__device__ __forceinline__ void lanes_reduce(float (&v)[K], int lane) {
+  int off = 16;
+#pragma unroll
+  for (int k = K; k > 1; k >>= 1, off >>= 1) {
+    const int half = k >> 1;
+    const bool upper = (lane & off) != 0;
+#pragma unroll
+    for (int i = 0; i < half; ++i) {
+      const float send = upper ? v[i] : v[i + half], keep = upper ? v[i + half] : v[i];
+      v[i] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+    }
+  }
+#pragma unroll
+  for (; off >= 1; off >>= 1) v[0] += __shfl_xor_sync(0xffffffffu, v[0], off);
+}
+
+template <int H, int NTHR, class WaitDadc, class WaitDpre>
+__device__ __forceinline__ void wgrad_tasks(const MacroParams& P, float* sm, int task0, WaitDadc wait_dadc,
+                                            WaitDpre wait_dpre) {
+  constexpr int G4 = 4 * H, KP = pow2ceil(G4), DP = G4 + 1, VB = 8;
+  const int T = P.T, M = P.M, Hr = P.H, G4r = 4 * P.H;      // Hr = 0 (no macro input): only db1 and dbq exist
+  float* dcs = sm;                                          // [T][9]
+  float* dps = sm + (size_t)T * 9;                          // [T][DP]
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int task = task0 + warp;
+  const int type = task < M ? 0 : task < M + D1 ? 1 : task < M + D1 + G4r ? 2 : task < M + D1 + G4r + KM ? 3 : 4;
+  // ---- first act
+  wait_dadc();
+  if (P.have_mom)
+    for (int i = tid; i < T * KM; i += NTHR) dcs[(i >> 3) * 9 + (i & 7)] = __ldcg(P.dadc + (size_t)(i >> 3) * 72 + 64 + (i & 7));
+  __syncthreads();
+  float v[VB];                 // type 0: the task's macro column, months lane + 32 i
+  float hp[VB][H];             // type 2: h_{t-1}
+#pragma unroll
+  for (int i = 0; i < VB; ++i) {
+    v[i] = 0.f;
+#pragma unroll
+    for (int k = 0; k < H; ++k) hp[i][k] = 0.f;
+  }
+  if (type == 0) {
+    const int m = task;
+#pragma unroll
+    for (int i = 0; i < VB; ++i) {
+      const int t = lane + 32 * i;
+      if (t < T) v[i] = __ldg(P.macro + (size_t)t * M + m);
+    }
+    if (P.have_mom) {
+      float a[KM];
+#pragma unroll
+      for (int k = 0; k < KM; ++k) a[k] = 0.f;
+      for (int base = 0; base < T; base += 32 * VB) {
+#pragma unroll
+        for (int i = 0; i < VB; ++i) {
+          const int t = base + lane + 32 * i;
+          if (t < T) {
+            const float xv = base == 0 ? v[i] : __ldg(P.macro + (size_t)t * M + m);
+#pragma unroll
+            for (int k = 0; k < KM; ++k) a[k] = fmaf(dcs[t * 9 + k], xv, a[k]);
+          }
+        }
+      }
+      lanes_reduce<KM>(a, lane);
+      if ((lane & 3) == 0) P.gWq[(size_t)(lane >> 2) * P.ldwq + m] = a[0];
+    }
+  } else if (type == 1) {
+    if (P.have_sdf) {
+      const int j = task - M;
+      float a[H], b = 0.f;
+#pragma unroll
+      for (int k = 0; k < H; ++k) a[k] = 0.f;
+#pragma unroll 8
+      for (int t = lane; t < T; t += 32) {
+        const float d = __ldcg(P.dadc + (size_t)t * 72 + j);
+        b += d;
+#pragma unroll
+        for (int k = 0; k < H; ++k)
+          if (k < Hr) a[k] = fmaf(d, __ldg(P.save + (size_t)t * 6 * Hr + k), a[k]);
+      }
+      b = warp_sum(b);
+#pragma unroll
+      for (int k = 0; k < H; ++k) a[k] = warp_sum(a[k]);
+      if (lane == 0) {
+        P.gb1[j] = b;
+#pragma unroll
+        for (int k = 0; k < H; ++k)
+          if (k < Hr) P.gW1[(size_t)j * P.ldw1 + P.F + k] = a[k];
+      }
+    }
+  } else if (type == 2) {
+    if (P.have_sdf) {
+#pragma unroll
+      for (int i = 0; i < VB; ++i) {
+        const int t = lane + 32 * i;
+        if (t < T) {
+#pragma unroll
+          for (int k = 0; k < H; ++k)
+            hp[i][k] = (t > 0) ? __ldg(P.save + (size_t)(t - 1) * 6 * H + k) : (P.h0 ? __ldg(P.h0 + k) : 0.f);
+        }
+      }
+    }
+  } else if (type == 3) {
+    if (P.have_mom) {
+      const int q = task - M - D1 - G4r;
+      float b = 0.f;
+      for (int t = lane; t < T; t += 32) b += dcs[t * 9 + q];
+      b = warp_sum(b);
+      if (lane == 0) P.gbq[q] = b;
+    }
+  }
+  // ---- second act: everything that needs dpre
+  if (!P.have_sdf || Hr == 0) return;
+  wait_dpre();
+  for (int i = tid; i < T * G4; i += NTHR) dps[(i / G4) * DP + i % G4] = __ldcg(P.dpre + i);
+  __syncthreads();
+  if (type == 0) {
+    const int m = task;
+    float a[KP];
+#pragma unroll
+    for (int r = 0; r < KP; ++r) a[r] = 0.f;
+    for (int base = 0; base < T; base += 32 * VB) {
+#pragma unroll
+      for (int i = 0; i < VB; ++i) {
+        const int t = base + lane + 32 * i;
+        if (t < T) {
+          const float xv = base == 0 ? v[i] : __ldg(P.macro + (size_t)t * M + m);
+#pragma unroll
+          for (int r = 0; r < G4; ++r) a[r] = fmaf(dps[t * DP + r], xv, a[r]);
+        }
+      }
+    }
+    lanes_reduce<KP>(a, lane);
+    constexpr int SH = 5 - log2i(KP);
+    const int r = lane >> SH;
+    if ((lane & ((1 << SH) - 1)) == 0 && r < G4) P.gWih[(size_t)r * M + m] = a[0];
+  } else if (type == 2) {
+    const int r = task - M - D1;
+    float a[H], b = 0.f;
+#pragma unroll
+    for (int k = 0; k < H; ++k) a[k] = 0.f;
+    for (int base = 0; base < T; base += 32 * VB) {
+#pragma unroll
+      for (int i = 0; i < VB; ++i) {
+        const int t = base + lane + 32 * i;
+        if (t < T) {
+          const float d = dps[t * DP + r];
+          b += d;
+#pragma unroll
+          for (int k = 0; k < H; ++k) {
+            const float hv = base == 0 ? hp[i][k]
+                                       : ((t > 0) ? __ldg(P.save + (size_t)(t - 1) * 6 * H + k) : 0.f);
+            a[k] = fmaf(d, hv, a[k]);
+          }
+        }
+      }
+    }
+    b = warp_sum(b);
+#pragma unroll
+    for (int k = 0; k < H; ++k) a[k] = warp_sum(a[k]);
+    if (lane == 0) {
+      P.gbih[r] = b; P.gbhh[r] = b;
+#pragma unroll
+      for (int k = 0; k < H; ++k) P.gWhh[r * H + k] = a[k];
+    }
+  }
+}
+
+// H = max(P.H, 1): without macro input (P.H = 0) only db1 and dbq are left
+template <int H>
+__global__ void __launch_bounds__(256) macro_wgrad_kernel(const MacroParams P) {
+  extern __shared__ float sm[];
+  wgrad_tasks<H, 256>(P, sm, blockIdx.x * 8, [] {}, [] {});
 }
 
 // BPTT: one CTA.  Writes dpre[T][4H] (pre-activation gradients) to P.dpre.
@@ -53,6 +248,7 @@ __device__ __forceinline__ void spin_until(const unsigned int* word, unsigned in
     if (sys) asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(word) : "memory");
     else asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(word) : "memory");
     if ((int)(v - value) >= 0) return;
+    __nanosleep(100);
     unsigned long long now;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
     if (t0 == 0) t0 = now;
@@ -60,9 +256,19 @@ __device__ __forceinline__ void spin_until(const unsigned int* word, unsigned in
   }
 }
 
+#define BPTT_STAMP(k)                                                                   \
+  do {                                                                                   \
+    if (FIN.tl && threadIdx.x == 0) {                                                    \
+      unsigned long long now_;                                                           \
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now_));                          \
+      FIN.tl[(blockIdx.x + 1 == gridDim.x ? 0 : 16 * (1 + blockIdx.x)) + (k)] = (long long)now_; \
+    }                                                                                    \
+  } while (0)
+
 template <int H>
 __global__ void __launch_bounds__(MT, 1) macro_bptt_kernel(const MacroParams P, const FinishParams FIN) {
   extern __shared__ float sm[];
+  BPTT_STAMP(0);
   const bool peers = FIN.world > 1;
   const unsigned int launch_no = peers ? __ldcg(FIN.gepoch) + 1u : 0u;
   if (blockIdx.x + 1 < gridDim.x) {
@@ -92,6 +298,32 @@ __global__ void __launch_bounds__(MT, 1) macro_bptt_kernel(const MacroParams P, 
     if ((int)(blockIdx.x + 1) * MT > stride) {            // this CTA wrote da_t | dc_t elements
       __syncthreads();
       if (threadIdx.x == 0) { __threadfence(); atomicAdd(FIN.counter, 1u); }
+    }
+    BPTT_STAMP(1);
+    if (FIN.fold_wgrad) {
+      // Second job: the month-summed weight gradients (what used to be the macro_wgrad launch behind this kernel),
+      // sixteen tasks per CTA, paced by two words of the recurrence CTA (rows final; dpre written).  The last CTA
+      // through puts the words back to zero.
+      wgrad_tasks<H, MT>(
+          P, sm, blockIdx.x * (MT / 32),
+          [&] {                                     // every da_t | dc_t row is final
+            if (threadIdx.x == 0) spin_until(FIN.counter + 3, 1u, false);
+            __syncthreads();
+            BPTT_STAMP(2);
+          },
+          [&] {                                     // the chain is through: dpre is written
+            if (threadIdx.x == 0) spin_until(FIN.counter + 1, 1u, false);
+            __syncthreads();
+            BPTT_STAMP(3);
+          });
+      __syncthreads();
+      BPTT_STAMP(4);
+      if (threadIdx.x == 0) {
+        __threadfence();
+        if (atomicAdd(FIN.counter + 2, 1u) == gridDim.x - 2) {
+          atomicExch(FIN.counter + 1, 0u); atomicExch(FIN.counter + 2, 0u); atomicExch(FIN.counter + 3, 0u);
+        }
+      }
     }
     return;
   }
@@ -129,16 +361,22 @@ __global__ void __launch_bounds__(MT, 1) macro_bptt_kernel(const MacroParams P, 
     spin_until(FIN.counter, (unsigned int)FIN.dadc_ctas, false);
     atomicExch(FIN.counter, 0u);
     if (peers) *FIN.gepoch = launch_no;
+    if (FIN.fold_wgrad)                                     // the summing CTAs' first act may start
+      asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(FIN.counter + 3), "r"(1u) : "memory");
   }
   __syncthreads();
+  BPTT_STAMP(1);
   // pass 1, thread = (month, unit): dhe_t = W1[:,F:]^T . da_t and the local derivatives
   for (int i = tid; i < T * H; i += MT) {
     const int t = i / H, j = i % H;
     const float4* da4 = reinterpret_cast<const float4*>(P.dadc + (size_t)t * 72);
     float v0 = 0.f, v1 = 0.f;
-#pragma unroll 4
+    float4 d4[D1 / 4];                                   // the whole row in flight: one L2 round trip, not four
+#pragma unroll
+    for (int j4 = 0; j4 < D1 / 4; ++j4) d4[j4] = __ldcg(da4 + j4);      // may have been written by this grid a moment ago
+#pragma unroll
     for (int j4 = 0; j4 < D1 / 4; ++j4) {
-      const float4 d = __ldcg(da4 + j4);                 // may have been written by this grid a moment ago
+      const float4 d = d4[j4];
       v0 = fmaf(w1m[(4 * j4) * H + j], d.x, v0);     v1 = fmaf(w1m[(4 * j4 + 1) * H + j], d.y, v1);
       v0 = fmaf(w1m[(4 * j4 + 2) * H + j], d.z, v0); v1 = fmaf(w1m[(4 * j4 + 3) * H + j], d.w, v1);
     }
@@ -173,6 +411,7 @@ __global__ void __launch_bounds__(MT, 1) macro_bptt_kernel(const MacroParams P, 
     }
   }
   __syncthreads();
+  BPTT_STAMP(2);
   // The chain over the months, as a chunked scan.  One step maps the carried state s = (dh_rec, dc) in R^2H to
   // M_t s + b_t (see above), so a run of steps is again an affine map.  (1) every warp composes the map of its own
   // chunk of months -- lane j < 2H pushes the unit vector e_j through the chunk's steps (column j of the composite
@@ -249,6 +488,7 @@ __global__ void __launch_bounds__(MT, 1) macro_bptt_kernel(const MacroParams P, 
     }
   }
   __syncthreads();
+  BPTT_STAMP(3);
   // gate gradients, thread = (month, unit)
   for (int i = tid; i < T * H; i += MT) {
     const int t = i / H, j = i % H;
@@ -257,120 +497,14 @@ __global__ void __launch_bounds__(MT, 1) macro_bptt_kernel(const MacroParams P, 
     float* dp = P.dpre + (size_t)t * G4;
     dp[j] = dcn * y[4]; dp[H + j] = dcn * y[5]; dp[2 * H + j] = dcn * y[6]; dp[3 * H + j] = dht * y[7];
   }
-}
-
-// Month-summed gradients, one warp per output row ("task"), lanes striding over the months, fixed-tree warp
-// sums; eight tasks per CTA, the coefficients (dpre | dc_t) staged in shared memory once per CTA:
-//   task m < M           dW_ih[r][m] = sum_t dpre[t][r] macro[t][m]  (r < 4H) ; dWq[k][m] = sum_t dc_t[k] macro[t][m]
-//   task M + j, j < 64   dW1[j][F+k] = sum_t da_t[j] h_t[k] ; db1[j] = sum_t da_t[j]
-//   task M + 64 + r      dW_hh[r][k] = sum_t dpre[t][r] h_{t-1}[k] ; db_ih[r] = db_hh[r] = sum_t dpre[t][r]
-//   task M + 64 + 4H + q dbq[q] = sum_t dc_t[q]
-// dynamic smem: coef[T][NR + 1]   (NR = 4H + 8; the odd pitch keeps the month-strided reads conflict-free)
-__global__ void __launch_bounds__(256) macro_wgrad_kernel(const MacroParams P) {
-  extern __shared__ float sm[];
-  const int T = P.T, M = P.M, H = P.H, G4 = 4 * H, NR = G4 + KM, CP = NR + 1;
-  float* coef = sm;
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  for (int i0 = tid; i0 < T * NR; i0 += 4 * 256) {         // four independent loads per thread and round
-    float v[4];
-#pragma unroll
-    for (int u = 0; u < 4; ++u) {
-      const int i = min(i0 + u * 256, T * NR - 1), t = i / NR, r = i % NR;
-      v[u] = (r < G4) ? (P.have_sdf ? __ldcg(P.dpre + (size_t)t * G4 + r) : 0.f)
-                      : (P.have_mom ? __ldg(P.dadc + (size_t)t * 72 + 64 + (r - G4)) : 0.f);
+  if (FIN.fold_wgrad) {                              // dpre is complete: release the summing CTAs into their second act
+    __syncthreads();
+    BPTT_STAMP(4);
+    if (tid == 0) {
+      __threadfence();
+      asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(FIN.counter + 1), "r"(1u) : "memory");
     }
-#pragma unroll
-    for (int u = 0; u < 4; ++u) {
-      const int i = i0 + u * 256;
-      if (i < T * NR) coef[(i / NR) * CP + i % NR] = v[u];
-    }
-  }
-  __syncthreads();
-  const int task = blockIdx.x * 8 + warp;
-  if (task < M) {
-    const int m = task;
-    float acc[4 * HMAX + KM];
-#pragma unroll
-    for (int r = 0; r < 4 * HMAX + KM; ++r) acc[r] = 0.f;
-    for (int t0 = lane; t0 < T; t0 += 4 * 32) {              // four months' loads in flight per lane
-      float v[4];
-#pragma unroll
-      for (int u = 0; u < 4; ++u) v[u] = __ldg(P.macro + (size_t)min(t0 + 32 * u, T - 1) * M + m);
-#pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        const int t = t0 + 32 * u;
-        if (t < T) {
-          const float* c = coef + t * CP;
-#pragma unroll
-          for (int r = 0; r < 4 * HMAX + KM; ++r)
-            if (r < NR) acc[r] = fmaf(c[r], v[u], acc[r]);
-        }
-      }
-    }
-#pragma unroll
-    for (int r = 0; r < 4 * HMAX + KM; ++r) {
-      if (r < NR) {
-        const float v = warp_sum(acc[r]);
-        if (lane == 0) {
-          if (r < G4) { if (P.have_sdf) P.gWih[(size_t)r * M + m] = v; }
-          else if (P.have_mom) P.gWq[(size_t)(r - G4) * P.ldwq + m] = v;
-        }
-      }
-    }
-  } else if (task < M + D1) {
-    if (!P.have_sdf) return;
-    const int j = task - M;
-    float a[HMAX], b = 0.f;
-#pragma unroll
-    for (int k = 0; k < HMAX; ++k) a[k] = 0.f;
-    for (int t = lane; t < T; t += 32) {
-      const float d = __ldg(P.dadc + (size_t)t * 72 + j);
-      b += d;
-#pragma unroll
-      for (int k = 0; k < HMAX; ++k)
-        if (k < H) a[k] = fmaf(d, __ldg(P.save + (size_t)t * 6 * H + k), a[k]);
-    }
-    b = warp_sum(b);
-#pragma unroll
-    for (int k = 0; k < HMAX; ++k) a[k] = warp_sum(a[k]);
-    if (lane == 0) {
-      P.gb1[j] = b;
-#pragma unroll
-      for (int k = 0; k < HMAX; ++k)
-        if (k < H) P.gW1[(size_t)j * P.ldw1 + P.F + k] = a[k];
-    }
-  } else if (task < M + D1 + G4) {
-    if (!P.have_sdf) return;
-    const int r = task - M - D1;
-    float a[HMAX], b = 0.f;
-#pragma unroll
-    for (int k = 0; k < HMAX; ++k) a[k] = 0.f;
-    for (int t = lane; t < T; t += 32) {
-      const float d = coef[t * CP + r];
-      b += d;
-#pragma unroll
-      for (int k = 0; k < HMAX; ++k)
-        if (k < H) {
-          const float hp = (t > 0) ? __ldg(P.save + (size_t)(t - 1) * 6 * H + k) : (P.h0 ? __ldg(P.h0 + k) : 0.f);
-          a[k] = fmaf(d, hp, a[k]);
-        }
-    }
-    b = warp_sum(b);
-#pragma unroll
-    for (int k = 0; k < HMAX; ++k) a[k] = warp_sum(a[k]);
-    if (lane == 0) {
-      P.gbih[r] = b; P.gbhh[r] = b;
-#pragma unroll
-      for (int k = 0; k < HMAX; ++k)
-        if (k < H) P.gWhh[r * H + k] = a[k];
-    }
-  } else if (task < M + D1 + G4 + KM) {
-    if (!P.have_mom) return;
-    const int q = task - M - D1 - G4;
-    float b = 0.f;
-    for (int t = lane; t < T; t += 32) b += coef[t * CP + G4 + q];
-    b = warp_sum(b);
-    if (lane == 0) P.gbq[q] = b;
+    BPTT_STAMP(5);
   }
 }
 
@@ -397,6 +531,11 @@ static cudaError_t launch_bptt_h(const MacroParams& P, const FinishParams& FIN, 
   if (FIN.dadc_part) {
     const int stride = wp_stride(round4(FIN.F)), total = stride + FIN.T * 72;
     extra = (total + MT - 1) / MT;
+    if (FIN.fold_wgrad) {                                   // enough CTAs for the month-summed gradients' tasks
+      const int per = MT / 32;
+      const int tasks = P.M + D1 + 4 * P.H + KM, need = (tasks + per - 1) / per;
+      if (extra < need) extra = need;
+    }
     F2.dadc_ctas = extra - stride / MT;                     // CTAs whose range reaches past the weight partials
     F2.nfin = extra;
     if (F2.world > 1 && total > F2.gcap) return cudaErrorInvalidValue;
@@ -431,21 +570,39 @@ static cudaError_t launch_bptt(const MacroParams& P, const FinishParams& FIN, cu
 }
 cudaError_t launch_grad_finish(const FinishParams& FIN, cudaStream_t st);      // reduce.cu
 // FIN.dadc_part / FIN.wpart non-null: the per-cell kernel's partials have not been summed yet
-cudaError_t launch_macro_bwd(const MacroParams& P, const FinishParams& FIN, cudaStream_t st) {
+template <int H>
+static cudaError_t launch_wgrad_h(const MacroParams& P, cudaStream_t st) {
+  const size_t smem = (size_t)P.T * (9 + 4 * H + 1) * 4;
+  cudaError_t e = cudaFuncSetAttribute(macro_wgrad_kernel<H>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return e;
+  const int tasks = P.M + D1 + 4 * P.H + KM;
+  macro_wgrad_kernel<H><<<(tasks + 7) / 8, 256, smem, st>>>(P);
+  return cudaGetLastError();
+}
+static cudaError_t launch_wgrad(const MacroParams& P, cudaStream_t st) {
+  if (P.H == 0) return launch_wgrad_h<1>(P, st);
+  DLAP_H_SWITCH(launch_wgrad_h, P, st)
+}
+
+static long long* g_timeline_bptt = nullptr;
+void set_bptt_timeline(long long* p) { g_timeline_bptt = p; }
+
+cudaError_t launch_macro_bwd(const MacroParams& P, const FinishParams& FIN0, cudaStream_t st) {
+  FinishParams FIN = FIN0;
+  FIN.tl = g_timeline_bptt;
+  // the month-summed gradients ride in the BPTT kernel whenever it has summing CTAs beside the recurrence -- and the
+  // grid is launched co-resident: those CTAs then wait for the recurrence's CTA, which is the last one of the grid
+  FIN.fold_wgrad = (P.have_sdf && P.H > 0 && FIN.dadc_part && FIN.counter && FIN.cooperative) ? 1 : 0;
+  if (const char* ev = getenv("DLAP_FOLD_WGRAD")) FIN.fold_wgrad = FIN.fold_wgrad && atoi(ev) != 0;
   if (P.have_sdf && P.H > 0) {
     cudaError_t e = launch_bptt(P, FIN, st);
     if (e != cudaSuccess) return e;
+    if (FIN.fold_wgrad) return cudaSuccess;
   } else if (FIN.dadc_part) {           // no recurrence to hide the sums behind: the plain finishing kernel
     cudaError_t e = launch_grad_finish(FIN, st);
     if (e != cudaSuccess) return e;
   }
-  const int NR = 4 * P.H + KM;
-  const size_t smem = (size_t)P.T * (NR + 1) * 4;
-  cudaError_t e = cudaFuncSetAttribute(macro_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  if (e != cudaSuccess) return e;
-  const int tasks = P.M + D1 + 4 * P.H + KM;
-  macro_wgrad_kernel<<<(tasks + 7) / 8, 256, smem, st>>>(P);
-  return cudaGetLastError();
+  return launch_wgrad(P, st);
 }
 
 // M = 0 (macro_features=None, src/model.py:247-257, :517-518): the per-month biases are just b1 / bq.

@@ -62,7 +62,7 @@ constexpr int MT = 512;    // threads of the single-CTA macro kernels
 //             (the only warp that writes global memory month by month).  With months_ready the
 //             progress is published device-wide, so that a per-cell forward kernel launched beside this one
 //             (another stream) can start on the first months while the later ones are still being computed.
-constexpr int PUB = 8;
+constexpr int PUB = 16;
 constexpr int NPROJ = 11;
 __device__ __forceinline__ void st_release_cta(int* p, int v) {
   asm volatile("st.release.cta.shared.s32 [%0], %1;" ::"r"((uint32_t)__cvta_generic_to_shared(p)), "r"(v) : "memory");

@@ -131,7 +131,7 @@ class Workspace:
         self.row_part = f64(p.row_part_bytes)
         self.bar = torch.zeros(max(p.bar_bytes // 4, 1), dtype=torch.int32, device=device)   # dlap_step_reduce's barrier words
         self.sync = torch.zeros(2, dtype=torch.int32, device=device)     # progress words of the fused dlap_cell_fwd
-        self.counter = torch.zeros(1, dtype=torch.int32, device=device)  # dlap_macro_bwd's (finished da_t | dc_t rows)
+        self.counter = torch.zeros(4, dtype=torch.int32, device=device)  # dlap_macro_bwd's progress words
         self.launches = 0          # kernels launched through this workspace (bench bookkeeping)
 
     def panel_index(self, mask: torch.Tensor) -> torch.Tensor:
@@ -719,7 +719,8 @@ class GanStepFn(torch.autograd.Function):
                                 _ptr(dadc), _ptr(ws.dpre), int(want_sdf), int(want_mom), C.byref(gt), _ptr(ws.wpart),
                                 _ptr(ws.dadc_part), _ptr(index), prec, _ptr(ws.counter),
                                 C.byref(sh.peers.g) if sh is not None else None, st)
-                    ws.launches += 2
+                    # the month-summed gradients ride in the BPTT kernel when its grid is launched co-resident
+                    ws.launches += 1 if (want_sdf and M > 0 and ws.plan.cooperative) else 2
                 else:   # exchange 2: per-cell weight grads + every month's da_t | dc_t row
                     dadc_all = buf[:head].view(T_rows, 72)
                     t0, stride = (0, 1) if stocks else (sh.t0, sh.stride)

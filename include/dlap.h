@@ -322,10 +322,12 @@ int dlap_grad_finish(const dlap_plan* plan, const float* wpart, const float* dad
  * wpart / dadc_part non-NULL (with the index and precision dlap_cell_bwd ran with; the plan is then also the
  * per-cell plan): the call also does dlap_grad_finish's work -- dadc [T,72] becomes an output -- on extra CTAs of
  * the BPTT kernel: the recurrence's CTA stages its tables meanwhile and waits for the da_t | dc_t rows, the
- * weight-gradient sums run beside the serial chain.  counter (device, one uint32, zero when the call starts and
- * zero again when it has finished; required with partials).  peers (stock shards over peer memory, see dlap_peers;
+ * weight-gradient sums run beside the serial chain; with plan->cooperative those CTAs then go on to the month-summed
+ * gradients as soon as the chain is through (one launch instead of two).  counter (device, four uint32, zero when
+ * the call starts and zero again when it has finished; required with partials).  peers (stock shards over peer memory, see dlap_peers;
  * NULL otherwise; needs the partials): the sums of the partials are this rank's share only, and the same kernel adds
- * all ranks' shares -- the backward pass' one exchange -- before the recurrence starts.  Two launches. */
+ * all ranks' shares -- the backward pass' one exchange -- before the recurrence starts.  One launch (partials and
+ * plan->cooperative), else two. */
 int dlap_macro_bwd(const dlap_plan* plan, const float* macro, const dlap_tensors* params, const float* h0,
                    const float* c0, const float* lstm_save, float* dadc, float* dpre, int want_sdf,
                    int want_mom, const dlap_tensors* grads, const float* wpart, const float* dadc_part,

@@ -13,14 +13,15 @@ model = AssetPricingGAN({"macro_feature_dim": 178, "individual_feature_dim": 46,
                          "b200_precision": "bf16x3"}).to(dev)
 for _ in range(3):
     model.zero_grad(); model(macro, x, R, mask)["loss"].backward()
-st = torch.zeros(3 * 256 * 16, dtype=torch.int64, device=dev)
+st = torch.zeros(4 * 256 * 16, dtype=torch.int64, device=dev)
 _lib.call("dlap_debug_timeline", st.data_ptr())
 model.zero_grad(); model(macro, x, R, mask)["loss"].backward()
 torch.cuda.synchronize()
 _lib.call("dlap_debug_timeline", None)
 s = st[:256 * 16].view(256, 16).cpu().double()
 f = st[256 * 16:2 * 256 * 16].view(256, 16).cpu().double()
-gb = st[2 * 256 * 16:].view(256, 16).cpu().double()
+gb = st[2 * 256 * 16:3 * 256 * 16].view(256, 16).cpu().double()
+bp = st[3 * 256 * 16:].view(256, 16).cpu()
 ntile = int((s[:, 0] > 0).sum())
 lo, hi = 5, max(ntile - 5, 7)
 print('tiles of CTA 0:', ntile)
@@ -65,3 +66,12 @@ cta = st[2 * 4096 + 2048:2 * 4096 + 2048 + 148].cpu()
 cyc = (cta >> 8).double(); nt = (cta & 255)
 print("BWD per-CTA active cycles: min", float(cyc.min()), "median", float(cyc.median()), "max", float(cyc.max()),
       "| tiles per CTA min/max", int(nt.min()), int(nt.max()), "| slowest CTAs", torch.topk(cyc, 5).indices.tolist())
+
+t0 = int(bp[0, 0])
+if t0:
+    print("BPTT recurrence CTA (ns from its start): dadc rows complete", int(bp[0, 1]) - t0, "| records built", int(bp[0, 2]) - t0,
+          "| scan done", int(bp[0, 3]) - t0, "| dpre written", int(bp[0, 4]) - t0, "| flag released", int(bp[0, 5]) - t0)
+    for c in (0, 5, 11, 12, 16, 30, 48):
+        r = bp[1 + c]
+        if int(r[0]):
+            print(f"BPTT summing CTA {c}: start {int(r[0]) - t0} | sums done {int(r[1]) - t0} | rows final seen {int(r[2]) - t0} | dpre seen {int(r[3]) - t0} | tasks done {int(r[4]) - t0}")

@@ -75,7 +75,9 @@ def test_graphed_epoch_matches_the_eager_torch_loop(precision, phase, dropout):
     before = [p.detach().clone() for p in pb]
     gs = b.train().graphed_step(macro, x, R, mask, phase=phase, optimizer=opt, max_norm=1.0)
     assert all(torch.equal(p, q) for p, q in zip(pb, before))          # warm-up and capture moved nothing
-    assert gs.launches == (6 if precision == "bf16x3" else 7)
+    # per-cell forward (+ the LSTM of its own for fp32), reductions, per-cell backward, month-level backward, clip + Adam;
+    # phase 2 freezes the SDF net: no BPTT kernel for the month-summed gradients to ride in, so they are one launch more
+    assert gs.launches == (5 if precision == "bf16x3" else 6) + (1 if phase == "moment" else 0)
     a.train()
     for epoch in range(20):
         ropt.zero_grad()
