@@ -131,7 +131,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
     headers = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cuh", ".h"))]
     headers.append(os.path.join(ROOT, "include", "dlap.h"))
     hdr_time = max(os.path.getmtime(h) for h in headers)
-    flags = [f for f in NVCC_FLAGS if f != "-shared"]
+    flags = [f for f in NVCC_FLAGS if f != "-shared"] + os.environ.get("DLAP_NVCC_EXTRA", "").split()
 
     def compile_one(src):
         obj = os.path.join(OBJ_DIR, src[:-3] + ".o")

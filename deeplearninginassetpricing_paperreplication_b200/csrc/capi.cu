@@ -40,6 +40,7 @@ size_t macro_fwd_smem(int T, int M, int H);
 void set_bwd_tc_timeline(long long* p);
 void set_fwd_tc_timeline(long long* p);
 void set_bptt_timeline(long long* p);
+void set_reduce_timeline(long long* p);
 size_t macro_bwd_smem(int T, int H);
 }  // namespace dlap
 
@@ -74,6 +75,7 @@ int dlap_debug_timeline(long long* stamps) {
   set_bwd_tc_timeline(stamps);
   set_fwd_tc_timeline(stamps ? stamps + 256 * 16 : nullptr);
   set_bptt_timeline(stamps ? stamps + 3 * 256 * 16 : nullptr);
+  set_reduce_timeline(stamps ? stamps + 3 * 256 * 16 + 2048 : nullptr);
   return DLAP_OK;
 }
 

@@ -180,7 +180,7 @@ __device__ __forceinline__ void image_role(const CellParams& P, int lane, const 
     mbar_wait(xop_empty + sl, (use & 1) ^ 1);
     if (lane == 0) {
       mbar_expect_tx(xop_full + sl, 2 * X_IMG);                         // arrival 1 of NB, and the bytes to come
-      bulk_g2s(x0 + (size_t)sl * 2 * X_IMG, P.ximg + (size_t)tile * (2 * X_IMG), 2 * X_IMG, xop_full + sl);
+      bulk_g2s_stream(x0 + (size_t)sl * 2 * X_IMG, P.ximg + (size_t)tile * (2 * X_IMG), 2 * X_IMG, xop_full + sl);
     }
     // bias column a_t | c_t | 0 of this tile's month (the recurrence that makes a_t may still be running)
     const size_t row = (size_t)mc.t * P.months_stride;

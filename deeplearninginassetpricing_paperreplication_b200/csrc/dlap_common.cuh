@@ -68,6 +68,18 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t by
       : "memory");
 }
 
+// the same for data that is read ONCE per kernel (the panel's X images): the L2 lines are marked evict-first, so the
+// stream does not push out what the next kernel wants to find there (u, q: 35 MB written beside 190 MB streamed)
+__device__ __forceinline__ void bulk_g2s_stream(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+  uint64_t policy;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(policy));
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;" ::
+          "r"(smem_u32(dst)),
+      "l"(src), "r"(bytes), "r"(smem_u32(bar)), "l"(policy)
+      : "memory");
+}
+
 // ---- smem tile layouts -----------------------------------------------------------------
 // Activation tiles are stored "unit-major": row = unit (k), 128 cells per row, the 4-cell
 // groups XOR-swizzled by the row so that (a) a thread storing its 4 cells for units

@@ -14,6 +14,8 @@
 // Every cross-CTA sum has a fixed order (no float atomics): results are reproducible run to run.
 // Data written in one phase and read in a later one is read with ld.cg / ld.acquire, never through the
 // read-only (nc) path.
+#include <cstdlib>
+#include <type_traits>
 #include "../../include/dlap.h"
 #include "dlap_common.cuh"
 #include "cell_f32.cuh"
@@ -61,10 +63,20 @@ struct ReduceParams {
   double* peer[8];
   unsigned int* epoch;       // launches so far (device, this rank's own): the value the flags are raised to
   int phase_lo, phase_hi;    // inclusive
+  long long* tl;             // diagnostics (dlap_debug_timeline): globaltimer stamps of CTA 0 and of the last CTA, or null
 };
 
 namespace {
 constexpr int RT = 256;
+
+#define RED_STAMP(k)                                                                                    \
+  do {                                                                                                    \
+    if (P.tl && threadIdx.x == 0 && (blockIdx.x == 0 || blockIdx.x == gridDim.x - 1)) {                   \
+      unsigned long long now_;                                                                            \
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now_));                                           \
+      P.tl[(blockIdx.x == 0 ? 0 : 32) + (k)] = (long long)now_;                                           \
+    }                                                                                                     \
+  } while (0)
 
 __device__ __forceinline__ float S_of(const float* rs, int weighted, float n_bar, float* pr_out) {
   const float P = __ldcg(rs + RS_P), nt = __ldcg(rs + RS_NT);
@@ -127,6 +139,7 @@ __device__ __forceinline__ double ld_peer(const double* p) {
 }
 }  // namespace
 
+template <int MB_, int ACC_>
 __global__ void __launch_bounds__(RT, 4) step_reduce_kernel(const ReduceParams P) {
   extern __shared__ float sm[];            // phase 1: S_t then mu_t of this CTA's month chunk
   __shared__ double red[32];
@@ -137,6 +150,7 @@ __global__ void __launch_bounds__(RT, 4) step_reduce_kernel(const ReduceParams P
   const bool peers = P.stock_shard && P.world > 1;
   const unsigned int launch_no = peers ? __ldcg(P.epoch) + 1u : 0u;
 
+  RED_STAMP(0);
   // ---------------------------------------------------------------- phase 0: row sums
   // A month is cut into nseg segments of its cells so that every CTA has work; the CTA that finishes a month's
   // last segment (a counter per month) adds the segments' partial sums in segment order.
@@ -152,10 +166,23 @@ __global__ void __launch_bounds__(RT, 4) step_reduce_kernel(const ReduceParams P
         const int cnt = __ldg(P.index + idx_off_cnt(T) + t);
         const int per = (cnt + nseg - 1) / nseg, j0 = seg * per, j1 = min(cnt, j0 + per);
         const int* vrow = P.index + idx_off_vidx(T) + base;
-#pragma unroll 4
-        for (int j = j0 + tid; j < j1; j += RT) {
-          const float uv = __ldcg(P.u + base + j), r = __ldg(P.R + base + __ldg(vrow + j));
-          v[1] += (double)uv; v[2] += (double)uv * (double)r; v[3] += (double)r;
+        for (int jb = j0 + tid; jb < j1; jb += 8 * RT) {        // stock numbers and u of eight cells, then their R
+          int ii[8];
+          float uu[8], rr[8];
+#pragma unroll
+          for (int b = 0; b < 8; ++b) {
+            const int j = min(jb + b * RT, j1 - 1);
+            ii[b] = __ldg(vrow + j);
+            uu[b] = __ldcg(P.u + base + j);
+          }
+#pragma unroll
+          for (int b = 0; b < 8; ++b) rr[b] = __ldg(P.R + base + ii[b]);
+#pragma unroll
+          for (int b = 0; b < 8; ++b) {
+            if (jb + b * RT < j1) {
+              v[1] += (double)uu[b]; v[2] += (double)uu[b] * (double)rr[b]; v[3] += (double)rr[b];
+            }
+          }
         }
         v[0] = tid == 0 ? (double)max(j1 - j0, 0) : 0.0;
       } else {
@@ -201,7 +228,9 @@ __global__ void __launch_bounds__(RT, 4) step_reduce_kernel(const ReduceParams P
         }
       }
     }
+    RED_STAMP(1);
     if (P.phase_hi >= 1) grid_sync(P.bar, ++nsync);
+    RED_STAMP(2);
   }
 
   // ---------------------------------------------------------------- phase 1: N_bar, S_t; column partial sums
@@ -263,6 +292,7 @@ __global__ void __launch_bounds__(RT, 4) step_reduce_kernel(const ReduceParams P
         if (!P.xbuf) P.scalars[SC_SHARPE] = (T > 1) ? (float)(mean / (sqrt(s2 / (double)(T - 1)) + 1e-8)) : nanf("");
       }
     }
+    RED_STAMP(3);
     const int nb = (N + RT - 1) / RT, nw = (N + 31) >> 5;
     const int tchunk = P.tchunk;
     for (int unit = blockIdx.x; unit < nb * P.nsplit; unit += gridDim.x) {
@@ -278,39 +308,87 @@ __global__ void __launch_bounds__(RT, 4) step_reduce_kernel(const ReduceParams P
       const int i = bx * RT + tid;
       const bool in = i < N;                   // whole warps stay: the packed position comes from a ballot
       const int* rank = P.index ? P.index + idx_off_rank(T, N) + (i >> 5) : nullptr;
-      double acc[KM + 2];
+      // Sums over the chunk's months.  ACC_ 0: doubles (ten conversions + ten double adds per stock-month on the
+      // quarter-rate pipe); 1: plain fp32 within the chunk; 2: fp32 with Kahan compensation (acc - cmp carries what a
+      // double would).  The chunk totals are handed on as doubles either way.
+      typedef typename std::conditional<ACC_ == 0, double, float>::type acc_t;
+      acc_t acc[KM + 2];
+      float cmp[ACC_ == 2 ? KM + 2 : 1];
 #pragma unroll
-      for (int k = 0; k < KM + 2; ++k) acc[k] = 0.0;
-      // latency-bound (two dependent round trips per month: mask, then values): branch-free body, masked lanes
-      // load from a clamped in-bounds position and drop the values, the unrolled months overlap their loads
+      for (int k = 0; k < KM + 2; ++k) { acc[k] = 0; if (ACC_ == 2) cmp[k] = 0.f; }
+      auto add = [&](int k, float x) {
+        if (ACC_ == 2) {
+          const float y = x - cmp[k], t = (float)acc[k] + y;
+          cmp[k] = (t - (float)acc[k]) - y;
+          acc[k] = t;
+        } else {
+          acc[k] += (acc_t)x;
+        }
+      };
+      // Latency-bound: per month a mask byte and a rank word, then (at a position that depends on them) u, R and
+      // eight q values.  Months go in batches of MB: the batch's keys are already in registers (fetched while the
+      // previous batch's values were in flight), all of its value loads are issued before anything is stored -- a
+      // store to w_out in between would pin every later load behind it, the pointers may alias as far as the
+      // compiler knows -- so a batch costs ONE round trip.  Masked lanes load from a clamped in-bounds position and
+      // drop the values.
+      constexpr int MB = MB_;
       const size_t ic = in ? (size_t)i : (size_t)N - 1;
-#pragma unroll 4
-      for (int t = t0; t < t1; ++t) {
-        const size_t gi = (size_t)t * N + ic;
-        const float S = sm[t - t0];
-        const bool live = in && P.mask[gi] != 0;
-        const unsigned b = __ballot_sync(0xffffffffu, live);
-        size_t vi = gi;
-        if (P.index) vi = (size_t)t * N + __ldg(rank + (size_t)t * nw) + __popc(b & ((1u << lane) - 1u));
-        if (vi >= plane) vi = plane - 1;       // a masked lane behind the last listed stock of the last month
-        const float uv = P.w_out ? __ldcg(P.u + vi) : 0.f;
-        const float r = __ldg(P.R + gi);
-        float qv[KM];
+      const unsigned below = (1u << lane) - 1u;
+      uint8_t mk[MB];
+      int rk[MB];
+      auto load_keys = [&](int tb) {
 #pragma unroll
-        for (int k = 0; k < KM; ++k) qv[k] = P.q ? __ldcg(P.q + k * plane + (P.q_dense ? gi : vi)) : 0.f;
-        if (P.w_out && in) P.w_out[gi] = live ? (uv - sm[tchunk + t - t0]) : 0.f;
-        acc[KM] += live ? (double)(r * S) : 0.0;
-        acc[KM + 1] += live ? 1.0 : 0.0;
+        for (int b = 0; b < MB; ++b) {
+          const int tt = min(tb + b, t1 - 1);
+          mk[b] = P.mask[(size_t)tt * N + ic];
+          rk[b] = P.index ? __ldg(rank + (size_t)tt * nw) : 0;
+        }
+      };
+      load_keys(t0);
+      for (int t = t0; t < t1; t += MB) {
+        bool live[MB];
+        uint32_t gi[MB], vi[MB];                 // T * N < 2^32 (dlap_make_plan)
 #pragma unroll
-        for (int k = 0; k < KM; ++k) acc[k] += live ? (double)((qv[k] * r) * S) : 0.0;
+        for (int b = 0; b < MB; ++b) {
+          const int tt = min(t + b, t1 - 1);
+          live[b] = in && (t + b < t1) && mk[b] != 0;
+          const unsigned bal = __ballot_sync(0xffffffffu, live[b]);
+          gi[b] = (uint32_t)((size_t)tt * N + ic);
+          uint32_t v = P.index ? (uint32_t)((size_t)tt * N) + (uint32_t)rk[b] + (uint32_t)__popc(bal & below) : gi[b];
+          if ((size_t)v >= plane) v = (uint32_t)(plane - 1);      // a masked lane behind the last listed stock of the last month
+          vi[b] = v;
+        }
+        float uv[MB], r[MB], qv[MB][KM];
+#pragma unroll
+        for (int b = 0; b < MB; ++b) {
+          uv[b] = P.w_out ? __ldcg(P.u + vi[b]) : 0.f;
+          r[b] = __ldg(P.R + gi[b]);
+#pragma unroll
+          for (int k = 0; k < KM; ++k) qv[b][k] = P.q ? __ldcg(P.q + k * plane + (P.q_dense ? gi[b] : vi[b])) : 0.f;
+        }
+        if (t + MB < t1) load_keys(t + MB);      // the next batch's keys ride with this batch's values
+#pragma unroll
+        for (int b = 0; b < MB; ++b) {
+          if (t + b < t1) {
+            const int tl = t + b - t0;
+            const float S = sm[tl];
+            if (P.w_out && in) P.w_out[gi[b]] = live[b] ? (uv[b] - sm[tchunk + tl]) : 0.f;
+            add(KM, live[b] ? (r[b] * S) : 0.f);
+            acc[KM + 1] += live[b] ? (acc_t)1 : (acc_t)0;           // a count: exact
+#pragma unroll
+            for (int k = 0; k < KM; ++k) add(k, live[b] ? ((qv[b][k] * r[b]) * S) : 0.f);
+          }
+        }
       }
       if (in) {
         double* out = P.col_part + (size_t)by * (KM + 2) * N + i;
 #pragma unroll
-        for (int k = 0; k < KM + 2; ++k) out[(size_t)k * N] = acc[k];
+        for (int k = 0; k < KM + 2; ++k) out[(size_t)k * N] = (double)acc[k] - (ACC_ == 2 ? (double)cmp[k] : 0.0);
       }
     }
+    RED_STAMP(4);
     if (P.phase_hi >= 2 && !(P.phase_hi == 2 && P.nsplit == 1 && !P.xbuf)) grid_sync(P.bar, ++nsync);
+    RED_STAMP(5);
   }
 
   // ---------------------------------------------------------------- phase 2: month chunks -> chunk 0
@@ -325,7 +403,9 @@ __global__ void __launch_bounds__(RT, 4) step_reduce_kernel(const ReduceParams P
     }
   }
 
+  RED_STAMP(6);
   if (P.phase_lo <= 2 && P.phase_hi >= 3 && (P.nsplit > 1 || P.xbuf)) grid_sync(P.bar, ++nsync);
+  RED_STAMP(7);
 
   // ---------------------------------------------------------------- phase 3: e, T_i, unit coefficients, sum e^2
   if (P.phase_lo <= 3 && P.phase_hi >= 3) {
@@ -375,7 +455,9 @@ __global__ void __launch_bounds__(RT, 4) step_reduce_kernel(const ReduceParams P
       s2 = block_sum(s2, red);
       if (tid == 0) P.scalars[SC_SHARPE] = (Ts > 1) ? (float)(mean / (sqrt(s2 / (double)(Ts - 1)) + 1e-8)) : nanf("");
     }
+    RED_STAMP(8);
     if (P.phase_hi >= 4) grid_sync(P.bar, ++nsync);
+    RED_STAMP(9);
   }
 
   // ---------------------------------------------------------------- phase 4: losses; per-month dS sums
@@ -420,10 +502,18 @@ __global__ void __launch_bounds__(RT, 4) step_reduce_kernel(const ReduceParams P
           const int cnt = __ldg(P.index + idx_off_cnt(T) + t);
           const int per = (cnt + nseg - 1) / nseg, j0 = seg * per, j1 = min(cnt, j0 + per);
           const int* vrow = P.index + idx_off_vidx(T) + base;
-#pragma unroll 2
-          for (int j = j0 + tid; j < j1; j += RT) {
-            const int i = __ldg(vrow + j);
-            cell(i, P.q_dense ? base + i : base + j, true);
+          // the stock numbers of eight of this thread's cells first (one round trip), then the cells in pairs: the
+          // gathers of G and R depend on them, and a loop that fetched number and values cell by cell paid two
+          // dependent round trips per pair of cells
+          for (int jb = j0 + tid; jb < j1; jb += 8 * RT) {
+            int ii[8];
+#pragma unroll
+            for (int b = 0; b < 8; ++b) ii[b] = __ldg(vrow + min(jb + b * RT, j1 - 1));
+#pragma unroll
+            for (int b = 0; b < 8; ++b) {
+              const int j = jb + b * RT;
+              if (j < j1) cell(ii[b], P.q_dense ? base + ii[b] : base + j, true);
+            }
           }
         } else {
           const int per = (N + nseg - 1) / nseg, i0 = seg * per, i1 = min(N, i0 + per);
@@ -471,23 +561,43 @@ __global__ void __launch_bounds__(RT, 4) step_reduce_kernel(const ReduceParams P
     P.scalars[SC_LC] = (float)(P.dS2[2 * (size_t)T] / ((double)KM * (double)P.n_total));
     P.scalars[SC_LU] = (float)(P.dS2[2 * (size_t)T + 1] / (double)P.n_total);
   }
+  RED_STAMP(10);
   if (peers && blockIdx.x == 0 && tid == 0) *P.epoch = launch_no;      // read by every CTA at its start, long ago
   grid_exit(P.bar, nsync);
 }
 
+static long long* g_timeline_reduce = nullptr;
+void set_reduce_timeline(long long* p) { g_timeline_reduce = p; }
+
 static bool peers_in_use(const ReduceParams& P) { return P.stock_shard && P.world > 1; }
 
 // co-resident CTAs of the kernel on `device` with `sms` SMs in use and this much dynamic shared memory
+typedef void (*reduce_kernel_t)(const ReduceParams);
+static reduce_kernel_t reduce_kernel() {
+  static int mb = -1, acc = 1;
+  if (mb < 0) {
+    const char* ev = getenv("DLAP_REDUCE_MB"); mb = ev ? atoi(ev) : 2;
+    ev = getenv("DLAP_REDUCE_ACC"); acc = ev ? atoi(ev) : 1;
+  }
+  switch (mb * 10 + acc) {
+    case 10: return step_reduce_kernel<1, 0>;
+    case 11: return step_reduce_kernel<1, 1>;
+    case 12: return step_reduce_kernel<1, 2>;
+    case 20: return step_reduce_kernel<2, 0>;
+    case 22: return step_reduce_kernel<2, 2>;
+    default: return step_reduce_kernel<2, 1>;
+  }
+}
 static int reduce_ctas_per_sm(size_t smem) {
   int per_sm = 0;
-  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, step_reduce_kernel, RT, smem) != cudaSuccess) per_sm = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, reduce_kernel(), RT, smem) != cudaSuccess) per_sm = 0;
   return per_sm;
 }
 
 cudaError_t launch_step_reduce(ReduceParams P, int sms, bool cooperative, cudaStream_t st) {
   const size_t smem = 2 * (size_t)P.tchunk * sizeof(float);
   if (smem > 48 * 1024) {
-    cudaError_t e = cudaFuncSetAttribute(step_reduce_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t e = cudaFuncSetAttribute(reduce_kernel(), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
   }
   int per_sm = reduce_ctas_per_sm(smem);
@@ -495,7 +605,7 @@ cudaError_t launch_step_reduce(ReduceParams P, int sms, bool cooperative, cudaSt
   if (per_sm > 4) per_sm = 4;
   // no more CTAs than any phase has work for
   if (P.phase_lo == 5 && !peers_in_use(P)) {          // two divisions
-    step_reduce_kernel<<<1, RT, smem, st>>>(P);
+    reduce_kernel()<<<1, RT, smem, st>>>(P);
     return cudaGetLastError();
   }
   const int nb = (P.N + RT - 1) / RT;
@@ -512,8 +622,8 @@ cudaError_t launch_step_reduce(ReduceParams P, int sms, bool cooperative, cudaSt
   if (grid < 1) grid = 1;
   void* args[] = {(void*)&P};
   if (cooperative)
-    return cudaLaunchCooperativeKernel((const void*)step_reduce_kernel, dim3(grid), dim3(RT), args, smem, st);
-  step_reduce_kernel<<<grid, RT, smem, st>>>(P);
+    return cudaLaunchCooperativeKernel((const void*)reduce_kernel(), dim3(grid), dim3(RT), args, smem, st);
+  reduce_kernel()<<<grid, RT, smem, st>>>(P);
   return cudaGetLastError();
 }
 
@@ -539,6 +649,7 @@ cudaError_t launch_step_reduce_c(const dlap_plan* plan, const float* u, const fl
   P.col_part = col_part; P.nsplit = plan->col_splits; P.tchunk = (plan->dims.T + plan->col_splits - 1) / plan->col_splits;
   P.e = e; P.t_i = t_i; P.G = G; P.loss_part = loss_part; P.dS2 = dS2; P.bar = bar;
   P.phase_lo = phase_lo; P.phase_hi = phase_hi;
+  P.tl = g_timeline_reduce;
   return launch_step_reduce(P, plan->sms, plan->cooperative != 0, st);
 }
 

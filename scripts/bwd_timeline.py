@@ -75,3 +75,10 @@ if t0:
         r = bp[1 + c]
         if int(r[0]):
             print(f"BPTT summing CTA {c}: start {int(r[0]) - t0} | sums done {int(r[1]) - t0} | rows final seen {int(r[2]) - t0} | dpre seen {int(r[3]) - t0} | tasks done {int(r[4]) - t0}")
+
+rd = st[3 * 256 * 16 + 2048:3 * 256 * 16 + 2048 + 64].cpu()
+if int(rd[0]):
+    names = ["start", "p0 done", "sync0", "cta0 stats", "p1 done", "sync1", "p2 done", "sync2", "p3 done", "sync3", "p4 done"]
+    r0 = int(rd[0])
+    for off, who in ((0, "CTA 0"), (32, "last CTA")):
+        print("REDUCE", who, "(ns):", " | ".join(f"{n} {int(rd[off + k]) - r0}" for k, n in enumerate(names)))
