@@ -9,7 +9,6 @@
 //            LSTM semantics: torch.nn.LSTM, gates i,f,g,o (src/model.py:39-45, :68).
 //   backward (one persistent CTA): dh_t = W1[:,F:]^T.da_t, BPTT on one warp, then the
 //            month-summed weight gradients (LSTM, W1[:,F:], b1, Wq[:,:M], bq).
-#include <cstdlib>
 #include "../../include/dlap.h"
 #include "dlap_common.cuh"
 #include "macro_role.cuh"
@@ -593,7 +592,6 @@ cudaError_t launch_macro_bwd(const MacroParams& P, const FinishParams& FIN0, cud
   // the month-summed gradients ride in the BPTT kernel whenever it has summing CTAs beside the recurrence -- and the
   // grid is launched co-resident: those CTAs then wait for the recurrence's CTA, which is the last one of the grid
   FIN.fold_wgrad = (P.have_sdf && P.H > 0 && FIN.dadc_part && FIN.counter && FIN.cooperative) ? 1 : 0;
-  if (const char* ev = getenv("DLAP_FOLD_WGRAD")) FIN.fold_wgrad = FIN.fold_wgrad && atoi(ev) != 0;
   if (P.have_sdf && P.H > 0) {
     cudaError_t e = launch_bptt(P, FIN, st);
     if (e != cudaSuccess) return e;

@@ -14,8 +14,6 @@
 // Every cross-CTA sum has a fixed order (no float atomics): results are reproducible run to run.
 // Data written in one phase and read in a later one is read with ld.cg / ld.acquire, never through the
 // read-only (nc) path.
-#include <cstdlib>
-#include <type_traits>
 #include "../../include/dlap.h"
 #include "dlap_common.cuh"
 #include "cell_f32.cuh"
@@ -139,7 +137,6 @@ __device__ __forceinline__ double ld_peer(const double* p) {
 }
 }  // namespace
 
-template <int MB_, int ACC_>
 __global__ void __launch_bounds__(RT, 4) step_reduce_kernel(const ReduceParams P) {
   extern __shared__ float sm[];            // phase 1: S_t then mu_t of this CTA's month chunk
   __shared__ double red[32];
@@ -308,30 +305,19 @@ __global__ void __launch_bounds__(RT, 4) step_reduce_kernel(const ReduceParams P
       const int i = bx * RT + tid;
       const bool in = i < N;                   // whole warps stay: the packed position comes from a ballot
       const int* rank = P.index ? P.index + idx_off_rank(T, N) + (i >> 5) : nullptr;
-      // Sums over the chunk's months.  ACC_ 0: doubles (ten conversions + ten double adds per stock-month on the
-      // quarter-rate pipe); 1: plain fp32 within the chunk; 2: fp32 with Kahan compensation (acc - cmp carries what a
-      // double would).  The chunk totals are handed on as doubles either way.
-      typedef typename std::conditional<ACC_ == 0, double, float>::type acc_t;
-      acc_t acc[KM + 2];
-      float cmp[ACC_ == 2 ? KM + 2 : 1];
+      // Sums over the chunk's months (at most a few dozen terms) in fp32, handed on as doubles: the chunks are added
+      // in fp64 (phase 2).  Doubles here cost ten conversions and ten double adds per stock-month on the quarter-rate
+      // pipe of an issue-bound loop (measured: 26 -> 22 us for this phase); the reference sums all T terms in fp32.
+      float acc[KM + 2];
 #pragma unroll
-      for (int k = 0; k < KM + 2; ++k) { acc[k] = 0; if (ACC_ == 2) cmp[k] = 0.f; }
-      auto add = [&](int k, float x) {
-        if (ACC_ == 2) {
-          const float y = x - cmp[k], t = (float)acc[k] + y;
-          cmp[k] = (t - (float)acc[k]) - y;
-          acc[k] = t;
-        } else {
-          acc[k] += (acc_t)x;
-        }
-      };
+      for (int k = 0; k < KM + 2; ++k) acc[k] = 0.f;
       // Latency-bound: per month a mask byte and a rank word, then (at a position that depends on them) u, R and
       // eight q values.  Months go in batches of MB: the batch's keys are already in registers (fetched while the
       // previous batch's values were in flight), all of its value loads are issued before anything is stored -- a
       // store to w_out in between would pin every later load behind it, the pointers may alias as far as the
       // compiler knows -- so a batch costs ONE round trip.  Masked lanes load from a clamped in-bounds position and
       // drop the values.
-      constexpr int MB = MB_;
+      constexpr int MB = 2;
       const size_t ic = in ? (size_t)i : (size_t)N - 1;
       const unsigned below = (1u << lane) - 1u;
       uint8_t mk[MB];
@@ -373,20 +359,27 @@ __global__ void __launch_bounds__(RT, 4) step_reduce_kernel(const ReduceParams P
             const int tl = t + b - t0;
             const float S = sm[tl];
             if (P.w_out && in) P.w_out[gi[b]] = live[b] ? (uv[b] - sm[tchunk + tl]) : 0.f;
-            add(KM, live[b] ? (r[b] * S) : 0.f);
-            acc[KM + 1] += live[b] ? (acc_t)1 : (acc_t)0;           // a count: exact
+            acc[KM] += live[b] ? (r[b] * S) : 0.f;
+            acc[KM + 1] += live[b] ? 1.f : 0.f;                     // a count: exact
 #pragma unroll
-            for (int k = 0; k < KM; ++k) add(k, live[b] ? ((qv[b][k] * r[b]) * S) : 0.f);
+            for (int k = 0; k < KM; ++k) acc[k] += live[b] ? ((qv[b][k] * r[b]) * S) : 0.f;
           }
         }
       }
       if (in) {
         double* out = P.col_part + (size_t)by * (KM + 2) * N + i;
 #pragma unroll
-        for (int k = 0; k < KM + 2; ++k) out[(size_t)k * N] = (double)acc[k] - (ACC_ == 2 ? (double)cmp[k] : 0.0);
+        for (int k = 0; k < KM + 2; ++k) out[(size_t)k * N] = (double)acc[k];
       }
     }
     RED_STAMP(4);
+    if (P.tl && threadIdx.x == 0) {                      // every CTA: when its phase-1 work was done, and on which SM
+      unsigned long long now_; unsigned int smid_;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now_));
+      asm volatile("mov.u32 %0, %%smid;" : "=r"(smid_));
+      P.tl[64 + blockIdx.x] = (long long)now_;
+      P.tl[64 + 640 + blockIdx.x] = (long long)smid_;
+    }
     if (P.phase_hi >= 2 && !(P.phase_hi == 2 && P.nsplit == 1 && !P.xbuf)) grid_sync(P.bar, ++nsync);
     RED_STAMP(5);
   }
@@ -572,32 +565,16 @@ void set_reduce_timeline(long long* p) { g_timeline_reduce = p; }
 static bool peers_in_use(const ReduceParams& P) { return P.stock_shard && P.world > 1; }
 
 // co-resident CTAs of the kernel on `device` with `sms` SMs in use and this much dynamic shared memory
-typedef void (*reduce_kernel_t)(const ReduceParams);
-static reduce_kernel_t reduce_kernel() {
-  static int mb = -1, acc = 1;
-  if (mb < 0) {
-    const char* ev = getenv("DLAP_REDUCE_MB"); mb = ev ? atoi(ev) : 2;
-    ev = getenv("DLAP_REDUCE_ACC"); acc = ev ? atoi(ev) : 1;
-  }
-  switch (mb * 10 + acc) {
-    case 10: return step_reduce_kernel<1, 0>;
-    case 11: return step_reduce_kernel<1, 1>;
-    case 12: return step_reduce_kernel<1, 2>;
-    case 20: return step_reduce_kernel<2, 0>;
-    case 22: return step_reduce_kernel<2, 2>;
-    default: return step_reduce_kernel<2, 1>;
-  }
-}
 static int reduce_ctas_per_sm(size_t smem) {
   int per_sm = 0;
-  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, reduce_kernel(), RT, smem) != cudaSuccess) per_sm = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, step_reduce_kernel, RT, smem) != cudaSuccess) per_sm = 0;
   return per_sm;
 }
 
 cudaError_t launch_step_reduce(ReduceParams P, int sms, bool cooperative, cudaStream_t st) {
   const size_t smem = 2 * (size_t)P.tchunk * sizeof(float);
   if (smem > 48 * 1024) {
-    cudaError_t e = cudaFuncSetAttribute(reduce_kernel(), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t e = cudaFuncSetAttribute(step_reduce_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
   }
   int per_sm = reduce_ctas_per_sm(smem);
@@ -605,7 +582,7 @@ cudaError_t launch_step_reduce(ReduceParams P, int sms, bool cooperative, cudaSt
   if (per_sm > 4) per_sm = 4;
   // no more CTAs than any phase has work for
   if (P.phase_lo == 5 && !peers_in_use(P)) {          // two divisions
-    reduce_kernel()<<<1, RT, smem, st>>>(P);
+    step_reduce_kernel<<<1, RT, smem, st>>>(P);
     return cudaGetLastError();
   }
   const int nb = (P.N + RT - 1) / RT;
@@ -622,8 +599,8 @@ cudaError_t launch_step_reduce(ReduceParams P, int sms, bool cooperative, cudaSt
   if (grid < 1) grid = 1;
   void* args[] = {(void*)&P};
   if (cooperative)
-    return cudaLaunchCooperativeKernel((const void*)reduce_kernel(), dim3(grid), dim3(RT), args, smem, st);
-  reduce_kernel()<<<grid, RT, smem, st>>>(P);
+    return cudaLaunchCooperativeKernel((const void*)step_reduce_kernel, dim3(grid), dim3(RT), args, smem, st);
+  step_reduce_kernel<<<grid, RT, smem, st>>>(P);
   return cudaGetLastError();
 }
 

@@ -82,3 +82,19 @@ if int(rd[0]):
     r0 = int(rd[0])
     for off, who in ((0, "CTA 0"), (32, "last CTA")):
         print("REDUCE", who, "(ns):", " | ".join(f"{n} {int(rd[off + k]) - r0}" for k, n in enumerate(names)))
+
+if int(rd[0]):
+    ends = st[3 * 256 * 16 + 2048 + 64:3 * 256 * 16 + 2048 + 64 + 592].cpu()
+    smid = st[3 * 256 * 16 + 2048 + 64 + 640:3 * 256 * 16 + 2048 + 64 + 640 + 592].cpu()
+    live = ends > 0
+    e = (ends[live] - r0).double() / 1000.0
+    print("REDUCE p1 end per CTA (us): n", int(live.sum()), "min %.1f p10 %.1f median %.1f p90 %.1f max %.1f" % (
+        float(e.min()), float(e.kthvalue(max(1, int(0.1 * e.numel()))).values), float(e.median()),
+        float(e.kthvalue(int(0.9 * e.numel())).values), float(e.max())))
+    order = torch.argsort(e, descending=True)[:12]
+    idx = torch.nonzero(live).flatten()[order]
+    print("REDUCE slowest CTAs (cta, sm, end):", [(int(c), int(smid[c]), round(float((ends[c] - r0)) / 1000, 1)) for c in idx])
+    per_sm = {}
+    for c in torch.nonzero(live).flatten().tolist():
+        per_sm.setdefault(int(smid[c]), []).append(c)
+    print("REDUCE CTAs per SM: min", min(len(v) for v in per_sm.values()), "max", max(len(v) for v in per_sm.values()), "SMs used", len(per_sm))

@@ -13,3 +13,10 @@ if [ "${REF:-0}" = "1" ]; then
   timeout 600 python bench.py --impl reference --steps 5 --warmup 2 > gpurun_out/${TAG}_ref.json 2> gpurun_out/${TAG}_ref.err
   echo "ref exit $?"; tail -c 400 gpurun_out/${TAG}_ref.json
 fi
+if [ "${NCU:-0}" = "1" ]; then
+  # launch list of the bench command (per-launch durations, cold cache, serialised) and one full capture of the dominant kernel
+  ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/${TAG}_launches.csv \
+    python bench.py --steps 20 --warmup 5 --no-legs --no-cpu > gpurun_out/${TAG}_ncu_bench.log 2>&1
+  echo "ncu launches exit $?"; python scripts/ncu_summary.py gpurun_out/${TAG}_launches.csv | grep dlap
+  TAG=${TAG}_bwd KERN=cell_bwd_tc SKIP=3 bash scripts/ncu_full.sh | grep -v "^  smsp__average" | head -40
+fi
