@@ -155,7 +155,16 @@ __device__ __forceinline__ void wgrad_tasks(const MacroParams& P, float* sm, int
   // ---- second act: everything that needs dpre
   if (!P.have_sdf || Hr == 0) return;
   wait_dpre();
-  for (int i = tid; i < T * G4; i += NTHR) dps[(i / G4) * DP + i % G4] = __ldcg(P.dpre + i);
+  for (int i0 = tid; i0 < T * G4; i0 += 8 * NTHR) {          // eight loads in flight per thread: one round trip
+    float ld[8];
+#pragma unroll
+    for (int b = 0; b < 8; ++b) ld[b] = __ldcg(P.dpre + min(i0 + b * NTHR, T * G4 - 1));
+#pragma unroll
+    for (int b = 0; b < 8; ++b) {
+      const int i = i0 + b * NTHR;
+      if (i < T * G4) dps[(i / G4) * DP + i % G4] = ld[b];
+    }
+  }
   __syncthreads();
   if (type == 0) {
     const int m = task;
@@ -366,6 +375,8 @@ __global__ void __launch_bounds__(MT, 1) macro_bptt_kernel(const MacroParams P, 
   __syncthreads();
   BPTT_STAMP(1);
   // pass 1, thread = (month, unit): dhe_t = W1[:,F:]^T . da_t and the local derivatives
+  // (measured against a warp per month with the row spread over the lanes and a lane reduction: one round trip
+  // instead of two, but the per-month tail on four lanes made the pass 3 us slower)
   for (int i = tid; i < T * H; i += MT) {
     const int t = i / H, j = i % H;
     const float4* da4 = reinterpret_cast<const float4*>(P.dadc + (size_t)t * 72);

@@ -41,8 +41,23 @@ struct MacroParams {
 
 // exp2/rcp-based activations for the serial recurrence (absolute error ~2e-7, far inside the parity
 // tolerance; the recurrence is contractive so it does not build up over the months)
-__device__ __forceinline__ float sigmoid_fast(float v) { return __fdividef(1.f, 1.f + __expf(-v)); }
-__device__ __forceinline__ float tanh_fast(float v) { return fmaf(2.f, sigmoid_fast(2.f * v), -1.f); }
+// Written with the two MUFU instructions directly: __expf / __fdividef wrap them in range fix-ups (an FSETP and two
+// predicated FMULs per ex2 on the serial chain of the recurrence) that only matter below 2^-126, where 1 + e is 1
+// either way; the scale of the argument is one constant (tanh: -2 log2 e) instead of two dependent multiplies.
+__device__ __forceinline__ float ex2_ftz(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float rcp_ftz(float x) {
+  float y;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float sigmoid_fast(float v) { return rcp_ftz(1.f + ex2_ftz(v * -1.4426950408889634f)); }
+__device__ __forceinline__ float tanh_fast(float v) {
+  return fmaf(2.f, rcp_ftz(1.f + ex2_ftz(v * -2.8853900817779268f)), -1.f);
+}
 
 constexpr int MT = 512;    // threads of the single-CTA macro kernels
 
