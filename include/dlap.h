@@ -161,8 +161,8 @@ int dlap_panel_index(const dlap_plan* plan, const uint8_t* mask, int32_t* index,
  * valid-cell index (<= 128 listed stocks of one month) `image` receives, at [tile * 24768), the 24,768 bytes the
  * BF16X3 kernels otherwise build in shared memory per tile and step: the rows of x split into bf16 hi + lo
  * (x = hi + lo up to 2^-18 |x|) in the no-swizzle canonical K-major layout, a ones column for the first-layer
- * biases, rows past the end of a tile repeating its last row.  image: plan->image_bytes, 16-B aligned.  Requires
- * F <= 46.  Rebuild whenever x or the index changes.  One launch; reads x once (listed rows only), HBM-bound. */
+ * biases, rows past the end of a tile repeating its last row.  image: 16-B aligned, at least 24768 * index[0] bytes
+ * (index[0]: the tiles the index lists; plan->image_bytes is the bound that holds for any mask).  Requires F <= 46.  Rebuild whenever x or the index changes.  One launch; reads x once (listed rows only), HBM-bound. */
 int dlap_panel_image(const dlap_plan* plan, const float* x, const int32_t* index, void* image, void* stream);
 
 /* Panel ingest without a staging copy (the per-epoch `batch[k].to(device)` of src/train.py:69-75 for the
