@@ -94,7 +94,7 @@ SIGNATURES = {
     "dlap_loss_finish": (_PLAN, _P, _I, _P, _P, _P, _P, _P, _P),
     "dlap_loss_finish_noalloc": (_PLAN, _P, _I, _P, _P, _P, _P),
     "dlap_cell_bwd": (_PLAN, _P, _P, _P, _P, _P, _TENS, _MIO, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _P, _P, _I,
-                      C.c_float, C.c_uint64, _P, _P),
+                      C.c_float, C.c_uint64, _P, _P, _P, _P),
     "dlap_grad_finish": (_PLAN, _P, _P, _P, _I, _I, _I, _TENS, _P, _I, _P),
     "dlap_macro_bwd": (_PLAN, _P, _TENS, _P, _P, _P, _P, _P, _I, _I, _TENS, _P, _P, _P, _I, _P, C.POINTER(DlapPeers), _P),
     "dlap_weights": (_PLAN, _P, _P, _P, _I, _I, _P, _P),

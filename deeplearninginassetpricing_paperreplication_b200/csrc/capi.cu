@@ -375,10 +375,12 @@ int dlap_cell_bwd(const dlap_plan* plan, const float* x, const float* R, const u
                   const void* x_image, const dlap_tensors* params, const dlap_macro_io* mio, const float* row_stats, const double* dS2,
                   const float* gc, const float* gu, const float* dpr_cot, const float* G, const float* scalars,
                   int weighted_loss, int want_sdf, int want_mom, float* wpart, float* dadc_part, int precision,
-                  float dropout_p, uint64_t dropout_seed, const uint64_t* dropout_seed_dev, void* stream) {
+                  float dropout_p, uint64_t dropout_seed, const uint64_t* dropout_seed_dev, const float* res_b,
+                  const float* u_fwd, void* stream) {
   int rc = check_plan(plan);
   if (rc) return rc;
   REQ(x); REQ(R); REQ(mask); REQ(params); REQ(mio); REQ(mio->a_t); REQ(mio->c_t); REQ(row_stats); REQ(dS2); REQ(G);
+  if (res_b) REQ(u_fwd);
   REQ(scalars); REQ(wpart); REQ(dadc_part);
   REQ(params->w1); REQ(params->w2); REQ(params->b2); REQ(params->w3); REQ(params->b3);
   if (want_mom) REQ(params->wq);
@@ -391,6 +393,7 @@ int dlap_cell_bwd(const dlap_plan* plan, const float* x, const float* R, const u
   P.cot[0] = gc ? gc : scalars + SC_ZERO; P.cot[1] = gu ? gu : scalars + SC_ZERO; P.ncot = 2;
   P.G = G; P.scalars = scalars; P.weighted = weighted_loss;
   P.wpart = wpart; P.dadc_part = dadc_part;
+  P.res_b = want_sdf ? res_b : nullptr; P.u_fwd = u_fwd;
   rc = set_dropout(P, dropout_p, dropout_seed, dropout_seed_dev);
   if (rc) return rc;
   if (precision == DLAP_PREC_BF16X3) {

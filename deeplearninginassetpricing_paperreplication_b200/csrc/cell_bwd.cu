@@ -116,6 +116,8 @@ __global__ void __launch_bounds__(NT, 1) cell_bwd_f32_kernel(const CellParams P)
       s.sc[1] = rs[RS_RBAR];
       s.sc[2] = rs[RS_S];
       s.sc[3] = __ldg(P.cot[0]);
+      s.sc[4] = P.res_b ? __ldg(P.res_b + t) : 0.f;
+      s.sc[5] = rs[RS_MU];
     }
     __syncthreads();
     const int ncell = L.ncell;
@@ -132,7 +134,9 @@ __global__ void __launch_bounds__(NT, 1) cell_bwd_f32_kernel(const CellParams P)
     if (half == 0) {
       float m = 0.f, r = 0.f;
       if (live) { m = P.mask[gi] ? 1.f : 0.f; r = __ldg(P.R + gi); }
-      b.dus[cell] = m * s.sc[0] * (r - s.sc[1]);
+      float du = m * s.sc[0] * (r - s.sc[1]);
+      if (P.res_b && live) du = fmaf(m * s.sc[4], __ldg(P.u_fwd + gi) - s.sc[5], du);     // residual loss (src/model.py:435-483)
+      b.dus[cell] = du;
       b.cqs[cell] = r * m * s.sc[2];
     }
 

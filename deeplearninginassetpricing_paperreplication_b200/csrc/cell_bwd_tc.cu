@@ -103,7 +103,9 @@ __device__ __forceinline__ void epi_barrier() { asm volatile("bar.sync 1, 512;" 
     if (P.timeline && blockIdx.x == 0 && (i) < 256) P.timeline[(i) * 16 + (k)] = clock64(); \
   } while (0)
 
-template <bool SDF, bool MOM, bool DROP>
+// RES: the residual-loss term of du (CellParams::res_b), a variant of its own so that the kernel everybody else runs
+// keeps its register allocation (80 registers, no spills)
+template <bool SDF, bool MOM, bool DROP, bool RES = false>
 __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P) {
   extern __shared__ __align__(128) uint8_t smem_raw[];
   SmemB s;
@@ -306,6 +308,7 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
     for (int k = 0; k < 8; ++k) pf_g[k] = 0.f;
     int ms_month = -1;
     float ms_dP = 0.f, ms_rbar = 0.f, ms_S = 0.f;
+    float pf_u = 0.f, ms_rb = 0.f, ms_mu = 0.f;          // RES only
     auto load_n = [&](int i) {
       const int tile = tile_lo + i;
       mc.seek(P, tile);
@@ -317,6 +320,7 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
       const size_t gi = (size_t)t * P.N + (pf_live ? n : 0);
       pf_gi = (uint32_t)gi;
       pf_r = pf_live ? __ldg(P.R + gi) : 0.f;            // consumed one phase later: no stall here
+      if (RES) pf_u = pf_live ? __ldg(P.u_fwd + (size_t)t * P.N + mc.j0(tile_lo + i) + cell) : 0.f;   // left-packed u
       if (mom_warp) {                                    // the stock's eight coefficients: one 32-byte piece of its G row
         const float4* gr = reinterpret_cast<const float4*>(P.G + (size_t)(pf_live ? n : 0) * GS);
         const float4 ga = __ldg(gr), gb = __ldg(gr + 1);
@@ -334,6 +338,7 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
         ms_rbar = rs[RS_RBAR];
         // S_t only ever multiplies the moment-side cotangent: carry dL/dL_c with it (G holds UNIT coefficients)
         ms_S = rs[RS_S] * __ldg(P.cot[0]);
+        if (RES) { ms_rb = __ldg(P.res_b + t); ms_mu = rs[RS_MU]; }
       }
       if (i + 1 < my_tiles) load_n(i + 1);
     };
@@ -348,6 +353,7 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
       e1_t = pf_t; gi_nxt = pf_gi;
       const float pf_m = pf_live ? 1.f : 0.f;            // every listed cell is unmasked
       du_nxt = pf_m * ms_dP * (pf_r - ms_rbar);
+      if (RES) du_nxt = fmaf(pf_m * ms_rb, pf_u - ms_mu, du_nxt);
       const float cq = pf_r * pf_m * ms_S;
       float gk[8];
 #pragma unroll
@@ -572,12 +578,12 @@ __global__ void __launch_bounds__(NT_B, 1) cell_bwd_tc_kernel(const CellParams P
   if (warp == 0) tc::tmem_dealloc(tbase, TMEM_COLS);
 }
 
-template <bool SDF, bool MOM, bool DROP>
+template <bool SDF, bool MOM, bool DROP, bool RES = false>
 static cudaError_t launch_bwd_tc_variant(const CellParams& P, int grid, cudaStream_t st) {
-  cudaError_t e = cudaFuncSetAttribute(cell_bwd_tc_kernel<SDF, MOM, DROP>,
+  cudaError_t e = cudaFuncSetAttribute(cell_bwd_tc_kernel<SDF, MOM, DROP, RES>,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_B_BYTES);
   if (e != cudaSuccess) return e;
-  cell_bwd_tc_kernel<SDF, MOM, DROP><<<grid, NT_B, SMEM_B_BYTES, st>>>(P);
+  cell_bwd_tc_kernel<SDF, MOM, DROP, RES><<<grid, NT_B, SMEM_B_BYTES, st>>>(P);
   return cudaGetLastError();
 }
 
@@ -588,6 +594,12 @@ cudaError_t launch_cell_bwd_tc(const CellParams& P0, int grid, bool sdf, bool mo
   CellParams P = P0;
   P.timeline = g_timeline;
   const bool drop = P.drop_thr != 0 && sdf;
+  if (sdf && P.res_b) {            // the residual-loss term only ever reaches the SDF net
+    if (mom) return drop ? launch_bwd_tc_variant<true, true, true, true>(P, grid, st)
+                         : launch_bwd_tc_variant<true, true, false, true>(P, grid, st);
+    return drop ? launch_bwd_tc_variant<true, false, true, true>(P, grid, st)
+                : launch_bwd_tc_variant<true, false, false, true>(P, grid, st);
+  }
   if (sdf && mom) return drop ? launch_bwd_tc_variant<true, true, true>(P, grid, st)
                               : launch_bwd_tc_variant<true, true, false>(P, grid, st);
   if (sdf) return drop ? launch_bwd_tc_variant<true, false, true>(P, grid, st)

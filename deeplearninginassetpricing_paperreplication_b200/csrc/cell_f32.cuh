@@ -46,6 +46,11 @@ struct CellParams {
   const float* G;            // [N,GS]  unit loss coefficients per stock: G_0..G_7 (times the L_c cotangent), G_u
   const float* scalars;      // [SC_W]  (n_bar)
   int weighted;              // weighted_loss flag
+  // residual-loss regulariser (src/model.py:435-483; null = off): its gradient reaches u as
+  //   du_ti += a_t (R_ti - Rbar_t) + res_b[t] (u_ti - mu_t);  a_t rides in dpr_cot, the second term needs the
+  //   forward's u (left-packed for the tensor-core kernels, dense for fp32) and one coefficient per month
+  const float* res_b;        // [T]
+  const float* u_fwd;        // [T,N]
   // backward outputs
   float* wpart;              // [grid, WP_STRIDE] per-CTA weight-gradient partials
   float* dadc_part;          // [T,tpm,72]  da_t (64) then dc_t (8)

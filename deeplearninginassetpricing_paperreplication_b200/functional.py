@@ -288,6 +288,7 @@ class StepOptions:
     dropout_seed_dev: Optional[torch.Tensor] = None   # int64 [1] on the device: overrides dropout_seed (GraphedStep)
     shard: Optional["MonthShard"] = None            # a MonthShard or a StockShard
     demean: bool = True             # normalize_w (src/model.py:274): False = the weights are m u, not demeaned
+    residual: bool = False          # residual_loss_factor > 0 (src/model.py:543-548): also return the residual loss
 
 
 @dataclass
@@ -603,8 +604,34 @@ def step_reduce(ws: Workspace, cp: CellPass, R, mask, weighted_loss: bool, want_
 RS_SR = 6     # row_stats: sum_i m R of the month
 
 
+def residual_terms(w, R, mask):
+    """compute_residual_loss (src/model.py:435-483) from the weights of a step: the loss L, and per month c_t and
+    beta_t with dL/dw_ti = c_t (R_ti - beta_t w_ti) on the listed cells.  Months with fewer than two listed stocks
+    are left out; months whose weights vanish (w.w <= 1e-8) only count in the denominator.  Per-month sums in fp64
+    ([T]-sized torch ops and four [T,N] reductions: this is a regulariser the reference's configurations leave at 0,
+    not a hot path); no host synchronisation, so it can be captured in a CUDA graph."""
+    m = mask.to(torch.float64)
+    wd, Rd = w.to(torch.float64), R.to(torch.float64)
+    n = m.sum(dim=1)
+    ww = (wd * wd * m).sum(dim=1)
+    Rw = (Rd * wd * m).sum(dim=1)
+    RR = (Rd * Rd * m).sum(dim=1)
+    zero, one = torch.zeros_like(n), torch.ones_like(n)
+    B = n >= 2                                               # src/model.py:458-459
+    A = B & (ww > 1e-8)                                      # :466
+    ns = torch.where(B, n, one)
+    beta = torch.where(A, Rw / torch.where(A, ww, one), zero)
+    res = torch.where(A, (RR - Rw * beta) / ns, zero)        # mean (R - beta w)^2 over the month's listed stocks
+    nA, nB = A.sum().to(torch.float64), B.sum().to(torch.float64)
+    den = (torch.where(B, RR / ns, zero).sum() / nB.clamp(min=1.0)).clamp(min=1e-8)      # :478, :480
+    loss = torch.where(nA > 0, res.sum() / nA.clamp(min=1.0) / den, torch.zeros_like(den))
+    c = torch.where(A, -2.0 * beta / (nA.clamp(min=1.0) * den * ns), zero)
+    return loss.to(torch.float32), c, beta
+
+
 class GanStepFn(torch.autograd.Function):
-    """(L_c, L_u, pr, weights, sharpe, h_n, c_n) = step(panel, params).
+    """(L_c, L_u, pr, weights, sharpe, h_n, c_n, L_res) = step(panel, params).  L_res: the residual-loss regulariser
+    (src/model.py:435-483) when opts.residual, else a zero that carries no gradient.
 
     `cells`: a CellPass of the same panel and parameters made earlier (the evaluation cache of AssetPricingGAN), or
     None.  Three optional tensor inputs widen the fast path to the reference's other configurations:
@@ -627,6 +654,8 @@ class GanStepFn(torch.autograd.Function):
             raise NotImplementedError("shards with caller-made bias tables / moment outputs")
         if isinstance(sh, StockShard) and not opts.demean:
             raise NotImplementedError("stock shards with normalize_w=False")
+        if opts.residual and (sh is not None or not opts.demean):
+            raise NotImplementedError("residual_loss_factor > 0 with a sharded panel or normalize_w=False")
         want_backward = any(ctx.needs_input_grad)
         kernel_moments = opts.need_moments and q_in is None
         with torch.cuda.device(dev):
@@ -648,13 +677,20 @@ class GanStepFn(torch.autograd.Function):
                     red.dS2, tables, q_dense is not None, cp.ximg)
         scalars = red.scalars
         l_c, l_u, sharpe = scalars[SC_LC], scalars[SC_LU], scalars[SC_SHARPE]
-        ctx.mark_non_differentiable(red.w, sharpe, cp.hn, cp.cn)
-        return l_c, l_u, red.pr, red.w, sharpe, cp.hn, cp.cn
+        if opts.residual:
+            l_res, res_c, res_beta = residual_terms(red.w, R, mask)
+            ctx.res = (res_c, res_beta, cp.u)              # [T] fp64 each; u: what dlap_cell_bwd needs for the term in u
+            ctx.mark_non_differentiable(red.w, sharpe, cp.hn, cp.cn)
+        else:
+            l_res, ctx.res = scalars[7], None              # SC_ZERO: always 0.0
+            ctx.mark_non_differentiable(red.w, sharpe, cp.hn, cp.cn, l_res)
+        return l_c, l_u, red.pr, red.w, sharpe, cp.hn, cp.cn, l_res
 
     @staticmethod
-    def backward(ctx, g_lc, g_lu, g_pr, *_unused):
+    def backward(ctx, g_lc, g_lu, g_pr, *rest):
         x, R, mask, macro, h0, c0, *params = ctx.saved_tensors
         opts, ws = ctx.opts, ctx.ws
+        g_lres = rest[4] if len(rest) > 4 else None
         save, a_t, c_t, index, mio, has_q, row_stats, scalars, G, dS2, tables, q_given, ximg = ctx.keep
         sh = opts.shard
         stocks = isinstance(sh, StockShard)
@@ -678,6 +714,17 @@ class GanStepFn(torch.autograd.Function):
         g_lc, g_lu = scalar(g_lc), scalar(g_lu)
         if g_pr is not None:
             g_pr = g_pr.detach().to(torch.float32).contiguous()
+        res_b = u_fwd = None
+        if ctx.res is not None and g_lres is not None and want_sdf:
+            # dL_res/dw_ti = c_t (R_ti - beta_t w_ti) on the listed cells and w = m (u - mu_t), so u receives
+            # a_t (R_ti - Rbar_t) + b_t (u_ti - mu_t) with a_t = g c_t, b_t = -g c_t beta_t.  The first term has the form
+            # of the portfolio return's (dP_t (R - Rbar_t), dP_t = dS_t N_bar / N_t when weighted): it joins g_pr.
+            res_c, res_beta, u_fwd = ctx.res
+            a = g_lres.detach().to(torch.float64) * res_c
+            res_b = (-(a * res_beta)).to(torch.float32).contiguous()
+            if opts.weighted_loss:
+                a = a * (row_stats[:, RS_NT].to(torch.float64) / scalars[SC_NBAR].to(torch.float64))
+            g_pr = a.to(torch.float32) if g_pr is None else g_pr + a.to(torch.float32)
         grad_a = grad_c = grad_q = None
         grads = [None] * len(params)
         with torch.cuda.device(dev):
@@ -688,7 +735,7 @@ class GanStepFn(torch.autograd.Function):
                             C.byref(mio), _ptr(row_stats), _ptr(dS2), _ptr(g_lc) if (has_q or q_given) else None,
                             _ptr(g_lu), _ptr(g_pr), _ptr(G), _ptr(scalars), int(opts.weighted_loss), int(want_sdf),
                             int(want_mom), _ptr(ws.wpart), _ptr(ws.dadc_part), prec, float(opts.dropout_p),
-                            int(opts.dropout_seed), _ptr(opts.dropout_seed_dev), st)
+                            int(opts.dropout_seed), _ptr(opts.dropout_seed_dev), _ptr(res_b), _ptr(u_fwd), st)
                 ws.launches += 1
                 # All gradient tensors are views of one flat buffer.  Month-sharded: the buffer starts with the
                 # [T_total,72] da_t | dc_t rows (this rank fills its months) and is zero-filled, so that exchange 2 is

@@ -260,7 +260,8 @@ class StepOutputs(dict):
 
 
 class AssetPricingGAN(nn.Module):
-    """src/model.py:284-617 (compute_residual_loss excluded: residual_loss_factor must be 0)."""
+    """src/model.py:284-617 (compute_residual_loss, :435-483, as functional.residual_terms + a term of the per-cell
+    backward kernel)."""
 
     def __init__(self, config: Dict):
         super().__init__()
@@ -311,8 +312,6 @@ class AssetPricingGAN(nn.Module):
         return 'bf16x3' if F <= Fn.TC_MAX_F else 'fp32'
 
     def _inputs(self, macro, x, want_q: bool) -> "KernelInputs":
-        if self.residual_loss_factor > 0:
-            _unsupported("residual_loss_factor > 0")
         return _kernel_inputs(self.sdf_net, self.moment_net, macro, x, want_q)
 
     def forward(self, macro_features, individual_features, returns, mask, hidden=None,
@@ -333,9 +332,10 @@ class AssetPricingGAN(nn.Module):
         opts = Fn.StepOptions(weighted_loss=bool(self.weighted_loss),
                               need_moments=(phase != 'unconditional'), precision=self._precision(x.shape[2]),
                               dropout_p=p_drop, dropout_seed=seed, dropout_seed_dev=seed_dev,
-                              shard=self.month_shard, demean=bool(self.sdf_net.normalize_weights))
+                              shard=self.month_shard, demean=bool(self.sdf_net.normalize_weights),
+                              residual=self.residual_loss_factor > 0)
         cells = self._cached_cells(macro_features, x, mask, hidden, opts)
-        l_c, l_u, pr, w, sharpe, hn, cn = Fn.GanStepFn.apply(
+        l_c, l_u, pr, w, sharpe, hn, cn, l_res = Fn.GanStepFn.apply(
             opts, cells, k.macro, x, returns, mask, h0, c0, k.a_in, k.c_in, k.q_in, *k.params)
         zero = self._zero(dev)
         if phase == 'unconditional':            # src/model.py:524-528
@@ -344,6 +344,10 @@ class AssetPricingGAN(nn.Module):
             loss_unc, loss_cond, total = zero, l_c, -l_c
         else:                                   # src/model.py:537-541
             loss_unc, loss_cond, total = l_u, l_c, l_c
+        if self.residual_loss_factor > 0:       # src/model.py:543-548
+            total = total + self.residual_loss_factor * l_res
+        else:
+            l_res = zero
         new_hidden = (hn.view(1, 1, H), cn.view(1, 1, H)) if with_macro else None
 
         def moments():
@@ -358,7 +362,7 @@ class AssetPricingGAN(nn.Module):
 
         return StepOutputs({
             'weights': w, 'loss': total, 'loss_unconditional': loss_unc, 'loss_conditional': loss_cond,
-            'loss_residual': zero, 'sharpe': sharpe, 'portfolio_returns': pr, 'hidden': new_hidden,
+            'loss_residual': l_res, 'sharpe': sharpe, 'portfolio_returns': pr, 'hidden': new_hidden,
         }, moments_fn=moments)
 
     def graphed_step(self, macro_features, individual_features, returns, mask, hidden=None,
@@ -501,10 +505,11 @@ class GraphedStep:
             if apply and self.optimizer is not None:
                 self.optimizer.step(self.max_norm)
                 # what an epoch reports (src/train.py:96-103), packed for ONE device-to-host copy:
-                # loss, L_u, L_c, gradient norm, then the T portfolio returns
+                # loss, L_u, L_c, gradient norm, residual loss, then the T portfolio returns
                 with torch.no_grad():
                     self.report = torch.cat([torch.stack([out['loss'], out['loss_unconditional'],
-                                                          out['loss_conditional'], self.optimizer.grad_norm[0]]),
+                                                          out['loss_conditional'], self.optimizer.grad_norm[0],
+                                                          out['loss_residual']]),
                                              out['portfolio_returns']])
         finally:
             self.model._seed_dev = None

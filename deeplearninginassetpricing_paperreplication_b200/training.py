@@ -191,8 +191,8 @@ def train_epoch(model, optimizer, data: dict, device: torch.device, phase: str =
     pinned.copy_(gs.report, non_blocking=True)        # the graph packed the epoch's numbers (GraphedStep.report)
     torch.cuda.current_stream(device).synchronize()
     vals = pinned.numpy()
-    pr = vals[4:].astype(np.float64)
+    pr = vals[5:].astype(np.float64)
     std = pr.std(ddof=1) if pr.size > 1 else float('nan')
     sharpe = 0.0 if std < 1e-8 else float(pr.mean() / std)          # compute_sharpe, src/train.py:29-34
-    return {'loss': float(vals[0]), 'loss_unc': float(vals[1]), 'loss_cond': float(vals[2]), 'loss_residual': 0.0,
+    return {'loss': float(vals[0]), 'loss_unc': float(vals[1]), 'loss_cond': float(vals[2]), 'loss_residual': float(vals[4]),
             'sharpe': sharpe, 'grad_norm': float(vals[3])}

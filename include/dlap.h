@@ -299,13 +299,18 @@ int dlap_loss_finish_noalloc(const dlap_plan* plan, const double* col_part, int 
  * want_sdf / want_mom select the parameter groups (requires_grad semantics of src/train.py:309-312).
  * mio: a_t, c_t, month0, month_stride as for dlap_cell_fwd (nothing else is read).
  * Outputs: wpart (per-CTA weight-gradient partials), dadc_part (per-tile da_t | dc_t).
- * index, x_image: as for dlap_cell_fwd. */
+ * index, x_image: as for dlap_cell_fwd.
+ * res_b, u_fwd (both NULL: off): the gradient of the residual-loss regulariser (compute_residual_loss,
+ * src/model.py:435-483, added to the loss at :543-548).  With w = m (u - mu_t) and beta_t = R.w / w.w it reaches u as
+ * a_t (R - Rbar_t) + res_b[t] (u - mu_t): the caller adds a_t to dpr_cot (divided by N_bar / N_t when weighted_loss)
+ * and passes res_b [T] and the forward's u (left-packed for BF16X3, dense for FP32). */
 int dlap_cell_bwd(const dlap_plan* plan, const float* x, const float* R, const uint8_t* mask,
                   const int32_t* index, const void* x_image, const dlap_tensors* params, const dlap_macro_io* mio,
                   const float* row_stats, const double* dS2, const float* gc, const float* gu,
                   const float* dpr_cot, const float* G, const float* scalars, int weighted_loss, int want_sdf,
                   int want_mom, float* wpart, float* dadc_part, int precision, float dropout_p,
-                  uint64_t dropout_seed, const uint64_t* dropout_seed_dev, void* stream);
+                  uint64_t dropout_seed, const uint64_t* dropout_seed_dev, const float* res_b, const float* u_fwd,
+                  void* stream);
 
 /* Fixed-order sum of the partials into the reference's gradient layouts: grads->w1[:, :F], w2, b2,
  * w3, b3 (= 0, demeaning), wq[:, M:]; and da_t | dc_t summed over stocks: row t of the panel goes to row

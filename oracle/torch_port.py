@@ -146,9 +146,30 @@ def conditional_loss(w, R, mask, q, weighted_loss: bool = True):
     return torch.stack(per_k).mean(), pr
 
 
+def residual_loss(w, R, mask):
+    """compute_residual_loss (src/model.py:435-483): per month with at least two listed stocks, the mean squared
+    residual of the returns after projecting them on the weights (months whose weights vanish are left out of the
+    numerator only), over the mean squared return."""
+    res, rsq = [], []
+    for t in range(w.shape[0]):
+        valid = mask[t].float() > 0                                            # :455-459
+        if valid.sum() < 2:
+            continue
+        wv, rv = w[t][valid], R[t][valid]
+        ww = (wv * wv).sum()                                                   # :464-470
+        if ww > 1e-8:
+            rhat = ((rv * wv).sum() / ww) * wv
+            res.append(((rv - rhat) ** 2).mean())
+        rsq.append((rv ** 2).mean())                                           # :472
+    if len(res) == 0:                                                          # :474-475
+        return torch.tensor(0.0, device=w.device)
+    return torch.stack(res).mean() / torch.stack(rsq).mean().clamp(min=1e-8)   # :477-480
+
+
 def forward(params, macro, x, R, mask, hidden=None, phase: str = "conditional",
-            weighted_loss: bool = True, normalize_w: bool = True) -> Dict[str, torch.Tensor]:
-    """AssetPricingGAN.forward (src/model.py:485-563) with ``residual_loss_factor == 0``."""
+            weighted_loss: bool = True, normalize_w: bool = True,
+            residual_loss_factor: float = 0.0) -> Dict[str, torch.Tensor]:
+    """AssetPricingGAN.forward (src/model.py:485-563)."""
     w, new_hidden = sdf_weights(params, macro, x, mask, hidden, normalize_w)
     q = moment_conditions(params, macro, x)
     zero = torch.zeros((), device=x.device)
@@ -162,9 +183,13 @@ def forward(params, macro, x, R, mask, hidden=None, phase: str = "conditional",
         l_c, pr = conditional_loss(w, R, mask, q, weighted_loss)
         l_u, _ = unconditional_loss(w, R, mask, weighted_loss)
         total = l_c
+    l_res = zero
+    if residual_loss_factor > 0:                                               # :543-548
+        l_res = residual_loss(w, R, mask)
+        total = total + residual_loss_factor * l_res
     sharpe = pr.mean() / (pr.std() + 1e-8)                                     # :551
     return {"weights": w, "loss": total, "loss_unconditional": l_u, "loss_conditional": l_c,
-            "loss_residual": zero, "sharpe": sharpe, "portfolio_returns": pr,
+            "loss_residual": l_res, "sharpe": sharpe, "portfolio_returns": pr,
             "hidden": new_hidden, "moments": q}
 
 
@@ -180,14 +205,14 @@ def normalized_weights(params, macro, x, mask, hidden=None):
 
 
 def step(params, macro, x, R, mask, phase: str = "conditional", hidden=None,
-         grad_keys: Optional[Tuple[str, ...]] = None):
+         grad_keys: Optional[Tuple[str, ...]] = None, **forward_kw):
     """One forward + backward the way train_epoch drives it (src/train.py:77-84): returns the
     forward dict (detached) and the gradient of ``loss`` for every key in ``grad_keys``
     (default: all twelve; the caller freezes groups by passing a subset, mirroring
     ``requires_grad=False`` at src/train.py:309-312)."""
     keys = PARAM_KEYS if grad_keys is None else tuple(grad_keys)
     live = {k: (v.detach().clone().requires_grad_(k in keys)) for k, v in params.items()}
-    out = forward(live, macro, x, R, mask, hidden=hidden, phase=phase)
+    out = forward(live, macro, x, R, mask, hidden=hidden, phase=phase, **forward_kw)
     out["loss"].backward()
     grads = {k: (live[k].grad if live[k].grad is not None else None) for k in keys}
     det = {}

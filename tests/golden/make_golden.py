@@ -28,6 +28,8 @@ Cases
                 ``get_date_count_list`` and ``create_small_sample`` -- `python make_golden.py loader` writes only this.
                 Bit-exact contract for the device-side loader.
   anchors       scalars of the full shipped training panel.
+  v_residual    residual_loss_factor = 0.25 (src/model.py:435-483): the regulariser on the weights, a month with one
+                listed stock -- `python make_golden.py residual` writes only this.
   v_*           config variants: the notebooks' [64,32] / use_rnn=False / hidden_dim_moment=[32],
                 normalize_w=False, narrow hidden layers with weighted_loss=False -- `python make_golden.py variants`
                 writes only these.
@@ -69,7 +71,7 @@ def run_case(name, macro, x, R, mask, seed, hidden=None, cfg_extra=None):
             prm.requires_grad = not frozen
         out = model(macro, x, R, mask, hidden=hidden, phase=phase)
         out["loss"].backward()
-        for key in ("weights", "loss", "loss_unconditional", "loss_conditional", "sharpe",
+        for key in ("weights", "loss", "loss_unconditional", "loss_conditional", "loss_residual", "sharpe",
                     "portfolio_returns"):
             blob[f"{phase}/{key}"] = out[key].detach().numpy().copy()
         if out["hidden"] is not None:
@@ -126,6 +128,25 @@ def variants():
     macro = torch.randn(T, M, generator=g)
     for i, (name, extra) in enumerate(VARIANTS.items()):
         run_case(name, macro, x, R, mask, seed=100 + i, cfg_extra=extra)
+
+
+def residual_case():
+    """residual_loss_factor > 0 (src/model.py:435-483, :543-548) on the variants' panel, with one month left with a
+    single listed stock (skipped by the `valid.sum() < 2` rule) next to the empty one -- `python make_golden.py
+    residual` writes only this."""
+    g = torch.Generator().manual_seed(77)
+    T, N, F, M = 10, 150, 46, 8
+    mask = torch.rand(T, N, generator=g) < 0.45
+    mask[6, :] = False
+    mask[:, 11] = False
+    x = torch.randn(T, N, F, generator=g).clamp_(-2, 2)
+    R = 0.1 * torch.randn(T, N, generator=g)
+    macro = torch.randn(T, M, generator=g)
+    mask[3, :] = False
+    mask[3, 42] = True
+    x = x * mask[:, :, None]
+    R = R * mask
+    run_case("v_residual", macro, x, R, mask, seed=131, cfg_extra={"residual_loss_factor": 0.25})
 
 
 def shipped():
@@ -239,8 +260,11 @@ if __name__ == "__main__":
         variants()
     elif sys.argv[1:] == ["loader"]:
         loader()
+    elif sys.argv[1:] == ["residual"]:
+        residual_case()
     else:
         loader()
+        residual_case()
         rand_small()
         shipped()
         variants()

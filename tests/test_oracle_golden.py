@@ -75,6 +75,26 @@ def test_torch_port_matches_reference(golden, phase):
     assert seen >= 2
 
 
+@pytest.mark.parametrize("phase", PHASES)
+def test_torch_port_residual_loss_matches_reference(phase):
+    """residual_loss_factor = 0.25 (src/model.py:435-483, :543-548) on a panel with an empty month and a month with a
+    single listed stock: the port against the reference's own numbers, gradients included."""
+    torch.set_num_threads(1)
+    g = load_golden("v_residual")
+    params, macro, x, R, mask, hidden = _inputs(g)
+    keys = tp.MOMENT_KEYS if phase == "moment" else tp.PARAM_KEYS
+    out, grads = tp.step(params, macro, x, R, mask, phase=phase, hidden=hidden, grad_keys=keys,
+                         residual_loss_factor=0.25)
+    for key in ("weights", "loss", "loss_unconditional", "loss_conditional", "loss_residual", "portfolio_returns"):
+        assert _same(out[key].numpy(), g[f"{phase}/{key}"]), key
+    assert float(out["loss_residual"]) > 0.5
+    for k in keys:
+        if f"{phase}/grad/{k}" not in g:                    # phase 1 never touches the moment network
+            assert grads[k] is None, k
+            continue
+        assert _same(grads[k].numpy(), g[f"{phase}/grad/{k}"]), k
+
+
 def test_torch_port_moments_and_normalized(golden):
     torch.set_num_threads(1)
     params, macro, x, R, mask, hidden = _inputs(golden)

@@ -642,7 +642,8 @@ def test_errors_are_loud():
         model(macro.to(d), x.to(d).double(), R.to(d), mask.to(d))
     with pytest.raises(ValueError):
         model(macro.to(d), x.to(d).transpose(0, 1), R.to(d), mask.to(d))
-    for cfg in ({"hidden_dim": [64, 64, 32]}, {"residual_loss_factor": 0.1}, {"num_units_rnn": [4, 4]}):
+    for cfg in ({"hidden_dim": [64, 64, 32]}, {"residual_loss_factor": 0.1, "normalize_w": False},
+                {"num_units_rnn": [4, 4]}):
         bad = AssetPricingGAN({"macro_feature_dim": 8, "individual_feature_dim": 46, **cfg}).to(d)
         with pytest.raises(NotImplementedError):
             bad(macro.to(d), x.to(d), R.to(d), mask.to(d))

@@ -14,7 +14,7 @@ from deeplearninginassetpricing_paperreplication_b200 import AssetPricingGAN
 from test_parity_gpu import LOSS_RTOL, WEIGHT_TOL, _np, dev
 
 pytestmark = pytest.mark.gpu
-VARIANTS = ["v_notebook", "v_6432", "v_norm_off", "v_no_rnn", "v_mom_hidden", "v_narrow"]
+VARIANTS = ["v_notebook", "v_6432", "v_norm_off", "v_no_rnn", "v_mom_hidden", "v_narrow", "v_residual"]
 
 
 def _model(g, precision):
@@ -38,7 +38,10 @@ def test_variant_step_matches_the_reference(name, phase, precision):
     out = model(macro, x, R, mask, phase=phase)
     out["loss"].backward()
     torch.cuda.synchronize()
-    for key in ("loss", "loss_unconditional", "loss_conditional"):
+    for key in ("loss", "loss_unconditional", "loss_conditional", "loss_residual"):
+        if f"{phase}/{key}" not in g:                        # goldens older than the residual loss: it is zero there
+            assert float(out[key]) == 0.0
+            continue
         a, b = float(out[key]), float(g[f"{phase}/{key}"])
         assert abs(a - b) <= LOSS_RTOL * abs(b) + 1e-30, (key, a, b)
     w = _np(out["weights"])
@@ -89,12 +92,40 @@ def test_variant_inference_matches_the_reference(name, precision):
     assert rel_err(_np(out["moments"]), g["moments"]) < 1e-4
 
 
+@pytest.mark.parametrize("precision", ["fp32", "bf16x3"])
+def test_residual_loss_in_a_graphed_epoch(precision):
+    """residual_loss_factor > 0 through GraphedStep + FusedClipAdam: the [T]-sized torch ops of the regulariser are part
+    of the capture; replays follow the eager model stepped by torch.optim.Adam, and the report carries the loss."""
+    from deeplearninginassetpricing_paperreplication_b200 import FusedClipAdam
+    g = load_golden("v_residual")
+    a, _ = _model(g, precision)
+    b, _ = _model(g, precision)
+    d = dev()
+    macro, x, R, mask = [torch.from_numpy(g[k]).to(d) for k in ("macro", "x", "R", "mask")]
+    ropt = torch.optim.Adam(a.sdf_net.parameters(), lr=1e-3)
+    opt = FusedClipAdam(b.sdf_net.parameters(), lr=1e-3)
+    gs = b.graphed_step(macro, x, R, mask, phase="conditional", optimizer=opt, max_norm=1.0)
+    for epoch in range(5):
+        ropt.zero_grad()
+        out = a(macro, x, R, mask, phase="conditional")
+        out["loss"].backward()
+        torch.nn.utils.clip_grad_norm_(a.sdf_net.parameters(), 1.0)
+        ropt.step()
+        got = gs.step()
+        torch.cuda.synchronize()
+        ref = float(out["loss"].detach())
+        assert abs(float(got["loss"].detach()) - ref) <= 2e-3 * abs(ref), epoch
+        rep = gs.report.cpu().numpy()
+        assert rep[4] == float(got["loss_residual"]) and rep[4] > 0.5
+        del out
+
+
 def test_still_unsupported_configurations_raise():
     d = dev()
     g = load_golden("v_6432")
     macro, x, R, mask = [torch.from_numpy(g[k]).to(d) for k in ("macro", "x", "R", "mask")]
-    for cfg in ({"hidden_dim": [64, 64, 64]}, {"hidden_dim": [128, 64]}, {"residual_loss_factor": 0.1},
-                {"num_units_rnn": [4, 4]}, {"num_condition_moment": 4}):
+    for cfg in ({"hidden_dim": [64, 64, 64]}, {"hidden_dim": [128, 64]}, {"num_units_rnn": [4, 4]},
+                {"num_condition_moment": 4}, {"residual_loss_factor": 0.1, "normalize_w": False}):
         bad = AssetPricingGAN({"macro_feature_dim": 8, "individual_feature_dim": 46, **cfg}).to(d)
         with pytest.raises(NotImplementedError):
             bad(macro, x, R, mask)
