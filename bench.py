@@ -403,7 +403,7 @@ def run_ours(args, rank, world):
                      "note": "achieved/peak/frac: 189 algorithmic bytes per stock-month of the DENSE panel per launch (x, R, "
                              "mask read once, SURVEY.md 8d) over the measured HBM copy peak, as the metric asks; the bf16x3 "
                              "kernels visit only the unmasked stock-months (valid_fraction; masked cells contribute exactly "
-                             "0), frac_visited_cells counts those alone and `traffic` is the real DRAM traffic per launch. "
+                             "0), frac_visited_cells counts those alone and `traffic` is the real DRAM traffic per launch (with X images the kernel reads 193.5 B per visited stock-month instead of gathering 184-byte rows). "
                              "What binds is the tensor pipe (138 FLOP/B): tensor_frac = issued bf16 MMA work (3 x 36.9 "
                              "kFLOP per visited stock-month) over the sustained dense bf16 peak of MEASURED_PEAKS.json; "
                              "step_frac_per_gpu = whole step at 378 B per stock-month, per GPU"},

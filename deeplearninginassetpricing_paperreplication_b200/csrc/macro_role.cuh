@@ -31,7 +31,6 @@ struct MacroParams {
   const float* dadc;    // [T,72]  da_t (64) | dc_t (8), summed over stocks
   float* dpre;          // [T,4H] scratch: LSTM pre-activation gradients
   int have_sdf, have_mom;
-  int wgrad_staged;     // macro_wgrad: h_t / da_t staged in shared memory (fits for T up to ~600)
   float* gWih; float* gWhh; float* gbih; float* gbhh;   // LSTM grads
   float* gW1;           // [64, ldw1]  (columns F.. written here)
   float* gb1;           // [64]
