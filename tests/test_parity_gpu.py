@@ -426,6 +426,23 @@ def test_step_vs_oracle_shapes(T, N, M, phase):
     _check_against_cf(model, macro, x, R, mask, phase)
 
 
+@pytest.mark.parametrize("precision", ["fp32", "bf16x3"])
+def test_series_longer_than_256_months(precision):
+    """T = 300: the month-summed gradients walk the series in sweeps of 256 months (macro_lstm.cu, wgrad_tasks: the
+    first sweep's operands are prefetched, later ones loaded on the spot), the BPTT scan's chunks are 19 months long,
+    and the LSTM publishes 19 groups.  fwd + bwd against the fp64 closed form; the frozen-SDF phase takes the
+    stand-alone month-summed-gradient kernel over the same series."""
+    T, N, M = 300, 70, 8
+    macro, x, R, mask = make_panel(T, N, M, seed=300)
+    mask[7] = False
+    x = x * mask[:, :, None]; R = R * mask
+    torch.manual_seed(5)
+    model = AssetPricingGAN({"b200_precision": precision, "macro_feature_dim": M, "individual_feature_dim": 46}).to(dev()).eval()
+    tol = GRAD_TOL if precision == "fp32" else 4e-2
+    for phase in ("conditional", "moment"):
+        _check_against_cf(model, macro, x, R, mask, phase, grad_tol=tol)
+
+
 def test_no_macro_and_other_feature_counts():
     for F in (46, 13, 64):
         _, x, R, mask = make_panel(6, 200, 0, F=F, seed=F)
