@@ -105,17 +105,61 @@ __global__ void __launch_bounds__(256) weights_kernel(
     const size_t vi = index ? base + __ldg(rank + (i >> 5)) + __popc(b & ((1u << lane) - 1u)) : base + i;
     return __ldg(u + vi);
   };
-  double su = 0.0, cnt = 0.0;
-  if (index) {                                   // the month's listed cells are contiguous in u
-    const int c = index[idx_off_cnt(T) + t];
-    for (int j = threadIdx.x; j < c; j += blockDim.x) su += (double)__ldg(u + base + j);
-    cnt = threadIdx.x == 0 ? (double)c : 0.0;
-  } else {
-    for (int i0 = 0; i0 < N; i0 += blockDim.x) {
-      bool live;
-      const float v = u_at(i0 + threadIdx.x, live);
-      if (live) { su += (double)v; cnt += 1.0; }
+  if (index) {
+    // u is left-packed: the month's listed cells are the contiguous run u[base .. base + c).  Everything is a pass over
+    // that run with several loads in flight -- the mean, the sum of |u - mu|, and the weights themselves, scattered to
+    // their stocks (vidx) over a row that was zero-filled first (the barrier orders the two stores to a listed cell).
+    // No mask byte, rank word or ballot per stock: the stock-by-stock loop below needed three dependent round trips for
+    // each of its 3 x N / 256 iterations (measured at the paper shape: 60 us; this form: see DESIGN.md 4.2).
+    const int c = __ldg(index + idx_off_cnt(T) + t);
+    const float* ur = u + base;
+    const int* vrow = index + idx_off_vidx(T) + base;
+    float4* z4 = reinterpret_cast<float4*>(w_out + base);
+    const bool al = (reinterpret_cast<uintptr_t>(w_out + base) & 15) == 0;
+    if (al) {
+      for (int i = threadIdx.x; i < (N >> 2); i += blockDim.x) z4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int i = (N & ~3) + threadIdx.x; i < N; i += blockDim.x) w_out[base + i] = 0.f;
+    } else {
+      for (int i = threadIdx.x; i < N; i += blockDim.x) w_out[base + i] = 0.f;
     }
+    double su = 0.0;
+#pragma unroll 8
+    for (int j = threadIdx.x; j < c; j += blockDim.x) su += (double)__ldg(ur + j);
+    su = block_sum(su, red);
+    const float mu = demean ? (float)(su / fmax((double)c, 1.0)) : 0.f;
+    float denom = 1.f;
+    if (normalized) {
+      double s = 0.0;
+#pragma unroll 8
+      for (int j = threadIdx.x; j < c; j += blockDim.x) s += (double)fabsf(__ldg(ur + j) - mu);
+      s = block_sum(s, red);
+      denom = fmaxf((float)s, 1e-8f);
+    }
+    __syncthreads();                             // the zero-fill before the listed cells' values
+    for (int j0 = threadIdx.x; j0 < c; j0 += 8 * blockDim.x) {
+      int ii[8];
+      float uu[8];
+#pragma unroll
+      for (int b = 0; b < 8; ++b) {
+        const int j = min(j0 + b * (int)blockDim.x, c - 1);
+        ii[b] = __ldg(vrow + j);
+        uu[b] = __ldg(ur + j);
+      }
+#pragma unroll
+      for (int b = 0; b < 8; ++b) {
+        if (j0 + b * (int)blockDim.x < c) {
+          const float w = uu[b] - mu;
+          w_out[base + ii[b]] = normalized ? w / denom : w;
+        }
+      }
+    }
+    return;
+  }
+  double su = 0.0, cnt = 0.0;
+  for (int i0 = 0; i0 < N; i0 += blockDim.x) {
+    bool live;
+    const float v = u_at(i0 + threadIdx.x, live);
+    if (live) { su += (double)v; cnt += 1.0; }
   }
   su = block_sum(su, red);
   cnt = block_sum(cnt, red);
