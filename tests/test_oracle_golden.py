@@ -95,6 +95,31 @@ def test_torch_port_residual_loss_matches_reference(phase):
         assert _same(grads[k].numpy(), g[f"{phase}/grad/{k}"]), k
 
 
+def test_residual_terms_value_and_gradient_on_cpu():
+    """functional.residual_terms (the host-side part of residual_loss_factor > 0: [T]-sized torch ops, device-agnostic)
+    against the port of compute_residual_loss: the value, and c_t (R - beta_t w) against autograd's dL/dw -- an empty
+    month, a month with one listed stock (skipped), a month whose weights vanish (denominator only)."""
+    from deeplearninginassetpricing_paperreplication_b200 import functional as Fn
+    torch.manual_seed(0)
+    T, N = 9, 40
+    mask = torch.rand(T, N) < 0.5
+    mask[2] = False
+    mask[4] = False; mask[4, 3] = True
+    w = torch.randn(T, N) * 0.01 * mask
+    w[6] = 0.0
+    w.requires_grad_(True)
+    R = torch.randn(T, N) * 0.1 * mask
+    loss = tp.residual_loss(w, R, mask)
+    loss.backward()
+    got, c, beta = Fn.residual_terms(w.detach(), R, mask)
+    assert abs(float(got) - float(loss.detach())) <= 1e-6 * float(loss.detach())
+    g = (c[:, None] * (R.double() - beta[:, None] * w.detach().double())) * mask
+    assert float((g - w.grad.double()).abs().max()) <= 1e-6 * float(w.grad.abs().max())
+    assert float(c[2]) == 0.0 and float(c[4]) == 0.0 and float(c[6]) == 0.0
+    none, c0, _ = Fn.residual_terms(torch.zeros(T, N), R, mask)          # no month with weights: the loss is 0
+    assert float(none) == 0.0 and not c0.any()
+
+
 def test_torch_port_moments_and_normalized(golden):
     torch.set_num_threads(1)
     params, macro, x, R, mask, hidden = _inputs(golden)
